@@ -1,0 +1,536 @@
+/*
+ * cvr_oracle.c -- CPU ORACLE (test infrastructure, NOT the product).
+ *
+ * Scalar restatement of the arithmetic the reference's dense stereo hot path
+ * performs.  The reference itself (asad-ahmed-pk/master-thesis, cv_reconstruct)
+ * only holds thin glue; the arithmetic lives in two un-vendored third-party
+ * libraries:
+ *   - OpenCV >= 4.1 (unpinned; cv_reconstruct/CMakeLists.txt:14), calib3d/imgproc:
+ *     cv::cvtColor, cv::StereoSGBM::compute, cv::medianBlur, cv::filterSpeckles,
+ *     cv::normalize, cv::meanStdDev, cv::threshold, cv::reprojectImageTo3D.
+ *   - PCL >= 1.8 (unpinned; cv_reconstruct/CMakeLists.txt:24): pcl::VoxelGrid,
+ *     pcl::StatisticalOutlierRemoval.
+ *
+ * Pinning: the OpenCV half of this file is pinned against the real library
+ * (python cv2 4.13.0 in the build container) by tests/golden/make_golden.py ->
+ * tests/golden/ (npz files) and tests/test_oracle_golden.py.  The PCL half is a
+ * restatement of PCL's published algorithm (filters/impl/voxel_grid.hpp,
+ * filters/impl/statistical_outlier_removal.hpp); PCL is absent from the image
+ * and the reference's tests hold no golden vectors => PCL-half "parity unpinned".
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl
+ * reference legs may load this library.  The product (libcvrecon_b200.so)
+ * never links or calls it.
+ *
+ * Call sites restated (reference file:line):
+ *   gray        cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:78-79
+ *   sgbm        cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:39-69, :81
+ *   prune       cv_reconstruct/src/system/TrackingFrame.cpp:25-44, 47-67
+ *   reproject   cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:26-36, 106-153
+ *   triangulate cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:156-216
+ *   voxel       cv_reconstruct/src/system/MappingSystem.cpp:297-300, 72-75
+ *   sor         cv_reconstruct/src/point_cloud/PointCloudPostProcessor.cpp:20-24, 38-41
+ *
+ * Build: see oracle/Makefile (gcc -O2 -ffp-contract=off: the reference's CMake
+ * sets no -march/-mfma, so float expressions are evaluated without contraction).
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <math.h>
+#include <float.h>
+
+#define ORC_MAX_COST 32767
+#define ORC_DISP_SHIFT 4
+#define ORC_DISP_SCALE 16
+
+typedef struct orc_sgbm_params {
+    int minDisparity;
+    int numDisparities;
+    int blockSize;
+    int P1;
+    int P2;
+    int disp12MaxDiff;
+    int preFilterCap;
+    int uniquenessRatio;
+    int speckleWindowSize;
+    int speckleRange;
+    int mode;              /* 0 = MODE_SGBM (5 paths, one pass), 1 = MODE_HH (8 paths, two passes) */
+} orc_sgbm_params;
+
+static inline int16_t sat16(int v) { return (int16_t)(v > 32767 ? 32767 : (v < -32768 ? -32768 : v)); }
+static inline int imin(int a, int b) { return a < b ? a : b; }
+static inline int imax(int a, int b) { return a > b ? a : b; }
+
+/* ------------------------------------------------------------------------- */
+/* cv::cvtColor(BGR2GRAY), 8-bit: (3735 B + 19235 G + 9798 R + 2^14) >> 15.   */
+/* Reference call: Reconstruct3D.cpp:78-79.                                   */
+void orc_gray_bgr(const uint8_t* bgr, size_t step, int W, int H, int channels, uint8_t* gray, size_t gstep)
+{
+    for (int y = 0; y < H; y++) {
+        const uint8_t* s = bgr + (size_t)y * step;
+        uint8_t* g = gray + (size_t)y * gstep;
+        for (int x = 0; x < W; x++, s += channels)
+            g[x] = (uint8_t)((3735 * s[0] + 19235 * s[1] + 9798 * s[2] + 16384) >> 15);
+    }
+}
+
+/* ------------------------------------------------------------------------- */
+/* 3x3 median on int16, BORDER_REPLICATE (cv::medianBlur(disp, disp, 3) inside */
+/* StereoSGBM::compute).                                                      */
+void orc_median3_s16(const int16_t* src, int16_t* dst, int W, int H)
+{
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            int16_t v[9]; int n = 0;
+            for (int dy = -1; dy <= 1; dy++)
+                for (int dx = -1; dx <= 1; dx++) {
+                    int yy = imin(imax(y + dy, 0), H - 1), xx = imin(imax(x + dx, 0), W - 1);
+                    v[n++] = src[(size_t)yy * W + xx];
+                }
+            for (int i = 1; i < 9; i++) { int16_t t = v[i]; int j = i - 1; while (j >= 0 && v[j] > t) { v[j + 1] = v[j]; j--; } v[j + 1] = t; }
+            dst[(size_t)y * W + x] = v[4];
+        }
+}
+
+/* ------------------------------------------------------------------------- */
+/* cv::filterSpeckles(img, newVal, maxSpeckleSize, maxDiff): 4-connected       */
+/* components over pixels != newVal, edge iff |v(p)-v(q)| <= maxDiff; every    */
+/* component with size <= maxSpeckleSize is set to newVal.                    */
+void orc_filter_speckles(int16_t* img, int W, int H, int newVal, int maxSpeckleSize, int maxDiff)
+{
+    size_t N = (size_t)W * H;
+    int32_t* label = (int32_t*)calloc(N, sizeof(int32_t));
+    int32_t* stack = (int32_t*)malloc(N * sizeof(int32_t));
+    int32_t* members = (int32_t*)malloc(N * sizeof(int32_t));
+    int cur = 0;
+    for (size_t s = 0; s < N; s++) {
+        if (img[s] == newVal || label[s]) continue;
+        cur++;
+        int sp = 0, cnt = 0;
+        stack[sp++] = (int32_t)s; label[s] = cur;
+        while (sp) {
+            int32_t p = stack[--sp];
+            members[cnt++] = p;
+            int y = p / W, x = p % W; int v = img[p];
+            const int nx[4] = { x - 1, x + 1, x, x }, ny[4] = { y, y, y - 1, y + 1 };
+            for (int k = 0; k < 4; k++) {
+                if (nx[k] < 0 || nx[k] >= W || ny[k] < 0 || ny[k] >= H) continue;
+                int32_t q = ny[k] * W + nx[k];
+                if (label[q] || img[q] == newVal) continue;
+                if (abs(v - img[q]) > maxDiff) continue;
+                label[q] = cur; stack[sp++] = q;
+            }
+        }
+        if (cnt <= maxSpeckleSize)
+            for (int i = 0; i < cnt; i++) label[members[i]] = -1;  /* erase after the scan so values stay intact */
+    }
+    for (size_t s = 0; s < N; s++) if (label[s] == -1) img[s] = (int16_t)newVal;
+    free(label); free(stack); free(members);
+}
+
+/* ------------------------------------------------------------------------- */
+/* StereoSGBM::compute (MODE_SGBM / MODE_HH), SURVEY.md Appendix A.0-A.7.      */
+/* left/right: 8-bit single channel.  disp: int16 W*H (x16 fixed point).       */
+/* Optional stage outputs (may be NULL): C_out, S_out volumes [H][W1][D] int16 */
+/* and raw_out (disparity before median/speckle).  stats[0] receives the       */
+/* minimum path cost L seen, stats[1] the minimum C (order-independence guard).*/
+int orc_sgbm_compute(const uint8_t* left, size_t stepL, const uint8_t* right, size_t stepR,
+                     int W, int H, const orc_sgbm_params* prm,
+                     int16_t* disp, int16_t* raw_out, int16_t* C_out, int16_t* S_out, int* stats)
+{
+    const int minD = prm->minDisparity, D = prm->numDisparities, maxD = minD + D;
+    const int bs = prm->blockSize > 0 ? prm->blockSize : 5;
+    const int SW2 = bs / 2, SH2 = bs / 2;
+    const int uniq = prm->uniquenessRatio >= 0 ? prm->uniquenessRatio : 10;
+    const int d12 = prm->disp12MaxDiff > 0 ? prm->disp12MaxDiff : 1;
+    const int P1 = prm->P1 > 0 ? prm->P1 : 2;
+    const int P2 = imax(prm->P2 > 0 ? prm->P2 : 5, P1 + 1);
+    const int ftzero = imax(prm->preFilterCap, 15) | 1;
+    const int minX1 = imax(maxD, 0), maxX1 = W + imin(minD, 0), W1 = maxX1 - minX1;
+    const int INVALID = (minD - 1) * ORC_DISP_SCALE;
+    const int npasses = prm->mode == 1 ? 2 : 1;
+    int16_t* raw = (int16_t*)malloc((size_t)W * H * sizeof(int16_t));
+    for (size_t i = 0; i < (size_t)W * H; i++) raw[i] = (int16_t)INVALID;
+    int minLseen = 32767, minCseen = 32767;
+
+    if (W1 > 0 && D > 0) {
+        const size_t rowCells = (size_t)W1 * D, cells = rowCells * H;
+        int16_t* pix = (int16_t*)malloc(cells * sizeof(int16_t));
+        int16_t* hsum = (int16_t*)malloc(cells * sizeof(int16_t));
+        int16_t* C = (int16_t*)malloc(cells * sizeof(int16_t));
+        int16_t* S = (int16_t*)calloc(cells, sizeof(int16_t));
+
+        /* A.2 per-row pixel cost: BT on clipped x-Sobel + BT on raw intensity >> 2 */
+        int* gL = (int*)malloc(sizeof(int) * W * 4); int* gR = gL + W; int* rL = gR + W; int* rR = rL + W;
+        for (int y = 0; y < H; y++) {
+            int yn = imax(y - 1, 0), ys = imin(y + 1, H - 1);
+            const uint8_t *l0 = left + (size_t)y * stepL, *ln = left + (size_t)yn * stepL, *ls = left + (size_t)ys * stepL;
+            const uint8_t *r0 = right + (size_t)y * stepR, *rn = right + (size_t)yn * stepR, *rs = right + (size_t)ys * stepR;
+            for (int x = 0; x < W; x++) { gL[x] = gR[x] = rL[x] = rR[x] = ftzero; }   /* borders: tab(0), also for the raw channel */
+            for (int x = 1; x < W - 1; x++) {
+                int a = 2 * (l0[x + 1] - l0[x - 1]) + (ln[x + 1] - ln[x - 1]) + (ls[x + 1] - ls[x - 1]);
+                int b = 2 * (r0[x + 1] - r0[x - 1]) + (rn[x + 1] - rn[x - 1]) + (rs[x + 1] - rs[x - 1]);
+                gL[x] = imin(imax(a, -ftzero), ftzero) + ftzero;
+                gR[x] = imin(imax(b, -ftzero), ftzero) + ftzero;
+                rL[x] = l0[x]; rR[x] = r0[x];
+            }
+            int16_t* prow = pix + (size_t)y * rowCells;
+            for (int xp = 0; xp < W1; xp++) {
+                int x = xp + minX1;
+                for (int d = 0; d < D; d++) {
+                    int xr = x - (minD + d);
+                    int cost = 0;
+                    for (int ch = 0; ch < 2; ch++) {
+                        const int* a = ch ? rL : gL; const int* b = ch ? rR : gR;
+                        int u = a[x];
+                        int ul = x > 0 ? (u + a[x - 1]) / 2 : u, ur = x < W - 1 ? (u + a[x + 1]) / 2 : u;
+                        int u0 = imin(imin(ul, ur), u), u1 = imax(imax(ul, ur), u);
+                        int v = b[xr];
+                        int vl = xr > 0 ? (v + b[xr - 1]) / 2 : v, vr = xr < W - 1 ? (v + b[xr + 1]) / 2 : v;
+                        int v0 = imin(imin(vl, vr), v), v1 = imax(imax(vl, vr), v);
+                        int c0 = imax(0, imax(u - v1, v0 - u)), c1 = imax(0, imax(v - u1, u0 - v));
+                        cost += imin(c0, c1) >> (ch ? 2 : 0);
+                    }
+                    prow[(size_t)xp * D + d] = (int16_t)cost;
+                }
+            }
+        }
+        free(gL);
+
+        /* A.3 block aggregation, saturating int16 recurrences in exactly this order */
+        for (int y = 0; y < H; y++) {
+            const int16_t* prow = pix + (size_t)y * rowCells; int16_t* hrow = hsum + (size_t)y * rowCells;
+            for (int d = 0; d < D; d++) {
+                int h = sat16(prow[d] * (SW2 + 1));
+                for (int k = 1; k <= SW2; k++) h = sat16(h + prow[(size_t)imin(k, W1 - 1) * D + d]);
+                hrow[d] = (int16_t)h;
+                for (int xp = 1; xp < W1; xp++) {
+                    h = sat16(sat16(h - prow[(size_t)imax(xp - SW2 - 1, 0) * D + d]) + prow[(size_t)imin(xp + SW2, W1 - 1) * D + d]);
+                    hrow[(size_t)xp * D + d] = (int16_t)h;
+                }
+            }
+        }
+        for (size_t i = 0; i < rowCells; i++) {
+            int c = (int16_t)P2;
+            for (int k = 0; k <= SH2; k++) c = sat16(c + sat16(hsum[(size_t)imin(k, H - 1) * rowCells + i] * (k == 0 ? SH2 + 1 : 1)));
+            C[i] = (int16_t)c;
+            for (int y = 1; y < H; y++) {
+                c = sat16(sat16(c - hsum[(size_t)imax(y - SH2 - 1, 0) * rowCells + i]) + hsum[(size_t)imin(y + SH2, H - 1) * rowCells + i]);
+                C[(size_t)y * rowCells + i] = (int16_t)c;
+            }
+        }
+        for (size_t i = 0; i < cells; i++) if (C[i] < minCseen) minCseen = C[i];
+        free(pix); free(hsum);
+
+        /* A.4 path aggregation.  Lr[b][x'+1][r][d+1], d in [-1, D]; border columns x'=-1, x'=W1 stay 0. */
+        const int D2 = D + 2; const int16_t P1s = (int16_t)P1;
+        const size_t colStride = (size_t)4 * D2, rowStride = (size_t)(W1 + 2) * colStride;
+        int16_t* Lr = (int16_t*)malloc(2 * rowStride * sizeof(int16_t));
+        int16_t* minLr = (int16_t*)malloc(2 * (size_t)(W1 + 2) * 4 * sizeof(int16_t));
+        int16_t* disp2 = (int16_t*)malloc(sizeof(int16_t) * W); int16_t* disp2cost = (int16_t*)malloc(sizeof(int16_t) * W);
+#define LRP(b, xp, r) (Lr + (size_t)(b) * rowStride + (size_t)((xp) + 1) * colStride + (size_t)(r) * D2 + 1)
+#define MINLR(b, xp, r) (minLr[(size_t)(b) * (W1 + 2) * 4 + (size_t)((xp) + 1) * 4 + (r)])
+        for (int pass = 1; pass <= npasses; pass++) {
+            int y1, y2, dy, x1, x2, dx;
+            if (pass == 1) { y1 = 0; y2 = H; dy = 1; x1 = 0; x2 = W1; dx = 1; }
+            else { y1 = H - 1; y2 = -1; dy = -1; x1 = W1 - 1; x2 = -1; dx = -1; }
+            memset(Lr, 0, 2 * rowStride * sizeof(int16_t));
+            memset(minLr, 0, 2 * (size_t)(W1 + 2) * 4 * sizeof(int16_t));
+            int cur = 0;
+            for (int y = y1; y != y2; y += dy, cur ^= 1) {
+                const int prev = cur ^ 1;
+                const int16_t* Crow = C + (size_t)y * rowCells; int16_t* Srow = S + (size_t)y * rowCells;
+                for (int xp = x1; xp != x2; xp += dx) {
+                    const int16_t* Cp = Crow + (size_t)xp * D; int16_t* Sp = Srow + (size_t)xp * D;
+                    for (int r = 0; r < 4; r++) {
+                        int sb = r == 0 ? cur : prev;
+                        int sx = r == 0 ? xp - dx : (r == 1 ? xp - 1 : (r == 2 ? xp : xp + 1));
+                        int16_t* Lp = LRP(sb, sx, r);
+                        const int16_t delta = (int16_t)(P2 + MINLR(sb, sx, r));
+                        Lp[-1] = Lp[D] = ORC_MAX_COST;
+                        int16_t* Lc = LRP(cur, xp, r);
+                        int mn = ORC_MAX_COST;
+                        for (int d = 0; d < D; d++) {
+                            int m = imin(imin(Lp[d], sat16(Lp[d - 1] + P1s)), imin(sat16(Lp[d + 1] + P1s), delta));
+                            int L = sat16(sat16(m - delta) + Cp[d]);
+                            Lc[d] = (int16_t)L; mn = imin(mn, L);
+                            Sp[d] = sat16(Sp[d] + L);
+                        }
+                        MINLR(cur, xp, r) = (int16_t)mn;
+                        if (mn < minLseen) minLseen = mn;
+                    }
+                }
+                if (pass != npasses) continue;
+                /* A.5 WTA (+ the 5th, right-to-left path for MODE_SGBM) */
+                int16_t* drow = raw + (size_t)y * W;
+                for (int x = 0; x < W; x++) { disp2[x] = (int16_t)INVALID; disp2cost[x] = ORC_MAX_COST; }
+                for (int xp = W1 - 1; xp >= 0; xp--) {
+                    int16_t* Sp = Srow + (size_t)xp * D;
+                    if (npasses == 1) {
+                        const int16_t* Cp = Crow + (size_t)xp * D;
+                        int16_t* Lp = LRP(cur, xp + 1, 0);
+                        const int16_t delta = (int16_t)(P2 + MINLR(cur, xp + 1, 0));
+                        Lp[-1] = Lp[D] = ORC_MAX_COST;
+                        int16_t* Lc = LRP(cur, xp, 0);
+                        int mn = ORC_MAX_COST;
+                        for (int d = 0; d < D; d++) {
+                            int m = imin(imin(Lp[d], sat16(Lp[d - 1] + P1s)), imin(sat16(Lp[d + 1] + P1s), delta));
+                            int L = sat16(sat16(m - delta) + Cp[d]);
+                            Lc[d] = (int16_t)L; mn = imin(mn, L);
+                            Sp[d] = sat16(Sp[d] + L);
+                        }
+                        MINLR(cur, xp, 0) = (int16_t)mn;
+                        if (mn < minLseen) minLseen = mn;
+                    }
+                    int minS = ORC_MAX_COST, best = -1;
+                    for (int d = 0; d < D; d++) if (Sp[d] < minS) { minS = Sp[d]; best = d; }
+                    int d;
+                    for (d = 0; d < D; d++) if (Sp[d] * (100 - uniq) < minS * 100 && abs(best - d) > 1) break;
+                    if (d < D) continue;
+                    if (best < 0) continue;   /* equivalent to letting -1 through */
+                    int x2i = xp + minX1 - best - minD;
+                    if (disp2cost[x2i] > minS) { disp2cost[x2i] = (int16_t)minS; disp2[x2i] = (int16_t)(best + minD); }
+                    int dd;
+                    if (0 < best && best < D - 1) {
+                        int den = imax(Sp[best - 1] + Sp[best + 1] - 2 * Sp[best], 1);
+                        dd = best * ORC_DISP_SCALE + ((Sp[best - 1] - Sp[best + 1]) * ORC_DISP_SCALE + den) / (den * 2);
+                    } else dd = best * ORC_DISP_SCALE;
+                    drow[xp + minX1] = (int16_t)(dd + minD * ORC_DISP_SCALE);
+                }
+                for (int x = minX1; x < maxX1; x++) {
+                    int d1 = drow[x];
+                    if (d1 == INVALID) continue;
+                    int _d = d1 >> ORC_DISP_SHIFT, d_ = (d1 + ORC_DISP_SCALE - 1) >> ORC_DISP_SHIFT;
+                    int _x = x - _d, x_ = x - d_;
+                    if (0 <= _x && _x < W && disp2[_x] >= minD && abs(disp2[_x] - _d) > d12 &&
+                        0 <= x_ && x_ < W && disp2[x_] >= minD && abs(disp2[x_] - d_) > d12)
+                        drow[x] = (int16_t)INVALID;
+                }
+            }
+        }
+#undef LRP
+#undef MINLR
+        if (C_out) memcpy(C_out, C, cells * sizeof(int16_t));
+        if (S_out) memcpy(S_out, S, cells * sizeof(int16_t));
+        free(Lr); free(minLr); free(disp2); free(disp2cost); free(C); free(S);
+    }
+    if (raw_out) memcpy(raw_out, raw, (size_t)W * H * sizeof(int16_t));
+    /* A.6 post filters */
+    orc_median3_s16(raw, disp, W, H);
+    if (prm->speckleWindowSize > 0)
+        orc_filter_speckles(disp, W, H, INVALID, prm->speckleWindowSize, ORC_DISP_SCALE * prm->speckleRange);
+    if (stats) { stats[0] = minLseen; stats[1] = minCseen; }
+    free(raw);
+    return 0;
+}
+
+/* ------------------------------------------------------------------------- */
+/* TrackingFrame::SetupFrame / PruneDisparityImage (TrackingFrame.cpp:25-67),  */
+/* SURVEY A.8.  disp is modified in place (pruned pixels -> 0).               */
+/* out_stats (optional, 4 doubles): mn, mx, sigma, ithresh.                   */
+void orc_prune(int16_t* disp, int W, int H, float* dispf, uint8_t* mask, uint8_t* norm_u8_out, double* out_stats)
+{
+    size_t N = (size_t)W * H;
+    int mn = 32767, mx = -32768;
+    for (size_t i = 0; i < N; i++) { if (disp[i] < mn) mn = disp[i]; if (disp[i] > mx) mx = disp[i]; }
+    /* cv::normalize(NORM_MINMAX, 0..255) -> convertTo(CV_8U, scale, shift) */
+    double dmn = mn, dmx = mx;
+    double scale = (255.0 - 0.0) * (dmx - dmn > DBL_EPSILON ? 1.0 / (dmx - dmn) : 0.0);
+    double shift = 0.0 - dmn * scale;
+    float a = (float)scale, b = (float)shift;
+    uint8_t* u8 = (uint8_t*)malloc(N);
+    uint64_t sum = 0, sq = 0;
+    for (size_t i = 0; i < N; i++) {
+        float f = fmaf((float)disp[i], a, b);
+        long r = lrintf(f);                       /* round-half-even under the default rounding mode */
+        uint8_t v = (uint8_t)(r < 0 ? 0 : (r > 255 ? 255 : r));
+        u8[i] = v; sum += v; sq += (uint64_t)v * v;
+    }
+    double inv = 1.0 / (double)N;                 /* cv::meanStdDev: scale = 1./total; mean = s*scale; var = sq*scale - mean^2 */
+    double mean = (double)sum * inv;
+    double var = (double)sq * inv - mean * mean;
+    double sigma = sqrt(var > 0 ? var : 0);
+    double thr = sigma * 1.3;
+    int ithr = (int)floor(thr);
+    for (size_t i = 0; i < N; i++) {
+        uint8_t m = u8[i] > ithr ? 255 : 0;
+        if (!m) disp[i] = 0;
+        float f = (float)disp[i] * (1.0f / 16.0f);
+        if (f <= 0.0f) m = 0;
+        if (dispf) dispf[i] = f;
+        if (mask) mask[i] = m;
+    }
+    if (norm_u8_out) memcpy(norm_u8_out, u8, N);
+    if (out_stats) { out_stats[0] = mn; out_stats[1] = mx; out_stats[2] = sigma; out_stats[3] = ithr; }
+    free(u8);
+}
+
+/* ------------------------------------------------------------------------- */
+/* cv::reprojectImageTo3D(disp16S, Q, handleMissingValues=true), SURVEY A.9.   */
+/* xyz: float [H][W][3].                                                      */
+void orc_reproject(const int16_t* disp, int W, int H, const float* Q /*4x4 row-major f32*/, int handleMissing, float* xyz)
+{
+    double q[16]; for (int i = 0; i < 16; i++) q[i] = (double)Q[i];
+    double minDisp = FLT_MAX;
+    if (handleMissing) { int mn = 32767; for (size_t i = 0; i < (size_t)W * H; i++) if (disp[i] < mn) mn = disp[i]; minDisp = (double)mn; }
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            double d = (double)(float)disp[(size_t)y * W + x];
+            double h[4];
+            for (int i = 0; i < 4; i++) h[i] = q[i * 4 + 0] * x + q[i * 4 + 1] * y + q[i * 4 + 2] * d + q[i * 4 + 3];
+            float p0 = (float)h[0], p1 = (float)h[1], p2 = (float)h[2];
+            double iw = 1.0 / h[3];
+            p0 = (float)((double)p0 * iw); p1 = (float)((double)p1 * iw); p2 = (float)((double)p2 * iw);
+            if (fabs(d - minDisp) <= FLT_EPSILON) p2 = 10000.0f;
+            float* o = xyz + ((size_t)y * W + x) * 3; o[0] = p0; o[1] = p1; o[2] = p2;
+        }
+}
+
+/* 16-byte packed output point: x,y,z f32 + b,g,r,a bytes (a=255).             */
+typedef struct orc_point { float x, y, z; uint8_t b, g, r, a; } orc_point;
+
+/* Reconstruct3D::GeneratePointCloud (Reconstruct3D.cpp:106-153): reproject,   */
+/* skip Z == 10000, recentre, flip Y, then the diag(-1,1,1,1) transform.       */
+int orc_generate_point_cloud(const int16_t* disp, const uint8_t* bgr, size_t bstep, int W, int H, const float* Q, orc_point* out)
+{
+    float* xyz = (float*)malloc((size_t)W * H * 3 * sizeof(float));
+    orc_reproject(disp, W, H, Q, 1, xyz);
+    int n = 0;
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            const float* c = xyz + ((size_t)y * W + x) * 3;
+            if (c[2] == 10000.0f) continue;
+            orc_point p;
+            float px = c[0] - (W / 2.0f);
+            p.y = -(c[1] - (H / 2.0f));
+            p.z = c[2];
+            /* pcl::transformPointCloud with P = diag(-1,1,1,1): x' = -1*x + 0*y + 0*z + 0 (f32) */
+            p.x = -px;
+            const uint8_t* s = bgr + (size_t)y * bstep + (size_t)x * 3;
+            p.b = s[0]; p.g = s[1]; p.r = s[2]; p.a = 255;
+            out[n++] = p;
+        }
+    free(xyz);
+    return n;
+}
+
+/* Reconstruct3D::Triangulate3D (Reconstruct3D.cpp:156-216).                   */
+int orc_triangulate(const float* dispf, const uint8_t* bgr, size_t bstep, const uint8_t* mask, int W, int H,
+                    float f, float b, float cx, float cy, orc_point* out)
+{
+    int n = 0;
+    for (int i = 0; i < H; i++)
+        for (int j = 0; j < W; j++) {
+            float d = dispf[(size_t)i * W + j];
+            if (d <= 0.0) continue;
+            if (mask && mask[(size_t)i * W + j] == 0) continue;
+            orc_point p;
+            p.z = f * b / d;
+            p.x = ((float)j - cx) * (p.z / f);
+            p.y = -((float)i - cy) * (p.z / f);
+            const uint8_t* s = bgr + (size_t)i * bstep + (size_t)j * 3;
+            p.b = s[0]; p.g = s[1]; p.r = s[2]; p.a = 255;
+            out[n++] = p;
+        }
+    return n;
+}
+
+/* ------------------------------------------------------------------------- */
+/* pcl::VoxelGrid<PointXYZRGB>::applyFilter.             */
+/* Returns number of output points (ascending voxel index), or -1 when the     */
+/* index would overflow int32 (PCL warns and copies the input through; the     */
+/* caller gets the input copied to out and *passthrough = 1).                  */
+typedef struct { int32_t idx; int32_t pt; } orc_vkey;
+static int vkey_cmp(const void* a, const void* b)
+{
+    const orc_vkey* p = (const orc_vkey*)a; const orc_vkey* q = (const orc_vkey*)b;
+    if (p->idx != q->idx) return p->idx < q->idx ? -1 : 1;
+    return p->pt < q->pt ? -1 : (p->pt > q->pt);      /* make the (unstable in PCL) order deterministic: by point index */
+}
+int orc_voxel_grid(const orc_point* in, int n, float lx, float ly, float lz, orc_point* out, int* counts_out, int* passthrough)
+{
+    if (passthrough) *passthrough = 0;
+    if (n <= 0) return 0;
+    float mnx = FLT_MAX, mny = FLT_MAX, mnz = FLT_MAX, mxx = -FLT_MAX, mxy = -FLT_MAX, mxz = -FLT_MAX;
+    for (int i = 0; i < n; i++) {
+        if (in[i].x < mnx) mnx = in[i].x; if (in[i].x > mxx) mxx = in[i].x;
+        if (in[i].y < mny) mny = in[i].y; if (in[i].y > mxy) mxy = in[i].y;
+        if (in[i].z < mnz) mnz = in[i].z; if (in[i].z > mxz) mxz = in[i].z;
+    }
+    float ix = 1.0f / lx, iy = 1.0f / ly, iz = 1.0f / lz;
+    int64_t dx = (int64_t)((mxx - mnx) * ix) + 1, dy = (int64_t)((mxy - mny) * iy) + 1, dz = (int64_t)((mxz - mnz) * iz) + 1;
+    if (dx * dy * dz > (int64_t)INT32_MAX) {
+        memcpy(out, in, (size_t)n * sizeof(orc_point));
+        if (passthrough) *passthrough = 1;
+        return n;
+    }
+    int mbx = (int)floorf(mnx * ix), mby = (int)floorf(mny * iy), mbz = (int)floorf(mnz * iz);
+    int Mbx = (int)floorf(mxx * ix), Mby = (int)floorf(mxy * iy);
+    int divx = Mbx - mbx + 1, divy = Mby - mby + 1;
+    int mul1 = divx, mul2 = divx * divy;
+    orc_vkey* keys = (orc_vkey*)malloc((size_t)n * sizeof(orc_vkey));
+    for (int i = 0; i < n; i++) {
+        int ijk0 = (int)floorf(in[i].x * ix) - mbx, ijk1 = (int)floorf(in[i].y * iy) - mby, ijk2 = (int)floorf(in[i].z * iz) - mbz;
+        keys[i].idx = ijk0 + ijk1 * mul1 + ijk2 * mul2; keys[i].pt = i;
+    }
+    qsort(keys, (size_t)n, sizeof(orc_vkey), vkey_cmp);
+    int m = 0;
+    for (int s = 0; s < n;) {
+        int e = s; float sx = 0, sy = 0, sz = 0, sr = 0, sg = 0, sb = 0, sa = 0;
+        while (e < n && keys[e].idx == keys[s].idx) {
+            const orc_point* p = in + keys[e].pt;
+            sx += p->x; sy += p->y; sz += p->z; sr += (float)p->r; sg += (float)p->g; sb += (float)p->b; sa += (float)p->a;
+            e++;
+        }
+        float cnt = (float)(e - s);
+        orc_point o; o.x = sx / cnt; o.y = sy / cnt; o.z = sz / cnt;
+        o.r = (uint8_t)(sr / cnt); o.g = (uint8_t)(sg / cnt); o.b = (uint8_t)(sb / cnt); o.a = (uint8_t)(sa / cnt);
+        if (counts_out) counts_out[m] = e - s;
+        out[m++] = o; s = e;
+    }
+    free(keys);
+    return m;
+}
+
+/* ------------------------------------------------------------------------- */
+/* pcl::StatisticalOutlierRemoval, exact brute-force kNN. */
+/* dist_out (optional, n floats): mean distance to the k nearest neighbours.   */
+/* Returns kept count; out keeps input order.  thr_out: the mu + alpha*sigma.   */
+int orc_sor(const orc_point* in, int n, int k, double alpha, orc_point* out, float* dist_out, double* thr_out, uint8_t* keep_out)
+{
+    if (n <= 0) return 0;
+    float* dist = (float*)calloc((size_t)n, sizeof(float));
+    int kk = k + 1;                                   /* the query itself is among the results */
+    float* best = (float*)malloc(sizeof(float) * (size_t)kk);
+    int valid = 0;
+    for (int i = 0; i < n; i++) {
+        if (n < kk) { dist[i] = 0.0f; continue; }     /* nearestKSearch cannot return k+1 results */
+        int cnt = 0;
+        for (int j = 0; j < n; j++) {
+            float dx = in[i].x - in[j].x, dy = in[i].y - in[j].y, dz = in[i].z - in[j].z;
+            float d2 = dx * dx; d2 += dy * dy; d2 += dz * dz;
+            if (cnt < kk) { int p = cnt++; while (p > 0 && best[p - 1] > d2) { best[p] = best[p - 1]; p--; } best[p] = d2; }
+            else if (d2 < best[kk - 1]) { int p = kk - 1; while (p > 0 && best[p - 1] > d2) { best[p] = best[p - 1]; p--; } best[p] = d2; }
+        }
+        double s = 0; for (int j = 1; j < kk; j++) s += (double)sqrtf(best[j]);   /* skip j = 0: the nearest (itself / a duplicate) */
+        dist[i] = (float)(s / (double)k);
+        valid++;
+    }
+    double sum = 0, sq = 0;
+    for (int i = 0; i < n; i++) { sum += dist[i]; float pr = dist[i] * dist[i]; sq += pr; }   /* PCL: float product, double accumulation */
+    double mean = sum / (double)valid;
+    double var = (sq - sum * sum / (double)valid) / ((double)valid - 1.0);
+    double sd = sqrt(var);
+    double thr = mean + alpha * sd;
+    int m = 0;
+    for (int i = 0; i < n; i++) {
+        int keep = !((double)dist[i] > thr);
+        if (keep_out) keep_out[i] = (uint8_t)keep;
+        if (keep) out[m++] = in[i];
+    }
+    if (dist_out) memcpy(dist_out, dist, (size_t)n * sizeof(float));
+    if (thr_out) *thr_out = thr;
+    free(dist); free(best);
+    return m;
+}

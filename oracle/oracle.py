@@ -1,0 +1,210 @@
+"""ctypes binding of the CPU ORACLE (oracle/cvr_oracle.c) -- test infrastructure only.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.  The product library (libcvrecon_b200.so) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libcvr_oracle.so")
+
+MODE_SGBM = 0
+MODE_HH = 1
+
+
+class SgbmParams(C.Structure):
+    _fields_ = [(n, C.c_int) for n in (
+        "minDisparity", "numDisparities", "blockSize", "P1", "P2", "disp12MaxDiff", "preFilterCap",
+        "uniquenessRatio", "speckleWindowSize", "speckleRange", "mode")]
+
+
+POINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), ("g", "u1"), ("r", "u1"), ("a", "u1")])
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "cvr_oracle.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _SO
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        _lib = C.CDLL(_SO)
+        _lib.orc_sgbm_compute.restype = C.c_int
+        _lib.orc_generate_point_cloud.restype = C.c_int
+        _lib.orc_triangulate.restype = C.c_int
+        _lib.orc_voxel_grid.restype = C.c_int
+        _lib.orc_sor.restype = C.c_int
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def reference_sgbm_params(block_size=27, num_disparities=128, uniqueness_ratio=10, speckle_range=2,
+                          speckle_window_size=100, pre_filter_cap=10, min_disparity=0, mode=MODE_SGBM,
+                          disp12_max_diff=0):
+    """Parameter mapping of Reconstruct3D::ConfigureSteoreoMatcher (Reconstruct3D.cpp:54-64):
+    P1 = 8*3*bs^2, P2 = 32*3*bs^2, disp12MaxDiff untouched (0), mode untouched (MODE_SGBM)."""
+    return dict(minDisparity=int(min_disparity), numDisparities=int(num_disparities), blockSize=int(block_size),
+                P1=8 * 3 * block_size * block_size, P2=32 * 3 * block_size * block_size,
+                disp12MaxDiff=disp12_max_diff, preFilterCap=pre_filter_cap, uniquenessRatio=uniqueness_ratio,
+                speckleWindowSize=speckle_window_size, speckleRange=speckle_range, mode=mode)
+
+
+def gray_bgr(bgr):
+    bgr = np.ascontiguousarray(bgr, dtype=np.uint8)
+    H, W, ch = bgr.shape
+    out = np.empty((H, W), np.uint8)
+    lib().orc_gray_bgr(_p(bgr), C.c_size_t(W * ch), W, H, ch, _p(out), C.c_size_t(W))
+    return out
+
+
+def sgbm(left, right, params, stages=False):
+    """left/right: uint8 (H, W).  Returns disp int16 (H, W); with stages=True also a dict with
+    raw (pre-median), C, S volumes and (minL, minC) stats."""
+    left = np.ascontiguousarray(left, np.uint8)
+    right = np.ascontiguousarray(right, np.uint8)
+    H, W = left.shape
+    prm = SgbmParams(**params)
+    disp = np.empty((H, W), np.int16)
+    stats = (C.c_int * 2)()
+    if not stages:
+        lib().orc_sgbm_compute(_p(left), C.c_size_t(W), _p(right), C.c_size_t(W), W, H, C.byref(prm),
+                               _p(disp), None, None, None, stats)
+        return disp
+    minD, D = params["minDisparity"], params["numDisparities"]
+    W1 = (W + min(minD, 0)) - max(minD + D, 0)
+    raw = np.empty((H, W), np.int16)
+    Cv = np.zeros((H, max(W1, 0), D), np.int16)
+    Sv = np.zeros((H, max(W1, 0), D), np.int16)
+    lib().orc_sgbm_compute(_p(left), C.c_size_t(W), _p(right), C.c_size_t(W), W, H, C.byref(prm),
+                           _p(disp), _p(raw), _p(Cv), _p(Sv), stats)
+    return disp, dict(raw=raw, C=Cv, S=Sv, minL=stats[0], minC=stats[1])
+
+
+def median3(img):
+    img = np.ascontiguousarray(img, np.int16)
+    out = np.empty_like(img)
+    lib().orc_median3_s16(_p(img), _p(out), img.shape[1], img.shape[0])
+    return out
+
+
+def filter_speckles(img, new_val, max_size, max_diff):
+    out = np.ascontiguousarray(img, np.int16).copy()
+    lib().orc_filter_speckles(_p(out), out.shape[1], out.shape[0], int(new_val), int(max_size), int(max_diff))
+    return out
+
+
+def prune(disp):
+    """TrackingFrame::SetupFrame.  Returns (pruned int16, dispf f32, mask u8, norm u8, stats[mn,mx,sigma,ithr])."""
+    d = np.ascontiguousarray(disp, np.int16).copy()
+    H, W = d.shape
+    f = np.empty((H, W), np.float32)
+    m = np.empty((H, W), np.uint8)
+    u8 = np.empty((H, W), np.uint8)
+    st = np.zeros(4, np.float64)
+    lib().orc_prune(_p(d), W, H, _p(f), _p(m), _p(u8), _p(st))
+    return d, f, m, u8, st
+
+
+def reproject(disp, Q, handle_missing=True):
+    d = np.ascontiguousarray(disp, np.int16)
+    H, W = d.shape
+    Q = np.ascontiguousarray(Q, np.float32)
+    xyz = np.empty((H, W, 3), np.float32)
+    lib().orc_reproject(_p(d), W, H, _p(Q), int(bool(handle_missing)), _p(xyz))
+    return xyz
+
+
+def generate_point_cloud(disp, bgr, Q):
+    d = np.ascontiguousarray(disp, np.int16)
+    bgr = np.ascontiguousarray(bgr, np.uint8)
+    H, W = d.shape
+    Q = np.ascontiguousarray(Q, np.float32)
+    out = np.empty(H * W, POINT_DTYPE)
+    n = lib().orc_generate_point_cloud(_p(d), _p(bgr), C.c_size_t(W * 3), W, H, _p(Q), _p(out))
+    return out[:n].copy()
+
+
+def triangulate(dispf, bgr, mask, f, b, cx, cy):
+    d = np.ascontiguousarray(dispf, np.float32)
+    bgr = np.ascontiguousarray(bgr, np.uint8)
+    H, W = d.shape
+    if mask is not None:
+        mask = np.ascontiguousarray(mask, np.uint8)
+    out = np.empty(H * W, POINT_DTYPE)
+    n = lib().orc_triangulate(_p(d), _p(bgr), C.c_size_t(W * 3), _p(mask), W, H,
+                              C.c_float(f), C.c_float(b), C.c_float(cx), C.c_float(cy), _p(out))
+    return out[:n].copy()
+
+
+def voxel_grid(pts, leaf):
+    pts = np.ascontiguousarray(pts, POINT_DTYPE)
+    n = len(pts)
+    out = np.empty(max(n, 1), POINT_DTYPE)
+    counts = np.zeros(max(n, 1), np.int32)
+    pt = C.c_int(0)
+    lx, ly, lz = (leaf, leaf, leaf) if np.isscalar(leaf) else leaf
+    m = lib().orc_voxel_grid(_p(pts), n, C.c_float(lx), C.c_float(ly), C.c_float(lz), _p(out), _p(counts), C.byref(pt))
+    return out[:m].copy(), counts[:m].copy(), bool(pt.value)
+
+
+def sor(pts, k, alpha):
+    """Brute-force exact kNN statistical outlier removal.  Returns (kept points, mean dists, thr, keep mask)."""
+    pts = np.ascontiguousarray(pts, POINT_DTYPE)
+    n = len(pts)
+    out = np.empty(max(n, 1), POINT_DTYPE)
+    dist = np.zeros(max(n, 1), np.float32)
+    keep = np.zeros(max(n, 1), np.uint8)
+    thr = C.c_double(0)
+    m = lib().orc_sor(_p(pts), n, int(k), C.c_double(alpha), _p(out), _p(dist), C.byref(thr), _p(keep))
+    return out[:m].copy(), dist[:n].copy(), thr.value, keep[:n].copy()
+
+
+# --------------------------------------------------------------------------------------------
+# Synthetic rectified pair generator; numpy only, so it is identical wherever
+# it runs.  Used by tests, the golden generator and bench.py.
+def _blur121(a):
+    """separable 5-tap binomial-ish blur (sigma ~ 1.2) in integer arithmetic -> deterministic."""
+    k = np.array([1, 4, 6, 4, 1], np.int32)
+    a = a.astype(np.int32)
+    p = np.pad(a, ((0, 0), (2, 2)), mode="edge")
+    h = sum(k[i] * p[:, i:i + a.shape[1]] for i in range(5))
+    p = np.pad(h, ((2, 2), (0, 0)), mode="edge")
+    v = sum(k[i] * p[i:i + a.shape[0], :] for i in range(5))
+    return ((v + 128) >> 8).astype(np.uint8)
+
+
+def synth_pair(H, W, D, seed, color=False):
+    """Returns (left, right) uint8 gray (H, W), or BGR (H, W, 3) when color=True.
+    Ground-truth disparity d(y,x) = floor(0.15 D + 0.5 D y/H) + D/8 inside the central third."""
+    rng = np.random.default_rng(seed)
+    T = _blur121(rng.integers(0, 256, size=(H, W + D), dtype=np.uint8))
+    left = T[:, D:D + W]
+    yy, xx = np.mgrid[0:H, 0:W]
+    d = np.floor(0.15 * D + 0.5 * D * yy / H).astype(np.int64)
+    box = (yy >= H // 3) & (yy < 2 * H // 3) & (xx >= W // 3) & (xx < 2 * W // 3)
+    d = d + np.where(box, D // 8, 0)
+    xs = np.minimum(xx + d, W - 1)
+    # right(y, x - d) = left(y, x)  <=>  right(y, x) = T[y, D + x + d]  (scene shifted left in the right view)
+    right = np.take_along_axis(left, xs, axis=1)
+    left = np.ascontiguousarray(left)
+    right = np.ascontiguousarray(right)
+    if not color:
+        return left, right
+    n = rng.integers(-3, 4, size=(2, H, W, 3))
+    lb = np.clip(left[..., None].astype(np.int64) + n[0], 0, 255).astype(np.uint8)
+    rb = np.clip(right[..., None].astype(np.int64) + n[1], 0, 255).astype(np.uint8)
+    return lb, rb
