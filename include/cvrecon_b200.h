@@ -1,0 +1,164 @@
+/*
+ * cvrecon_b200.h -- C ABI of libcvrecon_b200.so: the dense per-frame stereo hot path of
+ * asad-ahmed-pk/master-thesis (cv_reconstruct) as hand-written sm_100a CUDA.
+ *
+ * The reference has no FFI/plugin interface; its boundary for this path is the C++ class
+ * Reconstruct::Reconstruct3D (cv_reconstruct/include/reconstruct/Reconstruct3D.hpp:25-103),
+ * TrackingFrame::SetupFrame (cv_reconstruct/src/system/TrackingFrame.cpp:25-67) and the PCL
+ * filter call sites.  Each entry point below names the reference interface it replaces.  A
+ * header-only C++ mirror of the reference class on top of this ABI is in
+ * master-thesis_b200/host/Reconstruct3D_b200.hpp; the binding a maintainer of the reference
+ * would add is shown in INTEGRATION.md.
+ *
+ * Conventions: plain pointers and sizes only; every function returns 0 on success or a
+ * negative cvr_status; no exception crosses the ABI; cvr_last_error() returns a message for the
+ * last failure on this context.  A context is NOT re-entrant (like the reference's matcher,
+ * whose compute() mutates internal buffers): one caller thread per context.  There is no CPU
+ * fallback: cvr_create fails when no sm_100-class device is usable.
+ *
+ * Image layout = cv::Mat: `data`, rows, cols, `step` bytes per row.  Disparity = CV_16SC1,
+ * value 16*d, invalid = (minDisparity-1)*16.  Points are 16-byte cvr_point (x,y,z f32 + b,g,r,a);
+ * cvr_points_to_pcl() expands to the 32-byte pcl::PointXYZRGB layout.
+ */
+#ifndef CVRECON_B200_H
+#define CVRECON_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct cvr_ctx cvr_ctx;
+
+typedef enum cvr_status {
+    CVR_OK = 0,
+    CVR_ERR_INVALID_ARG = -1,
+    CVR_ERR_UNSUPPORTED = -2,     /* parameter combination outside what the kernels implement */
+    CVR_ERR_CUDA = -3,
+    CVR_ERR_NO_DEVICE = -4,
+    CVR_ERR_CAPACITY = -5         /* caller's output buffer too small / batch larger than max_batch */
+} cvr_status;
+
+enum { CVR_MODE_SGBM = 0, CVR_MODE_HH = 1 };
+enum { CVR_MEM_HOST = 0, CVR_MEM_DEVICE = 1 };
+enum { CVR_CLOUD_TRIANGULATE = 0, CVR_CLOUD_REPROJECT = 1 };
+
+/* cv::StereoSGBM parameters exactly as Reconstruct3D::ConfigureSteoreoMatcher sets them
+ * (cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:50-64; JSON keys in
+ * cv_reconstruct/resources/config/config_default.json:13-21).  The reference computes
+ * P1 = 8*3*bs^2 and P2 = 32*3*bs^2 and leaves disp12MaxDiff = 0 and mode = MODE_SGBM. */
+typedef struct cvr_sgbm_params {
+    int min_disparity;
+    int num_disparities;        /* multiple of 16, <= 256 */
+    int block_size;             /* odd, >= 1 */
+    int P1;
+    int P2;
+    int disp12_max_diff;        /* 0 => OpenCV uses 1 */
+    int pre_filter_cap;         /* <= 63 */
+    int uniqueness_ratio;
+    int speckle_window_size;    /* 0 => speckle filter off */
+    int speckle_range;
+    int mode;                   /* CVR_MODE_SGBM | CVR_MODE_HH */
+} cvr_sgbm_params;
+
+typedef struct cvr_params {
+    int width, height;          /* frame size; fixed per context */
+    cvr_sgbm_params sgbm;
+    float Q[16];                /* row-major 4x4 for GeneratePointCloud (Reconstruct3D.cpp:31-35) */
+    float tri_f, tri_b, tri_cx, tri_cy;   /* Triangulate3D constants (Reconstruct3D.cpp:167-172) */
+    double prune_sigma_factor;  /* 1.3 (a double literal) in TrackingFrame.cpp:55 */
+    float voxel_leaf[3];        /* MappingSystem.cpp:299: 0.2 */
+    int   sor_mean_k;           /* config_default.json:24 outlier_min_k = 30 */
+    double sor_stddev_mul;      /* config_default.json:25 outlier_std_threshold = 0.5 */
+    int   max_batch;            /* frames in flight per cvr_process_batch call (workspace is sized for it) */
+    int   cloud_mode;           /* CVR_CLOUD_TRIANGULATE (live path) | CVR_CLOUD_REPROJECT */
+    int   max_points;           /* point capacity per frame for the cloud filters; 0 => width*height */
+    int   filter_only;          /* 1 => no stereo workspace: only cvr_voxel_grid / cvr_sor are usable */
+} cvr_params;
+
+typedef struct cvr_point {      /* 16 bytes */
+    float x, y, z;
+    uint8_t b, g, r, a;
+} cvr_point;
+
+/* Fills *p with the reference's defaults: config_default.json SGBM section + P1/P2 rule,
+ * Q = diag(1,1,0.005*f,1), KITTI calib (resources/calib/kitti/calib_kitti_rectified.json),
+ * leaf 0.2, SOR k=30 alpha=0.5, prune factor 1.3, max_batch 1. */
+void cvr_default_params(cvr_params* p, int width, int height);
+
+/* Replaces: Reconstruct3D::Reconstruct3D(stereoSetup, config) (Reconstruct3D.cpp:26-36) --
+ * allocates the device workspace once. */
+int cvr_create(const cvr_params* p, int device, cvr_ctx** out);
+int cvr_destroy(cvr_ctx* ctx);
+const char* cvr_last_error(const cvr_ctx* ctx);
+const char* cvr_version(void);
+
+/* Replaces: Reconstruct3D::GenerateDisparityMap (Reconstruct3D.cpp:72-84):
+ * cvtColor(BGR2GRAY) x2 + StereoSGBM::compute.  channels = 3 or 4 (BGR/BGRA, converted like
+ * cv::cvtColor) or 1 (already gray).  Host pointers. */
+int cvr_disparity(cvr_ctx* ctx, const uint8_t* left, size_t step_left, const uint8_t* right, size_t step_right,
+                  int channels, int16_t* disp, size_t step_disp);
+
+/* Replaces: TrackingFrame::SetupFrame + PruneDisparityImage (TrackingFrame.cpp:25-67).
+ * disp is pruned in place; disp_f32 (CV_32F, tight W*4 step) and mask (CV_8U, tight) are outputs
+ * and may be NULL. */
+int cvr_prune(cvr_ctx* ctx, int16_t* disp_inout, size_t step_disp, float* disp_f32, uint8_t* mask);
+
+/* Replaces: Reconstruct3D::GeneratePointCloud (Reconstruct3D.cpp:106-153):
+ * reprojectImageTo3D(disp, Q, true), skip Z == 10000, recentre, flip, BGR->RGB, x negated.
+ * Output order = row-major over surviving pixels.  *n_out receives the count. */
+int cvr_reproject_cloud(cvr_ctx* ctx, const int16_t* disp, size_t step_disp, const uint8_t* bgr, size_t step_bgr,
+                        cvr_point* out, int capacity, int* n_out);
+
+/* Replaces: Reconstruct3D::Triangulate3D (Reconstruct3D.cpp:156-216); mask may be NULL. */
+int cvr_triangulate(cvr_ctx* ctx, const float* disp_f32, size_t step_disp, const uint8_t* bgr, size_t step_bgr,
+                    const uint8_t* mask, size_t step_mask, cvr_point* out, int capacity, int* n_out);
+
+/* Replaces: pcl::VoxelGrid<PointXYZRGB>::filter at MappingSystem.cpp:297-300 (leaf from cvr_params).
+ * Output in ascending voxel index.  *passthrough = 1 when PCL would warn "leaf size too small"
+ * (int32 index overflow) and copy the input through. */
+int cvr_voxel_grid(cvr_ctx* ctx, const cvr_point* in, int n, cvr_point* out, int capacity, int* m_out, int* passthrough);
+
+/* Replaces: PointCloudPostProcessor::RemoveOutliers (PointCloudPostProcessor.cpp:38-41) =
+ * pcl::StatisticalOutlierRemoval with meanK / stddevMulThresh from cvr_params.  in == out allowed. */
+int cvr_sor(cvr_ctx* ctx, const cvr_point* in, int n, cvr_point* out, int capacity, int* kept_out);
+
+/* Frame-parallel fused path: for each of nframes frames
+ *   GenerateDisparityMap -> SetupFrame(prune) -> Triangulate3D|GeneratePointCloud -> VoxelGrid -> SOR
+ * (the per-frame chain of ReconstructionSystem::ProcessStereoFrame, ReconstructionSystem.cpp:35-61,
+ * plus the filter call sites).  Frame i of a buffer is at base + i*frame_stride bytes.  mem selects
+ * host or device pointers for ALL buffers of the call.  Optional outputs may be NULL. */
+typedef struct cvr_batch {
+    int mem;                        /* CVR_MEM_HOST | CVR_MEM_DEVICE */
+    int channels;                   /* 1, 3 or 4 */
+    const uint8_t* left;  size_t left_step,  left_frame_stride;
+    const uint8_t* right; size_t right_step, right_frame_stride;
+    int16_t* disp;        size_t disp_step,  disp_frame_stride;     /* optional: final disparity (pre-prune) */
+    cvr_point* cloud;     size_t cloud_capacity;                    /* per frame, in points; frame i at cloud + i*capacity */
+    int32_t* cloud_count;                                           /* [nframes] */
+    int stages;                     /* bit 0 disparity, 1 prune+cloud, 2 voxel, 3 sor; 0 => all */
+} cvr_batch;
+int cvr_process_batch(cvr_ctx* ctx, int nframes, const cvr_batch* io);
+
+/* Expands 16-byte points to pcl::PointXYZRGB (32 B: x,y,z,1.0f, b,g,r,a, 12 B pad).  Host side. */
+void cvr_points_to_pcl(const cvr_point* in, int n, void* pcl_points_32B);
+
+/* Test/inspection hooks (no reference counterpart): copy an intermediate of the most recent
+ * cvr_disparity call to host.  which: 0 = C volume, 1 = S volume (both int16 [H][W1][Dp]),
+ * 2 = raw disparity before median/speckle (int16 [H][W]).  *dp receives the padded D pitch. */
+int cvr_debug_fetch(cvr_ctx* ctx, int which, void* host_dst, size_t bytes, int* w1, int* dp);
+
+/* Number of kernel launches issued by this context since creation (bench.py's gpu_launches). */
+long long cvr_launch_count(const cvr_ctx* ctx);
+/* Device time (ms, CUDA events on the context's stream) of each stage of the last call, and the
+ * launch count of that call; names[i] are static strings.  Returns the number of stages written. */
+int cvr_last_timings(const cvr_ctx* ctx, const char** names, float* ms, int max_stages);
+/* Enable/disable per-stage event timing (adds event records between stages). */
+int cvr_set_profiling(cvr_ctx* ctx, int enable);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CVRECON_B200_H */

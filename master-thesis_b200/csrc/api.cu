@@ -1,0 +1,487 @@
+// api.cu -- the C ABI of libcvrecon_b200.so (include/cvrecon_b200.h): context, workspace, host<->device staging
+// and the per-stage / batched entry points.  No CPU fallback exists: without a usable sm_100-class device
+// cvr_create fails.
+#include "cvr_internal.cuh"
+#include <string.h>
+#include <stdlib.h>
+#include <new>
+
+static const char* kVersion = "cvrecon_b200 0.1 (sm_100a)";
+static thread_local std::string g_create_err;
+
+extern "C" const char* cvr_version(void) { return kVersion; }
+
+extern "C" void cvr_default_params(cvr_params* p, int width, int height)
+{
+    memset(p, 0, sizeof(*p));
+    p->width = width; p->height = height;
+    // config_default.json:13-21 + Reconstruct3D.cpp:63-64
+    p->sgbm.block_size = 27; p->sgbm.num_disparities = 128; p->sgbm.uniqueness_ratio = 10; p->sgbm.speckle_range = 2;
+    p->sgbm.speckle_window_size = 100; p->sgbm.pre_filter_cap = 10; p->sgbm.min_disparity = 0;
+    p->sgbm.P1 = 8 * 3 * 27 * 27; p->sgbm.P2 = 32 * 3 * 27 * 27; p->sgbm.disp12_max_diff = 0; p->sgbm.mode = CVR_MODE_SGBM;
+    // Reconstruct3D.cpp:31-35 with resources/calib/kitti/calib_kitti_rectified.json
+    const float fl = 959.791f, fr = 903.7596f, fyl = 956.9251f;
+    for (int i = 0; i < 16; i++) p->Q[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+    const float f = (fl + fr) / 2.0f;
+    p->Q[10] = (float)(0.005 * (double)f);
+    p->tri_f = (fl + fyl) / 2.0f; p->tri_b = 0.532671f; p->tri_cx = 696.0217f; p->tri_cy = 224.1806f;
+    p->prune_sigma_factor = 1.3;
+    p->voxel_leaf[0] = p->voxel_leaf[1] = p->voxel_leaf[2] = 0.2f;
+    p->sor_mean_k = 30; p->sor_stddev_mul = 0.5;
+    p->max_batch = 1; p->cloud_mode = CVR_CLOUD_TRIANGULATE; p->max_points = 0; p->filter_only = 0;
+}
+
+void cvr_stage_mark(cvr_ctx* c, const char* name)
+{
+    if (!c->profiling) return;
+    if (c->timers_used >= (int)c->timers.size()) {
+        StageTimer t; t.name = name; cudaEventCreate(&t.ev);
+        c->timers.push_back(t);
+    }
+    c->timers[c->timers_used].name = name;
+    cudaEventRecord(c->timers[c->timers_used].ev, c->stream);
+    c->timers_used++;
+}
+static void timers_begin(cvr_ctx* c) { c->timers_used = 0; cvr_stage_mark(c, "begin"); }
+static void timers_end(cvr_ctx* c)
+{
+    c->t_names.clear(); c->t_ms.clear();
+    if (!c->profiling) return;
+    for (int i = 1; i < c->timers_used; i++) {
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, c->timers[i - 1].ev, c->timers[i].ev);
+        c->t_names.push_back(c->timers[i].name); c->t_ms.push_back(ms);
+    }
+}
+
+template <typename T>
+static cudaError_t dalloc(T** p, size_t count) { *p = nullptr; if (count == 0) count = 1; return cudaMalloc((void**)p, count * sizeof(T)); }
+
+static int validate(const cvr_params* p, std::string& err)
+{
+    if (!p || p->width <= 0 || p->height <= 0) { err = "width/height must be positive"; return CVR_ERR_INVALID_ARG; }
+    if (p->width > 65535) { err = "width > 65535 unsupported"; return CVR_ERR_UNSUPPORTED; }
+    if (p->max_batch < 1) { err = "max_batch must be >= 1"; return CVR_ERR_INVALID_ARG; }
+    if (p->filter_only) return CVR_OK;
+    const cvr_sgbm_params& s = p->sgbm;
+    if (s.num_disparities <= 0 || s.num_disparities % 16 != 0) { err = "num_disparities must be a positive multiple of 16 (OpenCV rejects others)"; return CVR_ERR_INVALID_ARG; }
+    if (s.num_disparities > 256) { err = "num_disparities > 256 unsupported"; return CVR_ERR_UNSUPPORTED; }
+    if (s.block_size > 0 && s.block_size % 2 == 0) { err = "block_size must be odd"; return CVR_ERR_INVALID_ARG; }
+    if (s.pre_filter_cap > 63) { err = "pre_filter_cap > 63 unsupported"; return CVR_ERR_UNSUPPORTED; }
+    if (s.mode != CVR_MODE_SGBM && s.mode != CVR_MODE_HH) { err = "mode must be CVR_MODE_SGBM or CVR_MODE_HH"; return CVR_ERR_UNSUPPORTED; }
+    const int bs = s.block_size > 0 ? s.block_size : 5;
+    const int ftzero = (s.pre_filter_cap > 15 ? s.pre_filter_cap : 15) | 1;
+    // the horizontal block sum is evaluated in closed form, which equals OpenCV's saturating recurrence only
+    // while a row sum cannot reach 32767
+    if ((long long)bs * (2 * ftzero + 63) > 32767) { err = "block_size too large: horizontal block sum could saturate int16"; return CVR_ERR_UNSUPPORTED; }
+    if (s.min_disparity < -32000 / 16 || s.min_disparity + s.num_disparities > 32000 / 16) { err = "disparity range does not fit the x16 int16 output"; return CVR_ERR_INVALID_ARG; }
+    return CVR_OK;
+}
+
+static void fill_dev_params(cvr_ctx* c)
+{
+    const cvr_params& p = c->prm;
+    SgbmDev& g = c->sg;
+    memset(&g, 0, sizeof(g));
+    g.W = p.width; g.H = p.height; g.Wp = (p.width + 15) & ~15;
+    const cvr_sgbm_params& s = p.sgbm;
+    g.minD = s.min_disparity; g.D = s.num_disparities; g.Dp = ((g.D + 63) / 64) * 64;
+    g.bs = s.block_size > 0 ? s.block_size : 5; g.SW2 = g.SH2 = g.bs / 2;
+    const int P1 = s.P1 > 0 ? s.P1 : 2;
+    const int P2a = s.P2 > 0 ? s.P2 : 5;
+    const int P2 = P2a > P1 + 1 ? P2a : P1 + 1;
+    g.P1s = (int)(short)P1; g.P2 = P2; g.P2s = (int)(short)P2;
+    g.uniq = s.uniqueness_ratio >= 0 ? s.uniqueness_ratio : 10;
+    g.d12 = s.disp12_max_diff > 0 ? s.disp12_max_diff : 1;
+    g.ftzero = (s.pre_filter_cap > 15 ? s.pre_filter_cap : 15) | 1;
+    const int maxD = g.minD + g.D;
+    g.minX1 = maxD > 0 ? maxD : 0;
+    g.maxX1 = g.W + (g.minD < 0 ? g.minD : 0);
+    g.W1 = g.maxX1 - g.minX1;
+    g.INVALID = (g.minD - 1) * CVR_DISP_SCALE;
+    g.mode = s.mode;
+    g.ring = 1; while (g.ring < g.bs + 1) g.ring <<= 1;
+    CloudDev& cl = c->cl;
+    memcpy(cl.Q, p.Q, sizeof(cl.Q));
+    cl.f = p.tri_f; cl.b = p.tri_b; cl.cx = p.tri_cx; cl.cy = p.tri_cy;
+    cl.sigma_factor = p.prune_sigma_factor;
+    cl.leaf[0] = p.voxel_leaf[0]; cl.leaf[1] = p.voxel_leaf[1]; cl.leaf[2] = p.voxel_leaf[2];
+    cl.sor_k = p.sor_mean_k; cl.sor_alpha = p.sor_stddev_mul;
+}
+
+extern "C" const char* cvr_last_error(const cvr_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+extern "C" long long cvr_launch_count(const cvr_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int cvr_set_profiling(cvr_ctx* ctx, int enable) { if (!ctx) return CVR_ERR_INVALID_ARG; ctx->profiling = enable != 0; return CVR_OK; }
+extern "C" int cvr_last_timings(const cvr_ctx* ctx, const char** names, float* ms, int max_stages)
+{
+    if (!ctx) return 0;
+    int n = (int)ctx->t_ms.size();
+    if (n > max_stages) n = max_stages;
+    for (int i = 0; i < n; i++) { names[i] = ctx->t_names[i].c_str(); ms[i] = ctx->t_ms[i]; }
+    return n;
+}
+
+static void free_all(cvr_ctx* c)
+{
+    void* ptrs[] = { c->d_in[0], c->d_in[1], c->d_gray, c->d_volA, c->d_volC, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, c->d_disp, c->d_med,
+                     c->d_label, c->d_size, c->d_pruned, c->d_dispf, c->d_mask, c->d_pstats, c->d_rowcnt, c->d_cloud, c->d_ncloud, c->d_vhdr,
+                     c->d_keys[0], c->d_keys[1], c->d_vals[0], c->d_vals[1], c->d_hist, c->d_segstart, c->d_vox, c->d_cellstart, c->d_cellidx,
+                     c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags };
+    for (void* p : ptrs) if (p) cudaFree(p);
+    if (c->h_counts) cudaFreeHost(c->h_counts);
+    for (auto& t : c->timers) cudaEventDestroy(t.ev);
+    if (c->stream) cudaStreamDestroy(c->stream);
+}
+
+extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
+{
+    if (!out) return CVR_ERR_INVALID_ARG;
+    *out = nullptr;
+    int rc = validate(p, g_create_err);
+    if (rc) return rc;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { g_create_err = "no CUDA device: libcvrecon_b200 has no CPU fallback"; cudaGetLastError(); return CVR_ERR_NO_DEVICE; }
+    if (device < 0 || device >= ndev) { g_create_err = "device index out of range"; return CVR_ERR_INVALID_ARG; }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { g_create_err = "cudaGetDeviceProperties failed"; return CVR_ERR_CUDA; }
+    if (prop.major != 10) { g_create_err = "device is not sm_100-class (this library is built for sm_100a only)"; return CVR_ERR_NO_DEVICE; }
+    if (cudaSetDevice(device) != cudaSuccess) { g_create_err = "cudaSetDevice failed"; return CVR_ERR_CUDA; }
+    cvr_ctx* c = new (std::nothrow) cvr_ctx();
+    if (!c) return CVR_ERR_CUDA;
+    c->prm = *p; c->device = device; c->maxB = p->max_batch; c->sm_count = prop.multiProcessorCount;
+    c->launches = 0; c->profiling = false; c->timers_used = 0; c->stream = nullptr; c->h_counts = nullptr;
+    fill_dev_params(c);
+    const SgbmDev& g = c->sg;
+    const size_t B = (size_t)c->maxB, HW = (size_t)g.W * g.H;
+    c->maxN = (int)(p->max_points > 0 ? (size_t)p->max_points : HW);
+    if (!p->filter_only && (size_t)c->maxN < HW) c->maxN = (int)HW;
+    const size_t N = (size_t)c->maxN;
+    c->sor_grid_cap = c->maxN < 4096 ? 4096 : c->maxN;
+    const size_t nblk = (N + 1023) / 1024 + 2;
+    const size_t nRuns = (N + 511) / 512;
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+#define A(call) if (e == cudaSuccess) e = (call)
+    if (!p->filter_only) {
+        const size_t W1 = g.W1 > 0 ? g.W1 : 0, vol = (size_t)g.H * W1 * g.Dp;
+        A(dalloc(&c->d_in[0], B * HW * 4)); A(dalloc(&c->d_in[1], B * HW * 4));
+        A(dalloc(&c->d_gray, B * 2 * g.H * g.Wp));
+        A(dalloc(&c->d_volA, B * vol)); A(dalloc(&c->d_volC, B * vol));
+        A(dalloc(&c->d_lr, B * 2 * (W1 + 2) * 3 * g.Dp)); A(dalloc(&c->d_minlr, B * 2 * (W1 + 2) * 4));
+        A(dalloc(&c->d_raw, B * HW)); A(dalloc(&c->d_aux, B * g.H * (W1 + 1))); A(dalloc(&c->d_disp, B * HW)); A(dalloc(&c->d_med, B * HW));
+        A(dalloc(&c->d_label, B * HW)); A(dalloc(&c->d_size, B * HW));
+        A(dalloc(&c->d_pruned, B * HW)); A(dalloc(&c->d_dispf, B * HW)); A(dalloc(&c->d_mask, B * HW));
+        A(dalloc(&c->d_pstats, B));
+    }
+    A(dalloc(&c->d_rowcnt, B * nblk));
+    A(dalloc(&c->d_cloud, B * N)); A(dalloc(&c->d_ncloud, B));
+    A(dalloc(&c->d_vhdr, B));
+    A(dalloc(&c->d_keys[0], B * N)); A(dalloc(&c->d_keys[1], B * N)); A(dalloc(&c->d_vals[0], B * N)); A(dalloc(&c->d_vals[1], B * N));
+    A(dalloc(&c->d_hist, B * (256 * nRuns + 1)));
+    A(dalloc(&c->d_segstart, B * (N + 1))); A(dalloc(&c->d_vox, B * N));
+    A(dalloc(&c->d_cellstart, B * 2 * ((size_t)c->sor_grid_cap + 2))); A(dalloc(&c->d_cellidx, B * N));
+    A(dalloc(&c->d_meand, B * N)); A(dalloc(&c->d_sstats, B)); A(dalloc(&c->d_sorout, B * N));
+    A(dalloc(&c->d_nout, B)); A(dalloc(&c->d_nvox, B)); A(dalloc(&c->d_spts, B * N));
+    A(dalloc(&c->d_flags, B * 64));
+    A(cudaHostAlloc((void**)&c->h_counts, sizeof(int) * B * 4, cudaHostAllocDefault));
+#undef A
+    if (e != cudaSuccess) {
+        g_create_err = std::string("workspace allocation failed: ") + cudaGetErrorString(e);
+        free_all(c); delete c; cudaGetLastError();
+        return CVR_ERR_CUDA;
+    }
+    *out = c;
+    return CVR_OK;
+}
+
+extern "C" int cvr_destroy(cvr_ctx* c)
+{
+    if (!c) return CVR_OK;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    free_all(c);
+    delete c;
+    return CVR_OK;
+}
+
+#define REQUIRE(ctx, cond, msg) do { if (!(cond)) { (ctx)->err = (msg); return CVR_ERR_INVALID_ARG; } } while (0)
+#define STEREO_ONLY(ctx) do { if ((ctx)->prm.filter_only) { (ctx)->err = "context was created with filter_only"; return CVR_ERR_INVALID_ARG; } } while (0)
+
+static int sync_check(cvr_ctx* c)
+{
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) { c->err = std::string("stream sync: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
+    return CVR_OK;
+}
+
+extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const uint8_t* right, size_t sr, int ch, int16_t* disp, size_t sd)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    REQUIRE(c, left && right && disp, "null image pointer");
+    // cv::cvtColor(BGR2GRAY) throws for anything but 3/4 channels; 1 = caller already has gray
+    REQUIRE(c, ch == 1 || ch == 3 || ch == 4, "channels must be 1, 3 or 4");
+    const int W = c->sg.W, H = c->sg.H;
+    REQUIRE(c, sl >= (size_t)W * ch && sr >= (size_t)W * ch && sd >= (size_t)W * 2, "step smaller than a row");
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * ch, left, sl, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], (size_t)W * ch, right, sr, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_gray(c, 1, c->d_in[0], (size_t)W * ch, 0, c->d_in[1], (size_t)W * ch, 0, ch);
+    if (rc) return rc;
+    cvr_stage_mark(c, "h2d_gray");
+    rc = cvr_launch_sgbm(c, 1);
+    if (rc) return rc;
+    CVR_CUDA(c, cudaMemcpy2DAsync(disp, sd, c->d_med, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->stream));
+    cvr_stage_mark(c, "d2h");
+    rc = sync_check(c);
+    timers_end(c);
+    return rc;
+}
+
+extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, int* w1, int* dp)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    const SgbmDev& g = c->sg;
+    if (w1) *w1 = g.W1;
+    if (dp) *dp = g.Dp;
+    const size_t vol = (size_t)g.H * (g.W1 > 0 ? g.W1 : 0) * g.Dp * 2;
+    const void* src; size_t need;
+    switch (which) {
+        case 0: src = c->d_volC; need = vol; break;
+        case 1: src = c->d_volA; need = vol; break;
+        case 2: src = c->d_raw; need = (size_t)g.W * g.H * 2; break;
+        case 3: src = c->d_disp; need = (size_t)g.W * g.H * 2; break;
+        default: c->err = "unknown debug buffer"; return CVR_ERR_INVALID_ARG;
+    }
+    if (!dst) return CVR_OK;
+    REQUIRE(c, bytes >= need, "debug buffer too small");
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    CVR_CUDA(c, cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
+    return CVR_OK;
+}
+
+extern "C" int cvr_prune(cvr_ctx* c, int16_t* disp, size_t sd, float* dispf, uint8_t* mask)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    REQUIRE(c, disp, "null disparity");
+    const int W = c->sg.W, H = c->sg.H;
+    REQUIRE(c, sd >= (size_t)W * 2, "step smaller than a row");
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_med, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_prune(c, 1, c->d_med);
+    if (rc) return rc;
+    CVR_CUDA(c, cudaMemcpy2DAsync(disp, sd, c->d_pruned, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->stream));
+    if (dispf) CVR_CUDA(c, cudaMemcpyAsync(dispf, c->d_dispf, (size_t)W * H * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (mask) CVR_CUDA(c, cudaMemcpyAsync(mask, c->d_mask, (size_t)W * H, cudaMemcpyDeviceToHost, c->stream));
+    rc = sync_check(c);
+    timers_end(c);
+    return rc;
+}
+
+static int fetch_cloud(cvr_ctx* c, const cvr_point* dsrc, const int* dcount, cvr_point* out, int capacity, int* n_out)
+{
+    CVR_CUDA(c, cudaMemcpyAsync(c->h_counts, dcount, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    int rc = sync_check(c);
+    if (rc) return rc;
+    const int n = c->h_counts[0];
+    if (n_out) *n_out = n;
+    if (n > capacity) { c->err = "output capacity too small for the cloud"; return CVR_ERR_CAPACITY; }
+    if (n > 0) CVR_CUDA(c, cudaMemcpyAsync(out, dsrc, (size_t)n * sizeof(cvr_point), cudaMemcpyDeviceToHost, c->stream));
+    return sync_check(c);
+}
+
+extern "C" int cvr_reproject_cloud(cvr_ctx* c, const int16_t* disp, size_t sd, const uint8_t* bgr, size_t sb, cvr_point* out, int capacity, int* n_out)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    REQUIRE(c, disp && bgr && out, "null pointer");
+    const int W = c->sg.W, H = c->sg.H;
+    REQUIRE(c, sd >= (size_t)W * 2 && sb >= (size_t)W * 3, "step smaller than a row");
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_pruned, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, c->d_in[0], (size_t)W * 3, 0, 3);
+    if (rc) return rc;
+    rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
+    timers_end(c);
+    return rc;
+}
+
+extern "C" int cvr_triangulate(cvr_ctx* c, const float* dispf, size_t sd, const uint8_t* bgr, size_t sb, const uint8_t* mask, size_t sm,
+                               cvr_point* out, int capacity, int* n_out)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    REQUIRE(c, dispf && bgr && out, "null pointer");
+    const int W = c->sg.W, H = c->sg.H;
+    REQUIRE(c, sd >= (size_t)W * 4 && sb >= (size_t)W * 3 && (!mask || sm >= (size_t)W), "step smaller than a row");
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_dispf, (size_t)W * 4, dispf, sd, (size_t)W * 4, H, cudaMemcpyHostToDevice, c->stream));
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
+    if (mask) CVR_CUDA(c, cudaMemcpy2DAsync(c->d_mask, (size_t)W, mask, sm, (size_t)W, H, cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, mask ? c->d_mask : nullptr, c->d_in[0], (size_t)W * 3, 0, 3);
+    if (rc) return rc;
+    rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
+    timers_end(c);
+    return rc;
+}
+
+extern "C" int cvr_voxel_grid(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, int capacity, int* m_out, int* passthrough)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    REQUIRE(c, n >= 0 && (n == 0 || (in && out)), "null pointer");
+    if (n > c->maxN) { c->err = "cloud larger than the context's point capacity (cvr_params.max_points)"; return CVR_ERR_CAPACITY; }
+    if (m_out) *m_out = 0;
+    if (passthrough) *passthrough = 0;
+    if (n == 0) return CVR_OK;
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    CVR_CUDA(c, cudaMemcpyAsync(c->d_cloud, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
+    c->h_counts[1] = n;
+    CVR_CUDA(c, cudaMemcpyAsync(c->d_ncloud, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_voxel(c, 1, c->d_cloud, (size_t)c->maxN, c->d_ncloud);
+    if (rc) return rc;
+    rc = fetch_cloud(c, c->d_vox, c->d_nvox, out, capacity, m_out);
+    if (rc) return rc;
+    if (passthrough) {
+        VoxelHdr h;
+        CVR_CUDA(c, cudaMemcpy(&h, c->d_vhdr, sizeof(h), cudaMemcpyDeviceToHost));
+        *passthrough = h.passthrough;
+    }
+    timers_end(c);
+    return CVR_OK;
+}
+
+extern "C" int cvr_sor(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, int capacity, int* kept_out)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    REQUIRE(c, n >= 0 && (n == 0 || (in && out)), "null pointer");
+    if (n > c->maxN) { c->err = "cloud larger than the context's point capacity (cvr_params.max_points)"; return CVR_ERR_CAPACITY; }
+    if (kept_out) *kept_out = 0;
+    if (n == 0) return CVR_OK;
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
+    c->h_counts[1] = n;
+    CVR_CUDA(c, cudaMemcpyAsync(c->d_nvox, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_sor(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, 0);
+    if (rc) return rc;
+    rc = fetch_cloud(c, c->d_sorout, c->d_nout, out, capacity, kept_out);
+    timers_end(c);
+    return rc;
+}
+
+__global__ void k_copy_clouds(const cvr_point* __restrict__ src, size_t srcStride, const int* __restrict__ cnt, cvr_point* __restrict__ dst,
+                              size_t cap, int* __restrict__ cntOut)
+{
+    const int b = blockIdx.y, n = min(cnt[b], (int)min(cap, (size_t)0x7fffffff));
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[(size_t)b * cap + i] = src[(size_t)b * srcStride + i];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && cntOut) cntOut[b] = cnt[b];
+}
+
+extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    REQUIRE(c, io && nframes >= 1, "bad batch");
+    if (nframes > c->maxB) { c->err = "nframes exceeds max_batch"; return CVR_ERR_CAPACITY; }
+    REQUIRE(c, io->left && io->right, "null image pointer");
+    const int ch = io->channels;
+    REQUIRE(c, ch == 1 || ch == 3 || ch == 4, "channels must be 1, 3 or 4");
+    const int W = c->sg.W, H = c->sg.H, B = nframes;
+    const size_t rowBytes = (size_t)W * ch;
+    REQUIRE(c, io->left_step >= rowBytes && io->right_step >= rowBytes, "step smaller than a row");
+    const int stages = io->stages ? io->stages : 15;
+    const bool wantCloud = (stages & 2) != 0, wantVox = (stages & 4) != 0, wantSor = (stages & 8) != 0;
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    const uint8_t *dl, *dr; size_t lstep, lfs, rstep, rfs;
+    if (io->mem == CVR_MEM_HOST) {
+        for (int i = 0; i < B; i++) {
+            CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0] + (size_t)i * rowBytes * H, rowBytes, io->left + (size_t)i * io->left_frame_stride, io->left_step, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
+            CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1] + (size_t)i * rowBytes * H, rowBytes, io->right + (size_t)i * io->right_frame_stride, io->right_step, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
+        }
+        dl = c->d_in[0]; dr = c->d_in[1]; lstep = rstep = rowBytes; lfs = rfs = rowBytes * H;
+        cvr_stage_mark(c, "h2d");
+    } else {
+        dl = io->left; dr = io->right; lstep = io->left_step; rstep = io->right_step; lfs = io->left_frame_stride; rfs = io->right_frame_stride;
+    }
+    int rc = cvr_launch_gray(c, B, dl, lstep, lfs, dr, rstep, rfs, ch);
+    if (rc) return rc;
+    cvr_stage_mark(c, "gray");
+    rc = cvr_launch_sgbm(c, B);
+    if (rc) return rc;
+    const cvr_point* fin = nullptr; const int* fcnt = nullptr;
+    if (wantCloud || wantVox || wantSor) {
+        rc = cvr_launch_prune(c, B, c->d_med);
+        if (rc) return rc;
+        if (c->prm.cloud_mode == CVR_CLOUD_REPROJECT)
+            rc = cvr_launch_cloud(c, B, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, dl, lstep, lfs, ch);
+        else
+            rc = cvr_launch_cloud(c, B, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, c->d_mask, dl, lstep, lfs, ch);
+        if (rc) return rc;
+        fin = c->d_cloud; fcnt = c->d_ncloud;
+        if (wantVox) {
+            rc = cvr_launch_voxel(c, B, fin, (size_t)c->maxN, fcnt);
+            if (rc) return rc;
+            fin = c->d_vox; fcnt = c->d_nvox;
+        }
+        if (wantSor) {
+            rc = cvr_launch_sor(c, B, fin, (size_t)c->maxN, fcnt, 0);
+            if (rc) return rc;
+            fin = c->d_sorout; fcnt = c->d_nout;
+        }
+    }
+    // ---- outputs ----
+    if (io->disp) {
+        const cudaMemcpyKind kind = io->mem == CVR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+        REQUIRE(c, io->disp_step >= (size_t)W * 2, "disp_step smaller than a row");
+        for (int i = 0; i < B; i++)
+            CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io->disp + (size_t)i * io->disp_frame_stride, io->disp_step, c->d_med + (size_t)i * W * H, (size_t)W * 2,
+                                          (size_t)W * 2, H, kind, c->stream));
+    }
+    if (fin && (io->cloud || io->cloud_count)) {
+        CVR_CUDA(c, cudaMemcpyAsync(c->h_counts, fcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+        rc = sync_check(c);
+        if (rc) return rc;
+        if (io->cloud)
+            for (int i = 0; i < B; i++)
+                if ((size_t)c->h_counts[i] > io->cloud_capacity) { c->err = "cloud_capacity too small"; return CVR_ERR_CAPACITY; }
+        if (io->mem == CVR_MEM_HOST) {
+            if (io->cloud_count) memcpy(io->cloud_count, c->h_counts, sizeof(int) * B);
+            if (io->cloud)
+                for (int i = 0; i < B; i++)
+                    if (c->h_counts[i] > 0)
+                        CVR_CUDA(c, cudaMemcpyAsync(io->cloud + (size_t)i * io->cloud_capacity, fin + (size_t)i * c->maxN, (size_t)c->h_counts[i] * sizeof(cvr_point),
+                                                    cudaMemcpyDeviceToHost, c->stream));
+        } else {
+            if (io->cloud) {
+                k_copy_clouds<<<dim3(64, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, io->cloud, io->cloud_capacity, io->cloud_count);
+                c->launches++;
+            } else if (io->cloud_count) {
+                CVR_CUDA(c, cudaMemcpyAsync(io->cloud_count, fcnt, sizeof(int) * B, cudaMemcpyDeviceToDevice, c->stream));
+            }
+        }
+    }
+    cvr_stage_mark(c, "out");
+    rc = sync_check(c);
+    timers_end(c);
+    return rc;
+}
+
+extern "C" void cvr_points_to_pcl(const cvr_point* in, int n, void* pcl32)
+{
+    // pcl::PointXYZRGB: float x,y,z, float pad (=1.0f); then b,g,r,a packed in 4 bytes; 12 bytes of padding
+    uint8_t* o = (uint8_t*)pcl32;
+    for (int i = 0; i < n; i++, o += 32) {
+        const float one = 1.0f;
+        memcpy(o, &in[i].x, 12); memcpy(o + 12, &one, 4);
+        o[16] = in[i].b; o[17] = in[i].g; o[18] = in[i].r; o[19] = in[i].a;
+        memset(o + 20, 0, 12);
+    }
+}

@@ -1,0 +1,157 @@
+// cvr_internal.cuh -- shared declarations of libcvrecon_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+
+#include "../../include/cvrecon_b200.h"
+
+#define CVR_MAX_COST 32767
+#define CVR_DISP_SCALE 16
+
+// Normalised StereoSGBM parameters, passed by value to kernels.
+struct SgbmDev {
+    int W, H;            // image size
+    int Wp;              // gray pitch in bytes
+    int minD, D, Dp;     // Dp = D padded to a multiple of 64 (DPL = Dp/32 values per lane)
+    int bs, SW2, SH2;
+    int P1s;             // (short)P1
+    int P2;              // full int P2 (delta = (short)(P2 + minLr))
+    int P2s;             // (short)P2 : bias of the cost volume
+    int uniq, d12, ftzero;
+    int minX1, maxX1, W1;
+    int INVALID;
+    int mode;            // CVR_MODE_*
+    int ring;            // pow2 >= bs + 1 (pixel-cost ring buffer of the horizontal box sum)
+};
+
+struct CloudDev {
+    float Q[16];
+    float f, b, cx, cy;
+    double sigma_factor;
+    float leaf[3];
+    int sor_k;
+    double sor_alpha;
+};
+
+// Per-frame voxel-grid header computed on device.
+struct VoxelHdr {
+    float mn[3], mx[3];
+    int minb[3];
+    int div[3];
+    int passthrough;     // int32 index overflow: PCL copies input through
+    int n;               // number of input points
+    int m;               // number of voxels (output points)
+    int maxkey;
+};
+
+struct PruneStats {
+    int mn, mx;
+    unsigned long long sum, sq;
+    float a, b;
+    int ithr;
+    int pad;
+};
+
+struct SorStats {
+    double sum, sq;      // over mean distances
+    double thr;
+    int valid;
+    int kept;
+};
+
+struct StageTimer {
+    const char* name;
+    cudaEvent_t ev;
+};
+
+struct cvr_ctx {
+    cvr_params prm;
+    SgbmDev sg;
+    CloudDev cl;
+    int device;
+    int maxB;
+    int maxN;                // point capacity per frame (>= W*H unless filter_only)
+    int sm_count;
+    cudaStream_t stream;
+    std::string err;
+    long long launches;
+    bool profiling;
+    std::vector<StageTimer> timers;
+    int timers_used;
+    std::vector<std::string> t_names;
+    std::vector<float> t_ms;
+
+    // ---- device workspace (all sized for maxB frames) ----
+    uint8_t* d_in[2];        // staged input images (host path), tight: [B][H][W*ch]
+    size_t in_bytes_per_frame;
+    uint8_t* d_gray;         // [B][2][H][Wp]
+    int16_t* d_volA;         // hsum, later S : [B][H][W1][Dp]
+    int16_t* d_volC;         // C             : [B][H][W1][Dp]
+    int16_t* d_lr;           // vertical path state [B][2][W1+2][3][Dp]
+    int* d_minlr;            // [B][2][W1+2][4]
+    int16_t* d_raw;          // WTA output [B][H][W]
+    int* d_aux;              // (minS<<16 | best&0xffff) per accepted pixel, -1 if rejected [B][H][W1]
+    int16_t* d_disp;         // after LR check  [B][H][W]
+    int16_t* d_med;          // after median / speckle [B][H][W]   (final disparity)
+    int* d_label;            // speckle CCL [B][H][W]
+    int* d_size;             // speckle component sizes [B][H][W]
+    int16_t* d_pruned;       // pruned disparity [B][H][W]
+    float* d_dispf;          // [B][H][W]
+    uint8_t* d_mask;         // [B][H][W]
+    PruneStats* d_pstats;    // [B]
+    int* d_rowcnt;           // [B][H+1]
+    cvr_point* d_cloud;      // dense cloud [B][H*W]
+    int* d_ncloud;           // [B]
+    // voxel
+    VoxelHdr* d_vhdr;        // [B]
+    uint32_t* d_keys[2];     // [B][H*W]
+    uint32_t* d_vals[2];     // [B][H*W]
+    uint32_t* d_hist;        // radix histograms [B][256][nTiles]
+    int sort_tiles;          // tiles per frame
+    int* d_segstart;         // voxel segment starts [B][H*W + 1]
+    cvr_point* d_vox;        // voxel output [B][H*W]
+    // sor
+    int* d_cellstart;        // grid cell starts [B][cells+1]
+    int* d_cellidx;          // point -> cell id
+    float* d_meand;          // mean kNN distance [B][H*W]
+    SorStats* d_sstats;      // [B]
+    cvr_point* d_sorout;     // [B][H*W]
+    int* d_nout;             // [B] final count
+    int* d_nvox;             // [B] voxel count
+    float4* d_spts;          // sor: points sorted by grid cell (w = original index) [B][maxN]
+    uint32_t* d_sortidx;     // sor: point order by cell
+    int sor_grid_cap;        // max cells per frame
+    int* h_counts;           // pinned [B]
+    int* d_flags;            // misc flags [B][4]
+};
+
+#define CVR_CUDA(ctx, call)                                                                       \
+    do {                                                                                          \
+        cudaError_t e__ = (call);                                                                 \
+        if (e__ != cudaSuccess) {                                                                 \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e__);                     \
+            return CVR_ERR_CUDA;                                                                  \
+        }                                                                                         \
+    } while (0)
+
+static inline int cvr_div_up(int a, int b) { return (a + b - 1) / b; }
+static inline size_t cvr_div_up_sz(size_t a, size_t b) { return (a + b - 1) / b; }
+
+// ---- stage launchers (each returns cudaError_t of the launch; all on ctx->stream) ----
+// k_sgbm.cu
+int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t lfs, const uint8_t* right, size_t rstep,
+                    size_t rfs, int channels);
+int cvr_launch_sgbm(cvr_ctx* c, int B);     // gray -> d_med (final disparity)
+// k_cloud.cu
+int cvr_launch_prune(cvr_ctx* c, int B, const int16_t* disp_in /*[B][H][W] tight*/);
+int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const float* dispf, const uint8_t* mask,
+                     const uint8_t* bgr, size_t bstep, size_t bfs, int channels);
+// k_voxel.cu
+int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in);
+// k_sor.cu
+int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in /*device*/, int n_is_vox);
+
+void cvr_stage_mark(cvr_ctx* c, const char* name);

@@ -1,0 +1,222 @@
+// k_cloud.cu -- the glue stages between disparity and point cloud:
+//   prune       TrackingFrame::SetupFrame / PruneDisparityImage  (cv_reconstruct/src/system/TrackingFrame.cpp:25-67)
+//   reproject   Reconstruct3D::GeneratePointCloud                (cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:106-153)
+//   triangulate Reconstruct3D::Triangulate3D                     (cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:156-216)
+// Both cloud generators emit surviving pixels in row-major order (the reference's push_back order) through an
+// ordered stream compaction: per-1024-pixel block counts -> per-frame exclusive scan -> write.
+// Floating point follows the reference's evaluation order with explicit round-to-nearest intrinsics so that
+// nvcc cannot contract a*b+c into an FMA where the CPU code has none.
+#include "cvr_internal.cuh"
+#include "cvr_scan.cuh"
+#include <float.h>
+
+#define LAUNCH_CHECK(c)                                                                  \
+    do {                                                                                 \
+        (c)->launches++;                                                                 \
+        cudaError_t e__ = cudaGetLastError();                                            \
+        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// prune
+__global__ void k_prune_init(PruneStats* st, int B)
+{
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    st[b].mn = 32767; st[b].mx = -32768; st[b].sum = 0; st[b].sq = 0; st[b].a = 0; st[b].b = 0; st[b].ithr = 0;
+}
+__global__ void k_prune_minmax(const int16_t* __restrict__ disp, int N, PruneStats* st)
+{
+    const int b = blockIdx.y;
+    const int16_t* d = disp + (size_t)b * N;
+    int mn = 32767, mx = -32768;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) { int v = d[i]; mn = min(mn, v); mx = max(mx, v); }
+    mn = __reduce_min_sync(0xffffffffu, mn); mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((threadIdx.x & 31) == 0) { atomicMin(&st[b].mn, mn); atomicMax(&st[b].mx, mx); }
+}
+// cv::normalize(NORM_MINMAX, 0, 255, CV_8U): scale/shift in f64, applied as one f32 FMA, round-half-even, saturate.
+__global__ void k_prune_norm(const int16_t* __restrict__ disp, int N, PruneStats* st, uint8_t* __restrict__ u8)
+{
+    const int b = blockIdx.y;
+    const int16_t* d = disp + (size_t)b * N;
+    uint8_t* o = u8 + (size_t)b * N;
+    const double dmn = (double)st[b].mn, dmx = (double)st[b].mx;
+    const double rng = __dsub_rn(dmx, dmn);
+    const double scale = __dmul_rn(255.0, (rng > DBL_EPSILON ? __ddiv_rn(1.0, rng) : 0.0));
+    const double shift = __dsub_rn(0.0, __dmul_rn(dmn, scale));
+    const float fa = (float)scale, fb = (float)shift;
+    unsigned long long sum = 0, sq = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const float f = __fmaf_rn((float)d[i], fa, fb);
+        int r = __float2int_rn(f);
+        r = min(max(r, 0), 255);
+        o[i] = (uint8_t)r;
+        sum += (unsigned)r; sq += (unsigned)(r * r);
+    }
+    __shared__ unsigned long long ssum[32], ssq[32];
+#pragma unroll
+    for (int k = 16; k > 0; k >>= 1) { sum += __shfl_down_sync(0xffffffffu, sum, k); sq += __shfl_down_sync(0xffffffffu, sq, k); }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { ssum[w] = sum; ssq[w] = sq; }
+    __syncthreads();
+    if (w == 0) {
+        const int nw = blockDim.x >> 5;
+        sum = lane < nw ? ssum[lane] : 0; sq = lane < nw ? ssq[lane] : 0;
+#pragma unroll
+        for (int k = 16; k > 0; k >>= 1) { sum += __shfl_down_sync(0xffffffffu, sum, k); sq += __shfl_down_sync(0xffffffffu, sq, k); }
+        if (lane == 0) { atomicAdd(&st[b].sum, sum); atomicAdd(&st[b].sq, sq); }
+    }
+}
+// cv::meanStdDev (population sigma, f64) -> cv::threshold(u8 > floor(sigma*factor)) -> zero pruned disparities ->
+// convertTo(CV_32F, 1/16) -> mask &= disparity > 0.
+__global__ void k_prune_apply(const int16_t* __restrict__ disp, const uint8_t* u8, int N, const PruneStats* __restrict__ st,
+                              double factor, int16_t* __restrict__ pruned, float* __restrict__ dispf, uint8_t* mask)
+{
+    const int b = blockIdx.y;
+    const double inv = __ddiv_rn(1.0, (double)N);
+    const double mean = __dmul_rn((double)st[b].sum, inv);
+    const double var = __dsub_rn(__dmul_rn((double)st[b].sq, inv), __dmul_rn(mean, mean));
+    const double sigma = sqrt(var > 0.0 ? var : 0.0);
+    const int ithr = (int)floor(__dmul_rn(sigma, factor));
+    const size_t o = (size_t)b * N;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) {
+        const int keep = (int)u8[o + i] > ithr;
+        const int v = keep ? (int)disp[o + i] : 0;
+        const float f = __fmul_rn((float)v, 0.0625f);
+        if (pruned) pruned[o + i] = (int16_t)v;
+        if (dispf) dispf[o + i] = f;
+        if (mask) mask[o + i] = (keep && f > 0.0f) ? 255 : 0;
+    }
+}
+
+int cvr_launch_prune(cvr_ctx* c, int B, const int16_t* disp_in)
+{
+    const int N = c->sg.W * c->sg.H;
+    const int gx = min(cvr_div_up(N, 256), 296);
+    k_prune_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_pstats, B);
+    LAUNCH_CHECK(c);
+    k_prune_minmax<<<dim3(gx, B), 256, 0, c->stream>>>(disp_in, N, c->d_pstats);
+    LAUNCH_CHECK(c);
+    // the normalised u8 image lives in d_mask until k_prune_apply overwrites it element-wise (same index read then written)
+    k_prune_norm<<<dim3(gx, B), 256, 0, c->stream>>>(disp_in, N, c->d_pstats, c->d_mask);
+    LAUNCH_CHECK(c);
+    k_prune_apply<<<dim3(gx, B), 256, 0, c->stream>>>(disp_in, c->d_mask, N, c->d_pstats, c->cl.sigma_factor, c->d_pruned, c->d_dispf, c->d_mask);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "prune");
+    return CVR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// cloud generation
+struct CloudArgs {
+    const int16_t* disp16;   // reproject input  [B][H][W]
+    const float* dispf;      // triangulate input [B][H][W]
+    const uint8_t* mask;     // optional [B][H][W]
+    const uint8_t* bgr; size_t bstep, bfs; int ch;
+    int W, H;
+    CloudDev cl;
+    const int* minDisp;      // reproject: per-frame min disparity (handleMissingValues)
+};
+
+template <int MODE>
+__device__ __forceinline__ bool make_point(const CloudArgs& a, int b, int i, cvr_point& pt)
+{
+    const int W = a.W, y = i / W, x = i - y * W;
+    const size_t o = (size_t)b * W * a.H + i;
+    if (MODE == CVR_CLOUD_TRIANGULATE) {
+        const float d = a.dispf[o];
+        if (!(d > 0.0f)) return false;                        // `if (d <= 0.0) continue;` (NaN falls through in the reference; disparities are finite)
+        if (a.mask && a.mask[o] == 0) return false;
+        const float z = __fdiv_rn(__fmul_rn(a.cl.f, a.cl.b), d);
+        const float zf = __fdiv_rn(z, a.cl.f);
+        pt.z = z;
+        pt.x = __fmul_rn(__fsub_rn((float)x, a.cl.cx), zf);
+        pt.y = __fmul_rn(-__fsub_rn((float)y, a.cl.cy), zf);
+    } else {
+        const double d = (double)(float)a.disp16[o];
+        const float* Q = a.cl.Q;
+        double h[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+            h[r] = __dadd_rn(__dadd_rn(__dadd_rn(__dmul_rn((double)Q[r * 4 + 0], (double)x), __dmul_rn((double)Q[r * 4 + 1], (double)y)),
+                                       __dmul_rn((double)Q[r * 4 + 2], d)), (double)Q[r * 4 + 3]);
+        const double iw = __ddiv_rn(1.0, h[3]);
+        float p0 = (float)__dmul_rn((double)(float)h[0], iw);
+        float p1 = (float)__dmul_rn((double)(float)h[1], iw);
+        float p2 = (float)__dmul_rn((double)(float)h[2], iw);
+        if (fabs(d - (double)a.minDisp[b]) <= (double)FLT_EPSILON) p2 = 10000.0f;
+        if (p2 == 10000.0f) return false;                     // MISSING_DISPARITY_Z, Reconstruct3D.cpp:124
+        const float px = __fsub_rn(p0, __fdiv_rn((float)W, 2.0f));
+        pt.x = -px;                                           // transformPointCloud(diag(-1,1,1,1))
+        pt.y = -__fsub_rn(p1, __fdiv_rn((float)a.H, 2.0f));
+        pt.z = p2;
+    }
+    const uint8_t* s = a.bgr + (size_t)b * a.bfs + (size_t)y * a.bstep + (size_t)x * a.ch;
+    if (a.ch == 1) { pt.b = pt.g = pt.r = s[0]; } else { pt.b = s[0]; pt.g = s[1]; pt.r = s[2]; }
+    pt.a = 255;
+    return true;
+}
+
+__global__ void k_min_s16(const int16_t* __restrict__ disp, int N, int* out)
+{
+    const int b = blockIdx.y;
+    int mn = 32767;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) mn = min(mn, (int)disp[(size_t)b * N + i]);
+    mn = __reduce_min_sync(0xffffffffu, mn);
+    if ((threadIdx.x & 31) == 0) atomicMin(&out[b], mn);
+}
+__global__ void k_fill_int(int* p, int n, int v) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = v; }
+
+template <int MODE>
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_cloud_count(CloudArgs a, int* blkcnt, size_t cntStride)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
+    cvr_point pt;
+    const int f = (i < a.W * a.H) ? (int)make_point<MODE>(a, b, i, pt) : 0;
+    int tot;
+    block_excl_scan(f, ws, &tot);
+    if (threadIdx.x == 0) blkcnt[(size_t)b * cntStride + blockIdx.x] = tot;
+}
+template <int MODE>
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_cloud_write(CloudArgs a, const int* __restrict__ blkoff, size_t cntStride, int nblk,
+                                                               cvr_point* __restrict__ out, size_t outStride, int* __restrict__ nout)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
+    cvr_point pt;
+    const int f = (i < a.W * a.H) ? (int)make_point<MODE>(a, b, i, pt) : 0;
+    const int e = block_excl_scan(f, ws, nullptr);
+    if (f) out[(size_t)b * outStride + blkoff[(size_t)b * cntStride + blockIdx.x] + e] = pt;
+    if (blockIdx.x == 0 && threadIdx.x == 0) nout[b] = blkoff[(size_t)b * cntStride + nblk];
+}
+
+int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const float* dispf, const uint8_t* mask,
+                     const uint8_t* bgr, size_t bstep, size_t bfs, int channels)
+{
+    const int W = c->sg.W, H = c->sg.H, N = W * H;
+    const int nblk = cvr_div_up(N, CVR_SEL_BLOCK);
+    const size_t cntStride = (size_t)nblk + 1;
+    CloudArgs a;
+    a.disp16 = disp16; a.dispf = dispf; a.mask = mask; a.bgr = bgr; a.bstep = bstep; a.bfs = bfs; a.ch = channels;
+    a.W = W; a.H = H; a.cl = c->cl; a.minDisp = c->d_flags;
+    if (mode == CVR_CLOUD_REPROJECT) {
+        k_fill_int<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_flags, B, 32767);
+        LAUNCH_CHECK(c);
+        k_min_s16<<<dim3(min(cvr_div_up(N, 256), 296), B), 256, 0, c->stream>>>(disp16, N, c->d_flags);
+        LAUNCH_CHECK(c);
+        k_cloud_count<CVR_CLOUD_REPROJECT><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride);
+    } else {
+        k_cloud_count<CVR_CLOUD_TRIANGULATE><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride);
+    }
+    LAUNCH_CHECK(c);
+    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
+    LAUNCH_CHECK(c);
+    if (mode == CVR_CLOUD_REPROJECT)
+        k_cloud_write<CVR_CLOUD_REPROJECT><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride, nblk, c->d_cloud, (size_t)c->maxN, c->d_ncloud);
+    else
+        k_cloud_write<CVR_CLOUD_TRIANGULATE><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride, nblk, c->d_cloud, (size_t)c->maxN, c->d_ncloud);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "cloud");
+    return CVR_OK;
+}

@@ -1,0 +1,666 @@
+// k_sgbm.cu -- semi-global block matching with cv::StereoSGBM (MODE_SGBM / MODE_HH) semantics,
+// bit-exact including the int16 saturation regime.  Replaces the OpenCV calls made by
+// Reconstruct3D::GenerateDisparityMap (cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:72-84).
+//
+// Kernel set (one launch covers all B frames of a batch):
+//   k_gray        BGR(A) -> gray                                   (A.1)
+//   k_pix_hsum    clipped x-Sobel + Birchfield-Tomasi pixel cost,   (A.2, A.3 horizontal)
+//                 horizontal block sum -> hsum volume
+//   k_vsum        saturating vertical block sum + P2 bias -> C      (A.3 vertical)
+//   k_path_h      horizontal path (-> or <-), one warp per row      (A.4 r=0 / 5th path)
+//   k_path_v      the three vertical/diagonal paths fused, a        (A.4 r=1..3)
+//                 thread-block cluster per frame marching over rows
+//   (WTA fused into the last path kernel)                           (A.5 first half)
+//   k_lrcheck     right-view map by packed atomicMin + LR check     (A.5 second half)
+//   k_median3     3x3 median                                        (A.6)
+//   k_ccl_*       speckle filter as union-find labelling            (A.7)
+//
+// Volumes are int16 [B][H][W1][Dp], Dp = D padded to a multiple of 64, so a warp owns one (x') column with
+// DPL = Dp/32 consecutive disparities per lane; the min over disparities is one CREDUX warp reduction.
+#include "cvr_internal.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+#define FULL 0xffffffffu
+
+// ------------------------------------------------------------------------------------------------
+// A.1 gray
+__global__ void k_gray(const uint8_t* __restrict__ src, size_t step, size_t fstride, int ch, uint8_t* __restrict__ dst,
+                       int Wp, size_t dstFrameStride, int W, int H)
+{
+    int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    if (x >= W) return;
+    const uint8_t* s = src + (size_t)b * fstride + (size_t)y * step + (size_t)x * ch;
+    uint8_t g;
+    if (ch == 1) g = s[0];
+    else g = (uint8_t)((3735 * s[0] + 19235 * s[1] + 9798 * s[2] + 16384) >> 15);
+    dst[(size_t)b * dstFrameStride + (size_t)y * Wp + x] = g;
+}
+
+// ------------------------------------------------------------------------------------------------
+// A.2 + A.3 (horizontal).  One CTA per (row, frame), one thread per disparity.
+// Per-pixel packed descriptors, G channel (clipped Sobel) in the low half, raw intensity in the high half:
+//   left : (U, U0, -U, -U1)     right: (V, V0, -V, -V1)
+// so that the four BT differences are four VIADD.16x2 and the two max(.,.,0) are VIMNMX3.S16x2.RELU.
+__device__ __forceinline__ unsigned pk_neg(unsigned a) { return __vneg2(a); }
+
+__global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStride, int16_t* __restrict__ hsum, SgbmDev p)
+{
+    extern __shared__ uint4 sm4[];
+    uint4* Lpk = sm4;
+    uint4* Rpk = sm4 + p.W;
+    unsigned* aL = (unsigned*)(Rpk + p.W);
+    unsigned* aR = aL + p.W;
+    uint8_t* ringbuf = (uint8_t*)(aR + p.W);
+
+    const int y = blockIdx.x, b = blockIdx.y, W = p.W, H = p.H;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const uint8_t* gl = gray + (size_t)b * grayFrameStride;
+    const uint8_t* gr = gl + (size_t)H * p.Wp;
+    const int yn = max(y - 1, 0), ys = min(y + 1, H - 1);
+    const int ft = p.ftzero;
+
+    for (int x = tid; x < W; x += nt) {
+        unsigned vl, vr;
+        if (x == 0 || x == W - 1) { vl = vr = (unsigned)ft | ((unsigned)ft << 16); }
+        else {
+            const uint8_t *l0 = gl + (size_t)y * p.Wp + x, *ln = gl + (size_t)yn * p.Wp + x, *ls = gl + (size_t)ys * p.Wp + x;
+            const uint8_t *r0 = gr + (size_t)y * p.Wp + x, *rn = gr + (size_t)yn * p.Wp + x, *rs = gr + (size_t)ys * p.Wp + x;
+            int a = 2 * ((int)l0[1] - (int)l0[-1]) + ((int)ln[1] - (int)ln[-1]) + ((int)ls[1] - (int)ls[-1]);
+            int c = 2 * ((int)r0[1] - (int)r0[-1]) + ((int)rn[1] - (int)rn[-1]) + ((int)rs[1] - (int)rs[-1]);
+            a = min(max(a, -ft), ft) + ft;
+            c = min(max(c, -ft), ft) + ft;
+            vl = (unsigned)a | ((unsigned)l0[0] << 16);
+            vr = (unsigned)c | ((unsigned)r0[0] << 16);
+        }
+        aL[x] = vl; aR[x] = vr;
+    }
+    __syncthreads();
+    for (int x = tid; x < W; x += nt) {
+#pragma unroll
+        for (int s = 0; s < 2; s++) {
+            const unsigned* a = s ? aR : aL;
+            unsigned u = a[x];
+            unsigned ul = x > 0 ? (((u + a[x - 1]) >> 1) & 0x7fff7fffu) : u;
+            unsigned ur = x < W - 1 ? (((u + a[x + 1]) >> 1) & 0x7fff7fffu) : u;
+            unsigned u0 = __vimin3_s16x2(ul, ur, u), u1 = __vimax3_s16x2(ul, ur, u);
+            uint4 o = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
+            if (s) Rpk[x] = o; else Lpk[x] = o;
+        }
+    }
+    __syncthreads();
+
+    const int d = tid;
+    const int W1 = p.W1, Dp = p.Dp;
+    int16_t* out = hsum + (((size_t)b * H + y) * W1) * Dp + d;
+    if (d >= p.D) {
+        for (int xp = 0; xp < W1; xp++) out[(size_t)xp * Dp] = 0;
+        return;
+    }
+    const int dd = p.minD + d, minX1 = p.minX1;
+    auto pixcost = [&](int xp) -> int {
+        const int x = xp + minX1;
+        const uint4 l = Lpk[x];
+        const uint4 r = Rpk[x - dd];
+        unsigned c0 = __vimax3_s16x2_relu(__vadd2(l.x, r.w), __vadd2(r.y, l.z), 0u);   // max(0, u - v1, v0 - u)
+        unsigned c1 = __vimax3_s16x2_relu(__vadd2(r.x, l.w), __vadd2(l.y, r.z), 0u);   // max(0, v - u1, u0 - v)
+        unsigned m = __vmins2(c0, c1);
+        return (int)(m & 0xffffu) + (int)(m >> 18);
+    };
+    uint8_t* ring = ringbuf + d;
+    const int SW2 = p.SW2, rmask = p.ring - 1;
+    const int last = min(SW2, W1 - 1);
+    int run = 0, pixLast = 0;
+    for (int k = 0; k <= last; k++) {
+        int c = pixcost(k);
+        ring[(k & rmask) * Dp] = (uint8_t)c;
+        run += (k == 0) ? c * (SW2 + 1) : c;
+        pixLast = c;
+    }
+    run += (SW2 - last) * pixLast;
+    out[0] = (int16_t)run;
+    for (int xp = 1; xp < W1; xp++) {
+        const int ia = xp + SW2;
+        int add;
+        if (ia <= W1 - 1) { add = pixcost(ia); ring[(ia & rmask) * Dp] = (uint8_t)add; pixLast = add; }
+        else add = pixLast;
+        const int is = max(xp - SW2 - 1, 0);
+        run += add - (int)ring[(is & rmask) * Dp];
+        out[(size_t)xp * Dp] = (int16_t)run;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// A.3 (vertical): C[0] = s16(P2) (+) hsum[0]*(SH2+1) (+) hsum[1..SH2];  C[y] = sat(sat(C[y-1] - old) + new)
+// (x' = 0: sat(sat(C[y-1] + new) - old)).
+// One thread per (frame, x', 4 disparities) marching down the rows.
+__device__ __forceinline__ int sat16i(int v) { return min(max(v, -32768), 32767); }
+__device__ __forceinline__ int lo16(unsigned w) { return (int)(short)(w & 0xffffu); }
+__device__ __forceinline__ int hi16(unsigned w) { return ((int)w) >> 16; }
+__device__ __forceinline__ unsigned pack16(int lo, int hi) { return ((unsigned)lo & 0xffffu) | ((unsigned)hi << 16); }
+
+__global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B)
+{
+    const size_t rowWords = (size_t)p.W1 * p.Dp / 4;          // uint2 words per row
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= rowWords * B) return;
+    const int b = (int)(t / rowWords);
+    const size_t i = t % rowWords;
+    const int H = p.H, SH2 = p.SH2;
+    const uint2* hs = (const uint2*)hsum + (size_t)b * H * rowWords + i;
+    uint2* cs = (uint2*)C + (size_t)b * H * rowWords + i;
+    // OpenCV evaluates the first computed column (x' = 0) as (Cprev + new) - old and all others as (Cprev - old) + new;
+    // in saturating int16 lanes the two differ once C sticks at 32767 (pinned by tests/golden/satdrift_d32_bs27.npz).
+    const bool first = i < (size_t)p.Dp / 4;
+    int c[4] = { p.P2s, p.P2s, p.P2s, p.P2s };
+    for (int k = 0; k <= SH2; k++) {
+        uint2 h = hs[(size_t)min(k, H - 1) * rowWords];
+        const int sc = (k == 0) ? SH2 + 1 : 1;
+        int hv[4] = { lo16(h.x), hi16(h.x), lo16(h.y), hi16(h.y) };
+#pragma unroll
+        for (int j = 0; j < 4; j++) c[j] = sat16i(c[j] + sat16i(hv[j] * sc));
+    }
+    cs[0] = make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3]));
+    for (int y = 1; y < H; y++) {
+        uint2 ho = hs[(size_t)max(y - SH2 - 1, 0) * rowWords];
+        uint2 hn = hs[(size_t)min(y + SH2, H - 1) * rowWords];
+        int ov[4] = { lo16(ho.x), hi16(ho.x), lo16(ho.y), hi16(ho.y) };
+        int nv[4] = { lo16(hn.x), hi16(hn.x), lo16(hn.y), hi16(hn.y) };
+#pragma unroll
+        for (int j = 0; j < 4; j++) c[j] = first ? sat16i(sat16i(c[j] + nv[j]) - ov[j]) : sat16i(sat16i(c[j] - ov[j]) + nv[j]);
+        cs[(size_t)y * rowWords] = make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3]));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Path-cost update of A.4 for one disparity, int32 lanes with the int16 saturations made explicit:
+//   m = min(Lp[d], sat(Lp[d-1]+P1s), sat(Lp[d+1]+P1s), delta);  L = sat(sat(m - delta) + C)
+// min(sat(a+k), sat(b+k)) == sat(min(a,b)+k) (monotone); the upper clamp of that term is absorbed by
+// min(., Lp[d]) (Lp[d] <= 32767); m <= delta so m - delta <= 0 and only lower clamps remain.
+__device__ __forceinline__ int path_cost(int lm1, int l0, int lp1, int delta, int P1s, int c)
+{
+    int n = max(min(lm1, lp1) + P1s, -32768);
+    int m = min(min(n, l0), delta);
+    int t = max(m - delta, -32768);
+    return max(t + c, -32768);
+}
+
+template <int DPL>
+__device__ __forceinline__ void load_vec(const int16_t* p, int (&v)[DPL])
+{
+    // DPL consecutive int16 at p (p is DPL*2-byte aligned; DPL in {2,4,6,8})
+    const unsigned* w = (const unsigned*)p;
+    if (DPL == 2) { unsigned a = w[0]; v[0] = lo16(a); v[1] = hi16(a); }
+    else if (DPL == 4) { uint2 a = *(const uint2*)p; v[0] = lo16(a.x); v[1] = hi16(a.x); v[2] = lo16(a.y); v[3] = hi16(a.y); }
+    else if (DPL == 8) { uint4 a = *(const uint4*)p; v[0] = lo16(a.x); v[1] = hi16(a.x); v[2] = lo16(a.y); v[3] = hi16(a.y);
+                         v[4] = lo16(a.z); v[5] = hi16(a.z); v[6] = lo16(a.w); v[7] = hi16(a.w); }
+    else {
+#pragma unroll
+        for (int i = 0; i < DPL / 2; i++) { unsigned a = w[i]; v[2 * i] = lo16(a); v[2 * i + 1] = hi16(a); }
+    }
+}
+template <int DPL>
+__device__ __forceinline__ void load_vec_cg(const int16_t* p, int (&v)[DPL])
+{
+    const unsigned* w = (const unsigned*)p;
+    if (DPL == 4) { uint2 a = __ldcg((const uint2*)p); v[0] = lo16(a.x); v[1] = hi16(a.x); v[2] = lo16(a.y); v[3] = hi16(a.y); }
+    else if (DPL == 8) { uint4 a = __ldcg((const uint4*)p); v[0] = lo16(a.x); v[1] = hi16(a.x); v[2] = lo16(a.y); v[3] = hi16(a.y);
+                         v[4] = lo16(a.z); v[5] = hi16(a.z); v[6] = lo16(a.w); v[7] = hi16(a.w); }
+    else {
+#pragma unroll
+        for (int i = 0; i < DPL / 2; i++) { unsigned a = __ldcg(w + i); v[2 * i] = lo16(a); v[2 * i + 1] = hi16(a); }
+    }
+}
+template <int DPL>
+__device__ __forceinline__ void store_vec(int16_t* p, const int (&v)[DPL])
+{
+    unsigned* w = (unsigned*)p;
+    if (DPL == 4) *(uint2*)p = make_uint2(pack16(v[0], v[1]), pack16(v[2], v[3]));
+    else if (DPL == 8) *(uint4*)p = make_uint4(pack16(v[0], v[1]), pack16(v[2], v[3]), pack16(v[4], v[5]), pack16(v[6], v[7]));
+    else {
+#pragma unroll
+        for (int i = 0; i < DPL / 2; i++) w[i] = pack16(v[2 * i], v[2 * i + 1]);
+    }
+}
+
+// A.5 (first half) for one column held by a warp: S[i] is the aggregated cost of disparity lane*DPL+i.
+// Writes raw disparity (x16) or INVALID, and aux = (minS << 16) | best for accepted pixels (0x7fffffff otherwise).
+template <int DPL>
+__device__ __forceinline__ void wta_column(const int (&S)[DPL], int lane, const SgbmDev& p, int16_t* rawPix, int* auxPix)
+{
+    const int d0 = lane * DPL;
+    int key = 0x7fffffff;
+#pragma unroll
+    for (int i = 0; i < DPL; i++)
+        if (d0 + i < p.D) key = min(key, (int)(((unsigned)S[i] << 16) | (unsigned)(d0 + i)));
+    key = __reduce_min_sync(FULL, key);
+    const int minS = key >> 16, best = key & 0xffff;
+    bool bad = false;
+    const int lim = minS * 100, mul = 100 - p.uniq;
+#pragma unroll
+    for (int i = 0; i < DPL; i++) {
+        const int d = d0 + i;
+        if (d < p.D && S[i] * mul < lim && abs(best - d) > 1) bad = true;
+    }
+    const bool reject = __any_sync(FULL, bad) || (minS == CVR_MAX_COST);
+    int out = p.INVALID, aux = 0x7fffffff;
+    if (!reject) {               // warp-uniform
+        int dd = best * CVR_DISP_SCALE;
+        if (0 < best && best < p.D - 1) {
+            int a = 0, c = 0;
+#pragma unroll
+            for (int i = 0; i < DPL; i++) {
+                a += (d0 + i == best - 1) ? S[i] : 0;
+                c += (d0 + i == best + 1) ? S[i] : 0;
+            }
+            a = __reduce_add_sync(FULL, a);
+            c = __reduce_add_sync(FULL, c);
+            const int den = max(a + c - 2 * minS, 1);
+            dd += ((a - c) * CVR_DISP_SCALE + den) / (den * 2);
+        }
+        out = dd + p.minD * CVR_DISP_SCALE;
+        aux = (int)(((unsigned)minS << 16) | (unsigned)best);
+    }
+    if (lane == 0) { *rawPix = (int16_t)out; *auxPix = aux; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Horizontal path: one warp per (frame, row); sequential over x', state in registers.
+//   REVERSE = false:  ->  (A.4 r = 0)        REVERSE = true:  <-  (MODE_SGBM 5th path / MODE_HH pass-2 r = 0)
+//   accumulate: S = sat(S + L) (else S = L, the first path written);  WTA: winner-take-all on the final S.
+template <int DPL, bool REVERSE, bool WTA>
+__global__ void __launch_bounds__(128) k_path_h(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
+                                                int* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS)
+{
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (warp >= B * p.H) return;
+    const int b = warp / p.H, y = warp % p.H;
+    const int W1 = p.W1, Dp = p.Dp, D = p.D;
+    const size_t rowBase = (((size_t)b * p.H + y) * W1) * Dp + (size_t)lane * DPL;
+    const int16_t* Crow = C + rowBase;
+    int16_t* Srow = S + rowBase;
+    const int d0 = lane * DPL;
+    int Lp[DPL];
+#pragma unroll
+    for (int i = 0; i < DPL; i++) Lp[i] = (d0 + i < D) ? 0 : CVR_MAX_COST;
+    int minPrev = 0;
+    const int P1s = p.P1s, P2 = p.P2;
+    int xp = REVERSE ? W1 - 1 : 0;
+    const int dx = REVERSE ? -1 : 1;
+    int cN[DPL], sN[DPL];
+    load_vec<DPL>(Crow + (size_t)xp * Dp, cN);
+    if (accumulate) load_vec<DPL>(Srow + (size_t)xp * Dp, sN);
+    for (int step = 0; step < W1; step++, xp += dx) {
+        int c[DPL], s[DPL];
+#pragma unroll
+        for (int i = 0; i < DPL; i++) { c[i] = cN[i]; s[i] = accumulate ? sN[i] : 0; }
+        if (step + 1 < W1) {
+            load_vec<DPL>(Crow + (size_t)(xp + dx) * Dp, cN);
+            if (accumulate) load_vec<DPL>(Srow + (size_t)(xp + dx) * Dp, sN);
+        }
+        const int delta = (int)(short)(P2 + minPrev);
+        int left = __shfl_up_sync(FULL, Lp[DPL - 1], 1);
+        int right = __shfl_down_sync(FULL, Lp[0], 1);
+        if (lane == 0) left = CVR_MAX_COST;
+        if (lane == 31) right = CVR_MAX_COST;
+        int L[DPL];
+        int mn = CVR_MAX_COST;
+#pragma unroll
+        for (int i = 0; i < DPL; i++) {
+            const int lm1 = (i == 0) ? left : Lp[i - 1];
+            const int lp1 = (i == DPL - 1) ? right : Lp[i + 1];
+            int v = path_cost(lm1, Lp[i], lp1, delta, P1s, c[i]);
+            if (d0 + i >= D) v = CVR_MAX_COST;
+            L[i] = v;
+            mn = min(mn, v);
+            s[i] = sat16i(s[i] + v);
+        }
+        minPrev = __reduce_min_sync(FULL, mn);
+#pragma unroll
+        for (int i = 0; i < DPL; i++) Lp[i] = L[i];
+        if (!WTA || storeS) store_vec<DPL>(Srow + (size_t)xp * Dp, s);
+        if (WTA) wta_column<DPL>(s, lane, p, raw + ((size_t)b * p.H + y) * p.W + xp + p.minX1, aux + ((size_t)b * p.H + y) * W1 + xp);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Vertical path state: lr [B][2][W1+2][3][Dp] int16, minlr [B][2][W1+2][4] int.  Border columns and the
+// buffer read by the first row hold the "zero state": L = 0 for d < D (MAX_COST in the padding), minL = 0.
+__global__ void k_lr_init(int16_t* lr, int* minlr, SgbmDev p, int B)
+{
+    const size_t n = (size_t)B * 2 * (p.W1 + 2) * 3 * p.Dp;
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) lr[i] = ((int)(i % p.Dp) < p.D) ? 0 : CVR_MAX_COST;
+    const size_t m = (size_t)B * 2 * (p.W1 + 2) * 4;
+    if (i < m) minlr[i] = 0;
+}
+
+// The three paths that cross rows (A.4 r = 1: from (x'-1), r = 2: from (x'), r = 3: from (x'+1) of the previous
+// row), fused.  A cluster of CL CTAs owns one frame; CTA `rank` owns the column strip [c0, c1); the per-row
+// hand-over of the strip edges goes through the L2-resident state arrays, ordered by one cluster barrier per row.
+// UP = false: rows top-down (pass 1);  UP = true: bottom-up (MODE_HH pass 2).  S = sat(S + L1), + L2, + L3.
+template <int DPL, bool UP, bool WTA, int NT>
+__global__ void __launch_bounds__(NT) k_path_v(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* lr, int* minlr,
+                                               int16_t* __restrict__ raw, int* __restrict__ aux, SgbmDev p, int CL, int storeS)
+{
+    const int b = blockIdx.y, rank = blockIdx.x;
+    const int W1 = p.W1, Dp = p.Dp, D = p.D, H = p.H;
+    const int c0 = (int)(((long long)W1 * rank) / CL), c1 = (int)(((long long)W1 * (rank + 1)) / CL);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, NW = NT / 32;
+    const int d0 = lane * DPL;
+    const size_t colStride = (size_t)3 * Dp, bufStride = (size_t)(W1 + 2) * colStride;
+    int16_t* lrb = lr + (size_t)b * 2 * bufStride + (size_t)lane * DPL;
+    int* mlb = minlr + (size_t)b * 2 * (W1 + 2) * 4;
+    const int P1s = p.P1s, P2 = p.P2;
+    for (int t = 0; t < H; t++) {
+        const int y = UP ? H - 1 - t : t;
+        const int cur = t & 1, prev = cur ^ 1;
+        const size_t rowBase = (((size_t)b * H + y) * W1) * Dp + (size_t)lane * DPL;
+        const int16_t* lrPrev = lrb + (size_t)prev * bufStride;
+        int16_t* lrCur = lrb + (size_t)cur * bufStride;
+        const int* mlPrev = mlb + (size_t)prev * (W1 + 2) * 4;
+        int* mlCur = mlb + (size_t)cur * (W1 + 2) * 4;
+        for (int xp = c0 + warp; xp < c1; xp += NW) {
+            int c[DPL], s[DPL];
+            load_vec<DPL>(C + rowBase + (size_t)xp * Dp, c);
+            load_vec<DPL>(S + rowBase + (size_t)xp * Dp, s);
+            int mins[3];
+#pragma unroll
+            for (int r = 0; r < 3; r++) {
+                const int sx = xp + r;                      // state column index (x'+1) of the source: x'-1, x', x'+1
+                int Lp[DPL];
+                load_vec_cg<DPL>(lrPrev + (size_t)sx * colStride + (size_t)r * Dp, Lp);
+                const int delta = (int)(short)(P2 + __ldcg(mlPrev + sx * 4 + r));
+                int left = __shfl_up_sync(FULL, Lp[DPL - 1], 1);
+                int right = __shfl_down_sync(FULL, Lp[0], 1);
+                if (lane == 0) left = CVR_MAX_COST;
+                if (lane == 31) right = CVR_MAX_COST;
+                int L[DPL];
+                int mn = CVR_MAX_COST;
+#pragma unroll
+                for (int i = 0; i < DPL; i++) {
+                    const int lm1 = (i == 0) ? left : Lp[i - 1];
+                    const int lp1 = (i == DPL - 1) ? right : Lp[i + 1];
+                    int v = path_cost(lm1, Lp[i], lp1, delta, P1s, c[i]);
+                    if (d0 + i >= D) v = CVR_MAX_COST;
+                    L[i] = v;
+                    mn = min(mn, v);
+                    s[i] = sat16i(s[i] + v);
+                }
+                mins[r] = __reduce_min_sync(FULL, mn);
+                store_vec<DPL>(lrCur + (size_t)(xp + 1) * colStride + (size_t)r * Dp, L);
+            }
+            if (lane < 3) mlCur[(xp + 1) * 4 + lane] = (lane == 0) ? mins[0] : (lane == 1 ? mins[1] : mins[2]);
+            if (!WTA || storeS) store_vec<DPL>(S + rowBase + (size_t)xp * Dp, s);
+            if (WTA) wta_column<DPL>(s, lane, p, raw + ((size_t)b * H + y) * p.W + xp + p.minX1, aux + ((size_t)b * H + y) * W1 + xp);
+        }
+        if (CL > 1) cg::this_cluster().sync(); else __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// A.5 second half.  One CTA per (row, frame).  disp2[x2] is the `best` of the pixel with the smallest minS
+// among those mapping to x2, the largest x' winning ties (the sequential right-to-left scan with strict '>').
+__global__ void k_lrcheck(const int16_t* __restrict__ raw, const int* __restrict__ aux, int16_t* __restrict__ disp, SgbmDev p)
+{
+    extern __shared__ unsigned key[];
+    const int y = blockIdx.x, b = blockIdx.y, W = p.W, W1 = p.W1;
+    const size_t row = (size_t)b * p.H + y;
+    const int* auxr = aux + row * W1;
+    const int16_t* rawr = raw + row * W;
+    int16_t* out = disp + row * W;
+    for (int x = threadIdx.x; x < W; x += blockDim.x) key[x] = 0xffffffffu;
+    __syncthreads();
+    for (int xp = threadIdx.x; xp < W1; xp += blockDim.x) {
+        const int a = auxr[xp];
+        if (a == 0x7fffffff) continue;
+        const int minS = a >> 16, best = a & 0xffff;
+        const int x2 = xp + p.minX1 - best - p.minD;
+        // minS == 32767 is always rejected upstream, so (minS + 32768) <= 65534 and a real key never equals the sentinel
+        atomicMin(&key[x2], ((unsigned)(minS + 32768) << 16) | (unsigned)(0xffff - xp));
+    }
+    __syncthreads();
+    for (int x = threadIdx.x; x < W; x += blockDim.x) {
+        int v = p.INVALID;
+        if (x >= p.minX1 && x < p.maxX1) {
+            const int d1 = rawr[x];
+            v = d1;
+            if (d1 != p.INVALID) {
+                const int _d = d1 >> 4, d_ = (d1 + CVR_DISP_SCALE - 1) >> 4;
+                const int _x = x - _d, x_ = x - d_;
+                bool f1 = false, f2 = false;
+                if (0 <= _x && _x < W) {
+                    const unsigned k = key[_x];
+                    if (k != 0xffffffffu) { const int d2 = (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD; f1 = d2 >= p.minD && abs(d2 - _d) > p.d12; }
+                }
+                if (0 <= x_ && x_ < W) {
+                    const unsigned k = key[x_];
+                    if (k != 0xffffffffu) { const int d2 = (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD; f2 = d2 >= p.minD && abs(d2 - d_) > p.d12; }
+                }
+                if (f1 && f2) v = p.INVALID;
+            }
+        }
+        out[x] = (int16_t)v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// A.6: 3x3 median, BORDER_REPLICATE; INVALID participates as an ordinary value.
+__device__ __forceinline__ void srt(int& a, int& b) { int t = min(a, b); b = max(a, b); a = t; }
+__global__ void k_median3(const int16_t* __restrict__ src, int16_t* __restrict__ dst, int W, int H)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    if (x >= W) return;
+    const int16_t* s = src + (size_t)b * W * H;
+    int v[9];
+#pragma unroll
+    for (int dy = -1; dy <= 1; dy++) {
+        const int yy = min(max(y + dy, 0), H - 1);
+#pragma unroll
+        for (int dx = -1; dx <= 1; dx++) v[(dy + 1) * 3 + dx + 1] = s[(size_t)yy * W + min(max(x + dx, 0), W - 1)];
+    }
+    // 19-exchange median-of-9 network
+    srt(v[1], v[2]); srt(v[4], v[5]); srt(v[7], v[8]); srt(v[0], v[1]); srt(v[3], v[4]); srt(v[6], v[7]);
+    srt(v[1], v[2]); srt(v[4], v[5]); srt(v[7], v[8]); srt(v[0], v[3]); srt(v[5], v[8]); srt(v[4], v[7]);
+    srt(v[3], v[6]); srt(v[1], v[4]); srt(v[2], v[5]); srt(v[4], v[7]); srt(v[4], v[2]); srt(v[6], v[4]);
+    srt(v[4], v[2]);
+    dst[(size_t)b * W * H + (size_t)y * W + x] = (int16_t)v[4];
+}
+
+// ------------------------------------------------------------------------------------------------
+// A.7: speckle filter = connected components (4-neighbours, |dv| <= maxDiff, value != newVal) of size
+// <= maxSize are erased.  Union-find with atomicMin roots; the result does not depend on the merge order.
+__device__ __forceinline__ int uf_find(const int* L, int i)
+{
+    int j;
+    while ((j = L[i]) != i) i = j;
+    return i;
+}
+__device__ __forceinline__ void uf_union(int* L, int a, int b)
+{
+    bool done;
+    do {
+        a = uf_find(L, a); b = uf_find(L, b);
+        if (a < b) { int old = atomicMin(&L[b], a); done = (old == b); b = old; }
+        else if (b < a) { int old = atomicMin(&L[a], b); done = (old == a); a = old; }
+        else done = true;
+    } while (!done);
+}
+__global__ void k_ccl_init(const int16_t* __restrict__ img, int* __restrict__ label, int* __restrict__ size, int N, int newVal)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (i >= N) return;
+    const size_t o = (size_t)b * N + i;
+    label[o] = (img[o] != newVal) ? i : -1;
+    size[o] = 0;
+}
+__global__ void k_ccl_merge(const int16_t* __restrict__ img, int* label, int W, int H, int newVal, int maxDiff)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
+    if (x >= W) return;
+    const size_t fo = (size_t)b * W * H;
+    const int i = y * W + x;
+    const int v = img[fo + i];
+    if (v == newVal) return;
+    int* L = label + fo;
+    if (x + 1 < W) { const int q = img[fo + i + 1]; if (q != newVal && abs(v - q) <= maxDiff) uf_union(L, i, i + 1); }
+    if (y + 1 < H) { const int q = img[fo + i + W]; if (q != newVal && abs(v - q) <= maxDiff) uf_union(L, i, i + W); }
+}
+__global__ void k_ccl_count(int* label, int* size, int N)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (i >= N) return;
+    int* L = label + (size_t)b * N;
+    if (L[i] < 0) return;
+    const int r = uf_find(L, i);
+    L[i] = r;                       // roots stay fixed points, so concurrent flattening is safe
+    atomicAdd(&size[(size_t)b * N + r], 1);
+}
+__global__ void k_ccl_apply(int16_t* img, const int* __restrict__ label, const int* __restrict__ size, int N, int newVal, int maxSize)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (i >= N) return;
+    const size_t o = (size_t)b * N + i;
+    const int l = label[o];
+    if (l >= 0 && size[(size_t)b * N + l] <= maxSize) img[o] = (int16_t)newVal;
+}
+
+__global__ void k_fill_s16(int16_t* p, size_t n, int v)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = (int16_t)v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host-side launchers
+#define LAUNCH_CHECK(c)                                                                  \
+    do {                                                                                 \
+        (c)->launches++;                                                                 \
+        cudaError_t e__ = cudaGetLastError();                                            \
+        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
+    } while (0)
+
+int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t lfs, const uint8_t* right, size_t rstep,
+                    size_t rfs, int channels)
+{
+    const SgbmDev& p = c->sg;
+    const size_t gfs = (size_t)2 * p.H * p.Wp;
+    dim3 g(cvr_div_up(p.W, 256), p.H, B);
+    k_gray<<<g, 256, 0, c->stream>>>(left, lstep, lfs, channels, c->d_gray, p.Wp, gfs, p.W, p.H);
+    LAUNCH_CHECK(c);
+    k_gray<<<g, 256, 0, c->stream>>>(right, rstep, rfs, channels, c->d_gray + (size_t)p.H * p.Wp, p.Wp, gfs, p.W, p.H);
+    LAUNCH_CHECK(c);
+    return CVR_OK;
+}
+
+template <int DPL>
+static int launch_paths(cvr_ctx* c, int B, int storeS)
+{
+    const SgbmDev& p = c->sg;
+    const int hblocks = cvr_div_up(B * p.H, 4);
+    // vertical kernel geometry: a cluster of CL CTAs per frame; fewer, larger clusters when the batch is small
+    constexpr int NT = (DPL <= 4) ? 512 : 256;
+    int CL = 1;
+    while (CL < 8 && B * CL * 2 <= c->sm_count * 2 && (p.W1 / (CL * 2)) >= NT / 32) CL *= 2;
+    const size_t lrN = (size_t)B * 2 * (p.W1 + 2) * 3 * p.Dp;
+    auto launch_v = [&](bool up, bool wta) -> int {
+        k_lr_init<<<(unsigned)cvr_div_up_sz(lrN, 256), 256, 0, c->stream>>>(c->d_lr, c->d_minlr, p, B);
+        LAUNCH_CHECK(c);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(CL, B, 1);
+        cfg.blockDim = dim3(NT, 1, 1);
+        cfg.dynamicSmemBytes = 0;
+        cfg.stream = c->stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        cudaError_t e;
+        if (!up) e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, false, false, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS);
+        else if (wta) e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, true, true, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS);
+        else e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, true, false, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS);
+        c->launches++;
+        if (e != cudaSuccess) { c->err = std::string("k_path_v launch: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
+        return CVR_OK;
+    };
+    // pass 1: -> then the three downward paths
+    k_path_h<DPL, false, false><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, 0, 1);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "path_h_fwd");
+    int rc = launch_v(false, false);
+    if (rc) return rc;
+    cvr_stage_mark(c, "path_v_down");
+    if (p.mode == CVR_MODE_HH) {
+        k_path_h<DPL, true, false><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, 1, 1);
+        LAUNCH_CHECK(c);
+        cvr_stage_mark(c, "path_h_rev");
+        rc = launch_v(true, true);
+        if (rc) return rc;
+        cvr_stage_mark(c, "path_v_up_wta");
+    } else {
+        k_path_h<DPL, true, true><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, 1, storeS);
+        LAUNCH_CHECK(c);
+        cvr_stage_mark(c, "path_h_rev_wta");
+    }
+    return CVR_OK;
+}
+
+int cvr_launch_sgbm(cvr_ctx* c, int B)
+{
+    const SgbmDev& p = c->sg;
+    const size_t npix = (size_t)B * p.W * p.H;
+    const int storeS = 1;   // keep S for cvr_debug_fetch; the write is ~1/8 of the stage's traffic
+    if (p.W1 <= 0) {
+        k_fill_s16<<<(unsigned)cvr_div_up_sz(npix, 256), 256, 0, c->stream>>>(c->d_med, npix, p.INVALID);
+        LAUNCH_CHECK(c);
+        return CVR_OK;
+    }
+    // raw disparity: columns outside [minX1, maxX1) are never written by WTA
+    k_fill_s16<<<(unsigned)cvr_div_up_sz(npix, 256), 256, 0, c->stream>>>(c->d_raw, npix, p.INVALID);
+    LAUNCH_CHECK(c);
+    {
+        const size_t smem = (size_t)p.W * (2 * sizeof(uint4) + 2 * sizeof(unsigned)) + (size_t)p.ring * p.Dp;
+        static size_t smem_set = 0;
+        if (smem > 48 * 1024 && smem > smem_set) {
+            CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            smem_set = smem;
+        }
+        k_pix_hsum<<<dim3(p.H, B), p.Dp, smem, c->stream>>>(c->d_gray, (size_t)2 * p.H * p.Wp, c->d_volA, p);
+        LAUNCH_CHECK(c);
+        cvr_stage_mark(c, "pix_hsum");
+    }
+    {
+        const size_t nthreads = (size_t)p.W1 * p.Dp / 4 * B;
+        k_vsum<<<(unsigned)cvr_div_up_sz(nthreads, 128), 128, 0, c->stream>>>(c->d_volA, c->d_volC, p, B);
+        LAUNCH_CHECK(c);
+        cvr_stage_mark(c, "vsum");
+    }
+    int rc;
+    switch (p.Dp / 32) {
+        case 2: rc = launch_paths<2>(c, B, storeS); break;
+        case 4: rc = launch_paths<4>(c, B, storeS); break;
+        case 6: rc = launch_paths<6>(c, B, storeS); break;
+        case 8: rc = launch_paths<8>(c, B, storeS); break;
+        default: c->err = "unsupported padded disparity count"; return CVR_ERR_UNSUPPORTED;
+    }
+    if (rc) return rc;
+    k_lrcheck<<<dim3(p.H, B), 256, (size_t)p.W * sizeof(int), c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p);
+    LAUNCH_CHECK(c);
+    k_median3<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "lr_median");
+    if (c->prm.sgbm.speckle_window_size > 0) {
+        const int N = p.W * p.H;
+        const int maxDiff = CVR_DISP_SCALE * c->prm.sgbm.speckle_range;
+        k_ccl_init<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, N, p.INVALID);
+        LAUNCH_CHECK(c);
+        k_ccl_merge<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, p.W, p.H, p.INVALID, maxDiff);
+        LAUNCH_CHECK(c);
+        k_ccl_count<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_label, c->d_size, N);
+        LAUNCH_CHECK(c);
+        k_ccl_apply<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, N, p.INVALID, c->prm.sgbm.speckle_window_size);
+        LAUNCH_CHECK(c);
+        cvr_stage_mark(c, "speckle");
+    }
+    return CVR_OK;
+}

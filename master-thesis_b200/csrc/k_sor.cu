@@ -1,0 +1,253 @@
+// k_sor.cu -- pcl::StatisticalOutlierRemoval<PointXYZRGB> for the call sites
+// cv_reconstruct/src/point_cloud/PointCloudPostProcessor.cpp:20-24, 38-41 (k = outlier_min_k, alpha = outlier_std_threshold)
+// and cv_reconstruct/src/system/MappingSystem.cpp:65-69.
+//   uniform grid over the cloud -> counting sort of points by cell -> exact k-nearest-neighbour search by
+//   expanding cubic shells until the k-th distance is provably final -> mean distance per point ->
+//   global mean / sample sigma in f64 (fixed-order reduction) -> ordered compaction of the kept points.
+// Squared distances are accumulated x,y,z in f32 without FMA (FLANN L2 on a CPU build without -mfma).
+#include "cvr_internal.cuh"
+#include "cvr_scan.cuh"
+#include <float.h>
+
+#define LAUNCH_CHECK(c)                                                                  \
+    do {                                                                                 \
+        (c)->launches++;                                                                 \
+        cudaError_t e__ = cudaGetLastError();                                            \
+        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
+    } while (0)
+
+struct SorGrid {
+    float mn[3];
+    float cell, inv;
+    int dim[3];
+    int ncell;
+    int n;
+};
+
+__global__ void k_sor_grid(const VoxBox* box, const int* nPtr, SorGrid* grid, int* ncellOut, int cap, int B)
+{
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    SorGrid g;
+    g.n = nPtr[b];
+    float ext[3], emax = 0.f;
+    for (int k = 0; k < 3; k++) {
+        g.mn[k] = g.n > 0 ? ord2f(box[b].mn[k]) : 0.f;
+        const float mx = g.n > 0 ? ord2f(box[b].mx[k]) : 0.f;
+        ext[k] = mx - g.mn[k];
+        emax = fmaxf(emax, ext[k]);
+    }
+    if (!(emax > 0.f)) emax = 1.f;
+    double vol = 1.0;
+    for (int k = 0; k < 3; k++) { ext[k] = fmaxf(ext[k], emax * 1e-3f); vol *= (double)ext[k]; }
+    // about two points per cell on a volume-filling cloud; surface-like clouds end up sparser, which only costs time
+    float s = (float)cbrt(2.0 * vol / (double)max(g.n, 1));
+    s = fmaxf(s, emax * 1e-4f);
+    for (int it = 0; it < 8; it++) {
+        long long tot = 1;
+        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
+        if (tot <= cap) break;
+        s *= 1.3f;
+    }
+    g.cell = s; g.inv = 1.0f / s;
+    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
+    grid[b] = g;
+    ncellOut[b] = g.ncell;
+}
+__device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, float z, int& cx, int& cy, int& cz)
+{
+    cx = min(max((int)((x - g.mn[0]) * g.inv), 0), g.dim[0] - 1);
+    cy = min(max((int)((y - g.mn[1]) * g.inv), 0), g.dim[1] - 1);
+    cz = min(max((int)((z - g.mn[2]) * g.inv), 0), g.dim[2] - 1);
+}
+__global__ void k_sor_zero(int* a, size_t stride, const int* lenPtr, int extra)
+{
+    const int b = blockIdx.y, len = lenPtr[b] + extra;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) a[(size_t)b * stride + i] = 0;
+}
+__global__ void k_sor_cellcount(const cvr_point* __restrict__ pts, size_t stride, const SorGrid* __restrict__ grid, int* cellcnt, size_t cellStride,
+                                int* __restrict__ cellOfPt, size_t ptStride)
+{
+    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    const SorGrid g = grid[b];
+    if (i >= g.n) return;
+    const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
+    int cx, cy, cz;
+    sor_cell(g, q.x, q.y, q.z, cx, cy, cz);
+    const int cid = (cz * g.dim[1] + cy) * g.dim[0] + cx;
+    cellOfPt[(size_t)b * ptStride + i] = cid;
+    atomicAdd(&cellcnt[(size_t)b * cellStride + cid], 1);
+}
+__global__ void k_sor_scatter(const cvr_point* __restrict__ pts, size_t stride, const SorGrid* __restrict__ grid, const int* __restrict__ cellstart,
+                              int* cellfill, size_t cellStride, const int* __restrict__ cellOfPt, size_t ptStride, float4* __restrict__ spts)
+{
+    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= grid[b].n) return;
+    const int cid = cellOfPt[(size_t)b * ptStride + i];
+    const int pos = cellstart[(size_t)b * cellStride + cid] + atomicAdd(&cellfill[(size_t)b * cellStride + cid], 1);
+    float4 q = *(const float4*)(pts + (size_t)b * stride + i);
+    q.w = __int_as_float(i);
+    spts[(size_t)b * ptStride + pos] = q;
+}
+
+// One thread per query point (in cell-sorted order).  best[] holds the k+1 smallest squared distances seen,
+// ascending; the query itself (distance 0) is one of them, exactly like nearestKSearch(i, k+1).
+template <int KCAP>
+__global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
+                                                 const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
+{
+    const int b = blockIdx.y, t = blockIdx.x * blockDim.x + threadIdx.x;
+    const SorGrid g = grid[b];
+    if (t >= g.n) return;
+    const float4* sp = spts + (size_t)b * ptStride;
+    const int* cs = cellstart + (size_t)b * cellStride;
+    const float4 q = sp[t];
+    const int orig = __float_as_int(q.w);
+    float* out = meand + (size_t)b * ptStride;
+    const int K1 = k + 1;
+    if (g.n < K1) { out[orig] = 0.f; return; }
+    float best[KCAP];
+    int cnt = 0;
+    int cx, cy, cz;
+    sor_cell(g, q.x, q.y, q.z, cx, cy, cz);
+    const int Rmax = max(max(g.dim[0], g.dim[1]), g.dim[2]);
+    for (int R = 0; R <= Rmax; R++) {
+        const int z0 = max(cz - R, 0), z1 = min(cz + R, g.dim[2] - 1);
+        const int y0 = max(cy - R, 0), y1 = min(cy + R, g.dim[1] - 1);
+        for (int iz = z0; iz <= z1; iz++) {
+            const bool zf = (iz == cz - R) || (iz == cz + R);
+            for (int iy = y0; iy <= y1; iy++) {
+                const bool face = zf || (iy == cy - R) || (iy == cy + R);
+                // on a z/y face of the shell the whole x run belongs to it; elsewhere only the two x end caps
+                const int xs = cx - R, xe = cx + R;
+                for (int part = 0; part < 2; part++) {
+                    int xa, xb;
+                    if (face) { if (part) break; xa = max(xs, 0); xb = min(xe, g.dim[0] - 1); }
+                    else {
+                        const int xx = part ? xe : xs;
+                        if (part && R == 0) break;
+                        if (xx < 0 || xx >= g.dim[0]) continue;
+                        xa = xb = xx;
+                    }
+                    if (xa > xb) continue;
+                    const int rowc = (iz * g.dim[1] + iy) * g.dim[0];
+                    const int jb = cs[rowc + xa], je = cs[rowc + xb + 1];     // cells of one x run are contiguous in the sorted order
+                    for (int j = jb; j < je; j++) {
+                        const float4 p = sp[j];
+                        const float dx = __fsub_rn(q.x, p.x), dy = __fsub_rn(q.y, p.y), dz = __fsub_rn(q.z, p.z);
+                        float d2 = __fmul_rn(dx, dx);
+                        d2 = __fadd_rn(d2, __fmul_rn(dy, dy));
+                        d2 = __fadd_rn(d2, __fmul_rn(dz, dz));
+                        if (cnt < K1) { int pz = cnt++; while (pz > 0 && best[pz - 1] > d2) { best[pz] = best[pz - 1]; pz--; } best[pz] = d2; }
+                        else if (d2 < best[K1 - 1]) { int pz = K1 - 1; while (pz > 0 && best[pz - 1] > d2) { best[pz] = best[pz - 1]; pz--; } best[pz] = d2; }
+                    }
+                }
+            }
+        }
+        if (cnt == K1) {
+            // every unvisited point lies outside the cube of half-width R*cell around the query's cell, hence farther
+            // than R*cell; the 1e-5 margin covers the f32 rounding of both sides
+            const float lim = (float)R * g.cell;
+            if (best[K1 - 1] <= lim * lim * (1.0f - 1e-5f)) break;
+        }
+    }
+    double s = 0.0;
+    for (int j = 1; j < K1; j++) s = __dadd_rn(s, (double)__fsqrt_rn(best[j]));
+    out[orig] = (float)__ddiv_rn(s, (double)k);
+}
+
+// mean / sample variance over all mean distances, f64, fixed reduction order (deterministic).
+__global__ void __launch_bounds__(1024) k_sor_stats(const float* __restrict__ meand, size_t ptStride, const int* __restrict__ nPtr, int k, double alpha, SorStats* st)
+{
+    __shared__ double ss[1024], sq[1024];
+    const int b = blockIdx.x, n = nPtr[b];
+    const float* d = meand + (size_t)b * ptStride;
+    double s = 0.0, q = 0.0;
+    for (int i = threadIdx.x; i < n; i += 1024) { const float v = d[i]; s = __dadd_rn(s, (double)v); q = __dadd_rn(q, (double)__fmul_rn(v, v)); }
+    ss[threadIdx.x] = s; sq[threadIdx.x] = q;
+    __syncthreads();
+    for (int o = 512; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { ss[threadIdx.x] = __dadd_rn(ss[threadIdx.x], ss[threadIdx.x + o]); sq[threadIdx.x] = __dadd_rn(sq[threadIdx.x], sq[threadIdx.x + o]); }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        const int valid = (n >= k + 1) ? n : 0;
+        const double sum = ss[0], sqs = sq[0];
+        const double mean = __ddiv_rn(sum, (double)valid);
+        const double var = __ddiv_rn(__dsub_rn(sqs, __ddiv_rn(__dmul_rn(sum, sum), (double)valid)), __dsub_rn((double)valid, 1.0));
+        const double thr = __dadd_rn(mean, __dmul_rn(alpha, sqrt(var)));
+        st[b].sum = sum; st[b].sq = sqs; st[b].thr = thr; st[b].valid = valid;
+    }
+}
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_count(const float* __restrict__ meand, size_t ptStride, const int* __restrict__ nPtr,
+                                                             const SorStats* __restrict__ st, int* blkcnt, size_t cntStride)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
+    const int f = (i < nPtr[b]) && !((double)meand[(size_t)b * ptStride + i] > st[b].thr);
+    int tot;
+    block_excl_scan(f, ws, &tot);
+    if (threadIdx.x == 0) blkcnt[(size_t)b * cntStride + blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_write(const cvr_point* __restrict__ pts, size_t stride, const float* __restrict__ meand, size_t ptStride,
+                                                             const int* __restrict__ nPtr, SorStats* st, const int* __restrict__ blkoff, size_t cntStride,
+                                                             int nblk, cvr_point* __restrict__ out, size_t outStride, int* __restrict__ nOut)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
+    const int f = (i < nPtr[b]) && !((double)meand[(size_t)b * ptStride + i] > st[b].thr);
+    const int e = block_excl_scan(f, ws, nullptr);
+    if (f) out[(size_t)b * outStride + blkoff[(size_t)b * cntStride + blockIdx.x] + e] = pts[(size_t)b * stride + i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) { const int m = blkoff[(size_t)b * cntStride + nblk]; nOut[b] = m; st[b].kept = m; }
+}
+
+int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, int /*unused*/)
+{
+    const int maxN = c->maxN;
+    const size_t ptStride = (size_t)maxN;
+    const int cap = c->sor_grid_cap;
+    const size_t cellStride = (size_t)cap + 2;
+    const int k = c->cl.sor_k;
+    if (k < 1 || k + 1 > 320) { c->err = "sor_mean_k must be in [1, 319]"; return CVR_ERR_UNSUPPORTED; }
+    VoxBox* box = (VoxBox*)c->d_flags;
+    SorGrid* grid = (SorGrid*)(c->d_flags + (size_t)c->maxB * 16);
+    int* ncell = c->d_flags + (size_t)c->maxB * 32;
+    int* cellstart = c->d_cellstart;
+    int* cellfill = c->d_cellstart + (size_t)c->maxB * cellStride;
+    k_bbox_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, B);
+    LAUNCH_CHECK(c);
+    k_bbox_minmax<<<dim3(64, B), 256, 0, c->stream>>>(in, in_stride, n_in, box);
+    LAUNCH_CHECK(c);
+    k_sor_grid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, n_in, grid, ncell, cap, B);
+    LAUNCH_CHECK(c);
+    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellstart, cellStride, ncell, 1);
+    LAUNCH_CHECK(c);
+    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellfill, cellStride, ncell, 1);
+    LAUNCH_CHECK(c);
+    k_sor_cellcount<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
+    LAUNCH_CHECK(c);
+    k_scan_excl<<<B, 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, 1);
+    LAUNCH_CHECK(c);
+    k_sor_scatter<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
+    LAUNCH_CHECK(c);
+    const float4* sp = c->d_spts;
+    dim3 g(cvr_div_up(maxN, 128), B);
+    if (k + 1 <= 32) k_sor_knn<32><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    else if (k + 1 <= 64) k_sor_knn<64><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    else if (k + 1 <= 128) k_sor_knn<128><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    else k_sor_knn<320><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    LAUNCH_CHECK(c);
+    k_sor_stats<<<B, 1024, 0, c->stream>>>(c->d_meand, ptStride, n_in, k, c->cl.sor_alpha, c->d_sstats);
+    LAUNCH_CHECK(c);
+    const int nblk = cvr_div_up(maxN, CVR_SEL_BLOCK);
+    const size_t cntStride = (size_t)nblk + 1;
+    k_sor_count<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride);
+    LAUNCH_CHECK(c);
+    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
+    LAUNCH_CHECK(c);
+    k_sor_write<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(in, in_stride, c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride, nblk,
+                                                                c->d_sorout, (size_t)maxN, c->d_nout);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "sor");
+    return CVR_OK;
+}

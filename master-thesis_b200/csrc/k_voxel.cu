@@ -1,0 +1,218 @@
+// k_voxel.cu -- pcl::VoxelGrid<PointXYZRGB>::applyFilter for the call site
+// cv_reconstruct/src/system/MappingSystem.cpp:297-300 (setLeafSize(0.2,0.2,0.2)).
+//   bounding box -> int32 voxel index per point -> stable LSD radix sort of (index, point id) ->
+//   segment heads -> one thread per voxel accumulates the centroid in sorted (= point id) order in f32.
+// The sort is hand-written: 8-bit digits, one warp per 512-element run, __match_any_sync ranking (stable).
+#include "cvr_internal.cuh"
+#include "cvr_scan.cuh"
+#include <float.h>
+
+#define LAUNCH_CHECK(c)                                                                  \
+    do {                                                                                 \
+        (c)->launches++;                                                                 \
+        cudaError_t e__ = cudaGetLastError();                                            \
+        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
+    } while (0)
+
+#define RS_WARP_ELEMS 512            // elements ranked by one warp per pass
+#define RS_BLOCK_WARPS 8
+
+__global__ void k_vox_setup(const VoxBox* box, const int* nPtr, VoxelHdr* hdr, float lx, float ly, float lz, int B)
+{
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    VoxelHdr h;
+    h.n = nPtr[b]; h.m = 0; h.passthrough = 0; h.maxkey = 0;
+    const float inv[3] = { __fdiv_rn(1.0f, lx), __fdiv_rn(1.0f, ly), __fdiv_rn(1.0f, lz) };
+    long long cells = 1;
+    for (int k = 0; k < 3; k++) {
+        h.mn[k] = h.n > 0 ? ord2f(box[b].mn[k]) : 0.f; h.mx[k] = h.n > 0 ? ord2f(box[b].mx[k]) : 0.f;
+        const long long dk = (long long)__fmul_rn(__fsub_rn(h.mx[k], h.mn[k]), inv[k]) + 1;
+        cells *= dk;                                       // PCL multiplies three int64 (each < 2^40 here would overflow only for absurd clouds)
+        h.minb[k] = (int)floorf(__fmul_rn(h.mn[k], inv[k]));
+        const int maxb = (int)floorf(__fmul_rn(h.mx[k], inv[k]));
+        h.div[k] = maxb - h.minb[k] + 1;
+    }
+    if (cells > 2147483647LL || cells <= 0) h.passthrough = 1;
+    hdr[b] = h;
+}
+__global__ void k_vox_keys(const cvr_point* __restrict__ pts, size_t stride, const VoxelHdr* __restrict__ hdr, float lx, float ly, float lz,
+                           uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, size_t kvStride)
+{
+    const int b = blockIdx.y;
+    const VoxelHdr h = hdr[b];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= h.n) return;
+    const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
+    const int i0 = (int)floorf(__fmul_rn(q.x, __fdiv_rn(1.0f, lx))) - h.minb[0];
+    const int i1 = (int)floorf(__fmul_rn(q.y, __fdiv_rn(1.0f, ly))) - h.minb[1];
+    const int i2 = (int)floorf(__fmul_rn(q.z, __fdiv_rn(1.0f, lz))) - h.minb[2];
+    keys[(size_t)b * kvStride + i] = h.passthrough ? 0u : (uint32_t)(i0 + i1 * h.div[0] + i2 * h.div[0] * h.div[1]);
+    vals[(size_t)b * kvStride + i] = (uint32_t)i;
+}
+
+// ---- stable LSD radix sort, 8 bits per pass ------------------------------------------------------
+// hist layout per frame: [256][nRuns] (digit-major) so one exclusive scan yields each run's base per digit.
+__global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_hist(const uint32_t* __restrict__ keys, size_t kvStride, const int* __restrict__ nPtr,
+                                                                 int nOff, int shift, int* __restrict__ hist, size_t histStride, int nRuns)
+{
+    __shared__ int sh[RS_BLOCK_WARPS][256];
+    const int b = blockIdx.y, n = nPtr[b * nOff];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int run = blockIdx.x * RS_BLOCK_WARPS + w;
+    for (int k = lane; k < 256; k += 32) sh[w][k] = 0;
+    __syncwarp();
+    if (run < nRuns) {
+        const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
+        const uint32_t* kk = keys + (size_t)b * kvStride;
+        for (int i = beg + lane; i < end; i += 32) atomicAdd(&sh[w][(kk[i] >> shift) & 255], 1);
+        __syncwarp();
+        int* h = hist + (size_t)b * histStride;
+        for (int k = lane; k < 256; k += 32) h[(size_t)k * nRuns + run] = sh[w][k];
+    }
+}
+__global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_scatter(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+                                                                    uint32_t* __restrict__ okeys, uint32_t* __restrict__ ovals, size_t kvStride,
+                                                                    const int* __restrict__ nPtr, int nOff, int shift, const int* __restrict__ hist,
+                                                                    size_t histStride, int nRuns)
+{
+    __shared__ int base[RS_BLOCK_WARPS][256];
+    const int b = blockIdx.y, n = nPtr[b * nOff];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int run = blockIdx.x * RS_BLOCK_WARPS + w;
+    if (run >= nRuns) return;
+    const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
+    if (beg >= end) return;
+    const int* h = hist + (size_t)b * histStride;
+    for (int k = lane; k < 256; k += 32) base[w][k] = h[(size_t)k * nRuns + run];
+    __syncwarp();
+    const uint32_t* kk = keys + (size_t)b * kvStride; const uint32_t* vv = vals + (size_t)b * kvStride;
+    uint32_t* ok = okeys + (size_t)b * kvStride; uint32_t* ov = ovals + (size_t)b * kvStride;
+    for (int i0 = beg; i0 < end; i0 += 32) {
+        const int i = i0 + lane;
+        const bool act = i < end;
+        const unsigned amask = __ballot_sync(0xffffffffu, act);
+        if (act) {
+            const uint32_t key = kk[i], val = vv[i];
+            const int dg = (key >> shift) & 255;
+            const unsigned peers = __match_any_sync(amask, dg);
+            const int rank = __popc(peers & ((1u << lane) - 1));
+            const int dst = base[w][dg] + rank;
+            ok[dst] = key; ov[dst] = val;
+            __syncwarp(amask);
+            if (rank == 0) base[w][dg] += __popc(peers);
+        }
+        __syncwarp();
+    }
+}
+
+// ---- segments + centroids -------------------------------------------------------------------------
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_seg_count(const uint32_t* __restrict__ keys, size_t kvStride, const VoxelHdr* __restrict__ hdr,
+                                                             int* blkcnt, size_t cntStride)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.y, n = hdr[b].n, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
+    const uint32_t* k = keys + (size_t)b * kvStride;
+    const int f = (i < n) && (hdr[b].passthrough || i == 0 || k[i] != k[i - 1]);
+    int tot;
+    block_excl_scan(f, ws, &tot);
+    if (threadIdx.x == 0) blkcnt[(size_t)b * cntStride + blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_seg_write(const uint32_t* __restrict__ keys, size_t kvStride, VoxelHdr* hdr,
+                                                             const int* __restrict__ blkoff, size_t cntStride, int nblk, int* __restrict__ segstart, size_t segStride)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.y, n = hdr[b].n, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
+    const uint32_t* k = keys + (size_t)b * kvStride;
+    const int f = (i < n) && (hdr[b].passthrough || i == 0 || k[i] != k[i - 1]);
+    const int e = block_excl_scan(f, ws, nullptr);
+    int* ss = segstart + (size_t)b * segStride;
+    if (f) ss[blkoff[(size_t)b * cntStride + blockIdx.x] + e] = i;
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        const int m = blkoff[(size_t)b * cntStride + nblk];
+        ss[m] = n;
+        hdr[b].m = m;
+    }
+}
+// One thread per voxel: PCL's CentroidPoint accumulates x,y,z and r,g,b,a as floats in member order, divides by
+// the count, truncates the colours.  Member order = ascending point index (stable sort), as in the oracle.
+__global__ void k_vox_centroid(const cvr_point* __restrict__ pts, size_t stride, const uint32_t* __restrict__ vals, size_t kvStride,
+                               const VoxelHdr* __restrict__ hdr, const int* __restrict__ segstart, size_t segStride,
+                               cvr_point* __restrict__ out, size_t outStride, int* __restrict__ mOut)
+{
+    const int b = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+    const VoxelHdr h = hdr[b];
+    if (j == 0) mOut[b] = h.m;
+    if (j >= h.m) return;
+    const cvr_point* p = pts + (size_t)b * stride;
+    if (h.passthrough) { out[(size_t)b * outStride + j] = p[j]; return; }
+    const int* ss = segstart + (size_t)b * segStride;
+    const uint32_t* v = vals + (size_t)b * kvStride;
+    const int s = ss[j], e = ss[j + 1];
+    float sx = 0, sy = 0, sz = 0, sr = 0, sg = 0, sb = 0, sa = 0;
+    for (int i = s; i < e; i++) {
+        const cvr_point q = p[v[i]];
+        sx = __fadd_rn(sx, q.x); sy = __fadd_rn(sy, q.y); sz = __fadd_rn(sz, q.z);
+        sr = __fadd_rn(sr, (float)q.r); sg = __fadd_rn(sg, (float)q.g); sb = __fadd_rn(sb, (float)q.b); sa = __fadd_rn(sa, (float)q.a);
+    }
+    const float cnt = (float)(e - s);
+    cvr_point o;
+    o.x = __fdiv_rn(sx, cnt); o.y = __fdiv_rn(sy, cnt); o.z = __fdiv_rn(sz, cnt);
+    o.r = (uint8_t)__fdiv_rn(sr, cnt); o.g = (uint8_t)__fdiv_rn(sg, cnt); o.b = (uint8_t)__fdiv_rn(sb, cnt); o.a = (uint8_t)__fdiv_rn(sa, cnt);
+    out[(size_t)b * outStride + j] = o;
+}
+
+// Sort (keys, vals) of every frame: d_keys[0]/d_vals[0] -> ... ; returns the index (0/1) of the buffer holding the result.
+int cvr_radix_sort_pairs(cvr_ctx* c, int B, const int* nPtr, int nOff, int maxN, int passes, int* result_buf)
+{
+    const int nRuns = cvr_div_up(maxN, RS_WARP_ELEMS);
+    const size_t histStride = (size_t)256 * nRuns + 1;
+    const size_t kvStride = (size_t)c->maxN;
+    int cur = 0;
+    for (int pass = 0; pass < passes; pass++) {
+        const int shift = pass * 8;
+        dim3 g(cvr_div_up(nRuns, RS_BLOCK_WARPS), B);
+        k_rs_hist<<<g, RS_BLOCK_WARPS * 32, 0, c->stream>>>(c->d_keys[cur], kvStride, nPtr, nOff, shift, (int*)c->d_hist, histStride, nRuns);
+        LAUNCH_CHECK(c);
+        k_scan_excl<<<B, 1024, 0, c->stream>>>((int*)c->d_hist, histStride, 256 * nRuns, nullptr, 1);
+        LAUNCH_CHECK(c);
+        k_rs_scatter<<<g, RS_BLOCK_WARPS * 32, 0, c->stream>>>(c->d_keys[cur], c->d_vals[cur], c->d_keys[cur ^ 1], c->d_vals[cur ^ 1], kvStride, nPtr,
+                                                                nOff, shift, (const int*)c->d_hist, histStride, nRuns);
+        LAUNCH_CHECK(c);
+        cur ^= 1;
+    }
+    *result_buf = cur;
+    return CVR_OK;
+}
+
+int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in)
+{
+    const int maxN = c->maxN;
+    const size_t kvStride = (size_t)maxN;
+    const float lx = c->cl.leaf[0], ly = c->cl.leaf[1], lz = c->cl.leaf[2];
+    VoxBox* box = (VoxBox*)c->d_flags;    // d_flags is sized >= B * sizeof(VoxBox)
+    k_bbox_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, B);
+    LAUNCH_CHECK(c);
+    k_bbox_minmax<<<dim3(64, B), 256, 0, c->stream>>>(in, in_stride, n_in, box);
+    LAUNCH_CHECK(c);
+    k_vox_setup<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, n_in, c->d_vhdr, lx, ly, lz, B);
+    LAUNCH_CHECK(c);
+    k_vox_keys<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, c->d_vhdr, lx, ly, lz, c->d_keys[0], c->d_vals[0], kvStride);
+    LAUNCH_CHECK(c);
+    int buf = 0;
+    int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, &buf);
+    if (rc) return rc;
+    const int nblk = cvr_div_up(maxN, CVR_SEL_BLOCK);
+    const size_t cntStride = (size_t)nblk + 1;
+    k_seg_count<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, c->d_rowcnt, cntStride);
+    LAUNCH_CHECK(c);
+    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
+    LAUNCH_CHECK(c);
+    k_seg_write<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, c->d_rowcnt, cntStride, nblk, c->d_segstart, (size_t)maxN + 1);
+    LAUNCH_CHECK(c);
+    k_vox_centroid<<<dim3(cvr_div_up(maxN, 128), B), 128, 0, c->stream>>>(in, in_stride, c->d_vals[buf], kvStride, c->d_vhdr, c->d_segstart, (size_t)maxN + 1,
+                                                                         c->d_vox, (size_t)maxN, c->d_nvox);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "voxel");
+    return CVR_OK;
+}

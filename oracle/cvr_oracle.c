@@ -216,7 +216,11 @@ int orc_sgbm_compute(const uint8_t* left, size_t stepL, const uint8_t* right, si
             for (int k = 0; k <= SH2; k++) c = sat16(c + sat16(hsum[(size_t)imin(k, H - 1) * rowCells + i] * (k == 0 ? SH2 + 1 : 1)));
             C[i] = (int16_t)c;
             for (int y = 1; y < H; y++) {
-                c = sat16(sat16(c - hsum[(size_t)imax(y - SH2 - 1, 0) * rowCells + i]) + hsum[(size_t)imin(y + SH2, H - 1) * rowCells + i]);
+                int ho = hsum[(size_t)imax(y - SH2 - 1, 0) * rowCells + i], hn = hsum[(size_t)imin(y + SH2, H - 1) * rowCells + i];
+                /* OpenCV evaluates the first computed column (x' = 0) as (Cprev + new) - old and every other column as
+                   (Cprev - old) + new; with saturating lanes the two differ once C sticks at 32767 (pinned by the
+                   satdrift golden fixture). */
+                c = (i < (size_t)D) ? sat16(sat16(c + hn) - ho) : sat16(sat16(c - ho) + hn);
                 C[(size_t)y * rowCells + i] = (int16_t)c;
             }
         }

@@ -208,3 +208,14 @@ def synth_pair(H, W, D, seed, color=False):
     lb = np.clip(left[..., None].astype(np.int64) + n[0], 0, 255).astype(np.uint8)
     rb = np.clip(right[..., None].astype(np.int64) + n[1], 0, 255).astype(np.uint8)
     return lb, rb
+
+
+def satdrift_pair(H=80, W=260, D=32, seed=5):
+    """Adversarial pair for the int16 saturation regime (block_size 27): the top half is flat 255 (left) against
+    flat 0 (right) so the raw-intensity BT cost is 63 everywhere and the vertical block sum sticks at 32767; the
+    bottom half is an ordinary textured pair, so the recurrence leaves saturation and drifts."""
+    l, r = synth_pair(H, W, D, seed)
+    l = l.copy(); r = r.copy()
+    l[:H // 2] = 255
+    r[:H // 2] = 0
+    return l, r

@@ -88,5 +88,22 @@ def main():
         print(name, "valid %.1f%%" % (100 * (disp >= minD * 16).mean()), os.path.getsize(os.path.join(HERE, name + ".npz")) // 1024, "KiB")
 
 
+def special():
+    """Saturate-and-drift case: cost volume sticks at 32767, then leaves saturation (pins the A.3 recurrences)."""
+    l, r = O.satdrift_pair()
+    H, W = l.shape
+    out = {}
+    for mode in (0, 1):
+        p = O.reference_sgbm_params(block_size=27, num_disparities=32, mode=mode)
+        out["disp_mode%d" % mode] = cv_sgbm(l, r, p, True)
+        p5 = O.reference_sgbm_params(block_size=27, num_disparities=32, mode=mode, uniqueness_ratio=0, speckle_window_size=0)
+        p5["P1"], p5["P2"] = 8, 32          # small penalties: everything else unsaturated, only C saturates
+        out["disp_smallP_mode%d" % mode] = cv_sgbm(l, r, p5, False)
+    out["crc"] = np.array([zlib.crc32(l.tobytes()), zlib.crc32(r.tobytes())], np.uint64)
+    np.savez_compressed(os.path.join(HERE, "satdrift_d32_bs27.npz"), **out)
+    print("satdrift", {k: int((v >= 0).sum()) for k, v in out.items() if k.startswith("disp")})
+
+
 if __name__ == "__main__":
+    special()
     main()

@@ -1,0 +1,216 @@
+"""GPU: the CUDA path (through the C ABI) against the CPU oracle and the cv2 golden fixtures.
+Bars: disparity bit-exact; reprojected / triangulated coordinates within 1e-5 relative
+(bitwise is what we assert first and report); voxel centroids within 1e-5*leaf, rgb +-1, identical voxel set and
+counts; SOR kept set identical except points within 1e-5*thr of the threshold."""
+import zlib
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN_LARGE, GOLDEN_SMALL, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def _cfg(bs, D, minD=0, uniq=10, spw=100, spr=2, cap=10, k=30, alpha=0.5):
+    return dict(block_size=bs, num_disparities=D, uniqueness_ratio=uniq, speckle_range=spr, speckle_window_size=spw,
+                pre_filter_cap=cap, min_disparity=minD, outlier_min_k=k, outlier_std_threshold=alpha)
+
+
+def _golden_inputs(O, g):
+    H, W, D, bs, mode, minD, seed = [int(v) for v in g["meta"]]
+    lb, rb = O.synth_pair(H, W, D, seed, color=True)
+    assert zlib.crc32(lb.tobytes()) == int(g["crc"][0])
+    return H, W, D, bs, mode, minD, lb, rb
+
+
+@pytest.mark.parametrize("bs,mode", [(5, 0), (27, 0), (9, 1), (27, 1)])
+def test_stages_against_oracle(cvr, oracle, bs, mode):
+    """Cost volume C, aggregated volume S, raw WTA/LR disparity and final disparity, each bit-exact."""
+    H, W, D = 48, 260, 64
+    l, r = oracle.synth_pair(H, W, D, seed=100 + bs + mode)
+    p = oracle.reference_sgbm_params(block_size=bs, num_disparities=D, mode=mode)
+    ref, st = oracle.sgbm(l, r, p, stages=True)
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D), mode=mode)
+    got = rec.GenerateDisparityMap(l, r)
+    C = rec.debug_fetch(0)[:, :, :D]
+    S = rec.debug_fetch(1)[:, :, :D]
+    lr = rec.debug_fetch(3)
+    assert np.array_equal(C, st["C"]), "C mismatches: %d" % int((C != st["C"]).sum())
+    assert np.array_equal(S, st["S"]), "S mismatches: %d" % int((S != st["S"]).sum())
+    assert np.array_equal(lr, st["raw"]), "raw mismatches: %d" % int((lr != st["raw"]).sum())
+    assert np.array_equal(got, ref), "final mismatches: %d" % int((got != ref).sum())
+    rec.close()
+
+
+@pytest.mark.parametrize("name", GOLDEN_SMALL + GOLDEN_LARGE)
+def test_disparity_bit_exact_vs_cv2_golden(cvr, oracle, name):
+    g = load_golden(name)
+    H, W, D, bs, mode, minD, lb, rb = _golden_inputs(oracle, g)
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD), mode=mode)
+    got = rec.GenerateDisparityMap(lb, rb)          # BGR in: cvtColor + StereoSGBM::compute
+    assert np.array_equal(got, g["disp"]), "%d pixels differ from cv2" % int((got != g["disp"]).sum())
+    rec.close()
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD, spw=0), mode=mode)
+    got = rec.GenerateDisparityMap(lb, rb)
+    assert np.array_equal(got, g["disp_nospeckle"])
+    rec.close()
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_saturation_stick_and_drift_vs_cv2_golden(cvr, oracle, mode):
+    g = load_golden("satdrift_d32_bs27")
+    l, r = oracle.satdrift_pair()
+    H, W = l.shape
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(27, 32), mode=mode)
+    assert np.array_equal(rec.GenerateDisparityMap(l, r), g["disp_mode%d" % mode])
+    rec.close()
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(27, 32, uniq=0, spw=0), mode=mode, P1=8, P2=32)
+    assert np.array_equal(rec.GenerateDisparityMap(l, r), g["disp_smallP_mode%d" % mode])
+    rec.close()
+
+
+@pytest.mark.parametrize("kw", [dict(cap=63), dict(cap=31, uniq=0), dict(uniq=15, minD=16), dict(minD=-16, uniq=5), dict(D=16), dict(D=48, bs=1),
+                                dict(D=96, bs=3), dict(D=160, bs=7), dict(D=192, bs=11), dict(D=256, bs=5), dict(D=112, bs=9)])
+def test_parameter_sweep_against_oracle(cvr, oracle, kw):
+    D = kw.get("D", 64)
+    bs = kw.get("bs", 7)
+    minD = kw.get("minD", 0)
+    H, W = 40, D + 150
+    for mode in (0, 1):
+        l, r = oracle.synth_pair(H, W, D, seed=7 + D + bs)
+        p = oracle.reference_sgbm_params(block_size=bs, num_disparities=D, mode=mode, min_disparity=minD,
+                                         pre_filter_cap=kw.get("cap", 10), uniqueness_ratio=kw.get("uniq", 10))
+        ref = oracle.sgbm(l, r, p)
+        rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD, uniq=kw.get("uniq", 10), cap=kw.get("cap", 10)), mode=mode)
+        got = rec.GenerateDisparityMap(l, r)
+        assert np.array_equal(got, ref), "mode %d: %d pixels differ" % (mode, int((got != ref).sum()))
+        rec.close()
+
+
+def test_degenerate_inputs(cvr, oracle):
+    # image narrower than the disparity range: everything invalid (A.0, W1 <= 0)
+    rec = cvr.Reconstruct3D(60, 20, config=_cfg(5, 64))
+    z = np.zeros((20, 60), np.uint8)
+    assert (rec.GenerateDisparityMap(z, z) == -16).all()
+    rec.close()
+    # constant images
+    rec = cvr.Reconstruct3D(200, 30, config=_cfg(5, 32))
+    a = np.full((30, 200), 77, np.uint8)
+    p = oracle.reference_sgbm_params(block_size=5, num_disparities=32)
+    assert np.array_equal(rec.GenerateDisparityMap(a, a), oracle.sgbm(a, a, p))
+    # padded row step (cv::Mat step > cols) through the raw ABI
+    import ctypes as C
+    lp = np.zeros((30, 256), np.uint8)
+    rp = np.zeros((30, 256), np.uint8)
+    l, r = oracle.synth_pair(30, 200, 32, 3)
+    lp[:, :200], rp[:, :200] = l, r
+    out = np.empty((30, 200), np.int16)
+    rc = rec.lib.cvr_disparity(rec.ctx, lp.ctypes.data, 256, rp.ctypes.data, 256, 1, out.ctypes.data, 400)
+    assert rc == 0 and np.array_equal(out, oracle.sgbm(l, r, p))
+    # wrong channel count is an error, like cv::cvtColor throwing
+    assert rec.lib.cvr_disparity(rec.ctx, lp.ctypes.data, 256, rp.ctypes.data, 256, 2, out.ctypes.data, 400) == -1
+    rec.close()
+
+
+def test_prune_reproject_triangulate(cvr, oracle):
+    g = load_golden("s100x420_d96_bs3")
+    H, W, D, bs, mode, minD, lb, rb = _golden_inputs(oracle, g)
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD), mode=mode)
+    pruned, dispf, mask = rec.SetupFrame(g["disp"])
+    assert np.array_equal(pruned, g["pruned"]) and np.array_equal(mask, g["mask"])          # vs cv2
+    assert np.array_equal(dispf, g["pruned"].astype(np.float32) / np.float32(16))
+    cloud = rec.GeneratePointCloud(pruned, lb)
+    ref = oracle.generate_point_cloud(pruned, lb, rec.Q)
+    assert len(cloud) == len(ref) == int(g["xyz_valid_count"][0])
+    for f in ("x", "y", "z"):
+        assert np.array_equal(cloud[f].view(np.uint32), ref[f].view(np.uint32)), f      # bitwise (bar: 1e-5 relative)
+    assert np.array_equal(cloud["r"], ref["r"]) and np.array_equal(cloud["b"], ref["b"])
+    tri = rec.Triangulate3D(dispf, lb, mask)
+    p = rec.params
+    tref = oracle.triangulate(dispf, lb, mask, p.tri_f, p.tri_b, p.tri_cx, p.tri_cy)
+    assert len(tri) == len(tref) > 1000
+    for f in ("x", "y", "z"):
+        assert np.allclose(tri[f], tref[f], rtol=1e-5, atol=0)
+        assert np.array_equal(tri[f].view(np.uint32), tref[f].view(np.uint32)), f
+    # no mask: every positive disparity
+    tri2 = rec.Triangulate3D(dispf, lb, None)
+    assert len(tri2) == int((dispf > 0).sum())
+    rec.close()
+
+
+def _cloud_for_filters(cvr, oracle, name="s100x420_d96_bs3"):
+    g = load_golden(name)
+    H, W, D, bs, mode, minD, lb, rb = _golden_inputs(oracle, g)
+    pruned, dispf, mask, _, _ = oracle.prune(g["disp"])
+    pts = oracle.triangulate(dispf, lb, mask, np.float32(958.35805), np.float32(0.532671), np.float32(W / 2), np.float32(H / 2))
+    return H, W, pts
+
+
+def test_voxel_grid_vs_oracle(cvr, oracle):
+    H, W, pts = _cloud_for_filters(cvr, oracle)
+    for leaf in (0.2, 0.05):
+        rec = cvr.Reconstruct3D(W, H, config=_cfg(3, 96), voxel_leaf=leaf)
+        got, pt = rec.VoxelGrid(pts)
+        ref, counts, rpt = oracle.voxel_grid(pts, leaf)
+        assert pt == rpt and len(got) == len(ref)
+        for f in ("x", "y", "z"):
+            assert np.abs(got[f] - ref[f]).max() <= 1e-5 * leaf
+        for f in ("r", "g", "b"):
+            assert np.abs(got[f].astype(int) - ref[f].astype(int)).max() <= 1
+        rec.close()
+    # int32 index overflow -> PCL passes the cloud through unchanged
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(3, 96), voxel_leaf=1e-6)
+    got, pt = rec.VoxelGrid(pts)
+    assert pt and np.array_equal(got, pts)
+    assert len(rec.VoxelGrid(pts[:0])[0]) == 0
+    rec.close()
+
+
+def test_sor_vs_oracle(cvr, oracle):
+    H, W, pts = _cloud_for_filters(cvr, oracle)
+    vox, _, _ = oracle.voxel_grid(pts, 0.05)
+    assert len(vox) > 500
+    for (k, alpha) in ((30, 0.5), (8, 1.0), (50, 0.3)):
+        rec = cvr.Reconstruct3D(W, H, config=_cfg(3, 96, k=k, alpha=alpha))
+        got = rec.RemoveOutliers(vox)
+        ref, dist, thr, keep = oracle.sor(vox, k, alpha)
+        near = np.abs(dist - thr) <= 1e-5 * thr
+        sure = vox[(keep == 1) & ~near]
+        # every surely-kept point is present, in input order, and nothing surely-removed appears
+        gk = set(map(bytes, got))
+        assert all(bytes(p) in gk for p in sure)
+        assert len(got) <= int(keep.sum()) + int(near.sum()) and len(got) >= len(sure)
+        if not near.any():
+            assert np.array_equal(got, ref)
+        rec.close()
+    # fewer points than k+1: nothing can be judged, everything is kept
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(3, 96, k=30))
+    assert np.array_equal(rec.RemoveOutliers(vox[:10]), vox[:10])
+    # duplicates are legal
+    dup = np.concatenate([vox[:200], vox[:200]])
+    assert np.array_equal(rec.RemoveOutliers(dup), oracle.sor(dup, 30, 0.5)[0])
+    rec.close()
+
+
+def test_batch_equals_single_frames(cvr, oracle):
+    H, W, D, bs = 60, 330, 64, 9
+    B = 5
+    Ls, Rs = zip(*[oracle.synth_pair(H, W, D, seed=40 + i, color=True) for i in range(B)])
+    Ls, Rs = np.stack(Ls), np.stack(Rs)
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, k=8), max_batch=B, voxel_leaf=0.05)
+    disp, clouds = rec.ProcessFrames(Ls, Rs, want_disp=True)
+    p = oracle.reference_sgbm_params(block_size=bs, num_disparities=D)
+    prm = rec.params
+    for i in range(B):
+        ref = oracle.sgbm(oracle.gray_bgr(Ls[i]), oracle.gray_bgr(Rs[i]), p)
+        assert np.array_equal(disp[i], ref), "frame %d" % i
+        pruned, dispf, mask, _, _ = oracle.prune(ref)
+        pts = oracle.triangulate(dispf, Ls[i], mask, prm.tri_f, prm.tri_b, prm.tri_cx, prm.tri_cy)
+        vox, _, _ = oracle.voxel_grid(pts, 0.05)
+        kept, dist, thr, keep = oracle.sor(vox, 8, 0.5)
+        near = int((np.abs(dist - thr) <= 1e-5 * thr).sum())
+        assert abs(len(clouds[i]) - len(kept)) <= near
+        if near == 0:
+            assert np.array_equal(clouds[i]["x"], kept["x"]) and np.array_equal(clouds[i]["r"], kept["r"])
+    rec.close()
