@@ -430,12 +430,15 @@ __global__ void k_lrcheck(const int16_t* __restrict__ raw, const int* __restrict
                 const int _x = x - _d, x_ = x - d_;
                 bool f1 = false, f2 = false;
                 if (0 <= _x && _x < W) {
+                    // an unset right-view entry holds INVALID_DISP_SCALED in OpenCV, which passes `>= minD` when minD > 1
                     const unsigned k = key[_x];
-                    if (k != 0xffffffffu) { const int d2 = (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD; f1 = d2 >= p.minD && abs(d2 - _d) > p.d12; }
+                    const int d2 = (k != 0xffffffffu) ? (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD : p.INVALID;
+                    f1 = d2 >= p.minD && abs(d2 - _d) > p.d12;
                 }
                 if (0 <= x_ && x_ < W) {
                     const unsigned k = key[x_];
-                    if (k != 0xffffffffu) { const int d2 = (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD; f2 = d2 >= p.minD && abs(d2 - d_) > p.d12; }
+                    const int d2 = (k != 0xffffffffu) ? (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD : p.INVALID;
+                    f2 = d2 >= p.minD && abs(d2 - d_) > p.d12;
                 }
                 if (f1 && f2) v = p.INVALID;
             }
