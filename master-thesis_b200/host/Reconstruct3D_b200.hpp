@@ -1,0 +1,140 @@
+// Reconstruct3D_b200.hpp -- header-only C++14 mirror of the reference's reconstruction-stage interface on top of the
+// C ABI (include/cvrecon_b200.h).  Same method names, argument meaning and error behaviour as
+//   Reconstruct::Reconstruct3D            cv_reconstruct/include/reconstruct/Reconstruct3D.hpp:25-103
+//   System::TrackingFrame::SetupFrame     cv_reconstruct/src/system/TrackingFrame.cpp:25-44
+//   PointCloudPostProcessor::RemoveOutliers  cv_reconstruct/include/point_cloud/PointCloudPostProcessor.hpp:38
+// OpenCV / PCL / Eigen headers are not available in this image, so images are passed as cvr::Mat views (the fields
+// of cv::Mat that matter: data, rows, cols, step) and clouds as std::vector<cvr_point>; INTEGRATION.md shows the
+// two-line adapters for cv::Mat and pcl::PointCloud<pcl::PointXYZRGB>.
+// Errors: the reference lets cv::Exception propagate; this mirror throws std::runtime_error with cvr_last_error().
+#pragma once
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/cvrecon_b200.h"
+
+namespace cvr {
+
+struct Mat {            // non-owning view with cv::Mat's layout
+    void* data;
+    int rows, cols;
+    std::size_t step;   // bytes per row
+    int channels;
+};
+
+struct StereoCalib {    // the fields of Camera::Calib::StereoCalib the path reads (CameraCalib.hpp:44-65)
+    float fxL, fyL, cxL, cyL;   // LeftCameraCalib.K(0,0), K(1,1), K(0,2), K(1,2)
+    float fxR, fyR, cxR, cyR;   // RightCameraCalib
+    float T0;                   // T(0): baseline
+};
+
+struct SGBMConfig {     // Config::Reconstruction::SGBM (Config.hpp:36-44)
+    int NumDisparities = 16, BlockSize = 128, UniquenessRatio = 2, SpeckleRange = 2, SpeckleWindowSize = 100, PreFilterCap = 10,
+        MinDisparity = 0;
+    int OutlierMinK = 30;            // point_cloud_post_processing.outlier_min_k (config_default.json:24)
+    double OutlierStdDevThreshold = 0.5;
+};
+
+class Reconstruct3D {
+public:
+    // Reconstruct3D::Reconstruct3D(stereoSetup, config) (Reconstruct3D.cpp:26-36) + ConfigureSteoreoMatcher (:39-69)
+    Reconstruct3D(const StereoCalib& calib, const SGBMConfig& cfg, int width, int height, int device = 0, int maxBatch = 1,
+                  int mode = CVR_MODE_SGBM)
+        : m_calib(calib)
+    {
+        cvr_params p;
+        cvr_default_params(&p, width, height);
+        p.sgbm.min_disparity = cfg.MinDisparity;
+        p.sgbm.pre_filter_cap = cfg.PreFilterCap;
+        p.sgbm.block_size = cfg.BlockSize;
+        p.sgbm.num_disparities = cfg.NumDisparities;
+        p.sgbm.speckle_range = cfg.SpeckleRange;
+        p.sgbm.speckle_window_size = cfg.SpeckleWindowSize;
+        p.sgbm.uniqueness_ratio = cfg.UniquenessRatio;
+        p.sgbm.P1 = 8 * 3 * cfg.BlockSize * cfg.BlockSize;      // Reconstruct3D.cpp:63
+        p.sgbm.P2 = 32 * 3 * cfg.BlockSize * cfg.BlockSize;     // Reconstruct3D.cpp:64
+        p.sgbm.mode = mode;
+        for (int i = 0; i < 16; i++) p.Q[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+        const float f = (calib.fxL + calib.fxR) / 2.0f;         // Reconstruct3D.cpp:33
+        p.Q[10] = static_cast<float>(0.005 * f);                // Reconstruct3D.cpp:34
+        p.tri_f = (calib.fxL + calib.fyL) / 2.0f;               // Reconstruct3D.cpp:168
+        p.tri_b = calib.T0; p.tri_cx = calib.cxL; p.tri_cy = calib.cyL;
+        p.sor_mean_k = cfg.OutlierMinK; p.sor_stddev_mul = cfg.OutlierStdDevThreshold;
+        p.max_batch = maxBatch;
+        m_width = width; m_height = height;
+        if (cvr_create(&p, device, &m_ctx) != CVR_OK) throw std::runtime_error(std::string("Reconstruct3D: ") + cvr_last_error(nullptr));
+    }
+    ~Reconstruct3D() { cvr_destroy(m_ctx); }
+    Reconstruct3D(const Reconstruct3D&) = delete;
+    Reconstruct3D& operator=(const Reconstruct3D&) = delete;
+
+    // cv::Mat GenerateDisparityMap(const cv::Mat& leftImage, const cv::Mat& rightImage) const  -> CV_16SC1 rows x cols
+    std::vector<int16_t> GenerateDisparityMap(const Mat& leftImage, const Mat& rightImage) const
+    {
+        std::vector<int16_t> disp(static_cast<std::size_t>(m_width) * m_height);
+        check(cvr_disparity(m_ctx, static_cast<const uint8_t*>(leftImage.data), leftImage.step, static_cast<const uint8_t*>(rightImage.data),
+                            rightImage.step, leftImage.channels, disp.data(), static_cast<std::size_t>(m_width) * 2));
+        return disp;
+    }
+    // TrackingFrame::SetupFrame: prunes `disparity` in place, fills the CV_32F disparity and the CV_8U mask
+    void SetupFrame(std::vector<int16_t>& disparity, std::vector<float>& disparityF32, std::vector<uint8_t>& mask) const
+    {
+        disparityF32.resize(disparity.size()); mask.resize(disparity.size());
+        check(cvr_prune(m_ctx, disparity.data(), static_cast<std::size_t>(m_width) * 2, disparityF32.data(), mask.data()));
+    }
+    // pcl::PointCloud<pcl::PointXYZRGB> GeneratePointCloud(const cv::Mat& disparity, const cv::Mat& cameraImage) const
+    std::vector<cvr_point> GeneratePointCloud(const std::vector<int16_t>& disparity, const Mat& cameraImage) const
+    {
+        std::vector<cvr_point> out(static_cast<std::size_t>(m_width) * m_height);
+        int n = 0;
+        check(cvr_reproject_cloud(m_ctx, disparity.data(), static_cast<std::size_t>(m_width) * 2, static_cast<const uint8_t*>(cameraImage.data),
+                                  cameraImage.step, out.data(), static_cast<int>(out.size()), &n));
+        out.resize(n);
+        return out;
+    }
+    // ... Triangulate3D(const cv::Mat& disparity, const cv::Mat& cameraImage, cv::InputArray& mask = cv::noArray()) const
+    std::vector<cvr_point> Triangulate3D(const std::vector<float>& disparity, const Mat& cameraImage, const std::vector<uint8_t>* mask = nullptr) const
+    {
+        std::vector<cvr_point> out(static_cast<std::size_t>(m_width) * m_height);
+        int n = 0;
+        check(cvr_triangulate(m_ctx, disparity.data(), static_cast<std::size_t>(m_width) * 4, static_cast<const uint8_t*>(cameraImage.data), cameraImage.step,
+                              mask ? mask->data() : nullptr, static_cast<std::size_t>(m_width), out.data(), static_cast<int>(out.size()), &n));
+        out.resize(n);
+        return out;
+    }
+    // pcl::VoxelGrid<pcl::PointXYZRGB>::filter with setLeafSize(0.2, 0.2, 0.2) (MappingSystem.cpp:297-300)
+    std::vector<cvr_point> VoxelGridFilter(const std::vector<cvr_point>& cloud) const
+    {
+        std::vector<cvr_point> out(cloud.size() ? cloud.size() : 1);
+        int m = 0, pass = 0;
+        check(cvr_voxel_grid(m_ctx, cloud.data(), static_cast<int>(cloud.size()), out.data(), static_cast<int>(out.size()), &m, &pass));
+        out.resize(m);
+        return out;
+    }
+    // void PointCloudPostProcessor::RemoveOutliers(input, output) -- called with input == output in the reference
+    void RemoveOutliers(const std::vector<cvr_point>& input, std::vector<cvr_point>& output) const
+    {
+        std::vector<cvr_point> out(input.size() ? input.size() : 1);
+        int k = 0;
+        check(cvr_sor(m_ctx, input.data(), static_cast<int>(input.size()), out.data(), static_cast<int>(out.size()), &k));
+        out.resize(k);
+        output.swap(out);
+    }
+    // void GetCameraParameters(float& fx, float& fy, float& cx, float& cy, int camNumber = 0) const (Reconstruct3D.cpp:87-103)
+    void GetCameraParameters(float& fx, float& fy, float& cx, float& cy, int camNumber = 0) const
+    {
+        if (camNumber == 1) { fx = m_calib.fxR; fy = m_calib.fyR; cx = m_calib.cxR; cy = m_calib.cyR; }
+        else { fx = m_calib.fxL; fy = m_calib.fyL; cx = m_calib.cxL; cy = m_calib.cyL; }
+    }
+    cvr_ctx* context() const { return m_ctx; }
+
+private:
+    void check(int rc) const { if (rc != CVR_OK) throw std::runtime_error(std::string("cvrecon_b200: ") + cvr_last_error(m_ctx)); }
+    cvr_ctx* m_ctx = nullptr;
+    StereoCalib m_calib;
+    int m_width = 0, m_height = 0;
+};
+
+}  // namespace cvr

@@ -1,0 +1,72 @@
+"""CPU: the C++ host mirror (master-thesis_b200/host/Reconstruct3D_b200.hpp) compiles against the C ABI with g++ and
+fails loudly without a GPU; config parsing mirrors the reference's JSON keys.  GPU: the C++ example runs one frame
+and agrees with the Python harness."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+
+
+def _build_example(tmp_path, cvr):
+    if not os.path.exists(cvr.LIB_PATH):
+        cvr.build()
+    exe = str(tmp_path / "example_frame")
+    libdir = os.path.dirname(cvr.LIB_PATH)
+    subprocess.check_call(["g++", "-std=c++14", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "master-thesis_b200", "host", "example_frame.cpp"), "-L", libdir, "-lcvrecon_b200",
+                           "-Wl,-rpath," + libdir, "-o", exe])
+    return exe
+
+
+def test_cpp_mirror_compiles_and_has_no_cpu_fallback(tmp_path, cvr):
+    exe = _build_example(tmp_path, cvr)
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test")
+    r = subprocess.run([exe, "320", "240", "/dev/zero", "/dev/zero", str(tmp_path / "d"), str(tmp_path / "c")], capture_output=True, text=True)
+    assert r.returncode == 3 and "no CPU fallback" in r.stderr
+
+
+def test_config_keys_follow_reference_json(cvr):
+    ref_json = {"config": {"server": {"port": 7000}, "reconstruction": {
+        "requires_rectification": False, "block_matcher": "stereo_sgbm", "SBM": {"window_size": 27, "num_disparities": 128},
+        "SGBM": {"block_size": 27, "num_disparities": 128, "uniqueness_ratio": 10, "speckle_range": 2, "speckle_window_size": 100,
+                 "pre_filter_cap": 10, "min_disparity": 0.0}},
+        "point_cloud_post_processing": {"outlier_min_k": 30, "outlier_std_threshold": 0.5, "keypoint_detector": "SIFT", "feature_detector": "FPFH"}}}
+    c = cvr.parse_config(ref_json)
+    assert c == dict(block_size=27, num_disparities=128, uniqueness_ratio=10, speckle_range=2, speckle_window_size=100, pre_filter_cap=10,
+                     min_disparity=0, outlier_min_k=30, outlier_std_threshold=0.5)
+    ref_json["config"]["reconstruction"]["block_matcher"] = "stereo_bm"      # the reference's default: not implemented, must be loud
+    with pytest.raises(cvr.CvrError):
+        cvr.parse_config(ref_json)
+
+
+def test_points_to_pcl_layout(cvr):
+    pts = np.zeros(3, cvr.POINT_DTYPE)
+    pts["x"], pts["y"], pts["z"] = [1, 2, 3], [4, 5, 6], [7, 8, 9]
+    pts["b"], pts["g"], pts["r"], pts["a"] = 10, 20, 30, 255
+    raw = cvr.points_to_pcl(pts)
+    assert raw.shape == (3, 32)
+    f = raw[:, :16].copy().view(np.float32).reshape(3, 4)
+    assert np.array_equal(f[:, 0], [1, 2, 3]) and (f[:, 3] == 1.0).all()          # pcl::PointXYZRGB: x,y,z,1.0f
+    assert (raw[:, 16] == 10).all() and (raw[:, 17] == 20).all() and (raw[:, 18] == 30).all() and (raw[:, 19] == 255).all()
+    assert (raw[:, 20:] == 0).all()
+
+
+@pytest.mark.gpu
+def test_cpp_example_matches_python_harness(tmp_path, cvr, oracle):
+    exe = _build_example(tmp_path, cvr)
+    H, W, D, bs = 80, 360, 64, 9
+    lb, rb = oracle.synth_pair(H, W, D, seed=21, color=True)
+    lb.tofile(tmp_path / "l.bgr"); rb.tofile(tmp_path / "r.bgr")
+    r = subprocess.run([exe, str(W), str(H), str(tmp_path / "l.bgr"), str(tmp_path / "r.bgr"), str(tmp_path / "d.i16"), str(tmp_path / "c.bin"),
+                        str(bs), str(D)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    disp = np.fromfile(tmp_path / "d.i16", np.int16).reshape(H, W)
+    ref = oracle.sgbm(oracle.gray_bgr(lb), oracle.gray_bgr(rb), oracle.reference_sgbm_params(block_size=bs, num_disparities=D))
+    assert np.array_equal(disp, ref)
+    cloud = np.fromfile(tmp_path / "c.bin", cvr.POINT_DTYPE)
+    assert int(r.stdout.split()[1]) == len(cloud)
