@@ -142,6 +142,25 @@ typedef struct cvr_batch {
 } cvr_batch;
 int cvr_process_batch(cvr_ctx* ctx, int nframes, const cvr_batch* io);
 
+/* No counterpart in the reference: TrackingFrame::SetupFrame / cvr_prune for callers that are not allowed to
+ * allocate GPU memory.  Think of a frame loop that must keep a fixed latency (cudaMalloc/cudaFree stall the whole
+ * device while they run), a plug-in host or safety-minded integrator that forbids device allocation once start-up
+ * is over, or a process whose memory pool belongs to another library.  Such a caller cannot create a cvr_ctx
+ * (cvr_create allocates the workspace) -- this call needs none.  It takes DEVICE pointers to tight width*height
+ * arrays: d_disp in, and any of d_pruned (int16), d_disp_f32 (float), d_mask (uint8) out (NULL = not wanted), and
+ * enqueues the work on `stream` (a cudaStream_t, NULL = default stream) of the CURRENT device without waiting for
+ * it.  It calls no cudaMalloc/cudaFree nor any allocating library routine: the little scratch it needs (a 256-byte
+ * statistics record and one byte per pixel) sits in a fixed array built into the library, which every GPU that
+ * loads the library keeps until the process exits (4 MiB + 256 B).
+ * Limit: width*height <= CVR_NOALLOC_MAX_PIXELS, larger frames are refused with CVR_ERR_CAPACITY and a message in
+ * cvr_last_error(NULL).  The first call on each device looks up the array's device address; make that first call
+ * before starting any stream capture.  All calls on a device share the one array and it keeps whatever the last
+ * call left there (the call resets what it relies on), so two calls whose GPU work can overlap -- different
+ * streams or threads -- race with each other: keep them ordered. */
+#define CVR_NOALLOC_MAX_PIXELS (4u << 20)
+int cvr_prune_noalloc(const int16_t* d_disp, int width, int height, double sigma_factor,
+                      int16_t* d_pruned, float* d_disp_f32, uint8_t* d_mask, void* stream);
+
 /* Expands 16-byte points to pcl::PointXYZRGB (32 B: x,y,z,1.0f, b,g,r,a, 12 B pad).  Host side. */
 void cvr_points_to_pcl(const cvr_point* in, int n, void* pcl_points_32B);
 

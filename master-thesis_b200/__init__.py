@@ -31,7 +31,7 @@ POINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), (
 EXPORTS = [
     "cvr_default_params", "cvr_create", "cvr_destroy", "cvr_last_error", "cvr_version", "cvr_disparity", "cvr_prune",
     "cvr_reproject_cloud", "cvr_triangulate", "cvr_voxel_grid", "cvr_sor", "cvr_process_batch", "cvr_points_to_pcl",
-    "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling",
+    "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling", "cvr_prune_noalloc",
 ]
 
 
@@ -109,6 +109,7 @@ def load_library():
     lib.cvr_set_profiling.argtypes = [C.c_void_p, C.c_int]
     lib.cvr_points_to_pcl.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.cvr_points_to_pcl.restype = None
+    lib.cvr_prune_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     _lib = lib
     return lib
 

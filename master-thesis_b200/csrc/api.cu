@@ -10,6 +10,7 @@ static const char* kVersion = "cvrecon_b200 0.1 (sm_100a)";
 static thread_local std::string g_create_err;
 
 extern "C" const char* cvr_version(void) { return kVersion; }
+void cvr_set_thread_error(const char* msg) { g_create_err = msg ? msg : ""; }
 
 extern "C" void cvr_default_params(cvr_params* p, int width, int height)
 {

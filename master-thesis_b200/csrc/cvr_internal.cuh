@@ -155,3 +155,5 @@ int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, c
 int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in /*device*/, int n_is_vox);
 
 void cvr_stage_mark(cvr_ctx* c, const char* name);
+// message slot read by cvr_last_error(NULL): used by entry points that have no context
+void cvr_set_thread_error(const char* msg);

@@ -9,6 +9,7 @@
 #include "cvr_internal.cuh"
 #include "cvr_scan.cuh"
 #include <float.h>
+#include <mutex>
 
 #define LAUNCH_CHECK(c)                                                                  \
     do {                                                                                 \
@@ -218,5 +219,59 @@ int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const f
         k_cloud_write<CVR_CLOUD_TRIANGULATE><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride, nblk, c->d_cloud, (size_t)c->maxN, c->d_ncloud);
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "cloud");
+    return CVR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free prune (cvr_prune_noalloc, include/cvrecon_b200.h).  Same four kernels as cvr_launch_prune, but
+// the scratch they need (the min/max/sum record and the normalised 8-bit image) lives in a fixed array that is
+// part of the library image, so the call never asks the driver for memory.
+#define CVR_NOALLOC_STATS_BYTES 256
+static __device__ __align__(256) unsigned char g_prune_scratch[CVR_NOALLOC_STATS_BYTES + CVR_NOALLOC_MAX_PIXELS];
+
+// g_prune_scratch as written in host code is only a host-side handle for the symbol; the device address has to be
+// asked for, once per device, with that device current.
+#define CVR_NOALLOC_MAX_DEVICES 64
+static unsigned char* g_prune_scratch_dev[CVR_NOALLOC_MAX_DEVICES];
+static std::mutex g_prune_scratch_mtx;
+
+extern "C" int cvr_prune_noalloc(const int16_t* d_disp, int width, int height, double sigma_factor,
+                                 int16_t* d_pruned, float* d_disp_f32, uint8_t* d_mask, void* stream)
+{
+    if (!d_disp || width <= 0 || height <= 0) { cvr_set_thread_error("cvr_prune_noalloc: null disparity or non-positive size"); return CVR_ERR_INVALID_ARG; }
+    const long long npix = (long long)width * height;
+    if (npix > (long long)CVR_NOALLOC_MAX_PIXELS) {
+        cvr_set_thread_error("cvr_prune_noalloc: width*height exceeds CVR_NOALLOC_MAX_PIXELS (the built-in scratch holds 4 Mi pixels)");
+        return CVR_ERR_CAPACITY;
+    }
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= CVR_NOALLOC_MAX_DEVICES) { cvr_set_thread_error("cvr_prune_noalloc: no current CUDA device (or device index >= 64)"); return CVR_ERR_NO_DEVICE; }
+    unsigned char* scratch;
+    {
+        std::lock_guard<std::mutex> lk(g_prune_scratch_mtx);
+        if (!g_prune_scratch_dev[dev]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_prune_scratch);
+            if (e != cudaSuccess || !p) {
+                cvr_set_thread_error((std::string("cvr_prune_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e)).c_str());
+                return CVR_ERR_CUDA;
+            }
+            g_prune_scratch_dev[dev] = (unsigned char*)p;
+        }
+        scratch = g_prune_scratch_dev[dev];
+    }
+    PruneStats* st = (PruneStats*)scratch;
+    uint8_t* u8 = scratch + CVR_NOALLOC_STATS_BYTES;
+    cudaStream_t s = (cudaStream_t)stream;
+    const int N = (int)npix;
+    const int gx = min(cvr_div_up(N, 256), 296);
+    // the record keeps the previous call's min/max/sums: reset it first; the 8-bit image is fully rewritten before use
+    k_prune_init<<<1, 32, 0, s>>>(st, 1);
+    k_prune_minmax<<<dim3(gx, 1), 256, 0, s>>>(d_disp, N, st);
+    k_prune_norm<<<dim3(gx, 1), 256, 0, s>>>(d_disp, N, st, u8);
+    k_prune_apply<<<dim3(gx, 1), 256, 0, s>>>(d_disp, u8, N, st, sigma_factor, d_pruned, d_disp_f32, d_mask);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { cvr_set_thread_error((std::string("cvr_prune_noalloc: kernel launch failed: ") + cudaGetErrorString(e)).c_str()); return CVR_ERR_CUDA; }
     return CVR_OK;
 }
