@@ -127,7 +127,7 @@ static void free_all(cvr_ctx* c)
     void* ptrs[] = { c->d_in[0], c->d_in[1], c->d_gray, c->d_volA, c->d_volC, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, c->d_disp, c->d_med,
                      c->d_label, c->d_size, c->d_pruned, c->d_dispf, c->d_mask, c->d_pstats, c->d_rowcnt, c->d_cloud, c->d_ncloud, c->d_vhdr,
                      c->d_keys[0], c->d_keys[1], c->d_vals[0], c->d_vals[1], c->d_hist, c->d_segstart, c->d_vox, c->d_cellstart, c->d_cellidx,
-                     c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags };
+                     c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags };
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->h_counts) cudaFreeHost(c->h_counts);
     for (auto& t : c->timers) cudaEventDestroy(t.ev);
@@ -152,6 +152,8 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     c->prm = *p; c->device = device; c->maxB = p->max_batch; c->sm_count = prop.multiProcessorCount;
     c->launches = 0; c->profiling = false; c->timers_used = 0; c->stream = nullptr; c->h_counts = nullptr;
     fill_dev_params(c);
+    c->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    { const char* e_ = getenv("CVR_PATH_KERNELS"); c->force_generic = e_ && strcmp(e_, "generic") == 0; }
     const SgbmDev& g = c->sg;
     const size_t B = (size_t)c->maxB, HW = (size_t)g.W * g.H;
     c->maxN = (int)(p->max_points > 0 ? (size_t)p->max_points : HW);
@@ -183,6 +185,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     A(dalloc(&c->d_meand, B * N)); A(dalloc(&c->d_sstats, B)); A(dalloc(&c->d_sorout, B * N));
     A(dalloc(&c->d_nout, B)); A(dalloc(&c->d_nvox, B)); A(dalloc(&c->d_spts, B * N));
     A(dalloc(&c->d_flags, B * 64));
+    A(dalloc(&c->d_sgflags, B));
     A(cudaHostAlloc((void**)&c->h_counts, sizeof(int) * B * 4, cudaHostAllocDefault));
 #undef A
     if (e != cudaSuccess) {

@@ -126,6 +126,9 @@ struct cvr_ctx {
     int sor_grid_cap;        // max cells per frame
     int* h_counts;           // pinned [B]
     int* d_flags;            // misc flags [B][4]
+    int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
+    int smem_optin;          // max dynamic shared memory per block (opt-in)
+    bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)
 };
 
 #define CVR_CUDA(ctx, call)                                                                       \

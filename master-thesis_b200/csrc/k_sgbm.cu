@@ -139,7 +139,7 @@ __device__ __forceinline__ int lo16(unsigned w) { return (int)(short)(w & 0xffff
 __device__ __forceinline__ int hi16(unsigned w) { return ((int)w) >> 16; }
 __device__ __forceinline__ unsigned pack16(int lo, int hi) { return ((unsigned)lo & 0xffffu) | ((unsigned)hi << 16); }
 
-__global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B)
+__global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B, int* flags)
 {
     const size_t rowWords = (size_t)p.W1 * p.Dp / 4;          // uint2 words per row
     const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -160,6 +160,7 @@ __global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C
 #pragma unroll
         for (int j = 0; j < 4; j++) c[j] = sat16i(c[j] + sat16i(hv[j] * sc));
     }
+    int neg = c[0] | c[1] | c[2] | c[3];
     cs[0] = make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3]));
     for (int y = 1; y < H; y++) {
         uint2 ho = hs[(size_t)max(y - SH2 - 1, 0) * rowWords];
@@ -168,8 +169,10 @@ __global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C
         int nv[4] = { lo16(hn.x), hi16(hn.x), lo16(hn.y), hi16(hn.y) };
 #pragma unroll
         for (int j = 0; j < 4; j++) c[j] = first ? sat16i(sat16i(c[j] + nv[j]) - ov[j]) : sat16i(sat16i(c[j] - ov[j]) + nv[j]);
+        neg |= c[0] | c[1] | c[2] | c[3];
         cs[(size_t)y * rowWords] = make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3]));
     }
+    if (neg < 0) atomicOr(&flags[b], 1);      // a negative C exists in this frame: the packed path kernels take their exact t + C form
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -270,7 +273,7 @@ __device__ __forceinline__ void wta_column(const int (&S)[DPL], int lane, const 
 //   accumulate: S = sat(S + L) (else S = L, the first path written);  WTA: winner-take-all on the final S.
 template <int DPL, bool REVERSE, bool WTA>
 __global__ void __launch_bounds__(128) k_path_h(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                int* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS)
+                                                int* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
 {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= B * p.H) return;
@@ -316,6 +319,7 @@ __global__ void __launch_bounds__(128) k_path_h(const int16_t* __restrict__ C, i
             s[i] = sat16i(s[i] + v);
         }
         minPrev = __reduce_min_sync(FULL, mn);
+        if (minPrev < 0 && lane == 0) atomicOr(&flags[b], 2);       // tells the packed kernels that S may hold negative values
 #pragma unroll
         for (int i = 0; i < DPL; i++) Lp[i] = L[i];
         if (!WTA || storeS) store_vec<DPL>(Srow + (size_t)xp * Dp, s);
@@ -341,7 +345,7 @@ __global__ void k_lr_init(int16_t* lr, int* minlr, SgbmDev p, int B)
 // UP = false: rows top-down (pass 1);  UP = true: bottom-up (MODE_HH pass 2).  S = sat(S + L1), + L2, + L3.
 template <int DPL, bool UP, bool WTA, int NT>
 __global__ void __launch_bounds__(NT) k_path_v(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* lr, int* minlr,
-                                               int16_t* __restrict__ raw, int* __restrict__ aux, SgbmDev p, int CL, int storeS)
+                                               int16_t* __restrict__ raw, int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags)
 {
     const int b = blockIdx.y, rank = blockIdx.x;
     const int W1 = p.W1, Dp = p.Dp, D = p.D, H = p.H;
@@ -388,6 +392,7 @@ __global__ void __launch_bounds__(NT) k_path_v(const int16_t* __restrict__ C, in
                     s[i] = sat16i(s[i] + v);
                 }
                 mins[r] = __reduce_min_sync(FULL, mn);
+                if (mins[r] < 0 && lane == 0) atomicOr(&flags[b], 2);
                 store_vec<DPL>(lrCur + (size_t)(xp + 1) * colStride + (size_t)r * Dp, L);
             }
             if (lane < 3) mlCur[(xp + 1) * 4 + lane] = (lane == 0) ? mins[0] : (lane == 1 ? mins[1] : mins[2]);
@@ -534,6 +539,8 @@ __global__ void k_fill_s16(int16_t* p, size_t n, int v)
     if (i < n) p[i] = (int16_t)v;
 }
 
+#include "k_paths_packed.cuh"
+
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
 #define LAUNCH_CHECK(c)                                                                  \
@@ -556,17 +563,65 @@ int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t
     return CVR_OK;
 }
 
-template <int DPL>
+struct VCfg { bool ok; int CL, NT; VState vs; size_t smem; };
+
+static VCfg pick_vcfg(const cvr_ctx* c)
+{
+    const SgbmDev& p = c->sg;
+    VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = 0;
+    const int nts[3] = { 1024, 512, 256 }, cls[4] = { 8, 4, 2, 1 };
+    for (int ni = 0; ni < 3; ni++)
+        for (int ci = 0; ci < 4; ci++) {
+            const int NT = nts[ni], CL = cls[ci], NW = NT / 32, GW = CL * NW;
+            if (GW > p.W1) continue;                                   // every warp must own at least one column
+            VState vs;
+            vs.colsMax = (p.W1 + CL - 1) / CL + 1; vs.colWords = 3 * p.Dp / 2 + 4; vs.inboxWords = p.Dp / 2 + 4;
+            const size_t smem = 4 * ((size_t)vs.colsMax * vs.colWords + (size_t)2 * NW * 2 * vs.inboxWords);
+            if (smem > (size_t)c->smem_optin) continue;
+            r.ok = true; r.CL = CL; r.NT = NT; r.vs = vs; r.smem = smem;
+            return r;
+        }
+    return r;
+}
+
+template <typename K>
+static cudaError_t launch_cluster(K kernel, int CL, int B, int NT, size_t smem, cudaStream_t st, const int16_t* C, int16_t* S, int16_t* raw, int* aux,
+                                  SgbmDev p, int storeS, int* flags, VState vs)
+{
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(CL, B, 1); cfg.blockDim = dim3(NT, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kernel, C, S, raw, aux, p, CL, storeS, flags, vs);
+}
+
+template <int DPL, bool HASPAD>
 static int launch_paths(cvr_ctx* c, int B, int storeS)
 {
     const SgbmDev& p = c->sg;
     const int hblocks = cvr_div_up(B * p.H, 4);
-    // vertical kernel geometry: a cluster of CL CTAs per frame; fewer, larger clusters when the batch is small
+    const bool packed = !c->force_generic && p.P1s >= 0;               // P1s < 0 (P1 in [32768, 65535] mod 65536): int32 kernels
+    const VCfg vc = packed ? pick_vcfg(c) : VCfg{ false, 1, 0, { 0, 0, 0 }, 0 };
+    int* fl = c->d_sgflags;
+    // generic vertical kernel geometry: a cluster of CL CTAs per frame; fewer, larger clusters when the batch is small
     constexpr int NT = (DPL <= 4) ? 512 : 256;
     int CL = 1;
     while (CL < 8 && B * CL * 2 <= c->sm_count * 2 && (p.W1 / (CL * 2)) >= NT / 32) CL *= 2;
     const size_t lrN = (size_t)B * 2 * (p.W1 + 2) * 3 * p.Dp;
     auto launch_v = [&](bool up, bool wta) -> int {
+        cudaError_t e;
+        if (vc.ok) {
+            if (!up) e = launch_cluster(k_path_v2<DPL, false, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+            else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+            else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+            c->launches++;
+            if (e != cudaSuccess) { c->err = std::string("k_path_v2 launch: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
+            return CVR_OK;
+        }
         k_lr_init<<<(unsigned)cvr_div_up_sz(lrN, 256), 256, 0, c->stream>>>(c->d_lr, c->d_minlr, p, B);
         LAUNCH_CHECK(c);
         cudaLaunchConfig_t cfg = {};
@@ -578,31 +633,43 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
         cfg.attrs = at; cfg.numAttrs = 1;
-        cudaError_t e;
-        if (!up) e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, false, false, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS);
-        else if (wta) e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, true, true, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS);
-        else e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, true, false, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS);
+        if (!up) e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, false, false, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS, fl);
+        else if (wta) e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, true, true, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS, fl);
+        else e = cudaLaunchKernelEx(&cfg, k_path_v<DPL, true, false, NT>, (const int16_t*)c->d_volC, c->d_volA, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, p, CL, storeS, fl);
         c->launches++;
         if (e != cudaSuccess) { c->err = std::string("k_path_v launch: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
         return CVR_OK;
     };
+    auto launch_h = [&](bool rev, bool wta, int accumulate, int store) -> int {
+        if (packed) {
+            if (!rev) k_path_h2<DPL, false, false, HASPAD><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+            else if (wta) k_path_h2<DPL, true, true, HASPAD><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+            else k_path_h2<DPL, true, false, HASPAD><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+        } else {
+            if (!rev) k_path_h<DPL, false, false><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+            else if (wta) k_path_h<DPL, true, true><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+            else k_path_h<DPL, true, false><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+        }
+        LAUNCH_CHECK(c);
+        return CVR_OK;
+    };
     // pass 1: -> then the three downward paths
-    k_path_h<DPL, false, false><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, 0, 1);
-    LAUNCH_CHECK(c);
+    int rc = launch_h(false, false, 0, 1);
+    if (rc) return rc;
     cvr_stage_mark(c, "path_h_fwd");
-    int rc = launch_v(false, false);
+    rc = launch_v(false, false);
     if (rc) return rc;
     cvr_stage_mark(c, "path_v_down");
     if (p.mode == CVR_MODE_HH) {
-        k_path_h<DPL, true, false><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, 1, 1);
-        LAUNCH_CHECK(c);
+        rc = launch_h(true, false, 1, 1);
+        if (rc) return rc;
         cvr_stage_mark(c, "path_h_rev");
         rc = launch_v(true, true);
         if (rc) return rc;
         cvr_stage_mark(c, "path_v_up_wta");
     } else {
-        k_path_h<DPL, true, true><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, 1, storeS);
-        LAUNCH_CHECK(c);
+        rc = launch_h(true, true, 1, storeS);
+        if (rc) return rc;
         cvr_stage_mark(c, "path_h_rev_wta");
     }
     return CVR_OK;
@@ -618,6 +685,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         LAUNCH_CHECK(c);
         return CVR_OK;
     }
+    CVR_CUDA(c, cudaMemsetAsync(c->d_sgflags, 0, sizeof(int) * B, c->stream));
     // raw disparity: columns outside [minX1, maxX1) are never written by WTA
     k_fill_s16<<<(unsigned)cvr_div_up_sz(npix, 256), 256, 0, c->stream>>>(c->d_raw, npix, p.INVALID);
     LAUNCH_CHECK(c);
@@ -634,16 +702,16 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     }
     {
         const size_t nthreads = (size_t)p.W1 * p.Dp / 4 * B;
-        k_vsum<<<(unsigned)cvr_div_up_sz(nthreads, 128), 128, 0, c->stream>>>(c->d_volA, c->d_volC, p, B);
+        k_vsum<<<(unsigned)cvr_div_up_sz(nthreads, 128), 128, 0, c->stream>>>(c->d_volA, c->d_volC, p, B, c->d_sgflags);
         LAUNCH_CHECK(c);
         cvr_stage_mark(c, "vsum");
     }
     int rc;
     switch (p.Dp / 32) {
-        case 2: rc = launch_paths<2>(c, B, storeS); break;
-        case 4: rc = launch_paths<4>(c, B, storeS); break;
-        case 6: rc = launch_paths<6>(c, B, storeS); break;
-        case 8: rc = launch_paths<8>(c, B, storeS); break;
+        case 2: rc = (p.D == p.Dp) ? launch_paths<2, false>(c, B, storeS) : launch_paths<2, true>(c, B, storeS); break;
+        case 4: rc = (p.D == p.Dp) ? launch_paths<4, false>(c, B, storeS) : launch_paths<4, true>(c, B, storeS); break;
+        case 6: rc = (p.D == p.Dp) ? launch_paths<6, false>(c, B, storeS) : launch_paths<6, true>(c, B, storeS); break;
+        case 8: rc = (p.D == p.Dp) ? launch_paths<8, false>(c, B, storeS) : launch_paths<8, true>(c, B, storeS); break;
         default: c->err = "unsupported padded disparity count"; return CVR_ERR_UNSUPPORTED;
     }
     if (rc) return rc;

@@ -71,7 +71,7 @@ def test_saturation_stick_and_drift_vs_cv2_golden(cvr, oracle, mode):
 
 
 @pytest.mark.parametrize("kw", [dict(cap=63), dict(cap=31, uniq=0), dict(uniq=15, minD=16), dict(minD=-16, uniq=5), dict(D=16), dict(D=48, bs=1),
-                                dict(D=96, bs=3), dict(D=160, bs=7), dict(D=192, bs=11), dict(D=256, bs=5), dict(D=112, bs=9)])
+                                dict(D=96, bs=3), dict(D=160, bs=7), dict(D=192, bs=11), dict(D=256, bs=5), dict(D=112, bs=9), dict(D=32, bs=37), dict(D=80, bs=5, uniq=0)])
 def test_parameter_sweep_against_oracle(cvr, oracle, kw):
     D = kw.get("D", 64)
     bs = kw.get("bs", 7)
@@ -86,6 +86,25 @@ def test_parameter_sweep_against_oracle(cvr, oracle, kw):
         got = rec.GenerateDisparityMap(l, r)
         assert np.array_equal(got, ref), "mode %d: %d pixels differ" % (mode, int((got != ref).sum()))
         rec.close()
+
+
+@pytest.mark.parametrize("D,bs,mode", [(64, 5, 0), (128, 27, 0), (48, 9, 1), (256, 3, 1)])
+def test_generic_int32_path_kernels(cvr, oracle, monkeypatch, D, bs, mode):
+    """The int32 path kernels (used when P1 wraps negative or the shared-memory state does not fit) stay bit-exact;
+    CVR_PATH_KERNELS=generic forces them."""
+    monkeypatch.setenv("CVR_PATH_KERNELS", "generic")
+    H, W = 44, D + 170
+    l, r = oracle.synth_pair(H, W, D, seed=D + bs)
+    ref = oracle.sgbm(l, r, oracle.reference_sgbm_params(block_size=bs, num_disparities=D, mode=mode))
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D), mode=mode)
+    assert np.array_equal(rec.GenerateDisparityMap(l, r), ref)
+    rec.close()
+    # and on the adversarial saturation pair (negative C and negative path costs)
+    g = load_golden("satdrift_d32_bs27")
+    l, r = oracle.satdrift_pair()
+    rec = cvr.Reconstruct3D(l.shape[1], l.shape[0], config=_cfg(27, 32), mode=mode)
+    assert np.array_equal(rec.GenerateDisparityMap(l, r), g["disp_mode%d" % mode])
+    rec.close()
 
 
 def test_degenerate_inputs(cvr, oracle):
