@@ -21,24 +21,18 @@ struct PathK {                 // per-launch constants of the packed update
     unsigned Qp;               // 32767 - P1s (P1s >= 0) or -32768 - P1s (P1s < 0)
 };
 
-template <bool P1NEG>
+// EXACT = false assumes C >= 0 (frame flag bit 0 clear); EXACT = true takes the general form of t + C.
+template <bool EXACT>
 __device__ __forceinline__ unsigned path_cost2(unsigned lm1, unsigned l0, unsigned lp1, unsigned deltap, unsigned lop, unsigned ndeltap,
-                                               const PathK& k, unsigned c, bool cneg)
+                                               const PathK& k, unsigned c)
 {
-    unsigned n;
-    if (!P1NEG) n = __vimin3_s16x2(lm1, lp1, k.Qp);
-    else n = __vmaxs2(__vmins2(lm1, lp1), k.Qp);
+    const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);               // min(Lp[d-1], Lp[d+1], 32767 - P1s)
     const unsigned t = __viaddmin_s16x2(n, k.P1p, l0);               // min(n + P1s, Lp[d])
     const unsigned m = __vmaxs2(__vmins2(t, deltap), lop);           // min(., delta), kept >= delta - 32768
     const unsigned t2 = __vadd2(m, ndeltap);                         // m - delta in [-32768, 0]
-    if (!cneg) return __vadd2(t2, c);
+    if (!EXACT) return __vadd2(t2, c);
     const unsigned w = __vadd2(~t2, 0x80018001u);                    // -32768 - t2
     return __vadd2(__vmaxs2(c, w), t2);                              // max(t2 + C, -32768)
-}
-
-__device__ __forceinline__ unsigned acc_s2(unsigned s, unsigned L, bool sneg)
-{
-    return sneg ? __vaddss2(s, L) : __viaddmin_u16x2(s, L, 0x7fff7fffu);
 }
 
 template <int NWD>
@@ -62,11 +56,11 @@ __device__ __forceinline__ void stw(unsigned* p, const unsigned (&v)[NWD])
     }
 }
 
-// One column update for one direction: Lp (previous costs of the source pixel, packed) -> L (this pixel), returns
-// the warp-wide minimum of L.  `left`/`right` are the neighbouring lanes' boundary words (fetched by the caller).
-template <int NWD, bool P1NEG, bool HASPAD>
+// One column update for one direction: Lp (previous costs of the source pixel, packed) -> L (this pixel); returns
+// the warp-wide minimum of L.
+template <int NWD, bool EXACT, bool HASPAD>
 __device__ __forceinline__ int column_update(const unsigned (&Lp)[NWD], int minPrev, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
-                                             int P2, const PathK& k, bool cneg)
+                                             int P2, const PathK& k)
 {
     const int delta = (int)(short)(P2 + minPrev);
     const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768)), ndeltap = pk2(-delta);
@@ -79,7 +73,7 @@ __device__ __forceinline__ int column_update(const unsigned (&Lp)[NWD], int minP
     for (int j = 0; j < NWD; j++) {
         const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);           // (Lp[2j-1], Lp[2j])
         const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);     // (Lp[2j+1], Lp[2j+2])
-        unsigned v = path_cost2<P1NEG>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j], cneg);
+        unsigned v = path_cost2<EXACT>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
         if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
         L[j] = v;
         mnp = __vmins2(mnp, v);
@@ -88,6 +82,77 @@ __device__ __forceinline__ int column_update(const unsigned (&Lp)[NWD], int minP
     return __reduce_min_sync(0xffffffffu, m);
 }
 
+template <int NWD>
+__device__ __forceinline__ void acc_fast(unsigned (&s)[NWD], const unsigned (&L)[NWD])        // S, L >= 0: min(S + L, 32767) in unsigned lanes
+{
+#pragma unroll
+    for (int j = 0; j < NWD; j++) s[j] = __viaddmin_u16x2(s[j], L[j], 0x7fff7fffu);
+}
+template <int NWD>
+__device__ __forceinline__ void acc_exact(unsigned (&s)[NWD], const unsigned (&L)[NWD])       // generic saturating int16 add
+{
+#pragma unroll
+    for (int j = 0; j < NWD; j++) s[j] = __vaddss2(s[j], L[j]);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Winner-take-all on packed S (A.5 first half): same result as wta_column, fewer instructions.
+//   argmin: one CREDUX.MIN on (S << 16 | d); uniqueness as an order-free predicate; S[best-1], S[best+1] fetched from
+//   their owner lanes by shuffle; the small truncating division done in float with an exact +-1 correction.
+template <int NWD>
+__device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, const SgbmDev& p, int16_t* rawPix, int* auxPix)
+{
+    const int d0 = lane * NWD * 2;
+    int key = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < NWD; j++)
+        if (d0 + 2 * j < p.D) {                                       // a packed word is either all real disparities or all padding
+            key = min(key, (int)((s[j] << 16) | (unsigned)(d0 + 2 * j)));
+            key = min(key, (int)((s[j] & 0xffff0000u) | (unsigned)(d0 + 2 * j + 1)));
+        }
+    key = __reduce_min_sync(0xffffffffu, key);
+    const int minS = key >> 16, best = key & 0xffff;
+    const int lim = minS * 100, mul = 100 - p.uniq;
+    const int rel = best - d0 + 1;                                    // position i is within one of best iff (unsigned)(rel - i) < 3
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < NWD; j++) {
+        if (d0 + 2 * j < p.D) {
+            const int v0 = lo16(s[j]), v1 = hi16(s[j]);
+            bad |= (v0 * mul < lim) && ((unsigned)(rel - 2 * j) >= 3u);
+            bad |= (v1 * mul < lim) && ((unsigned)(rel - 2 * j - 1) >= 3u);
+        }
+    }
+    const bool reject = __any_sync(0xffffffffu, bad) || (minS == CVR_MAX_COST);
+    int out = p.INVALID, aux = 0x7fffffff;
+    if (!reject) {                                                    // warp-uniform
+        int dd = best * CVR_DISP_SCALE;
+        if (0 < best && best < p.D - 1) {
+            const int ia = best - 1, ic = best + 1;
+            unsigned wa = s[0], wc = s[0];
+#pragma unroll
+            for (int j = 1; j < NWD; j++) { if (((ia >> 1) % NWD) == j) wa = s[j]; if (((ic >> 1) % NWD) == j) wc = s[j]; }
+            wa = __shfl_sync(0xffffffffu, wa, ia / (2 * NWD));
+            wc = __shfl_sync(0xffffffffu, wc, ic / (2 * NWD));
+            const int a = (ia & 1) ? hi16(wa) : lo16(wa), c = (ic & 1) ? hi16(wc) : lo16(wc);
+            const int den = max(a + c - 2 * minS, 1);
+            const int num = (a - c) * CVR_DISP_SCALE + den, den2 = den * 2;
+            // trunc(num / den2): |num| < 2^24 and den2 < 2^24 are exact in float, the quotient is within +-1
+            int q = __float2int_rz(__fdividef((float)num, (float)den2));
+            int r = num - q * den2;
+            if (num >= 0) { if (r < 0) q--; else if (r >= den2) q++; }       // remainder must end in [0, den2)
+            else { if (r > 0) q++; else if (r <= -den2) q--; }                // remainder must end in (-den2, 0]
+            dd += q;
+        }
+        out = dd + p.minD * CVR_DISP_SCALE;
+        aux = (int)(((unsigned)minS << 16) | (unsigned)best);
+    }
+    if (lane == 0) { *rawPix = (int16_t)out; *auxPix = aux; }
+}
+
+// keeps a value in a register across the loop (stops the compiler from re-deriving it from constant memory every iteration)
+#define CVR_PIN(x) asm volatile("" : "+r"(x))
+
 // ------------------------------------------------------------------------------------------------
 // Horizontal path, packed.  Same contract as k_path_h.
 template <int DPL, bool REVERSE, bool WTA, bool HASPAD>
@@ -95,49 +160,56 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
                                                  int* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
 {
     constexpr int NWD = DPL / 2;
-    constexpr bool P1NEG = false;            // P1s < 0 is routed to the int32 kernels by the host
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= B * p.H) return;
     const int b = warp / p.H, y = warp % p.H;
     const int W1 = p.W1, D = p.D;
-    const size_t colW = (size_t)p.Dp / 2;                                   // 32-bit words per column
+    int P2 = p.P2;
+    const long long colW = (long long)p.Dp / 2;                             // 32-bit words per column
     const size_t rowBase = (((size_t)b * p.H + y) * W1) * colW + (size_t)lane * NWD;
-    const unsigned* Crow = (const unsigned*)C + rowBase;
-    unsigned* Srow = (unsigned*)S + rowBase;
-    const int fl = flags[b];
-    const bool cneg = (fl & 1) != 0;
-    bool sneg = (fl & 2) != 0;
-    PathK k; k.P1p = pk2(p.P1s); k.Qp = P1NEG ? pk2(-32768 - p.P1s) : pk2(32767 - p.P1s);
+    const int dx = REVERSE ? -1 : 1;
+    const long long stepW = dx * colW;
+    const unsigned* Cp = (const unsigned*)C + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
+    unsigned* Sp = (unsigned*)S + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
+    int16_t* rawp = raw + ((size_t)b * p.H + y) * p.W + p.minX1 + (REVERSE ? W1 - 1 : 0);
+    int* auxp = aux + ((size_t)b * p.H + y) * W1 + (REVERSE ? W1 - 1 : 0);
+    bool exact = flags[b] != 0;
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
+    CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
     unsigned Lp[NWD];
 #pragma unroll
     for (int j = 0; j < NWD; j++) Lp[j] = ((lane * NWD + j) * 2 < D) ? 0u : 0x7fff7fffu;
     int minPrev = 0;
-    int xp = REVERSE ? W1 - 1 : 0;
-    const int dx = REVERSE ? -1 : 1;
     unsigned cN[NWD], sN[NWD];
 #pragma unroll
     for (int j = 0; j < NWD; j++) sN[j] = 0u;
-    ldw<NWD>(Crow + (size_t)xp * colW, cN);
-    if (accumulate) ldw<NWD>(Srow + (size_t)xp * colW, sN);
-    for (int step = 0; step < W1; step++, xp += dx) {
+    ldw<NWD>(Cp, cN);
+    if (accumulate) ldw<NWD>(Sp, sN);
+    for (int step = 0; step < W1; step++) {
         unsigned c[NWD], s[NWD], L[NWD];
 #pragma unroll
         for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = sN[j]; }
         if (step + 1 < W1) {
-            ldw<NWD>(Crow + (size_t)(xp + dx) * colW, cN);
-            if (accumulate) ldw<NWD>(Srow + (size_t)(xp + dx) * colW, sN);
+            ldw<NWD>(Cp + stepW, cN);
+            if (accumulate) ldw<NWD>(Sp + stepW, sN);
         }
-        minPrev = column_update<NWD, P1NEG, HASPAD>(Lp, minPrev, c, L, lane, D, p.P2, k, cneg);
-        if (minPrev < 0 && !sneg) { sneg = true; if (lane == 0) atomicOr(&flags[b], 2); }
-#pragma unroll
-        for (int j = 0; j < NWD; j++) { Lp[j] = L[j]; s[j] = accumulate ? acc_s2(s[j], L[j], sneg) : L[j]; }
-        if (!WTA || storeS) stw<NWD>(Srow + (size_t)xp * colW, s);
-        if (WTA) {
-            int Si[DPL];
-#pragma unroll
-            for (int j = 0; j < NWD; j++) { Si[2 * j] = lo16(s[j]); Si[2 * j + 1] = hi16(s[j]); }
-            wta_column<DPL>(Si, lane, p, raw + ((size_t)b * p.H + y) * p.W + xp + p.minX1, aux + ((size_t)b * p.H + y) * W1 + xp);
+        if (!exact) {
+            minPrev = column_update<NWD, false, HASPAD>(Lp, minPrev, c, L, lane, D, P2, k);
+            if (minPrev < 0) {                                             // first negative path cost of this frame: go exact (L itself is still right)
+                exact = true;
+                if (lane == 0) atomicOr(&flags[b], 2);
+                if (accumulate) acc_exact<NWD>(s, L);
+            } else if (accumulate) acc_fast<NWD>(s, L);
+        } else {
+            minPrev = column_update<NWD, true, HASPAD>(Lp, minPrev, c, L, lane, D, P2, k);
+            if (minPrev < 0 && lane == 0) atomicOr(&flags[b], 2);
+            if (accumulate) acc_exact<NWD>(s, L);
         }
+#pragma unroll
+        for (int j = 0; j < NWD; j++) { Lp[j] = L[j]; if (!accumulate) s[j] = L[j]; }
+        if (!WTA || storeS) stw<NWD>(Sp, s);
+        if (WTA) wta_column2<NWD>(s, lane, p, rawp, auxp);
+        Cp += stepW; Sp += stepW; rawp += dx; auxp += dx;
     }
 }
 
@@ -161,39 +233,39 @@ struct VState {                // shared-memory carve-up (in 32-bit words) compu
 };
 
 template <int DPL, bool UP, bool WTA, bool HASPAD>
-__global__ void __launch_bounds__(1024, 1) k_path_v2(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                   int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
+__global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v2(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
+                                                     int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     constexpr int NWD = DPL / 2;
-    constexpr bool P1NEG = false;            // P1s < 0 is routed to the int32 kernels by the host
     const int NT = blockDim.x, NW = NT / 32;
     extern __shared__ unsigned smv[];
     cg::cluster_group cluster = cg::this_cluster();
     const int b = blockIdx.y, rank = blockIdx.x;
     const int W1 = p.W1, D = p.D, H = p.H;
+    int P2 = p.P2;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int GW = CL * NW, gw = rank * NW + warp;
     const int ctaFirst = (int)(((long long)W1 * (rank * NW)) / GW);
     const int a = (int)(((long long)W1 * gw) / GW), e = (int)(((long long)W1 * (gw + 1)) / GW);
     const int dwords = p.Dp / 2;                                      // words per direction per column
+    const int colWords = vs.colWords;
     unsigned* state = smv;                                            // [colsMax][colWords]
-    unsigned* inbox = smv + (size_t)vs.colsMax * vs.colWords;         // [2 parity][NW][2 sides][inboxWords]
+    unsigned* inbox = smv + (size_t)vs.colsMax * colWords;            // [2 parity][NW][2 sides][inboxWords]
     // ---- zero state: L = 0 for d < D, MAX_COST in the padding; minima 0 (also the never-written frame borders) ----
-    for (int i = threadIdx.x; i < vs.colsMax * vs.colWords; i += NT) {
-        const int w = i % vs.colWords;
+    for (int i = threadIdx.x; i < vs.colsMax * colWords; i += NT) {
+        const int w = i % colWords;
         state[i] = (w < 3 * dwords) ? (((w % dwords) * 2 < D) ? 0u : 0x7fff7fffu) : 0u;
     }
     for (int i = threadIdx.x; i < 2 * NW * 2 * vs.inboxWords; i += NT) {
         const int w = i % vs.inboxWords;
         inbox[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : 0u;
     }
-    const int fl = flags[b];
-    const bool cneg = (fl & 1) != 0;
-    bool sneg = (fl & 2) != 0;
-    PathK k; k.P1p = pk2(p.P1s); k.Qp = P1NEG ? pk2(-32768 - p.P1s) : pk2(32767 - p.P1s);
+    bool exact = flags[b] != 0;
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
+    CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
     const size_t colW = (size_t)dwords;
-    // where this warp's edge costs go: right neighbour's LEFT inbox (side 0) gets my last column's down-right costs,
-    // left neighbour's RIGHT inbox (side 1) gets my first column's down-left costs
+    // where this warp's edge costs go: the right neighbour's LEFT inbox (side 0) gets my last column's down-right
+    // costs, the left neighbour's RIGHT inbox (side 1) gets my first column's down-left costs
     unsigned* pushRight = nullptr; unsigned* pushLeft = nullptr;
     if (gw + 1 < GW) {
         const int r2 = (gw + 1) / NW, w2 = (gw + 1) % NW;
@@ -208,86 +280,279 @@ __global__ void __launch_bounds__(1024, 1) k_path_v2(const int16_t* __restrict__
     const size_t parityStride = (size_t)NW * 2 * vs.inboxWords;
     const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * vs.inboxWords;
     const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * vs.inboxWords;
+    unsigned* const col0 = state + (size_t)(a - ctaFirst) * colWords + lane * NWD;    // this lane's words of the chunk's first column
     if (CL > 1) cluster.sync(); else __syncthreads();
 
     for (int t = 0; t < H; t++) {
         const int y = UP ? H - 1 - t : t;
         const int rd = (t + 1) & 1, wr = t & 1;                       // inbox parity read / written in this row
-        const size_t rowBase = (((size_t)b * H + y) * W1) * colW + (size_t)lane * NWD;
-        const unsigned* Crow = (const unsigned*)C + rowBase;
-        unsigned* Srow = (unsigned*)S + rowBase;
+        const size_t rowBase = (((size_t)b * H + y) * W1 + a) * colW + (size_t)lane * NWD;
+        const unsigned* Cp = (const unsigned*)C + rowBase;
+        unsigned* Sp = (unsigned*)S + rowBase;
         unsigned carry[NWD];
-        int carryMin;
+        int carryMin = 0;
         unsigned cN[NWD], sN[NWD];
         if (a < e) {
-            ldw<NWD>(Crow + (size_t)a * colW, cN);
-            ldw<NWD>(Srow + (size_t)a * colW, sN);
+            ldw<NWD>(Cp, cN);
+            ldw<NWD>(Sp, sN);
             ldw<NWD>(myInL + rd * parityStride + lane * NWD, carry);
             carryMin = (int)myInL[rd * parityStride + dwords];
         }
-        for (int xp = a; xp < e; xp++) {
-            unsigned* col = state + (size_t)(xp - ctaFirst) * vs.colWords;
-            unsigned c[NWD], s[NWD];
+        unsigned* col = col0;
+        for (int xp = a; xp < e; xp++, col += colWords, Cp += colW, Sp += colW) {
+            const unsigned* colm = col - lane * NWD + 3 * dwords;      // the three minima of this column
+            unsigned c[NWD], s[NWD], s0[NWD];
 #pragma unroll
-            for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = sN[j]; }
-            if (xp + 1 < e) {
-                ldw<NWD>(Crow + (size_t)(xp + 1) * colW, cN);
-                ldw<NWD>(Srow + (size_t)(xp + 1) * colW, sN);
-            }
-            unsigned L[NWD], Lp[NWD];
-            int mn;
-            // ---- down-right (source: column x'-1, previous row) ----
+            for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = s0[j] = sN[j]; }
+            const bool lastCol = (xp + 1 == e);
+            if (!lastCol) { ldw<NWD>(Cp + colW, cN); ldw<NWD>(Sp + colW, sN); }
+            // ---- sources (all read before anything of this column is overwritten) ----
+            unsigned Lp1[NWD], Lp2[NWD], Lp3[NWD], L1[NWD], L2[NWD], L3[NWD];
 #pragma unroll
-            for (int j = 0; j < NWD; j++) Lp[j] = carry[j];
-            int minSrc = carryMin;
-            ldw<NWD>(col + lane * NWD, carry);                         // old costs of this column: next column's source
-            carryMin = (int)col[3 * dwords + 0];
-            mn = column_update<NWD, P1NEG, HASPAD>(Lp, minSrc, c, L, lane, D, p.P2, k, cneg);
-            if (mn < 0 && !sneg) { sneg = true; if (lane == 0) atomicOr(&flags[b], 2); }
+            for (int j = 0; j < NWD; j++) Lp1[j] = carry[j];
+            const int min1 = carryMin;
+            ldw<NWD>(col, carry);                                      // old down-right costs of this column: next column's source
+            carryMin = (int)colm[0];
+            ldw<NWD>(col + dwords, Lp2);
+            const int min2 = (int)colm[1];
+            int min3;
+            if (!lastCol) { ldw<NWD>(col + colWords + 2 * dwords, Lp3); min3 = (int)colm[colWords + 2]; }
+            else { ldw<NWD>(myInR + rd * parityStride + lane * NWD, Lp3); min3 = (int)myInR[rd * parityStride + dwords]; }
+            int mn1, mn2, mn3;
+            if (!exact) {
+                mn1 = column_update<NWD, false, HASPAD>(Lp1, min1, c, L1, lane, D, P2, k);
+                mn2 = column_update<NWD, false, HASPAD>(Lp2, min2, c, L2, lane, D, P2, k);
+                mn3 = column_update<NWD, false, HASPAD>(Lp3, min3, c, L3, lane, D, P2, k);
+                acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3);
+                if (min(min(mn1, mn2), mn3) < 0) {                     // first negative path cost of this frame: redo the sums exactly, stay exact
+                    exact = true;
+                    if (lane == 0) atomicOr(&flags[b], 2);
 #pragma unroll
-            for (int j = 0; j < NWD; j++) s[j] = acc_s2(s[j], L[j], sneg);
-            stw<NWD>(col + lane * NWD, L);
-            if (lane == 0) col[3 * dwords + 0] = (unsigned)mn;
-            if (xp == e - 1 && pushRight) {
-                stw<NWD>(pushRight + wr * parityStride + lane * NWD, L);
-                if (lane == 0) pushRight[wr * parityStride + dwords] = (unsigned)mn;
-            }
-            // ---- down (source: this column, previous row) ----
-            ldw<NWD>(col + dwords + lane * NWD, Lp);
-            minSrc = (int)col[3 * dwords + 1];
-            mn = column_update<NWD, P1NEG, HASPAD>(Lp, minSrc, c, L, lane, D, p.P2, k, cneg);
-            if (mn < 0 && !sneg) { sneg = true; if (lane == 0) atomicOr(&flags[b], 2); }
-#pragma unroll
-            for (int j = 0; j < NWD; j++) s[j] = acc_s2(s[j], L[j], sneg);
-            stw<NWD>(col + dwords + lane * NWD, L);
-            if (lane == 0) col[3 * dwords + 1] = (unsigned)mn;
-            // ---- down-left (source: column x'+1, previous row) ----
-            if (xp + 1 < e) {
-                ldw<NWD>(col + vs.colWords + 2 * dwords + lane * NWD, Lp);
-                minSrc = (int)col[vs.colWords + 3 * dwords + 2];
+                    for (int j = 0; j < NWD; j++) s[j] = s0[j];
+                    acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
+                }
             } else {
-                ldw<NWD>(myInR + rd * parityStride + lane * NWD, Lp);
-                minSrc = (int)myInR[rd * parityStride + dwords];
+                mn1 = column_update<NWD, true, HASPAD>(Lp1, min1, c, L1, lane, D, P2, k);
+                mn2 = column_update<NWD, true, HASPAD>(Lp2, min2, c, L2, lane, D, P2, k);
+                mn3 = column_update<NWD, true, HASPAD>(Lp3, min3, c, L3, lane, D, P2, k);
+                if (min(min(mn1, mn2), mn3) < 0 && lane == 0) atomicOr(&flags[b], 2);
+                acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
             }
-            mn = column_update<NWD, P1NEG, HASPAD>(Lp, minSrc, c, L, lane, D, p.P2, k, cneg);
-            if (mn < 0 && !sneg) { sneg = true; if (lane == 0) atomicOr(&flags[b], 2); }
-#pragma unroll
-            for (int j = 0; j < NWD; j++) s[j] = acc_s2(s[j], L[j], sneg);
-            stw<NWD>(col + 2 * dwords + lane * NWD, L);
-            if (lane == 0) col[3 * dwords + 2] = (unsigned)mn;
+            stw<NWD>(col, L1); stw<NWD>(col + dwords, L2); stw<NWD>(col + 2 * dwords, L3);
+            if (lane < 3) (col - lane * NWD)[3 * dwords + lane] = (unsigned)(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3));
+            if (lastCol && pushRight) {
+                stw<NWD>(pushRight + wr * parityStride + lane * NWD, L1);
+                if (lane == 0) pushRight[wr * parityStride + dwords] = (unsigned)mn1;
+            }
             if (xp == a && pushLeft) {
-                stw<NWD>(pushLeft + wr * parityStride + lane * NWD, L);
-                if (lane == 0) pushLeft[wr * parityStride + dwords] = (unsigned)mn;
+                stw<NWD>(pushLeft + wr * parityStride + lane * NWD, L3);
+                if (lane == 0) pushLeft[wr * parityStride + dwords] = (unsigned)mn3;
             }
-            __syncwarp();
-            if (!WTA || storeS) stw<NWD>(Srow + (size_t)xp * colW, s);
-            if (WTA) {
-                int Si[DPL];
-#pragma unroll
-                for (int j = 0; j < NWD; j++) { Si[2 * j] = lo16(s[j]); Si[2 * j + 1] = hi16(s[j]); }
-                wta_column<DPL>(Si, lane, p, raw + ((size_t)b * H + y) * p.W + xp + p.minX1, aux + ((size_t)b * H + y) * W1 + xp);
-            }
+            if (!WTA || storeS) stw<NWD>(Sp, s);
+            if (WTA) wta_column2<NWD>(s, lane, p, raw + ((size_t)b * H + y) * p.W + xp + p.minX1, aux + ((size_t)b * H + y) * W1 + xp);
         }
         if (CL > 1) cluster.sync(); else __syncthreads();
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_path_v3: as k_path_v2, but without any CTA- or cluster-wide barrier inside the row loop.
+// A warp only depends on its two neighbour warps (their chunk-edge costs of the previous row).  The edge hand-over
+// uses the distributed-shared-memory producer/consumer mechanism of sm_90+/sm_100: the producer writes the 256-byte
+// edge with `st.async ... mbarrier::complete_tx::bytes` into the consumer's inbox (same CTA or another CTA of the
+// cluster), which counts the bytes on an mbarrier that lives next to that inbox; the consumer posts the expected
+// byte count (`mbarrier.arrive.expect_tx`) and waits on the barrier's phase.  No fence, no MEMBAR, and warps drift
+// freely (at most one row apart from their neighbours), so global-load latency of one warp overlaps the arithmetic
+// of the others.  Inboxes and barriers are double-buffered by row parity; the k-th use of a slot waits on phase
+// parity (k & 1).
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ unsigned mapa_u32(unsigned addr, unsigned rank)
+{
+    unsigned r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void st_async_b32(unsigned raddr, unsigned v, unsigned rbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];" ::"r"(raddr), "r"(v), "r"(rbar) : "memory");
+}
+template <int NWD>
+__device__ __forceinline__ void st_async_words(unsigned raddr, const unsigned (&v)[NWD], unsigned rbar)
+{
+    if (NWD == 2) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(raddr), "r"(v[0]), "r"(v[1]), "r"(rbar) : "memory");
+    else if (NWD == 4) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(raddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(rbar) : "memory");
+    else {
+#pragma unroll
+        for (int i = 0; i < NWD; i++) st_async_b32(raddr + 4 * i, v[i], rbar);
+    }
+}
+
+template <int DPL, bool UP, bool WTA, bool HASPAD>
+__global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
+                                                                        int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
+{
+    constexpr int NWD = DPL / 2;
+    const int NT = blockDim.x, NW = NT / 32;
+    extern __shared__ unsigned smv[];
+    cg::cluster_group cluster = cg::this_cluster();
+    const int b = blockIdx.y, rank = blockIdx.x;
+    const int W1 = p.W1, D = p.D, H = p.H;
+    int P2 = p.P2;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int GW = CL * NW, gw = rank * NW + warp;
+    const int ctaFirst = (int)(((long long)W1 * (rank * NW)) / GW);
+    const int a = (int)(((long long)W1 * gw) / GW), e = (int)(((long long)W1 * (gw + 1)) / GW);
+    const int dwords = p.Dp / 2;
+    const int colWords = vs.colWords;
+    unsigned* state = smv;                                            // [colsMax][colWords]
+    unsigned* inbox = smv + (size_t)vs.colsMax * colWords;            // [2 parity][NW][2 sides][inboxWords]
+    const size_t parityStride = (size_t)NW * 2 * vs.inboxWords;
+    unsigned long long* bars = (unsigned long long*)(inbox + 2 * parityStride);   // [2 parity][NW][2 sides] mbarriers (8-byte aligned: all counts are even)
+    for (int i = threadIdx.x; i < vs.colsMax * colWords; i += NT) {
+        const int w = i % colWords;
+        state[i] = (w < 3 * dwords) ? (((w % dwords) * 2 < D) ? 0u : 0x7fff7fffu) : 0u;
+    }
+    for (int i = threadIdx.x; i < 2 * NW * 2 * vs.inboxWords; i += NT) {
+        const int w = i % vs.inboxWords;
+        inbox[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : 0u;
+    }
+    if (threadIdx.x < 2 * NW * 2) mbar_init(smem_u32(bars + threadIdx.x), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    bool exact = flags[b] != 0;
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
+    CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
+    const size_t colW = (size_t)dwords;
+    const unsigned edgeBytes = 32u * NWD * 4u + 4u;                   // 32 lanes x NWD words + the minimum
+    // my inboxes / barriers (side 0 = from the left neighbour, side 1 = from the right neighbour), parity 0 addresses
+    const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * vs.inboxWords;
+    const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * vs.inboxWords;
+    const unsigned myBarL = smem_u32(bars + (size_t)warp * 2 + 0), myBarR = smem_u32(bars + (size_t)warp * 2 + 1);
+    const unsigned barParityStride = (unsigned)(NW * 2 * 8), inboxParityBytes = (unsigned)(parityStride * 4);
+    const bool hasL = gw > 0, hasR = gw + 1 < GW;
+    // remote (shared::cluster) addresses of the neighbour slots I fill, parity 0
+    unsigned pushR_data = 0, pushR_bar = 0, pushL_data = 0, pushL_bar = 0;
+    if (hasR) {
+        const int r2 = (gw + 1) / NW, w2 = (gw + 1) % NW;
+        pushR_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 0) * vs.inboxWords), r2);
+        pushR_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 0), r2);
+    }
+    if (hasL) {
+        const int r2 = (gw - 1) / NW, w2 = (gw - 1) % NW;
+        pushL_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 1) * vs.inboxWords), r2);
+        pushL_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 1), r2);
+    }
+    unsigned* const col0 = state + (size_t)(a - ctaFirst) * colWords + lane * NWD;
+    cluster.sync();                                                   // state, inboxes and barriers of every CTA are initialised
+
+    const size_t frameRow0 = (size_t)b * H;
+    unsigned cN[NWD], sN[NWD];
+    {
+        const int y0 = UP ? H - 1 : 0;
+        const size_t rb = ((frameRow0 + y0) * W1 + a) * colW + (size_t)lane * NWD;
+        ldw<NWD>((const unsigned*)C + rb, cN);
+        ldw<NWD>((const unsigned*)S + rb, sN);
+    }
+    for (int t = 0; t < H; t++) {
+        const int y = UP ? H - 1 - t : t;
+        const int rd = (t + 1) & 1, wr = t & 1;
+        const unsigned waitPhase = (unsigned)(((t - 1) >> 1) & 1);
+        const size_t rowBase = ((frameRow0 + y) * W1 + a) * colW + (size_t)lane * NWD;
+        const unsigned* Cp = (const unsigned*)C + rowBase;
+        unsigned* Sp = (unsigned*)S + rowBase;
+        const long long nextRow = (UP ? -1LL : 1LL) * (long long)W1 * (long long)colW;
+        if (t > 0) {                                                   // previous row's edges of both neighbours
+            if (lane == 0) {
+                if (hasL) mbar_arrive_expect_tx(myBarL + rd * barParityStride, edgeBytes);
+                if (hasR) mbar_arrive_expect_tx(myBarR + rd * barParityStride, edgeBytes);
+            }
+            __syncwarp();
+            if (hasL) mbar_wait(myBarL + rd * barParityStride, waitPhase);
+            if (hasR) mbar_wait(myBarR + rd * barParityStride, waitPhase);
+        }
+        unsigned carry[NWD], edgeR[NWD];
+        ldw<NWD>(myInL + rd * parityStride + lane * NWD, carry);
+        int carryMin = (int)myInL[rd * parityStride + dwords];
+        ldw<NWD>(myInR + rd * parityStride + lane * NWD, edgeR);      // read before anything is pushed in this row
+        const int edgeRMin = (int)myInR[rd * parityStride + dwords];
+        unsigned* col = col0;
+        for (int xp = a; xp < e; xp++, col += colWords, Cp += colW, Sp += colW) {
+            const unsigned* colm = col - lane * NWD + 3 * dwords;
+            unsigned c[NWD], s[NWD], s0[NWD];
+#pragma unroll
+            for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = s0[j] = sN[j]; }
+            const bool lastCol = (xp + 1 == e);
+            if (!lastCol) { ldw<NWD>(Cp + colW, cN); ldw<NWD>(Sp + colW, sN); }
+            else if (t + 1 < H) {                                      // next row's first column: in flight while the neighbours catch up
+                const unsigned* Cn = Cp - (size_t)(e - 1 - a) * colW + nextRow;
+                ldw<NWD>(Cn, cN);
+                ldw<NWD>((const unsigned*)Sp - (size_t)(e - 1 - a) * colW + nextRow, sN);
+            }
+            unsigned Lp1[NWD], Lp2[NWD], Lp3[NWD], L1[NWD], L2[NWD], L3[NWD];
+#pragma unroll
+            for (int j = 0; j < NWD; j++) Lp1[j] = carry[j];
+            const int min1 = carryMin;
+            ldw<NWD>(col, carry);
+            carryMin = (int)colm[0];
+            ldw<NWD>(col + dwords, Lp2);
+            const int min2 = (int)colm[1];
+            int min3;
+            if (!lastCol) { ldw<NWD>(col + colWords + 2 * dwords, Lp3); min3 = (int)colm[colWords + 2]; }
+            else {
+#pragma unroll
+                for (int j = 0; j < NWD; j++) Lp3[j] = edgeR[j];
+                min3 = edgeRMin;
+            }
+            int mn1, mn2, mn3;
+            if (!exact) {
+                mn1 = column_update<NWD, false, HASPAD>(Lp1, min1, c, L1, lane, D, P2, k);
+                mn2 = column_update<NWD, false, HASPAD>(Lp2, min2, c, L2, lane, D, P2, k);
+                mn3 = column_update<NWD, false, HASPAD>(Lp3, min3, c, L3, lane, D, P2, k);
+                acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3);
+                if (min(min(mn1, mn2), mn3) < 0) {
+                    exact = true;
+                    if (lane == 0) atomicOr(&flags[b], 2);
+#pragma unroll
+                    for (int j = 0; j < NWD; j++) s[j] = s0[j];
+                    acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
+                }
+            } else {
+                mn1 = column_update<NWD, true, HASPAD>(Lp1, min1, c, L1, lane, D, P2, k);
+                mn2 = column_update<NWD, true, HASPAD>(Lp2, min2, c, L2, lane, D, P2, k);
+                mn3 = column_update<NWD, true, HASPAD>(Lp3, min3, c, L3, lane, D, P2, k);
+                if (min(min(mn1, mn2), mn3) < 0 && lane == 0) atomicOr(&flags[b], 2);
+                acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
+            }
+            stw<NWD>(col, L1); stw<NWD>(col + dwords, L2); stw<NWD>(col + 2 * dwords, L3);
+            if (lane < 3) (col - lane * NWD)[3 * dwords + lane] = (unsigned)(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3));
+            if (xp == a && hasL) {                                     // my first column's down-left costs -> left neighbour's right inbox
+                st_async_words<NWD>(pushL_data + wr * inboxParityBytes + lane * NWD * 4, L3, pushL_bar + wr * barParityStride);
+                if (lane == 0) st_async_b32(pushL_data + wr * inboxParityBytes + dwords * 4, (unsigned)mn3, pushL_bar + wr * barParityStride);
+            }
+            if (lastCol && hasR) {                                     // my last column's down-right costs -> right neighbour's left inbox
+                st_async_words<NWD>(pushR_data + wr * inboxParityBytes + lane * NWD * 4, L1, pushR_bar + wr * barParityStride);
+                if (lane == 0) st_async_b32(pushR_data + wr * inboxParityBytes + dwords * 4, (unsigned)mn1, pushR_bar + wr * barParityStride);
+            }
+            if (!WTA || storeS) stw<NWD>(Sp, s);
+            if (WTA) wta_column2<NWD>(s, lane, p, raw + (frameRow0 + y) * p.W + xp + p.minX1, aux + (frameRow0 + y) * W1 + xp);
+            __syncwarp();                                              // the minima written by lanes 0..2 are read by all lanes in the next row
+        }
+    }
+    cluster.sync();                                                   // nobody exits while a neighbour may still write into its inbox
 }

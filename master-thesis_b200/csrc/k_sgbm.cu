@@ -573,10 +573,11 @@ static VCfg pick_vcfg(const cvr_ctx* c)
     for (int ni = 0; ni < 3; ni++)
         for (int ci = 0; ci < 4; ci++) {
             const int NT = nts[ni], CL = cls[ci], NW = NT / 32, GW = CL * NW;
+            if (NT > 512 && p.Dp > 128) continue;                      // wide disparity ranges need > 64 registers per thread
             if (GW > p.W1) continue;                                   // every warp must own at least one column
             VState vs;
             vs.colsMax = (p.W1 + CL - 1) / CL + 1; vs.colWords = 3 * p.Dp / 2 + 4; vs.inboxWords = p.Dp / 2 + 4;
-            const size_t smem = 4 * ((size_t)vs.colsMax * vs.colWords + (size_t)2 * NW * 2 * vs.inboxWords);
+            const size_t smem = 4 * ((size_t)vs.colsMax * vs.colWords + (size_t)2 * NW * 2 * vs.inboxWords) + (size_t)2 * NW * 2 * 8;
             if (smem > (size_t)c->smem_optin) continue;
             r.ok = true; r.CL = CL; r.NT = NT; r.vs = vs; r.smem = smem;
             return r;
@@ -615,9 +616,15 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     auto launch_v = [&](bool up, bool wta) -> int {
         cudaError_t e;
         if (vc.ok) {
-            if (!up) e = launch_cluster(k_path_v2<DPL, false, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-            else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-            else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+            if (c->path_v_variant == 2) {          // CVR_PATH_KERNELS=v2: per-row cluster barrier instead of point-to-point hand-over
+                if (!up) e = launch_cluster(k_path_v2<DPL, false, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+            } else {
+                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+            }
             c->launches++;
             if (e != cudaSuccess) { c->err = std::string("k_path_v2 launch: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
             return CVR_OK;
