@@ -494,35 +494,63 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b)
         else done = true;
     } while (!done);
 }
-__global__ void k_ccl_init(const int16_t* __restrict__ img, int* __restrict__ label, int* __restrict__ size, int N, int newVal)
+// Run-based labelling: a pixel's first label is the start of its horizontal run (maximal stretch of valid pixels
+// whose neighbours differ by <= maxDiff), found with one ballot per 32 pixels; unions are then only needed between
+// vertically connected runs, once per run pair (at the first column of their overlap), and component sizes are
+// accumulated with one atomic per (warp, root) instead of one per pixel.
+__global__ void __launch_bounds__(128) k_ccl_runs(const int16_t* __restrict__ img, int* __restrict__ label, int* __restrict__ size, int W, int H, int B,
+                                                  int newVal, int maxDiff)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
-    if (i >= N) return;
-    const size_t o = (size_t)b * N + i;
-    label[o] = (img[o] != newVal) ? i : -1;
-    size[o] = 0;
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= B * H) return;
+    const size_t base = (size_t)row * W;
+    const int rowInFrame = row % H;
+    int carry = -1;                                           // start of the run that reaches into this chunk
+    int prevV = newVal;
+    for (int x0 = 0; x0 < W; x0 += 32) {
+        const int x = x0 + lane;
+        const int v = x < W ? (int)img[base + x] : newVal;
+        int left = __shfl_up_sync(0xffffffffu, v, 1);
+        if (lane == 0) left = prevV;
+        const bool valid = v != newVal;
+        const bool conn = valid && left != newVal && abs(v - left) <= maxDiff;       // connected to x-1 (false at x == 0: prevV starts as newVal)
+        const unsigned starts = __ballot_sync(0xffffffffu, valid && !conn);
+        const unsigned le = starts & (0xffffffffu >> (31 - lane));
+        const int s = le ? x0 + 31 - __clz(le) : carry;
+        if (x < W) { label[base + x] = valid ? rowInFrame * W + s : -1; size[base + x] = 0; }
+        // the run continuing into the next chunk starts at the last start of this chunk, or is the carried one
+        const int lastS = starts ? x0 + 31 - __clz(starts) : carry;
+        carry = __shfl_sync(0xffffffffu, valid ? lastS : -1, 31);
+        prevV = __shfl_sync(0xffffffffu, v, 31);
+    }
 }
-__global__ void k_ccl_merge(const int16_t* __restrict__ img, int* label, int W, int H, int newVal, int maxDiff)
+__global__ void k_ccl_vmerge(const int16_t* __restrict__ img, int* label, int W, int H, int newVal, int maxDiff)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, b = blockIdx.z;
-    if (x >= W) return;
+    if (x >= W || y + 1 >= H) return;
     const size_t fo = (size_t)b * W * H;
     const int i = y * W + x;
-    const int v = img[fo + i];
-    if (v == newVal) return;
+    const int v = img[fo + i], q = img[fo + i + W];
+    if (v == newVal || q == newVal || abs(v - q) > maxDiff) return;
+    if (x > 0) {
+        // the same pair of runs was already united at x-1 if both runs continue from x-1 and x-1 is vertically connected too
+        const int vl = img[fo + i - 1], ql = img[fo + i + W - 1];
+        if (vl != newVal && ql != newVal && abs(v - vl) <= maxDiff && abs(q - ql) <= maxDiff && abs(vl - ql) <= maxDiff) return;
+    }
     int* L = label + fo;
-    if (x + 1 < W) { const int q = img[fo + i + 1]; if (q != newVal && abs(v - q) <= maxDiff) uf_union(L, i, i + 1); }
-    if (y + 1 < H) { const int q = img[fo + i + W]; if (q != newVal && abs(v - q) <= maxDiff) uf_union(L, i, i + W); }
+    uf_union(L, L[i], L[i + W]);
 }
 __global__ void k_ccl_count(int* label, int* size, int N)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
-    if (i >= N) return;
     int* L = label + (size_t)b * N;
-    if (L[i] < 0) return;
-    const int r = uf_find(L, i);
+    const bool act = i < N && L[i] >= 0;
+    const unsigned amask = __ballot_sync(0xffffffffu, act);
+    if (!act) return;
+    const int r = uf_find(L, L[i]);
     L[i] = r;                       // roots stay fixed points, so concurrent flattening is safe
-    atomicAdd(&size[(size_t)b * N + r], 1);
+    const unsigned peers = __match_any_sync(amask, r);
+    if ((peers & ((1u << (threadIdx.x & 31)) - 1)) == 0) atomicAdd(&size[(size_t)b * N + r], __popc(peers));
 }
 __global__ void k_ccl_apply(int16_t* img, const int* __restrict__ label, const int* __restrict__ size, int N, int newVal, int maxSize)
 {
@@ -730,9 +758,9 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     if (c->prm.sgbm.speckle_window_size > 0) {
         const int N = p.W * p.H;
         const int maxDiff = CVR_DISP_SCALE * c->prm.sgbm.speckle_range;
-        k_ccl_init<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, N, p.INVALID);
+        k_ccl_runs<<<cvr_div_up(B * p.H, 4), 128, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, p.W, p.H, B, p.INVALID, maxDiff);
         LAUNCH_CHECK(c);
-        k_ccl_merge<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, p.W, p.H, p.INVALID, maxDiff);
+        k_ccl_vmerge<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, p.W, p.H, p.INVALID, maxDiff);
         LAUNCH_CHECK(c);
         k_ccl_count<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_label, c->d_size, N);
         LAUNCH_CHECK(c);
