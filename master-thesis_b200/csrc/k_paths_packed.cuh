@@ -57,26 +57,47 @@ __device__ __forceinline__ void stw(unsigned* p, const unsigned (&v)[NWD])
 }
 
 // One column update for one direction: Lp (previous costs of the source pixel, packed) -> L (this pixel); returns
-// the warp-wide minimum of L.
+// the warp-wide minimum of L.  EXACT = true: general form (any sign of C, Lp, delta).  EXACT = false: the caller
+// knows C >= 0 for this frame; if in addition the source costs are non-negative (minPrev >= 0) and delta >= 0 --
+// which is every column outside the wrap/saturation regimes -- the update shrinks to
+//     t = min(min(Lp[d-1], Lp[d+1], 32767 - P1s) + P1s, Lp[d]);  L = min(t - delta, 0) + C
+// (t in [0, 32767] and delta in [0, 32767], so t - delta cannot wrap); otherwise it takes the clamped form.
 template <int NWD, bool EXACT, bool HASPAD>
 __device__ __forceinline__ int column_update(const unsigned (&Lp)[NWD], int minPrev, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
                                              int P2, const PathK& k)
 {
     const int delta = (int)(short)(P2 + minPrev);
-    const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768)), ndeltap = pk2(-delta);
     unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1);
     unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1);
     if (lane == 0) left = 0x7fff7fffu;                 // Lp[-1] = MAX_COST
     if (lane == 31) right = 0x7fff7fffu;               // Lp[D]  = MAX_COST (padding lanes hold MAX_COST too)
+    const unsigned ndeltap = pk2(-delta);
     unsigned mnp = 0x7fff7fffu;
+    if (!EXACT && (minPrev | delta) >= 0) {
 #pragma unroll
-    for (int j = 0; j < NWD; j++) {
-        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);           // (Lp[2j-1], Lp[2j])
-        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);     // (Lp[2j+1], Lp[2j+2])
-        unsigned v = path_cost2<EXACT>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
-        if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
-        L[j] = v;
-        mnp = __vmins2(mnp, v);
+        for (int j = 0; j < NWD; j++) {
+            const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);           // (Lp[2j-1], Lp[2j])
+            const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);     // (Lp[2j+1], Lp[2j+2])
+            const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);
+            const unsigned t = __viaddmin_s16x2(n, k.P1p, Lp[j]);
+            unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, 0u), c[j]);
+            if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            L[j] = v;
+            mnp = __vmins2(mnp, v);
+        }
+    } else {
+        const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768));
+#pragma unroll
+        for (int j = 0; j < NWD; j++) {
+            const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
+            const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
+            unsigned v;
+            if (EXACT) v = path_cost2<true>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
+            else v = path_cost2<false>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
+            if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            L[j] = v;
+            mnp = __vmins2(mnp, v);
+        }
     }
     const int m = min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
     return __reduce_min_sync(0xffffffffu, m);
@@ -404,8 +425,8 @@ __device__ __forceinline__ void st_async_words(unsigned raddr, const unsigned (&
     }
 }
 
-template <int DPL, bool UP, bool WTA, bool HASPAD>
-__global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
+template <int DPL, bool UP, bool WTA, bool HASPAD, int MAXT>
+__global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
                                                                         int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     constexpr int NWD = DPL / 2;
@@ -463,20 +484,19 @@ __global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v3(const in
 
     const size_t frameRow0 = (size_t)b * H;
     unsigned cN[NWD], sN[NWD];
-    {
-        const int y0 = UP ? H - 1 : 0;
-        const size_t rb = ((frameRow0 + y0) * W1 + a) * colW + (size_t)lane * NWD;
-        ldw<NWD>((const unsigned*)C + rb, cN);
-        ldw<NWD>((const unsigned*)S + rb, sN);
-    }
-    for (int t = 0; t < H; t++) {
+    const long long nextRow = (UP ? -1LL : 1LL) * (long long)W1 * (long long)colW;
+    const size_t rb0 = ((frameRow0 + (UP ? H - 1 : 0)) * W1 + a) * colW + (size_t)lane * NWD;
+    const unsigned* rowC = (const unsigned*)C + rb0;                  // this lane's words of column a in the current row
+    unsigned* rowS = (unsigned*)S + rb0;
+    ldw<NWD>(rowC, cN);
+    ldw<NWD>(rowS, sN);
+    const int ncols = e - a;
+    for (int t = 0; t < H; t++, rowC += nextRow, rowS += nextRow) {
         const int y = UP ? H - 1 - t : t;
         const int rd = (t + 1) & 1, wr = t & 1;
         const unsigned waitPhase = (unsigned)(((t - 1) >> 1) & 1);
-        const size_t rowBase = ((frameRow0 + y) * W1 + a) * colW + (size_t)lane * NWD;
-        const unsigned* Cp = (const unsigned*)C + rowBase;
-        unsigned* Sp = (unsigned*)S + rowBase;
-        const long long nextRow = (UP ? -1LL : 1LL) * (long long)W1 * (long long)colW;
+        const unsigned* Cp = rowC;
+        unsigned* Sp = rowS;
         if (t > 0) {                                                   // previous row's edges of both neighbours
             if (lane == 0) {
                 if (hasL) mbar_arrive_expect_tx(myBarL + rd * barParityStride, edgeBytes);
@@ -492,17 +512,17 @@ __global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v3(const in
         ldw<NWD>(myInR + rd * parityStride + lane * NWD, edgeR);      // read before anything is pushed in this row
         const int edgeRMin = (int)myInR[rd * parityStride + dwords];
         unsigned* col = col0;
-        for (int xp = a; xp < e; xp++, col += colWords, Cp += colW, Sp += colW) {
+        for (int ci = 0; ci < ncols; ci++, col += colWords, Cp += colW, Sp += colW) {
+            const int xp = a + ci;
             const unsigned* colm = col - lane * NWD + 3 * dwords;
             unsigned c[NWD], s[NWD], s0[NWD];
 #pragma unroll
             for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = s0[j] = sN[j]; }
-            const bool lastCol = (xp + 1 == e);
+            const bool lastCol = (ci + 1 == ncols);
             if (!lastCol) { ldw<NWD>(Cp + colW, cN); ldw<NWD>(Sp + colW, sN); }
             else if (t + 1 < H) {                                      // next row's first column: in flight while the neighbours catch up
-                const unsigned* Cn = Cp - (size_t)(e - 1 - a) * colW + nextRow;
-                ldw<NWD>(Cn, cN);
-                ldw<NWD>((const unsigned*)Sp - (size_t)(e - 1 - a) * colW + nextRow, sN);
+                ldw<NWD>(rowC + nextRow, cN);
+                ldw<NWD>(rowS + nextRow, sN);
             }
             unsigned Lp1[NWD], Lp2[NWD], Lp3[NWD], L1[NWD], L2[NWD], L3[NWD];
 #pragma unroll
@@ -541,7 +561,7 @@ __global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v3(const in
             }
             stw<NWD>(col, L1); stw<NWD>(col + dwords, L2); stw<NWD>(col + 2 * dwords, L3);
             if (lane < 3) (col - lane * NWD)[3 * dwords + lane] = (unsigned)(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3));
-            if (xp == a && hasL) {                                     // my first column's down-left costs -> left neighbour's right inbox
+            if (ci == 0 && hasL) {                                     // my first column's down-left costs -> left neighbour's right inbox
                 st_async_words<NWD>(pushL_data + wr * inboxParityBytes + lane * NWD * 4, L3, pushL_bar + wr * barParityStride);
                 if (lane == 0) st_async_b32(pushL_data + wr * inboxParityBytes + dwords * 4, (unsigned)mn3, pushL_bar + wr * barParityStride);
             }

@@ -598,7 +598,7 @@ static VCfg pick_vcfg(const cvr_ctx* c)
     const SgbmDev& p = c->sg;
     VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = 0;
     const int nts[3] = { 1024, 512, 256 }, cls[4] = { 8, 4, 2, 1 };
-    for (int ni = 0; ni < 3; ni++)
+    for (int ni = (c->pathv_max_nt <= 256 ? 2 : (c->pathv_max_nt <= 512 ? 1 : 0)); ni < 3; ni++)
         for (int ci = 0; ci < 4; ci++) {
             const int NT = nts[ni], CL = cls[ci], NW = NT / 32, GW = CL * NW;
             if (NT > 512 && p.Dp > 128) continue;                      // wide disparity ranges need > 64 registers per thread
@@ -648,10 +648,14 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
                 if (!up) e = launch_cluster(k_path_v2<DPL, false, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+            } else if (vc.NT > 512) {
+                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             } else {
-                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             }
             c->launches++;
             if (e != cudaSuccess) { c->err = std::string("k_path_v2 launch: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
