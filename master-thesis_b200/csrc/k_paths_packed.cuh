@@ -425,9 +425,63 @@ __device__ __forceinline__ void st_async_words(unsigned raddr, const unsigned (&
     }
 }
 
+// Fast column update (preconditions checked by the caller, all warp-uniform: C >= 0 in this frame, source costs
+// non-negative, 0 <= delta <= 32767): returns this lane's minimum of L (not yet reduced over the warp).
+template <int NWD, bool HASPAD>
+__device__ __forceinline__ int col_fast(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
+                                        const PathK& k)
+{
+    unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1);
+    unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1);
+    if (lane == 0) left = 0x7fff7fffu;
+    if (lane == 31) right = 0x7fff7fffu;
+    unsigned mnp = 0x7fff7fffu;
+#pragma unroll
+    for (int j = 0; j < NWD; j++) {
+        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
+        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
+        const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);
+        const unsigned t = __viaddmin_s16x2(n, k.P1p, Lp[j]);
+        unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, 0u), c[j]);
+        if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+        L[j] = v;
+        mnp = __vmins2(mnp, v);
+    }
+    return min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
+}
+// General column update for a given delta (any sign of Lp, delta; EXACT also any sign of C).
+template <int NWD, bool EXACT, bool HASPAD>
+__device__ __forceinline__ int col_general(const unsigned (&Lp)[NWD], int delta, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D, const PathK& k)
+{
+    unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1);
+    unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1);
+    if (lane == 0) left = 0x7fff7fffu;
+    if (lane == 31) right = 0x7fff7fffu;
+    const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768)), ndeltap = pk2(-delta);
+    unsigned mnp = 0x7fff7fffu;
+#pragma unroll
+    for (int j = 0; j < NWD; j++) {
+        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
+        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
+        unsigned v = path_cost2<EXACT>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
+        if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+        L[j] = v;
+        mnp = __vmins2(mnp, v);
+    }
+    return min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
+}
+// What the next pixel on a path needs to know about this pixel's minimum, precomputed by the producer:
+//   A = -delta in both halves, B = (delta & 0xffff) | 0x80000000 if the fast form is not allowed (min < 0 or delta < 0)
+__device__ __forceinline__ void path_info(int mn, int P2, unsigned& A, unsigned& B)
+{
+    const int delta = (int)(short)(P2 + mn);
+    A = pk2(-delta);
+    B = ((unsigned)delta & 0xffffu) | ((unsigned)(mn | delta) & 0x80000000u);
+}
+
 template <int DPL, bool UP, bool WTA, bool HASPAD, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                                        int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
+                                                     int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     constexpr int NWD = DPL / 2;
     const int NT = blockDim.x, NW = NT / 32;
@@ -441,18 +495,24 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     const int ctaFirst = (int)(((long long)W1 * (rank * NW)) / GW);
     const int a = (int)(((long long)W1 * gw) / GW), e = (int)(((long long)W1 * (gw + 1)) / GW);
     const int dwords = p.Dp / 2;
-    const int colWords = vs.colWords;
+    const int colWords = vs.colWords;                                 // 3*dwords + 8: costs of 3 directions, then A[3], pad, B[3], pad (path_info)
+    const int infoOff = 3 * dwords;
     unsigned* state = smv;                                            // [colsMax][colWords]
-    unsigned* inbox = smv + (size_t)vs.colsMax * colWords;            // [2 parity][NW][2 sides][inboxWords]
+    unsigned* inbox = smv + (size_t)vs.colsMax * colWords;            // [2 parity][NW][2 sides][inboxWords]: costs, A, B, pad
     const size_t parityStride = (size_t)NW * 2 * vs.inboxWords;
-    unsigned long long* bars = (unsigned long long*)(inbox + 2 * parityStride);   // [2 parity][NW][2 sides] mbarriers (8-byte aligned: all counts are even)
+    unsigned long long* bars = (unsigned long long*)(inbox + 2 * parityStride);
+    unsigned A0, B0;
+    path_info(0, P2, A0, B0);                                         // the zero state: minimum 0
     for (int i = threadIdx.x; i < vs.colsMax * colWords; i += NT) {
         const int w = i % colWords;
-        state[i] = (w < 3 * dwords) ? (((w % dwords) * 2 < D) ? 0u : 0x7fff7fffu) : 0u;
+        unsigned v;
+        if (w < infoOff) v = ((w % dwords) * 2 < D) ? 0u : 0x7fff7fffu;
+        else v = (w - infoOff < 3) ? A0 : ((w - infoOff >= 4 && w - infoOff < 7) ? B0 : 0u);
+        state[i] = v;
     }
     for (int i = threadIdx.x; i < 2 * NW * 2 * vs.inboxWords; i += NT) {
         const int w = i % vs.inboxWords;
-        inbox[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : 0u;
+        inbox[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : (w == dwords ? A0 : (w == dwords + 1 ? B0 : 0u));
     }
     if (threadIdx.x < 2 * NW * 2) mbar_init(smem_u32(bars + threadIdx.x), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -460,14 +520,12 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
     CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
     const size_t colW = (size_t)dwords;
-    const unsigned edgeBytes = 32u * NWD * 4u + 4u;                   // 32 lanes x NWD words + the minimum
-    // my inboxes / barriers (side 0 = from the left neighbour, side 1 = from the right neighbour), parity 0 addresses
+    const unsigned edgeBytes = 32u * NWD * 4u + 8u;                   // 32 lanes x NWD words + A + B
     const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * vs.inboxWords;
     const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * vs.inboxWords;
     const unsigned myBarL = smem_u32(bars + (size_t)warp * 2 + 0), myBarR = smem_u32(bars + (size_t)warp * 2 + 1);
     const unsigned barParityStride = (unsigned)(NW * 2 * 8), inboxParityBytes = (unsigned)(parityStride * 4);
     const bool hasL = gw > 0, hasR = gw + 1 < GW;
-    // remote (shared::cluster) addresses of the neighbour slots I fill, parity 0
     unsigned pushR_data = 0, pushR_bar = 0, pushL_data = 0, pushL_bar = 0;
     if (hasR) {
         const int r2 = (gw + 1) / NW, w2 = (gw + 1) % NW;
@@ -479,7 +537,7 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
         pushL_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 1) * vs.inboxWords), r2);
         pushL_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 1), r2);
     }
-    unsigned* const col0 = state + (size_t)(a - ctaFirst) * colWords + lane * NWD;
+    unsigned* const colBase0 = state + (size_t)(a - ctaFirst) * colWords;
     cluster.sync();                                                   // state, inboxes and barriers of every CTA are initialised
 
     const size_t frameRow0 = (size_t)b * H;
@@ -494,10 +552,10 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     for (int t = 0; t < H; t++, rowC += nextRow, rowS += nextRow) {
         const int y = UP ? H - 1 - t : t;
         const int rd = (t + 1) & 1, wr = t & 1;
-        const unsigned waitPhase = (unsigned)(((t - 1) >> 1) & 1);
         const unsigned* Cp = rowC;
         unsigned* Sp = rowS;
         if (t > 0) {                                                   // previous row's edges of both neighbours
+            const unsigned waitPhase = (unsigned)(((t - 1) >> 1) & 1);
             if (lane == 0) {
                 if (hasL) mbar_arrive_expect_tx(myBarL + rd * barParityStride, edgeBytes);
                 if (hasR) mbar_arrive_expect_tx(myBarR + rd * barParityStride, edgeBytes);
@@ -506,72 +564,93 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
             if (hasL) mbar_wait(myBarL + rd * barParityStride, waitPhase);
             if (hasR) mbar_wait(myBarR + rd * barParityStride, waitPhase);
         }
+        // sources that come from the neighbours (read before anything is pushed in this row)
         unsigned carry[NWD], edgeR[NWD];
-        ldw<NWD>(myInL + rd * parityStride + lane * NWD, carry);
-        int carryMin = (int)myInL[rd * parityStride + dwords];
-        ldw<NWD>(myInR + rd * parityStride + lane * NWD, edgeR);      // read before anything is pushed in this row
-        const int edgeRMin = (int)myInR[rd * parityStride + dwords];
-        unsigned* col = col0;
-        for (int ci = 0; ci < ncols; ci++, col += colWords, Cp += colW, Sp += colW) {
-            const int xp = a + ci;
-            const unsigned* colm = col - lane * NWD + 3 * dwords;
+        const unsigned* inL = myInL + rd * parityStride;
+        const unsigned* inR = myInR + rd * parityStride;
+        ldw<NWD>(inL + lane * NWD, carry);
+        unsigned carryA = inL[dwords], carryB = inL[dwords + 1];
+        ldw<NWD>(inR + lane * NWD, edgeR);
+        const unsigned edgeRA = inR[dwords], edgeRB = inR[dwords + 1];
+        unsigned* cb = colBase0;                                       // base of the current column's record
+        for (int ci = 0; ci < ncols; ci++, cb += colWords, Cp += colW, Sp += colW) {
+            unsigned* col = cb + lane * NWD;
             unsigned c[NWD], s[NWD], s0[NWD];
 #pragma unroll
             for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = s0[j] = sN[j]; }
             const bool lastCol = (ci + 1 == ncols);
             if (!lastCol) { ldw<NWD>(Cp + colW, cN); ldw<NWD>(Sp + colW, sN); }
-            else if (t + 1 < H) {                                      // next row's first column: in flight while the neighbours catch up
-                ldw<NWD>(rowC + nextRow, cN);
-                ldw<NWD>(rowS + nextRow, sN);
-            }
+            else if (t + 1 < H) { ldw<NWD>(rowC + nextRow, cN); ldw<NWD>(rowS + nextRow, sN); }   // next row's first column
+            // ---- sources: everything is read before this column's record is overwritten ----
             unsigned Lp1[NWD], Lp2[NWD], Lp3[NWD], L1[NWD], L2[NWD], L3[NWD];
 #pragma unroll
             for (int j = 0; j < NWD; j++) Lp1[j] = carry[j];
-            const int min1 = carryMin;
-            ldw<NWD>(col, carry);
-            carryMin = (int)colm[0];
+            const unsigned A1 = carryA, B1 = carryB;
+            ldw<NWD>(col, carry);                                      // old down-right costs of this column: next column's source
+            carryA = cb[infoOff + 0]; carryB = cb[infoOff + 4];
             ldw<NWD>(col + dwords, Lp2);
-            const int min2 = (int)colm[1];
-            int min3;
-            if (!lastCol) { ldw<NWD>(col + colWords + 2 * dwords, Lp3); min3 = (int)colm[colWords + 2]; }
+            const unsigned A2 = cb[infoOff + 1], B2 = cb[infoOff + 5];
+            unsigned A3, B3;
+            if (!lastCol) { ldw<NWD>(col + colWords + 2 * dwords, Lp3); A3 = cb[colWords + infoOff + 2]; B3 = cb[colWords + infoOff + 6]; }
             else {
 #pragma unroll
                 for (int j = 0; j < NWD; j++) Lp3[j] = edgeR[j];
-                min3 = edgeRMin;
+                A3 = edgeRA; B3 = edgeRB;
             }
             int mn1, mn2, mn3;
-            if (!exact) {
-                mn1 = column_update<NWD, false, HASPAD>(Lp1, min1, c, L1, lane, D, P2, k);
-                mn2 = column_update<NWD, false, HASPAD>(Lp2, min2, c, L2, lane, D, P2, k);
-                mn3 = column_update<NWD, false, HASPAD>(Lp3, min3, c, L3, lane, D, P2, k);
+            const bool fastCol = !exact && (int)(B1 | B2 | B3) >= 0;
+            if (fastCol) {                                             // the common case: one straight-line block for all three directions
+                const int m1 = col_fast<NWD, HASPAD>(Lp1, A1, c, L1, lane, D, k);
+                const int m2 = col_fast<NWD, HASPAD>(Lp2, A2, c, L2, lane, D, k);
+                const int m3 = col_fast<NWD, HASPAD>(Lp3, A3, c, L3, lane, D, k);
+                mn1 = __reduce_min_sync(0xffffffffu, m1);
+                mn2 = __reduce_min_sync(0xffffffffu, m2);
+                mn3 = __reduce_min_sync(0xffffffffu, m3);
                 acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3);
-                if (min(min(mn1, mn2), mn3) < 0) {
-                    exact = true;
-                    if (lane == 0) atomicOr(&flags[b], 2);
+            } else {
+                const int d1 = (int)(short)(B1 & 0xffffu), d2 = (int)(short)(B2 & 0xffffu), d3 = (int)(short)(B3 & 0xffffu);
+                int m1, m2, m3;
+                if (!exact) {
+                    m1 = col_general<NWD, false, HASPAD>(Lp1, d1, c, L1, lane, D, k);
+                    m2 = col_general<NWD, false, HASPAD>(Lp2, d2, c, L2, lane, D, k);
+                    m3 = col_general<NWD, false, HASPAD>(Lp3, d3, c, L3, lane, D, k);
+                } else {
+                    m1 = col_general<NWD, true, HASPAD>(Lp1, d1, c, L1, lane, D, k);
+                    m2 = col_general<NWD, true, HASPAD>(Lp2, d2, c, L2, lane, D, k);
+                    m3 = col_general<NWD, true, HASPAD>(Lp3, d3, c, L3, lane, D, k);
+                }
+                mn1 = __reduce_min_sync(0xffffffffu, m1);
+                mn2 = __reduce_min_sync(0xffffffffu, m2);
+                mn3 = __reduce_min_sync(0xffffffffu, m3);
+                acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);   // valid for any signs
+            }
+            if (min(min(mn1, mn2), mn3) < 0) {                         // a negative path cost: the unsigned fast sums are void, stay exact from here on
+                if (fastCol) {
 #pragma unroll
                     for (int j = 0; j < NWD; j++) s[j] = s0[j];
                     acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
                 }
-            } else {
-                mn1 = column_update<NWD, true, HASPAD>(Lp1, min1, c, L1, lane, D, P2, k);
-                mn2 = column_update<NWD, true, HASPAD>(Lp2, min2, c, L2, lane, D, P2, k);
-                mn3 = column_update<NWD, true, HASPAD>(Lp3, min3, c, L3, lane, D, P2, k);
-                if (min(min(mn1, mn2), mn3) < 0 && lane == 0) atomicOr(&flags[b], 2);
-                acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
+                exact = true;
+                if (lane == 0) atomicOr(&flags[b], 2);
             }
             stw<NWD>(col, L1); stw<NWD>(col + dwords, L2); stw<NWD>(col + 2 * dwords, L3);
-            if (lane < 3) (col - lane * NWD)[3 * dwords + lane] = (unsigned)(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3));
+            // lanes 0..2 derive what the next pixel on each path needs from this pixel's minimum
+            unsigned iA, iB;
+            path_info(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3), P2, iA, iB);
+            if (lane < 3) { cb[infoOff + lane] = iA; cb[infoOff + 4 + lane] = iB; }
             if (ci == 0 && hasL) {                                     // my first column's down-left costs -> left neighbour's right inbox
-                st_async_words<NWD>(pushL_data + wr * inboxParityBytes + lane * NWD * 4, L3, pushL_bar + wr * barParityStride);
-                if (lane == 0) st_async_b32(pushL_data + wr * inboxParityBytes + dwords * 4, (unsigned)mn3, pushL_bar + wr * barParityStride);
+                const unsigned dst = pushL_data + wr * inboxParityBytes, bar = pushL_bar + wr * barParityStride;
+                st_async_words<NWD>(dst + lane * NWD * 4, L3, bar);
+                if (lane == 2) { st_async_b32(dst + dwords * 4, iA, bar); st_async_b32(dst + dwords * 4 + 4, iB, bar); }
             }
             if (lastCol && hasR) {                                     // my last column's down-right costs -> right neighbour's left inbox
-                st_async_words<NWD>(pushR_data + wr * inboxParityBytes + lane * NWD * 4, L1, pushR_bar + wr * barParityStride);
-                if (lane == 0) st_async_b32(pushR_data + wr * inboxParityBytes + dwords * 4, (unsigned)mn1, pushR_bar + wr * barParityStride);
+                const unsigned dst = pushR_data + wr * inboxParityBytes, bar = pushR_bar + wr * barParityStride;
+                st_async_words<NWD>(dst + lane * NWD * 4, L1, bar);
+                if (lane == 0) { st_async_b32(dst + dwords * 4, iA, bar); st_async_b32(dst + dwords * 4 + 4, iB, bar); }
             }
             if (!WTA || storeS) stw<NWD>(Sp, s);
-            if (WTA) wta_column2<NWD>(s, lane, p, raw + (frameRow0 + y) * p.W + xp + p.minX1, aux + (frameRow0 + y) * W1 + xp);
-            __syncwarp();                                              // the minima written by lanes 0..2 are read by all lanes in the next row
+            if (WTA) wta_column2<NWD>(s, lane, p, raw + (frameRow0 + y) * p.W + a + ci + p.minX1, aux + (frameRow0 + y) * W1 + a + ci);
+            __syncwarp();                                              // the info words written by lanes 0..2 are read by all lanes in the next row
         }
     }
     cluster.sync();                                                   // nobody exits while a neighbour may still write into its inbox

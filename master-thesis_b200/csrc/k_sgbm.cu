@@ -604,7 +604,7 @@ static VCfg pick_vcfg(const cvr_ctx* c)
             if (NT > 512 && p.Dp > 128) continue;                      // wide disparity ranges need > 64 registers per thread
             if (GW > p.W1) continue;                                   // every warp must own at least one column
             VState vs;
-            vs.colsMax = (p.W1 + CL - 1) / CL + 1; vs.colWords = 3 * p.Dp / 2 + 4; vs.inboxWords = p.Dp / 2 + 4;
+            vs.colsMax = (p.W1 + CL - 1) / CL + 1; vs.colWords = 3 * p.Dp / 2 + 8; vs.inboxWords = p.Dp / 2 + 4;
             const size_t smem = 4 * ((size_t)vs.colsMax * vs.colWords + (size_t)2 * NW * 2 * vs.inboxWords) + (size_t)2 * NW * 2 * 8;
             if (smem > (size_t)c->smem_optin) continue;
             r.ok = true; r.CL = CL; r.NT = NT; r.vs = vs; r.smem = smem;
