@@ -32,6 +32,7 @@ EXPORTS = [
     "cvr_default_params", "cvr_create", "cvr_destroy", "cvr_last_error", "cvr_version", "cvr_disparity", "cvr_prune",
     "cvr_reproject_cloud", "cvr_triangulate", "cvr_voxel_grid", "cvr_sor", "cvr_process_batch", "cvr_points_to_pcl",
     "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling", "cvr_prune_noalloc",
+    "cvr_submit_batch", "cvr_wait_batch",
 ]
 
 
@@ -104,6 +105,8 @@ def load_library():
     lib.cvr_voxel_grid.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.cvr_sor.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     lib.cvr_process_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(Batch)]
+    lib.cvr_submit_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(Batch)]
+    lib.cvr_wait_batch.argtypes = [C.c_void_p]
     lib.cvr_debug_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.cvr_last_timings.argtypes = [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_float), C.c_int]
     lib.cvr_set_profiling.argtypes = [C.c_void_p, C.c_int]
@@ -335,6 +338,12 @@ class Reconstruct3D:
 
     def process_batch_raw(self, io, nframes):
         self._check(self.lib.cvr_process_batch(self.ctx, int(nframes), C.byref(io)))
+
+    def submit_batch_raw(self, io, nframes):
+        self._check(self.lib.cvr_submit_batch(self.ctx, int(nframes), C.byref(io)))
+
+    def wait_batch(self):
+        self._check(self.lib.cvr_wait_batch(self.ctx))
 
 
 def points_to_pcl(points):

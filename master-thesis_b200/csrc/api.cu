@@ -130,6 +130,14 @@ static void free_all(cvr_ctx* c)
                      c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags };
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->pipe_ready) {
+        for (int s = 0; s < 2; s++) {
+            PipeSlot& sl = c->slot[s];
+            cudaFree(sl.d_in[0]); cudaFree(sl.d_in[1]); cudaFree(sl.d_out); cudaFree(sl.d_outcnt); cudaFree(sl.d_outdisp);
+            cudaEventDestroy(sl.evH2D); cudaEventDestroy(sl.evDone);
+        }
+        cudaStreamDestroy(c->copy_stream); cudaStreamDestroy(c->d2h_stream);
+    }
     for (auto& t : c->timers) cudaEventDestroy(t.ev);
     if (c->stream) cudaStreamDestroy(c->stream);
 }
@@ -151,6 +159,8 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     if (!c) return CVR_ERR_CUDA;
     c->prm = *p; c->device = device; c->maxB = p->max_batch; c->sm_count = prop.multiProcessorCount;
     c->launches = 0; c->profiling = false; c->timers_used = 0; c->stream = nullptr; c->h_counts = nullptr;
+    c->pipe_ready = false; c->copy_stream = nullptr; c->d2h_stream = nullptr; c->n_submit = c->n_wait = 0;
+    memset(c->slot, 0, sizeof(c->slot));
     fill_dev_params(c);
     c->smem_optin = (int)prop.sharedMemPerBlockOptin;
     { const char* e_ = getenv("CVR_PATH_KERNELS"); c->force_generic = e_ && strcmp(e_, "generic") == 0; c->path_v_variant = (e_ && strcmp(e_, "v2") == 0) ? 2 : 3;
@@ -203,6 +213,7 @@ extern "C" int cvr_destroy(cvr_ctx* c)
     if (!c) return CVR_OK;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
+    if (c->pipe_ready) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->d2h_stream); }
     free_all(c);
     delete c;
     return CVR_OK;
@@ -389,20 +400,64 @@ __global__ void k_copy_clouds(const cvr_point* __restrict__ src, size_t srcStrid
     if (blockIdx.x == 0 && threadIdx.x == 0 && cntOut) cntOut[b] = cnt[b];
 }
 
-extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
+// Enqueues the whole per-frame chain for B frames on the compute stream; *fin / *fcnt receive the buffers that hold
+// the last enabled stage's clouds (nullptr when only disparity was asked for).
+static int enqueue_chain(cvr_ctx* c, int B, int stages, const uint8_t* dl, size_t lstep, size_t lfs, const uint8_t* dr, size_t rstep, size_t rfs, int ch,
+                         const cvr_point** fin, const int** fcnt)
 {
-    if (!c) return CVR_ERR_INVALID_ARG;
-    STEREO_ONLY(c);
+    const bool wantCloud = (stages & 2) != 0, wantVox = (stages & 4) != 0, wantSor = (stages & 8) != 0;
+    *fin = nullptr; *fcnt = nullptr;
+    int rc = cvr_launch_gray(c, B, dl, lstep, lfs, dr, rstep, rfs, ch);
+    if (rc) return rc;
+    cvr_stage_mark(c, "gray");
+    rc = cvr_launch_sgbm(c, B);
+    if (rc) return rc;
+    if (wantCloud || wantVox || wantSor) {
+        rc = cvr_launch_prune(c, B, c->d_med);
+        if (rc) return rc;
+        if (c->prm.cloud_mode == CVR_CLOUD_REPROJECT)
+            rc = cvr_launch_cloud(c, B, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, dl, lstep, lfs, ch);
+        else
+            rc = cvr_launch_cloud(c, B, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, c->d_mask, dl, lstep, lfs, ch);
+        if (rc) return rc;
+        *fin = c->d_cloud; *fcnt = c->d_ncloud;
+        if (wantVox) {
+            rc = cvr_launch_voxel(c, B, *fin, (size_t)c->maxN, *fcnt);
+            if (rc) return rc;
+            *fin = c->d_vox; *fcnt = c->d_nvox;
+        }
+        if (wantSor) {
+            rc = cvr_launch_sor(c, B, *fin, (size_t)c->maxN, *fcnt, 0);
+            if (rc) return rc;
+            *fin = c->d_sorout; *fcnt = c->d_nout;
+        }
+    }
+    return CVR_OK;
+}
+
+static int check_batch_args(cvr_ctx* c, int nframes, const cvr_batch* io)
+{
     REQUIRE(c, io && nframes >= 1, "bad batch");
     if (nframes > c->maxB) { c->err = "nframes exceeds max_batch"; return CVR_ERR_CAPACITY; }
     REQUIRE(c, io->left && io->right, "null image pointer");
     const int ch = io->channels;
     REQUIRE(c, ch == 1 || ch == 3 || ch == 4, "channels must be 1, 3 or 4");
+    const size_t rowBytes = (size_t)c->sg.W * ch;
+    REQUIRE(c, io->left_step >= rowBytes && io->right_step >= rowBytes, "step smaller than a row");
+    REQUIRE(c, !io->disp || io->disp_step >= (size_t)c->sg.W * 2, "disp_step smaller than a row");
+    return CVR_OK;
+}
+
+extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    int rc = check_batch_args(c, nframes, io);
+    if (rc) return rc;
+    const int ch = io->channels;
     const int W = c->sg.W, H = c->sg.H, B = nframes;
     const size_t rowBytes = (size_t)W * ch;
-    REQUIRE(c, io->left_step >= rowBytes && io->right_step >= rowBytes, "step smaller than a row");
     const int stages = io->stages ? io->stages : 15;
-    const bool wantCloud = (stages & 2) != 0, wantVox = (stages & 4) != 0, wantSor = (stages & 8) != 0;
     CVR_CUDA(c, cudaSetDevice(c->device));
     timers_begin(c);
     const uint8_t *dl, *dr; size_t lstep, lfs, rstep, rfs;
@@ -416,36 +471,12 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     } else {
         dl = io->left; dr = io->right; lstep = io->left_step; rstep = io->right_step; lfs = io->left_frame_stride; rfs = io->right_frame_stride;
     }
-    int rc = cvr_launch_gray(c, B, dl, lstep, lfs, dr, rstep, rfs, ch);
-    if (rc) return rc;
-    cvr_stage_mark(c, "gray");
-    rc = cvr_launch_sgbm(c, B);
-    if (rc) return rc;
     const cvr_point* fin = nullptr; const int* fcnt = nullptr;
-    if (wantCloud || wantVox || wantSor) {
-        rc = cvr_launch_prune(c, B, c->d_med);
-        if (rc) return rc;
-        if (c->prm.cloud_mode == CVR_CLOUD_REPROJECT)
-            rc = cvr_launch_cloud(c, B, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, dl, lstep, lfs, ch);
-        else
-            rc = cvr_launch_cloud(c, B, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, c->d_mask, dl, lstep, lfs, ch);
-        if (rc) return rc;
-        fin = c->d_cloud; fcnt = c->d_ncloud;
-        if (wantVox) {
-            rc = cvr_launch_voxel(c, B, fin, (size_t)c->maxN, fcnt);
-            if (rc) return rc;
-            fin = c->d_vox; fcnt = c->d_nvox;
-        }
-        if (wantSor) {
-            rc = cvr_launch_sor(c, B, fin, (size_t)c->maxN, fcnt, 0);
-            if (rc) return rc;
-            fin = c->d_sorout; fcnt = c->d_nout;
-        }
-    }
+    rc = enqueue_chain(c, B, stages, dl, lstep, lfs, dr, rstep, rfs, ch, &fin, &fcnt);
+    if (rc) return rc;
     // ---- outputs ----
     if (io->disp) {
         const cudaMemcpyKind kind = io->mem == CVR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
-        REQUIRE(c, io->disp_step >= (size_t)W * 2, "disp_step smaller than a row");
         for (int i = 0; i < B; i++)
             CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io->disp + (size_t)i * io->disp_frame_stride, io->disp_step, c->d_med + (size_t)i * W * H, (size_t)W * 2,
                                           (size_t)W * 2, H, kind, c->stream));
@@ -476,6 +507,96 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     cvr_stage_mark(c, "out");
     rc = sync_check(c);
     timers_end(c);
+    return rc;
+}
+
+// ---- pipelined host path: two batches in flight, the upload of batch i+1 overlaps the kernels of batch i ----
+static int pipe_init(cvr_ctx* c)
+{
+    if (c->pipe_ready) return CVR_OK;
+    const size_t B = (size_t)c->maxB, HW = (size_t)c->sg.W * c->sg.H, N = (size_t)c->maxN;
+    CVR_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    CVR_CUDA(c, cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
+    for (int s = 0; s < 2; s++) {
+        PipeSlot& sl = c->slot[s];
+        CVR_CUDA(c, dalloc(&sl.d_in[0], B * HW * 4)); CVR_CUDA(c, dalloc(&sl.d_in[1], B * HW * 4));
+        CVR_CUDA(c, dalloc(&sl.d_out, B * N)); CVR_CUDA(c, dalloc(&sl.d_outcnt, B)); CVR_CUDA(c, dalloc(&sl.d_outdisp, B * HW));
+        CVR_CUDA(c, cudaEventCreateWithFlags(&sl.evH2D, cudaEventDisableTiming));
+        CVR_CUDA(c, cudaEventCreateWithFlags(&sl.evDone, cudaEventDisableTiming));
+        sl.busy = false; sl.used = false;
+    }
+    c->pipe_ready = true;
+    return CVR_OK;
+}
+
+extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    int rc = check_batch_args(c, nframes, io);
+    if (rc) return rc;
+    REQUIRE(c, io->mem == CVR_MEM_HOST, "cvr_submit_batch takes host buffers (device-resident data needs no pipelining)");
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    rc = pipe_init(c);
+    if (rc) return rc;
+    PipeSlot& sl = c->slot[c->n_submit & 1];
+    if (sl.busy) { c->err = "two batches are already in flight: call cvr_wait_batch first"; return CVR_ERR_CAPACITY; }
+    const int ch = io->channels, W = c->sg.W, H = c->sg.H, B = nframes;
+    const size_t rowBytes = (size_t)W * ch;
+    const int stages = io->stages ? io->stages : 15;
+    // upload on the copy stream, after the kernels of the batch that last used this slot's staging buffers
+    if (sl.used) CVR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, sl.evDone, 0));
+    for (int i = 0; i < B; i++) {
+        CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[0] + (size_t)i * rowBytes * H, rowBytes, io->left + (size_t)i * io->left_frame_stride, io->left_step, rowBytes, H, cudaMemcpyHostToDevice, c->copy_stream));
+        CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[1] + (size_t)i * rowBytes * H, rowBytes, io->right + (size_t)i * io->right_frame_stride, io->right_step, rowBytes, H, cudaMemcpyHostToDevice, c->copy_stream));
+    }
+    CVR_CUDA(c, cudaEventRecord(sl.evH2D, c->copy_stream));
+    CVR_CUDA(c, cudaStreamWaitEvent(c->stream, sl.evH2D, 0));
+    const cvr_point* fin = nullptr; const int* fcnt = nullptr;
+    rc = enqueue_chain(c, B, stages, sl.d_in[0], rowBytes, rowBytes * H, sl.d_in[1], rowBytes, rowBytes * H, ch, &fin, &fcnt);
+    if (rc) return rc;
+    sl.hasCloud = fin != nullptr;
+    if (fin) {                                                         // park the results in the slot so the next batch may overwrite the workspace
+        k_copy_clouds<<<dim3(64, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, sl.d_out, (size_t)c->maxN, sl.d_outcnt);
+        c->launches++;
+    }
+    if (io->disp) CVR_CUDA(c, cudaMemcpyAsync(sl.d_outdisp, c->d_med, (size_t)B * W * H * 2, cudaMemcpyDeviceToDevice, c->stream));
+    CVR_CUDA(c, cudaEventRecord(sl.evDone, c->stream));
+    sl.io = *io; sl.nframes = B; sl.busy = true; sl.used = true;
+    c->n_submit++;
+    return CVR_OK;
+}
+
+extern "C" int cvr_wait_batch(cvr_ctx* c)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    if (!c->pipe_ready || c->n_wait >= c->n_submit) { c->err = "no batch in flight"; return CVR_ERR_INVALID_ARG; }
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    PipeSlot& sl = c->slot[c->n_wait & 1];
+    const cvr_batch& io = sl.io;
+    const int B = sl.nframes, W = c->sg.W, H = c->sg.H;
+    CVR_CUDA(c, cudaEventSynchronize(sl.evDone));
+    int* hc = c->h_counts + (size_t)c->maxB * (1 + (c->n_wait & 1));
+    int rc = CVR_OK;
+    if (sl.hasCloud && (io.cloud || io.cloud_count)) {
+        CVR_CUDA(c, cudaMemcpyAsync(hc, sl.d_outcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, c->d2h_stream));
+        CVR_CUDA(c, cudaStreamSynchronize(c->d2h_stream));
+        if (io.cloud_count) memcpy(io.cloud_count, hc, sizeof(int) * B);
+        if (io.cloud)
+            for (int i = 0; i < B; i++) {
+                if ((size_t)hc[i] > io.cloud_capacity) { c->err = "cloud_capacity too small"; rc = CVR_ERR_CAPACITY; break; }
+                if (hc[i] > 0)
+                    CVR_CUDA(c, cudaMemcpyAsync(io.cloud + (size_t)i * io.cloud_capacity, sl.d_out + (size_t)i * c->maxN, (size_t)hc[i] * sizeof(cvr_point),
+                                                cudaMemcpyDeviceToHost, c->d2h_stream));
+            }
+    }
+    if (io.disp)
+        for (int i = 0; i < B; i++)
+            CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io.disp + (size_t)i * io.disp_frame_stride, io.disp_step, sl.d_outdisp + (size_t)i * W * H, (size_t)W * 2,
+                                          (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->d2h_stream));
+    CVR_CUDA(c, cudaStreamSynchronize(c->d2h_stream));
+    sl.busy = false;
+    c->n_wait++;
     return rc;
 }
 

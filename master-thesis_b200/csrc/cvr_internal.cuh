@@ -67,6 +67,19 @@ struct StageTimer {
     cudaEvent_t ev;
 };
 
+// One in-flight batch of the pipelined host path (cvr_submit_batch / cvr_wait_batch).
+struct PipeSlot {
+    uint8_t* d_in[2];        // staged BGR/gray input of this slot
+    cvr_point* d_out;        // filtered clouds [B][maxN]
+    int* d_outcnt;           // [B]
+    int16_t* d_outdisp;      // [B][H][W]
+    cudaEvent_t evH2D, evDone;
+    bool busy, used;
+    cvr_batch io;
+    int nframes;
+    bool hasCloud;
+};
+
 struct cvr_ctx {
     cvr_params prm;
     SgbmDev sg;
@@ -126,6 +139,10 @@ struct cvr_ctx {
     int sor_grid_cap;        // max cells per frame
     int* h_counts;           // pinned [B]
     int* d_flags;            // misc flags [B][4]
+    PipeSlot slot[2];
+    bool pipe_ready;
+    cudaStream_t copy_stream, d2h_stream;
+    long long n_submit, n_wait;
     int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
     int smem_optin;          // max dynamic shared memory per block (opt-in)
     bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)

@@ -233,3 +233,50 @@ def test_batch_equals_single_frames(cvr, oracle):
         if near == 0:
             assert np.array_equal(clouds[i]["x"], kept["x"]) and np.array_equal(clouds[i]["r"], kept["r"])
     rec.close()
+
+
+def test_pipelined_submit_wait_equals_synchronous(cvr, oracle):
+    """cvr_submit_batch / cvr_wait_batch (two batches in flight) return exactly what cvr_process_batch returns."""
+    H, W, D, bs, B, NB = 60, 330, 64, 9, 3, 4
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, k=8), max_batch=B, voxel_leaf=0.05)
+    batches = []
+    for nb in range(NB):
+        Ls, Rs = zip(*[oracle.synth_pair(H, W, D, seed=70 + nb * B + i, color=True) for i in range(B)])
+        batches.append((np.stack(Ls), np.stack(Rs)))
+    want = [rec.ProcessFrames(L, R, want_disp=True) for (L, R) in batches]
+    cap = W * H
+    ios, outs = [], []
+    for (L, R) in batches:
+        disp = np.empty((B, H, W), np.int16)
+        clouds = np.empty((B, cap), cvr.POINT_DTYPE)
+        counts = np.zeros(B, np.int32)
+        io = cvr.Batch()
+        io.mem, io.channels = cvr.MEM_HOST, 3
+        io.left, io.left_step, io.left_frame_stride = L.ctypes.data, L.strides[1], L.strides[0]
+        io.right, io.right_step, io.right_frame_stride = R.ctypes.data, R.strides[1], R.strides[0]
+        io.disp, io.disp_step, io.disp_frame_stride = disp.ctypes.data, disp.strides[1], disp.strides[0]
+        io.cloud, io.cloud_capacity, io.cloud_count = clouds.ctypes.data, cap, counts.ctypes.data
+        io.stages = 15
+        ios.append(io)
+        outs.append((disp, clouds, counts))
+    rec.submit_batch_raw(ios[0], B)
+    for nb in range(1, NB):
+        rec.submit_batch_raw(ios[nb], B)
+        rec.wait_batch()
+    with pytest.raises(cvr.CvrError):          # only one batch is left in flight: a second wait after the last must fail
+        rec.wait_batch()
+        rec.wait_batch()
+    for nb in range(NB):
+        disp, clouds, counts = outs[nb]
+        wd, wc = want[nb]
+        assert np.array_equal(disp, wd), "batch %d" % nb
+        for i in range(B):
+            assert counts[i] == len(wc[i]) and np.array_equal(clouds[i, :counts[i]], wc[i])
+    # three outstanding submits are refused
+    rec.submit_batch_raw(ios[0], B)
+    rec.submit_batch_raw(ios[1], B)
+    with pytest.raises(cvr.CvrError):
+        rec.submit_batch_raw(ios[2], B)
+    rec.wait_batch()
+    rec.wait_batch()
+    rec.close()
