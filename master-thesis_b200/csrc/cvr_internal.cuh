@@ -146,6 +146,7 @@ struct cvr_ctx {
     int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
     int smem_optin;          // max dynamic shared memory per block (opt-in)
     bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)
+    bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)
     int path_v_variant;      // 3 = point-to-point edge hand-over (default), 2 = per-row cluster barrier (CVR_PATH_KERNELS=v2)
 };

@@ -116,6 +116,78 @@ __device__ __forceinline__ void acc_exact(unsigned (&s)[NWD], const unsigned (&L
     for (int j = 0; j < NWD; j++) s[j] = __vaddss2(s[j], L[j]);
 }
 
+// Fast column update (preconditions checked by the caller, all warp-uniform: C >= 0 in this frame, source costs
+// non-negative, 0 <= delta <= 32767): returns this lane's minimum of L (not yet reduced over the warp).
+// NN ("no neighbours"): when 0 <= P2s <= P1s (P2s = (short)P2 -- the reference's own default, block_size 27, lands
+// here because 96*27^2 wraps to 4448 while P1 stays 17496) and delta did not wrap (delta == P2s + min), the two
+// neighbour terms Lp[d+-1] + P1s >= min + P1s >= min + P2s = delta can never win the four-way minimum, so the update
+// is exactly  L = min(Lp[d] - delta, 0) + C  -- no shuffles, no permutes.
+template <int NWD, bool HASPAD, bool NN>
+__device__ __forceinline__ int col_fast(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
+                                        const PathK& k)
+{
+    unsigned mnp = 0x7fff7fffu;
+    if (NN) {
+#pragma unroll
+        for (int j = 0; j < NWD; j++) {
+            unsigned v = __vadd2(__viaddmin_s16x2(Lp[j], ndeltap, 0u), c[j]);
+            if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            L[j] = v;
+            mnp = __vmins2(mnp, v);
+        }
+    } else {
+        unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1);
+        unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1);
+        if (lane == 0) left = 0x7fff7fffu;
+        if (lane == 31) right = 0x7fff7fffu;
+#pragma unroll
+        for (int j = 0; j < NWD; j++) {
+            const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
+            const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
+            const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);
+            const unsigned t = __viaddmin_s16x2(n, k.P1p, Lp[j]);
+            unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, 0u), c[j]);
+            if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            L[j] = v;
+            mnp = __vmins2(mnp, v);
+        }
+    }
+    return min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
+}
+// General column update for a given delta (any sign of Lp, delta; EXACT also any sign of C).
+template <int NWD, bool EXACT, bool HASPAD>
+__device__ __forceinline__ int col_general(const unsigned (&Lp)[NWD], int delta, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D, const PathK& k)
+{
+    unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1);
+    unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1);
+    if (lane == 0) left = 0x7fff7fffu;
+    if (lane == 31) right = 0x7fff7fffu;
+    const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768)), ndeltap = pk2(-delta);
+    unsigned mnp = 0x7fff7fffu;
+#pragma unroll
+    for (int j = 0; j < NWD; j++) {
+        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
+        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
+        unsigned v = path_cost2<EXACT>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
+        if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+        L[j] = v;
+        mnp = __vmins2(mnp, v);
+    }
+    return min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
+}
+// What the next pixel on a path needs to know about this pixel's minimum, precomputed by the producer:
+//   A = -delta in both halves, B = (delta & 0xffff) | 0x80000000 if the fast form is not allowed (min < 0 or delta < 0)
+template <bool NN>
+__device__ __forceinline__ void path_info(int mn, int P2, unsigned& A, unsigned& B)
+{
+    const int delta = (int)(short)(P2 + mn);
+    A = pk2(-delta);
+    int bad = mn | delta;                                              // negative minimum or negative delta
+    if (NN && (delta - mn) != (int)(short)P2) bad = -1;                // delta wrapped around int16: the shortcut does not apply
+    B = ((unsigned)delta & 0xffffu) | ((unsigned)bad & 0x80000000u);
+}
+
+
 // ------------------------------------------------------------------------------------------------
 // Winner-take-all on packed S (A.5 first half): same result as wta_column, fewer instructions.
 //   argmin: one CREDUX.MIN on (S << 16 | d); uniqueness as an order-free predicate; S[best-1], S[best+1] fetched from
@@ -176,12 +248,13 @@ __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, 
 
 // ------------------------------------------------------------------------------------------------
 // Horizontal path, packed.  Same contract as k_path_h.
-template <int DPL, bool REVERSE, bool WTA, bool HASPAD>
+template <int DPL, bool REVERSE, bool WTA, bool HASPAD, bool NN>
 __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
                                                  int* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
 {
     constexpr int NWD = DPL / 2;
-    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    int lane = threadIdx.x & 31;
     if (warp >= B * p.H) return;
     const int b = warp / p.H, y = warp % p.H;
     const int W1 = p.W1, D = p.D;
@@ -194,13 +267,15 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
     unsigned* Sp = (unsigned*)S + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
     int16_t* rawp = raw + ((size_t)b * p.H + y) * p.W + p.minX1 + (REVERSE ? W1 - 1 : 0);
     int* auxp = aux + ((size_t)b * p.H + y) * W1 + (REVERSE ? W1 - 1 : 0);
-    bool exact = flags[b] != 0;
+    int* flagp = flags + b;
+    bool exact = *flagp != 0;
     PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
-    CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
+    CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2); CVR_PIN(lane);
     unsigned Lp[NWD];
 #pragma unroll
     for (int j = 0; j < NWD; j++) Lp[j] = ((lane * NWD + j) * 2 < D) ? 0u : 0x7fff7fffu;
-    int minPrev = 0;
+    unsigned iA, iB;
+    path_info<NN>(0, P2, iA, iB);                                          // the border column: minimum 0
     unsigned cN[NWD], sN[NWD];
 #pragma unroll
     for (int j = 0; j < NWD; j++) sN[j] = 0u;
@@ -214,17 +289,20 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
             ldw<NWD>(Cp + stepW, cN);
             if (accumulate) ldw<NWD>(Sp + stepW, sN);
         }
-        if (!exact) {
-            minPrev = column_update<NWD, false, HASPAD>(Lp, minPrev, c, L, lane, D, P2, k);
-            if (minPrev < 0) {                                             // first negative path cost of this frame: go exact (L itself is still right)
-                exact = true;
-                if (lane == 0) atomicOr(&flags[b], 2);
-                if (accumulate) acc_exact<NWD>(s, L);
-            } else if (accumulate) acc_fast<NWD>(s, L);
-        } else {
-            minPrev = column_update<NWD, true, HASPAD>(Lp, minPrev, c, L, lane, D, P2, k);
-            if (minPrev < 0 && lane == 0) atomicOr(&flags[b], 2);
-            if (accumulate) acc_exact<NWD>(s, L);
+        const bool fastCol = !exact && (int)iB >= 0;
+        int m;
+        if (fastCol) m = col_fast<NWD, HASPAD, NN>(Lp, iA, c, L, lane, D, k);
+        else if (!exact) m = col_general<NWD, false, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, lane, D, k);
+        else m = col_general<NWD, true, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, lane, D, k);
+        const int mn = __reduce_min_sync(0xffffffffu, m);
+        path_info<NN>(mn, P2, iA, iB);
+        if (accumulate) {
+            if (fastCol && mn >= 0) acc_fast<NWD>(s, L);
+            else acc_exact<NWD>(s, L);
+        }
+        if (mn < 0) {                                                  // negative path cost: later unsigned sums would be void -> exact from here on
+            exact = true;
+            if (lane == 0) atomicOr(flagp, 2);
         }
 #pragma unroll
         for (int j = 0; j < NWD; j++) { Lp[j] = L[j]; if (!accumulate) s[j] = L[j]; }
@@ -425,61 +503,7 @@ __device__ __forceinline__ void st_async_words(unsigned raddr, const unsigned (&
     }
 }
 
-// Fast column update (preconditions checked by the caller, all warp-uniform: C >= 0 in this frame, source costs
-// non-negative, 0 <= delta <= 32767): returns this lane's minimum of L (not yet reduced over the warp).
-template <int NWD, bool HASPAD>
-__device__ __forceinline__ int col_fast(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
-                                        const PathK& k)
-{
-    unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1);
-    unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1);
-    if (lane == 0) left = 0x7fff7fffu;
-    if (lane == 31) right = 0x7fff7fffu;
-    unsigned mnp = 0x7fff7fffu;
-#pragma unroll
-    for (int j = 0; j < NWD; j++) {
-        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
-        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
-        const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);
-        const unsigned t = __viaddmin_s16x2(n, k.P1p, Lp[j]);
-        unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, 0u), c[j]);
-        if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
-        L[j] = v;
-        mnp = __vmins2(mnp, v);
-    }
-    return min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
-}
-// General column update for a given delta (any sign of Lp, delta; EXACT also any sign of C).
-template <int NWD, bool EXACT, bool HASPAD>
-__device__ __forceinline__ int col_general(const unsigned (&Lp)[NWD], int delta, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D, const PathK& k)
-{
-    unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1);
-    unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1);
-    if (lane == 0) left = 0x7fff7fffu;
-    if (lane == 31) right = 0x7fff7fffu;
-    const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768)), ndeltap = pk2(-delta);
-    unsigned mnp = 0x7fff7fffu;
-#pragma unroll
-    for (int j = 0; j < NWD; j++) {
-        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
-        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
-        unsigned v = path_cost2<EXACT>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
-        if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
-        L[j] = v;
-        mnp = __vmins2(mnp, v);
-    }
-    return min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
-}
-// What the next pixel on a path needs to know about this pixel's minimum, precomputed by the producer:
-//   A = -delta in both halves, B = (delta & 0xffff) | 0x80000000 if the fast form is not allowed (min < 0 or delta < 0)
-__device__ __forceinline__ void path_info(int mn, int P2, unsigned& A, unsigned& B)
-{
-    const int delta = (int)(short)(P2 + mn);
-    A = pk2(-delta);
-    B = ((unsigned)delta & 0xffffu) | ((unsigned)(mn | delta) & 0x80000000u);
-}
-
-template <int DPL, bool UP, bool WTA, bool HASPAD, int MAXT>
+template <int DPL, bool UP, bool WTA, bool HASPAD, bool NN, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
                                                      int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
@@ -502,7 +526,7 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     const size_t parityStride = (size_t)NW * 2 * vs.inboxWords;
     unsigned long long* bars = (unsigned long long*)(inbox + 2 * parityStride);
     unsigned A0, B0;
-    path_info(0, P2, A0, B0);                                         // the zero state: minimum 0
+    path_info<NN>(0, P2, A0, B0);                                     // the zero state: minimum 0
     for (int i = threadIdx.x; i < vs.colsMax * colWords; i += NT) {
         const int w = i % colWords;
         unsigned v;
@@ -600,9 +624,9 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
             int mn1, mn2, mn3;
             const bool fastCol = !exact && (int)(B1 | B2 | B3) >= 0;
             if (fastCol) {                                             // the common case: one straight-line block for all three directions
-                const int m1 = col_fast<NWD, HASPAD>(Lp1, A1, c, L1, lane, D, k);
-                const int m2 = col_fast<NWD, HASPAD>(Lp2, A2, c, L2, lane, D, k);
-                const int m3 = col_fast<NWD, HASPAD>(Lp3, A3, c, L3, lane, D, k);
+                const int m1 = col_fast<NWD, HASPAD, NN>(Lp1, A1, c, L1, lane, D, k);
+                const int m2 = col_fast<NWD, HASPAD, NN>(Lp2, A2, c, L2, lane, D, k);
+                const int m3 = col_fast<NWD, HASPAD, NN>(Lp3, A3, c, L3, lane, D, k);
                 mn1 = __reduce_min_sync(0xffffffffu, m1);
                 mn2 = __reduce_min_sync(0xffffffffu, m2);
                 mn3 = __reduce_min_sync(0xffffffffu, m3);
@@ -636,7 +660,7 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
             stw<NWD>(col, L1); stw<NWD>(col + dwords, L2); stw<NWD>(col + 2 * dwords, L3);
             // lanes 0..2 derive what the next pixel on each path needs from this pixel's minimum
             unsigned iA, iB;
-            path_info(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3), P2, iA, iB);
+            path_info<NN>(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3), P2, iA, iB);
             if (lane < 3) { cb[infoOff + lane] = iA; cb[infoOff + 4 + lane] = iB; }
             if (ci == 0 && hasL) {                                     // my first column's down-left costs -> left neighbour's right inbox
                 const unsigned dst = pushL_data + wr * inboxParityBytes, bar = pushL_bar + wr * barParityStride;

@@ -628,7 +628,7 @@ static cudaError_t launch_cluster(K kernel, int CL, int B, int NT, size_t smem, 
     return cudaLaunchKernelEx(&cfg, kernel, C, S, raw, aux, p, CL, storeS, flags, vs);
 }
 
-template <int DPL, bool HASPAD>
+template <int DPL, bool HASPAD, bool NN>
 static int launch_paths(cvr_ctx* c, int B, int storeS)
 {
     const SgbmDev& p = c->sg;
@@ -649,13 +649,13 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
                 else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             } else if (vc.NT > 512) {
-                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             } else {
-                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, NN, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, NN, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else e = launch_cluster(k_path_v3<DPL, true, false, HASPAD, NN, 512>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             }
             c->launches++;
             if (e != cudaSuccess) { c->err = std::string("k_path_v2 launch: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
@@ -681,9 +681,9 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     };
     auto launch_h = [&](bool rev, bool wta, int accumulate, int store) -> int {
         if (packed) {
-            if (!rev) k_path_h2<DPL, false, false, HASPAD><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
-            else if (wta) k_path_h2<DPL, true, true, HASPAD><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
-            else k_path_h2<DPL, true, false, HASPAD><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+            if (!rev) k_path_h2<DPL, false, false, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+            else if (wta) k_path_h2<DPL, true, true, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
+            else k_path_h2<DPL, true, false, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
         } else {
             if (!rev) k_path_h<DPL, false, false><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
             else if (wta) k_path_h<DPL, true, true><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
@@ -746,11 +746,17 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         cvr_stage_mark(c, "vsum");
     }
     int rc;
+    const bool nn = !c->force_no_nn && p.P2s >= 0 && p.P1s >= p.P2s;
     switch (p.Dp / 32) {
-        case 2: rc = (p.D == p.Dp) ? launch_paths<2, false>(c, B, storeS) : launch_paths<2, true>(c, B, storeS); break;
-        case 4: rc = (p.D == p.Dp) ? launch_paths<4, false>(c, B, storeS) : launch_paths<4, true>(c, B, storeS); break;
-        case 6: rc = (p.D == p.Dp) ? launch_paths<6, false>(c, B, storeS) : launch_paths<6, true>(c, B, storeS); break;
-        case 8: rc = (p.D == p.Dp) ? launch_paths<8, false>(c, B, storeS) : launch_paths<8, true>(c, B, storeS); break;
+        // NN: 0 <= (short)P2 <= (short)P1 -- the neighbour terms of the path update can never win (see col_fast); this is the
+        // regime of the reference's default config (block_size 27: P2 = 69984 wraps to 4448, P1 = 17496)
+#define CVR_DISPATCH(DPL_)                                                                                                   \
+    case DPL_:                                                                                                               \
+        if (nn) rc = (p.D == p.Dp) ? launch_paths<DPL_, false, true>(c, B, storeS) : launch_paths<DPL_, true, true>(c, B, storeS);   \
+        else rc = (p.D == p.Dp) ? launch_paths<DPL_, false, false>(c, B, storeS) : launch_paths<DPL_, true, false>(c, B, storeS);    \
+        break;
+        CVR_DISPATCH(2) CVR_DISPATCH(4) CVR_DISPATCH(6) CVR_DISPATCH(8)
+#undef CVR_DISPATCH
         default: c->err = "unsupported padded disparity count"; return CVR_ERR_UNSUPPORTED;
     }
     if (rc) return rc;

@@ -107,6 +107,31 @@ def test_generic_int32_path_kernels(cvr, oracle, monkeypatch, D, bs, mode):
     rec.close()
 
 
+@pytest.mark.parametrize("mode", [0, 1])
+def test_no_neighbour_shortcut_on_and_off(cvr, oracle, monkeypatch, mode):
+    """block_size 27 (P2 wraps to 4448 <= P1 = 17496) takes the no-neighbour form of the path update; with CVR_NO_NN=1
+    the same parameters run through the ordinary packed update.  Both must equal cv2 / the oracle."""
+    g = load_golden("s64x300_d64_bs27")
+    H, W, D, bs, _, minD, lb, rb = _golden_inputs(oracle, g)
+    gl, gr = oracle.gray_bgr(lb), oracle.gray_bgr(rb)
+    ref = g["disp"] if mode == 0 else oracle.sgbm(gl, gr, oracle.reference_sgbm_params(block_size=bs, num_disparities=D, mode=1))
+    for no_nn in ("0", "1"):
+        monkeypatch.setenv("CVR_NO_NN", no_nn)
+        rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD), mode=mode)
+        assert np.array_equal(rec.GenerateDisparityMap(gl, gr), ref), "CVR_NO_NN=%s" % no_nn
+        rec.close()
+    # P1 >= P2s >= 0 with a P2 that does NOT wrap (P1 = 300, P2 = 301 after OpenCV's max(P2, P1+1)): also the shortcut regime
+    l, r = oracle.synth_pair(40, 220, 32, seed=9)
+    p = oracle.reference_sgbm_params(block_size=5, num_disparities=32, mode=mode)
+    p["P1"], p["P2"] = 300, 10
+    want = oracle.sgbm(l, r, p)
+    for no_nn in ("0", "1"):
+        monkeypatch.setenv("CVR_NO_NN", no_nn)
+        rec = cvr.Reconstruct3D(220, 40, config=_cfg(5, 32), mode=mode, P1=300, P2=10)
+        assert np.array_equal(rec.GenerateDisparityMap(l, r), want)
+        rec.close()
+
+
 def test_degenerate_inputs(cvr, oracle):
     # image narrower than the disparity range: everything invalid (A.0, W1 <= 0)
     rec = cvr.Reconstruct3D(60, 20, config=_cfg(5, 64))
