@@ -56,6 +56,25 @@ __device__ __forceinline__ void stw(unsigned* p, const unsigned (&v)[NWD])
     }
 }
 
+// ---- per-lane asynchronous prefetch ring (cp.async, Ampere+ LDGSTS): each lane copies its own NWD words of C and S
+// several columns ahead into shared memory, so the long global-load latency is off the per-column critical path.
+// A lane only ever reads back bytes it copied itself, hence cp.async.wait_group is all the synchronisation needed.
+template <int NWD>
+__device__ __forceinline__ void cpa_words(unsigned* sdst, const unsigned* gsrc)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(sdst);
+    if (NWD == 2) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(d), "l"(gsrc) : "memory");
+    else if (NWD == 4) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+    else {
+#pragma unroll
+        for (int i = 0; i < NWD; i++) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4 * i), "l"(gsrc + i) : "memory");
+    }
+}
+__device__ __forceinline__ void cpa_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cpa_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+#define CVR_PF_DEPTH 4          // columns in flight per warp
+
 // One column update for one direction: Lp (previous costs of the source pixel, packed) -> L (this pixel); returns
 // the warp-wide minimum of L.  EXACT = true: general form (any sign of C, Lp, delta).  EXACT = false: the caller
 // knows C >= 0 for this frame; if in addition the source costs are non-negative (minPrev >= 0) and delta >= 0 --
@@ -245,6 +264,7 @@ __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, 
 
 // keeps a value in a register across the loop (stops the compiler from re-deriving it from constant memory every iteration)
 #define CVR_PIN(x) asm volatile("" : "+r"(x))
+#define CVR_PIN64(x) asm volatile("" : "+l"(x))
 
 // ------------------------------------------------------------------------------------------------
 // Horizontal path, packed.  Same contract as k_path_h.
@@ -276,18 +296,28 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
     for (int j = 0; j < NWD; j++) Lp[j] = ((lane * NWD + j) * 2 < D) ? 0u : 0x7fff7fffu;
     unsigned iA, iB;
     path_info<NN>(0, P2, iA, iB);                                          // the border column: minimum 0
-    unsigned cN[NWD], sN[NWD];
+    __shared__ __align__(16) unsigned ringsm[4][CVR_PF_DEPTH][2][32 * NWD];
+    unsigned (*ring)[2][32 * NWD] = ringsm[threadIdx.x >> 5];
+    {   // prologue: the first CVR_PF_DEPTH columns
+        const unsigned* pc = Cp; const unsigned* ps = Sp;
 #pragma unroll
-    for (int j = 0; j < NWD; j++) sN[j] = 0u;
-    ldw<NWD>(Cp, cN);
-    if (accumulate) ldw<NWD>(Sp, sN);
+        for (int i = 0; i < CVR_PF_DEPTH; i++) {
+            if (i < W1) { cpa_words<NWD>(&ring[i][0][lane * NWD], pc); if (accumulate) cpa_words<NWD>(&ring[i][1][lane * NWD], ps); }
+            cpa_commit();
+            pc += stepW; ps += stepW;
+        }
+    }
+    const unsigned* pfC = Cp + CVR_PF_DEPTH * stepW;                       // next column to fetch
+    const unsigned* pfS = Sp + CVR_PF_DEPTH * stepW;
     for (int step = 0; step < W1; step++) {
         unsigned c[NWD], s[NWD], L[NWD];
+        const int slot = step % CVR_PF_DEPTH;
+        cpa_wait<CVR_PF_DEPTH - 1>();
+        ldw<NWD>(&ring[slot][0][lane * NWD], c);
+        if (accumulate) ldw<NWD>(&ring[slot][1][lane * NWD], s);
+        else {
 #pragma unroll
-        for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = sN[j]; }
-        if (step + 1 < W1) {
-            ldw<NWD>(Cp + stepW, cN);
-            if (accumulate) ldw<NWD>(Sp + stepW, sN);
+            for (int j = 0; j < NWD; j++) s[j] = 0u;
         }
         const bool fastCol = !exact && (int)iB >= 0;
         int m;
@@ -308,6 +338,12 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
         for (int j = 0; j < NWD; j++) { Lp[j] = L[j]; if (!accumulate) s[j] = L[j]; }
         if (!WTA || storeS) stw<NWD>(Sp, s);
         if (WTA) wta_column2<NWD>(s, lane, p, rawp, auxp);
+        if (step + CVR_PF_DEPTH < W1) {                                  // refill the slot just consumed
+            cpa_words<NWD>(&ring[slot][0][lane * NWD], pfC);
+            if (accumulate) cpa_words<NWD>(&ring[slot][1][lane * NWD], pfS);
+        }
+        cpa_commit();
+        pfC += stepW; pfS += stepW;
         Cp += stepW; Sp += stepW; rawp += dx; auxp += dx;
     }
 }
@@ -518,12 +554,13 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     const int GW = CL * NW, gw = rank * NW + warp;
     const int ctaFirst = (int)(((long long)W1 * (rank * NW)) / GW);
     const int a = (int)(((long long)W1 * gw) / GW), e = (int)(((long long)W1 * (gw + 1)) / GW);
-    const int dwords = p.Dp / 2;
-    const int colWords = vs.colWords;                                 // 3*dwords + 8: costs of 3 directions, then A[3], pad, B[3], pad (path_info)
-    const int infoOff = 3 * dwords;
+    constexpr int dwords = DPL * 16;                                  // Dp / 2 words per direction per column (Dp = 32 * DPL)
+    constexpr int colWords = 3 * dwords + 8;                          // costs of 3 directions, then A[3], pad, B[3], pad (path_info)
+    constexpr int infoOff = 3 * dwords;
+    constexpr int inboxWords = dwords + 4;
     unsigned* state = smv;                                            // [colsMax][colWords]
     unsigned* inbox = smv + (size_t)vs.colsMax * colWords;            // [2 parity][NW][2 sides][inboxWords]: costs, A, B, pad
-    const size_t parityStride = (size_t)NW * 2 * vs.inboxWords;
+    const size_t parityStride = (size_t)NW * 2 * inboxWords;
     unsigned long long* bars = (unsigned long long*)(inbox + 2 * parityStride);
     unsigned A0, B0;
     path_info<NN>(0, P2, A0, B0);                                     // the zero state: minimum 0
@@ -534,8 +571,8 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
         else v = (w - infoOff < 3) ? A0 : ((w - infoOff >= 4 && w - infoOff < 7) ? B0 : 0u);
         state[i] = v;
     }
-    for (int i = threadIdx.x; i < 2 * NW * 2 * vs.inboxWords; i += NT) {
-        const int w = i % vs.inboxWords;
+    for (int i = threadIdx.x; i < 2 * NW * 2 * inboxWords; i += NT) {
+        const int w = i % inboxWords;
         inbox[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : (w == dwords ? A0 : (w == dwords + 1 ? B0 : 0u));
     }
     if (threadIdx.x < 2 * NW * 2) mbar_init(smem_u32(bars + threadIdx.x), 1);
@@ -543,36 +580,36 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     bool exact = flags[b] != 0;
     PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
     CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
-    const size_t colW = (size_t)dwords;
+    constexpr size_t colW = (size_t)dwords;
     const unsigned edgeBytes = 32u * NWD * 4u + 8u;                   // 32 lanes x NWD words + A + B
-    const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * vs.inboxWords;
-    const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * vs.inboxWords;
+    const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * inboxWords;
+    const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * inboxWords;
     const unsigned myBarL = smem_u32(bars + (size_t)warp * 2 + 0), myBarR = smem_u32(bars + (size_t)warp * 2 + 1);
     const unsigned barParityStride = (unsigned)(NW * 2 * 8), inboxParityBytes = (unsigned)(parityStride * 4);
     const bool hasL = gw > 0, hasR = gw + 1 < GW;
     unsigned pushR_data = 0, pushR_bar = 0, pushL_data = 0, pushL_bar = 0;
     if (hasR) {
         const int r2 = (gw + 1) / NW, w2 = (gw + 1) % NW;
-        pushR_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 0) * vs.inboxWords), r2);
+        pushR_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 0) * inboxWords), r2);
         pushR_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 0), r2);
     }
     if (hasL) {
         const int r2 = (gw - 1) / NW, w2 = (gw - 1) % NW;
-        pushL_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 1) * vs.inboxWords), r2);
+        pushL_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 1) * inboxWords), r2);
         pushL_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 1), r2);
     }
     unsigned* const colBase0 = state + (size_t)(a - ctaFirst) * colWords;
     cluster.sync();                                                   // state, inboxes and barriers of every CTA are initialised
 
     const size_t frameRow0 = (size_t)b * H;
-    unsigned cN[NWD], sN[NWD];
     const long long nextRow = (UP ? -1LL : 1LL) * (long long)W1 * (long long)colW;
     const size_t rb0 = ((frameRow0 + (UP ? H - 1 : 0)) * W1 + a) * colW + (size_t)lane * NWD;
     const unsigned* rowC = (const unsigned*)C + rb0;                  // this lane's words of column a in the current row
     unsigned* rowS = (unsigned*)S + rb0;
+    const int ncols = e - a;
+    unsigned cN[NWD], sN[NWD];
     ldw<NWD>(rowC, cN);
     ldw<NWD>(rowS, sN);
-    const int ncols = e - a;
     for (int t = 0; t < H; t++, rowC += nextRow, rowS += nextRow) {
         const int y = UP ? H - 1 - t : t;
         const int rd = (t + 1) & 1, wr = t & 1;
