@@ -139,6 +139,8 @@ __device__ __forceinline__ int lo16(unsigned w) { return (int)(short)(w & 0xffff
 __device__ __forceinline__ int hi16(unsigned w) { return ((int)w) >> 16; }
 __device__ __forceinline__ unsigned pack16(int lo, int hi) { return ((unsigned)lo & 0xffffu) | ((unsigned)hi << 16); }
 
+// One thread per (frame, x', 4 disparities) marching down the rows.  The "old" row (y - SH2 - 1) was read as the
+// "new" row bs rows earlier and is still L2-resident (measured: re-reading it beats a shared-memory ring).
 __global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B, int* flags)
 {
     const size_t rowWords = (size_t)p.W1 * p.Dp / 4;          // uint2 words per row

@@ -14,7 +14,7 @@
         if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
     } while (0)
 
-#define RS_WARP_ELEMS 512            // elements ranked by one warp per pass
+#define RS_WARP_ELEMS 1024           // elements ranked by one warp per pass
 #define RS_BLOCK_WARPS 8
 
 __global__ void k_vox_setup(const VoxBox* box, const int* nPtr, VoxelHdr* hdr, float lx, float ly, float lz, int B)
@@ -34,6 +34,7 @@ __global__ void k_vox_setup(const VoxBox* box, const int* nPtr, VoxelHdr* hdr, f
         h.div[k] = maxb - h.minb[k] + 1;
     }
     if (cells > 2147483647LL || cells <= 0) h.passthrough = 1;
+    h.maxkey = h.passthrough ? 0 : (int)(cells - 1);          // keys are < cells: radix passes above its top bit are skipped
     hdr[b] = h;
 }
 __global__ void k_vox_keys(const cvr_point* __restrict__ pts, size_t stride, const VoxelHdr* __restrict__ hdr, float lx, float ly, float lz,
@@ -52,29 +53,48 @@ __global__ void k_vox_keys(const cvr_point* __restrict__ pts, size_t stride, con
 }
 
 // ---- stable LSD radix sort, 8 bits per pass ------------------------------------------------------
-// hist layout per frame: [256][nRuns] (digit-major) so one exclusive scan yields each run's base per digit.
+// hist layout per frame: [run][256] (run-major).  k_rs_scan turns it, per digit, into the global start of that
+// run's elements with that digit.  Passes whose digit lies above the top bit of the largest possible key
+// (VoxelHdr::maxkey) only copy the pairs through, so the ping-pong order stays fixed without a host round trip.
+__device__ __forceinline__ bool rs_pass_needed(const VoxelHdr* hdr, int b, int shift) { return !hdr || ((unsigned)hdr[b].maxkey >> shift) != 0 || shift == 0; }
+
 __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_hist(const uint32_t* __restrict__ keys, size_t kvStride, const int* __restrict__ nPtr,
-                                                                 int nOff, int shift, int* __restrict__ hist, size_t histStride, int nRuns)
+                                                                 int nOff, int shift, int* __restrict__ hist, size_t histStride, int nRuns,
+                                                                 const VoxelHdr* __restrict__ hdr)
 {
     __shared__ int sh[RS_BLOCK_WARPS][256];
     const int b = blockIdx.y, n = nPtr[b * nOff];
+    if (!rs_pass_needed(hdr, b, shift)) return;
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int run = blockIdx.x * RS_BLOCK_WARPS + w;
+    const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
+    if (run >= nRuns || beg >= end) return;
     for (int k = lane; k < 256; k += 32) sh[w][k] = 0;
     __syncwarp();
-    if (run < nRuns) {
-        const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
-        const uint32_t* kk = keys + (size_t)b * kvStride;
-        for (int i = beg + lane; i < end; i += 32) atomicAdd(&sh[w][(kk[i] >> shift) & 255], 1);
-        __syncwarp();
-        int* h = hist + (size_t)b * histStride;
-        for (int k = lane; k < 256; k += 32) h[(size_t)k * nRuns + run] = sh[w][k];
-    }
+    const uint32_t* kk = keys + (size_t)b * kvStride;
+    for (int i = beg + lane; i < end; i += 32) atomicAdd(&sh[w][(kk[i] >> shift) & 255], 1);
+    __syncwarp();
+    int* h = hist + (size_t)b * histStride + (size_t)run * 256;
+    for (int k = lane; k < 256; k += 32) h[k] = sh[w][k];
+}
+// one CTA of 256 threads per frame: thread d walks the runs of digit d (coalesced 1 KB rows)
+__global__ void __launch_bounds__(256) k_rs_scan(int* __restrict__ hist, size_t histStride, const int* __restrict__ nPtr, int nOff, int shift,
+                                                 const VoxelHdr* __restrict__ hdr)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.x, n = nPtr[b * nOff], d = threadIdx.x;
+    if (!rs_pass_needed(hdr, b, shift)) return;
+    const int nr = (n + RS_WARP_ELEMS - 1) / RS_WARP_ELEMS;
+    int* h = hist + (size_t)b * histStride + d;
+    int sum = 0;
+    for (int r = 0; r < nr; r++) { const int v = h[(size_t)r * 256]; h[(size_t)r * 256] = sum; sum += v; }
+    const int base = block_excl_scan(sum, ws, nullptr);           // start of digit d in the output
+    for (int r = 0; r < nr; r++) h[(size_t)r * 256] += base;
 }
 __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_scatter(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
                                                                     uint32_t* __restrict__ okeys, uint32_t* __restrict__ ovals, size_t kvStride,
                                                                     const int* __restrict__ nPtr, int nOff, int shift, const int* __restrict__ hist,
-                                                                    size_t histStride, int nRuns)
+                                                                    size_t histStride, int nRuns, const VoxelHdr* __restrict__ hdr)
 {
     __shared__ int base[RS_BLOCK_WARPS][256];
     const int b = blockIdx.y, n = nPtr[b * nOff];
@@ -83,11 +103,15 @@ __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_scatter(const uint32
     if (run >= nRuns) return;
     const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
     if (beg >= end) return;
-    const int* h = hist + (size_t)b * histStride;
-    for (int k = lane; k < 256; k += 32) base[w][k] = h[(size_t)k * nRuns + run];
-    __syncwarp();
     const uint32_t* kk = keys + (size_t)b * kvStride; const uint32_t* vv = vals + (size_t)b * kvStride;
     uint32_t* ok = okeys + (size_t)b * kvStride; uint32_t* ov = ovals + (size_t)b * kvStride;
+    if (!rs_pass_needed(hdr, b, shift)) {                              // digit is 0 for every key: the pass is the identity
+        for (int i = beg + lane; i < end; i += 32) { ok[i] = kk[i]; ov[i] = vv[i]; }
+        return;
+    }
+    const int* h = hist + (size_t)b * histStride + (size_t)run * 256;
+    for (int k = lane; k < 256; k += 32) base[w][k] = h[k];
+    __syncwarp();
     for (int i0 = beg; i0 < end; i0 += 32) {
         const int i = i0 + lane;
         const bool act = i < end;
@@ -163,7 +187,7 @@ __global__ void k_vox_centroid(const cvr_point* __restrict__ pts, size_t stride,
 }
 
 // Sort (keys, vals) of every frame: d_keys[0]/d_vals[0] -> ... ; returns the index (0/1) of the buffer holding the result.
-int cvr_radix_sort_pairs(cvr_ctx* c, int B, const int* nPtr, int nOff, int maxN, int passes, int* result_buf)
+int cvr_radix_sort_pairs(cvr_ctx* c, int B, const int* nPtr, int nOff, int maxN, int passes, const VoxelHdr* hdr, int* result_buf)
 {
     const int nRuns = cvr_div_up(maxN, RS_WARP_ELEMS);
     const size_t histStride = (size_t)256 * nRuns + 1;
@@ -172,12 +196,12 @@ int cvr_radix_sort_pairs(cvr_ctx* c, int B, const int* nPtr, int nOff, int maxN,
     for (int pass = 0; pass < passes; pass++) {
         const int shift = pass * 8;
         dim3 g(cvr_div_up(nRuns, RS_BLOCK_WARPS), B);
-        k_rs_hist<<<g, RS_BLOCK_WARPS * 32, 0, c->stream>>>(c->d_keys[cur], kvStride, nPtr, nOff, shift, (int*)c->d_hist, histStride, nRuns);
+        k_rs_hist<<<g, RS_BLOCK_WARPS * 32, 0, c->stream>>>(c->d_keys[cur], kvStride, nPtr, nOff, shift, (int*)c->d_hist, histStride, nRuns, hdr);
         LAUNCH_CHECK(c);
-        k_scan_excl<<<B, 1024, 0, c->stream>>>((int*)c->d_hist, histStride, 256 * nRuns, nullptr, 1);
+        k_rs_scan<<<B, 256, 0, c->stream>>>((int*)c->d_hist, histStride, nPtr, nOff, shift, hdr);
         LAUNCH_CHECK(c);
         k_rs_scatter<<<g, RS_BLOCK_WARPS * 32, 0, c->stream>>>(c->d_keys[cur], c->d_vals[cur], c->d_keys[cur ^ 1], c->d_vals[cur ^ 1], kvStride, nPtr,
-                                                                nOff, shift, (const int*)c->d_hist, histStride, nRuns);
+                                                                nOff, shift, (const int*)c->d_hist, histStride, nRuns, hdr);
         LAUNCH_CHECK(c);
         cur ^= 1;
     }
@@ -200,7 +224,7 @@ int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, c
     k_vox_keys<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, c->d_vhdr, lx, ly, lz, c->d_keys[0], c->d_vals[0], kvStride);
     LAUNCH_CHECK(c);
     int buf = 0;
-    int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, &buf);
+    int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, c->d_vhdr, &buf);
     if (rc) return rc;
     const int nblk = cvr_div_up(maxN, CVR_SEL_BLOCK);
     const size_t cntStride = (size_t)nblk + 1;
