@@ -106,7 +106,7 @@ struct cvr_ctx {
     int16_t* d_lr;           // vertical path state [B][2][W1+2][3][Dp]
     int* d_minlr;            // [B][2][W1+2][4]
     int16_t* d_raw;          // WTA output [B][H][W]
-    int* d_aux;              // (minS<<16 | best&0xffff) per accepted pixel, -1 if rejected [B][H][W1]
+    int2* d_aux;             // WTA result per computed pixel: {minS<<16 | best, S[best-1]<<16 | S[best+1]&0xffff}, x = 0x7fffffff if rejected [B][H][W1]
     int16_t* d_disp;         // after LR check  [B][H][W]
     int16_t* d_med;          // after median / speckle [B][H][W]   (final disparity)
     int* d_label;            // speckle CCL [B][H][W]

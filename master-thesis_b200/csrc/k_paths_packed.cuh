@@ -212,8 +212,9 @@ __device__ __forceinline__ void path_info(int mn, int P2, unsigned& A, unsigned&
 //   argmin: one CREDUX.MIN on (S << 16 | d); uniqueness as an order-free predicate; S[best-1], S[best+1] fetched from
 //   their owner lanes by shuffle; the small truncating division done in float with an exact +-1 correction.
 template <int NWD>
-__device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, const SgbmDev& p, int16_t* rawPix, int* auxPix)
+__device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, const SgbmDev& p, int16_t* rawPix, int2* auxPix)
 {
+    (void)rawPix;
     const int d0 = lane * NWD * 2;
     int key = 0x7fffffff;
 #pragma unroll
@@ -236,30 +237,22 @@ __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, 
         }
     }
     const bool reject = __any_sync(0xffffffffu, bad) || (minS == CVR_MAX_COST);
-    int out = p.INVALID, aux = 0x7fffffff;
+    int2 aux = make_int2(0x7fffffff, 0);
     if (!reject) {                                                    // warp-uniform
-        int dd = best * CVR_DISP_SCALE;
-        if (0 < best && best < p.D - 1) {
+        unsigned ac = 0;
+        if (0 < best && best < p.D - 1) {                             // fetch S[best-1], S[best+1] from their owner lanes
             const int ia = best - 1, ic = best + 1;
             unsigned wa = s[0], wc = s[0];
 #pragma unroll
             for (int j = 1; j < NWD; j++) { if (((ia >> 1) % NWD) == j) wa = s[j]; if (((ic >> 1) % NWD) == j) wc = s[j]; }
             wa = __shfl_sync(0xffffffffu, wa, ia / (2 * NWD));
             wc = __shfl_sync(0xffffffffu, wc, ic / (2 * NWD));
-            const int a = (ia & 1) ? hi16(wa) : lo16(wa), c = (ic & 1) ? hi16(wc) : lo16(wc);
-            const int den = max(a + c - 2 * minS, 1);
-            const int num = (a - c) * CVR_DISP_SCALE + den, den2 = den * 2;
-            // trunc(num / den2): |num| < 2^24 and den2 < 2^24 are exact in float, the quotient is within +-1
-            int q = __float2int_rz(__fdividef((float)num, (float)den2));
-            int r = num - q * den2;
-            if (num >= 0) { if (r < 0) q--; else if (r >= den2) q++; }       // remainder must end in [0, den2)
-            else { if (r > 0) q++; else if (r <= -den2) q--; }                // remainder must end in (-den2, 0]
-            dd += q;
+            const unsigned a = (ia & 1) ? (wa >> 16) : (wa & 0xffffu), c = (ic & 1) ? (wc >> 16) : (wc & 0xffffu);
+            ac = (a << 16) | c;
         }
-        out = dd + p.minD * CVR_DISP_SCALE;
-        aux = (int)(((unsigned)minS << 16) | (unsigned)best);
+        aux = make_int2((int)(((unsigned)minS << 16) | (unsigned)best), (int)ac);
     }
-    if (lane == 0) { *rawPix = (int16_t)out; *auxPix = aux; }
+    if (lane == 0) *auxPix = aux;
 }
 
 // keeps a value in a register across the loop (stops the compiler from re-deriving it from constant memory every iteration)
@@ -270,7 +263,7 @@ __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, 
 // Horizontal path, packed.  Same contract as k_path_h.
 template <int DPL, bool REVERSE, bool WTA, bool HASPAD, bool NN>
 __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                 int* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
+                                                 int2* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
 {
     constexpr int NWD = DPL / 2;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -286,7 +279,7 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
     const unsigned* Cp = (const unsigned*)C + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
     unsigned* Sp = (unsigned*)S + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
     int16_t* rawp = raw + ((size_t)b * p.H + y) * p.W + p.minX1 + (REVERSE ? W1 - 1 : 0);
-    int* auxp = aux + ((size_t)b * p.H + y) * W1 + (REVERSE ? W1 - 1 : 0);
+    int2* auxp = aux + ((size_t)b * p.H + y) * W1 + (REVERSE ? W1 - 1 : 0);
     int* flagp = flags + b;
     bool exact = *flagp != 0;
     PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
@@ -369,7 +362,7 @@ struct VState {                // shared-memory carve-up (in 32-bit words) compu
 
 template <int DPL, bool UP, bool WTA, bool HASPAD>
 __global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v2(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                     int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
+                                                     int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     constexpr int NWD = DPL / 2;
     const int NT = blockDim.x, NW = NT / 32;
@@ -541,7 +534,7 @@ __device__ __forceinline__ void st_async_words(unsigned raddr, const unsigned (&
 
 template <int DPL, bool UP, bool WTA, bool HASPAD, bool NN, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                     int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
+                                                     int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     constexpr int NWD = DPL / 2;
     const int NT = blockDim.x, NW = NT / 32;

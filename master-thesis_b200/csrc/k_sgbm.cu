@@ -229,10 +229,12 @@ __device__ __forceinline__ void store_vec(int16_t* p, const int (&v)[DPL])
 }
 
 // A.5 (first half) for one column held by a warp: S[i] is the aggregated cost of disparity lane*DPL+i.
-// Writes raw disparity (x16) or INVALID, and aux = (minS << 16) | best for accepted pixels (0x7fffffff otherwise).
+// Writes aux = { (minS << 16) | best, (S[best-1] << 16) | (S[best+1] & 0xffff) } for accepted pixels ({0x7fffffff, 0}
+// otherwise); the sub-pixel division itself is done one thread per pixel in k_lrcheck.
 template <int DPL>
-__device__ __forceinline__ void wta_column(const int (&S)[DPL], int lane, const SgbmDev& p, int16_t* rawPix, int* auxPix)
+__device__ __forceinline__ void wta_column(const int (&S)[DPL], int lane, const SgbmDev& p, int16_t* rawPix, int2* auxPix)
 {
+    (void)rawPix;
     const int d0 = lane * DPL;
     int key = 0x7fffffff;
 #pragma unroll
@@ -248,11 +250,10 @@ __device__ __forceinline__ void wta_column(const int (&S)[DPL], int lane, const 
         if (d < p.D && S[i] * mul < lim && abs(best - d) > 1) bad = true;
     }
     const bool reject = __any_sync(FULL, bad) || (minS == CVR_MAX_COST);
-    int out = p.INVALID, aux = 0x7fffffff;
+    int2 aux = make_int2(0x7fffffff, 0);
     if (!reject) {               // warp-uniform
-        int dd = best * CVR_DISP_SCALE;
+        int a = 0, c = 0;
         if (0 < best && best < p.D - 1) {
-            int a = 0, c = 0;
 #pragma unroll
             for (int i = 0; i < DPL; i++) {
                 a += (d0 + i == best - 1) ? S[i] : 0;
@@ -260,13 +261,10 @@ __device__ __forceinline__ void wta_column(const int (&S)[DPL], int lane, const 
             }
             a = __reduce_add_sync(FULL, a);
             c = __reduce_add_sync(FULL, c);
-            const int den = max(a + c - 2 * minS, 1);
-            dd += ((a - c) * CVR_DISP_SCALE + den) / (den * 2);
         }
-        out = dd + p.minD * CVR_DISP_SCALE;
-        aux = (int)(((unsigned)minS << 16) | (unsigned)best);
+        aux = make_int2((int)(((unsigned)minS << 16) | (unsigned)best), (int)(((unsigned)a << 16) | ((unsigned)c & 0xffffu)));
     }
-    if (lane == 0) { *rawPix = (int16_t)out; *auxPix = aux; }
+    if (lane == 0) *auxPix = aux;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -275,7 +273,7 @@ __device__ __forceinline__ void wta_column(const int (&S)[DPL], int lane, const 
 //   accumulate: S = sat(S + L) (else S = L, the first path written);  WTA: winner-take-all on the final S.
 template <int DPL, bool REVERSE, bool WTA>
 __global__ void __launch_bounds__(128) k_path_h(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                int* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
+                                                int2* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
 {
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= B * p.H) return;
@@ -347,7 +345,7 @@ __global__ void k_lr_init(int16_t* lr, int* minlr, SgbmDev p, int B)
 // UP = false: rows top-down (pass 1);  UP = true: bottom-up (MODE_HH pass 2).  S = sat(S + L1), + L2, + L3.
 template <int DPL, bool UP, bool WTA, int NT>
 __global__ void __launch_bounds__(NT) k_path_v(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* lr, int* minlr,
-                                               int16_t* __restrict__ raw, int* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags)
+                                               int16_t* __restrict__ raw, int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags)
 {
     const int b = blockIdx.y, rank = blockIdx.x;
     const int W1 = p.W1, Dp = p.Dp, D = p.D, H = p.H;
@@ -408,20 +406,29 @@ __global__ void __launch_bounds__(NT) k_path_v(const int16_t* __restrict__ C, in
 // ------------------------------------------------------------------------------------------------
 // A.5 second half.  One CTA per (row, frame).  disp2[x2] is the `best` of the pixel with the smallest minS
 // among those mapping to x2, the largest x' winning ties (the sequential right-to-left scan with strict '>').
-__global__ void k_lrcheck(const int16_t* __restrict__ raw, const int* __restrict__ aux, int16_t* __restrict__ disp, SgbmDev p)
+__global__ void k_lrcheck(int16_t* __restrict__ raw, const int2* __restrict__ aux, int16_t* __restrict__ disp, SgbmDev p)
 {
-    extern __shared__ unsigned key[];
+    extern __shared__ unsigned key[];                   // [W] right-view keys, then [W] raw disparities of this row
+    int* rawsm = (int*)(key + p.W);
     const int y = blockIdx.x, b = blockIdx.y, W = p.W, W1 = p.W1;
     const size_t row = (size_t)b * p.H + y;
-    const int* auxr = aux + row * W1;
-    const int16_t* rawr = raw + row * W;
+    const int2* auxr = aux + row * W1;
+    int16_t* rawr = raw + row * W;
     int16_t* out = disp + row * W;
-    for (int x = threadIdx.x; x < W; x += blockDim.x) key[x] = 0xffffffffu;
+    for (int x = threadIdx.x; x < W; x += blockDim.x) { key[x] = 0xffffffffu; rawsm[x] = p.INVALID; }
     __syncthreads();
     for (int xp = threadIdx.x; xp < W1; xp += blockDim.x) {
-        const int a = auxr[xp];
-        if (a == 0x7fffffff) continue;
-        const int minS = a >> 16, best = a & 0xffff;
+        const int2 a = auxr[xp];
+        if (a.x == 0x7fffffff) continue;
+        const int minS = a.x >> 16, best = a.x & 0xffff;
+        // sub-pixel interpolation (A.5): C++ '/' truncates toward zero
+        int dd = best * CVR_DISP_SCALE;
+        if (0 < best && best < p.D - 1) {
+            const int sa = a.y >> 16, sc = (int)(short)(a.y & 0xffff);
+            const int den = max(sa + sc - 2 * minS, 1);
+            dd += ((sa - sc) * CVR_DISP_SCALE + den) / (den * 2);
+        }
+        rawsm[xp + p.minX1] = dd + p.minD * CVR_DISP_SCALE;
         const int x2 = xp + p.minX1 - best - p.minD;
         // minS == 32767 is always rejected upstream, so (minS + 32768) <= 65534 and a real key never equals the sentinel
         atomicMin(&key[x2], ((unsigned)(minS + 32768) << 16) | (unsigned)(0xffff - xp));
@@ -429,8 +436,9 @@ __global__ void k_lrcheck(const int16_t* __restrict__ raw, const int* __restrict
     __syncthreads();
     for (int x = threadIdx.x; x < W; x += blockDim.x) {
         int v = p.INVALID;
+        const int d1 = rawsm[x];
+        rawr[x] = (int16_t)d1;                          // kept for cvr_debug_fetch
         if (x >= p.minX1 && x < p.maxX1) {
-            const int d1 = rawr[x];
             v = d1;
             if (d1 != p.INVALID) {
                 const int _d = d1 >> 4, d_ = (d1 + CVR_DISP_SCALE - 1) >> 4;
@@ -439,12 +447,12 @@ __global__ void k_lrcheck(const int16_t* __restrict__ raw, const int* __restrict
                 if (0 <= _x && _x < W) {
                     // an unset right-view entry holds INVALID_DISP_SCALED in OpenCV, which passes `>= minD` when minD > 1
                     const unsigned k = key[_x];
-                    const int d2 = (k != 0xffffffffu) ? (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD : p.INVALID;
+                    const int d2 = (k != 0xffffffffu) ? (auxr[0xffff - (k & 0xffff)].x & 0xffff) + p.minD : p.INVALID;
                     f1 = d2 >= p.minD && abs(d2 - _d) > p.d12;
                 }
                 if (0 <= x_ && x_ < W) {
                     const unsigned k = key[x_];
-                    const int d2 = (k != 0xffffffffu) ? (auxr[0xffff - (k & 0xffff)] & 0xffff) + p.minD : p.INVALID;
+                    const int d2 = (k != 0xffffffffu) ? (auxr[0xffff - (k & 0xffff)].x & 0xffff) + p.minD : p.INVALID;
                     f2 = d2 >= p.minD && abs(d2 - d_) > p.d12;
                 }
                 if (f1 && f2) v = p.INVALID;
@@ -616,7 +624,7 @@ static VCfg pick_vcfg(const cvr_ctx* c)
 }
 
 template <typename K>
-static cudaError_t launch_cluster(K kernel, int CL, int B, int NT, size_t smem, cudaStream_t st, const int16_t* C, int16_t* S, int16_t* raw, int* aux,
+static cudaError_t launch_cluster(K kernel, int CL, int B, int NT, size_t smem, cudaStream_t st, const int16_t* C, int16_t* S, int16_t* raw, int2* aux,
                                   SgbmDev p, int storeS, int* flags, VState vs)
 {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -762,7 +770,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         default: c->err = "unsupported padded disparity count"; return CVR_ERR_UNSUPPORTED;
     }
     if (rc) return rc;
-    k_lrcheck<<<dim3(p.H, B), 256, (size_t)p.W * sizeof(int), c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p);
+    k_lrcheck<<<dim3(p.H, B), 256, (size_t)p.W * 2 * sizeof(int), c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p);
     LAUNCH_CHECK(c);
     k_median3<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
     LAUNCH_CHECK(c);
