@@ -44,89 +44,84 @@ __global__ void k_gray(const uint8_t* __restrict__ src, size_t step, size_t fstr
 // so that the four BT differences are four VIADD.16x2 and the two max(.,.,0) are VIMNMX3.S16x2.RELU.
 __device__ __forceinline__ unsigned pk_neg(unsigned a) { return __vneg2(a); }
 
-__global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStride, int16_t* __restrict__ hsum, SgbmDev p)
+// grid.x = H * nseg: a CTA owns one segment [s, e) of the computed columns of one row, which keeps the per-pixel
+// descriptors of just that segment (plus the block-sum halo and the disparity range) in shared memory, so that many
+// CTAs fit on an SM.  The horizontal block sum is a sliding window over j = s - SW2 .. e - 1 + SW2 with the column index
+// clamped to [0, W1-1] exactly like OpenCV's clamped recurrence (closed form: provably unsaturated, see cvr_create).
+__global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStride, int16_t* __restrict__ hsum, SgbmDev p, int nseg)
 {
     extern __shared__ uint4 sm4[];
-    uint4* Lpk = sm4;
-    uint4* Rpk = sm4 + p.W;
-    unsigned* aL = (unsigned*)(Rpk + p.W);
-    unsigned* aR = aL + p.W;
-    uint8_t* ringbuf = (uint8_t*)(aR + p.W);
-
-    const int y = blockIdx.x, b = blockIdx.y, W = p.W, H = p.H;
+    const int y = blockIdx.x / nseg, seg = blockIdx.x % nseg, b = blockIdx.y, W = p.W, H = p.H;
+    const int W1 = p.W1, Dp = p.Dp, SW2 = p.SW2;
+    const int s = (int)(((long long)W1 * seg) / nseg), e = (int)(((long long)W1 * (seg + 1)) / nseg);
+    const int ps = max(s - SW2, 0), pe = min(e - 1 + SW2, W1 - 1);                 // computed columns whose pixel cost is needed
+    const int xl0 = ps + p.minX1, xl1 = pe + p.minX1;                              // left pixels needed: [xl0, xl1]
+    const int xr0 = max(xl0 - p.minD - (p.D - 1), 0), xr1 = min(xl1 - p.minD, W - 1);   // right pixels needed: [xr0, xr1]
+    const int nL = xl1 - xl0 + 1, nR = xr1 - xr0 + 1;
+    uint4* Lpk = sm4;                                   // [nL]
+    uint4* Rpk = sm4 + nL;                              // [nR]
+    unsigned* aL = (unsigned*)(Rpk + nR);               // [nL + 2]  packed (G | R << 16) of left pixels xl0-1 .. xl1+1
+    unsigned* aR = aL + nL + 2;                         // [nR + 2]
+    uint8_t* ringbuf = (uint8_t*)(aR + nR + 2);
     const int tid = threadIdx.x, nt = blockDim.x;
     const uint8_t* gl = gray + (size_t)b * grayFrameStride;
     const uint8_t* gr = gl + (size_t)H * p.Wp;
     const int yn = max(y - 1, 0), ys = min(y + 1, H - 1);
     const int ft = p.ftzero;
-
-    for (int x = tid; x < W; x += nt) {
-        unsigned vl, vr;
-        if (x == 0 || x == W - 1) { vl = vr = (unsigned)ft | ((unsigned)ft << 16); }
-        else {
-            const uint8_t *l0 = gl + (size_t)y * p.Wp + x, *ln = gl + (size_t)yn * p.Wp + x, *ls = gl + (size_t)ys * p.Wp + x;
-            const uint8_t *r0 = gr + (size_t)y * p.Wp + x, *rn = gr + (size_t)yn * p.Wp + x, *rs = gr + (size_t)ys * p.Wp + x;
-            int a = 2 * ((int)l0[1] - (int)l0[-1]) + ((int)ln[1] - (int)ln[-1]) + ((int)ls[1] - (int)ls[-1]);
-            int c = 2 * ((int)r0[1] - (int)r0[-1]) + ((int)rn[1] - (int)rn[-1]) + ((int)rs[1] - (int)rs[-1]);
+    const unsigned border = (unsigned)ft | ((unsigned)ft << 16);
+    for (int i = tid; i < nL + 2 + nR + 2; i += nt) {
+        const bool right = i >= nL + 2;
+        const int x = right ? xr0 - 1 + (i - nL - 2) : xl0 - 1 + i;
+        const uint8_t* g = right ? gr : gl;
+        unsigned v = border;
+        if (x > 0 && x < W - 1) {
+            const uint8_t *r0 = g + (size_t)y * p.Wp + x, *rn = g + (size_t)yn * p.Wp + x, *rs = g + (size_t)ys * p.Wp + x;
+            int a = 2 * ((int)r0[1] - (int)r0[-1]) + ((int)rn[1] - (int)rn[-1]) + ((int)rs[1] - (int)rs[-1]);
             a = min(max(a, -ft), ft) + ft;
-            c = min(max(c, -ft), ft) + ft;
-            vl = (unsigned)a | ((unsigned)l0[0] << 16);
-            vr = (unsigned)c | ((unsigned)r0[0] << 16);
+            v = (unsigned)a | ((unsigned)r0[0] << 16);
         }
-        aL[x] = vl; aR[x] = vr;
+        (right ? aR : aL)[right ? i - nL - 2 : i] = v;      // columns outside the image never matter (guarded below)
     }
     __syncthreads();
-    for (int x = tid; x < W; x += nt) {
-#pragma unroll
-        for (int s = 0; s < 2; s++) {
-            const unsigned* a = s ? aR : aL;
-            unsigned u = a[x];
-            unsigned ul = x > 0 ? (((u + a[x - 1]) >> 1) & 0x7fff7fffu) : u;
-            unsigned ur = x < W - 1 ? (((u + a[x + 1]) >> 1) & 0x7fff7fffu) : u;
-            unsigned u0 = __vimin3_s16x2(ul, ur, u), u1 = __vimax3_s16x2(ul, ur, u);
-            uint4 o = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
-            if (s) Rpk[x] = o; else Lpk[x] = o;
-        }
+    for (int i = tid; i < nL + nR; i += nt) {
+        const bool right = i >= nL;
+        const int j = right ? i - nL : i;
+        const int x = (right ? xr0 : xl0) + j;
+        const unsigned* a = (right ? aR : aL) + j + 1;
+        const unsigned u = a[0];
+        const unsigned ul = x > 0 ? (((u + a[-1]) >> 1) & 0x7fff7fffu) : u;
+        const unsigned ur = x < W - 1 ? (((u + a[1]) >> 1) & 0x7fff7fffu) : u;
+        const unsigned u0 = __vimin3_s16x2(ul, ur, u), u1 = __vimax3_s16x2(ul, ur, u);
+        (right ? Rpk : Lpk)[j] = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
     }
     __syncthreads();
 
     const int d = tid;
-    const int W1 = p.W1, Dp = p.Dp;
     int16_t* out = hsum + (((size_t)b * H + y) * W1) * Dp + d;
     if (d >= p.D) {
-        for (int xp = 0; xp < W1; xp++) out[(size_t)xp * Dp] = 0;
+        for (int xp = s; xp < e; xp++) out[(size_t)xp * Dp] = 0;
         return;
     }
-    const int dd = p.minD + d, minX1 = p.minX1;
+    const int offR = p.minX1 - p.minD - d - xr0;        // right descriptor index of computed column xp: xp + offR
+    const int offL = p.minX1 - xl0;
     auto pixcost = [&](int xp) -> int {
-        const int x = xp + minX1;
-        const uint4 l = Lpk[x];
-        const uint4 r = Rpk[x - dd];
+        const uint4 l = Lpk[xp + offL];
+        const uint4 r = Rpk[xp + offR];
         unsigned c0 = __vimax3_s16x2_relu(__vadd2(l.x, r.w), __vadd2(r.y, l.z), 0u);   // max(0, u - v1, v0 - u)
         unsigned c1 = __vimax3_s16x2_relu(__vadd2(r.x, l.w), __vadd2(l.y, r.z), 0u);   // max(0, v - u1, u0 - v)
         unsigned m = __vmins2(c0, c1);
         return (int)(m & 0xffffu) + (int)(m >> 18);
     };
     uint8_t* ring = ringbuf + d;
-    const int SW2 = p.SW2, rmask = p.ring - 1;
-    const int last = min(SW2, W1 - 1);
-    int run = 0, pixLast = 0;
-    for (int k = 0; k <= last; k++) {
-        int c = pixcost(k);
-        ring[(k & rmask) * Dp] = (uint8_t)c;
-        run += (k == 0) ? c * (SW2 + 1) : c;
-        pixLast = c;
-    }
-    run += (SW2 - last) * pixLast;
-    out[0] = (int16_t)run;
-    for (int xp = 1; xp < W1; xp++) {
-        const int ia = xp + SW2;
-        int add;
-        if (ia <= W1 - 1) { add = pixcost(ia); ring[(ia & rmask) * Dp] = (uint8_t)add; pixLast = add; }
-        else add = pixLast;
-        const int is = max(xp - SW2 - 1, 0);
-        run += add - (int)ring[(is & rmask) * Dp];
-        out[(size_t)xp * Dp] = (int16_t)run;
+    const int rmask = p.ring - 1, bs = p.bs;
+    int run = 0;
+    const int j0 = s - SW2, j1 = e - 1 + SW2;
+    for (int j = j0; j <= j1; j++) {
+        const int c = pixcost(min(max(j, 0), W1 - 1));
+        ring[((j - j0) & rmask) * Dp] = (uint8_t)c;
+        run += c;
+        if (j - j0 >= bs) run -= (int)ring[((j - j0 - bs) & rmask) * Dp];
+        if (j >= s + SW2) out[(size_t)(j - SW2) * Dp] = (int16_t)run;
     }
 }
 
@@ -739,13 +734,17 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     k_fill_s16<<<(unsigned)cvr_div_up_sz(npix, 256), 256, 0, c->stream>>>(c->d_raw, npix, p.INVALID);
     LAUNCH_CHECK(c);
     {
-        const size_t smem = (size_t)p.W * (2 * sizeof(uint4) + 2 * sizeof(unsigned)) + (size_t)p.ring * p.Dp;
+        int nseg = (p.W1 + 160) / 320;
+        if (nseg < 1) nseg = 1;
+        const int segMax = cvr_div_up(p.W1, nseg) + 1;
+        const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;
+        const size_t smem = (nLmax + nRmax) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)p.ring * p.Dp;
         static size_t smem_set = 0;
         if (smem > 48 * 1024 && smem > smem_set) {
             CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             smem_set = smem;
         }
-        k_pix_hsum<<<dim3(p.H, B), p.Dp, smem, c->stream>>>(c->d_gray, (size_t)2 * p.H * p.Wp, c->d_volA, p);
+        k_pix_hsum<<<dim3(p.H * nseg, B), p.Dp, smem, c->stream>>>(c->d_gray, (size_t)2 * p.H * p.Wp, c->d_volA, p, nseg);
         LAUNCH_CHECK(c);
         cvr_stage_mark(c, "pix_hsum");
     }
