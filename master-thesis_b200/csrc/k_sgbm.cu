@@ -113,15 +113,51 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
         return (int)(m & 0xffffu) + (int)(m >> 18);
     };
     uint8_t* ring = ringbuf + d;
-    const int rmask = p.ring - 1, bs = p.bs;
+    const int bs = p.bs, ringBytes = p.ring * Dp;
     int run = 0;
     const int j0 = s - SW2, j1 = e - 1 + SW2;
-    for (int j = j0; j <= j1; j++) {
+    // warm-up: the first bs - 1 window elements (clamped at the left image border), nothing to emit or to drop yet
+    int j = j0, wi = 0;                                               // wi: byte offset of the ring slot written next
+    for (; j < s + SW2; j++) {
         const int c = pixcost(min(max(j, 0), W1 - 1));
-        ring[((j - j0) & rmask) * Dp] = (uint8_t)c;
+        ring[wi] = (uint8_t)c;
         run += c;
-        if (j - j0 >= bs) run -= (int)ring[((j - j0 - bs) & rmask) * Dp];
-        if (j >= s + SW2) out[(size_t)(j - SW2) * Dp] = (int16_t)run;
+        wi += Dp; if (wi == ringBytes) wi = 0;
+    }
+    // steady state: one new element, one output; from the second output on the element leaving the window is dropped.
+    // No clamping while j <= W1 - 1: running pointers only.
+    int16_t* o = out + (size_t)s * Dp;
+    int ri = 0;                                                       // byte offset of the ring slot holding element j - bs
+    {
+        const int c = pixcost(min(j, W1 - 1));
+        ring[wi] = (uint8_t)c; run += c; wi += Dp; if (wi == ringBytes) wi = 0;
+        *o = (int16_t)run; o += Dp; j++;
+    }
+    const int jmid = min(j1, W1 - 1);
+    const uint4* lp = Lpk + (j + offL);
+    const uint4* rp = Rpk + (j + offR);
+    for (; j <= jmid; j++, lp++, rp++, o += Dp) {
+        const uint4 l = *lp;
+        const uint4 r = *rp;
+        const unsigned c0 = __vimax3_s16x2_relu(__vadd2(l.x, r.w), __vadd2(r.y, l.z), 0u);
+        const unsigned c1 = __vimax3_s16x2_relu(__vadd2(r.x, l.w), __vadd2(l.y, r.z), 0u);
+        const unsigned m = __vmins2(c0, c1);
+        const int c = (int)(m & 0xffffu) + (int)(m >> 18);
+        run += c - (int)ring[ri];
+        ring[wi] = (uint8_t)c;
+        *o = (int16_t)run;
+        wi += Dp; if (wi == ringBytes) wi = 0;
+        ri += Dp; if (ri == ringBytes) ri = 0;
+    }
+    if (j <= j1) {                                                    // right image border: the last column repeats
+        const int cl = pixcost(W1 - 1);
+        for (; j <= j1; j++, o += Dp) {
+            run += cl - (int)ring[ri];
+            ring[wi] = (uint8_t)cl;
+            *o = (int16_t)run;
+            wi += Dp; if (wi == ringBytes) wi = 0;
+            ri += Dp; if (ri == ringBytes) ri = 0;
+        }
     }
 }
 
