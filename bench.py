@@ -193,7 +193,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--batch", type=int, default=36, help="frames per GPU per step")
+    ap.add_argument("--batch", type=int, default=72, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -316,20 +316,23 @@ def main():
     if rank == 0:
         peak, peak_kind = hbm_peak()
         cells = (W - D) * H * D
-        alg_bytes = 6.0 * cells * B                 # k_path_v per launch: read C, read S, write S (int16 each)
+        alg_bytes = 6.0 * cells * B                 # k_path_v3 per launch: read C, read S, write S (int16 each)
         kv = stage_ms.get("path_v_down", [])
         kv_ms = float(np.mean(kv)) if kv else None
         roof = None
         if kv_ms:
             ach = alg_bytes / (kv_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "k_path_v<4,false,false,512>", "achieved": ach, "peak": peak, "peak_kind": peak_kind, "unit": "GB/s",
-                    "frac": ach / peak, "traffic": None, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": kv_ms,
+            # DRAM traffic of this kernel from the committed ncu --set full capture (profiles/r01d_top_kernels_raw.csv:
+            # dram__bytes_read.sum + dram__bytes_write.sum = 7.702 + 3.809 GB for a 36-frame launch), scaled to this batch
+            traffic = (7.701787e9 + 3.808850e9) / 36.0 * B
+            roof = {"bound": "hbm", "kernel": "k_path_v3<4,false,false,false,true,1024>", "achieved": ach, "peak": peak, "peak_kind": peak_kind,
+                    "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": kv_ms,
                     "share_of_step": kv_ms / (ms_dev / args.steps)}
         out = {
             "metric": "stereo frames/sec (SGBM->cloud->filter)", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int16", "data": "synthetic (%d unique seeded pairs cycled)" % UNIQUE_PAIRS,
-            "config": {"workload": WORKLOAD, "frames_per_gpu_per_step": B, "l2": "working set per step (cost volumes 214 MB/frame) >> 126 MB L2",
+            "config": {"workload": WORKLOAD, "frames_per_gpu_per_step": B, "l2": "inputs larger than L2: working set per step (cost volumes 214 MB/frame x batch) >> 126 MB L2",
                        "parallelism": "frames sharded, dp%d, NCCL gather of filtered clouds to rank 0" % world},
             "e2e": {"value": e2e_v, "unit": "frames/s", "h2d_bytes_per_step": 2 * frame_bytes * B, "d2h_bytes_per_step": int(counts.sum()) * 16 + 4 * B,
                     "ms_per_step": ms_e2e / args.steps},
