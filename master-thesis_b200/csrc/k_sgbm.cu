@@ -196,14 +196,14 @@ __global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C
     int neg = c[0] | c[1] | c[2] | c[3];
     cs[0] = make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3]));
     for (int y = 1; y < H; y++) {
-        uint2 ho = hs[(size_t)max(y - SH2 - 1, 0) * rowWords];
-        uint2 hn = hs[(size_t)min(y + SH2, H - 1) * rowWords];
+        const uint2 ho = __ldcs(hs + (size_t)max(y - SH2 - 1, 0) * rowWords);   // last use of that row: evict-first
+        const uint2 hn = hs[(size_t)min(y + SH2, H - 1) * rowWords];              // read again bs rows later: keep in L2
         int ov[4] = { lo16(ho.x), hi16(ho.x), lo16(ho.y), hi16(ho.y) };
         int nv[4] = { lo16(hn.x), hi16(hn.x), lo16(hn.y), hi16(hn.y) };
 #pragma unroll
         for (int j = 0; j < 4; j++) c[j] = first ? sat16i(sat16i(c[j] + nv[j]) - ov[j]) : sat16i(sat16i(c[j] - ov[j]) + nv[j]);
         neg |= c[0] | c[1] | c[2] | c[3];
-        cs[(size_t)y * rowWords] = make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3]));
+        __stcs(cs + (size_t)y * rowWords, make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3])));   // streamed out, not re-read here
     }
     if (neg < 0) atomicOr(&flags[b], 1);      // a negative C exists in this frame: the packed path kernels take their exact t + C form
 }
