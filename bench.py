@@ -195,6 +195,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=72, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--matcher", default="sgbm", choices=["sgbm", "bm"], help="sgbm = the headline path; bm = the reference's other block matcher (side measurement)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -215,7 +216,10 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
     cvr = importlib.import_module("master-thesis_b200")
     B = args.batch
-    rec = cvr.Reconstruct3D(W, H, max_batch=B, device=local)          # defaults = config_default.json SGBM section, leaf 0.2, SOR 30/0.5
+    cfg = cvr.parse_config(None)
+    if args.matcher == "bm":
+        cfg["block_matcher"] = cvr.MATCHER_BM
+    rec = cvr.Reconstruct3D(W, H, config=cfg, max_batch=B, device=local)   # defaults = config_default.json SGBM/SBM sections, leaf 0.2, SOR 30/0.5
     Ls, Rs = make_pairs(UNIQUE_PAIRS)
     idx = [(rank * B + i) % UNIQUE_PAIRS for i in range(B)]            # frame_id sharding; the pool of unique pairs is cycled
     hL = torch.from_numpy(Ls[idx]).pin_memory(); hR = torch.from_numpy(Rs[idx]).pin_memory()
@@ -323,6 +327,8 @@ def main():
         cells = (W - D) * H * D
         alg_bytes = 6.0 * cells * B                 # k_path_v3 per launch: read C, read S, write S (int16 each)
         kv = stage_ms.get("path_v_down", [])
+        if args.matcher == "bm":
+            kv = []
         kv_ms = float(np.mean(kv)) if kv else None
         roof = None
         if kv_ms:

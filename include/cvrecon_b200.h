@@ -44,6 +44,7 @@ typedef enum cvr_status {
 enum { CVR_MODE_SGBM = 0, CVR_MODE_HH = 1 };
 enum { CVR_MEM_HOST = 0, CVR_MEM_DEVICE = 1 };
 enum { CVR_CLOUD_TRIANGULATE = 0, CVR_CLOUD_REPROJECT = 1 };
+enum { CVR_MATCHER_SGBM = 0, CVR_MATCHER_BM = 1 };
 
 /* cv::StereoSGBM parameters exactly as Reconstruct3D::ConfigureSteoreoMatcher sets them
  * (cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:50-64; JSON keys in
@@ -76,6 +77,18 @@ typedef struct cvr_params {
     int   cloud_mode;           /* CVR_CLOUD_TRIANGULATE (live path) | CVR_CLOUD_REPROJECT */
     int   max_points;           /* point capacity per frame for the cloud filters; 0 => width*height */
     int   filter_only;          /* 1 => no stereo workspace: only cvr_voxel_grid / cvr_sor are usable */
+    /* "block_matcher" switch of config.json (Reconstruct3D.cpp:41-68): CVR_MATCHER_SGBM | CVR_MATCHER_BM.  The BM branch is
+     * cv::StereoBM::create(16, 21) + setBlockSize(SBM.window_size) + setNumDisparities(SBM.num_disparities)
+     * (Reconstruct3D.cpp:43-48, :378-380); the remaining fields are OpenCV's StereoBM defaults. */
+    int   block_matcher;
+    int   bm_window_size;       /* odd, 5..255 (config SBM.window_size = 27) */
+    int   bm_num_disparities;   /* multiple of 16, <= 256 (config SBM.num_disparities = 128) */
+    int   bm_min_disparity;     /* 0 (values > 0 unsupported) */
+    int   bm_pre_filter_cap;    /* 31 */
+    int   bm_texture_threshold; /* 10 */
+    int   bm_uniqueness_ratio;  /* 15 */
+    int   bm_speckle_window_size; /* 0 = off */
+    int   bm_speckle_range;     /* 0 */
 } cvr_params;
 
 typedef struct cvr_point {      /* 16 bytes */

@@ -23,6 +23,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libcvrecon_b200.so")
 MODE_SGBM, MODE_HH = 0, 1
 MEM_HOST, MEM_DEVICE = 0, 1
 CLOUD_TRIANGULATE, CLOUD_REPROJECT = 0, 1
+MATCHER_SGBM, MATCHER_BM = 0, 1
 STAGE_DISPARITY, STAGE_CLOUD, STAGE_VOXEL, STAGE_SOR = 1, 2, 4, 8
 
 POINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), ("g", "u1"), ("r", "u1"), ("a", "u1")])
@@ -48,7 +49,9 @@ class Params(C.Structure):
         ("tri_f", C.c_float), ("tri_b", C.c_float), ("tri_cx", C.c_float), ("tri_cy", C.c_float),
         ("prune_sigma_factor", C.c_double), ("voxel_leaf", C.c_float * 3), ("sor_mean_k", C.c_int),
         ("sor_stddev_mul", C.c_double), ("max_batch", C.c_int), ("cloud_mode", C.c_int), ("max_points", C.c_int),
-        ("filter_only", C.c_int),
+        ("filter_only", C.c_int), ("block_matcher", C.c_int), ("bm_window_size", C.c_int), ("bm_num_disparities", C.c_int),
+        ("bm_min_disparity", C.c_int), ("bm_pre_filter_cap", C.c_int), ("bm_texture_threshold", C.c_int), ("bm_uniqueness_ratio", C.c_int),
+        ("bm_speckle_window_size", C.c_int), ("bm_speckle_range", C.c_int),
     ]
 
 
@@ -146,12 +149,13 @@ def parse_config(path_or_dict=None):
         with open(cfg) as f:
             cfg = json.load(f)
     rec = cfg["config"]["reconstruction"]
-    if rec.get("block_matcher", "stereo_bm") != "stereo_sgbm":
-        raise CvrError(-2, "block_matcher '%s': only the stereo_sgbm branch is implemented (StereoBM is a SURVEY 8(f) 'next' row)"
-                       % rec.get("block_matcher"))
+    # ConfigParser.cpp:40-50: "stereo_bm" / "stereo_sgbm", anything else falls back to the block matcher
+    bm = rec.get("block_matcher", "stereo_bm") != "stereo_sgbm"
     s = rec["SGBM"]
+    sbm = rec.get("SBM", {"window_size": 21, "num_disparities": 16})
     pp = cfg["config"].get("point_cloud_post_processing", {})
-    return dict(block_size=int(s["block_size"]), num_disparities=int(s["num_disparities"]),
+    return dict(block_matcher=MATCHER_BM if bm else MATCHER_SGBM, window_size=int(sbm["window_size"]),
+                bm_num_disparities=int(sbm["num_disparities"]), block_size=int(s["block_size"]), num_disparities=int(s["num_disparities"]),
                 uniqueness_ratio=int(s["uniqueness_ratio"]), speckle_range=int(s["speckle_range"]),
                 speckle_window_size=int(s["speckle_window_size"]), pre_filter_cap=int(s["pre_filter_cap"]),
                 min_disparity=int(s["min_disparity"]), outlier_min_k=int(pp.get("outlier_min_k", 30)),
@@ -205,6 +209,12 @@ class Reconstruct3D:
         p.max_batch = int(max_batch)
         p.cloud_mode = int(cloud_mode)
         p.max_points = int(max_points)
+        p.block_matcher = int(cfg.get("block_matcher", MATCHER_SGBM))
+        p.bm_window_size = int(cfg.get("window_size", 27))               # Reconstruct3D.cpp:45
+        p.bm_num_disparities = int(cfg.get("bm_num_disparities", 128))     # Reconstruct3D.cpp:46
+        for k_ in ("bm_min_disparity", "bm_pre_filter_cap", "bm_texture_threshold", "bm_uniqueness_ratio", "bm_speckle_window_size", "bm_speckle_range"):
+            if k_ in cfg:
+                setattr(p, k_, int(cfg[k_]))
         p.filter_only = int(bool(filter_only))
         self.params = p
         self.Q = Qm

@@ -30,6 +30,10 @@ extern "C" void cvr_default_params(cvr_params* p, int width, int height)
     p->voxel_leaf[0] = p->voxel_leaf[1] = p->voxel_leaf[2] = 0.2f;
     p->sor_mean_k = 30; p->sor_stddev_mul = 0.5;
     p->max_batch = 1; p->cloud_mode = CVR_CLOUD_TRIANGULATE; p->max_points = 0; p->filter_only = 0;
+    // config_default.json:8-12 ("block_matcher": "stereo_bm" is the file's default; this library's default stays SGBM, the path
+    // named by the north star) + cv::StereoBM::create(16, 21) defaults
+    p->block_matcher = CVR_MATCHER_SGBM; p->bm_window_size = 27; p->bm_num_disparities = 128; p->bm_min_disparity = 0;
+    p->bm_pre_filter_cap = 31; p->bm_texture_threshold = 10; p->bm_uniqueness_ratio = 15; p->bm_speckle_window_size = 0; p->bm_speckle_range = 0;
 }
 
 void cvr_stage_mark(cvr_ctx* c, const char* name)
@@ -64,6 +68,17 @@ static int validate(const cvr_params* p, std::string& err)
     if (p->width > 65535) { err = "width > 65535 unsupported"; return CVR_ERR_UNSUPPORTED; }
     if (p->max_batch < 1) { err = "max_batch must be >= 1"; return CVR_ERR_INVALID_ARG; }
     if (p->filter_only) return CVR_OK;
+    if (p->block_matcher == CVR_MATCHER_BM) {
+        // the checks of cv::StereoBM::compute
+        if (p->bm_pre_filter_cap < 1 || p->bm_pre_filter_cap > 63) { err = "bm_pre_filter_cap must be within 1..63"; return CVR_ERR_INVALID_ARG; }
+        if (p->bm_window_size < 5 || p->bm_window_size > 255 || p->bm_window_size % 2 == 0 || p->bm_window_size >= (p->width < p->height ? p->width : p->height)) {
+            err = "bm_window_size must be odd, within 5..255 and smaller than the image"; return CVR_ERR_INVALID_ARG; }
+        if (p->bm_num_disparities <= 0 || p->bm_num_disparities % 16 != 0) { err = "bm_num_disparities must be a positive multiple of 16"; return CVR_ERR_INVALID_ARG; }
+        if (p->bm_num_disparities > 256) { err = "bm_num_disparities > 256 unsupported"; return CVR_ERR_UNSUPPORTED; }
+        if (p->bm_texture_threshold < 0 || p->bm_uniqueness_ratio < 0) { err = "bm texture threshold / uniqueness ratio must be non-negative"; return CVR_ERR_INVALID_ARG; }
+        if (p->bm_min_disparity > 0) { err = "bm_min_disparity > 0 unsupported (the reference never sets it; OpenCV's own loop overruns the row there)"; return CVR_ERR_UNSUPPORTED; }
+        return CVR_OK;
+    } else if (p->block_matcher != CVR_MATCHER_SGBM) { err = "block_matcher must be CVR_MATCHER_SGBM or CVR_MATCHER_BM"; return CVR_ERR_INVALID_ARG; }
     const cvr_sgbm_params& s = p->sgbm;
     if (s.num_disparities <= 0 || s.num_disparities % 16 != 0) { err = "num_disparities must be a positive multiple of 16 (OpenCV rejects others)"; return CVR_ERR_INVALID_ARG; }
     if (s.num_disparities > 256) { err = "num_disparities > 256 unsupported"; return CVR_ERR_UNSUPPORTED; }
@@ -102,6 +117,15 @@ static void fill_dev_params(cvr_ctx* c)
     g.INVALID = (g.minD - 1) * CVR_DISP_SCALE;
     g.mode = s.mode;
     g.ring = 1; while (g.ring < g.bs + 1) g.ring <<= 1;
+    BmDev& m = c->bm;
+    memset(&m, 0, sizeof(m));
+    m.W = p.width; m.H = p.height; m.Wp = g.Wp;
+    m.minD = p.bm_min_disparity; m.ndisp = p.bm_num_disparities; m.Dp = ((m.ndisp + 63) / 64) * 64;
+    m.wsz = p.bm_window_size; m.wsz2 = m.wsz / 2; m.cap = p.bm_pre_filter_cap; m.textureThreshold = p.bm_texture_threshold; m.uniq = p.bm_uniqueness_ratio;
+    { const int t = m.ndisp - 1 + m.minD; m.lofs = t > 0 ? t : 0; m.rofs = t < 0 ? -t : 0; }
+    m.width1 = m.W - m.rofs - m.ndisp + 1;
+    m.FILTERED = (m.minD - 1) * CVR_DISP_SCALE;
+    m.ring = 1; while (m.ring < m.wsz + 1) m.ring <<= 1;
     CloudDev& cl = c->cl;
     memcpy(cl.Q, p.Q, sizeof(cl.Q));
     cl.f = p.tri_f; cl.b = p.tri_b; cl.cx = p.tri_cx; cl.cy = p.tri_cy;
@@ -127,7 +151,7 @@ static void free_all(cvr_ctx* c)
     void* ptrs[] = { c->d_in[0], c->d_in[1], c->d_gray, c->d_volA, c->d_volC, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, c->d_disp, c->d_med,
                      c->d_label, c->d_size, c->d_pruned, c->d_dispf, c->d_mask, c->d_pstats, c->d_rowcnt, c->d_cloud, c->d_ncloud, c->d_vhdr,
                      c->d_keys[0], c->d_keys[1], c->d_vals[0], c->d_vals[1], c->d_hist, c->d_segstart, c->d_vox, c->d_cellstart, c->d_cellidx,
-                     c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags };
+                     c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags, c->d_bmpre };
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->pipe_ready) {
@@ -177,10 +201,13 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
 #define A(call) if (e == cudaSuccess) e = (call)
     if (!p->filter_only) {
-        const size_t W1 = g.W1 > 0 ? g.W1 : 0, vol = (size_t)g.H * W1 * g.Dp;
+        const bool isBM = p->block_matcher == CVR_MATCHER_BM;
+        const size_t W1 = isBM ? (c->bm.width1 > 0 ? c->bm.width1 : 0) : (g.W1 > 0 ? g.W1 : 0);
+        const size_t vol = (size_t)g.H * W1 * (isBM ? c->bm.Dp : g.Dp) * (isBM ? 1 : 1);
         A(dalloc(&c->d_in[0], B * HW * 4)); A(dalloc(&c->d_in[1], B * HW * 4));
         A(dalloc(&c->d_gray, B * 2 * g.H * g.Wp));
-        A(dalloc(&c->d_volA, B * vol)); A(dalloc(&c->d_volC, B * vol));
+        A(dalloc(&c->d_bmpre, isBM ? B * 2 * g.H * g.Wp : 1));
+        A(dalloc(&c->d_volA, B * vol)); A(dalloc(&c->d_volC, isBM ? 1 : B * vol));
         A(dalloc(&c->d_lr, B * 2 * (W1 + 2) * 3 * g.Dp)); A(dalloc(&c->d_minlr, B * 2 * (W1 + 2) * 4));
         A(dalloc(&c->d_raw, B * HW)); A(dalloc(&c->d_aux, B * g.H * (W1 + 1))); A(dalloc(&c->d_disp, B * HW)); A(dalloc(&c->d_med, B * HW));
         A(dalloc(&c->d_label, B * HW)); A(dalloc(&c->d_size, B * HW));
@@ -246,7 +273,7 @@ extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const u
     int rc = cvr_launch_gray(c, 1, c->d_in[0], (size_t)W * ch, 0, c->d_in[1], (size_t)W * ch, 0, ch);
     if (rc) return rc;
     cvr_stage_mark(c, "h2d_gray");
-    rc = cvr_launch_sgbm(c, 1);
+    rc = (c->prm.block_matcher == CVR_MATCHER_BM) ? cvr_launch_bm(c, 1) : cvr_launch_sgbm(c, 1);
     if (rc) return rc;
     CVR_CUDA(c, cudaMemcpy2DAsync(disp, sd, c->d_med, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->stream));
     cvr_stage_mark(c, "d2h");
@@ -259,6 +286,7 @@ extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, i
 {
     if (!c) return CVR_ERR_INVALID_ARG;
     STEREO_ONLY(c);
+    if (c->prm.block_matcher != CVR_MATCHER_SGBM) { c->err = "debug buffers exist for the SGBM matcher only"; return CVR_ERR_INVALID_ARG; }
     const SgbmDev& g = c->sg;
     if (w1) *w1 = g.W1;
     if (dp) *dp = g.Dp;
@@ -411,7 +439,7 @@ static int enqueue_chain(cvr_ctx* c, int B, int stages, const uint8_t* dl, size_
     int rc = cvr_launch_gray(c, B, dl, lstep, lfs, dr, rstep, rfs, ch);
     if (rc) return rc;
     cvr_stage_mark(c, "gray");
-    rc = cvr_launch_sgbm(c, B);
+    rc = (c->prm.block_matcher == CVR_MATCHER_BM) ? cvr_launch_bm(c, B) : cvr_launch_sgbm(c, B);
     if (rc) return rc;
     if (wantCloud || wantVox || wantSor) {
         rc = cvr_launch_prune(c, B, c->d_med);

@@ -27,6 +27,15 @@ struct SgbmDev {
     int ring;            // pow2 >= bs + 1 (pixel-cost ring buffer of the horizontal box sum)
 };
 
+struct BmDev {
+    int W, H, Wp;
+    int minD, ndisp, Dp;
+    int wsz, wsz2, cap, textureThreshold, uniq;
+    int lofs, rofs, width1;
+    int FILTERED;
+    int ring;            // pow2 >= wsz + 1
+};
+
 struct CloudDev {
     float Q[16];
     float f, b, cx, cy;
@@ -83,6 +92,7 @@ struct PipeSlot {
 struct cvr_ctx {
     cvr_params prm;
     SgbmDev sg;
+    BmDev bm;
     CloudDev cl;
     int device;
     int maxB;
@@ -101,6 +111,7 @@ struct cvr_ctx {
     uint8_t* d_in[2];        // staged input images (host path), tight: [B][H][W*ch]
     size_t in_bytes_per_frame;
     uint8_t* d_gray;         // [B][2][H][Wp]
+    uint8_t* d_bmpre;        // StereoBM: x-Sobel prefiltered images [B][2][H][Wp]
     int16_t* d_volA;         // hsum, later S : [B][H][W1][Dp]
     int16_t* d_volC;         // C             : [B][H][W1][Dp]
     int16_t* d_lr;           // vertical path state [B][2][W1+2][3][Dp]
@@ -168,6 +179,8 @@ static inline size_t cvr_div_up_sz(size_t a, size_t b) { return (a + b - 1) / b;
 int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t lfs, const uint8_t* right, size_t rstep,
                     size_t rfs, int channels);
 int cvr_launch_sgbm(cvr_ctx* c, int B);     // gray -> d_med (final disparity)
+int cvr_launch_bm(cvr_ctx* c, int B);       // k_bm.cu: gray -> d_med with StereoBM semantics
+int cvr_launch_speckle(cvr_ctx* c, int B, int newVal, int maxSize, int maxDiff);   // in place on d_med
 // k_cloud.cu
 int cvr_launch_prune(cvr_ctx* c, int B, const int16_t* disp_in /*[B][H][W] tight*/);
 int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const float* dispf, const uint8_t* mask,

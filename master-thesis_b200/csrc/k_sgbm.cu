@@ -755,6 +755,21 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     return CVR_OK;
 }
 
+// cv::filterSpeckles(d_med, newVal, maxSize, maxDiff) for every frame of the batch, in place.
+int cvr_launch_speckle(cvr_ctx* c, int B, int newVal, int maxSize, int maxDiff)
+{
+    const int W = c->prm.width, H = c->prm.height, N = W * H;
+    k_ccl_runs<<<cvr_div_up(B * H, 4), 128, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, W, H, B, newVal, maxDiff);
+    LAUNCH_CHECK(c);
+    k_ccl_vmerge<<<dim3(cvr_div_up(W, 128), H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, W, H, newVal, maxDiff);
+    LAUNCH_CHECK(c);
+    k_ccl_count<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_label, c->d_size, N);
+    LAUNCH_CHECK(c);
+    k_ccl_apply<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, N, newVal, maxSize);
+    LAUNCH_CHECK(c);
+    return CVR_OK;
+}
+
 int cvr_launch_sgbm(cvr_ctx* c, int B)
 {
     const SgbmDev& p = c->sg;
@@ -811,16 +826,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "lr_median");
     if (c->prm.sgbm.speckle_window_size > 0) {
-        const int N = p.W * p.H;
-        const int maxDiff = CVR_DISP_SCALE * c->prm.sgbm.speckle_range;
-        k_ccl_runs<<<cvr_div_up(B * p.H, 4), 128, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, p.W, p.H, B, p.INVALID, maxDiff);
-        LAUNCH_CHECK(c);
-        k_ccl_vmerge<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, p.W, p.H, p.INVALID, maxDiff);
-        LAUNCH_CHECK(c);
-        k_ccl_count<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_label, c->d_size, N);
-        LAUNCH_CHECK(c);
-        k_ccl_apply<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, N, p.INVALID, c->prm.sgbm.speckle_window_size);
-        LAUNCH_CHECK(c);
+        rc = cvr_launch_speckle(c, B, p.INVALID, c->prm.sgbm.speckle_window_size, CVR_DISP_SCALE * c->prm.sgbm.speckle_range);
+        if (rc) return rc;
         cvr_stage_mark(c, "speckle");
     }
     return CVR_OK;

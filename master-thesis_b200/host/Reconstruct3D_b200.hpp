@@ -30,9 +30,13 @@ struct StereoCalib {    // the fields of Camera::Calib::StereoCalib the path rea
     float T0;                   // T(0): baseline
 };
 
-struct SGBMConfig {     // Config::Reconstruction::SGBM (Config.hpp:36-44)
+enum StereoBlockMatcherType { STEREO_BLOCK_MATCHER = 0, STEREO_SEMI_GLOBAL_BLOCK_MATCHER = 1 };   // Reconstruct3DTypes.hpp:12-15
+
+struct SGBMConfig {     // Config::Reconstruction (Config.hpp:25-45): BlockMatcherType, SBM, SGBM
     int NumDisparities = 16, BlockSize = 128, UniquenessRatio = 2, SpeckleRange = 2, SpeckleWindowSize = 100, PreFilterCap = 10,
         MinDisparity = 0;
+    StereoBlockMatcherType BlockMatcherType = STEREO_SEMI_GLOBAL_BLOCK_MATCHER;
+    int SBMNumDisparities = 16, SBMWindowSize = 21;                          // Config::Reconstruction::SBM (Config.hpp:31-34)
     int OutlierMinK = 30;            // point_cloud_post_processing.outlier_min_k (config_default.json:24)
     double OutlierStdDevThreshold = 0.5;
 };
@@ -56,6 +60,9 @@ public:
         p.sgbm.P1 = 8 * 3 * cfg.BlockSize * cfg.BlockSize;      // Reconstruct3D.cpp:63
         p.sgbm.P2 = 32 * 3 * cfg.BlockSize * cfg.BlockSize;     // Reconstruct3D.cpp:64
         p.sgbm.mode = mode;
+        // Reconstruct3D.cpp:41-48: the STEREO_BLOCK_MATCHER branch = StereoBM::create(16, 21) + block size + disparities
+        p.block_matcher = cfg.BlockMatcherType == STEREO_BLOCK_MATCHER ? CVR_MATCHER_BM : CVR_MATCHER_SGBM;
+        p.bm_window_size = cfg.SBMWindowSize; p.bm_num_disparities = cfg.SBMNumDisparities;
         for (int i = 0; i < 16; i++) p.Q[i] = (i % 5 == 0) ? 1.0f : 0.0f;
         const float f = (calib.fxL + calib.fxR) / 2.0f;         // Reconstruct3D.cpp:33
         p.Q[10] = static_cast<float>(0.005 * f);                // Reconstruct3D.cpp:34

@@ -538,3 +538,108 @@ int orc_sor(const orc_point* in, int n, int k, double alpha, orc_point* out, flo
     free(dist); free(best);
     return m;
 }
+
+/* ------------------------------------------------------------------------- */
+/* cv::StereoBM::compute (PREFILTER_XSOBEL), the other branch of the reference's  */
+/* block-matcher switch: Reconstruct3D.cpp:43-48 (StereoBM::create(16, 21) +      */
+/* setBlockSize(window_size) + setNumDisparities), SURVEY 8(f) row n2.            */
+/* Restated from OpenCV's published algorithm (modules/calib3d/src/stereobm.cpp:  */
+/* prefilterXSobel, findStereoCorrespondenceBM, getValidDisparityROI); pinned     */
+/* against cv2.StereoBM by tests/golden (bm_*.npz).                              */
+typedef struct orc_bm_params {
+    int minDisparity, numDisparities, blockSize, preFilterCap, textureThreshold, uniquenessRatio, speckleWindowSize, speckleRange;
+} orc_bm_params;
+
+static void orc_prefilter_xsobel(const uint8_t* src, size_t step, int W, int H, int cap, uint8_t* dst)
+{
+    /* rows are processed in pairs; a trailing odd row is filled with the neutral value `cap` */
+    int y;
+    for (y = 0; y < H - 1; y += 2) {
+        const uint8_t* s1 = src + (size_t)y * step;
+        const uint8_t* s0 = y > 0 ? s1 - step : (H > 1 ? s1 + step : s1);
+        const uint8_t* s2 = y < H - 1 ? s1 + step : (H > 1 ? s1 - step : s1);
+        const uint8_t* s3 = y < H - 2 ? s1 + 2 * step : s1;
+        uint8_t* d0 = dst + (size_t)y * W; uint8_t* d1 = d0 + W;
+        d0[0] = d0[W - 1] = d1[0] = d1[W - 1] = (uint8_t)cap;
+        for (int x = 1; x < W - 1; x++) {
+            int e0 = s0[x + 1] - s0[x - 1], e1 = s1[x + 1] - s1[x - 1], e2 = s2[x + 1] - s2[x - 1], e3 = s3[x + 1] - s3[x - 1];
+            int v0 = e0 + e1 * 2 + e2, v1 = e1 + e2 * 2 + e3;
+            d0[x] = (uint8_t)(imin(imax(v0, -cap), cap) + cap);
+            d1[x] = (uint8_t)(imin(imax(v1, -cap), cap) + cap);
+        }
+    }
+    for (; y < H; y++) memset(dst + (size_t)y * W, cap, (size_t)W);
+}
+
+int orc_stereobm_compute(const uint8_t* left, size_t stepL, const uint8_t* right, size_t stepR, int W, int H,
+                         const orc_bm_params* p, int16_t* disp)
+{
+    const int ndisp = p->numDisparities, mindisp = p->minDisparity, wsz = p->blockSize, wsz2 = wsz / 2;
+    const int cap = p->preFilterCap, FILTERED = (mindisp - 1) * 16;
+    const int lofs = imax(ndisp - 1 + mindisp, 0), rofs = -imin(ndisp - 1 + mindisp, 0), width1 = W - rofs - ndisp + 1;
+    for (size_t i = 0; i < (size_t)W * H; i++) disp[i] = (int16_t)FILTERED;
+    if (lofs >= W || rofs >= W || width1 < 1) return 0;
+    uint8_t* L = (uint8_t*)malloc((size_t)W * H); uint8_t* R = (uint8_t*)malloc((size_t)W * H);
+    orc_prefilter_xsobel(left, stepL, W, H, cap, L);
+    orc_prefilter_xsobel(right, stepR, W, H, cap, R);
+    /* column SAD and texture sums with replicated borders, then the window sums -- direct (non-incremental) evaluation of
+       what findStereoCorrespondenceBM maintains incrementally */
+    int* sad = (int*)malloc(sizeof(int) * (size_t)(ndisp + 2));
+    int32_t* hsad = (int32_t*)malloc(sizeof(int32_t) * (size_t)H * ndisp);
+    int32_t* htext = (int32_t*)malloc(sizeof(int32_t) * (size_t)H);
+    /* for minDisparity > 0 OpenCV's loop runs to lofs + x >= W (its stores spill into the masked left border of the next
+       row); those columns do not exist, so the restatement stops at the image edge */
+    for (int x = 0; x < width1 && lofs + x < W; x++) {
+        /* hsad[y][d] = sum over window columns of |L(y, xl) - R(y, xr + d)|, xl = lofs + clamp(xx, -lofs, W-1-lofs),
+           xr = rofs + clamp(xx, -rofs, W-ndisp-rofs); array index d means disparity ndisp-1-d+mindisp */
+        for (int y = 0; y < H; y++) {
+            int32_t* hs = hsad + (size_t)y * ndisp;
+            memset(hs, 0, sizeof(int32_t) * (size_t)ndisp);
+            int t = 0;
+            for (int xx = x - wsz2; xx <= x + wsz2; xx++) {
+                int xl = lofs + imin(imax(xx, -lofs), W - 1 - lofs);
+                int xr = rofs + imin(imax(xx, -rofs), W - ndisp - rofs);
+                int lval = L[(size_t)y * W + xl];
+                const uint8_t* rp = R + (size_t)y * W + xr;
+                for (int d = 0; d < ndisp; d++) hs[d] += abs(lval - rp[d]);
+                t += abs(lval - cap);
+            }
+            htext[y] = t;
+        }
+        for (int y = 0; y < H; y++) {
+            int tsum = 0;
+            for (int d = 0; d < ndisp; d++) sad[d + 1] = 0;
+            for (int yy = y - wsz2; yy <= y + wsz2; yy++) {
+                int yc = imin(imax(yy, 0), H - 1);
+                const int32_t* hs = hsad + (size_t)yc * ndisp;
+                for (int d = 0; d < ndisp; d++) sad[d + 1] += hs[d];
+                tsum += htext[yc];
+            }
+            int16_t* dp = disp + (size_t)y * W + lofs + x;
+            int minsad = 0x7fffffff, mind = -1;
+            for (int d = 0; d < ndisp; d++) if (sad[d + 1] < minsad) { minsad = sad[d + 1]; mind = d; }
+            if (tsum < p->textureThreshold) { *dp = (int16_t)FILTERED; continue; }
+            if (p->uniquenessRatio > 0) {
+                int thresh = minsad + (minsad * p->uniquenessRatio / 100), d;
+                for (d = 0; d < ndisp; d++) if ((d < mind - 1 || d > mind + 1) && sad[d + 1] <= thresh) break;
+                if (d < ndisp) { *dp = (int16_t)FILTERED; continue; }
+            }
+            sad[0] = sad[2]; sad[ndisp + 1] = sad[ndisp - 1];
+            int pp = sad[mind + 2], nn = sad[mind], dd = pp + nn - 2 * sad[mind + 1] + abs(pp - nn);
+            *dp = (int16_t)((((ndisp - mind - 1 + mindisp) * 256 + (dd != 0 ? (pp - nn) * 256 / dd : 0)) + 15) >> 4);
+        }
+    }
+    free(sad); free(hsad); free(htext); free(L); free(R);
+    /* validDisparityRect (getValidDisparityROI with both ROIs = whole image): everything outside is FILTERED */
+    {
+        const int maxD = mindisp + ndisp - 1;
+        const int xmin = imax(0, maxD) + wsz2, xmax = W - wsz2, ymin = wsz2, ymax = H - wsz2;
+        const int ok = (xmax - xmin > 0) && (ymax - ymin > 0);
+        for (int y = 0; y < H; y++)
+            for (int x = 0; x < W; x++)
+                if (!ok || x < xmin || x >= xmax || y < ymin || y >= ymax) disp[(size_t)y * W + x] = (int16_t)FILTERED;
+    }
+    if (p->speckleRange >= 0 && p->speckleWindowSize > 0)
+        orc_filter_speckles(disp, W, H, FILTERED, p->speckleWindowSize, p->speckleRange);
+    return 0;
+}

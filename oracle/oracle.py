@@ -94,6 +94,28 @@ def sgbm(left, right, params, stages=False):
     return disp, dict(raw=raw, C=Cv, S=Sv, minL=stats[0], minC=stats[1])
 
 
+class BmParams(C.Structure):
+    _fields_ = [(n, C.c_int) for n in ("minDisparity", "numDisparities", "blockSize", "preFilterCap", "textureThreshold",
+                                      "uniquenessRatio", "speckleWindowSize", "speckleRange")]
+
+
+def reference_bm_params(window_size=27, num_disparities=128):
+    """Reconstruct3D::ConfigureSteoreoMatcher, STEREO_BLOCK_MATCHER branch (Reconstruct3D.cpp:43-48, :378-380):
+    cv::StereoBM::create(16, 21) then setBlockSize / setNumDisparities; everything else stays at OpenCV's defaults."""
+    return dict(minDisparity=0, numDisparities=int(num_disparities), blockSize=int(window_size), preFilterCap=31, textureThreshold=10,
+                uniquenessRatio=15, speckleWindowSize=0, speckleRange=0)
+
+
+def stereobm(left, right, params):
+    left = np.ascontiguousarray(left, np.uint8)
+    right = np.ascontiguousarray(right, np.uint8)
+    H, W = left.shape
+    prm = BmParams(**params)
+    disp = np.empty((H, W), np.int16)
+    lib().orc_stereobm_compute(_p(left), C.c_size_t(W), _p(right), C.c_size_t(W), W, H, C.byref(prm), _p(disp))
+    return disp
+
+
 def median3(img):
     img = np.ascontiguousarray(img, np.int16)
     out = np.empty_like(img)

@@ -104,6 +104,38 @@ def special():
     print("satdrift", {k: int((v >= 0).sum()) for k, v in out.items() if k.startswith("disp")})
 
 
+BM_CASES = {   # name: (H, W, ndisp, window, seed, extra StereoBM setters)
+    "bm_60x300_d64_w9": (60, 300, 64, 9, 21, {}),
+    "bm_61x300_d64_w21": (61, 300, 64, 21, 22, {}),
+    "bm_64x260_d32_w11_minneg": (64, 260, 32, 11, 23, dict(minDisparity=-16)),
+    "bm_64x260_d48_w15_nouniq": (64, 260, 48, 15, 24, dict(uniquenessRatio=0, textureThreshold=0)),
+    "bm_64x260_d48_w15_speckle": (64, 260, 48, 15, 25, dict(speckleWindowSize=50, speckleRange=16, preFilterCap=63)),
+    "bm_kitti_d128_w27": (375, 1242, 128, 27, 0, {}),
+}
+
+
+def cv_bm(l, r, p):
+    """Reconstruct3D.cpp:378-380 + :45-46: StereoBM::create(16, 21), setBlockSize, setNumDisparities."""
+    m = cv2.StereoBM_create(16, 21)
+    m.setBlockSize(p["blockSize"]); m.setNumDisparities(p["numDisparities"])
+    m.setMinDisparity(p["minDisparity"]); m.setPreFilterCap(p["preFilterCap"]); m.setTextureThreshold(p["textureThreshold"])
+    m.setUniquenessRatio(p["uniquenessRatio"]); m.setSpeckleWindowSize(p["speckleWindowSize"]); m.setSpeckleRange(p["speckleRange"])
+    return m.compute(l, r)
+
+
+def bm_cases():
+    for name, (H, W, D, ws, seed, kw) in BM_CASES.items():
+        lb, rb = O.synth_pair(H, W, D, seed, color=True)
+        gl = cv2.cvtColor(lb, cv2.COLOR_BGR2GRAY); gr = cv2.cvtColor(rb, cv2.COLOR_BGR2GRAY)
+        p = O.reference_bm_params(ws, D); p.update(kw)
+        disp = cv_bm(gl, gr, p)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), disp=disp, meta=np.array([H, W, D, ws, seed], np.int64),
+                            params=np.array([p[k] for k in sorted(p)], np.int64), param_names=np.array(sorted(p)),
+                            crc=np.array([zlib.crc32(lb.tobytes()), zlib.crc32(rb.tobytes())], np.uint64))
+        print(name, "valid %.1f%%" % (100 * (disp >= p["minDisparity"] * 16).mean()))
+
+
 if __name__ == "__main__":
+    bm_cases()
     special()
     main()

@@ -305,3 +305,47 @@ def test_pipelined_submit_wait_equals_synchronous(cvr, oracle):
     rec.wait_batch()
     rec.wait_batch()
     rec.close()
+
+
+def _bm_cfg(p):
+    return dict(block_matcher=1, window_size=p["blockSize"], bm_num_disparities=p["numDisparities"], bm_min_disparity=p["minDisparity"],
+                bm_pre_filter_cap=p["preFilterCap"], bm_texture_threshold=p["textureThreshold"], bm_uniqueness_ratio=p["uniquenessRatio"],
+                bm_speckle_window_size=p["speckleWindowSize"], bm_speckle_range=p["speckleRange"],
+                block_size=5, num_disparities=16, uniqueness_ratio=10, speckle_range=2, speckle_window_size=100, pre_filter_cap=10, min_disparity=0)
+
+
+@pytest.mark.parametrize("name", ["bm_60x300_d64_w9", "bm_61x300_d64_w21", "bm_64x260_d32_w11_minneg", "bm_64x260_d48_w15_nouniq",
+                                  "bm_64x260_d48_w15_speckle", "bm_kitti_d128_w27"])
+def test_stereobm_bit_exact_vs_cv2_golden(cvr, oracle, name):
+    """The reference's default block matcher (config_default.json "block_matcher": "stereo_bm"), SURVEY 8(f) n2."""
+    from test_oracle_golden import bm_golden_inputs
+    g = load_golden(name)
+    lb, rb, p = bm_golden_inputs(oracle, g)
+    H, W = lb.shape[:2]
+    rec = cvr.Reconstruct3D(W, H, config=_bm_cfg(p))
+    got = rec.GenerateDisparityMap(lb, rb)
+    assert np.array_equal(got, g["disp"]), "%d pixels differ from cv2.StereoBM" % int((got != g["disp"]).sum())
+    rec.close()
+
+
+@pytest.mark.parametrize("D,ws", [(16, 5), (32, 7), (80, 13), (160, 9), (256, 17), (96, 31)])
+def test_stereobm_sweep_against_oracle(cvr, oracle, D, ws):
+    H, W = 50 + ws, D + 140
+    l, r = oracle.synth_pair(H, W, D, seed=D + ws)
+    p = oracle.reference_bm_params(ws, D)
+    want = oracle.stereobm(l, r, p)
+    rec = cvr.Reconstruct3D(W, H, config=_bm_cfg(p), max_batch=2)
+    assert np.array_equal(rec.GenerateDisparityMap(l, r), want)
+    # through the batched chain as well (disparity -> prune -> cloud ...)
+    disp, clouds = rec.ProcessFrames(np.stack([l, l]), np.stack([r, r]), want_disp=True, stages=3)
+    assert np.array_equal(disp[0], want) and np.array_equal(disp[1], want)
+    rec.close()
+
+
+def test_stereobm_rejects_what_opencv_rejects(cvr):
+    for bad in (dict(window_size=4), dict(window_size=3), dict(bm_num_disparities=24), dict(bm_pre_filter_cap=64), dict(bm_min_disparity=8)):
+        cfg = _bm_cfg(dict(blockSize=9, numDisparities=32, minDisparity=0, preFilterCap=31, textureThreshold=10, uniquenessRatio=15,
+                           speckleWindowSize=0, speckleRange=0))
+        cfg.update(bad)
+        with pytest.raises(cvr.CvrError):
+            cvr.Reconstruct3D(200, 60, config=cfg)

@@ -129,3 +129,24 @@ def test_pcl_side_hand_cases(oracle):
     dup = np.concatenate([c[:20], c[:20]])
     k3, d3, _, _ = oracle.sor(dup, 4, 1.0)
     assert np.isfinite(d3).all()
+
+
+BM_GOLDEN = ["bm_60x300_d64_w9", "bm_61x300_d64_w21", "bm_64x260_d32_w11_minneg", "bm_64x260_d48_w15_nouniq", "bm_64x260_d48_w15_speckle",
+             "bm_kitti_d128_w27"]
+
+
+def bm_golden_inputs(O, g):
+    H, W, D, ws, seed = [int(v) for v in g["meta"]]
+    lb, rb = O.synth_pair(H, W, D, seed, color=True)
+    assert zlib.crc32(lb.tobytes()) == int(g["crc"][0])
+    p = {str(k): int(v) for k, v in zip(g["param_names"], g["params"])}
+    return lb, rb, p
+
+
+@pytest.mark.parametrize("name", BM_GOLDEN)
+def test_stereobm_oracle_matches_cv2(oracle, name):
+    """the StereoBM branch of the block-matcher switch, pinned against cv2.StereoBM."""
+    g = load_golden(name)
+    lb, rb, p = bm_golden_inputs(oracle, g)
+    got = oracle.stereobm(oracle.gray_bgr(lb), oracle.gray_bgr(rb), p)
+    assert np.array_equal(got, g["disp"]), "%d pixels differ from cv2.StereoBM" % int((got != g["disp"]).sum())
