@@ -138,6 +138,14 @@ int cvr_voxel_grid(cvr_ctx* ctx, const cvr_point* in, int n, cvr_point* out, int
  * pcl::StatisticalOutlierRemoval with meanK / stddevMulThresh from cvr_params.  in == out allowed. */
 int cvr_sor(cvr_ctx* ctx, const cvr_point* in, int n, cvr_point* out, int capacity, int* kept_out);
 
+/* SURVEY 8(f) row n3 -- the consumer-side steps MappingSystem applies to the cloud right after the path.
+ * Replaces: pcl::RadiusOutlierRemoval::filter at MappingSystem.cpp:303-307 (setRadiusSearch(1.0), setMinNeighborsInRadius(300)):
+ * a point is kept iff at least min_neighbors + 1 points (itself included) lie within `radius`.  Input order preserved. */
+int cvr_radius_outlier_removal(cvr_ctx* ctx, const cvr_point* in, int n, float radius, int min_neighbors, cvr_point* out, int capacity,
+                               int* kept_out);
+/* Replaces: pcl::transformPointCloud(cloud, cloud, pose) at MappingSystem.cpp:318 (T: row-major 4x4, f32; colours untouched). */
+int cvr_transform_cloud(cvr_ctx* ctx, const cvr_point* in, int n, const float* T, cvr_point* out);
+
 /* Frame-parallel fused path: for each of nframes frames
  *   GenerateDisparityMap -> SetupFrame(prune) -> Triangulate3D|GeneratePointCloud -> VoxelGrid -> SOR
  * (the per-frame chain of ReconstructionSystem::ProcessStereoFrame, ReconstructionSystem.cpp:35-61,

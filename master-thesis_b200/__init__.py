@@ -33,7 +33,7 @@ EXPORTS = [
     "cvr_default_params", "cvr_create", "cvr_destroy", "cvr_last_error", "cvr_version", "cvr_disparity", "cvr_prune",
     "cvr_reproject_cloud", "cvr_triangulate", "cvr_voxel_grid", "cvr_sor", "cvr_process_batch", "cvr_points_to_pcl",
     "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling", "cvr_prune_noalloc",
-    "cvr_submit_batch", "cvr_wait_batch",
+    "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
 ]
 
 
@@ -108,6 +108,8 @@ def load_library():
     lib.cvr_voxel_grid.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     lib.cvr_sor.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     lib.cvr_process_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(Batch)]
+    lib.cvr_radius_outlier_removal.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+    lib.cvr_transform_cloud.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     lib.cvr_submit_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(Batch)]
     lib.cvr_wait_batch.argtypes = [C.c_void_p]
     lib.cvr_debug_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -318,6 +320,22 @@ class Reconstruct3D:
         k = C.c_int()
         self._check(self.lib.cvr_sor(self.ctx, _ptr(pts), len(pts), _ptr(out), len(out), C.byref(k)))
         return out[:k.value].copy()
+
+    # -- pcl::RadiusOutlierRemoval::filter at MappingSystem.cpp:303-307 --
+    def RadiusOutlierRemoval(self, cloud, radius=1.0, min_neighbors=300):
+        pts = np.ascontiguousarray(cloud, POINT_DTYPE)
+        out = np.empty(max(len(pts), 1), POINT_DTYPE)
+        k = C.c_int()
+        self._check(self.lib.cvr_radius_outlier_removal(self.ctx, _ptr(pts), len(pts), float(radius), int(min_neighbors), _ptr(out), len(out), C.byref(k)))
+        return out[:k.value].copy()
+
+    # -- pcl::transformPointCloud at MappingSystem.cpp:318 --
+    def TransformPointCloud(self, cloud, T):
+        pts = np.ascontiguousarray(cloud, POINT_DTYPE)
+        Tm = np.ascontiguousarray(T, np.float32).reshape(4, 4)
+        out = np.empty(len(pts), POINT_DTYPE)
+        self._check(self.lib.cvr_transform_cloud(self.ctx, _ptr(pts), len(pts), _ptr(Tm), _ptr(out)))
+        return out
 
     # -- ReconstructionSystem::ProcessStereoFrame chain for a batch of frames (host buffers) --
     def ProcessFrames(self, lefts, rights, stages=0, want_disp=False, cloud_capacity=None):

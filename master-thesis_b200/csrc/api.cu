@@ -421,6 +421,39 @@ extern "C" int cvr_sor(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, i
     return rc;
 }
 
+extern "C" int cvr_radius_outlier_removal(cvr_ctx* c, const cvr_point* in, int n, float radius, int min_neighbors, cvr_point* out, int capacity, int* kept_out)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    REQUIRE(c, n >= 0 && (n == 0 || (in && out)) && radius > 0.f && min_neighbors >= 0, "bad argument");
+    if (n > c->maxN) { c->err = "cloud larger than the context's point capacity (cvr_params.max_points)"; return CVR_ERR_CAPACITY; }
+    if (kept_out) *kept_out = 0;
+    if (n == 0) return CVR_OK;
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c);
+    CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
+    c->h_counts[1] = n;
+    CVR_CUDA(c, cudaMemcpyAsync(c->d_nvox, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_ror(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, radius, min_neighbors);
+    if (rc) return rc;
+    rc = fetch_cloud(c, c->d_sorout, c->d_nout, out, capacity, kept_out);
+    timers_end(c);
+    return rc;
+}
+
+extern "C" int cvr_transform_cloud(cvr_ctx* c, const cvr_point* in, int n, const float* T, cvr_point* out)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    REQUIRE(c, n >= 0 && T && (n == 0 || (in && out)), "bad argument");
+    if (n > c->maxN) { c->err = "cloud larger than the context's point capacity (cvr_params.max_points)"; return CVR_ERR_CAPACITY; }
+    if (n == 0) return CVR_OK;
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_transform(c, c->d_vox, c->d_sorout, n, T);
+    if (rc) return rc;
+    CVR_CUDA(c, cudaMemcpyAsync(out, c->d_sorout, (size_t)n * sizeof(cvr_point), cudaMemcpyDeviceToHost, c->stream));
+    return sync_check(c);
+}
+
 __global__ void k_copy_clouds(const cvr_point* __restrict__ src, size_t srcStride, const int* __restrict__ cnt, cvr_point* __restrict__ dst,
                               size_t cap, int* __restrict__ cntOut)
 {

@@ -190,6 +190,8 @@ int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, c
 // k_sor.cu
 int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in /*device*/, int n_is_vox);
 
+int cvr_launch_ror(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, float radius, int min_pts);
+int cvr_launch_transform(cvr_ctx* c, const cvr_point* in, cvr_point* out, int n, const float* T);
 void cvr_stage_mark(cvr_ctx* c, const char* name);
 // message slot read by cvr_last_error(NULL): used by entry points that have no context
 void cvr_set_thread_error(const char* msg);

@@ -251,3 +251,130 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     cvr_stage_mark(c, "sor");
     return CVR_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// SURVEY 8(f) row n3 -- what MappingSystem does with the cloud right after the path.
+// pcl::RadiusOutlierRemoval (cv_reconstruct/src/system/MappingSystem.cpp:303-307): keep a point iff at least min_pts + 1 points
+// (itself included) lie within `radius` (squared distance <= r^2).  Same uniform grid as the SOR search, cell = radius.
+__global__ void k_ror_grid(const VoxBox* box, const int* nPtr, SorGrid* grid, int* ncellOut, float radius, int cap, int B)
+{
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    SorGrid g;
+    g.n = nPtr[b];
+    float ext[3];
+    for (int k = 0; k < 3; k++) {
+        g.mn[k] = g.n > 0 ? ord2f(box[b].mn[k]) : 0.f;
+        const float mx = g.n > 0 ? ord2f(box[b].mx[k]) : 0.f;
+        ext[k] = fmaxf(mx - g.mn[k], 0.f);
+    }
+    float s = radius;                                  // cell edge: a multiple of the radius when the grid would get too large
+    for (int it = 0; it < 32; it++) {
+        long long tot = 1;
+        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
+        if (tot <= cap) break;
+        s *= 1.5f;
+    }
+    g.cell = s; g.inv = 1.0f / s;
+    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
+    grid[b] = g;
+    ncellOut[b] = g.ncell;
+}
+__global__ void __launch_bounds__(128) k_ror_count(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
+                                                   const int* __restrict__ cellstart, size_t cellStride, float radius, int min_pts, float* __restrict__ flag)
+{
+    const int b = blockIdx.y, t = blockIdx.x * blockDim.x + threadIdx.x;
+    const SorGrid g = grid[b];
+    if (t >= g.n) return;
+    const float4* sp = spts + (size_t)b * ptStride;
+    const int* cs = cellstart + (size_t)b * cellStride;
+    const float4 q = sp[t];
+    const float r2 = __fmul_rn(radius, radius);
+    int cx, cy, cz;
+    sor_cell(g, q.x, q.y, q.z, cx, cy, cz);
+    const int R = (int)ceilf(radius * g.inv);           // rings of cells that can hold a point within the radius (1 unless the grid was coarsened)
+    int cnt = 0;
+    for (int iz = max(cz - R, 0); iz <= min(cz + R, g.dim[2] - 1) && cnt <= min_pts; iz++)
+        for (int iy = max(cy - R, 0); iy <= min(cy + R, g.dim[1] - 1) && cnt <= min_pts; iy++) {
+            const int rowc = (iz * g.dim[1] + iy) * g.dim[0];
+            const int jb = cs[rowc + max(cx - R, 0)], je = cs[rowc + min(cx + R, g.dim[0] - 1) + 1];
+            for (int j = jb; j < je && cnt <= min_pts; j++) {
+                const float4 p = sp[j];
+                const float dx = __fsub_rn(q.x, p.x), dy = __fsub_rn(q.y, p.y), dz = __fsub_rn(q.z, p.z);
+                float d2 = __fmul_rn(dx, dx);
+                d2 = __fadd_rn(d2, __fmul_rn(dy, dy));
+                d2 = __fadd_rn(d2, __fmul_rn(dz, dz));
+                cnt += d2 <= r2;
+            }
+        }
+    // reuse the SOR compaction: "mean distance" 0 keeps, 1 drops against a threshold of 0.5
+    flag[(size_t)b * ptStride + __float_as_int(q.w)] = cnt > min_pts ? 0.f : 1.f;
+}
+__global__ void k_ror_thr(SorStats* st, int B) { int b = blockIdx.x * blockDim.x + threadIdx.x; if (b < B) st[b].thr = 0.5; }
+
+int cvr_launch_ror(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, float radius, int min_pts)
+{
+    const int maxN = c->maxN;
+    const size_t ptStride = (size_t)maxN;
+    const int cap = c->sor_grid_cap;
+    const size_t cellStride = (size_t)cap + 2;
+    VoxBox* box = (VoxBox*)c->d_flags;
+    SorGrid* grid = (SorGrid*)(c->d_flags + (size_t)c->maxB * 16);
+    int* ncell = c->d_flags + (size_t)c->maxB * 32;
+    int* cellstart = c->d_cellstart;
+    int* cellfill = c->d_cellstart + (size_t)c->maxB * cellStride;
+    k_bbox_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, B);
+    LAUNCH_CHECK(c);
+    k_bbox_minmax<<<dim3(64, B), 256, 0, c->stream>>>(in, in_stride, n_in, box);
+    LAUNCH_CHECK(c);
+    k_ror_grid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, n_in, grid, ncell, radius, cap, B);
+    LAUNCH_CHECK(c);
+    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellstart, cellStride, ncell, 1);
+    LAUNCH_CHECK(c);
+    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellfill, cellStride, ncell, 1);
+    LAUNCH_CHECK(c);
+    k_sor_cellcount<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
+    LAUNCH_CHECK(c);
+    k_scan_excl<<<B, 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, 1);
+    LAUNCH_CHECK(c);
+    k_sor_scatter<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
+    LAUNCH_CHECK(c);
+    k_ror_count<<<dim3(cvr_div_up(maxN, 128), B), 128, 0, c->stream>>>(c->d_spts, ptStride, grid, cellstart, cellStride, radius, min_pts, c->d_meand);
+    LAUNCH_CHECK(c);
+    k_ror_thr<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_sstats, B);
+    LAUNCH_CHECK(c);
+    const int nblk = cvr_div_up(maxN, CVR_SEL_BLOCK);
+    const size_t cntStride = (size_t)nblk + 1;
+    k_sor_count<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride);
+    LAUNCH_CHECK(c);
+    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
+    LAUNCH_CHECK(c);
+    k_sor_write<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(in, in_stride, c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride, nblk,
+                                                                c->d_sorout, (size_t)maxN, c->d_nout);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "ror");
+    return CVR_OK;
+}
+
+// pcl::transformPointCloud (MappingSystem.cpp:318): p' = T * (x, y, z, 1) in f32, ((col0*x + col1*y) + col2*z) + col3, no FMA.
+struct Mat4 { float m[16]; };
+__global__ void k_transform_cloud(const cvr_point* __restrict__ in, cvr_point* __restrict__ out, int n, Mat4 T)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    cvr_point p = in[i];
+    float v[3];
+#pragma unroll
+    for (int r = 0; r < 3; r++)
+        v[r] = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T.m[r * 4 + 0], p.x), __fmul_rn(T.m[r * 4 + 1], p.y)), __fmul_rn(T.m[r * 4 + 2], p.z)), T.m[r * 4 + 3]);
+    p.x = v[0]; p.y = v[1]; p.z = v[2];
+    out[i] = p;
+}
+int cvr_launch_transform(cvr_ctx* c, const cvr_point* in, cvr_point* out, int n, const float* T)
+{
+    Mat4 m;
+    for (int i = 0; i < 16; i++) m.m[i] = T[i];
+    k_transform_cloud<<<cvr_div_up(n, 256), 256, 0, c->stream>>>(in, out, n, m);
+    LAUNCH_CHECK(c);
+    return CVR_OK;
+}

@@ -643,3 +643,44 @@ int orc_stereobm_compute(const uint8_t* left, size_t stepL, const uint8_t* right
         orc_filter_speckles(disp, W, H, FILTERED, p->speckleWindowSize, p->speckleRange);
     return 0;
 }
+
+/* ------------------------------------------------------------------------- */
+/* the steps right after the path in MappingSystem.           */
+/* pcl::RadiusOutlierRemoval (MappingSystem.cpp:303-307: radius 1.0, 300          */
+/* neighbours; .filter commented in the reference): for dense clouds PCL asks for  */
+/* the min_pts+1 nearest neighbours (the query included) and keeps the point iff   */
+/* the farthest of them is within the radius (squared distance <= r^2).            */
+int orc_radius_outlier_removal(const orc_point* in, int n, float radius, int min_pts, orc_point* out, uint8_t* keep_out)
+{
+    const float r2 = radius * radius;
+    int m = 0;
+    for (int i = 0; i < n; i++) {
+        int cnt = 0;
+        for (int j = 0; j < n && cnt <= min_pts; j++) {
+            float dx = in[i].x - in[j].x, dy = in[i].y - in[j].y, dz = in[i].z - in[j].z;
+            float d2 = dx * dx; d2 += dy * dy; d2 += dz * dz;
+            if (d2 <= r2) cnt++;
+        }
+        int keep = cnt > min_pts;                      /* min_pts + 1 points (itself included) lie within the radius */
+        if (keep_out) keep_out[i] = (uint8_t)keep;
+        if (keep) out[m++] = in[i];
+    }
+    return m;
+}
+
+/* pcl::transformPointCloud(cloud, cloud, T) (MappingSystem.cpp:318; Reconstruct3D.cpp:149-150): p' = T * (x, y, z, 1),   */
+/* evaluated as Eigen does for a 4x4 float matrix: ((col0*x + col1*y) + col2*z) + col3, no FMA (no -mfma in the build). */
+void orc_transform_cloud(const orc_point* in, int n, const float* T /*4x4 row-major*/, orc_point* out)
+{
+    for (int i = 0; i < n; i++) {
+        orc_point p = in[i];
+        float v[3];
+        for (int r = 0; r < 3; r++) {
+            float a = T[r * 4 + 0] * in[i].x; float b = T[r * 4 + 1] * in[i].y; float s = a + b;
+            float c = T[r * 4 + 2] * in[i].z; s = s + c; s = s + T[r * 4 + 3];
+            v[r] = s;
+        }
+        p.x = v[0]; p.y = v[1]; p.z = v[2];
+        out[i] = p;
+    }
+}

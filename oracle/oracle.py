@@ -183,6 +183,24 @@ def voxel_grid(pts, leaf):
     return out[:m].copy(), counts[:m].copy(), bool(pt.value)
 
 
+def radius_outlier_removal(pts, radius, min_pts):
+    pts = np.ascontiguousarray(pts, POINT_DTYPE)
+    n = len(pts)
+    out = np.empty(max(n, 1), POINT_DTYPE)
+    keep = np.zeros(max(n, 1), np.uint8)
+    lib().orc_radius_outlier_removal.restype = C.c_int
+    m = lib().orc_radius_outlier_removal(_p(pts), n, C.c_float(radius), int(min_pts), _p(out), _p(keep))
+    return out[:m].copy(), keep[:n].copy()
+
+
+def transform_cloud(pts, T):
+    pts = np.ascontiguousarray(pts, POINT_DTYPE)
+    T = np.ascontiguousarray(T, np.float32)
+    out = np.empty(len(pts), POINT_DTYPE)
+    lib().orc_transform_cloud(_p(pts), len(pts), _p(T), _p(out))
+    return out
+
+
 def sor(pts, k, alpha):
     """Brute-force exact kNN statistical outlier removal.  Returns (kept points, mean dists, thr, keep mask)."""
     pts = np.ascontiguousarray(pts, POINT_DTYPE)

@@ -349,3 +349,23 @@ def test_stereobm_rejects_what_opencv_rejects(cvr):
         cfg.update(bad)
         with pytest.raises(cvr.CvrError):
             cvr.Reconstruct3D(200, 60, config=cfg)
+
+
+def test_radius_outlier_removal_and_transform_vs_oracle(cvr, oracle):
+    """SURVEY 8(f) n3: pcl::RadiusOutlierRemoval and pcl::transformPointCloud as MappingSystem.cpp:303-318 calls them."""
+    H, W, pts = _cloud_for_filters(cvr, oracle)
+    vox, _, _ = oracle.voxel_grid(pts, 0.05)
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(3, 96))
+    for radius, mn in ((0.2, 5), (0.5, 40), (1.0, 300), (0.05, 0)):
+        got = rec.RadiusOutlierRemoval(vox, radius, mn)
+        ref, keep = oracle.radius_outlier_removal(vox, radius, mn)
+        assert np.array_equal(got, ref), (radius, mn, len(got), len(ref))
+    assert 0 < len(oracle.radius_outlier_removal(vox, 0.2, 5)[0]) < len(vox)            # the comparison above is not vacuous
+    th = 0.3
+    T = np.array([[np.cos(th), 0, np.sin(th), 1.5], [0, 1, 0, -0.25], [-np.sin(th), 0, np.cos(th), 7.0], [0, 0, 0, 1]], np.float32)
+    got = rec.TransformPointCloud(vox, T)
+    ref = oracle.transform_cloud(vox, T)
+    for f in ("x", "y", "z"):
+        assert np.array_equal(got[f].view(np.uint32), ref[f].view(np.uint32))
+    assert np.array_equal(got["r"], vox["r"])
+    rec.close()
