@@ -132,6 +132,20 @@ def test_no_neighbour_shortcut_on_and_off(cvr, oracle, monkeypatch, mode):
         rec.close()
 
 
+@pytest.mark.parametrize("W1", [1, 3, 7, 8, 9, 17, 33, 65, 127])
+def test_narrow_images_pick_every_cluster_geometry(cvr, oracle, W1):
+    """Very narrow computed ranges walk through all launch geometries of the vertical path kernel (cluster size 1..8,
+    256..1024 threads, down to the int32 fallback when even 8 warps do not get a column each)."""
+    D, H = 32, 36
+    W = D + W1
+    for bs, mode in ((5, 0), (27, 1)):
+        l, r = oracle.synth_pair(H, W, D, seed=W1 + bs)
+        want = oracle.sgbm(l, r, oracle.reference_sgbm_params(block_size=bs, num_disparities=D, mode=mode))
+        rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D), mode=mode)
+        assert np.array_equal(rec.GenerateDisparityMap(l, r), want), (W1, bs, mode)
+        rec.close()
+
+
 def test_degenerate_inputs(cvr, oracle):
     # image narrower than the disparity range: everything invalid (A.0, W1 <= 0)
     rec = cvr.Reconstruct3D(60, 20, config=_cfg(5, 64))
