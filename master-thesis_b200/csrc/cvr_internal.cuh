@@ -159,6 +159,7 @@ struct cvr_ctx {
     bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)
     bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)
+    int pathv_active[3][9];  // concurrent clusters of the vertical path kernel per (CTA size, cluster size): 0 = not asked yet, -1 = cannot run
     int path_v_variant;      // 3 = point-to-point edge hand-over (default), 2 = per-row cluster barrier (CVR_PATH_KERNELS=v2)
 };
 

@@ -634,23 +634,59 @@ int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t
 
 struct VCfg { bool ok; int CL, NT; VState vs; size_t smem; };
 
-static VCfg pick_vcfg(const cvr_ctx* c)
+static size_t vcfg_smem(const SgbmDev& p, int CL, int NT, VState* vs)
+{
+    const int NW = NT / 32;
+    vs->colsMax = (p.W1 + CL - 1) / CL + 1; vs->colWords = 3 * p.Dp / 2 + 8; vs->inboxWords = p.Dp / 2 + 4;
+    return 4 * ((size_t)vs->colsMax * vs->colWords + (size_t)2 * NW * 2 * vs->inboxWords) + (size_t)2 * NW * 2 * 8;
+}
+
+// Geometry of the vertical path kernel: the largest CTA that fits the register budget, then the cluster size.
+// A cluster must sit inside one GPC, so the number of clusters that run at once depends on the cluster size in a way
+// only the occupancy query knows (measured on this B200: 15 clusters of 8, 22 of 6, 26 of 5); a frame takes time
+// proportional to the columns per CTA, and the batch runs in ceil(B / concurrent clusters) waves.  The cluster size
+// with the smallest waves x columns-per-CTA wins.  The query results are cached per context (first launch only).
+template <typename K>
+static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512)
 {
     const SgbmDev& p = c->sg;
     VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = 0;
-    const int nts[3] = { 1024, 512, 256 }, cls[4] = { 8, 4, 2, 1 };
-    for (int ni = (c->pathv_max_nt <= 256 ? 2 : (c->pathv_max_nt <= 512 ? 1 : 0)); ni < 3; ni++)
-        for (int ci = 0; ci < 4; ci++) {
-            const int NT = nts[ni], CL = cls[ci], NW = NT / 32, GW = CL * NW;
-            if (NT > 512 && p.Dp > 128) continue;                      // wide disparity ranges need > 64 registers per thread
-            if (GW > p.W1) continue;                                   // every warp must own at least one column
+    const int nts[3] = { 1024, 512, 256 };
+    const char* fcl = getenv("CVR_PATHV_CL");
+    const int forced = fcl ? atoi(fcl) : 0;
+    for (int ni = (c->pathv_max_nt <= 256 ? 2 : (c->pathv_max_nt <= 512 ? 1 : 0)); ni < 3; ni++) {
+        const int NT = nts[ni], NW = NT / 32;
+        if (NT > 512 && p.Dp > 128) continue;                          // wide disparity ranges need > 64 registers per thread
+        double best = 0;
+        for (int CL = 8; CL >= 1; CL--) {
+            if (forced && CL != forced) continue;
+            if (CL * NW > p.W1) continue;                              // every warp must own at least one column
             VState vs;
-            vs.colsMax = (p.W1 + CL - 1) / CL + 1; vs.colWords = 3 * p.Dp / 2 + 8; vs.inboxWords = p.Dp / 2 + 4;
-            const size_t smem = 4 * ((size_t)vs.colsMax * vs.colWords + (size_t)2 * NW * 2 * vs.inboxWords) + (size_t)2 * NW * 2 * 8;
+            const size_t smem = vcfg_smem(p, CL, NT, &vs);
             if (smem > (size_t)c->smem_optin) continue;
-            r.ok = true; r.CL = CL; r.NT = NT; r.vs = vs; r.smem = smem;
-            return r;
+            int& act = c->pathv_active[ni][CL];
+            if (act == 0) {                                            // not asked yet
+                K kernel = NT > 512 ? kernel1024 : kernel512;
+                act = -1;
+                if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess) {
+                    cudaLaunchConfig_t cfg = {};
+                    cfg.gridDim = dim3(CL, 64, 1); cfg.blockDim = dim3(NT, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
+                    cudaLaunchAttribute at[1];
+                    at[0].id = cudaLaunchAttributeClusterDimension;
+                    at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+                    cfg.attrs = at; cfg.numAttrs = 1;
+                    int n = 0;
+                    if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) == cudaSuccess && n > 0) act = n;
+                }
+                (void)cudaGetLastError();
+                if (getenv("CVR_VCFG_DEBUG")) fprintf(stderr, "[vcfg] NT=%d CL=%d smem=%zu concurrent clusters=%d\n", NT, CL, smem, act);
+            }
+            if (act <= 0) continue;
+            const double cost = (double)((B + act - 1) / act) * (double)(vs.colsMax + 8);
+            if (!r.ok || cost < best) { best = cost; r.ok = true; r.CL = CL; r.NT = NT; r.vs = vs; r.smem = smem; }
         }
+        if (r.ok) return r;
+    }
     return r;
 }
 
@@ -675,7 +711,8 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     const SgbmDev& p = c->sg;
     const int hblocks = cvr_div_up(B * p.H, 4);
     const bool packed = !c->force_generic && p.P1s >= 0;               // P1s < 0 (P1 in [32768, 65535] mod 65536): int32 kernels
-    const VCfg vc = packed ? pick_vcfg(c) : VCfg{ false, 1, 0, { 0, 0, 0 }, 0 };
+    const VCfg vc = packed ? pick_vcfg(c, B, k_path_v3<DPL, false, false, HASPAD, NN, 1024>, k_path_v3<DPL, false, false, HASPAD, NN, 512>)
+                           : VCfg{ false, 1, 0, { 0, 0, 0 }, 0 };
     int* fl = c->d_sgflags;
     // generic vertical kernel geometry: a cluster of CL CTAs per frame; fewer, larger clusters when the batch is small
     constexpr int NT = (DPL <= 4) ? 512 : 256;
