@@ -19,6 +19,7 @@ __device__ __forceinline__ unsigned pk2(int v) { return ((unsigned)v & 0xffffu) 
 struct PathK {                 // per-launch constants of the packed update
     unsigned P1p;              // P1s in both halves
     unsigned Qp;               // 32767 - P1s (P1s >= 0) or -32768 - P1s (P1s < 0)
+    unsigned Z;                // 0, kept in a register (a literal zero operand of min.s16x2 costs a PRMT per use)
 };
 
 // EXACT = false assumes C >= 0 (frame flag bit 0 clear); EXACT = true takes the general form of t + C.
@@ -142,14 +143,14 @@ __device__ __forceinline__ void acc_exact(unsigned (&s)[NWD], const unsigned (&L
 // neighbour terms Lp[d+-1] + P1s >= min + P1s >= min + P2s = delta can never win the four-way minimum, so the update
 // is exactly  L = min(Lp[d] - delta, 0) + C  -- no shuffles, no permutes.
 template <int NWD, bool HASPAD, bool NN>
-__device__ __forceinline__ int col_fast(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
+__device__ __forceinline__ unsigned col_fast_pk(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
                                         const PathK& k)
 {
     unsigned mnp = 0x7fff7fffu;
     if (NN) {
 #pragma unroll
         for (int j = 0; j < NWD; j++) {
-            unsigned v = __vadd2(__viaddmin_s16x2(Lp[j], ndeltap, 0u), c[j]);
+            unsigned v = __vadd2(__viaddmin_s16x2(Lp[j], ndeltap, k.Z), c[j]);
             if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
             L[j] = v;
             mnp = __vmins2(mnp, v);
@@ -165,12 +166,19 @@ __device__ __forceinline__ int col_fast(const unsigned (&Lp)[NWD], unsigned ndel
             const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
             const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);
             const unsigned t = __viaddmin_s16x2(n, k.P1p, Lp[j]);
-            unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, 0u), c[j]);
+            unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, k.Z), c[j]);
             if (HASPAD && (lane * NWD + j) * 2 >= D) v = 0x7fff7fffu;
             L[j] = v;
             mnp = __vmins2(mnp, v);
         }
     }
+    return mnp;                                                       // the lane's two candidate minima, packed
+}
+template <int NWD, bool HASPAD, bool NN>
+__device__ __forceinline__ int col_fast(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int lane, int D,
+                                        const PathK& k)
+{
+    const unsigned mnp = col_fast_pk<NWD, HASPAD, NN>(Lp, ndeltap, c, L, lane, D, k);
     return min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16);
 }
 // General column update for a given delta (any sign of Lp, delta; EXACT also any sign of C).
@@ -282,7 +290,7 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
     int2* auxp = aux + ((size_t)b * p.H + y) * W1 + (REVERSE ? W1 - 1 : 0);
     int* flagp = flags + b;
     bool exact = *flagp != 0;
-    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s); k.Z = (unsigned)p.D >> 20; CVR_PIN(k.Z);   // 0 (D < 2^15), but not a compile-time constant
     CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2); CVR_PIN(lane);
     unsigned Lp[NWD];
 #pragma unroll
@@ -356,7 +364,7 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
 // HBM traffic is the algorithmic minimum: read C, read S, write S.
 struct VState {                // shared-memory carve-up (in 32-bit words) computed on the host
     int colsMax;               // columns per CTA (upper bound)
-    int colWords;              // words per column: 3 * Dp/2 + 4 (three minima + pad)
+    int colWords;              // words per column: 3 * (Dp/2 + 4) (k_path_v2 keeps its three minima after the 3 * Dp/2 cost words)
     int inboxWords;            // words per inbox slot: Dp/2 + 4
 };
 
@@ -389,7 +397,7 @@ __global__ void __launch_bounds__((DPL <= 4 ? 1024 : 512), 1) k_path_v2(const in
         inbox[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : 0u;
     }
     bool exact = flags[b] != 0;
-    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s); k.Z = (unsigned)p.D >> 20; CVR_PIN(k.Z);   // 0 (D < 2^15), but not a compile-time constant
     CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
     const size_t colW = (size_t)dwords;
     // where this warp's edge costs go: the right neighbour's LEFT inbox (side 0) gets my last column's down-right
@@ -532,13 +540,131 @@ __device__ __forceinline__ void st_async_words(unsigned raddr, const unsigned (&
     }
 }
 
+__device__ __forceinline__ void st_async_v2(unsigned raddr, unsigned v0, unsigned v1, unsigned rbar)
+{
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v2.b32 [%0], {%1, %2}, [%3];" ::"r"(raddr), "r"(v0), "r"(v1), "r"(rbar) : "memory");
+}
+
+// Shared-memory layout: one "block" per (column, direction) = Dp/2 words of packed costs, then the two path_info words
+// (A, B) of that pixel's minimum and two pad words (keeps every block 16-byte aligned).  An inbox slot is one such block,
+// so "the old down-left block of the column to my right" is read through one pointer whether it lives in my own state or
+// in the inbox my right neighbour filled.  The column loop is unrolled by two with alternating register sets for the
+// prefetched C/S words and for the carried down-right block, which keeps the loop free of register-to-register moves.
+struct V3Ctx {                  // per-warp invariants of k_path_v3's column step (everything lives in registers after inlining)
+    int lane, D, P2, ncols, b, y, a, W1, storeS;
+    bool hasL, hasR, moreRows;
+    unsigned pushL_dst, pushL_bar, pushR_dst, pushR_bar;               // remote inbox slot / barrier of this row's parity
+    const unsigned* inR;                                               // my right inbox (previous row's parity)
+    const unsigned* rowC; unsigned* rowS; long long nextRow;           // this lane's words of the chunk's first column, row pitch in words
+    size_t frameRow0;
+    int16_t* raw; int2* aux; int* flags;
+    PathK k;
+};
+
+// stores of one finished column: the three new blocks, their path_info, the edge pushes, S (and the winner when WTA)
+template <int NWD, int FT, int LT, bool WTA, bool NN, int BLK, int DW>
+__device__ __forceinline__ void v3_finish(const V3Ctx& x, const SgbmDev& p, const int ci, unsigned* const cb, unsigned* const Sp, const bool firstCol,
+                                          const bool lastCol, const unsigned (&M1)[NWD], const unsigned (&M2)[NWD], const unsigned (&M3)[NWD],
+                                          const unsigned (&s)[NWD], const int mn1, const int mn2, const int mn3)
+{
+    const int lane = x.lane;
+    unsigned* const col = cb + lane * NWD;
+    stw<NWD>(col, M1); stw<NWD>(col + BLK, M2); stw<NWD>(col + 2 * BLK, M3);
+    // lanes 0..2 derive what the next pixel on each path needs from this pixel's minimum
+    unsigned iA, iB;
+    path_info<NN>(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3), x.P2, iA, iB);
+    if (lane < 3) *(uint2*)(cb + lane * BLK + DW) = make_uint2(iA, iB);
+    if (FT != 0 && firstCol && x.hasL) {                              // my first column's down-left block -> left neighbour's right inbox
+        st_async_words<NWD>(x.pushL_dst + lane * NWD * 4, M3, x.pushL_bar);
+        if (lane == 2) st_async_v2(x.pushL_dst + DW * 4, iA, iB, x.pushL_bar);
+    }
+    if (LT != 0 && lastCol && x.hasR) {                               // my last column's down-right block -> right neighbour's left inbox
+        st_async_words<NWD>(x.pushR_dst + lane * NWD * 4, M1, x.pushR_bar);
+        if (lane == 0) st_async_v2(x.pushR_dst + DW * 4, iA, iB, x.pushR_bar);
+    }
+    if (!WTA || x.storeS) stw<NWD>(Sp, s);
+    if (WTA) wta_column2<NWD>(s, lane, p, x.raw + (x.frameRow0 + x.y) * p.W + x.a + ci + p.minX1, x.aux + (x.frameRow0 + x.y) * x.W1 + x.a + ci);
+}
+
+// One column of one row.  FT / LT say whether this call can be the chunk's first / last column: 0 = never, 1 = always,
+// 2 = decide at run time.  c, s: this column's C and S words (s is updated); cNx, sNx receive the prefetched words of the
+// next column (or of the next row's first column); kin/kiIn: the carried old down-right block of the column to the left;
+// kout/kiOut receive this column's old down-right block for the next call.
+template <int NWD, int FT, int LT, bool WTA, bool HASPAD, bool NN, int BLK, int DW>
+__device__ __forceinline__ void v3_column(const V3Ctx& x, const SgbmDev& p, bool& exact, const int ci, unsigned* const cb, const unsigned* const Cp,
+                                          unsigned* const Sp, const unsigned (&c)[NWD], unsigned (&s)[NWD], unsigned (&cNx)[NWD], unsigned (&sNx)[NWD],
+                                          const unsigned (&kin)[NWD], const uint2 kiIn, unsigned (&kout)[NWD], uint2& kiOut)
+{
+    constexpr int colWords = 3 * BLK;
+    const int lane = x.lane;
+    const bool firstCol = FT == 2 ? (ci == 0) : (FT == 1);
+    const bool lastCol = LT == 2 ? (ci + 1 == x.ncols) : (LT == 1);
+    // ---- prefetch: the next column of this row, or the first column of the next row ----
+    if (LT == 0) { ldw<NWD>(Cp + DW, cNx); ldw<NWD>(Sp + DW, sNx); }
+    else {
+        const unsigned* nC = lastCol ? x.rowC + x.nextRow : Cp + DW;
+        const unsigned* nS = lastCol ? x.rowS + x.nextRow : Sp + DW;
+        if (!lastCol || x.moreRows) { ldw<NWD>(nC, cNx); ldw<NWD>(nS, sNx); }
+    }
+    // ---- sources: everything is read before this column's blocks are overwritten ----
+    unsigned* const col = cb + lane * NWD;
+    unsigned Lp2[NWD], Lp3[NWD], L1[NWD], L2[NWD], L3[NWD];
+    if (LT == 0 || (LT == 2 && !lastCol)) { ldw<NWD>(col, kout); kiOut = *(const uint2*)(cb + DW); }   // old down-right block: the next column's source
+    ldw<NWD>(col + BLK, Lp2);
+    const uint2 i2 = *(const uint2*)(cb + BLK + DW);
+    const unsigned* src3 = (LT == 0 || !lastCol) ? cb + colWords + 2 * BLK : x.inR;
+    ldw<NWD>(src3 + lane * NWD, Lp3);
+    const uint2 i3 = *(const uint2*)(src3 + DW);
+    if (!exact && (int)(kiIn.y | i2.y | i3.y) >= 0) {                  // the common case: one straight-line block for all three directions
+        const unsigned q1 = col_fast_pk<NWD, HASPAD, NN>(kin, kiIn.x, c, L1, lane, x.D, x.k);
+        const unsigned q2 = col_fast_pk<NWD, HASPAD, NN>(Lp2, i2.x, c, L2, lane, x.D, x.k);
+        const unsigned q3 = col_fast_pk<NWD, HASPAD, NN>(Lp3, i3.x, c, L3, lane, x.D, x.k);
+        // lane minima of two directions side by side; a 32-bit signed minimum over the warp is decided by the high half
+        const unsigned z12 = __vmins2(__byte_perm(q1, q2, 0x5410), __byte_perm(q1, q2, 0x7632));   // (min1 | min2 << 16)
+        const unsigned z3 = __vmins2(q3, __byte_perm(q3, q3, 0x1032));                              // min3 in both halves
+        const int r2 = __reduce_min_sync(0xffffffffu, (int)z12);
+        const int r1 = __reduce_min_sync(0xffffffffu, (int)(z12 << 16));
+        const int r3 = __reduce_min_sync(0xffffffffu, (int)z3);
+        const int mn1 = r1 >> 16, mn2 = r2 >> 16, mn3 = r3 >> 16;
+        if ((r1 | r2 | r3) < 0) {                                      // a negative path cost: unsigned sums are void, stay exact from here on
+            exact = true;
+            if (lane == 0) atomicOr(&x.flags[x.b], 2);
+            acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
+        } else {
+            acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3);
+        }
+        v3_finish<NWD, FT, LT, WTA, NN, BLK, DW>(x, p, ci, cb, Sp, firstCol, lastCol, L1, L2, L3, s, mn1, mn2, mn3);
+    } else {
+        const int d1 = (int)(short)(kiIn.y & 0xffffu), d2 = (int)(short)(i2.y & 0xffffu), d3 = (int)(short)(i3.y & 0xffffu);
+        int m1, m2, m3;
+        if (!exact) {
+            m1 = col_general<NWD, false, HASPAD>(kin, d1, c, L1, lane, x.D, x.k);
+            m2 = col_general<NWD, false, HASPAD>(Lp2, d2, c, L2, lane, x.D, x.k);
+            m3 = col_general<NWD, false, HASPAD>(Lp3, d3, c, L3, lane, x.D, x.k);
+        } else {
+            m1 = col_general<NWD, true, HASPAD>(kin, d1, c, L1, lane, x.D, x.k);
+            m2 = col_general<NWD, true, HASPAD>(Lp2, d2, c, L2, lane, x.D, x.k);
+            m3 = col_general<NWD, true, HASPAD>(Lp3, d3, c, L3, lane, x.D, x.k);
+        }
+        const int mn1 = __reduce_min_sync(0xffffffffu, m1);
+        const int mn2 = __reduce_min_sync(0xffffffffu, m2);
+        const int mn3 = __reduce_min_sync(0xffffffffu, m3);
+        if (min(min(mn1, mn2), mn3) < 0 && !exact) {
+            exact = true;
+            if (lane == 0) atomicOr(&x.flags[x.b], 2);
+        }
+        acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);   // valid for any signs
+        v3_finish<NWD, FT, LT, WTA, NN, BLK, DW>(x, p, ci, cb, Sp, firstCol, lastCol, L1, L2, L3, s, mn1, mn2, mn3);
+    }
+}
+
 template <int DPL, bool UP, bool WTA, bool HASPAD, bool NN, int MAXT>
 __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
                                                      int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     constexpr int NWD = DPL / 2;
     const int NT = blockDim.x, NW = NT / 32;
-    extern __shared__ unsigned smv[];
+    extern __shared__ uint4 smv3[];
     cg::cluster_group cluster = cg::this_cluster();
     const int b = blockIdx.y, rank = blockIdx.x;
     const int W1 = p.W1, D = p.D, H = p.H;
@@ -548,47 +674,42 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     const int ctaFirst = (int)(((long long)W1 * (rank * NW)) / GW);
     const int a = (int)(((long long)W1 * gw) / GW), e = (int)(((long long)W1 * (gw + 1)) / GW);
     constexpr int dwords = DPL * 16;                                  // Dp / 2 words per direction per column (Dp = 32 * DPL)
-    constexpr int colWords = 3 * dwords + 8;                          // costs of 3 directions, then A[3], pad, B[3], pad (path_info)
-    constexpr int infoOff = 3 * dwords;
-    constexpr int inboxWords = dwords + 4;
-    unsigned* state = smv;                                            // [colsMax][colWords]
-    unsigned* inbox = smv + (size_t)vs.colsMax * colWords;            // [2 parity][NW][2 sides][inboxWords]: costs, A, B, pad
-    const size_t parityStride = (size_t)NW * 2 * inboxWords;
+    constexpr int blk = dwords + 4;                                   // costs, A, B (path_info), 2 pad words
+    constexpr int colWords = 3 * blk;
+    unsigned* const state = (unsigned*)smv3;                          // [colsMax][3 directions][blk]
+    unsigned* const inbox = state + (size_t)vs.colsMax * colWords;    // [2 parity][NW][2 sides][blk]
+    const size_t parityStride = (size_t)NW * 2 * blk;
     unsigned long long* bars = (unsigned long long*)(inbox + 2 * parityStride);
-    unsigned A0, B0;
-    path_info<NN>(0, P2, A0, B0);                                     // the zero state: minimum 0
-    for (int i = threadIdx.x; i < vs.colsMax * colWords; i += NT) {
-        const int w = i % colWords;
-        unsigned v;
-        if (w < infoOff) v = ((w % dwords) * 2 < D) ? 0u : 0x7fff7fffu;
-        else v = (w - infoOff < 3) ? A0 : ((w - infoOff >= 4 && w - infoOff < 7) ? B0 : 0u);
-        state[i] = v;
-    }
-    for (int i = threadIdx.x; i < 2 * NW * 2 * inboxWords; i += NT) {
-        const int w = i % inboxWords;
-        inbox[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : (w == dwords ? A0 : (w == dwords + 1 ? B0 : 0u));
+    {
+        unsigned A0, B0;
+        path_info<NN>(0, P2, A0, B0);                                 // the zero state: all costs 0 (padding: MAX_COST), minimum 0
+        const int nwords = (vs.colsMax * 3 + 2 * NW * 2) * blk;       // state and inboxes are one run of blocks
+        for (int i = threadIdx.x; i < nwords; i += NT) {
+            const int w = i % blk;
+            state[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : (w == dwords ? A0 : (w == dwords + 1 ? B0 : 0u));
+        }
     }
     if (threadIdx.x < 2 * NW * 2) mbar_init(smem_u32(bars + threadIdx.x), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     bool exact = flags[b] != 0;
-    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s);
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s); k.Z = (unsigned)p.D >> 20; CVR_PIN(k.Z);   // 0 (D < 2^15), but not a compile-time constant
     CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
     constexpr size_t colW = (size_t)dwords;
     const unsigned edgeBytes = 32u * NWD * 4u + 8u;                   // 32 lanes x NWD words + A + B
-    const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * inboxWords;
-    const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * inboxWords;
+    const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * blk;
+    const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * blk;
     const unsigned myBarL = smem_u32(bars + (size_t)warp * 2 + 0), myBarR = smem_u32(bars + (size_t)warp * 2 + 1);
     const unsigned barParityStride = (unsigned)(NW * 2 * 8), inboxParityBytes = (unsigned)(parityStride * 4);
     const bool hasL = gw > 0, hasR = gw + 1 < GW;
     unsigned pushR_data = 0, pushR_bar = 0, pushL_data = 0, pushL_bar = 0;
     if (hasR) {
         const int r2 = (gw + 1) / NW, w2 = (gw + 1) % NW;
-        pushR_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 0) * inboxWords), r2);
+        pushR_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 0) * blk), r2);
         pushR_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 0), r2);
     }
     if (hasL) {
         const int r2 = (gw - 1) / NW, w2 = (gw - 1) % NW;
-        pushL_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 1) * inboxWords), r2);
+        pushL_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 1) * blk), r2);
         pushL_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 1), r2);
     }
     unsigned* const colBase0 = state + (size_t)(a - ctaFirst) * colWords;
@@ -600,111 +721,47 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     const unsigned* rowC = (const unsigned*)C + rb0;                  // this lane's words of column a in the current row
     unsigned* rowS = (unsigned*)S + rb0;
     const int ncols = e - a;
-    unsigned cN[NWD], sN[NWD];
-    ldw<NWD>(rowC, cN);
-    ldw<NWD>(rowS, sN);
+    V3Ctx x;
+    x.lane = lane; x.D = D; x.P2 = P2; x.ncols = ncols; x.b = b; x.a = a; x.W1 = W1; x.storeS = storeS; x.hasL = hasL; x.hasR = hasR;
+    x.nextRow = nextRow; x.frameRow0 = frameRow0; x.raw = raw; x.aux = aux; x.flags = flags; x.k = k;
+    unsigned cA[NWD], sA[NWD], cB[NWD], sB[NWD];                       // C and S words of the current / the next column (roles alternate)
+    ldw<NWD>(rowC, cA);
+    ldw<NWD>(rowS, sA);
     for (int t = 0; t < H; t++, rowC += nextRow, rowS += nextRow) {
         const int y = UP ? H - 1 - t : t;
         const int rd = (t + 1) & 1, wr = t & 1;
-        const unsigned* Cp = rowC;
-        unsigned* Sp = rowS;
         if (t > 0) {                                                   // previous row's edges of both neighbours
             const unsigned waitPhase = (unsigned)(((t - 1) >> 1) & 1);
             if (lane == 0) {
                 if (hasL) mbar_arrive_expect_tx(myBarL + rd * barParityStride, edgeBytes);
                 if (hasR) mbar_arrive_expect_tx(myBarR + rd * barParityStride, edgeBytes);
             }
-            __syncwarp();
+            __syncwarp();                                              // also: the info words lanes 0..2 wrote in the previous row
             if (hasL) mbar_wait(myBarL + rd * barParityStride, waitPhase);
             if (hasR) mbar_wait(myBarR + rd * barParityStride, waitPhase);
         }
-        // sources that come from the neighbours (read before anything is pushed in this row)
-        unsigned carry[NWD], edgeR[NWD];
-        const unsigned* inL = myInL + rd * parityStride;
-        const unsigned* inR = myInR + rd * parityStride;
-        ldw<NWD>(inL + lane * NWD, carry);
-        unsigned carryA = inL[dwords], carryB = inL[dwords + 1];
-        ldw<NWD>(inR + lane * NWD, edgeR);
-        const unsigned edgeRA = inR[dwords], edgeRB = inR[dwords + 1];
-        unsigned* cb = colBase0;                                       // base of the current column's record
-        for (int ci = 0; ci < ncols; ci++, cb += colWords, Cp += colW, Sp += colW) {
-            unsigned* col = cb + lane * NWD;
-            unsigned c[NWD], s[NWD], s0[NWD];
+        const unsigned* inL = myInL + rd * parityStride;               // filled by the neighbours in the previous row; this row's
+        const unsigned* inR = myInR + rd * parityStride;               // pushes go to the other parity
+        x.y = y; x.moreRows = t + 1 < H; x.inR = inR; x.rowC = rowC; x.rowS = rowS;
+        x.pushL_dst = pushL_data + wr * inboxParityBytes; x.pushL_bar = pushL_bar + wr * barParityStride;
+        x.pushR_dst = pushR_data + wr * inboxParityBytes; x.pushR_bar = pushR_bar + wr * barParityStride;
+        unsigned kA[NWD], kB[NWD];                                     // the carried down-right block (costs) ...
+        uint2 kiA, kiB;                                                // ... and its (A, B)
+        ldw<NWD>(inL + lane * NWD, kA);
+        kiA = *(const uint2*)(inL + dwords);
+
+        unsigned* cb = colBase0;                                       // base of the current column's blocks
+        const unsigned* Cp = rowC;
+        unsigned* Sp = rowS;
+        int ci = 0;
+        for (; ci + 2 <= ncols; ci += 2, cb += 2 * colWords, Cp += 2 * colW, Sp += 2 * colW) {
+            v3_column<NWD, 2, 0, WTA, HASPAD, NN, blk, dwords>(x, p, exact, ci, cb, Cp, Sp, cA, sA, cB, sB, kA, kiA, kB, kiB);
+            v3_column<NWD, 0, 2, WTA, HASPAD, NN, blk, dwords>(x, p, exact, ci + 1, cb + colWords, Cp + colW, Sp + colW, cB, sB, cA, sA, kB, kiB, kA, kiA);
+        }
+        if (ci < ncols) {                                              // odd chunk: one more column, then hand the prefetched words back
+            v3_column<NWD, 2, 1, WTA, HASPAD, NN, blk, dwords>(x, p, exact, ci, cb, Cp, Sp, cA, sA, cB, sB, kA, kiA, kB, kiB);
 #pragma unroll
-            for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = s0[j] = sN[j]; }
-            const bool lastCol = (ci + 1 == ncols);
-            if (!lastCol) { ldw<NWD>(Cp + colW, cN); ldw<NWD>(Sp + colW, sN); }
-            else if (t + 1 < H) { ldw<NWD>(rowC + nextRow, cN); ldw<NWD>(rowS + nextRow, sN); }   // next row's first column
-            // ---- sources: everything is read before this column's record is overwritten ----
-            unsigned Lp1[NWD], Lp2[NWD], Lp3[NWD], L1[NWD], L2[NWD], L3[NWD];
-#pragma unroll
-            for (int j = 0; j < NWD; j++) Lp1[j] = carry[j];
-            const unsigned A1 = carryA, B1 = carryB;
-            ldw<NWD>(col, carry);                                      // old down-right costs of this column: next column's source
-            carryA = cb[infoOff + 0]; carryB = cb[infoOff + 4];
-            ldw<NWD>(col + dwords, Lp2);
-            const unsigned A2 = cb[infoOff + 1], B2 = cb[infoOff + 5];
-            unsigned A3, B3;
-            if (!lastCol) { ldw<NWD>(col + colWords + 2 * dwords, Lp3); A3 = cb[colWords + infoOff + 2]; B3 = cb[colWords + infoOff + 6]; }
-            else {
-#pragma unroll
-                for (int j = 0; j < NWD; j++) Lp3[j] = edgeR[j];
-                A3 = edgeRA; B3 = edgeRB;
-            }
-            int mn1, mn2, mn3;
-            const bool fastCol = !exact && (int)(B1 | B2 | B3) >= 0;
-            if (fastCol) {                                             // the common case: one straight-line block for all three directions
-                const int m1 = col_fast<NWD, HASPAD, NN>(Lp1, A1, c, L1, lane, D, k);
-                const int m2 = col_fast<NWD, HASPAD, NN>(Lp2, A2, c, L2, lane, D, k);
-                const int m3 = col_fast<NWD, HASPAD, NN>(Lp3, A3, c, L3, lane, D, k);
-                mn1 = __reduce_min_sync(0xffffffffu, m1);
-                mn2 = __reduce_min_sync(0xffffffffu, m2);
-                mn3 = __reduce_min_sync(0xffffffffu, m3);
-                acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3);
-            } else {
-                const int d1 = (int)(short)(B1 & 0xffffu), d2 = (int)(short)(B2 & 0xffffu), d3 = (int)(short)(B3 & 0xffffu);
-                int m1, m2, m3;
-                if (!exact) {
-                    m1 = col_general<NWD, false, HASPAD>(Lp1, d1, c, L1, lane, D, k);
-                    m2 = col_general<NWD, false, HASPAD>(Lp2, d2, c, L2, lane, D, k);
-                    m3 = col_general<NWD, false, HASPAD>(Lp3, d3, c, L3, lane, D, k);
-                } else {
-                    m1 = col_general<NWD, true, HASPAD>(Lp1, d1, c, L1, lane, D, k);
-                    m2 = col_general<NWD, true, HASPAD>(Lp2, d2, c, L2, lane, D, k);
-                    m3 = col_general<NWD, true, HASPAD>(Lp3, d3, c, L3, lane, D, k);
-                }
-                mn1 = __reduce_min_sync(0xffffffffu, m1);
-                mn2 = __reduce_min_sync(0xffffffffu, m2);
-                mn3 = __reduce_min_sync(0xffffffffu, m3);
-                acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);   // valid for any signs
-            }
-            if (min(min(mn1, mn2), mn3) < 0) {                         // a negative path cost: the unsigned fast sums are void, stay exact from here on
-                if (fastCol) {
-#pragma unroll
-                    for (int j = 0; j < NWD; j++) s[j] = s0[j];
-                    acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);
-                }
-                exact = true;
-                if (lane == 0) atomicOr(&flags[b], 2);
-            }
-            stw<NWD>(col, L1); stw<NWD>(col + dwords, L2); stw<NWD>(col + 2 * dwords, L3);
-            // lanes 0..2 derive what the next pixel on each path needs from this pixel's minimum
-            unsigned iA, iB;
-            path_info<NN>(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3), P2, iA, iB);
-            if (lane < 3) { cb[infoOff + lane] = iA; cb[infoOff + 4 + lane] = iB; }
-            if (ci == 0 && hasL) {                                     // my first column's down-left costs -> left neighbour's right inbox
-                const unsigned dst = pushL_data + wr * inboxParityBytes, bar = pushL_bar + wr * barParityStride;
-                st_async_words<NWD>(dst + lane * NWD * 4, L3, bar);
-                if (lane == 2) { st_async_b32(dst + dwords * 4, iA, bar); st_async_b32(dst + dwords * 4 + 4, iB, bar); }
-            }
-            if (lastCol && hasR) {                                     // my last column's down-right costs -> right neighbour's left inbox
-                const unsigned dst = pushR_data + wr * inboxParityBytes, bar = pushR_bar + wr * barParityStride;
-                st_async_words<NWD>(dst + lane * NWD * 4, L1, bar);
-                if (lane == 0) { st_async_b32(dst + dwords * 4, iA, bar); st_async_b32(dst + dwords * 4 + 4, iB, bar); }
-            }
-            if (!WTA || storeS) stw<NWD>(Sp, s);
-            if (WTA) wta_column2<NWD>(s, lane, p, raw + (frameRow0 + y) * p.W + a + ci + p.minX1, aux + (frameRow0 + y) * W1 + a + ci);
-            __syncwarp();                                              // the info words written by lanes 0..2 are read by all lanes in the next row
+            for (int j = 0; j < NWD; j++) { cA[j] = cB[j]; sA[j] = sB[j]; }
         }
     }
     cluster.sync();                                                   // nobody exits while a neighbour may still write into its inbox

@@ -637,7 +637,7 @@ struct VCfg { bool ok; int CL, NT; VState vs; size_t smem; };
 static size_t vcfg_smem(const SgbmDev& p, int CL, int NT, VState* vs)
 {
     const int NW = NT / 32;
-    vs->colsMax = (p.W1 + CL - 1) / CL + 1; vs->colWords = 3 * p.Dp / 2 + 8; vs->inboxWords = p.Dp / 2 + 4;
+    vs->colsMax = (p.W1 + CL - 1) / CL + 1; vs->colWords = 3 * (p.Dp / 2 + 4); vs->inboxWords = p.Dp / 2 + 4;
     return 4 * ((size_t)vs->colsMax * vs->colWords + (size_t)2 * NW * 2 * vs->inboxWords) + (size_t)2 * NW * 2 * 8;
 }
 
