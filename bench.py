@@ -195,6 +195,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=104, help="frames per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--rectify", action="store_true", help="side measurement: config requires_rectification = true (RectifyImages on the device before the matcher)")
     ap.add_argument("--matcher", default="sgbm", choices=["sgbm", "bm"], help="sgbm = the headline path; bm = the reference's other block matcher (side measurement)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -219,7 +220,15 @@ def main():
     cfg = cvr.parse_config(None)
     if args.matcher == "bm":
         cfg["block_matcher"] = cvr.MATCHER_BM
+    cfg["requires_rectification"] = bool(args.rectify)
     rec = cvr.Reconstruct3D(W, H, config=cfg, max_batch=B, device=local)   # defaults = config_default.json SGBM/SBM sections, leaf 0.2, SOR 30/0.5
+    if args.rectify:                                                   # a KITTI-like raw calibration (5 distortion terms, small rotation)
+        K = np.array([[959.791, 0, 696.0217], [0, 956.9251, 224.1806], [0, 0, 1]])
+        Dk = [-0.3728755, 0.2037299, 0.002219027, 0.001383707, -0.07233722]
+        a = 0.009
+        Rr = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
+        Pp = np.array([[880.0, 0, 660.0, 0], [0, 880.0, 200.0, 0], [0, 0, 1, 0]])
+        rec.SetRectification(K, Dk, Rr, Pp, K, Dk, Rr, Pp)
     Ls, Rs = make_pairs(UNIQUE_PAIRS)
     idx = [(rank * B + i) % UNIQUE_PAIRS for i in range(B)]            # frame_id sharding; the pool of unique pairs is cycled
     hL = torch.from_numpy(Ls[idx]).pin_memory(); hR = torch.from_numpy(Rs[idx]).pin_memory()
@@ -343,7 +352,7 @@ def main():
             "metric": "stereo frames/sec (SGBM->cloud->filter)", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int16", "data": "synthetic (%d unique seeded pairs cycled)" % UNIQUE_PAIRS,
-            "config": {"workload": WORKLOAD, "frames_per_gpu_per_step": B, "l2": "inputs larger than L2: working set per step (cost volumes 214 MB/frame x batch) >> 126 MB L2",
+            "config": {"workload": WORKLOAD + (" + RectifyImages (requires_rectification)" if args.rectify else ""), "frames_per_gpu_per_step": B, "l2": "inputs larger than L2: working set per step (cost volumes 214 MB/frame x batch) >> 126 MB L2",
                        "parallelism": "frames sharded, dp%d, NCCL gather of filtered clouds to rank 0" % world},
             "e2e": {"value": e2e_v, "unit": "frames/s", "h2d_bytes_per_step": 2 * frame_bytes * B, "d2h_bytes_per_step": int(counts.sum()) * 16 + 4 * B,
                     "ms_per_step": ms_e2e / args.steps},

@@ -89,6 +89,9 @@ typedef struct cvr_params {
     int   bm_uniqueness_ratio;  /* 15 */
     int   bm_speckle_window_size; /* 0 = off */
     int   bm_speckle_range;     /* 0 */
+    /* config.json "requires_rectification" (ConfigParser.cpp:39; ReconstructionSystem.cpp:42-44): 1 => every batch is
+     * rectified with the maps of cvr_set_rectification before the matcher, and the rectified left image colours the cloud. */
+    int   requires_rectification;
 } cvr_params;
 
 typedef struct cvr_point {      /* 16 bytes */
@@ -113,6 +116,22 @@ const char* cvr_version(void);
  * cv::cvtColor) or 1 (already gray).  Host pointers. */
 int cvr_disparity(cvr_ctx* ctx, const uint8_t* left, size_t step_left, const uint8_t* right, size_t step_right,
                   int channels, int16_t* disp, size_t step_disp);
+
+/* Replaces: the two cv::initUndistortRectifyMap(K, D, R, P, size, CV_16SC2, map1, map2) calls of
+ * Reconstruct3D::RectifyImages (Reconstruct3D.cpp:351-356), done once per calibration instead of once per frame.
+ * K: 3x3 row-major camera matrix; D: n_dist (0, 4, 5, 8 or 12) distortion coefficients k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4
+ * (the tilt terms of 14-coefficient vectors are not supported); R: 3x3 rectification rotation; P: 3 x p_cols (3 or 4)
+ * row-major projection matrix.  Camera 1 = left, 2 = right.  Builds the four maps on the device. */
+int cvr_set_rectification(cvr_ctx* ctx, const double* K1, const double* D1, int n_dist1, const double* R1, const double* P1, int p1_cols,
+                          const double* K2, const double* D2, int n_dist2, const double* R2, const double* P2, int p2_cols);
+
+/* Replaces: Reconstruct3D::RectifyImages (Reconstruct3D.cpp:330-361): cv::remap(image, rectified, map1, map2,
+ * INTER_LINEAR) for both images of one stereo pair (constant border 0).  Host pointers; channels = 1, 3 or 4. */
+int cvr_rectify(cvr_ctx* ctx, int channels, const uint8_t* left, size_t step_left, const uint8_t* right, size_t step_right,
+                uint8_t* rect_left, size_t step_rect_left, uint8_t* rect_right, size_t step_rect_right);
+
+/* Test hook: copies the maps of one camera (0 = left, 1 = right) to the host: map1 = H*W*2 int16, map2 = H*W uint16. */
+int cvr_get_rectification_maps(cvr_ctx* ctx, int camera, int16_t* map1, uint16_t* map2);
 
 /* Replaces: TrackingFrame::SetupFrame + PruneDisparityImage (TrackingFrame.cpp:25-67).
  * disp is pruned in place; disp_f32 (CV_32F, tight W*4 step) and mask (CV_8U, tight) are outputs

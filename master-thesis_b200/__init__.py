@@ -34,6 +34,7 @@ EXPORTS = [
     "cvr_reproject_cloud", "cvr_triangulate", "cvr_voxel_grid", "cvr_sor", "cvr_process_batch", "cvr_points_to_pcl",
     "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling", "cvr_prune_noalloc",
     "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
+    "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps",
 ]
 
 
@@ -51,7 +52,7 @@ class Params(C.Structure):
         ("sor_stddev_mul", C.c_double), ("max_batch", C.c_int), ("cloud_mode", C.c_int), ("max_points", C.c_int),
         ("filter_only", C.c_int), ("block_matcher", C.c_int), ("bm_window_size", C.c_int), ("bm_num_disparities", C.c_int),
         ("bm_min_disparity", C.c_int), ("bm_pre_filter_cap", C.c_int), ("bm_texture_threshold", C.c_int), ("bm_uniqueness_ratio", C.c_int),
-        ("bm_speckle_window_size", C.c_int), ("bm_speckle_range", C.c_int),
+        ("bm_speckle_window_size", C.c_int), ("bm_speckle_range", C.c_int), ("requires_rectification", C.c_int),
     ]
 
 
@@ -110,6 +111,9 @@ def load_library():
     lib.cvr_process_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(Batch)]
     lib.cvr_radius_outlier_removal.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     lib.cvr_transform_cloud.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    lib.cvr_set_rectification.argtypes = [C.c_void_p] + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int] * 2
+    lib.cvr_rectify.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
+    lib.cvr_get_rectification_maps.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
     lib.cvr_submit_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(Batch)]
     lib.cvr_wait_batch.argtypes = [C.c_void_p]
     lib.cvr_debug_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -156,7 +160,8 @@ def parse_config(path_or_dict=None):
     s = rec["SGBM"]
     sbm = rec.get("SBM", {"window_size": 21, "num_disparities": 16})
     pp = cfg["config"].get("point_cloud_post_processing", {})
-    return dict(block_matcher=MATCHER_BM if bm else MATCHER_SGBM, window_size=int(sbm["window_size"]),
+    return dict(requires_rectification=bool(rec.get("requires_rectification", False)),       # ConfigParser.cpp:39
+                block_matcher=MATCHER_BM if bm else MATCHER_SGBM, window_size=int(sbm["window_size"]),
                 bm_num_disparities=int(sbm["num_disparities"]), block_size=int(s["block_size"]), num_disparities=int(s["num_disparities"]),
                 uniqueness_ratio=int(s["uniqueness_ratio"]), speckle_range=int(s["speckle_range"]),
                 speckle_window_size=int(s["speckle_window_size"]), pre_filter_cap=int(s["pre_filter_cap"]),
@@ -218,6 +223,7 @@ class Reconstruct3D:
             if k_ in cfg:
                 setattr(p, k_, int(cfg[k_]))
         p.filter_only = int(bool(filter_only))
+        p.requires_rectification = int(bool(cfg.get("requires_rectification", False)))
         self.params = p
         self.Q = Qm
         self.W, self.H = int(width), int(height)
@@ -254,6 +260,39 @@ class Reconstruct3D:
         ms = (C.c_float * 64)()
         n = self.lib.cvr_last_timings(self.ctx, names, ms, 64)
         return [(names[i].decode(), float(ms[i])) for i in range(n)]
+
+    # -- Reconstruct3D::RectifyImages (Reconstruct3D.cpp:330-361) --
+    def SetRectification(self, K1, D1, R1, P1, K2, D2, R2, P2):
+        """The calibration RectifyImages reads from m_StereoCameraSetup (K, D per camera; Rectification.RL/RR/PL/PR):
+        builds the CV_16SC2 maps of both cameras on the device, once."""
+        def prep(K, D, R, P):
+            K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
+            D = np.ascontiguousarray(np.asarray(D, np.float64).ravel())
+            R = np.ascontiguousarray(R, np.float64).reshape(3, 3)
+            P = np.ascontiguousarray(P, np.float64)
+            P = P.reshape(3, -1)
+            return K, D, R, P
+        a, b = prep(K1, D1, R1, P1), prep(K2, D2, R2, P2)
+        self._rect_keep = (a, b)
+        args = []
+        for K, D, R, P in (a, b):
+            args += [_ptr(K), _ptr(D) if D.size else None, int(D.size), _ptr(R), _ptr(P), int(P.shape[1])]
+        self._check(self.lib.cvr_set_rectification(self.ctx, *args))
+
+    def RectifyImages(self, leftImage, rightImage):
+        l = np.ascontiguousarray(leftImage, np.uint8)
+        r = np.ascontiguousarray(rightImage, np.uint8)
+        ch = 1 if l.ndim == 2 else l.shape[2]
+        ol, orr = np.empty_like(l), np.empty_like(r)
+        step = self.W * ch
+        self._check(self.lib.cvr_rectify(self.ctx, ch, _ptr(l), step, _ptr(r), step, _ptr(ol), step, _ptr(orr), step))
+        return ol, orr
+
+    def rectification_maps(self, camera):
+        m1 = np.empty((self.H, self.W, 2), np.int16)
+        m2 = np.empty((self.H, self.W), np.uint16)
+        self._check(self.lib.cvr_get_rectification_maps(self.ctx, int(camera), _ptr(m1), _ptr(m2)))
+        return m1, m2
 
     # -- Reconstruct3D::GenerateDisparityMap (Reconstruct3D.cpp:72-84) --
     def GenerateDisparityMap(self, leftImage, rightImage):

@@ -34,6 +34,7 @@ extern "C" void cvr_default_params(cvr_params* p, int width, int height)
     // named by the north star) + cv::StereoBM::create(16, 21) defaults
     p->block_matcher = CVR_MATCHER_SGBM; p->bm_window_size = 27; p->bm_num_disparities = 128; p->bm_min_disparity = 0;
     p->bm_pre_filter_cap = 31; p->bm_texture_threshold = 10; p->bm_uniqueness_ratio = 15; p->bm_speckle_window_size = 0; p->bm_speckle_range = 0;
+    p->requires_rectification = 0;
 }
 
 void cvr_stage_mark(cvr_ctx* c, const char* name)
@@ -151,7 +152,8 @@ static void free_all(cvr_ctx* c)
     void* ptrs[] = { c->d_in[0], c->d_in[1], c->d_gray, c->d_volA, c->d_volC, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, c->d_disp, c->d_med,
                      c->d_label, c->d_size, c->d_pruned, c->d_dispf, c->d_mask, c->d_pstats, c->d_rowcnt, c->d_cloud, c->d_ncloud, c->d_vhdr,
                      c->d_keys[0], c->d_keys[1], c->d_vals[0], c->d_vals[1], c->d_hist, c->d_segstart, c->d_vox, c->d_cellstart, c->d_cellidx,
-                     c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags, c->d_bmpre };
+                     c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags, c->d_bmpre,
+                     c->d_rmap1[0], c->d_rmap1[1], c->d_rmap2[0], c->d_rmap2[1], c->d_rect[0], c->d_rect[1] };
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->pipe_ready) {
@@ -280,6 +282,73 @@ extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const u
     rc = sync_check(c);
     timers_end(c);
     return rc;
+}
+
+static int rect_alloc(cvr_ctx* c)
+{
+    const size_t HW = (size_t)c->prm.width * c->prm.height;
+    for (int cam = 0; cam < 2; cam++) {
+        if (!c->d_rmap1[cam]) CVR_CUDA(c, dalloc(&c->d_rmap1[cam], HW));
+        if (!c->d_rmap2[cam]) CVR_CUDA(c, dalloc(&c->d_rmap2[cam], HW));
+        if (!c->d_rect[cam]) CVR_CUDA(c, dalloc(&c->d_rect[cam], (size_t)c->maxB * HW * 4));
+    }
+    return CVR_OK;
+}
+
+extern "C" int cvr_set_rectification(cvr_ctx* c, const double* K1, const double* D1, int nD1, const double* R1, const double* P1, int p1c,
+                                     const double* K2, const double* D2, int nD2, const double* R2, const double* P2, int p2c)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    REQUIRE(c, K1 && R1 && P1 && K2 && R2 && P2, "null calibration matrix");
+    REQUIRE(c, (p1c == 3 || p1c == 4) && (p2c == 3 || p2c == 4), "P must have 3 or 4 columns");
+    REQUIRE(c, nD1 >= 0 && nD2 >= 0 && (nD1 == 0 || D1) && (nD2 == 0 || D2), "bad distortion vector");
+    if (nD1 > 12 || nD2 > 12) { c->err = "distortion vectors with tilt terms (more than 12 coefficients) are not supported"; return CVR_ERR_UNSUPPORTED; }
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    int rc = rect_alloc(c);
+    if (rc) return rc;
+    c->rect_ready = false;
+    rc = cvr_launch_rectify_maps(c, 0, K1, D1, nD1, R1, P1, p1c);
+    if (rc) return rc;
+    rc = cvr_launch_rectify_maps(c, 1, K2, D2, nD2, R2, P2, p2c);
+    if (rc) return rc;
+    rc = sync_check(c);
+    if (rc) return rc;
+    c->rect_ready = true;
+    return CVR_OK;
+}
+
+extern "C" int cvr_get_rectification_maps(cvr_ctx* c, int cam, int16_t* map1, uint16_t* map2)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    REQUIRE(c, c->rect_ready, "cvr_set_rectification was not called");
+    REQUIRE(c, cam == 0 || cam == 1, "camera must be 0 or 1");
+    const size_t HW = (size_t)c->prm.width * c->prm.height;
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    if (map1) CVR_CUDA(c, cudaMemcpy(map1, c->d_rmap1[cam], HW * 4, cudaMemcpyDeviceToHost));
+    if (map2) CVR_CUDA(c, cudaMemcpy(map2, c->d_rmap2[cam], HW * 2, cudaMemcpyDeviceToHost));
+    return CVR_OK;
+}
+
+extern "C" int cvr_rectify(cvr_ctx* c, int ch, const uint8_t* left, size_t sl, const uint8_t* right, size_t sr, uint8_t* outL, size_t sol,
+                           uint8_t* outR, size_t sor_)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    STEREO_ONLY(c);
+    REQUIRE(c, c->rect_ready, "cvr_set_rectification was not called");
+    REQUIRE(c, left && right && outL && outR, "null image pointer");
+    REQUIRE(c, ch == 1 || ch == 3 || ch == 4, "channels must be 1, 3 or 4");
+    const int W = c->sg.W, H = c->sg.H;
+    const size_t rowBytes = (size_t)W * ch;
+    REQUIRE(c, sl >= rowBytes && sr >= rowBytes && sol >= rowBytes && sor_ >= rowBytes, "step smaller than a row");
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], rowBytes, left, sl, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
+    CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], rowBytes, right, sr, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
+    int rc = cvr_launch_remap(c, 1, ch, c->d_in[0], rowBytes, rowBytes * H, c->d_in[1], rowBytes, rowBytes * H, c->d_rect[0], c->d_rect[1], rowBytes, rowBytes * H);
+    if (rc) return rc;
+    CVR_CUDA(c, cudaMemcpy2DAsync(outL, sol, c->d_rect[0], rowBytes, rowBytes, H, cudaMemcpyDeviceToHost, c->stream));
+    CVR_CUDA(c, cudaMemcpy2DAsync(outR, sor_, c->d_rect[1], rowBytes, rowBytes, H, cudaMemcpyDeviceToHost, c->stream));
+    return sync_check(c);
 }
 
 extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, int* w1, int* dp)
@@ -469,7 +538,16 @@ static int enqueue_chain(cvr_ctx* c, int B, int stages, const uint8_t* dl, size_
 {
     const bool wantCloud = (stages & 2) != 0, wantVox = (stages & 4) != 0, wantSor = (stages & 8) != 0;
     *fin = nullptr; *fcnt = nullptr;
-    int rc = cvr_launch_gray(c, B, dl, lstep, lfs, dr, rstep, rfs, ch);
+    int rc;
+    if (c->prm.requires_rectification) {                               // ReconstructionSystem.cpp:42-44: everything downstream sees the rectified pair
+        if (!c->rect_ready) { c->err = "requires_rectification is set but cvr_set_rectification was not called"; return CVR_ERR_INVALID_ARG; }
+        const size_t orow = (size_t)c->sg.W * ch, ofs = orow * c->sg.H;
+        rc = cvr_launch_remap(c, B, ch, dl, lstep, lfs, dr, rstep, rfs, c->d_rect[0], c->d_rect[1], orow, ofs);
+        if (rc) return rc;
+        dl = c->d_rect[0]; dr = c->d_rect[1]; lstep = rstep = orow; lfs = rfs = ofs;
+        cvr_stage_mark(c, "rectify");
+    }
+    rc = cvr_launch_gray(c, B, dl, lstep, lfs, dr, rstep, rfs, ch);
     if (rc) return rc;
     cvr_stage_mark(c, "gray");
     rc = (c->prm.block_matcher == CVR_MATCHER_BM) ? cvr_launch_bm(c, B) : cvr_launch_sgbm(c, B);

@@ -145,6 +145,10 @@ struct cvr_ctx {
     cvr_point* d_sorout;     // [B][H*W]
     int* d_nout;             // [B] final count
     int* d_nvox;             // [B] voxel count
+    short2* d_rmap1[2];      // rectification: CV_16SC2 map per camera [H][W] (cvr_set_rectification)
+    uint16_t* d_rmap2[2];    // rectification: CV_16UC1 fractional map per camera [H][W]
+    uint8_t* d_rect[2];      // rectified left / right images of the current batch [B][H][W*4]
+    bool rect_ready;
     float4* d_spts;          // sor: points sorted by grid cell (w = original index) [B][maxN]
     uint32_t* d_sortidx;     // sor: point order by cell
     int sor_grid_cap;        // max cells per frame
@@ -180,6 +184,10 @@ static inline size_t cvr_div_up_sz(size_t a, size_t b) { return (a + b - 1) / b;
 int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t lfs, const uint8_t* right, size_t rstep,
                     size_t rfs, int channels);
 int cvr_launch_sgbm(cvr_ctx* c, int B);     // gray -> d_med (final disparity)
+// k_rectify.cu: initUndistortRectifyMap (CV_16SC2) for one camera into d_rmap1/2[cam]; remap of B stereo pairs
+int cvr_launch_rectify_maps(cvr_ctx* c, int cam, const double* K, const double* D, int nD, const double* R, const double* P, int pcols);
+int cvr_launch_remap(cvr_ctx* c, int B, int ch, const uint8_t* dl, size_t lstep, size_t lfs, const uint8_t* dr, size_t rstep, size_t rfs,
+                     uint8_t* outL, uint8_t* outR, size_t ostep, size_t ofs);
 int cvr_launch_bm(cvr_ctx* c, int B);       // k_bm.cu: gray -> d_med with StereoBM semantics
 int cvr_launch_speckle(cvr_ctx* c, int B, int newVal, int maxSize, int maxDiff);   // in place on d_med
 // k_cloud.cu

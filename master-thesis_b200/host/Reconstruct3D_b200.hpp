@@ -30,6 +30,13 @@ struct StereoCalib {    // the fields of Camera::Calib::StereoCalib the path rea
     float T0;                   // T(0): baseline
 };
 
+struct RectificationCalib {   // what RectifyImages reads from m_StereoCameraSetup (Reconstruct3D.cpp:333-349), row-major doubles
+    double K1[9], K2[9];       // LeftCameraCalib.K / RightCameraCalib.K
+    std::vector<double> D1, D2;   // distortion coefficients (0, 4, 5, 8 or 12)
+    double R1[9], R2[9];       // Rectification.RL / RR
+    double P1[12], P2[12];     // Rectification.PL / PR (3x4)
+};
+
 enum StereoBlockMatcherType { STEREO_BLOCK_MATCHER = 0, STEREO_SEMI_GLOBAL_BLOCK_MATCHER = 1 };   // Reconstruct3DTypes.hpp:12-15
 
 struct SGBMConfig {     // Config::Reconstruction (Config.hpp:25-45): BlockMatcherType, SBM, SGBM
@@ -77,6 +84,19 @@ public:
     Reconstruct3D(const Reconstruct3D&) = delete;
     Reconstruct3D& operator=(const Reconstruct3D&) = delete;
 
+    // The calibration half of RectifyImages: the reference rebuilds both maps on every call (Reconstruct3D.cpp:351-356); here once.
+    void SetRectification(const RectificationCalib& r)
+    {
+        check(cvr_set_rectification(m_ctx, r.K1, r.D1.data(), static_cast<int>(r.D1.size()), r.R1, r.P1, 4, r.K2, r.D2.data(),
+                                    static_cast<int>(r.D2.size()), r.R2, r.P2, 4));
+    }
+    // void RectifyImages(const cv::Mat& leftImage, const cv::Mat& rightImage, cv::Mat& rectLeftImage, cv::Mat& rectRightImage) const
+    void RectifyImages(const Mat& leftImage, const Mat& rightImage, Mat& rectLeftImage, Mat& rectRightImage) const
+    {
+        check(cvr_rectify(m_ctx, leftImage.channels, static_cast<const uint8_t*>(leftImage.data), leftImage.step,
+                          static_cast<const uint8_t*>(rightImage.data), rightImage.step, static_cast<uint8_t*>(rectLeftImage.data),
+                          rectLeftImage.step, static_cast<uint8_t*>(rectRightImage.data), rectRightImage.step));
+    }
     // cv::Mat GenerateDisparityMap(const cv::Mat& leftImage, const cv::Mat& rightImage) const  -> CV_16SC1 rows x cols
     std::vector<int16_t> GenerateDisparityMap(const Mat& leftImage, const Mat& rightImage) const
     {

@@ -684,3 +684,92 @@ void orc_transform_cloud(const orc_point* in, int n, const float* T /*4x4 row-ma
         out[i] = p;
     }
 }
+
+/* ------------------------------------------------------------------------------------------------
+ * Stereo rectification of the input images: Reconstruct3D::RectifyImages
+ * (cv_reconstruct/src/reconstruct/Reconstruct3D.cpp:330-361) =
+ *   cv::initUndistortRectifyMap(K, D, R, P, size, CV_16SC2, map1, map2)  for each camera, then
+ *   cv::remap(image, rectified, map1, map2, cv::INTER_LINEAR)            (BORDER_CONSTANT, value 0).
+ * OpenCV is a third-party dependency of the reference (4.x; pinned here against cv2 4.13.0 by
+ * tests/golden/rect_*.npz).  Restated from its published algorithm:
+ *   - iR = inverse(P[:, :3] * R) by the 3x3 closed form (adjugate times 1/det), all in double;
+ *   - per row i the homogeneous coordinate starts at (i*ir1 + ir2, i*ir4 + ir5, i*ir7 + ir8) and is advanced by
+ *     REPEATED ADDITION of (ir0, ir3, ir6) per column (the running sums are part of the result's rounding);
+ *   - radial/tangential/thin-prism distortion with up to 12 coefficients (k1 k2 p1 p2 k3 k4 k5 k6 s1 s2 s3 s4);
+ *     the tilt model (tauX, tauY) of 14-coefficient vectors is not restated (identity), callers must pass <= 12;
+ *   - fixed point: iu = round_half_even(u * 32), map1 = (iu >> 5, iv >> 5) as int16, map2 = (iv & 31) * 32 + (iu & 31).
+ * remap, 8-bit, bilinear: weights w = {(32-fx)(32-fy), fx(32-fy), (32-fx)fy, fx*fy} * 32 (sum 2^15; the float table
+ * OpenCV builds is exact for these values), result = (sum w_i * S_i + 2^14) >> 15; a tap outside the image reads 0.
+ */
+static void orc_inv3(const double* S, double* t)
+{
+    double d = S[0] * (S[4] * S[8] - S[5] * S[7]) - S[1] * (S[3] * S[8] - S[5] * S[6]) + S[2] * (S[3] * S[7] - S[4] * S[6]);
+    if (d != 0.0) d = 1. / d;
+    t[0] = (S[4] * S[8] - S[5] * S[7]) * d;
+    t[1] = (S[2] * S[7] - S[1] * S[8]) * d;
+    t[2] = (S[1] * S[5] - S[2] * S[4]) * d;
+    t[3] = (S[5] * S[6] - S[3] * S[8]) * d;
+    t[4] = (S[0] * S[8] - S[2] * S[6]) * d;
+    t[5] = (S[2] * S[3] - S[0] * S[5]) * d;
+    t[6] = (S[3] * S[7] - S[4] * S[6]) * d;
+    t[7] = (S[1] * S[6] - S[0] * S[7]) * d;
+    t[8] = (S[0] * S[4] - S[1] * S[3]) * d;
+}
+
+/* the nine doubles the per-pixel loop needs: inverse(P3x3 * R).  P has row pitch pstride (3 or 4). */
+void orc_rectify_inverse(const double* R, const double* P, int pstride, double* ir)
+{
+    double M[9];
+    for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++) M[i * 3 + j] = P[i * pstride + 0] * R[0 * 3 + j] + P[i * pstride + 1] * R[1 * 3 + j] + P[i * pstride + 2] * R[2 * 3 + j];
+    orc_inv3(M, ir);
+}
+
+static inline int orc_round_half_even(double v) { return (int)lrint(v); }
+
+void orc_init_undistort_rectify_map(const double* K, const double* D, int nD, const double* R, const double* P, int pstride, int W, int H,
+                                    int16_t* map1 /* H*W*2 */, uint16_t* map2 /* H*W */)
+{
+    double ir[9], k[12] = { 0 };
+    for (int i = 0; i < nD && i < 12; i++) k[i] = D[i];
+    orc_rectify_inverse(R, P, pstride, ir);
+    const double u0 = K[2], v0 = K[5], fx = K[0], fy = K[4];
+    const double k1 = k[0], k2 = k[1], p1 = k[2], p2 = k[3], k3 = k[4], k4 = k[5], k5 = k[6], k6 = k[7], s1 = k[8], s2 = k[9], s3 = k[10], s4 = k[11];
+    for (int i = 0; i < H; i++) {
+        double _x = i * ir[1] + ir[2], _y = i * ir[4] + ir[5], _w = i * ir[7] + ir[8];
+        for (int j = 0; j < W; j++, _x += ir[0], _y += ir[3], _w += ir[6]) {
+            double w = 1. / _w, x = _x * w, y = _y * w;
+            double x2 = x * x, y2 = y * y;
+            double r2 = x2 + y2, _2xy = 2 * x * y;
+            double kr = (1 + ((k3 * r2 + k2) * r2 + k1) * r2) / (1 + ((k6 * r2 + k5) * r2 + k4) * r2);
+            double xd = (x * kr + p1 * _2xy + p2 * (r2 + 2 * x2) + s1 * r2 + s2 * r2 * r2);
+            double yd = (y * kr + p1 * (r2 + 2 * y2) + p2 * _2xy + s3 * r2 + s4 * r2 * r2);
+            double u = fx * xd + u0;                    /* identity tilt: vecTilt = (xd, yd, 1), invProj = 1 */
+            double v = fy * yd + v0;
+            int iu = orc_round_half_even(u * 32), iv = orc_round_half_even(v * 32);
+            map1[((size_t)i * W + j) * 2 + 0] = (int16_t)(iu >> 5);
+            map1[((size_t)i * W + j) * 2 + 1] = (int16_t)(iv >> 5);
+            map2[(size_t)i * W + j] = (uint16_t)((iv & 31) * 32 + (iu & 31));
+        }
+    }
+}
+
+void orc_remap_bilinear_u8(const uint8_t* src, size_t sstep, int sw, int sh, int cn, const int16_t* map1, const uint16_t* map2, int W, int H,
+                           uint8_t* dst, size_t dstep)
+{
+    for (int y = 0; y < H; y++)
+        for (int x = 0; x < W; x++) {
+            const int sx = map1[((size_t)y * W + x) * 2], sy = map1[((size_t)y * W + x) * 2 + 1];
+            const int f = map2[(size_t)y * W + x] & 1023, fx = f & 31, fy = f >> 5;
+            const int w[4] = { (32 - fx) * (32 - fy) * 32, fx * (32 - fy) * 32, (32 - fx) * fy * 32, fx * fy * 32 };
+            for (int c = 0; c < cn; c++) {
+                int acc = 0;
+                for (int t = 0; t < 4; t++) {
+                    const int xx = sx + (t & 1), yy = sy + (t >> 1);
+                    const int s = (xx >= 0 && xx < sw && yy >= 0 && yy < sh) ? src[(size_t)yy * sstep + (size_t)xx * cn + c] : 0;
+                    acc += s * w[t];
+                }
+                dst[(size_t)y * dstep + (size_t)x * cn + c] = (uint8_t)((acc + (1 << 14)) >> 15);
+            }
+        }
+}

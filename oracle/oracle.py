@@ -213,6 +213,42 @@ def sor(pts, k, alpha):
     return out[:m].copy(), dist[:n].copy(), thr.value, keep[:n].copy()
 
 
+def rectify_inverse(R, P):
+    """inverse(P[:, :3] @ R) as initUndistortRectifyMap computes it (3x3 closed form in double)."""
+    R = np.ascontiguousarray(R, np.float64).reshape(3, 3)
+    P = np.ascontiguousarray(P, np.float64)
+    P = P.reshape(3, -1)
+    ir = np.empty(9, np.float64)
+    lib().orc_rectify_inverse(_p(R), _p(P), int(P.shape[1]), _p(ir))
+    return ir
+
+
+def init_undistort_rectify_map(K, D, R, P, W, H):
+    """cv::initUndistortRectifyMap(K, D, R, P, (W, H), CV_16SC2): returns (map1 int16 (H, W, 2), map2 uint16 (H, W))."""
+    K = np.ascontiguousarray(K, np.float64).reshape(3, 3)
+    D = np.ascontiguousarray(D, np.float64).ravel()
+    assert D.size <= 12, "the tilt terms (tauX, tauY) are not restated"
+    R = np.ascontiguousarray(R, np.float64).reshape(3, 3)
+    P = np.ascontiguousarray(P, np.float64).reshape(3, -1)
+    m1 = np.empty((H, W, 2), np.int16)
+    m2 = np.empty((H, W), np.uint16)
+    lib().orc_init_undistort_rectify_map(_p(K), _p(D) if D.size else None, int(D.size), _p(R), _p(P), int(P.shape[1]), int(W), int(H), _p(m1), _p(m2))
+    return m1, m2
+
+
+def remap_bilinear(src, map1, map2):
+    """cv::remap(src, map1, map2, INTER_LINEAR) for 8-bit images with CV_16SC2 + CV_16UC1 maps, constant border 0."""
+    src = np.ascontiguousarray(src, np.uint8)
+    sh, sw = src.shape[:2]
+    cn = 1 if src.ndim == 2 else src.shape[2]
+    map1 = np.ascontiguousarray(map1, np.int16)
+    map2 = np.ascontiguousarray(map2, np.uint16)
+    H, W = map2.shape
+    dst = np.empty((H, W) if src.ndim == 2 else (H, W, cn), np.uint8)
+    lib().orc_remap_bilinear_u8(_p(src), C.c_size_t(sw * cn), sw, sh, cn, _p(map1), _p(map2), W, H, _p(dst), C.c_size_t(W * cn))
+    return dst
+
+
 # --------------------------------------------------------------------------------------------
 # Synthetic rectified pair generator (SURVEY.md 8(d)): lives in the package (numpy only, no compute-path code) so
 # that bench.py can synthesise inputs without importing the oracle; re-exported here for the tests.

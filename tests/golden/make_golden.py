@@ -135,7 +135,52 @@ def bm_cases():
         print(name, "valid %.1f%%" % (100 * (disp >= p["minDisparity"] * 16).mean()))
 
 
+# ---- stereo rectification of the inputs: Reconstruct3D::RectifyImages (Reconstruct3D.cpp:330-361) ----
+def _rot(rx, ry, rz):
+    R, _ = cv2.Rodrigues(np.array([rx, ry, rz], np.float64))
+    return R
+
+
+_K_KITTI = np.array([[959.791, 0, 696.0217], [0, 956.9251, 224.1806], [0, 0, 1]], np.float64)   # calib_kitti_rectified.json, left
+RECT_CASES = {   # name: (H, W, channels, K, D, R, P, image seed, keep full arrays)
+    "rect_small_k5": (94, 311, 3, _K_KITTI / np.array([[4.0], [4.0], [1.0]]),
+                      [-0.3728755, 0.2037299, 0.002219027, 0.001383707, -0.07233722], _rot(0.009, -0.004, 0.012),
+                      np.array([[180.4, 0, 152.4, 0], [0, 180.4, 43.2, 0], [0, 0, 1, 0]], np.float64), 31, True),
+    "rect_small_k8_border": (94, 311, 3, _K_KITTI / np.array([[4.0], [4.0], [1.0]]),
+                             [-0.28, 0.09, 0.0011, -0.0007, 0.01, 0.02, -0.01, 0.003], _rot(-0.05, 0.08, -0.03),
+                             np.array([[225.0, 0, 162.5, -100.0], [0, 225.0, 50.0, 0], [0, 0, 1, 0]], np.float64), 32, True),
+    "rect_small_nodist_shift": (80, 300, 1, np.array([[300.0, 0, 150.0], [0, 300.0, 40.0], [0, 0, 1]]), [], np.eye(3),
+                                np.array([[300.0, 0, 143.3], [0, 300.0, 44.7], [0, 0, 1]], np.float64), 33, True),
+    "rect_small_k12": (90, 280, 4, np.array([[240.0, 0, 140.0], [0, 243.0, 45.0], [0, 0, 1]]),
+                       [-0.25, 0.07, 0.0013, -0.0004, 0.012, 0.018, -0.012, 0.002, 0.001, -0.0005, 0.0007, 0.0002], _rot(0.03, 0.02, 0.05),
+                       np.array([[200.0, 0, 150.0], [0, 202.5, 47.5], [0, 0, 1]], np.float64), 34, True),
+    "rect_kitti_k5": (375, 1242, 3, _K_KITTI, [-0.3728755, 0.2037299, 0.002219027, 0.001383707, -0.07233722], _rot(0.009, -0.004, 0.012),
+                      np.array([[721.5377, 0, 609.5593, 0], [0, 721.5377, 172.854, 0], [0, 0, 1, 0]], np.float64), 35, False),
+}
+
+
+def rect_image(H, W, ch, seed):
+    img = np.random.default_rng(seed).integers(0, 256, (H, W, ch), dtype=np.uint8)
+    return img[:, :, 0].copy() if ch == 1 else img
+
+
+def rect_cases():
+    for name, (H, W, ch, K, D, R, P, seed, full) in RECT_CASES.items():
+        D = np.asarray(D, np.float64)
+        m1, m2 = cv2.initUndistortRectifyMap(K, D, R, P, (W, H), cv2.CV_16SC2)
+        img = rect_image(H, W, ch, seed)
+        out = cv2.remap(img, m1, m2, cv2.INTER_LINEAR)
+        d = dict(K=K, D=D, R=R, P=P, meta=np.array([H, W, ch, seed], np.int64),
+                 crc=np.array([zlib.crc32(img.tobytes()), zlib.crc32(m1.tobytes()), zlib.crc32(m2.tobytes()), zlib.crc32(out.tobytes())], np.uint64))
+        if full:
+            d.update(map1=m1, map2=m2, out=out)
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **d)
+        inside = ((m1[..., 0] >= 0) & (m1[..., 0] < W - 1) & (m1[..., 1] >= 0) & (m1[..., 1] < H - 1)).mean()
+        print(name, "interior taps %.1f%%" % (100 * inside))
+
+
 if __name__ == "__main__":
+    rect_cases()
     bm_cases()
     special()
     main()

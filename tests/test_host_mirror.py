@@ -37,7 +37,7 @@ def test_config_keys_follow_reference_json(cvr):
                  "pre_filter_cap": 10, "min_disparity": 0.0}},
         "point_cloud_post_processing": {"outlier_min_k": 30, "outlier_std_threshold": 0.5, "keypoint_detector": "SIFT", "feature_detector": "FPFH"}}}
     c = cvr.parse_config(ref_json)
-    assert c == dict(block_matcher=cvr.MATCHER_SGBM, window_size=27, bm_num_disparities=128, block_size=27, num_disparities=128,
+    assert c == dict(requires_rectification=False, block_matcher=cvr.MATCHER_SGBM, window_size=27, bm_num_disparities=128, block_size=27, num_disparities=128,
                      uniqueness_ratio=10, speckle_range=2, speckle_window_size=100, pre_filter_cap=10, min_disparity=0, outlier_min_k=30,
                      outlier_std_threshold=0.5)
     ref_json["config"]["reconstruction"]["block_matcher"] = "stereo_bm"      # the reference's default

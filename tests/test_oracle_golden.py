@@ -150,3 +150,26 @@ def test_stereobm_oracle_matches_cv2(oracle, name):
     lb, rb, p = bm_golden_inputs(oracle, g)
     got = oracle.stereobm(oracle.gray_bgr(lb), oracle.gray_bgr(rb), p)
     assert np.array_equal(got, g["disp"]), "%d pixels differ from cv2.StereoBM" % int((got != g["disp"]).sum())
+
+
+# ---- stereo rectification of the inputs (Reconstruct3D::RectifyImages): oracle vs cv2 fixtures ----
+RECT_GOLDEN = ["rect_small_k5", "rect_small_k8_border", "rect_small_nodist_shift", "rect_small_k12", "rect_kitti_k5"]
+
+
+def rect_image(H, W, ch, seed):
+    img = np.random.default_rng(seed).integers(0, 256, (H, W, ch), dtype=np.uint8)
+    return img[:, :, 0].copy() if ch == 1 else img
+
+
+@pytest.mark.parametrize("name", RECT_GOLDEN)
+def test_oracle_rectification_matches_cv2(oracle, name):
+    g = load_golden(name)
+    H, W, ch, seed = (int(v) for v in g["meta"])
+    img = rect_image(H, W, ch, seed)
+    assert zlib.crc32(img.tobytes()) == int(g["crc"][0]), "input generator drifted"
+    m1, m2 = oracle.init_undistort_rectify_map(g["K"], g["D"], g["R"], g["P"], W, H)
+    assert zlib.crc32(m1.tobytes()) == int(g["crc"][1]) and zlib.crc32(m2.tobytes()) == int(g["crc"][2])
+    out = oracle.remap_bilinear(img, m1, m2)
+    assert zlib.crc32(out.tobytes()) == int(g["crc"][3])
+    if "map1" in g.files:
+        assert np.array_equal(m1, g["map1"]) and np.array_equal(m2, g["map2"]) and np.array_equal(out, g["out"])
