@@ -190,6 +190,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     fill_dev_params(c);
     c->smem_optin = (int)prop.sharedMemPerBlockOptin;
     { const char* e_ = getenv("CVR_PATH_KERNELS"); c->force_generic = e_ && strcmp(e_, "generic") == 0; c->path_v_variant = (e_ && strcmp(e_, "v2") == 0) ? 2 : 3;
+      const char* ks_ = getenv("CVR_KEEP_S"); c->keep_S = ks_ && atoi(ks_) != 0;
       const char* nn_ = getenv("CVR_NO_NN"); c->force_no_nn = nn_ && atoi(nn_) != 0;
       const char* n_ = getenv("CVR_PATHV_NT"); c->pathv_max_nt = n_ ? atoi(n_) : 1024; memset(c->pathv_active, 0, sizeof(c->pathv_active)); }
     const SgbmDev& g = c->sg;
@@ -363,7 +364,9 @@ extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, i
     const void* src; size_t need;
     switch (which) {
         case 0: src = c->d_volC; need = vol; break;
-        case 1: src = c->d_volA; need = vol; break;
+        case 1:
+            if (!c->keep_S) { c->err = "the final S volume is only kept when the context was created with CVR_KEEP_S=1 in the environment"; return CVR_ERR_INVALID_ARG; }
+            src = c->d_volA; need = vol; break;
         case 2: src = c->d_raw; need = (size_t)g.W * g.H * 2; break;
         case 3: src = c->d_disp; need = (size_t)g.W * g.H * 2; break;
         default: c->err = "unknown debug buffer"; return CVR_ERR_INVALID_ARG;

@@ -57,9 +57,11 @@ __device__ __forceinline__ void stw(unsigned* p, const unsigned (&v)[NWD])
     }
 }
 
-// ---- per-lane asynchronous prefetch ring (cp.async, Ampere+ LDGSTS): each lane copies its own NWD words of C and S
-// several columns ahead into shared memory, so the long global-load latency is off the per-column critical path.
-// A lane only ever reads back bytes it copied itself, hence cp.async.wait_group is all the synchronisation needed.
+// ---- asynchronous prefetch ring (cp.async, Ampere+ LDGSTS): the warp copies the C and S words of a column several
+// columns ahead into shared memory, so the long global-load latency is off the per-column critical path.
+// cpa_words: a lane copies its own NWD words (a lane then only reads back bytes it copied itself, cp.async.wait_group is
+// all the synchronisation needed).  cpa_16: 16-byte chunks (the k_path_h2 ring: the first Dp/8 lanes cover the column of
+// C, the next Dp/8 the column of S, one instruction for both arrays when Dp <= 128; needs a __syncwarp after the wait).
 template <int NWD>
 __device__ __forceinline__ void cpa_words(unsigned* sdst, const unsigned* gsrc)
 {
@@ -70,6 +72,10 @@ __device__ __forceinline__ void cpa_words(unsigned* sdst, const unsigned* gsrc)
 #pragma unroll
         for (int i = 0; i < NWD; i++) asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d + 4 * i), "l"(gsrc + i) : "memory");
     }
+}
+__device__ __forceinline__ void cpa_16(unsigned sdst, const void* gsrc)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sdst), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void cpa_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -219,7 +225,7 @@ __device__ __forceinline__ void path_info(int mn, int P2, unsigned& A, unsigned&
 // Winner-take-all on packed S (A.5 first half): same result as wta_column, fewer instructions.
 //   argmin: one CREDUX.MIN on (S << 16 | d); uniqueness as an order-free predicate; S[best-1], S[best+1] fetched from
 //   their owner lanes by shuffle; the small truncating division done in float with an exact +-1 correction.
-template <int NWD>
+template <int NWD, bool HASPAD = true>
 __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, const SgbmDev& p, int16_t* rawPix, int2* auxPix)
 {
     (void)rawPix;
@@ -227,7 +233,7 @@ __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, 
     int key = 0x7fffffff;
 #pragma unroll
     for (int j = 0; j < NWD; j++)
-        if (d0 + 2 * j < p.D) {                                       // a packed word is either all real disparities or all padding
+        if (!HASPAD || d0 + 2 * j < p.D) {                            // a packed word is either all real disparities or all padding
             key = min(key, (int)((s[j] << 16) | (unsigned)(d0 + 2 * j)));
             key = min(key, (int)((s[j] & 0xffff0000u) | (unsigned)(d0 + 2 * j + 1)));
         }
@@ -238,7 +244,7 @@ __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, 
     bool bad = false;
 #pragma unroll
     for (int j = 0; j < NWD; j++) {
-        if (d0 + 2 * j < p.D) {
+        if (!HASPAD || d0 + 2 * j < p.D) {
             const int v0 = lo16(s[j]), v1 = hi16(s[j]);
             bad |= (v0 * mul < lim) && ((unsigned)(rel - 2 * j) >= 3u);
             bad |= (v1 * mul < lim) && ((unsigned)(rel - 2 * j - 1) >= 3u);
@@ -299,21 +305,32 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
     path_info<NN>(0, P2, iA, iB);                                          // the border column: minimum 0
     __shared__ __align__(16) unsigned ringsm[4][CVR_PF_DEPTH][2][32 * NWD];
     unsigned (*ring)[2][32 * NWD] = ringsm[threadIdx.x >> 5];
-    {   // prologue: the first CVR_PF_DEPTH columns
-        const unsigned* pc = Cp; const unsigned* ps = Sp;
+    // Prefetch roles: a column of C (and of S) is Dp*2 bytes = CH 16-byte chunks.  Dp <= 128: lanes [0, CH) fetch C, lanes
+    // [CH, 2*CH) fetch S with ONE cp.async per lane and column; wider columns: lanes [0, CH) fetch both arrays.
+    constexpr int CH = 8 * NWD;
+    constexpr bool ONE = (2 * CH <= 32);
+    const bool roleS = ONE && lane >= CH;
+    const int chunk = roleS ? lane - CH : lane;
+    const bool pfOn = ONE ? (lane < (accumulate ? 2 * CH : CH)) : (lane < CH);
+    const long long laneOff = (long long)chunk * 4 - (long long)lane * NWD;                     // from this lane's words to its chunk
+    const unsigned* pf0 = (roleS ? (const unsigned*)Sp : Cp) + laneOff;                         // next column to fetch (array 0 of this lane)
+    const unsigned* pf1 = (const unsigned*)Sp + laneOff;                                        // !ONE: the S stream
+    const unsigned ringBase = (unsigned)__cvta_generic_to_shared(&ring[0][roleS ? 1 : 0][chunk * 4]);
+    constexpr unsigned slotBytes = 2u * 32u * NWD * 4u, arrBytes = 32u * NWD * 4u;
 #pragma unroll
-        for (int i = 0; i < CVR_PF_DEPTH; i++) {
-            if (i < W1) { cpa_words<NWD>(&ring[i][0][lane * NWD], pc); if (accumulate) cpa_words<NWD>(&ring[i][1][lane * NWD], ps); }
-            cpa_commit();
-            pc += stepW; ps += stepW;
+    for (int i = 0; i < CVR_PF_DEPTH; i++) {                               // prologue: the first CVR_PF_DEPTH columns
+        if (i < W1 && pfOn) {
+            cpa_16(ringBase + i * slotBytes, pf0);
+            if (!ONE && accumulate) cpa_16(ringBase + i * slotBytes + arrBytes, pf1);
         }
+        cpa_commit();
+        pf0 += stepW; pf1 += stepW;
     }
-    const unsigned* pfC = Cp + CVR_PF_DEPTH * stepW;                       // next column to fetch
-    const unsigned* pfS = Sp + CVR_PF_DEPTH * stepW;
     for (int step = 0; step < W1; step++) {
         unsigned c[NWD], s[NWD], L[NWD];
         const int slot = step % CVR_PF_DEPTH;
         cpa_wait<CVR_PF_DEPTH - 1>();
+        __syncwarp();                                                  // the chunks were copied by other lanes
         ldw<NWD>(&ring[slot][0][lane * NWD], c);
         if (accumulate) ldw<NWD>(&ring[slot][1][lane * NWD], s);
         else {
@@ -338,13 +355,13 @@ __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, 
 #pragma unroll
         for (int j = 0; j < NWD; j++) { Lp[j] = L[j]; if (!accumulate) s[j] = L[j]; }
         if (!WTA || storeS) stw<NWD>(Sp, s);
-        if (WTA) wta_column2<NWD>(s, lane, p, rawp, auxp);
-        if (step + CVR_PF_DEPTH < W1) {                                  // refill the slot just consumed
-            cpa_words<NWD>(&ring[slot][0][lane * NWD], pfC);
-            if (accumulate) cpa_words<NWD>(&ring[slot][1][lane * NWD], pfS);
+        if (WTA) wta_column2<NWD, HASPAD>(s, lane, p, rawp, auxp);
+        if (step + CVR_PF_DEPTH < W1 && pfOn) {                          // refill the slot just consumed (every lane read it before the reduce)
+            cpa_16(ringBase + slot * slotBytes, pf0);
+            if (!ONE && accumulate) cpa_16(ringBase + slot * slotBytes + arrBytes, pf1);
         }
         cpa_commit();
-        pfC += stepW; pfS += stepW;
+        pf0 += stepW; pf1 += stepW;
         Cp += stepW; Sp += stepW; rawp += dx; auxp += dx;
     }
 }
@@ -562,7 +579,7 @@ struct V3Ctx {                  // per-warp invariants of k_path_v3's column ste
 };
 
 // stores of one finished column: the three new blocks, their path_info, the edge pushes, S (and the winner when WTA)
-template <int NWD, int FT, int LT, bool WTA, bool NN, int BLK, int DW>
+template <int NWD, int FT, int LT, bool WTA, bool HASPAD, bool NN, int BLK, int DW>
 __device__ __forceinline__ void v3_finish(const V3Ctx& x, const SgbmDev& p, const int ci, unsigned* const cb, unsigned* const Sp, const bool firstCol,
                                           const bool lastCol, const unsigned (&M1)[NWD], const unsigned (&M2)[NWD], const unsigned (&M3)[NWD],
                                           const unsigned (&s)[NWD], const int mn1, const int mn2, const int mn3)
@@ -583,7 +600,7 @@ __device__ __forceinline__ void v3_finish(const V3Ctx& x, const SgbmDev& p, cons
         if (lane == 0) st_async_v2(x.pushR_dst + DW * 4, iA, iB, x.pushR_bar);
     }
     if (!WTA || x.storeS) stw<NWD>(Sp, s);
-    if (WTA) wta_column2<NWD>(s, lane, p, x.raw + (x.frameRow0 + x.y) * p.W + x.a + ci + p.minX1, x.aux + (x.frameRow0 + x.y) * x.W1 + x.a + ci);
+    if (WTA) wta_column2<NWD, HASPAD>(s, lane, p, x.raw + (x.frameRow0 + x.y) * p.W + x.a + ci + p.minX1, x.aux + (x.frameRow0 + x.y) * x.W1 + x.a + ci);
 }
 
 // One column of one row.  FT / LT say whether this call can be the chunk's first / last column: 0 = never, 1 = always,
@@ -633,7 +650,7 @@ __device__ __forceinline__ void v3_column(const V3Ctx& x, const SgbmDev& p, bool
         } else {
             acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3);
         }
-        v3_finish<NWD, FT, LT, WTA, NN, BLK, DW>(x, p, ci, cb, Sp, firstCol, lastCol, L1, L2, L3, s, mn1, mn2, mn3);
+        v3_finish<NWD, FT, LT, WTA, HASPAD, NN, BLK, DW>(x, p, ci, cb, Sp, firstCol, lastCol, L1, L2, L3, s, mn1, mn2, mn3);
     } else {
         const int d1 = (int)(short)(kiIn.y & 0xffffu), d2 = (int)(short)(i2.y & 0xffffu), d3 = (int)(short)(i3.y & 0xffffu);
         int m1, m2, m3;
@@ -654,7 +671,7 @@ __device__ __forceinline__ void v3_column(const V3Ctx& x, const SgbmDev& p, bool
             if (lane == 0) atomicOr(&x.flags[x.b], 2);
         }
         acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3);   // valid for any signs
-        v3_finish<NWD, FT, LT, WTA, NN, BLK, DW>(x, p, ci, cb, Sp, firstCol, lastCol, L1, L2, L3, s, mn1, mn2, mn3);
+        v3_finish<NWD, FT, LT, WTA, HASPAD, NN, BLK, DW>(x, p, ci, cb, Sp, firstCol, lastCol, L1, L2, L3, s, mn1, mn2, mn3);
     }
 }
 

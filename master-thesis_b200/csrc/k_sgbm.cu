@@ -811,7 +811,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
 {
     const SgbmDev& p = c->sg;
     const size_t npix = (size_t)B * p.W * p.H;
-    const int storeS = 1;   // keep S for cvr_debug_fetch; the write is ~1/8 of the stage's traffic
+    const int storeS = c->keep_S ? 1 : 0;   // the final S is only written out for cvr_debug_fetch (CVR_KEEP_S=1): 1/8 of the stage's traffic
     if (p.W1 <= 0) {
         k_fill_s16<<<(unsigned)cvr_div_up_sz(npix, 256), 256, 0, c->stream>>>(c->d_med, npix, p.INVALID);
         LAUNCH_CHECK(c);

@@ -5,6 +5,8 @@ import os
 import sys
 import time
 
+import os
+os.environ.setdefault("CVR_KEEP_S", "1")
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

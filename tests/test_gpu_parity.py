@@ -25,8 +25,9 @@ def _golden_inputs(O, g):
 
 
 @pytest.mark.parametrize("bs,mode", [(5, 0), (27, 0), (9, 1), (27, 1)])
-def test_stages_against_oracle(cvr, oracle, bs, mode):
+def test_stages_against_oracle(cvr, oracle, monkeypatch, bs, mode):
     """Cost volume C, aggregated volume S, raw WTA/LR disparity and final disparity, each bit-exact."""
+    monkeypatch.setenv("CVR_KEEP_S", "1")              # the last pass only writes the final S out when asked to
     H, W, D = 48, 260, 64
     l, r = oracle.synth_pair(H, W, D, seed=100 + bs + mode)
     p = oracle.reference_sgbm_params(block_size=bs, num_disparities=D, mode=mode)
