@@ -48,6 +48,11 @@ __device__ __forceinline__ unsigned pk_neg(unsigned a) { return __vneg2(a); }
 // descriptors of just that segment (plus the block-sum halo and the disparity range) in shared memory, so that many
 // CTAs fit on an SM.  The horizontal block sum is a sliding window over j = s - SW2 .. e - 1 + SW2 with the column index
 // clamped to [0, W1-1] exactly like OpenCV's clamped recurrence (closed form: provably unsaturated, see cvr_create).
+// Right-image descriptors are read at a stride of two entries (a thread owns two adjacent disparities), which would put
+// the 8 lanes of a 128-bit load phase on 4 bank groups; flipping the lowest index bit in every other block of 8 entries
+// spreads any 8 stride-2 entries over all 8 groups.
+__device__ __forceinline__ int rswz(int i) { return i ^ ((i >> 3) & 1); }
+
 __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStride, int16_t* __restrict__ hsum, SgbmDev p, int nseg)
 {
     extern __shared__ uint4 sm4[];
@@ -60,7 +65,7 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
     const int nL = xl1 - xl0 + 1, nR = xr1 - xr0 + 1;
     uint4* Lpk = sm4;                                   // [nL]
     uint4* Rpk = sm4 + nL;                              // [nR]
-    unsigned* aL = (unsigned*)(Rpk + nR);               // [nL + 2]  packed (G | R << 16) of left pixels xl0-1 .. xl1+1
+    unsigned* aL = (unsigned*)(Rpk + nR + 2);           // [nL + 2]  packed (G | R << 16) of left pixels xl0-1 .. xl1+1 (Rpk: swizzled, up to nR + 1)
     unsigned* aR = aL + nL + 2;                         // [nR + 2]
     uint8_t* ringbuf = (uint8_t*)(aR + nR + 2);
     const int tid = threadIdx.x, nt = blockDim.x;
@@ -92,71 +97,80 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
         const unsigned ul = x > 0 ? (((u + a[-1]) >> 1) & 0x7fff7fffu) : u;
         const unsigned ur = x < W - 1 ? (((u + a[1]) >> 1) & 0x7fff7fffu) : u;
         const unsigned u0 = __vimin3_s16x2(ul, ur, u), u1 = __vimax3_s16x2(ul, ur, u);
-        (right ? Rpk : Lpk)[j] = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
+        (right ? Rpk : Lpk)[right ? rswz(j) : j] = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
     }
     __syncthreads();
 
-    const int d = tid;
-    int16_t* out = hsum + (((size_t)b * H + y) * W1) * Dp + d;
-    if (d >= p.D) {
-        for (int xp = s; xp < e; xp++) out[(size_t)xp * Dp] = 0;
+    // ---- sliding block sums.  The CTA's Dp threads form two groups of Dp/2; each group owns one half of the segment and
+    // each thread two adjacent disparities (d, d+1), whose costs, running sums and outputs travel as packed 16-bit pairs:
+    // per pair of elements one broadcast load of the left descriptor, two of the right ones, one 16-bit ring read and
+    // write, one 32-bit store -- the kernel is bound by shared-memory wavefronts (ncu: 98 % of the LSU data pipe).
+    const int half = Dp >> 1, grp = tid / half, q = tid - grp * half, d = 2 * q;
+    const int mid = s + ((e - s + 1) >> 1);
+    const int hs_ = grp ? mid : s, he_ = grp ? e : mid;                        // this group's output columns [hs_, he_)
+    if (hs_ >= he_) return;
+    unsigned* out = (unsigned*)(hsum + (((size_t)b * H + y) * W1) * Dp) + q;    // pair q of column 0; a column is Dp/2 words
+    if (d >= p.D) {                                                           // padding disparities (D is even: a pair is all padding or none)
+        for (int xp = hs_; xp < he_; xp++) out[(size_t)xp * half] = 0u;
         return;
     }
-    const int offR = p.minX1 - p.minD - d - xr0;        // right descriptor index of computed column xp: xp + offR
+    const int offR = p.minX1 - p.minD - d - xr0;        // right descriptor index of computed column xp for disparity d: xp + offR (d + 1: one less)
     const int offL = p.minX1 - xl0;
-    auto pixcost = [&](int xp) -> int {
-        const uint4 l = Lpk[xp + offL];
-        const uint4 r = Rpk[xp + offR];
-        unsigned c0 = __vimax3_s16x2_relu(__vadd2(l.x, r.w), __vadd2(r.y, l.z), 0u);   // max(0, u - v1, v0 - u)
-        unsigned c1 = __vimax3_s16x2_relu(__vadd2(r.x, l.w), __vadd2(l.y, r.z), 0u);   // max(0, v - u1, u0 - v)
-        unsigned m = __vmins2(c0, c1);
-        return (int)(m & 0xffffu) + (int)(m >> 18);
+    auto cost1 = [](const uint4& l, const uint4& r) -> unsigned {
+        const unsigned c0 = __vimax3_s16x2_relu(__vadd2(l.x, r.w), __vadd2(r.y, l.z), 0u);   // max(0, u - v1, v0 - u)
+        const unsigned c1 = __vimax3_s16x2_relu(__vadd2(r.x, l.w), __vadd2(l.y, r.z), 0u);   // max(0, v - u1, u0 - v)
+        const unsigned m = __vmins2(c0, c1);
+        return (m & 0xffffu) + (m >> 18);                                     // Sobel-channel cost + (intensity cost >> 2), <= 255
     };
-    uint8_t* ring = ringbuf + d;
-    const int bs = p.bs, ringBytes = p.ring * Dp;
-    int run = 0;
-    const int j0 = s - SW2, j1 = e - 1 + SW2;
+    auto pixcost2 = [&](int xp, unsigned& c8) -> unsigned {                   // packed pair of costs; c8 = the same as two bytes
+        const uint4 l = Lpk[xp + offL];
+        const unsigned ca = cost1(l, Rpk[rswz(xp + offR)]), cb = cost1(l, Rpk[rswz(xp + offR - 1)]);
+        c8 = ca | (cb << 8);
+        return ca | (cb << 16);
+    };
+    auto widen = [](unsigned c8) -> unsigned { return (c8 & 0xffu) | ((c8 & 0xff00u) << 8); };
+    uint16_t* ring = (uint16_t*)ringbuf + (size_t)grp * p.ring * half + q;      // [ring slots][Dp/2] per group
+    const int ringLen = p.ring * half;
+    unsigned run = 0;                                                         // two running sums (each < 2^15: provably unsaturated)
+    const int j0 = hs_ - SW2, j1 = he_ - 1 + SW2;
     // warm-up: the first bs - 1 window elements (clamped at the left image border), nothing to emit or to drop yet
-    int j = j0, wi = 0;                                               // wi: byte offset of the ring slot written next
-    for (; j < s + SW2; j++) {
-        const int c = pixcost(min(max(j, 0), W1 - 1));
-        ring[wi] = (uint8_t)c;
-        run += c;
-        wi += Dp; if (wi == ringBytes) wi = 0;
+    int j = j0, wi = 0;                                                       // wi: index of the ring slot written next
+    for (; j < hs_ + SW2; j++) {
+        unsigned c8;
+        run += pixcost2(min(max(j, 0), W1 - 1), c8);
+        ring[wi] = (uint16_t)c8;
+        wi += half; if (wi == ringLen) wi = 0;
     }
     // steady state: one new element, one output; from the second output on the element leaving the window is dropped.
-    // No clamping while j <= W1 - 1: running pointers only.
-    int16_t* o = out + (size_t)s * Dp;
-    int ri = 0;                                                       // byte offset of the ring slot holding element j - bs
+    unsigned* o = out + (size_t)hs_ * half;
+    int ri = 0;                                                               // index of the ring slot holding element j - bs
     {
-        const int c = pixcost(min(j, W1 - 1));
-        ring[wi] = (uint8_t)c; run += c; wi += Dp; if (wi == ringBytes) wi = 0;
-        *o = (int16_t)run; o += Dp; j++;
+        unsigned c8;
+        run += pixcost2(min(j, W1 - 1), c8);
+        ring[wi] = (uint16_t)c8; wi += half; if (wi == ringLen) wi = 0;
+        *o = run; o += half; j++;
     }
     const int jmid = min(j1, W1 - 1);
     const uint4* lp = Lpk + (j + offL);
-    const uint4* rp = Rpk + (j + offR);
-    for (; j <= jmid; j++, lp++, rp++, o += Dp) {
+    int ridx = j + offR;
+    for (; j <= jmid; j++, lp++, ridx++, o += half) {                         // no clamping while j <= W1 - 1
         const uint4 l = *lp;
-        const uint4 r = *rp;
-        const unsigned c0 = __vimax3_s16x2_relu(__vadd2(l.x, r.w), __vadd2(r.y, l.z), 0u);
-        const unsigned c1 = __vimax3_s16x2_relu(__vadd2(r.x, l.w), __vadd2(l.y, r.z), 0u);
-        const unsigned m = __vmins2(c0, c1);
-        const int c = (int)(m & 0xffffu) + (int)(m >> 18);
-        run += c - (int)ring[ri];
-        ring[wi] = (uint8_t)c;
-        *o = (int16_t)run;
-        wi += Dp; if (wi == ringBytes) wi = 0;
-        ri += Dp; if (ri == ringBytes) ri = 0;
+        const unsigned ca = cost1(l, Rpk[rswz(ridx)]), cb = cost1(l, Rpk[rswz(ridx - 1)]);
+        run = run + (ca | (cb << 16)) - widen(ring[ri]);
+        ring[wi] = (uint16_t)(ca | (cb << 8));
+        *o = run;
+        wi += half; if (wi == ringLen) wi = 0;
+        ri += half; if (ri == ringLen) ri = 0;
     }
-    if (j <= j1) {                                                    // right image border: the last column repeats
-        const int cl = pixcost(W1 - 1);
-        for (; j <= j1; j++, o += Dp) {
-            run += cl - (int)ring[ri];
-            ring[wi] = (uint8_t)cl;
-            *o = (int16_t)run;
-            wi += Dp; if (wi == ringBytes) wi = 0;
-            ri += Dp; if (ri == ringBytes) ri = 0;
+    if (j <= j1) {                                                            // right image border: the last column repeats
+        unsigned c8;
+        const unsigned cl = pixcost2(W1 - 1, c8);
+        for (; j <= j1; j++, o += half) {
+            run = run + cl - widen(ring[ri]);
+            ring[wi] = (uint16_t)c8;
+            *o = run;
+            wi += half; if (wi == ringLen) wi = 0;
+            ri += half; if (ri == ringLen) ri = 0;
         }
     }
 }
@@ -170,42 +184,56 @@ __device__ __forceinline__ int lo16(unsigned w) { return (int)(short)(w & 0xffff
 __device__ __forceinline__ int hi16(unsigned w) { return ((int)w) >> 16; }
 __device__ __forceinline__ unsigned pack16(int lo, int hi) { return ((unsigned)lo & 0xffffu) | ((unsigned)hi << 16); }
 
-// One thread per (frame, x', 4 disparities) marching down the rows.  The "old" row (y - SH2 - 1) was read as the
-// "new" row bs rows earlier and is still L2-resident (measured: re-reading it beats a shared-memory ring).
-__global__ void k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B, int* flags)
+// Saturating int16 add / subtract of a NON-NEGATIVE operand, two lanes per word: only one side can saturate, which leaves
+// three native packed instructions each (the generic __vaddss2 / __vsubss2 expand to six).
+//   sat(a + n) = min(a, 32767 - n) + n,  32767 - n = n ^ 0x7fff     sat(a - b) = max(a, b - 32768) - b,  b - 32768 = b ^ 0x8000
+__device__ __forceinline__ unsigned sat_add_pos2(unsigned a, unsigned n) { return __vadd2(__vmins2(a, n ^ 0x7fff7fffu), n); }
+__device__ __forceinline__ unsigned sat_sub_pos2(unsigned a, unsigned b) { return __vsub2(__vmaxs2(a, b ^ 0x80008000u), b); }
+
+// One thread per (frame, x', 8 disparities) marching down the rows.  The "old" row (y - SH2 - 1) was read as the "new"
+// row bs rows earlier and is simply read again.  ncu: 288 MB of DRAM traffic per KITTI frame (214 MB algorithmic: the
+// re-read mostly misses the L2, whose share per resident row step is too small for 27 rows) at 92 % of the measured HBM
+// peak.  Measured and rejected on B200: a shared-memory ring of the last bs rows (caps the resident threads: 58-61 us
+// against 48 us), register prefetch 2-3 rows ahead, and capping the occupancy to make the window fit the L2 (all slower).
+__global__ void __launch_bounds__(128) k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B, int* flags)
 {
-    const size_t rowWords = (size_t)p.W1 * p.Dp / 4;          // uint2 words per row
+    const size_t rowWords = (size_t)p.W1 * p.Dp / 8;          // uint4 words per row (Dp is a multiple of 32)
     const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= rowWords * B) return;
     const int b = (int)(t / rowWords);
     const size_t i = t % rowWords;
     const int H = p.H, SH2 = p.SH2;
-    const uint2* hs = (const uint2*)hsum + (size_t)b * H * rowWords + i;
-    uint2* cs = (uint2*)C + (size_t)b * H * rowWords + i;
+    const uint4* hs = (const uint4*)hsum + (size_t)b * H * rowWords + i;
+    uint4* cs = (uint4*)C + (size_t)b * H * rowWords + i;
     // OpenCV evaluates the first computed column (x' = 0) as (Cprev + new) - old and all others as (Cprev - old) + new;
     // in saturating int16 lanes the two differ once C sticks at 32767 (pinned by tests/golden/satdrift_d32_bs27.npz).
-    const bool first = i < (size_t)p.Dp / 4;
-    int c[4] = { p.P2s, p.P2s, p.P2s, p.P2s };
+    const bool first = i < (size_t)p.Dp / 8;
+    int c[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) c[j] = p.P2s;
     for (int k = 0; k <= SH2; k++) {
-        uint2 h = hs[(size_t)min(k, H - 1) * rowWords];
+        const uint4 h = hs[(size_t)min(k, H - 1) * rowWords];
         const int sc = (k == 0) ? SH2 + 1 : 1;
-        int hv[4] = { lo16(h.x), hi16(h.x), lo16(h.y), hi16(h.y) };
+        const int hv[8] = { lo16(h.x), hi16(h.x), lo16(h.y), hi16(h.y), lo16(h.z), hi16(h.z), lo16(h.w), hi16(h.w) };
 #pragma unroll
-        for (int j = 0; j < 4; j++) c[j] = sat16i(c[j] + sat16i(hv[j] * sc));
+        for (int j = 0; j < 8; j++) c[j] = sat16i(c[j] + sat16i(hv[j] * sc));
     }
-    int neg = c[0] | c[1] | c[2] | c[3];
-    cs[0] = make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3]));
+    // hsum is a sum of non-negative pixel costs, so the row recurrence only ever adds / subtracts non-negative values
+    unsigned w[4] = { pack16(c[0], c[1]), pack16(c[2], c[3]), pack16(c[4], c[5]), pack16(c[6], c[7]) };
+    unsigned negw = w[0] | w[1] | w[2] | w[3];
+    cs[0] = make_uint4(w[0], w[1], w[2], w[3]);
     for (int y = 1; y < H; y++) {
-        const uint2 ho = __ldcs(hs + (size_t)max(y - SH2 - 1, 0) * rowWords);   // last use of that row: evict-first
-        const uint2 hn = hs[(size_t)min(y + SH2, H - 1) * rowWords];              // read again bs rows later: keep in L2
-        int ov[4] = { lo16(ho.x), hi16(ho.x), lo16(ho.y), hi16(ho.y) };
-        int nv[4] = { lo16(hn.x), hi16(hn.x), lo16(hn.y), hi16(hn.y) };
+        const uint4 ho = __ldcs(hs + (size_t)max(y - SH2 - 1, 0) * rowWords);   // last use of that row: evict-first
+        const uint4 hn = hs[(size_t)min(y + SH2, H - 1) * rowWords];              // read again bs rows later
+        const unsigned o[4] = { ho.x, ho.y, ho.z, ho.w }, n[4] = { hn.x, hn.y, hn.z, hn.w };
 #pragma unroll
-        for (int j = 0; j < 4; j++) c[j] = first ? sat16i(sat16i(c[j] + nv[j]) - ov[j]) : sat16i(sat16i(c[j] - ov[j]) + nv[j]);
-        neg |= c[0] | c[1] | c[2] | c[3];
-        __stcs(cs + (size_t)y * rowWords, make_uint2(pack16(c[0], c[1]), pack16(c[2], c[3])));   // streamed out, not re-read here
+        for (int j = 0; j < 4; j++) {
+            w[j] = first ? sat_sub_pos2(sat_add_pos2(w[j], n[j]), o[j]) : sat_add_pos2(sat_sub_pos2(w[j], o[j]), n[j]);
+            negw |= w[j];
+        }
+        __stcs(cs + (size_t)y * rowWords, make_uint4(w[0], w[1], w[2], w[3]));   // streamed out, not re-read here
     }
-    if (neg < 0) atomicOr(&flags[b], 1);      // a negative C exists in this frame: the packed path kernels take their exact t + C form
+    if (negw & 0x80008000u) atomicOr(&flags[b], 1);   // a negative C exists in this frame: the packed path kernels take their exact t + C form
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -826,7 +854,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         if (nseg < 1) nseg = 1;
         const int segMax = cvr_div_up(p.W1, nseg) + 1;
         const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;
-        const size_t smem = (nLmax + nRmax) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)p.ring * p.Dp;
+        const size_t smem = (nLmax + nRmax + 2) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)2 * p.ring * p.Dp;   // descriptors + two rings of 16-bit cost pairs
         static size_t smem_set = 0;
         if (smem > 48 * 1024 && smem > smem_set) {
             CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -837,7 +865,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         cvr_stage_mark(c, "pix_hsum");
     }
     {
-        const size_t nthreads = (size_t)p.W1 * p.Dp / 4 * B;
+        const size_t nthreads = (size_t)p.W1 * p.Dp / 8 * B;
         k_vsum<<<(unsigned)cvr_div_up_sz(nthreads, 128), 128, 0, c->stream>>>(c->d_volA, c->d_volC, p, B, c->d_sgflags);
         LAUNCH_CHECK(c);
         cvr_stage_mark(c, "vsum");
