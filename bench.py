@@ -234,10 +234,12 @@ def main():
     hL = torch.from_numpy(Ls[idx]).pin_memory(); hR = torch.from_numpy(Rs[idx]).pin_memory()
     dL = hL.to(dev); dR = hR.to(dev)
     cap = 65536                                                        # points per frame after voxel + SOR (~11k observed)
-    d_cloud = torch.empty((B, cap, 16), dtype=torch.uint8, device=dev)
-    d_cnt = torch.zeros(B, dtype=torch.int32, device=dev)
-    h_cloud = torch.empty((B, cap, 16), dtype=torch.uint8).pin_memory()
-    h_cnt = torch.zeros(B, dtype=torch.int32).pin_memory()
+    # two batches are in flight at a time: two sets of output buffers, used alternately
+    d_clouds = [torch.empty((B, cap, 16), dtype=torch.uint8, device=dev) for _ in range(2)]
+    d_cnts = [torch.zeros(B, dtype=torch.int32, device=dev) for _ in range(2)]
+    h_clouds = [torch.empty((B, cap, 16), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    h_cnts = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(2)]
+    h_cnt = h_cnts[0]
     frame_bytes = W * H * 3
 
     def batch_struct(mem, L, R, cloud, cnt):
@@ -248,15 +250,16 @@ def main():
         io.cloud, io.cloud_capacity, io.cloud_count = cloud.data_ptr(), cap, cnt.data_ptr()
         io.stages = 15
         return io
-    io_dev = batch_struct(cvr.MEM_DEVICE, dL, dR, d_cloud, d_cnt)
-    io_host = batch_struct(cvr.MEM_HOST, hL, hR, h_cloud, h_cnt)
+    io_dev = [batch_struct(cvr.MEM_DEVICE, dL, dR, d_clouds[k], d_cnts[k]) for k in range(2)]
+    io_host = [batch_struct(cvr.MEM_HOST, hL, hR, h_clouds[k], h_cnts[k]) for k in range(2)]
 
     # gather of the filtered clouds to the mapping rank (rank 0): counts by all_gather, payload by grouped send/recv
     gather_buf = torch.empty((world, B * cap // 4, 16), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None
 
-    def gather_clouds():
+    def gather_clouds(k):
         if world == 1:
             return
+        d_cnt, d_cloud = d_cnts[k], d_clouds[k]
         cnts = [torch.empty_like(d_cnt) for _ in range(world)]
         dist.all_gather(cnts, d_cnt)
         tot = [int(c.sum().item()) for c in cnts]
@@ -287,24 +290,25 @@ def main():
         e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
         e0.record()
         t0 = time.perf_counter()
-        if pipelined:
-            # host buffers, two batches in flight: the upload of step i+1 overlaps the kernels of step i; every step's
-            # H2D and D2H are inside the timed region (the same pinned host buffers are re-sent every step).  Each rank
-            # delivers its filtered clouds to its own host process; the NCCL gather to the mapping rank is part of the
-            # device-resident path (`value`) only.
-            rec.submit_batch_raw(io, B)
-            for _ in range(steps - 1):
-                rec.submit_batch_raw(io, B)
-                rec.wait_batch()
+        # Two batches in flight (cvr_submit_batch / cvr_wait_batch): the upload and the matcher of step i+1 overlap the
+        # filter stages of step i and the download of step i-1.  `pipelined` = host buffers (every step's H2D and D2H are
+        # inside the timed region; the same pinned host buffers are re-sent every step; each rank delivers its filtered
+        # clouds to its own host process).  Otherwise device-resident inputs and outputs, and the NCCL gather of each
+        # step's clouds to the mapping rank follows its wait.  With `profile` the library brackets every stage with
+        # events on the stream it runs on and hands the durations back at the wait.
+        def collected(i):
+            if with_gather and not pipelined:
+                gather_clouds(i & 1)
+            if profile:
+                for n_, ms_ in rec.last_timings():
+                    stage_ms.setdefault(n_, []).append(ms_)
+        rec.submit_batch_raw(io[0], B)
+        for i in range(1, steps):
+            rec.submit_batch_raw(io[i & 1], B)
             rec.wait_batch()
-        else:
-            for _ in range(steps):
-                rec.process_batch_raw(io, B)
-                if with_gather:
-                    gather_clouds()
-                if profile:
-                    for n_, ms_ in rec.last_timings():
-                        stage_ms.setdefault(n_, []).append(ms_)
+            collected(i - 1)
+        rec.wait_batch()
+        collected(steps - 1)
         e1.record()
         torch.cuda.synchronize()
         # every library call blocks until its (own) stream is idle, so both torch-stream events are recorded with all

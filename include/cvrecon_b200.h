@@ -182,13 +182,15 @@ typedef struct cvr_batch {
 } cvr_batch;
 int cvr_process_batch(cvr_ctx* ctx, int nframes, const cvr_batch* io);
 
-/* Pipelined form of cvr_process_batch for HOST buffers: up to two batches in flight, so that the upload of batch
- * i+1 overlaps the kernels of batch i.  This is how the frame loop of the reference's server thread
- * (cv_reconstruct/src/server/ReconstructionServer.cpp:134-153: dequeue a stereo message, ProcessStereoFrame, repeat)
- * is meant to drive the library at full rate: submit the frames just dequeued, then collect the previous batch.
- *   cvr_submit_batch  enqueues upload + the whole chain and returns at once; the io struct is copied, the host
- *                     buffers it points to (inputs AND outputs) must stay valid until the matching cvr_wait_batch
- *   cvr_wait_batch    blocks until the OLDEST submitted batch is done and its outputs are in the host buffers
+/* Pipelined form of cvr_process_batch: up to two batches in flight, so that the upload of batch i+1 overlaps the kernels
+ * of batch i and the download of batch i-1.  This is how the frame loop
+ * of the reference's server thread (cv_reconstruct/src/server/ReconstructionServer.cpp:134-153: dequeue a stereo message,
+ * ProcessStereoFrame, repeat) is meant to drive the library at full rate: submit the frames just dequeued, then collect
+ * the previous batch.
+ *   cvr_submit_batch  enqueues upload + the whole chain and returns at once; the io struct is copied, the buffers it
+ *                     points to (inputs AND outputs, host or device) must stay valid and untouched until the matching
+ *                     cvr_wait_batch.  Host batches are staged through the slot; device batches are read and written in place.
+ *   cvr_wait_batch    blocks until the OLDEST submitted batch is done and its outputs are in the caller's buffers
  * At most two submits may be outstanding (a third returns CVR_ERR_CAPACITY).  The first submit allocates the two
  * pipeline slots (inputs + parked outputs).  Mixing with the synchronous entry points is allowed once every
  * submitted batch has been waited for. */

@@ -40,24 +40,27 @@ extern "C" void cvr_default_params(cvr_params* p, int width, int height)
 void cvr_stage_mark(cvr_ctx* c, const char* name)
 {
     if (!c->profiling) return;
-    if (c->timers_used >= (int)c->timers.size()) {
+    std::vector<StageTimer>& tv = c->timers[c->tset];
+    int& used = c->timers_used[c->tset];
+    if (used >= (int)tv.size()) {
         StageTimer t; t.name = name; cudaEventCreate(&t.ev);
-        c->timers.push_back(t);
+        tv.push_back(t);
     }
-    c->timers[c->timers_used].name = name;
-    cudaEventRecord(c->timers[c->timers_used].ev, c->stream);
-    c->timers_used++;
+    tv[used].name = name;
+    cudaEventRecord(tv[used].ev, c->stream);
+    used++;
 }
-static void timers_begin(cvr_ctx* c) { c->timers_used = 0; cvr_stage_mark(c, "begin"); }
-static void timers_end(cvr_ctx* c)
+static void timers_begin(cvr_ctx* c, int set) { c->tset = set; c->timers_used[set] = 0; cvr_stage_mark(c, "begin"); }
+static void timers_end(cvr_ctx* c, int set)                           // after the events of that set have completed
 {
     c->t_names.clear(); c->t_ms.clear();
     if (!c->profiling) return;
-    for (int i = 1; i < c->timers_used; i++) {
+    for (int i = 1; i < c->timers_used[set]; i++) {
         float ms = 0.f;
-        cudaEventElapsedTime(&ms, c->timers[i - 1].ev, c->timers[i].ev);
-        c->t_names.push_back(c->timers[i].name); c->t_ms.push_back(ms);
+        cudaEventElapsedTime(&ms, c->timers[set][i - 1].ev, c->timers[set][i].ev);
+        c->t_names.push_back(c->timers[set][i].name); c->t_ms.push_back(ms);
     }
+    c->timers_used[set] = 0;
 }
 
 template <typename T>
@@ -164,7 +167,7 @@ static void free_all(cvr_ctx* c)
         }
         cudaStreamDestroy(c->copy_stream); cudaStreamDestroy(c->d2h_stream);
     }
-    for (auto& t : c->timers) cudaEventDestroy(t.ev);
+    for (auto& tv : c->timers) for (auto& t : tv) cudaEventDestroy(t.ev);
     if (c->stream) cudaStreamDestroy(c->stream);
 }
 
@@ -184,7 +187,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     cvr_ctx* c = new (std::nothrow) cvr_ctx();
     if (!c) return CVR_ERR_CUDA;
     c->prm = *p; c->device = device; c->maxB = p->max_batch; c->sm_count = prop.multiProcessorCount;
-    c->launches = 0; c->profiling = false; c->timers_used = 0; c->stream = nullptr; c->h_counts = nullptr;
+    c->launches = 0; c->profiling = false; c->timers_used[0] = c->timers_used[1] = c->timers_used[2] = 0; c->tset = 0; c->stream = nullptr; c->h_counts = nullptr;
     c->pipe_ready = false; c->copy_stream = nullptr; c->d2h_stream = nullptr; c->n_submit = c->n_wait = 0;
     memset(c->slot, 0, sizeof(c->slot));
     fill_dev_params(c);
@@ -270,7 +273,7 @@ extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const u
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sl >= (size_t)W * ch && sr >= (size_t)W * ch && sd >= (size_t)W * 2, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * ch, left, sl, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], (size_t)W * ch, right, sr, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_gray(c, 1, c->d_in[0], (size_t)W * ch, 0, c->d_in[1], (size_t)W * ch, 0, ch);
@@ -281,7 +284,7 @@ extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const u
     CVR_CUDA(c, cudaMemcpy2DAsync(disp, sd, c->d_med, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->stream));
     cvr_stage_mark(c, "d2h");
     rc = sync_check(c);
-    timers_end(c);
+    timers_end(c, 0);
     return rc;
 }
 
@@ -386,7 +389,7 @@ extern "C" int cvr_prune(cvr_ctx* c, int16_t* disp, size_t sd, float* dispf, uin
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sd >= (size_t)W * 2, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_med, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_prune(c, 1, c->d_med);
     if (rc) return rc;
@@ -394,7 +397,7 @@ extern "C" int cvr_prune(cvr_ctx* c, int16_t* disp, size_t sd, float* dispf, uin
     if (dispf) CVR_CUDA(c, cudaMemcpyAsync(dispf, c->d_dispf, (size_t)W * H * 4, cudaMemcpyDeviceToHost, c->stream));
     if (mask) CVR_CUDA(c, cudaMemcpyAsync(mask, c->d_mask, (size_t)W * H, cudaMemcpyDeviceToHost, c->stream));
     rc = sync_check(c);
-    timers_end(c);
+    timers_end(c, 0);
     return rc;
 }
 
@@ -418,13 +421,13 @@ extern "C" int cvr_reproject_cloud(cvr_ctx* c, const int16_t* disp, size_t sd, c
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sd >= (size_t)W * 2 && sb >= (size_t)W * 3, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_pruned, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, c->d_in[0], (size_t)W * 3, 0, 3);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
-    timers_end(c);
+    timers_end(c, 0);
     return rc;
 }
 
@@ -437,14 +440,14 @@ extern "C" int cvr_triangulate(cvr_ctx* c, const float* dispf, size_t sd, const 
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sd >= (size_t)W * 4 && sb >= (size_t)W * 3 && (!mask || sm >= (size_t)W), "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_dispf, (size_t)W * 4, dispf, sd, (size_t)W * 4, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
     if (mask) CVR_CUDA(c, cudaMemcpy2DAsync(c->d_mask, (size_t)W, mask, sm, (size_t)W, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, mask ? c->d_mask : nullptr, c->d_in[0], (size_t)W * 3, 0, 3);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
-    timers_end(c);
+    timers_end(c, 0);
     return rc;
 }
 
@@ -457,7 +460,7 @@ extern "C" int cvr_voxel_grid(cvr_ctx* c, const cvr_point* in, int n, cvr_point*
     if (passthrough) *passthrough = 0;
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_cloud, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_ncloud, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
@@ -470,7 +473,7 @@ extern "C" int cvr_voxel_grid(cvr_ctx* c, const cvr_point* in, int n, cvr_point*
         CVR_CUDA(c, cudaMemcpy(&h, c->d_vhdr, sizeof(h), cudaMemcpyDeviceToHost));
         *passthrough = h.passthrough;
     }
-    timers_end(c);
+    timers_end(c, 0);
     return CVR_OK;
 }
 
@@ -482,14 +485,14 @@ extern "C" int cvr_sor(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, i
     if (kept_out) *kept_out = 0;
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_nvox, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_sor(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, 0);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_sorout, c->d_nout, out, capacity, kept_out);
-    timers_end(c);
+    timers_end(c, 0);
     return rc;
 }
 
@@ -501,14 +504,14 @@ extern "C" int cvr_radius_outlier_removal(cvr_ctx* c, const cvr_point* in, int n
     if (kept_out) *kept_out = 0;
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_nvox, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_ror(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, radius, min_neighbors);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_sorout, c->d_nout, out, capacity, kept_out);
-    timers_end(c);
+    timers_end(c, 0);
     return rc;
 }
 
@@ -534,48 +537,62 @@ __global__ void k_copy_clouds(const cvr_point* __restrict__ src, size_t srcStrid
     if (blockIdx.x == 0 && threadIdx.x == 0 && cntOut) cntOut[b] = cnt[b];
 }
 
-// Enqueues the whole per-frame chain for B frames on the compute stream; *fin / *fcnt receive the buffers that hold
-// the last enabled stage's clouds (nullptr when only disparity was asked for).
-static int enqueue_chain(cvr_ctx* c, int B, int stages, const uint8_t* dl, size_t lstep, size_t lfs, const uint8_t* dr, size_t rstep, size_t rfs, int ch,
-                         const cvr_point** fin, const int** fcnt)
+// The per-frame chain in two halves, each enqueued on c->stream (whatever that currently is):
+//   enqueue_matcher: (rectify ->) gray -> SGBM / BM, final disparity in c->d_med; *dl / *lstep / *lfs are updated to the
+//                    left image the cloud must be coloured from (the rectified one when requires_rectification is set);
+//   enqueue_filters: prune -> cloud -> voxel grid -> SOR from the disparity in `disp`; *fin / *fcnt receive the buffers
+//                    that hold the last enabled stage's clouds (nullptr when only disparity was asked for).
+static int enqueue_matcher(cvr_ctx* c, int B, const uint8_t** dl, size_t* lstep, size_t* lfs, const uint8_t* dr, size_t rstep, size_t rfs, int ch)
 {
-    const bool wantCloud = (stages & 2) != 0, wantVox = (stages & 4) != 0, wantSor = (stages & 8) != 0;
-    *fin = nullptr; *fcnt = nullptr;
     int rc;
     if (c->prm.requires_rectification) {                               // ReconstructionSystem.cpp:42-44: everything downstream sees the rectified pair
         if (!c->rect_ready) { c->err = "requires_rectification is set but cvr_set_rectification was not called"; return CVR_ERR_INVALID_ARG; }
         const size_t orow = (size_t)c->sg.W * ch, ofs = orow * c->sg.H;
-        rc = cvr_launch_remap(c, B, ch, dl, lstep, lfs, dr, rstep, rfs, c->d_rect[0], c->d_rect[1], orow, ofs);
+        rc = cvr_launch_remap(c, B, ch, *dl, *lstep, *lfs, dr, rstep, rfs, c->d_rect[0], c->d_rect[1], orow, ofs);
         if (rc) return rc;
-        dl = c->d_rect[0]; dr = c->d_rect[1]; lstep = rstep = orow; lfs = rfs = ofs;
+        *dl = c->d_rect[0]; dr = c->d_rect[1]; *lstep = rstep = orow; *lfs = rfs = ofs;
         cvr_stage_mark(c, "rectify");
     }
-    rc = cvr_launch_gray(c, B, dl, lstep, lfs, dr, rstep, rfs, ch);
+    rc = cvr_launch_gray(c, B, *dl, *lstep, *lfs, dr, rstep, rfs, ch);
     if (rc) return rc;
     cvr_stage_mark(c, "gray");
-    rc = (c->prm.block_matcher == CVR_MATCHER_BM) ? cvr_launch_bm(c, B) : cvr_launch_sgbm(c, B);
+    return (c->prm.block_matcher == CVR_MATCHER_BM) ? cvr_launch_bm(c, B) : cvr_launch_sgbm(c, B);
+}
+
+static int enqueue_filters(cvr_ctx* c, int B, int stages, const int16_t* disp, const uint8_t* dl, size_t lstep, size_t lfs, int ch,
+                           const cvr_point** fin, const int** fcnt)
+{
+    const bool wantCloud = (stages & 2) != 0, wantVox = (stages & 4) != 0, wantSor = (stages & 8) != 0;
+    *fin = nullptr; *fcnt = nullptr;
+    if (!(wantCloud || wantVox || wantSor)) return CVR_OK;
+    int rc = cvr_launch_prune(c, B, disp);
     if (rc) return rc;
-    if (wantCloud || wantVox || wantSor) {
-        rc = cvr_launch_prune(c, B, c->d_med);
+    if (c->prm.cloud_mode == CVR_CLOUD_REPROJECT)
+        rc = cvr_launch_cloud(c, B, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, dl, lstep, lfs, ch);
+    else
+        rc = cvr_launch_cloud(c, B, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, c->d_mask, dl, lstep, lfs, ch);
+    if (rc) return rc;
+    *fin = c->d_cloud; *fcnt = c->d_ncloud;
+    if (wantVox) {
+        rc = cvr_launch_voxel(c, B, *fin, (size_t)c->maxN, *fcnt);
         if (rc) return rc;
-        if (c->prm.cloud_mode == CVR_CLOUD_REPROJECT)
-            rc = cvr_launch_cloud(c, B, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, dl, lstep, lfs, ch);
-        else
-            rc = cvr_launch_cloud(c, B, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, c->d_mask, dl, lstep, lfs, ch);
+        *fin = c->d_vox; *fcnt = c->d_nvox;
+    }
+    if (wantSor) {
+        rc = cvr_launch_sor(c, B, *fin, (size_t)c->maxN, *fcnt, 0);
         if (rc) return rc;
-        *fin = c->d_cloud; *fcnt = c->d_ncloud;
-        if (wantVox) {
-            rc = cvr_launch_voxel(c, B, *fin, (size_t)c->maxN, *fcnt);
-            if (rc) return rc;
-            *fin = c->d_vox; *fcnt = c->d_nvox;
-        }
-        if (wantSor) {
-            rc = cvr_launch_sor(c, B, *fin, (size_t)c->maxN, *fcnt, 0);
-            if (rc) return rc;
-            *fin = c->d_sorout; *fcnt = c->d_nout;
-        }
+        *fin = c->d_sorout; *fcnt = c->d_nout;
     }
     return CVR_OK;
+}
+
+static int enqueue_chain(cvr_ctx* c, int B, int stages, const uint8_t* dl, size_t lstep, size_t lfs, const uint8_t* dr, size_t rstep, size_t rfs, int ch,
+                         const cvr_point** fin, const int** fcnt)
+{
+    *fin = nullptr; *fcnt = nullptr;
+    int rc = enqueue_matcher(c, B, &dl, &lstep, &lfs, dr, rstep, rfs, ch);
+    if (rc) return rc;
+    return enqueue_filters(c, B, stages, c->d_med, dl, lstep, lfs, ch, fin, fcnt);
 }
 
 static int check_batch_args(cvr_ctx* c, int nframes, const cvr_batch* io)
@@ -602,7 +619,7 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     const size_t rowBytes = (size_t)W * ch;
     const int stages = io->stages ? io->stages : 15;
     CVR_CUDA(c, cudaSetDevice(c->device));
-    timers_begin(c);
+    timers_begin(c, 0);
     const uint8_t *dl, *dr; size_t lstep, lfs, rstep, rfs;
     if (io->mem == CVR_MEM_HOST) {
         for (int i = 0; i < B; i++) {
@@ -649,11 +666,10 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     }
     cvr_stage_mark(c, "out");
     rc = sync_check(c);
-    timers_end(c);
+    timers_end(c, 0);
     return rc;
 }
 
-// ---- pipelined host path: two batches in flight, the upload of batch i+1 overlaps the kernels of batch i ----
 static int pipe_init(cvr_ctx* c)
 {
     if (c->pipe_ready) return CVR_OK;
@@ -672,13 +688,16 @@ static int pipe_init(cvr_ctx* c)
     return CVR_OK;
 }
 
+// ---- pipelined path: two batches in flight.  The upload of batch i+1 (copy stream) overlaps the kernels of batch i
+// (compute stream) and the download of batch i-1 (d2h stream).  Measured and rejected: running the filter stages of batch
+// i on a third stream beside the matcher of batch i+1 -- the matcher kernels already saturate HBM, both halves only slow
+// each other down (+1 % device-resident, -6 % end to end).
 extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
 {
     if (!c) return CVR_ERR_INVALID_ARG;
     STEREO_ONLY(c);
     int rc = check_batch_args(c, nframes, io);
     if (rc) return rc;
-    REQUIRE(c, io->mem == CVR_MEM_HOST, "cvr_submit_batch takes host buffers (device-resident data needs no pipelining)");
     CVR_CUDA(c, cudaSetDevice(c->device));
     rc = pipe_init(c);
     if (rc) return rc;
@@ -687,24 +706,52 @@ extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     const int ch = io->channels, W = c->sg.W, H = c->sg.H, B = nframes;
     const size_t rowBytes = (size_t)W * ch;
     const int stages = io->stages ? io->stages : 15;
-    // upload on the copy stream, after the kernels of the batch that last used this slot's staging buffers
-    if (sl.used) CVR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, sl.evDone, 0));
-    for (int i = 0; i < B; i++) {
-        CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[0] + (size_t)i * rowBytes * H, rowBytes, io->left + (size_t)i * io->left_frame_stride, io->left_step, rowBytes, H, cudaMemcpyHostToDevice, c->copy_stream));
-        CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[1] + (size_t)i * rowBytes * H, rowBytes, io->right + (size_t)i * io->right_frame_stride, io->right_step, rowBytes, H, cudaMemcpyHostToDevice, c->copy_stream));
+    const bool host = io->mem == CVR_MEM_HOST;
+    const uint8_t *dl, *dr; size_t lstep, lfs, rstep, rfs;
+    const int tset = 1 + (c->n_submit & 1);
+    if (host) {
+        // upload on the copy stream, after the kernels of the batch that last used this slot's staging buffers
+        if (sl.used) CVR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, sl.evDone, 0));
+        const bool dense = io->left_frame_stride == io->left_step * (size_t)H && io->right_frame_stride == io->right_step * (size_t)H;
+        if (dense) {                                                   // frames back to back: one 2-D copy per camera for the whole batch
+            CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[0], rowBytes, io->left, io->left_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->copy_stream));
+            CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[1], rowBytes, io->right, io->right_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->copy_stream));
+        } else {
+            for (int i = 0; i < B; i++) {
+                CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[0] + (size_t)i * rowBytes * H, rowBytes, io->left + (size_t)i * io->left_frame_stride, io->left_step, rowBytes, H, cudaMemcpyHostToDevice, c->copy_stream));
+                CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[1] + (size_t)i * rowBytes * H, rowBytes, io->right + (size_t)i * io->right_frame_stride, io->right_step, rowBytes, H, cudaMemcpyHostToDevice, c->copy_stream));
+            }
+        }
+        CVR_CUDA(c, cudaEventRecord(sl.evH2D, c->copy_stream));
+        CVR_CUDA(c, cudaStreamWaitEvent(c->stream, sl.evH2D, 0));
+        dl = sl.d_in[0]; dr = sl.d_in[1]; lstep = rstep = rowBytes; lfs = rfs = rowBytes * H;
+    } else {                                                           // device-resident inputs: read in place (the caller keeps them until cvr_wait_batch)
+        dl = io->left; dr = io->right; lstep = io->left_step; rstep = io->right_step; lfs = io->left_frame_stride; rfs = io->right_frame_stride;
     }
-    CVR_CUDA(c, cudaEventRecord(sl.evH2D, c->copy_stream));
-    CVR_CUDA(c, cudaStreamWaitEvent(c->stream, sl.evH2D, 0));
+    timers_begin(c, tset);                                             // stage timers of this slot (read back by cvr_wait_batch)
     const cvr_point* fin = nullptr; const int* fcnt = nullptr;
-    rc = enqueue_chain(c, B, stages, sl.d_in[0], rowBytes, rowBytes * H, sl.d_in[1], rowBytes, rowBytes * H, ch, &fin, &fcnt);
+    rc = enqueue_chain(c, B, stages, dl, lstep, lfs, dr, rstep, rfs, ch, &fin, &fcnt);
     if (rc) return rc;
     sl.hasCloud = fin != nullptr;
-    if (fin) {                                                         // park the results in the slot so the next batch may overwrite the workspace
+    if (fin && host) {                                                 // park the results in the slot so the next batch may overwrite the workspace
         k_copy_clouds<<<dim3(64, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, sl.d_out, (size_t)c->maxN, sl.d_outcnt);
         c->launches++;
+    } else if (fin) {                                                  // device-resident outputs: straight into the caller's buffers
+        if (io->cloud) {
+            k_copy_clouds<<<dim3(64, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, io->cloud, io->cloud_capacity, io->cloud_count);
+            c->launches++;
+        } else if (io->cloud_count) {
+            CVR_CUDA(c, cudaMemcpyAsync(io->cloud_count, fcnt, sizeof(int) * B, cudaMemcpyDeviceToDevice, c->stream));
+        }
     }
-    if (io->disp) CVR_CUDA(c, cudaMemcpyAsync(sl.d_outdisp, c->d_med, (size_t)B * W * H * 2, cudaMemcpyDeviceToDevice, c->stream));
+    if (io->disp && host) CVR_CUDA(c, cudaMemcpyAsync(sl.d_outdisp, c->d_med, (size_t)B * W * H * 2, cudaMemcpyDeviceToDevice, c->stream));
+    if (io->disp && !host)
+        for (int i = 0; i < B; i++)
+            CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io->disp + (size_t)i * io->disp_frame_stride, io->disp_step, c->d_med + (size_t)i * W * H, (size_t)W * 2,
+                                          (size_t)W * 2, H, cudaMemcpyDeviceToDevice, c->stream));
+    cvr_stage_mark(c, "out");
     CVR_CUDA(c, cudaEventRecord(sl.evDone, c->stream));
+    c->tset = 0;
     sl.io = *io; sl.nframes = B; sl.busy = true; sl.used = true;
     c->n_submit++;
     return CVR_OK;
@@ -719,8 +766,14 @@ extern "C" int cvr_wait_batch(cvr_ctx* c)
     const cvr_batch& io = sl.io;
     const int B = sl.nframes, W = c->sg.W, H = c->sg.H;
     CVR_CUDA(c, cudaEventSynchronize(sl.evDone));
+    timers_end(c, 1 + (c->n_wait & 1));
     int* hc = c->h_counts + (size_t)c->maxB * (1 + (c->n_wait & 1));
     int rc = CVR_OK;
+    if (io.mem != CVR_MEM_HOST) {                                      // device-resident batch: the results are already in the caller's buffers
+        sl.busy = false;
+        c->n_wait++;
+        return CVR_OK;
+    }
     if (sl.hasCloud && (io.cloud || io.cloud_count)) {
         CVR_CUDA(c, cudaMemcpyAsync(hc, sl.d_outcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, c->d2h_stream));
         CVR_CUDA(c, cudaStreamSynchronize(c->d2h_stream));

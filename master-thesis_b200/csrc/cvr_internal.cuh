@@ -82,7 +82,7 @@ struct PipeSlot {
     cvr_point* d_out;        // filtered clouds [B][maxN]
     int* d_outcnt;           // [B]
     int16_t* d_outdisp;      // [B][H][W]
-    cudaEvent_t evH2D, evDone;
+    cudaEvent_t evH2D, evDone;   // inputs uploaded / results parked, slot reusable
     bool busy, used;
     cvr_batch io;
     int nframes;
@@ -102,8 +102,9 @@ struct cvr_ctx {
     std::string err;
     long long launches;
     bool profiling;
-    std::vector<StageTimer> timers;
-    int timers_used;
+    std::vector<StageTimer> timers[3];   // event timers of the synchronous calls [0] and of the two pipeline slots [1], [2]
+    int timers_used[3];
+    int tset;                            // the set cvr_stage_mark appends to
     std::vector<std::string> t_names;
     std::vector<float> t_ms;
 

@@ -850,7 +850,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     k_fill_s16<<<(unsigned)cvr_div_up_sz(npix, 256), 256, 0, c->stream>>>(c->d_raw, npix, p.INVALID);
     LAUNCH_CHECK(c);
     {
-        int nseg = (p.W1 + 160) / 320;
+        static const int segLen = getenv("CVR_HSUM_SEG") ? atoi(getenv("CVR_HSUM_SEG")) : 320;   // tuning hook
+        int nseg = (p.W1 + segLen / 2) / segLen;
         if (nseg < 1) nseg = 1;
         const int segMax = cvr_div_up(p.W1, nseg) + 1;
         const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;

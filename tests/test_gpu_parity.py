@@ -322,6 +322,56 @@ def test_pipelined_submit_wait_equals_synchronous(cvr, oracle):
     rec.close()
 
 
+@pytest.mark.parametrize("rect", [False, True])
+def test_pipelined_device_resident_batches(cvr, oracle, rect):
+    """cvr_submit_batch with DEVICE buffers: inputs are read in place, outputs land in the caller's device buffers; the
+    matcher of batch i+1 overlaps the filters of batch i (with rectification: shares the rectified-image buffer)."""
+    import torch
+    H, W, D, bs, B, NB = 60, 330, 64, 9, 3, 5
+    cfg = _cfg(bs, D, k=8)
+    cfg["requires_rectification"] = rect
+    rec = cvr.Reconstruct3D(W, H, config=cfg, max_batch=B, voxel_leaf=0.05)
+    if rect:
+        K = np.array([[300.0, 0, 165.0], [0, 300.0, 30.0], [0, 0, 1]])
+        P = np.array([[295.0, 0, 163.0, 0], [0, 295.0, 31.0, 0], [0, 0, 1, 0]])
+        rec.SetRectification(K, [-0.05, 0.01, 0.0003, -0.0002, 0.0], np.eye(3), P, K, [-0.04, 0.012, -0.0001, 0.0002, 0.0], np.eye(3), P)
+    batches = []
+    for nb in range(NB):
+        Ls, Rs = zip(*[oracle.synth_pair(H, W, D, seed=170 + nb * B + i, color=True) for i in range(B)])
+        batches.append((np.stack(Ls), np.stack(Rs)))
+    want = [rec.ProcessFrames(L, R, want_disp=True) for (L, R) in batches]
+    cap = W * H
+    dev = torch.device("cuda", 0)
+    ios, outs, keep = [], [], []
+    for (L, R) in batches:
+        dL, dR = torch.from_numpy(L).to(dev), torch.from_numpy(R).to(dev)
+        disp = torch.empty((B, H, W), dtype=torch.int16, device=dev)
+        clouds = torch.zeros((B, cap, 16), dtype=torch.uint8, device=dev)
+        counts = torch.zeros(B, dtype=torch.int32, device=dev)
+        io = cvr.Batch()
+        io.mem, io.channels = cvr.MEM_DEVICE, 3
+        io.left, io.left_step, io.left_frame_stride = dL.data_ptr(), W * 3, W * H * 3
+        io.right, io.right_step, io.right_frame_stride = dR.data_ptr(), W * 3, W * H * 3
+        io.disp, io.disp_step, io.disp_frame_stride = disp.data_ptr(), W * 2, W * H * 2
+        io.cloud, io.cloud_capacity, io.cloud_count = clouds.data_ptr(), cap, counts.data_ptr()
+        io.stages = 15
+        ios.append(io); outs.append((disp, clouds, counts)); keep.append((dL, dR))
+    torch.cuda.synchronize()
+    rec.submit_batch_raw(ios[0], B)
+    for nb in range(1, NB):
+        rec.submit_batch_raw(ios[nb], B)
+        rec.wait_batch()
+    rec.wait_batch()
+    for nb in range(NB):
+        disp, clouds, counts = (t.cpu().numpy() for t in outs[nb])
+        wd, wc = want[nb]
+        assert np.array_equal(disp, wd), "batch %d" % nb
+        for i in range(B):
+            got = clouds[i, :counts[i]].reshape(-1).view(cvr.POINT_DTYPE)
+            assert counts[i] == len(wc[i]) and np.array_equal(got, wc[i]), "batch %d frame %d" % (nb, i)
+    rec.close()
+
+
 def _bm_cfg(p):
     return dict(block_matcher=1, window_size=p["blockSize"], bm_num_disparities=p["numDisparities"], bm_min_disparity=p["minDisparity"],
                 bm_pre_filter_cap=p["preFilterCap"], bm_texture_threshold=p["textureThreshold"], bm_uniqueness_ratio=p["uniquenessRatio"],
