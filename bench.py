@@ -346,9 +346,9 @@ def main():
         roof = None
         if kv_ms:
             ach = alg_bytes / (kv_ms * 1e-3) / 1e9
-            # DRAM traffic of this kernel from the committed ncu --set full capture (profiles/r01d_top_kernels_raw.csv:
-            # dram__bytes_read.sum + dram__bytes_write.sum = 7.702 + 3.809 GB for a 36-frame launch), scaled to this batch
-            traffic = (7.701787e9 + 3.808850e9) / 36.0 * B
+            # DRAM traffic of this kernel from the committed ncu --set full capture (profiles/r01f_k_path_v3_raw.csv:
+            # dram__bytes_read.sum + dram__bytes_write.sum = 22.245 + 11.087 GB for a 104-frame launch), scaled to this batch
+            traffic = (22.245403e9 + 11.087477e9) / 104.0 * B
             roof = {"bound": "hbm", "kernel": "k_path_v3<4,false,false,false,true,1024>", "achieved": ach, "peak": peak, "peak_kind": peak_kind,
                     "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": kv_ms,
                     "share_of_step": kv_ms / (ms_dev / args.steps)}
