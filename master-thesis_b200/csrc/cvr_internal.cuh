@@ -162,6 +162,7 @@ struct cvr_ctx {
     int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
     int smem_optin;          // max dynamic shared memory per block (opt-in)
     bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)
+    size_t hsum_smem_set;    // dynamic shared memory k_pix_hsum has been opted in to on this context's device
     bool keep_S;             // CVR_KEEP_S=1: the last aggregation pass also writes the final S volume (cvr_debug_fetch(1); test hook)
     bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)

@@ -856,7 +856,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         const int segMax = cvr_div_up(p.W1, nseg) + 1;
         const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;
         const size_t smem = (nLmax + nRmax + 2) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)2 * p.ring * p.Dp;   // descriptors + two rings of 16-bit cost pairs
-        static size_t smem_set = 0;
+        size_t& smem_set = c->hsum_smem_set;                          // per context: the attribute belongs to this context's device
         if (smem > 48 * 1024 && smem > smem_set) {
             CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             smem_set = smem;
