@@ -166,7 +166,7 @@ struct cvr_ctx {
     bool keep_S;             // CVR_KEEP_S=1: the last aggregation pass also writes the final S volume (cvr_debug_fetch(1); test hook)
     bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)
-    int pathv_active[3][9];  // concurrent clusters of the vertical path kernel per (CTA size, cluster size): 0 = not asked yet, -1 = cannot run
+    int pathv_active[3][17]; // concurrent clusters of the vertical path kernel per (CTA size, cluster size): 0 = not asked yet, -1 = cannot run
     int path_v_variant;      // 3 = point-to-point edge hand-over (default), 2 = per-row cluster barrier (CVR_PATH_KERNELS=v2)
 };
 

@@ -686,7 +686,7 @@ static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512)
         const int NT = nts[ni], NW = NT / 32;
         if (NT > 512 && p.Dp > 128) continue;                          // wide disparity ranges need > 64 registers per thread
         double best = 0;
-        for (int CL = 8; CL >= 1; CL--) {
+        for (int CL = 16; CL >= 1; CL--) {                              // 9..16: non-portable cluster sizes (wide disparity ranges at HD need them)
             if (forced && CL != forced) continue;
             if (CL * NW > p.W1) continue;                              // every warp must own at least one column
             VState vs;
@@ -696,7 +696,8 @@ static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512)
             if (act == 0) {                                            // not asked yet
                 K kernel = NT > 512 ? kernel1024 : kernel512;
                 act = -1;
-                if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess) {
+                if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess &&
+                    (CL <= 8 || cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess)) {
                     cudaLaunchConfig_t cfg = {};
                     cfg.gridDim = dim3(CL, 64, 1); cfg.blockDim = dim3(NT, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = c->stream;
                     cudaLaunchAttribute at[1];
@@ -724,6 +725,10 @@ static cudaError_t launch_cluster(K kernel, int CL, int B, int NT, size_t smem, 
 {
     cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+    if (CL > 8) {
+        e = cudaFuncSetAttribute(kernel, cudaFuncAttributeNonPortableClusterSizeAllowed, 1);
+        if (e != cudaSuccess) return e;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(CL, B, 1); cfg.blockDim = dim3(NT, 1, 1); cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute at[1];
