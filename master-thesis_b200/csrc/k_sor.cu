@@ -138,8 +138,23 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
                         float d2 = __fmul_rn(dx, dx);
                         d2 = __fadd_rn(d2, __fmul_rn(dy, dy));
                         d2 = __fadd_rn(d2, __fmul_rn(dz, dz));
-                        if (cnt < K1) { int pz = cnt++; while (pz > 0 && best[pz - 1] > d2) { best[pz] = best[pz - 1]; pz--; } best[pz] = d2; }
-                        else if (d2 < best[K1 - 1]) { int pz = K1 - 1; while (pz > 0 && best[pz - 1] > d2) { best[pz] = best[pz - 1]; pz--; } best[pz] = d2; }
+                        // binary max-heap of the K1 smallest squared distances seen so far (root = the largest of them)
+                        if (cnt < K1) {
+                            int pz = cnt++;
+                            while (pz > 0) { const int par = (pz - 1) >> 1; const float pv = best[par]; if (pv >= d2) break; best[pz] = pv; pz = par; }
+                            best[pz] = d2;
+                        } else if (d2 < best[0]) {
+                            int pz = 0;
+                            for (;;) {
+                                int ch = 2 * pz + 1;
+                                if (ch >= K1) break;
+                                float cv = best[ch];
+                                if (ch + 1 < K1) { const float c2 = best[ch + 1]; if (c2 > cv) { cv = c2; ch++; } }
+                                if (cv <= d2) break;
+                                best[pz] = cv; pz = ch;
+                            }
+                            best[pz] = d2;
+                        }
                     }
                 }
             }
@@ -148,8 +163,23 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
             // every unvisited point lies outside the cube of half-width R*cell around the query's cell, hence farther
             // than R*cell; the 1e-5 margin covers the f32 rounding of both sides
             const float lim = (float)R * g.cell;
-            if (best[K1 - 1] <= lim * lim * (1.0f - 1e-5f)) break;
+            if (best[0] <= lim * lim * (1.0f - 1e-5f)) break;
         }
+    }
+    // heap sort in place (ascending), so that the sum below runs in the order PCL's sorted neighbour list gives it
+    for (int m = K1 - 1; m > 0; m--) {
+        const float v = best[m];
+        best[m] = best[0];
+        int pz = 0;
+        for (;;) {
+            int ch = 2 * pz + 1;
+            if (ch >= m) break;
+            float cv = best[ch];
+            if (ch + 1 < m) { const float c2 = best[ch + 1]; if (c2 > cv) { cv = c2; ch++; } }
+            if (cv <= v) break;
+            best[pz] = cv; pz = ch;
+        }
+        best[pz] = v;
     }
     double s = 0.0;
     for (int j = 1; j < K1; j++) s = __dadd_rn(s, (double)__fsqrt_rn(best[j]));
