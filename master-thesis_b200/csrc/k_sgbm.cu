@@ -122,32 +122,29 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
         const unsigned m = __vmins2(c0, c1);
         return (m & 0xffffu) + (m >> 18);                                     // Sobel-channel cost + (intensity cost >> 2), <= 255
     };
-    auto pixcost2 = [&](int xp, unsigned& c8) -> unsigned {                   // packed pair of costs; c8 = the same as two bytes
+    auto pixcost2 = [&](int xp) -> unsigned {                                 // the costs of (d, d + 1) as a packed 16-bit pair
         const uint4 l = Lpk[xp + offL];
-        const unsigned ca = cost1(l, Rpk[rswz(xp + offR)]), cb = cost1(l, Rpk[rswz(xp + offR - 1)]);
-        c8 = ca | (cb << 8);
-        return ca | (cb << 16);
+        return cost1(l, Rpk[rswz(xp + offR)]) | (cost1(l, Rpk[rswz(xp + offR - 1)]) << 16);
     };
-    auto widen = [](unsigned c8) -> unsigned { return (c8 & 0xffu) | ((c8 & 0xff00u) << 8); };
-    uint16_t* ring = (uint16_t*)ringbuf + (size_t)grp * p.ring * half + q;      // [ring slots][Dp/2] per group
-    const int ringLen = p.ring * half;
+    // ring of the last bs + 1 cost pairs per thread: p.ring slots (a power of two), slot s of this thread at ring[s * half]
+    unsigned* ring = (unsigned*)ringbuf + (size_t)grp * p.ring * half + q;
+    const int mask = p.ring - 1, bs = p.bs;
     unsigned run = 0;                                                         // two running sums (each < 2^15: provably unsaturated)
     const int j0 = hs_ - SW2, j1 = he_ - 1 + SW2;
     // warm-up: the first bs - 1 window elements (clamped at the left image border), nothing to emit or to drop yet
-    int j = j0, wi = 0;                                                       // wi: index of the ring slot written next
+    int j = j0, ws = 0;                                                       // ws: the ring slot written next
     for (; j < hs_ + SW2; j++) {
-        unsigned c8;
-        run += pixcost2(min(max(j, 0), W1 - 1), c8);
-        ring[wi] = (uint16_t)c8;
-        wi += half; if (wi == ringLen) wi = 0;
+        const unsigned cp = pixcost2(min(max(j, 0), W1 - 1));
+        run += cp;
+        ring[ws * half] = cp;
+        ws = (ws + 1) & mask;
     }
     // steady state: one new element, one output; from the second output on the element leaving the window is dropped.
     unsigned* o = out + (size_t)hs_ * half;
-    int ri = 0;                                                               // index of the ring slot holding element j - bs
     {
-        unsigned c8;
-        run += pixcost2(min(j, W1 - 1), c8);
-        ring[wi] = (uint16_t)c8; wi += half; if (wi == ringLen) wi = 0;
+        const unsigned cp = pixcost2(min(j, W1 - 1));
+        run += cp;
+        ring[ws * half] = cp; ws = (ws + 1) & mask;
         *o = run; o += half; j++;
     }
     const int jmid = min(j1, W1 - 1);
@@ -155,22 +152,19 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
     int ridx = j + offR;
     for (; j <= jmid; j++, lp++, ridx++, o += half) {                         // no clamping while j <= W1 - 1
         const uint4 l = *lp;
-        const unsigned ca = cost1(l, Rpk[rswz(ridx)]), cb = cost1(l, Rpk[rswz(ridx - 1)]);
-        run = run + (ca | (cb << 16)) - widen(ring[ri]);
-        ring[wi] = (uint16_t)(ca | (cb << 8));
+        const unsigned cp = cost1(l, Rpk[rswz(ridx)]) | (cost1(l, Rpk[rswz(ridx - 1)]) << 16);
+        run = run + cp - ring[((ws - bs) & mask) * half];                     // the element written bs steps ago leaves the window
+        ring[ws * half] = cp;
         *o = run;
-        wi += half; if (wi == ringLen) wi = 0;
-        ri += half; if (ri == ringLen) ri = 0;
+        ws = (ws + 1) & mask;
     }
     if (j <= j1) {                                                            // right image border: the last column repeats
-        unsigned c8;
-        const unsigned cl = pixcost2(W1 - 1, c8);
+        const unsigned cl = pixcost2(W1 - 1);
         for (; j <= j1; j++, o += half) {
-            run = run + cl - widen(ring[ri]);
-            ring[wi] = (uint16_t)c8;
+            run = run + cl - ring[((ws - bs) & mask) * half];
+            ring[ws * half] = cl;
             *o = run;
-            wi += half; if (wi == ringLen) wi = 0;
-            ri += half; if (ri == ringLen) ri = 0;
+            ws = (ws + 1) & mask;
         }
     }
 }
@@ -860,7 +854,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         if (nseg < 1) nseg = 1;
         const int segMax = cvr_div_up(p.W1, nseg) + 1;
         const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;
-        const size_t smem = (nLmax + nRmax + 2) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)2 * p.ring * p.Dp;   // descriptors + two rings of 16-bit cost pairs
+        const size_t smem = (nLmax + nRmax + 2) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)4 * p.ring * p.Dp;   // descriptors + two rings (one per thread group) of packed cost pairs
         size_t& smem_set = c->hsum_smem_set;                          // per context: the attribute belongs to this context's device
         if (smem > 48 * 1024 && smem > smem_set) {
             CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
