@@ -49,10 +49,9 @@ __device__ __forceinline__ unsigned pk_neg(unsigned a) { return __vneg2(a); }
 // CTAs fit on an SM.  The horizontal block sum is a sliding window over j = s - SW2 .. e - 1 + SW2 with the column index
 // clamped to [0, W1-1] exactly like OpenCV's clamped recurrence (closed form: provably unsaturated, see cvr_create).
 // Right-image descriptors are read at a stride of two entries (a thread owns two adjacent disparities), which would put
-// the 8 lanes of a 128-bit load phase on 4 bank groups; flipping the lowest index bit in every other block of 8 entries
-// spreads any 8 stride-2 entries over all 8 groups.
-__device__ __forceinline__ int rswz(int i) { return i ^ ((i >> 3) & 1); }
-
+// the 8 lanes of a 128-bit load phase on 4 bank groups.  They are therefore kept as two arrays, entries of even and of odd
+// index: for a given column all threads read the same parity, i.e. consecutive entries of one array (conflict free), and
+// of the four descriptors two neighbouring columns need, two are the same entry.
 __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStride, int16_t* __restrict__ hsum, SgbmDev p, int nseg)
 {
     extern __shared__ uint4 sm4[];
@@ -65,7 +64,10 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
     const int nL = xl1 - xl0 + 1, nR = xr1 - xr0 + 1;
     uint4* Lpk = sm4;                                   // [nL]
     uint4* Rpk = sm4 + nL;                              // [nR]
-    unsigned* aL = (unsigned*)(Rpk + nR + 2);           // [nL + 2]  packed (G | R << 16) of left pixels xl0-1 .. xl1+1 (Rpk: swizzled, up to nR + 1)
+    const int nRh = (nR + 3) >> 1;                      // entries per parity array (index -1 is never read: see offR below)
+    uint4* const Rev = Rpk;                             // R[2j]
+    uint4* const Rod = Rpk + nRh;                       // R[2j + 1]
+    unsigned* aL = (unsigned*)(Rpk + 2 * nRh);          // [nL + 2]  packed (G | R << 16) of left pixels xl0-1 .. xl1+1
     unsigned* aR = aL + nL + 2;                         // [nR + 2]
     uint8_t* ringbuf = (uint8_t*)(aR + nR + 2);
     const int tid = threadIdx.x, nt = blockDim.x;
@@ -97,7 +99,7 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
         const unsigned ul = x > 0 ? (((u + a[-1]) >> 1) & 0x7fff7fffu) : u;
         const unsigned ur = x < W - 1 ? (((u + a[1]) >> 1) & 0x7fff7fffu) : u;
         const unsigned u0 = __vimin3_s16x2(ul, ur, u), u1 = __vimax3_s16x2(ul, ur, u);
-        (right ? Rpk : Lpk)[right ? rswz(j) : j] = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
+        (right ? ((j & 1) ? Rod : Rev) : Lpk)[right ? (j >> 1) : j] = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
     }
     __syncthreads();
 
@@ -124,7 +126,9 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
     };
     auto pixcost2 = [&](int xp) -> unsigned {                                 // the costs of (d, d + 1) as a packed 16-bit pair
         const uint4 l = Lpk[xp + offL];
-        return cost1(l, Rpk[rswz(xp + offR)]) | (cost1(l, Rpk[rswz(xp + offR - 1)]) << 16);
+        const int i = xp + offR;                                              // right descriptor of disparity d; d + 1 uses i - 1
+        const uint4 ra = (i & 1) ? Rod[i >> 1] : Rev[i >> 1], rb = (i & 1) ? Rev[i >> 1] : Rod[(i >> 1) - 1];
+        return cost1(l, ra) | (cost1(l, rb) << 16);
     };
     // ring of the last bs + 1 cost pairs per thread: p.ring slots (a power of two), slot s of this thread at ring[s * half]
     unsigned* ring = (unsigned*)ringbuf + (size_t)grp * p.ring * half + q;
@@ -148,24 +152,27 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
         *o = run; o += half; j++;
     }
     const int jmid = min(j1, W1 - 1);
-    const uint4* lp = Lpk + (j + offL);
-    int ridx = j + offR;
-    for (; j <= jmid; j++, lp++, ridx++, o += half) {                         // no clamping while j <= W1 - 1
-        const uint4 l = *lp;
-        const unsigned cp = cost1(l, Rpk[rswz(ridx)]) | (cost1(l, Rpk[rswz(ridx - 1)]) << 16);
+    auto emit = [&](unsigned cp) {                                            // one steady-state step with the cost pair of element j
         run = run + cp - ring[((ws - bs) & mask) * half];                     // the element written bs steps ago leaves the window
         ring[ws * half] = cp;
-        *o = run;
+        *o = run; o += half;
         ws = (ws + 1) & mask;
+    };
+    if (j <= jmid && ((j + offR) & 1)) { emit(pixcost2(j)); j++; }            // make the right index even
+    {
+        const uint4* lp = Lpk + (j + offL);
+        const uint4* ev = Rev + ((j + offR) >> 1);
+        const uint4* od = Rod + ((j + offR) >> 1);
+        for (; j + 1 <= jmid; j += 2, lp += 2, ev++, od++) {                  // two columns per turn: right indices 2m and 2m + 1
+            const uint4 l0 = lp[0], l1 = lp[1], e0 = ev[0], o0 = od[-1], o1 = od[0];
+            emit(cost1(l0, e0) | (cost1(l0, o0) << 16));                      // column j    : d -> R[2m],     d + 1 -> R[2m - 1]
+            emit(cost1(l1, o1) | (cost1(l1, e0) << 16));                      // column j + 1: d -> R[2m + 1], d + 1 -> R[2m]
+        }
     }
+    if (j <= jmid) { emit(pixcost2(j)); j++; }
     if (j <= j1) {                                                            // right image border: the last column repeats
         const unsigned cl = pixcost2(W1 - 1);
-        for (; j <= j1; j++, o += half) {
-            run = run + cl - ring[((ws - bs) & mask) * half];
-            ring[ws * half] = cl;
-            *o = run;
-            ws = (ws + 1) & mask;
-        }
+        for (; j <= j1; j++) emit(cl);
     }
 }
 
@@ -854,7 +861,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         if (nseg < 1) nseg = 1;
         const int segMax = cvr_div_up(p.W1, nseg) + 1;
         const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;
-        const size_t smem = (nLmax + nRmax + 2) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)4 * p.ring * p.Dp;   // descriptors + two rings (one per thread group) of packed cost pairs
+        const size_t smem = (nLmax + nRmax + 4) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)4 * p.ring * p.Dp;   // descriptors + two rings (one per thread group) of packed cost pairs
         size_t& smem_set = c->hsum_smem_set;                          // per context: the attribute belongs to this context's device
         if (smem > 48 * 1024 && smem > smem_set) {
             CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
