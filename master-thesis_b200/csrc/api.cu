@@ -154,7 +154,7 @@ static void free_all(cvr_ctx* c)
 {
     void* ptrs[] = { c->d_in[0], c->d_in[1], c->d_gray, c->d_volA, c->d_volC, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, c->d_disp, c->d_med,
                      c->d_label, c->d_size, c->d_pruned, c->d_dispf, c->d_mask, c->d_pstats, c->d_rowcnt, c->d_cloud, c->d_ncloud, c->d_vhdr,
-                     c->d_keys[0], c->d_keys[1], c->d_vals[0], c->d_vals[1], c->d_hist, c->d_segstart, c->d_vox, c->d_cellstart, c->d_cellidx,
+                     c->d_keys[0], c->d_keys[1], c->d_vals[0], c->d_vals[1], c->d_hist, c->d_segstart, c->d_vox, c->d_cellstart, c->d_scanaux, c->d_cellidx,
                      c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags, c->d_bmpre,
                      c->d_rmap1[0], c->d_rmap1[1], c->d_rmap2[0], c->d_rmap2[1], c->d_rect[0], c->d_rect[1] };
     for (void* p : ptrs) if (p) cudaFree(p);
@@ -226,7 +226,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     A(dalloc(&c->d_keys[0], B * N)); A(dalloc(&c->d_keys[1], B * N)); A(dalloc(&c->d_vals[0], B * N)); A(dalloc(&c->d_vals[1], B * N));
     A(dalloc(&c->d_hist, B * (256 * nRuns + 1)));
     A(dalloc(&c->d_segstart, B * (N + 1))); A(dalloc(&c->d_vox, B * N));
-    A(dalloc(&c->d_cellstart, B * 2 * ((size_t)c->sor_grid_cap + 2))); A(dalloc(&c->d_cellidx, B * N));
+    A(dalloc(&c->d_cellstart, B * 2 * ((size_t)c->sor_grid_cap + 2))); A(dalloc(&c->d_scanaux, B * ((size_t)c->sor_grid_cap / 1024 + 4))); A(dalloc(&c->d_cellidx, B * N));
     A(dalloc(&c->d_meand, B * N)); A(dalloc(&c->d_sstats, B)); A(dalloc(&c->d_sorout, B * N));
     A(dalloc(&c->d_nout, B)); A(dalloc(&c->d_nvox, B)); A(dalloc(&c->d_spts, B * N));
     A(dalloc(&c->d_flags, B * 64));

@@ -140,6 +140,7 @@ struct cvr_ctx {
     cvr_point* d_vox;        // voxel output [B][H*W]
     // sor
     int* d_cellstart;        // grid cell starts [B][cells+1]
+    int* d_scanaux;          // chunk totals of the two-level cell scan [B][cells/1024 + 3]
     int* d_cellidx;          // point -> cell id
     float* d_meand;          // mean kNN distance [B][H*W]
     SorStats* d_sstats;      // [B]

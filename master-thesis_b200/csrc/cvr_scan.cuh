@@ -53,6 +53,31 @@ static __global__ void k_scan_excl(int* data, size_t frameStride, int maxLen, co
     if (threadIdx.x == 0) d[len] = carry;
 }
 
+// Two-level form of k_scan_excl for long arrays (the cell table of a multi-million-point cloud): k_scan_chunks scans
+// chunks of 1024 in place and writes the chunk totals to aux[b][chunk]; k_scan_excl turns those into chunk offsets (and the
+// grand total in aux[b][nChunks]); k_scan_addoff adds them and stores the total at data[b][len].  grid = (nChunks, B).
+static __global__ void __launch_bounds__(1024) k_scan_chunks(int* data, size_t frameStride, int maxLen, const int* lenPtr, int* aux, size_t auxStride)
+{
+    __shared__ int ws[33];
+    const int b = blockIdx.y, i = blockIdx.x * 1024 + threadIdx.x;
+    int* d = data + (size_t)b * frameStride;
+    const int len = lenPtr ? min(maxLen, lenPtr[b]) : maxLen;
+    const int v = i < len ? d[i] : 0;
+    int tot;
+    const int e = block_excl_scan(v, ws, &tot);
+    if (i < len) d[i] = e;
+    if (threadIdx.x == 0) aux[(size_t)b * auxStride + blockIdx.x] = tot;
+}
+static __global__ void __launch_bounds__(1024) k_scan_addoff(int* data, size_t frameStride, int maxLen, const int* lenPtr, const int* aux, size_t auxStride,
+                                                             int nChunks)
+{
+    const int b = blockIdx.y, i = blockIdx.x * 1024 + threadIdx.x;
+    int* d = data + (size_t)b * frameStride;
+    const int len = lenPtr ? min(maxLen, lenPtr[b]) : maxLen;
+    if (i < len) d[i] += aux[(size_t)b * auxStride + blockIdx.x];
+    if (i == len) d[len] = aux[(size_t)b * auxStride + nChunks];
+}
+
 // ---- per-frame bounding box of a point array (float min/max through an order-preserving uint mapping) ----
 __device__ __forceinline__ unsigned f2ord(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
 __device__ __forceinline__ float ord2f(unsigned u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }

@@ -231,6 +231,25 @@ __global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_write(const cvr_point* __
     if (blockIdx.x == 0 && threadIdx.x == 0) { const int m = blkoff[(size_t)b * cntStride + nblk]; nOut[b] = m; st[b].kept = m; }
 }
 
+// exclusive scan of the per-frame cell counts: one CTA per frame while the table is short, two levels when it is long
+static int scan_cells(cvr_ctx* c, int B, int* cellstart, size_t cellStride, int cap, const int* ncell)
+{
+    if (cap <= 32768) {
+        k_scan_excl<<<B, 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, 1);
+        LAUNCH_CHECK(c);
+        return CVR_OK;
+    }
+    const int nChunks = cvr_div_up(cap, 1024) + 1;                    // + 1: the chunk that holds index len when len == cap
+    const size_t auxStride = (size_t)nChunks + 1;
+    k_scan_chunks<<<dim3(nChunks, B), 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, c->d_scanaux, auxStride);
+    LAUNCH_CHECK(c);
+    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_scanaux, auxStride, nChunks, nullptr, 1);
+    LAUNCH_CHECK(c);
+    k_scan_addoff<<<dim3(nChunks, B), 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, c->d_scanaux, auxStride, nChunks);
+    LAUNCH_CHECK(c);
+    return CVR_OK;
+}
+
 int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, int /*unused*/)
 {
     const int maxN = c->maxN;
@@ -256,8 +275,7 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     LAUNCH_CHECK(c);
     k_sor_cellcount<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
     LAUNCH_CHECK(c);
-    k_scan_excl<<<B, 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, 1);
-    LAUNCH_CHECK(c);
+    { const int rcs = scan_cells(c, B, cellstart, cellStride, cap, ncell); if (rcs) return rcs; }
     k_sor_scatter<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
     LAUNCH_CHECK(c);
     const float4* sp = c->d_spts;
@@ -365,8 +383,7 @@ int cvr_launch_ror(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     LAUNCH_CHECK(c);
     k_sor_cellcount<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
     LAUNCH_CHECK(c);
-    k_scan_excl<<<B, 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, 1);
-    LAUNCH_CHECK(c);
+    { const int rcs = scan_cells(c, B, cellstart, cellStride, cap, ncell); if (rcs) return rcs; }
     k_sor_scatter<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
     LAUNCH_CHECK(c);
     k_ror_count<<<dim3(cvr_div_up(maxN, 128), B), 128, 0, c->stream>>>(c->d_spts, ptStride, grid, cellstart, cellStride, radius, min_pts, c->d_meand);
