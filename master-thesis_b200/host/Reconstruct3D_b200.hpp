@@ -77,7 +77,7 @@ public:
         p.tri_b = calib.T0; p.tri_cx = calib.cxL; p.tri_cy = calib.cyL;
         p.sor_mean_k = cfg.OutlierMinK; p.sor_stddev_mul = cfg.OutlierStdDevThreshold;
         p.max_batch = maxBatch;
-        m_width = width; m_height = height;
+        m_width = width; m_height = height; m_params = p; m_device = device;
         if (cvr_create(&p, device, &m_ctx) != CVR_OK) throw std::runtime_error(std::string("Reconstruct3D: ") + cvr_last_error(nullptr));
     }
     ~Reconstruct3D() { cvr_destroy(m_ctx); }
@@ -155,10 +155,63 @@ public:
         if (camNumber == 1) { fx = m_calib.fxR; fy = m_calib.fyR; cx = m_calib.cxR; cy = m_calib.cyR; }
         else { fx = m_calib.fxL; fy = m_calib.fyL; cx = m_calib.cxL; cy = m_calib.cyL; }
     }
+    // pcl::PointXYZRGB TriangulateUV(float u, float v, float disparity, const cv::Vec3b& color) const (Reconstruct3D.cpp:305-328):
+    // the single-point form of Triangulate3D the sparse tracker calls; host arithmetic, same operation order.
+    cvr_point TriangulateUV(float u, float v, float disparity, const uint8_t colorBGR[3]) const
+    {
+        const float b = m_calib.T0, f = (m_calib.fxL + m_calib.fyL) / 2.0f;
+        cvr_point pt;
+        pt.z = f * b / disparity;
+        pt.x = (u - m_calib.cxL) * (pt.z / f);
+        pt.y = -(v - m_calib.cyL) * (pt.z / f);
+        pt.r = colorBGR[2]; pt.g = colorBGR[1]; pt.b = colorBGR[0]; pt.a = 255;
+        return pt;
+    }
+    // pcl::PointXYZ BackProjectPoint(float x, float y) const (Reconstruct3D.cpp:283-302): the ray through pixel (x, y) at Z = 1
+    void BackProjectPoint(float x, float y, float xyz[3]) const
+    {
+        const float Z = 1.0f;
+        xyz[0] = (x - m_calib.cxL) * Z / m_calib.fxL; xyz[1] = (y - m_calib.cyL) * Z / m_calib.fyL; xyz[2] = Z;
+    }
+    // The three setters (Reconstruct3D.cpp:364-388) act on the cv::StereoMatcher the reference holds; here the workspace
+    // depends on these parameters, so the context is rebuilt (rectification maps, if any, must be set again).
+    void SetStereoBMWindowSize(int size)        // m_StereoMatcher->setBlockSize(size): whichever matcher is active
+    {
+        if (m_params.block_matcher == CVR_MATCHER_BM) m_params.bm_window_size = size; else m_params.sgbm.block_size = size;
+        rebuild();
+    }
+    void SetStereoBMNumDisparities(int num)     // m_StereoMatcher->setNumDisparities(num)
+    {
+        if (m_params.block_matcher == CVR_MATCHER_BM) m_params.bm_num_disparities = num; else m_params.sgbm.num_disparities = num;
+        rebuild();
+    }
+    void SetBlockMatcherType(StereoBlockMatcherType type)   // a NEW matcher with OpenCV's defaults, as the reference creates it
+    {
+        if (type == STEREO_BLOCK_MATCHER) {                  // cv::StereoBM::create(16, 21)
+            m_params.block_matcher = CVR_MATCHER_BM; m_params.bm_num_disparities = 16; m_params.bm_window_size = 21;
+            m_params.bm_min_disparity = 0; m_params.bm_pre_filter_cap = 31; m_params.bm_texture_threshold = 10; m_params.bm_uniqueness_ratio = 15;
+            m_params.bm_speckle_window_size = 0; m_params.bm_speckle_range = 0;
+        } else {                                             // cv::StereoSGBM::create(0, 16, 3): every other parameter 0, MODE_SGBM
+            m_params.block_matcher = CVR_MATCHER_SGBM;
+            m_params.sgbm.min_disparity = 0; m_params.sgbm.num_disparities = 16; m_params.sgbm.block_size = 3; m_params.sgbm.P1 = 0; m_params.sgbm.P2 = 0;
+            m_params.sgbm.disp12_max_diff = 0; m_params.sgbm.pre_filter_cap = 0; m_params.sgbm.uniqueness_ratio = 0;
+            m_params.sgbm.speckle_window_size = 0; m_params.sgbm.speckle_range = 0; m_params.sgbm.mode = CVR_MODE_SGBM;
+        }
+        rebuild();
+    }
     cvr_ctx* context() const { return m_ctx; }
 
 private:
     void check(int rc) const { if (rc != CVR_OK) throw std::runtime_error(std::string("cvrecon_b200: ") + cvr_last_error(m_ctx)); }
+    void rebuild()
+    {
+        cvr_ctx* fresh = nullptr;
+        if (cvr_create(&m_params, m_device, &fresh) != CVR_OK) throw std::runtime_error(std::string("Reconstruct3D: ") + cvr_last_error(nullptr));
+        cvr_destroy(m_ctx);
+        m_ctx = fresh;
+    }
+    cvr_params m_params;
+    int m_device = 0;
     cvr_ctx* m_ctx = nullptr;
     StereoCalib m_calib;
     int m_width = 0, m_height = 0;

@@ -19,7 +19,7 @@ static std::vector<uint8_t> slurp(const char* path, std::size_t n)
 
 int main(int argc, char** argv)
 {
-    if (argc < 7) { std::cerr << "usage: example_frame W H left.bgr right.bgr out_disp.i16 out_cloud.bin [block_size num_disparities]\n"; return 2; }
+    if (argc < 7) { std::cerr << "usage: example_frame W H left.bgr right.bgr out_disp.i16 out_cloud.bin [block_size num_disparities [out_bm_disp.i16]]\n"; return 2; }
     const int W = std::atoi(argv[1]), H = std::atoi(argv[2]);
     cvr::StereoCalib calib{959.791f, 956.9251f, 696.0217f, 224.1806f, 903.7596f, 901.9653f, 695.7519f, 224.2509f, 0.532671f};
     cvr::SGBMConfig cfg;
@@ -38,6 +38,16 @@ int main(int argc, char** argv)
         recon.RemoveOutliers(cloud, cloud);
         std::ofstream(argv[6], std::ios::binary).write(reinterpret_cast<const char*>(cloud.data()), static_cast<std::streamsize>(cloud.size() * sizeof(cvr_point)));
         std::cout << "points " << cloud.size() << "\n";
+        if (argc > 9) {      // the reference's setters: a new StereoBM with OpenCV's defaults, then window size and disparity range
+            recon.SetBlockMatcherType(cvr::STEREO_BLOCK_MATCHER);
+            recon.SetStereoBMNumDisparities(cfg.NumDisparities);
+            recon.SetStereoBMWindowSize(cfg.BlockSize);
+            std::vector<int16_t> bm = recon.GenerateDisparityMap(left, right);
+            std::ofstream(argv[9], std::ios::binary).write(reinterpret_cast<const char*>(bm.data()), static_cast<std::streamsize>(bm.size() * 2));
+            const uint8_t white[3] = {255, 255, 255};
+            const cvr_point q = recon.TriangulateUV(100.f, 50.f, 16.f, white);
+            std::cout << "uv " << q.x << " " << q.y << " " << q.z << "\n";
+        }
     } catch (const std::exception& e) {
         std::cerr << e.what() << "\n";
         return 3;

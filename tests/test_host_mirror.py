@@ -65,10 +65,16 @@ def test_cpp_example_matches_python_harness(tmp_path, cvr, oracle):
     lb, rb = oracle.synth_pair(H, W, D, seed=21, color=True)
     lb.tofile(tmp_path / "l.bgr"); rb.tofile(tmp_path / "r.bgr")
     r = subprocess.run([exe, str(W), str(H), str(tmp_path / "l.bgr"), str(tmp_path / "r.bgr"), str(tmp_path / "d.i16"), str(tmp_path / "c.bin"),
-                        str(bs), str(D)], capture_output=True, text=True)
+                        str(bs), str(D), str(tmp_path / "bm.i16")], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
     disp = np.fromfile(tmp_path / "d.i16", np.int16).reshape(H, W)
     ref = oracle.sgbm(oracle.gray_bgr(lb), oracle.gray_bgr(rb), oracle.reference_sgbm_params(block_size=bs, num_disparities=D))
     assert np.array_equal(disp, ref)
     cloud = np.fromfile(tmp_path / "c.bin", cvr.POINT_DTYPE)
     assert int(r.stdout.split()[1]) == len(cloud)
+    # SetBlockMatcherType(STEREO_BLOCK_MATCHER) + SetStereoBMNumDisparities + SetStereoBMWindowSize (Reconstruct3D.cpp:364-388)
+    bm = np.fromfile(tmp_path / "bm.i16", np.int16).reshape(H, W)
+    assert np.array_equal(bm, oracle.stereobm(oracle.gray_bgr(lb), oracle.gray_bgr(rb), oracle.reference_bm_params(bs, D)))
+    uv = [float(v) for v in r.stdout.split("uv")[1].split()]
+    f = np.float32((np.float32(959.791) + np.float32(956.9251)) / np.float32(2)); z = f * np.float32(0.532671) / np.float32(16)
+    assert np.allclose(uv, [(np.float32(100) - np.float32(696.0217)) * (z / f), -(np.float32(50) - np.float32(224.1806)) * (z / f), z], rtol=1e-5)
