@@ -545,6 +545,54 @@ __global__ void k_median3(const int16_t* __restrict__ src, int16_t* __restrict__
     dst[(size_t)b * W * H + (size_t)y * W + x] = (int16_t)v[4];
 }
 
+// Two horizontally adjacent pixels per thread (even image width): aligned 32-bit loads, the 19-exchange network on
+// packed int16 pairs (VIMNMX.S16x2), one 32-bit store.  Pairs that touch the left/right border take the scalar form.
+__device__ __forceinline__ void srt2(unsigned& a, unsigned& b) { const unsigned t = __vmins2(a, b); b = __vmaxs2(a, b); a = t; }
+__device__ __forceinline__ int median9(int (&v)[9])
+{
+    srt(v[1], v[2]); srt(v[4], v[5]); srt(v[7], v[8]); srt(v[0], v[1]); srt(v[3], v[4]); srt(v[6], v[7]);
+    srt(v[1], v[2]); srt(v[4], v[5]); srt(v[7], v[8]); srt(v[0], v[3]); srt(v[5], v[8]); srt(v[4], v[7]);
+    srt(v[3], v[6]); srt(v[1], v[4]); srt(v[2], v[5]); srt(v[4], v[7]); srt(v[4], v[2]); srt(v[6], v[4]);
+    srt(v[4], v[2]);
+    return v[4];
+}
+__global__ void __launch_bounds__(128) k_median3_x2(const int16_t* __restrict__ src, int16_t* __restrict__ dst, int W, int H)
+{
+    const int x = 2 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y, b = blockIdx.z;
+    if (x >= W) return;
+    const int16_t* s = src + (size_t)b * W * H;
+    int16_t* d = dst + (size_t)b * W * H + (size_t)y * W + x;
+    const int ym = max(y - 1, 0), yp = min(y + 1, H - 1);
+    if (x >= 2 && x + 3 < W) {
+        unsigned v[9];
+        const int rows[3] = { ym, y, yp };
+#pragma unroll
+        for (int r = 0; r < 3; r++) {
+            const unsigned* rp = (const unsigned*)(s + (size_t)rows[r] * W + x);       // (v[x], v[x+1]); its neighbours hold x-2..x-1 and x+2..x+3
+            const unsigned w0 = rp[-1], w1 = rp[0], w2 = rp[1];
+            v[3 * r + 0] = __byte_perm(w0, w1, 0x5432);                                 // (v[x-1], v[x])   : left neighbours of the pair
+            v[3 * r + 1] = w1;                                                          // (v[x],   v[x+1])
+            v[3 * r + 2] = __byte_perm(w1, w2, 0x5432);                                 // (v[x+1], v[x+2]) : right neighbours
+        }
+        srt2(v[1], v[2]); srt2(v[4], v[5]); srt2(v[7], v[8]); srt2(v[0], v[1]); srt2(v[3], v[4]); srt2(v[6], v[7]);
+        srt2(v[1], v[2]); srt2(v[4], v[5]); srt2(v[7], v[8]); srt2(v[0], v[3]); srt2(v[5], v[8]); srt2(v[4], v[7]);
+        srt2(v[3], v[6]); srt2(v[1], v[4]); srt2(v[2], v[5]); srt2(v[4], v[7]); srt2(v[4], v[2]); srt2(v[6], v[4]);
+        srt2(v[4], v[2]);
+        *(unsigned*)d = v[4];
+        return;
+    }
+    for (int k = 0; k < 2 && x + k < W; k++) {
+        int v[9];
+#pragma unroll
+        for (int dy = 0; dy < 3; dy++) {
+            const int yy = dy == 0 ? ym : (dy == 1 ? y : yp);
+#pragma unroll
+            for (int dx = -1; dx <= 1; dx++) v[dy * 3 + dx + 1] = s[(size_t)yy * W + min(max(x + k + dx, 0), W - 1)];
+        }
+        d[k] = (int16_t)median9(v);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // A.7: speckle filter = connected components (4-neighbours, |dv| <= maxDiff, value != newVal) of size
 // <= maxSize are erased.  Union-find with atomicMin roots; the result does not depend on the merge order.
@@ -894,7 +942,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     if (rc) return rc;
     k_lrcheck<<<dim3(p.H, B), 256, (size_t)p.W * 2 * sizeof(int), c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p);
     LAUNCH_CHECK(c);
-    k_median3<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
+    if ((p.W & 1) == 0) k_median3_x2<<<dim3(cvr_div_up(p.W, 256), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
+    else k_median3<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "lr_median");
     if (c->prm.sgbm.speckle_window_size > 0) {
