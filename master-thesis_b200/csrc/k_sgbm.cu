@@ -195,7 +195,8 @@ __device__ __forceinline__ unsigned sat_sub_pos2(unsigned a, unsigned b) { retur
 // row bs rows earlier and is simply read again.  ncu: 288 MB of DRAM traffic per KITTI frame (214 MB algorithmic: the
 // re-read mostly misses the L2, whose share per resident row step is too small for 27 rows) at 92 % of the measured HBM
 // peak.  Measured and rejected on B200: a shared-memory ring of the last bs rows (caps the resident threads: 58-61 us
-// against 48 us), register prefetch 2-3 rows ahead, and capping the occupancy to make the window fit the L2 (all slower).
+// against 48 us), the window in a statically indexed register ring with one 32-bit word per thread (104 us), register
+// prefetch 2-3 rows ahead, and capping the occupancy to make the window fit the L2 (all slower).
 __global__ void __launch_bounds__(128) k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B, int* flags)
 {
     const size_t rowWords = (size_t)p.W1 * p.Dp / 8;          // uint4 words per row (Dp is a multiple of 32)
