@@ -37,6 +37,33 @@ __global__ void k_gray(const uint8_t* __restrict__ src, size_t step, size_t fstr
     dst[(size_t)b * dstFrameStride + (size_t)y * Wp + x] = g;
 }
 
+// BGR -> gray, four pixels per thread, both cameras in one launch (blockIdx.z = 2 * frame + camera): the 12 source bytes
+// come from four aligned 32-bit words (funnel-shifted by the row's misalignment), the result is one 32-bit store (the gray
+// pitch Wp is a multiple of 16).  A thread whose words would run past the end of the frame's last row takes the byte form.
+__global__ void __launch_bounds__(128) k_gray3_x4(const uint8_t* __restrict__ srcL, size_t lstep, size_t lfs, const uint8_t* __restrict__ srcR, size_t rstep,
+                                                  size_t rfs, uint8_t* __restrict__ dst, int Wp, size_t dstFrameStride, int W, int H)
+{
+    const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x), y = blockIdx.y, b = blockIdx.z >> 1, cam = blockIdx.z & 1;
+    if (x >= W) return;
+    const uint8_t* row = (cam ? srcR + (size_t)b * rfs + (size_t)y * rstep : srcL + (size_t)b * lfs + (size_t)y * lstep);
+    const uint8_t* s = row + (size_t)x * 3;
+    uint8_t* d = dst + (size_t)b * dstFrameStride + (size_t)cam * H * Wp + (size_t)y * Wp + x;
+    unsigned g[4];
+    if (x + 4 <= W && !(y == H - 1 && x + 8 > W)) {            // the 16 bytes read below stay inside this frame
+        const unsigned sh = ((unsigned)(size_t)s & 3u) * 8u;
+        const unsigned* wp = (const unsigned*)((size_t)s & ~(size_t)3);
+        const unsigned a0 = wp[0], a1 = wp[1], a2 = wp[2], a3 = wp[3];
+        const unsigned w0 = __funnelshift_r(a0, a1, sh), w1 = __funnelshift_r(a1, a2, sh), w2 = __funnelshift_r(a2, a3, sh);   // bytes 0..11
+        const unsigned px[4][3] = { { w0 & 255u, (w0 >> 8) & 255u, (w0 >> 16) & 255u }, { w0 >> 24, w1 & 255u, (w1 >> 8) & 255u },
+                                    { (w1 >> 16) & 255u, w1 >> 24, w2 & 255u }, { (w2 >> 8) & 255u, (w2 >> 16) & 255u, w2 >> 24 } };
+#pragma unroll
+        for (int k = 0; k < 4; k++) g[k] = (3735u * px[k][0] + 19235u * px[k][1] + 9798u * px[k][2] + 16384u) >> 15;
+        *(unsigned*)d = g[0] | (g[1] << 8) | (g[2] << 16) | (g[3] << 24);
+        return;
+    }
+    for (int k = 0; k < 4 && x + k < W; k++) d[k] = (uint8_t)((3735 * s[3 * k] + 19235 * s[3 * k + 1] + 9798 * s[3 * k + 2] + 16384) >> 15);
+}
+
 // ------------------------------------------------------------------------------------------------
 // A.2 + A.3 (horizontal).  One CTA per (row, frame), one thread per disparity.
 // Per-pixel packed descriptors, G channel (clipped Sobel) in the low half, raw intensity in the high half:
@@ -702,6 +729,11 @@ int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t
 {
     const SgbmDev& p = c->sg;
     const size_t gfs = (size_t)2 * p.H * p.Wp;
+    if (channels == 3) {
+        k_gray3_x4<<<dim3(cvr_div_up(p.W, 512), p.H, 2 * B), 128, 0, c->stream>>>(left, lstep, lfs, right, rstep, rfs, c->d_gray, p.Wp, gfs, p.W, p.H);
+        LAUNCH_CHECK(c);
+        return CVR_OK;
+    }
     dim3 g(cvr_div_up(p.W, 256), p.H, B);
     k_gray<<<g, 256, 0, c->stream>>>(left, lstep, lfs, channels, c->d_gray, p.Wp, gfs, p.W, p.H);
     LAUNCH_CHECK(c);
