@@ -372,6 +372,41 @@ def test_pipelined_device_resident_batches(cvr, oracle, rect):
     rec.close()
 
 
+@pytest.mark.parametrize("extra", [5, 6, 7, 8])
+def test_unaligned_device_images_all_width_residues(cvr, oracle, extra):
+    """Device-resident BGR frames with a padded row step and a base pointer that is not 4-byte aligned, image widths of
+    every residue mod 4 (the gray kernel reads aligned words and funnel-shifts; the median takes pixel pairs only for
+    even widths)."""
+    import torch
+    D, bs, H, B = 32, 5, 11, 3
+    W = D + 60 + extra
+    pairs = [oracle.synth_pair(H, W, D, seed=300 + extra * 10 + i, color=True) for i in range(B)]
+    step, off = W * 3 + 5, 1
+    fs = step * H + 3
+    dev = torch.device("cuda", 0)
+    bufL = torch.zeros(off + fs * B + 64, dtype=torch.uint8, device=dev)
+    bufR = torch.zeros_like(bufL)
+    for i, (l, r) in enumerate(pairs):
+        for (buf, img) in ((bufL, l), (bufR, r)):
+            view = buf[off + i * fs: off + i * fs + step * H].view(H, step)
+            view[:, :W * 3] = torch.from_numpy(img.reshape(H, W * 3)).to(dev)
+    disp = torch.empty((B, H, W), dtype=torch.int16, device=dev)
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D), max_batch=B)
+    io = cvr.Batch()
+    io.mem, io.channels = cvr.MEM_DEVICE, 3
+    io.left, io.left_step, io.left_frame_stride = bufL.data_ptr() + off, step, fs
+    io.right, io.right_step, io.right_frame_stride = bufR.data_ptr() + off, step, fs
+    io.disp, io.disp_step, io.disp_frame_stride = disp.data_ptr(), W * 2, W * H * 2
+    io.stages = 1
+    torch.cuda.synchronize()
+    rec.process_batch_raw(io, B)
+    got = disp.cpu().numpy()
+    p = oracle.reference_sgbm_params(block_size=bs, num_disparities=D)
+    for i, (l, r) in enumerate(pairs):
+        assert np.array_equal(got[i], oracle.sgbm(oracle.gray_bgr(l), oracle.gray_bgr(r), p)), "frame %d" % i
+    rec.close()
+
+
 def _bm_cfg(p):
     return dict(block_matcher=1, window_size=p["blockSize"], bm_num_disparities=p["numDisparities"], bm_min_disparity=p["minDisparity"],
                 bm_pre_filter_cap=p["preFilterCap"], bm_texture_threshold=p["textureThreshold"], bm_uniqueness_ratio=p["uniquenessRatio"],
