@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_write(const cvr_point* __
 // exclusive scan of the per-frame cell counts: one CTA per frame while the table is short, two levels when it is long
 static int scan_cells(cvr_ctx* c, int B, int* cellstart, size_t cellStride, int cap, const int* ncell)
 {
-    if (cap <= 32768) {
+    if (cap <= (1 << 20)) {                                          // the single-CTA scan only walks the cells in use (lenPtr)
         k_scan_excl<<<B, 1024, 0, c->stream>>>(cellstart, cellStride, cap, ncell, 1);
         LAUNCH_CHECK(c);
         return CVR_OK;
