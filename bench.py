@@ -194,6 +194,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=104, help="frames per GPU per step")
+    ap.add_argument("--exact-batch", action="store_true", help="use --batch as given instead of letting the library round it to full cluster waves")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--rectify", action="store_true", help="side measurement: config requires_rectification = true (RectifyImages on the device before the matcher)")
     ap.add_argument("--matcher", default="sgbm", choices=["sgbm", "bm"], help="sgbm = the headline path; bm = the reference's other block matcher (side measurement)")
@@ -221,7 +222,9 @@ def main():
     if args.matcher == "bm":
         cfg["block_matcher"] = cvr.MATCHER_BM
     cfg["requires_rectification"] = bool(args.rectify)
-    rec = cvr.Reconstruct3D(W, H, config=cfg, max_batch=B, device=local)   # defaults = config_default.json SGBM/SBM sections, leaf 0.2, SOR 30/0.5
+    # --batch is a target: the library rounds it to a multiple of the clusters its vertical path kernel runs at once on this
+    # GPU (26 on the B200s measured so far => 104); every rank asks its own GPU, all ranks then use the smallest answer
+    rec = cvr.Reconstruct3D(W, H, config=cfg, max_batch=B + B // 4, device=local)   # defaults = config_default.json SGBM/SBM sections, leaf 0.2, SOR 30/0.5
     if args.rectify:                                                   # a KITTI-like raw calibration (5 distortion terms, small rotation)
         K = np.array([[959.791, 0, 696.0217], [0, 956.9251, 224.1806], [0, 0, 1]])
         Dk = [-0.3728755, 0.2037299, 0.002219027, 0.001383707, -0.07233722]
@@ -229,6 +232,12 @@ def main():
         Rr = np.array([[np.cos(a), -np.sin(a), 0], [np.sin(a), np.cos(a), 0], [0, 0, 1]])
         Pp = np.array([[880.0, 0, 660.0, 0], [0, 880.0, 200.0, 0], [0, 0, 1, 0]])
         rec.SetRectification(K, Dk, Rr, Pp, K, Dk, Rr, Pp)
+    if not args.exact_batch:
+        B = rec.suggest_batch(B)
+        if world > 1:
+            tb = torch.tensor([B], dtype=torch.int32, device=dev)
+            dist.all_reduce(tb, op=dist.ReduceOp.MIN)
+            B = int(tb.item())
     Ls, Rs = make_pairs(UNIQUE_PAIRS)
     idx = [(rank * B + i) % UNIQUE_PAIRS for i in range(B)]            # frame_id sharding; the pool of unique pairs is cycled
     hL = torch.from_numpy(Ls[idx]).pin_memory(); hR = torch.from_numpy(Rs[idx]).pin_memory()

@@ -182,6 +182,13 @@ typedef struct cvr_batch {
 } cvr_batch;
 int cvr_process_batch(cvr_ctx* ctx, int nframes, const cvr_batch* io);
 
+/* No counterpart in the reference (which processes one frame per call).  The vertical path kernel gives every frame of a
+ * batch to one thread-block cluster and the GPU holds a fixed number of those at once (found by an occupancy query: e.g. 26
+ * clusters of 5 CTAs on a 148-SM B200 at KITTI shape), so a batch that is a multiple of that number has no part-filled
+ * last wave.  Returns the batch size within a quarter of `around` (and <= max_batch) with the lowest cost per frame, or a
+ * negative cvr_status. */
+int cvr_suggest_batch(cvr_ctx* ctx, int around);
+
 /* Pipelined form of cvr_process_batch: up to two batches in flight, so that the upload of batch i+1 overlaps the kernels
  * of batch i and the download of batch i-1.  This is how the frame loop
  * of the reference's server thread (cv_reconstruct/src/server/ReconstructionServer.cpp:134-153: dequeue a stereo message,

@@ -34,7 +34,7 @@ EXPORTS = [
     "cvr_reproject_cloud", "cvr_triangulate", "cvr_voxel_grid", "cvr_sor", "cvr_process_batch", "cvr_points_to_pcl",
     "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling", "cvr_prune_noalloc",
     "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
-    "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps",
+    "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps", "cvr_suggest_batch",
 ]
 
 
@@ -114,6 +114,7 @@ def load_library():
     lib.cvr_set_rectification.argtypes = [C.c_void_p] + [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int] * 2
     lib.cvr_rectify.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t]
     lib.cvr_get_rectification_maps.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+    lib.cvr_suggest_batch.argtypes = [C.c_void_p, C.c_int]
     lib.cvr_submit_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(Batch)]
     lib.cvr_wait_batch.argtypes = [C.c_void_p]
     lib.cvr_debug_fetch.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
@@ -248,6 +249,13 @@ class Reconstruct3D:
             self.close()
         except Exception:
             pass
+
+    def suggest_batch(self, around):
+        """Batch size near `around` (<= max_batch) that fills the vertical path kernel's cluster waves on this GPU."""
+        n = int(self.lib.cvr_suggest_batch(self.ctx, int(around)))
+        if n < 1:
+            raise CvrError(n, self.lib.cvr_last_error(self.ctx).decode())
+        return n
 
     def launch_count(self):
         return int(self.lib.cvr_launch_count(self.ctx))

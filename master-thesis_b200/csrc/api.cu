@@ -140,6 +140,13 @@ static void fill_dev_params(cvr_ctx* c)
 
 extern "C" const char* cvr_last_error(const cvr_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 extern "C" long long cvr_launch_count(const cvr_ctx* ctx) { return ctx ? ctx->launches : 0; }
+extern "C" int cvr_suggest_batch(cvr_ctx* ctx, int around)
+{
+    if (!ctx) return CVR_ERR_INVALID_ARG;
+    if (ctx->prm.filter_only) return around < 1 ? 1 : around;
+    if (cudaSetDevice(ctx->device) != cudaSuccess) return CVR_ERR_CUDA;
+    return cvr_sgbm_suggest_batch(ctx, around);
+}
 extern "C" int cvr_set_profiling(cvr_ctx* ctx, int enable) { if (!ctx) return CVR_ERR_INVALID_ARG; ctx->profiling = enable != 0; return CVR_OK; }
 extern "C" int cvr_last_timings(const cvr_ctx* ctx, const char** names, float* ms, int max_stages)
 {

@@ -188,6 +188,7 @@ static inline size_t cvr_div_up_sz(size_t a, size_t b) { return (a + b - 1) / b;
 int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t lfs, const uint8_t* right, size_t rstep,
                     size_t rfs, int channels);
 int cvr_launch_sgbm(cvr_ctx* c, int B);     // gray -> d_med (final disparity)
+int cvr_sgbm_suggest_batch(cvr_ctx* c, int around);   // batch size near `around` that fills the vertical kernel's cluster waves
 // k_rectify.cu: initUndistortRectifyMap (CV_16SC2) for one camera into d_rmap1/2[cam]; remap of B stereo pairs
 int cvr_launch_rectify_maps(cvr_ctx* c, int cam, const double* K, const double* D, int nD, const double* R, const double* P, int pcols);
 int cvr_launch_remap(cvr_ctx* c, int B, int ch, const uint8_t* dl, size_t lstep, size_t lfs, const uint8_t* dr, size_t rstep, size_t rfs,

@@ -742,7 +742,7 @@ int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t
     return CVR_OK;
 }
 
-struct VCfg { bool ok; int CL, NT; VState vs; size_t smem; };
+struct VCfg { bool ok; int CL, NT; VState vs; size_t smem; double cost; };   // cost: waves x columns per CTA of the whole batch
 
 static size_t vcfg_smem(const SgbmDev& p, int CL, int NT, VState* vs)
 {
@@ -760,7 +760,7 @@ template <typename K>
 static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512)
 {
     const SgbmDev& p = c->sg;
-    VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = 0;
+    VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.cost = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = 0;
     const int nts[3] = { 1024, 512, 256 };
     const char* fcl = getenv("CVR_PATHV_CL");
     const int forced = fcl ? atoi(fcl) : 0;
@@ -794,7 +794,7 @@ static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512)
             }
             if (act <= 0) continue;
             const double cost = (double)((B + act - 1) / act) * (double)(vs.colsMax + 8);
-            if (!r.ok || cost < best) { best = cost; r.ok = true; r.CL = CL; r.NT = NT; r.vs = vs; r.smem = smem; }
+            if (!r.ok || cost < best) { best = cost; r.ok = true; r.CL = CL; r.NT = NT; r.vs = vs; r.smem = smem; r.cost = cost; }
         }
         if (r.ok) return r;
     }
@@ -827,7 +827,7 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     const int hblocks = cvr_div_up(B * p.H, 4);
     const bool packed = !c->force_generic && p.P1s >= 0;               // P1s < 0 (P1 in [32768, 65535] mod 65536): int32 kernels
     const VCfg vc = packed ? pick_vcfg(c, B, k_path_v3<DPL, false, false, HASPAD, NN, 1024>, k_path_v3<DPL, false, false, HASPAD, NN, 512>)
-                           : VCfg{ false, 1, 0, { 0, 0, 0 }, 0 };
+                           : VCfg{ false, 1, 0, { 0, 0, 0 }, 0, 0 };
     int* fl = c->d_sgflags;
     // generic vertical kernel geometry: a cluster of CL CTAs per frame; fewer, larger clusters when the batch is small
     constexpr int NT = (DPL <= 4) ? 512 : 256;
@@ -985,4 +985,42 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         cvr_stage_mark(c, "speckle");
     }
     return CVR_OK;
+}
+
+// The batch size near `around` (within a quarter of it, at most max_batch) at which the vertical path kernel wastes the
+// least: its clusters run in waves of as many as fit the GPU at once, so a batch that is a multiple of that count has no
+// part-filled last wave.  Falls back to `around` where the kernel is not used (StereoBM, int32 fallback kernels).
+template <int DPL, bool HASPAD, bool NN>
+static int suggest_batch(cvr_ctx* c, int around)
+{
+    const int lo = around - around / 4 > 1 ? around - around / 4 : 1, hi = around + around / 4 < c->maxB ? around + around / 4 : c->maxB;
+    int bestB = around < c->maxB ? around : c->maxB;
+    double bestCost = -1;
+    for (int B = lo; B <= hi; B++) {
+        const VCfg vc = pick_vcfg(c, B, k_path_v3<DPL, false, false, HASPAD, NN, 1024>, k_path_v3<DPL, false, false, HASPAD, NN, 512>);
+        if (!vc.ok) return bestB;
+        const double perFrame = vc.cost / B;
+        const bool closer = (B > around ? B - around : around - B) < (bestB > around ? bestB - around : around - bestB);
+        if (bestCost < 0 || perFrame < bestCost * (1.0 - 1e-9) || (perFrame <= bestCost * (1.0 + 1e-9) && closer)) { bestCost = perFrame; bestB = B; }
+    }
+    return bestB;
+}
+
+int cvr_sgbm_suggest_batch(cvr_ctx* c, int around)
+{
+    const SgbmDev& p = c->sg;
+    if (around < 1) around = 1;
+    const int fallback = around < c->maxB ? around : c->maxB;
+    if (c->prm.block_matcher != CVR_MATCHER_SGBM || p.W1 <= 0 || c->force_generic || p.P1s < 0) return fallback;
+    const bool nn = !c->force_no_nn && p.P2s >= 0 && p.P1s >= p.P2s;
+    const bool pad = p.D != p.Dp;
+    switch (p.Dp / 32) {
+#define CVR_SUGGEST(DPL_)                                                                                                \
+    case DPL_:                                                                                                           \
+        if (nn) return pad ? suggest_batch<DPL_, true, true>(c, around) : suggest_batch<DPL_, false, true>(c, around);    \
+        return pad ? suggest_batch<DPL_, true, false>(c, around) : suggest_batch<DPL_, false, false>(c, around);
+        CVR_SUGGEST(2) CVR_SUGGEST(4) CVR_SUGGEST(6) CVR_SUGGEST(8)
+#undef CVR_SUGGEST
+        default: return fallback;
+    }
 }

@@ -1,7 +1,7 @@
 # cluster size x batch sweep for the vertical path kernel (tuning record; CVR_PATHV_CL forces the cluster size)
 for cl in 8 6 5; do
  for b in 60 66 75 78 88 104; do
-  CVR_PATHV_CL=$cl timeout 300 python bench.py --batch $b --steps 5 --warmup 3 --no-cpu-baseline 2> /dev/null | python -c "
+  CVR_PATHV_CL=$cl timeout 300 python bench.py --exact-batch --batch $b --steps 5 --warmup 3 --no-cpu-baseline 2> /dev/null | python -c "
 import sys,json
 for l in sys.stdin:
     try: j=json.loads(l)

@@ -407,6 +407,21 @@ def test_unaligned_device_images_all_width_residues(cvr, oracle, extra):
     rec.close()
 
 
+def test_suggest_batch_fills_cluster_waves(cvr):
+    """cvr_suggest_batch: stays within a quarter of the target and below max_batch, is idempotent, and leaves the target
+    alone where the clustered kernel is not used (StereoBM)."""
+    rec = cvr.Reconstruct3D(1242, 375, config=cvr.parse_config(None), max_batch=40)
+    b = rec.suggest_batch(30)
+    assert 23 <= b <= 37 and rec.suggest_batch(b) == b
+    assert rec.suggest_batch(1000) <= 40 and rec.suggest_batch(1) == 1
+    rec.close()
+    cfg = cvr.parse_config(None)
+    cfg["block_matcher"] = cvr.MATCHER_BM
+    rec = cvr.Reconstruct3D(640, 120, config=cfg, max_batch=16)
+    assert rec.suggest_batch(9) == 9
+    rec.close()
+
+
 def _bm_cfg(p):
     return dict(block_matcher=1, window_size=p["blockSize"], bm_num_disparities=p["numDisparities"], bm_min_disparity=p["minDisparity"],
                 bm_pre_filter_cap=p["preFilterCap"], bm_texture_threshold=p["textureThreshold"], bm_uniqueness_ratio=p["uniquenessRatio"],
