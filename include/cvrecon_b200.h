@@ -179,6 +179,12 @@ typedef struct cvr_batch {
     cvr_point* cloud;     size_t cloud_capacity;                    /* per frame, in points; frame i at cloud + i*capacity */
     int32_t* cloud_count;                                           /* [nframes] */
     int stages;                     /* bit 0 disparity, 1 prune+cloud, 2 voxel, 3 sor; 0 => all */
+    /* Packed form of the cloud output; when cloud_packed is set it is used INSTEAD of `cloud`: the clouds of all frames back
+     * to back, frame i = cloud_packed[cloud_offsets[i] .. cloud_offsets[i+1]) -- the layout MapDataBase::InsertBlock
+     * (cv_reconstruct/src/system/MapDataBase.cpp:28-54) appends block by block.  One device->host copy per batch instead of
+     * one per frame.  cloud_offsets has nframes + 1 entries; cloud_count is still filled when given. */
+    cvr_point* cloud_packed; size_t cloud_packed_capacity;          /* in points, for the whole batch */
+    int32_t* cloud_offsets;
 } cvr_batch;
 int cvr_process_batch(cvr_ctx* ctx, int nframes, const cvr_batch* io);
 
@@ -203,6 +209,41 @@ int cvr_suggest_batch(cvr_ctx* ctx, int around);
  * submitted batch has been waited for. */
 int cvr_submit_batch(cvr_ctx* ctx, int nframes, const cvr_batch* io);
 int cvr_wait_batch(cvr_ctx* ctx);
+/* Error behaviour of the batched calls: a cloud that does not fit cloud_capacity / cloud_packed_capacity makes the call (for
+ * submitted batches: the matching cvr_wait_batch) return CVR_ERR_CAPACITY -- for host AND device buffers; device buffers then
+ * hold the points that fitted and the true counts.  A failed cvr_wait_batch still releases its pipeline slot. */
+
+/* ---- multi-GPU: gather of the filtered clouds to the mapping rank ------------------------------------------
+ * Replaces: the hand-over of every processed frame's cloud to the one map, MappingSystem::AddFrame -> MapDataBase::InsertBlock
+ * (cv_reconstruct/src/system/MappingSystem.cpp:344-345, MapDataBase.cpp:28-54), for frames sharded over one process per GPU.
+ * Frames are independent, so this is the only exchange on the path: per-frame counts by ncclAllGather, the packed clouds by
+ * grouped ncclSend / ncclRecv straight from the device buffer the filters wrote, on a stream of its own (it overlaps the
+ * kernels of the next submitted batch).  libnccl.so.2 is bound at run time (dlopen; the copy already loaded into the process
+ * is preferred), nothing links against it.
+ *
+ *   cvr_comm_get_unique_id  rank 0 makes an id (CVR_COMM_ID_BYTES bytes) and hands it to the other processes by any means
+ *   cvr_comm_init           every rank: ncclCommInitRank on the context's device
+ *   cvr_comm_attach         alternative: use an ncclComm_t the host already owns (not destroyed by the library)
+ *   cvr_gather_clouds       collective over all ranks: sends the clouds of the batch this rank completed last
+ *                           (cvr_process_batch, or the most recent cvr_wait_batch) to `root`.  On root, `out` (host or device
+ *                           memory according to `mem`) receives the points rank by rank, frames in batch order;
+ *                           frame_offsets[0 .. total_frames] are the frame boundaries in `out`, frames_of_rank[r] the number
+ *                           of frames rank r contributed.  Other ranks pass NULL / 0 for the outputs.  Blocks until this
+ *                           rank's part is done.  Call it before submitting the batch after next (which reuses the buffer
+ *                           the payload is parked in).  Every rank must have been created with the same max_batch.
+ *                           Without a communicator the call is the one-rank case (a local copy).
+ *   cvr_gather_layout       the host arithmetic of the gather, exported for tests: headers = nranks records of header_ints
+ *                           int32 {nframes, total points, per-frame counts...}; writes rank_offset[0..nranks] (points) and,
+ *                           if wanted, the global frame_offsets; returns the total number of frames or a negative status. */
+#define CVR_COMM_ID_BYTES 128
+int cvr_comm_get_unique_id(void* id);
+int cvr_comm_init(cvr_ctx* ctx, int nranks, int rank, const void* id);
+int cvr_comm_attach(cvr_ctx* ctx, void* nccl_comm);
+int cvr_comm_destroy(cvr_ctx* ctx);
+int cvr_gather_clouds(cvr_ctx* ctx, int root, int mem, cvr_point* out, size_t out_capacity, int32_t* frame_offsets, int frame_offsets_capacity,
+                      int32_t* frames_of_rank);
+int cvr_gather_layout(const int32_t* headers, int nranks, int header_ints, int64_t* rank_offset, int32_t* frame_offsets, int frame_offsets_capacity,
+                      int32_t* frames_of_rank);
 
 /* No counterpart in the reference: TrackingFrame::SetupFrame / cvr_prune for callers that are not allowed to
  * allocate GPU memory.  Think of a frame loop that must keep a fixed latency (cudaMalloc/cudaFree stall the whole
@@ -218,7 +259,8 @@ int cvr_wait_batch(cvr_ctx* ctx);
  * cvr_last_error(NULL).  The first call on each device looks up the array's device address; make that first call
  * before starting any stream capture.  All calls on a device share the one array and it keeps whatever the last
  * call left there (the call resets what it relies on), so two calls whose GPU work can overlap -- different
- * streams or threads -- race with each other: keep them ordered. */
+ * streams or threads -- race with each other: keep them ordered.  d_pruned may be the same buffer as d_disp (pruning in
+ * place, as TrackingFrame::PruneDisparityImage does).  The looked-up address does not survive cudaDeviceReset. */
 #define CVR_NOALLOC_MAX_PIXELS (4u << 20)
 int cvr_prune_noalloc(const int16_t* d_disp, int width, int height, double sigma_factor,
                       int16_t* d_pruned, float* d_disp_f32, uint8_t* d_mask, void* stream);
@@ -228,7 +270,9 @@ void cvr_points_to_pcl(const cvr_point* in, int n, void* pcl_points_32B);
 
 /* Test/inspection hooks (no reference counterpart): copy an intermediate of the most recent
  * cvr_disparity call to host.  which: 0 = C volume, 1 = S volume (both int16 [H][W1][Dp]),
- * 2 = raw disparity before median/speckle (int16 [H][W]).  *dp receives the padded D pitch. */
+ * 2 = raw disparity before median/speckle (int16 [H][W]), 3 = after the LR check.  *dp receives the padded D pitch.
+ * Of the most recent cvr_sor call: 4 = mean k-NN distance per input point (bytes/4 floats, input order),
+ * 5 = {double sum, sum of squares, threshold; int valid, kept} (32 bytes). */
 int cvr_debug_fetch(cvr_ctx* ctx, int which, void* host_dst, size_t bytes, int* w1, int* dp);
 
 /* Number of kernel launches issued by this context since creation (bench.py's gpu_launches). */

@@ -35,7 +35,9 @@ EXPORTS = [
     "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling", "cvr_prune_noalloc",
     "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
     "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps", "cvr_suggest_batch",
+    "cvr_comm_get_unique_id", "cvr_comm_init", "cvr_comm_attach", "cvr_comm_destroy", "cvr_gather_clouds", "cvr_gather_layout",
 ]
+COMM_ID_BYTES = 128
 
 
 class SgbmParams(C.Structure):
@@ -63,6 +65,7 @@ class Batch(C.Structure):
         ("right", C.c_void_p), ("right_step", C.c_size_t), ("right_frame_stride", C.c_size_t),
         ("disp", C.c_void_p), ("disp_step", C.c_size_t), ("disp_frame_stride", C.c_size_t),
         ("cloud", C.c_void_p), ("cloud_capacity", C.c_size_t), ("cloud_count", C.c_void_p), ("stages", C.c_int),
+        ("cloud_packed", C.c_void_p), ("cloud_packed_capacity", C.c_size_t), ("cloud_offsets", C.c_void_p),
     ]
 
 
@@ -123,8 +126,37 @@ def load_library():
     lib.cvr_points_to_pcl.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.cvr_points_to_pcl.restype = None
     lib.cvr_prune_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.cvr_comm_get_unique_id.argtypes = [C.c_void_p]
+    lib.cvr_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+    lib.cvr_comm_attach.argtypes = [C.c_void_p, C.c_void_p]
+    lib.cvr_comm_destroy.argtypes = [C.c_void_p]
+    lib.cvr_gather_clouds.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_size_t, C.c_void_p, C.c_int, C.c_void_p]
+    lib.cvr_gather_layout.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
     _lib = lib
     return lib
+
+
+def comm_unique_id():
+    """ncclGetUniqueId through the library (rank 0 calls it and hands the 128 bytes to the other ranks)."""
+    buf = (C.c_ubyte * COMM_ID_BYTES)()
+    rc = load_library().cvr_comm_get_unique_id(buf)
+    if rc != 0:
+        raise CvrError(rc, load_library().cvr_last_error(None).decode())
+    return bytes(buf)
+
+
+def gather_layout(headers):
+    """cvr_gather_layout: headers = int32 array [nranks][2 + max_batch] of {nframes, total, counts...}.
+    Returns (rank_offset[nranks+1] int64, frame_offsets[total_frames+1] int32, frames_of_rank[nranks] int32)."""
+    h = np.ascontiguousarray(headers, np.int32)
+    nr, hi = h.shape
+    roff = np.zeros(nr + 1, np.int64)
+    foff = np.zeros(int(h[:, 0].clip(0).sum()) + 1, np.int32)
+    fr = np.zeros(nr, np.int32)
+    rc = load_library().cvr_gather_layout(_ptr(h), nr, hi, _ptr(roff), _ptr(foff), len(foff), _ptr(fr))
+    if rc < 0:
+        raise CvrError(rc, "cvr_gather_layout failed")
+    return roff, foff[:rc + 1], fr
 
 
 def _ptr(a):
@@ -323,6 +355,14 @@ class Reconstruct3D:
         self._check(self.lib.cvr_debug_fetch(self.ctx, which, _ptr(out), out.nbytes, C.byref(w1), C.byref(dp)))
         return out
 
+    def sor_debug(self, n):
+        """Mean k-NN distances (input order) and (sum, sq, thr, valid, kept) of the last RemoveOutliers call (test hook)."""
+        d = np.empty(n, np.float32)
+        self._check(self.lib.cvr_debug_fetch(self.ctx, 4, _ptr(d), d.nbytes, None, None))
+        st = np.zeros(1, np.dtype([("sum", "<f8"), ("sq", "<f8"), ("thr", "<f8"), ("valid", "<i4"), ("kept", "<i4")]))
+        self._check(self.lib.cvr_debug_fetch(self.ctx, 5, _ptr(st), st.nbytes, None, None))
+        return d, st[0]
+
     # -- TrackingFrame::SetupFrame / PruneDisparityImage (TrackingFrame.cpp:25-67) --
     def SetupFrame(self, disparity):
         d = np.ascontiguousarray(disparity, np.int16).copy()
@@ -419,6 +459,28 @@ class Reconstruct3D:
 
     def wait_batch(self):
         self._check(self.lib.cvr_wait_batch(self.ctx))
+
+    # -- the gather of the filtered clouds to the mapping rank (MappingSystem::AddFrame -> MapDataBase::InsertBlock) --
+    def comm_init(self, nranks, rank, unique_id):
+        self._check(self.lib.cvr_comm_init(self.ctx, int(nranks), int(rank), C.c_char_p(bytes(unique_id))))
+        self._nranks = int(nranks)
+
+    def gather_clouds_raw(self, root, mem, out_ptr, out_capacity, frame_offsets_ptr, frame_offsets_capacity, frames_of_rank_ptr):
+        self._check(self.lib.cvr_gather_clouds(self.ctx, int(root), int(mem), out_ptr, int(out_capacity), frame_offsets_ptr,
+                                               int(frame_offsets_capacity), frames_of_rank_ptr))
+
+    def GatherClouds(self, root=0, capacity=None, max_frames=None):
+        """Gathers the clouds of the batch completed last to `root` (host memory).  Returns (points, frame_offsets,
+        frames_of_rank) on the root, None elsewhere."""
+        nr = getattr(self, "_nranks", 1)
+        cap = capacity or self.max_points * self.params.max_batch
+        mf = max_frames or nr * self.params.max_batch
+        out = np.empty(cap, POINT_DTYPE)
+        foff = np.zeros(mf + 1, np.int32)
+        fr = np.zeros(nr, np.int32)
+        self.gather_clouds_raw(root, MEM_HOST, _ptr(out), cap, _ptr(foff), len(foff), _ptr(fr))
+        nf = int(fr.sum())
+        return out[:foff[nf]].copy(), foff[:nf + 1].copy(), fr
 
 
 def points_to_pcl(points):

@@ -84,6 +84,7 @@ static int validate(const cvr_params* p, std::string& err)
         return CVR_OK;
     } else if (p->block_matcher != CVR_MATCHER_SGBM) { err = "block_matcher must be CVR_MATCHER_SGBM or CVR_MATCHER_BM"; return CVR_ERR_INVALID_ARG; }
     const cvr_sgbm_params& s = p->sgbm;
+    if (p->width > 16384) { err = "width > 16384 unsupported by the SGBM matcher (the LR check keeps a row's right-view map in shared memory)"; return CVR_ERR_UNSUPPORTED; }
     if (s.num_disparities <= 0 || s.num_disparities % 16 != 0) { err = "num_disparities must be a positive multiple of 16 (OpenCV rejects others)"; return CVR_ERR_INVALID_ARG; }
     if (s.num_disparities > 256) { err = "num_disparities > 256 unsupported"; return CVR_ERR_UNSUPPORTED; }
     if (s.block_size > 0 && s.block_size % 2 == 0) { err = "block_size must be odd"; return CVR_ERR_INVALID_ARG; }
@@ -166,10 +167,13 @@ static void free_all(cvr_ctx* c)
                      c->d_rmap1[0], c->d_rmap1[1], c->d_rmap2[0], c->d_rmap2[1], c->d_rect[0], c->d_rect[1] };
     for (void* p : ptrs) if (p) cudaFree(p);
     if (c->h_counts) cudaFreeHost(c->h_counts);
+    if (c->h_meta0) cudaFreeHost(c->h_meta0);
+    if (c->d_meta0) cudaFree(c->d_meta0);
+    cvr_comm_release(c);
     if (c->pipe_ready) {
         for (int s = 0; s < 2; s++) {
             PipeSlot& sl = c->slot[s];
-            cudaFree(sl.d_in[0]); cudaFree(sl.d_in[1]); cudaFree(sl.d_out); cudaFree(sl.d_outcnt); cudaFree(sl.d_outdisp);
+            cudaFree(sl.d_in[0]); cudaFree(sl.d_in[1]); cudaFree(sl.d_out); cudaFree(sl.d_meta); cudaFree(sl.d_outdisp); if (sl.h_meta) cudaFreeHost(sl.h_meta);
             cudaEventDestroy(sl.evH2D); cudaEventDestroy(sl.evDone);
         }
         cudaStreamDestroy(c->copy_stream); cudaStreamDestroy(c->d2h_stream);
@@ -194,7 +198,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     cvr_ctx* c = new (std::nothrow) cvr_ctx();
     if (!c) return CVR_ERR_CUDA;
     c->prm = *p; c->device = device; c->maxB = p->max_batch; c->sm_count = prop.multiProcessorCount;
-    c->launches = 0; c->profiling = false; c->timers_used[0] = c->timers_used[1] = c->timers_used[2] = 0; c->tset = 0; c->stream = nullptr; c->h_counts = nullptr;
+    c->launches = 0; c->profiling = false; c->timers_used[0] = c->timers_used[1] = c->timers_used[2] = 0; c->tset = 0; c->stream = nullptr; c->h_counts = nullptr; c->h_meta0 = nullptr; c->d_meta0 = nullptr; c->lp_valid = false; cvr_comm_reset(c);
     c->pipe_ready = false; c->copy_stream = nullptr; c->d2h_stream = nullptr; c->n_submit = c->n_wait = 0;
     memset(c->slot, 0, sizeof(c->slot));
     fill_dev_params(c);
@@ -202,7 +206,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     { const char* e_ = getenv("CVR_PATH_KERNELS"); c->force_generic = e_ && strcmp(e_, "generic") == 0; c->path_v_variant = (e_ && strcmp(e_, "v2") == 0) ? 2 : 3;
       const char* ks_ = getenv("CVR_KEEP_S"); c->keep_S = ks_ && atoi(ks_) != 0;
       const char* nn_ = getenv("CVR_NO_NN"); c->force_no_nn = nn_ && atoi(nn_) != 0;
-      const char* n_ = getenv("CVR_PATHV_NT"); c->pathv_max_nt = n_ ? atoi(n_) : 1024; memset(c->pathv_active, 0, sizeof(c->pathv_active)); c->hsum_smem_set = 0; }
+      const char* n_ = getenv("CVR_PATHV_NT"); c->pathv_max_nt = n_ ? atoi(n_) : 1024; memset(c->pathv_active, 0, sizeof(c->pathv_active)); }
     const SgbmDev& g = c->sg;
     const size_t B = (size_t)c->maxB, HW = (size_t)g.W * g.H;
     c->maxN = (int)(p->max_points > 0 ? (size_t)p->max_points : HW);
@@ -239,6 +243,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     A(dalloc(&c->d_flags, B * 64));
     A(dalloc(&c->d_sgflags, B));
     A(cudaHostAlloc((void**)&c->h_counts, sizeof(int) * B * 4, cudaHostAllocDefault));
+    A(dalloc(&c->d_meta0, CVR_META_INTS(B))); A(cudaHostAlloc((void**)&c->h_meta0, CVR_META_INTS(B) * sizeof(int), cudaHostAllocDefault));
 #undef A
     if (e != cudaSuccess) {
         g_create_err = std::string("workspace allocation failed: ") + cudaGetErrorString(e);
@@ -365,6 +370,17 @@ extern "C" int cvr_rectify(cvr_ctx* c, int ch, const uint8_t* left, size_t sl, c
 extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, int* w1, int* dp)
 {
     if (!c) return CVR_ERR_INVALID_ARG;
+    if (which == 4 || which == 5) {                                    // cloud filters: usable on filter_only contexts too
+        // 4: mean k-NN distance of every input point of the last cvr_sor call (frame 0, input order, `bytes`/4 floats);
+        // 5: its SorStats record {double sum, sq, thr; int valid, kept}
+        const void* src = which == 4 ? (const void*)c->d_meand : (const void*)c->d_sstats;
+        const size_t need = which == 4 ? bytes : sizeof(SorStats);
+        if (!dst) return CVR_OK;
+        REQUIRE(c, bytes >= need && (which == 5 || bytes <= (size_t)c->maxN * 4), "debug buffer size");
+        CVR_CUDA(c, cudaSetDevice(c->device));
+        CVR_CUDA(c, cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
+        return CVR_OK;
+    }
     STEREO_ONLY(c);
     if (c->prm.block_matcher != CVR_MATCHER_SGBM) { c->err = "debug buffers exist for the SGBM matcher only"; return CVR_ERR_INVALID_ARG; }
     const SgbmDev& g = c->sg;
@@ -536,12 +552,66 @@ extern "C" int cvr_transform_cloud(cvr_ctx* c, const cvr_point* in, int n, const
     return sync_check(c);
 }
 
-__global__ void k_copy_clouds(const cvr_point* __restrict__ src, size_t srcStride, const int* __restrict__ cnt, cvr_point* __restrict__ dst,
-                              size_t cap, int* __restrict__ cntOut)
+// ---- output side of the batched calls ----------------------------------------------------------------------------
+// The per-frame clouds of the last filter stage sit in [B][maxN] slabs.  k_pack_clouds writes them back to back into one
+// payload (frame i = points [off[i], off[i+1])) and builds the record the cloud gather exchanges between ranks:
+//   meta[0 .. maxB]                 off[0..B]   exclusive prefix of the per-frame counts (off[B] = total)
+//   meta[maxB+1], meta[maxB+2]      nframes, total points            \  "header": 2 + maxB ints, the same size on every rank
+//   meta[maxB+3 .. 2*maxB+2]        per-frame counts (0 beyond B)    /
+//   meta[2*maxB+3]                  overflow flag: a cloud did not fit the caller's device buffer
+// One payload serves the single device->host copy of the host path, the caller's packed output and the NCCL send.
+__global__ void __launch_bounds__(256) k_pack_clouds(const cvr_point* __restrict__ src, size_t srcStride, const int* __restrict__ cnt, int B, int maxB,
+                                                     cvr_point* __restrict__ dst, int* __restrict__ meta)
 {
-    const int b = blockIdx.y, n = min(cnt[b], (int)min(cap, (size_t)0x7fffffff));
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[(size_t)b * cap + i] = src[(size_t)b * srcStride + i];
-    if (blockIdx.x == 0 && threadIdx.x == 0 && cntOut) cntOut[b] = cnt[b];
+    __shared__ int ws[8];
+    const int b = blockIdx.y, lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int part = 0;
+    for (int i = threadIdx.x; i < b; i += blockDim.x) part += cnt[i];
+    part = __reduce_add_sync(0xffffffffu, part);
+    if (lane == 0) ws[w] = part;
+    __syncthreads();
+    int off = 0;
+#pragma unroll
+    for (int k = 0; k < 8; k++) off += ws[k];
+    const int n = cnt[b];
+    const uint4* s4 = (const uint4*)(src + (size_t)b * srcStride);
+    uint4* d4 = (uint4*)(dst + off);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) d4[i] = s4[i];
+    if (blockIdx.x == 0) {
+        int* hdr = meta + maxB + 1;
+        if (threadIdx.x == 0) {
+            meta[b] = off; hdr[2 + b] = n;
+            if (b == B - 1) { meta[B] = off + n; hdr[0] = B; hdr[1] = off + n; }
+            if (b == 0) meta[2 * maxB + 3] = 0;
+        }
+        if (b == 0) for (int i = B + threadIdx.x; i < maxB; i += blockDim.x) hdr[2 + i] = 0;
+    }
+}
+// device-resident callers, frame-strided layout: frame i at dst + i*cap; raises the overflow flag instead of truncating silently
+__global__ void k_copy_clouds(const cvr_point* __restrict__ src, size_t srcStride, const int* __restrict__ cnt, cvr_point* __restrict__ dst,
+                              size_t cap, int* __restrict__ cntOut, int* ovf)
+{
+    const int b = blockIdx.y, full = cnt[b], n = (int)min((size_t)full, cap);
+    const uint4* s4 = (const uint4*)(src + (size_t)b * srcStride);
+    uint4* d4 = (uint4*)(dst + (size_t)b * cap);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) d4[i] = s4[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        if (cntOut) cntOut[b] = full;
+        if (full > n) atomicExch(ovf, 1);
+    }
+}
+// device-resident callers, packed layout: the payload and its offsets
+__global__ void k_copy_packed(const cvr_point* __restrict__ src, const int* __restrict__ meta, int B, cvr_point* __restrict__ dst, size_t cap,
+                              int* __restrict__ offOut, int* __restrict__ cntOut, int maxB, int* ovf)
+{
+    const int total = meta[B], n = (int)min((size_t)total, cap);
+    const uint4* s4 = (const uint4*)src;
+    uint4* d4 = (uint4*)dst;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) d4[i] = s4[i];
+    if (blockIdx.x == 0) {
+        for (int i = threadIdx.x; i <= B; i += blockDim.x) { if (offOut) offOut[i] = meta[i]; if (cntOut && i < B) cntOut[i] = meta[maxB + 3 + i]; }
+        if (threadIdx.x == 0 && total > n) atomicExch(ovf, 1);
+    }
 }
 
 // The per-frame chain in two halves, each enqueued on c->stream (whatever that currently is):
@@ -615,6 +685,60 @@ static int check_batch_args(cvr_ctx* c, int nframes, const cvr_batch* io)
     return CVR_OK;
 }
 
+// The workspace slab that is free once the last enabled filter stage has written `fin`: the packed payload of the synchronous
+// call goes there (the pipelined calls pack into their slot instead).
+static cvr_point* free_slab(cvr_ctx* c, const cvr_point* fin) { return fin == c->d_cloud ? c->d_vox : c->d_cloud; }
+
+static int enqueue_pack(cvr_ctx* c, int B, const cvr_point* fin, const int* fcnt, cvr_point* dst, int* meta)
+{
+    k_pack_clouds<<<dim3(32, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, B, c->maxB, dst, meta);
+    LAUNCH_CHECK(c);
+    return CVR_OK;
+}
+
+// Device-resident outputs of one batch (strided or packed layout), from the packed payload `pk` / the slabs `fin`.
+static int enqueue_device_outputs(cvr_ctx* c, int B, const cvr_batch* io, const cvr_point* fin, const int* fcnt, const cvr_point* pk, int* meta)
+{
+    int* ovf = meta + 2 * (size_t)c->maxB + 3;
+    if (io->cloud_packed) {
+        k_copy_packed<<<64, 256, 0, c->stream>>>(pk, meta, B, io->cloud_packed, io->cloud_packed_capacity, io->cloud_offsets, io->cloud_count, c->maxB, ovf);
+        LAUNCH_CHECK(c);
+    } else if (io->cloud) {
+        k_copy_clouds<<<dim3(32, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, io->cloud, io->cloud_capacity, io->cloud_count, ovf);
+        LAUNCH_CHECK(c);
+    } else if (io->cloud_count) {
+        CVR_CUDA(c, cudaMemcpyAsync(io->cloud_count, fcnt, sizeof(int) * B, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    return CVR_OK;
+}
+
+// Host-side outputs of one batch from its packed payload on the device (meta already on the host in hm).
+static int fetch_host_outputs(cvr_ctx* c, int B, const cvr_batch* io, const cvr_point* pk, const int* hm, cudaStream_t st)
+{
+    const int* off = hm; const int* cnt = hm + c->maxB + 3;
+    const size_t total = (size_t)off[B];
+    if (io->cloud_count) memcpy(io->cloud_count, cnt, sizeof(int) * B);
+    if (io->cloud_packed) {
+        if (io->cloud_offsets) memcpy(io->cloud_offsets, off, sizeof(int) * (B + 1));
+        if (total > io->cloud_packed_capacity) { c->err = "cloud_packed_capacity too small"; return CVR_ERR_CAPACITY; }
+        if (total) CVR_CUDA(c, cudaMemcpyAsync(io->cloud_packed, pk, total * sizeof(cvr_point), cudaMemcpyDeviceToHost, st));   // ONE copy for the batch
+    } else if (io->cloud) {
+        for (int i = 0; i < B; i++)
+            if ((size_t)cnt[i] > io->cloud_capacity) { c->err = "cloud_capacity too small"; return CVR_ERR_CAPACITY; }
+        // frames that fill their slot exactly are rare: the strided layout costs one copy per frame
+        for (int i = 0; i < B; i++)
+            if (cnt[i] > 0)
+                CVR_CUDA(c, cudaMemcpyAsync(io->cloud + (size_t)i * io->cloud_capacity, pk + off[i], (size_t)cnt[i] * sizeof(cvr_point), cudaMemcpyDeviceToHost, st));
+    }
+    return CVR_OK;
+}
+
+static void set_last_pack(cvr_ctx* c, const cvr_point* pk, const int* d_meta, const int* h_meta, int B, bool valid)
+{
+    c->lp_valid = valid; c->lp_pts = pk; c->lp_dhdr = d_meta ? d_meta + c->maxB + 1 : nullptr; c->lp_nframes = B;
+    c->lp_total = (valid && h_meta) ? h_meta[B] : 0;
+}
+
 extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
 {
     if (!c) return CVR_ERR_INVALID_ARG;
@@ -625,13 +749,21 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     const int W = c->sg.W, H = c->sg.H, B = nframes;
     const size_t rowBytes = (size_t)W * ch;
     const int stages = io->stages ? io->stages : 15;
+    const bool host = io->mem == CVR_MEM_HOST;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    c->lp_valid = false;
     timers_begin(c, 0);
     const uint8_t *dl, *dr; size_t lstep, lfs, rstep, rfs;
-    if (io->mem == CVR_MEM_HOST) {
-        for (int i = 0; i < B; i++) {
-            CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0] + (size_t)i * rowBytes * H, rowBytes, io->left + (size_t)i * io->left_frame_stride, io->left_step, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
-            CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1] + (size_t)i * rowBytes * H, rowBytes, io->right + (size_t)i * io->right_frame_stride, io->right_step, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
+    if (host) {
+        const bool dense = io->left_frame_stride == io->left_step * (size_t)H && io->right_frame_stride == io->right_step * (size_t)H;
+        if (dense) {                                                   // frames back to back: one 2-D copy per camera for the whole batch
+            CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], rowBytes, io->left, io->left_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->stream));
+            CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], rowBytes, io->right, io->right_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->stream));
+        } else {
+            for (int i = 0; i < B; i++) {
+                CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0] + (size_t)i * rowBytes * H, rowBytes, io->left + (size_t)i * io->left_frame_stride, io->left_step, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
+                CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1] + (size_t)i * rowBytes * H, rowBytes, io->right + (size_t)i * io->right_frame_stride, io->right_step, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
+            }
         }
         dl = c->d_in[0]; dr = c->d_in[1]; lstep = rstep = rowBytes; lfs = rfs = rowBytes * H;
         cvr_stage_mark(c, "h2d");
@@ -643,33 +775,25 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     if (rc) return rc;
     // ---- outputs ----
     if (io->disp) {
-        const cudaMemcpyKind kind = io->mem == CVR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
-        for (int i = 0; i < B; i++)
-            CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io->disp + (size_t)i * io->disp_frame_stride, io->disp_step, c->d_med + (size_t)i * W * H, (size_t)W * 2,
-                                          (size_t)W * 2, H, kind, c->stream));
+        const cudaMemcpyKind kind = host ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+        const bool denseD = io->disp_frame_stride == io->disp_step * (size_t)H;
+        if (denseD) CVR_CUDA(c, cudaMemcpy2DAsync(io->disp, io->disp_step, c->d_med, (size_t)W * 2, (size_t)W * 2, (size_t)H * B, kind, c->stream));
+        else
+            for (int i = 0; i < B; i++)
+                CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io->disp + (size_t)i * io->disp_frame_stride, io->disp_step, c->d_med + (size_t)i * W * H, (size_t)W * 2,
+                                              (size_t)W * 2, H, kind, c->stream));
     }
-    if (fin && (io->cloud || io->cloud_count)) {
-        CVR_CUDA(c, cudaMemcpyAsync(c->h_counts, fcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, c->stream));
+    if (fin) {
+        cvr_point* pk = free_slab(c, fin);
+        rc = enqueue_pack(c, B, fin, fcnt, pk, c->d_meta0);
+        if (rc) return rc;
+        if (!host) { rc = enqueue_device_outputs(c, B, io, fin, fcnt, pk, c->d_meta0); if (rc) return rc; }
+        CVR_CUDA(c, cudaMemcpyAsync(c->h_meta0, c->d_meta0, CVR_META_INTS(c->maxB) * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
         rc = sync_check(c);
         if (rc) return rc;
-        if (io->cloud)
-            for (int i = 0; i < B; i++)
-                if ((size_t)c->h_counts[i] > io->cloud_capacity) { c->err = "cloud_capacity too small"; return CVR_ERR_CAPACITY; }
-        if (io->mem == CVR_MEM_HOST) {
-            if (io->cloud_count) memcpy(io->cloud_count, c->h_counts, sizeof(int) * B);
-            if (io->cloud)
-                for (int i = 0; i < B; i++)
-                    if (c->h_counts[i] > 0)
-                        CVR_CUDA(c, cudaMemcpyAsync(io->cloud + (size_t)i * io->cloud_capacity, fin + (size_t)i * c->maxN, (size_t)c->h_counts[i] * sizeof(cvr_point),
-                                                    cudaMemcpyDeviceToHost, c->stream));
-        } else {
-            if (io->cloud) {
-                k_copy_clouds<<<dim3(64, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, io->cloud, io->cloud_capacity, io->cloud_count);
-                c->launches++;
-            } else if (io->cloud_count) {
-                CVR_CUDA(c, cudaMemcpyAsync(io->cloud_count, fcnt, sizeof(int) * B, cudaMemcpyDeviceToDevice, c->stream));
-            }
-        }
+        set_last_pack(c, pk, c->d_meta0, c->h_meta0, B, true);
+        if (host) { rc = fetch_host_outputs(c, B, io, pk, c->h_meta0, c->stream); if (rc) return rc; }
+        else if (c->h_meta0[2 * (size_t)c->maxB + 3]) { c->err = "a cloud did not fit the caller's device buffer (cloud_capacity / cloud_packed_capacity too small)"; return CVR_ERR_CAPACITY; }
     }
     cvr_stage_mark(c, "out");
     rc = sync_check(c);
@@ -686,7 +810,8 @@ static int pipe_init(cvr_ctx* c)
     for (int s = 0; s < 2; s++) {
         PipeSlot& sl = c->slot[s];
         CVR_CUDA(c, dalloc(&sl.d_in[0], B * HW * 4)); CVR_CUDA(c, dalloc(&sl.d_in[1], B * HW * 4));
-        CVR_CUDA(c, dalloc(&sl.d_out, B * N)); CVR_CUDA(c, dalloc(&sl.d_outcnt, B)); CVR_CUDA(c, dalloc(&sl.d_outdisp, B * HW));
+        CVR_CUDA(c, dalloc(&sl.d_out, B * N)); CVR_CUDA(c, dalloc(&sl.d_meta, CVR_META_INTS(B))); CVR_CUDA(c, dalloc(&sl.d_outdisp, B * HW));
+        CVR_CUDA(c, cudaHostAlloc((void**)&sl.h_meta, CVR_META_INTS(B) * sizeof(int), cudaHostAllocDefault));
         CVR_CUDA(c, cudaEventCreateWithFlags(&sl.evH2D, cudaEventDisableTiming));
         CVR_CUDA(c, cudaEventCreateWithFlags(&sl.evDone, cudaEventDisableTiming));
         sl.busy = false; sl.used = false;
@@ -740,22 +865,23 @@ extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     rc = enqueue_chain(c, B, stages, dl, lstep, lfs, dr, rstep, rfs, ch, &fin, &fcnt);
     if (rc) return rc;
     sl.hasCloud = fin != nullptr;
-    if (fin && host) {                                                 // park the results in the slot so the next batch may overwrite the workspace
-        k_copy_clouds<<<dim3(64, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, sl.d_out, (size_t)c->maxN, sl.d_outcnt);
-        c->launches++;
-    } else if (fin) {                                                  // device-resident outputs: straight into the caller's buffers
-        if (io->cloud) {
-            k_copy_clouds<<<dim3(64, B), 256, 0, c->stream>>>(fin, (size_t)c->maxN, fcnt, io->cloud, io->cloud_capacity, io->cloud_count);
-            c->launches++;
-        } else if (io->cloud_count) {
-            CVR_CUDA(c, cudaMemcpyAsync(io->cloud_count, fcnt, sizeof(int) * B, cudaMemcpyDeviceToDevice, c->stream));
-        }
+    if (fin) {
+        // the packed payload is parked in the slot (the next batch may overwrite the workspace); it feeds the host copy,
+        // device-resident packed outputs and cvr_gather_clouds
+        rc = enqueue_pack(c, B, fin, fcnt, sl.d_out, sl.d_meta);
+        if (rc) return rc;
+        if (!host) { rc = enqueue_device_outputs(c, B, io, fin, fcnt, sl.d_out, sl.d_meta); if (rc) return rc; }
+        CVR_CUDA(c, cudaMemcpyAsync(sl.h_meta, sl.d_meta, CVR_META_INTS(c->maxB) * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     }
     if (io->disp && host) CVR_CUDA(c, cudaMemcpyAsync(sl.d_outdisp, c->d_med, (size_t)B * W * H * 2, cudaMemcpyDeviceToDevice, c->stream));
-    if (io->disp && !host)
-        for (int i = 0; i < B; i++)
-            CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io->disp + (size_t)i * io->disp_frame_stride, io->disp_step, c->d_med + (size_t)i * W * H, (size_t)W * 2,
-                                          (size_t)W * 2, H, cudaMemcpyDeviceToDevice, c->stream));
+    if (io->disp && !host) {
+        if (io->disp_frame_stride == io->disp_step * (size_t)H)
+            CVR_CUDA(c, cudaMemcpy2DAsync(io->disp, io->disp_step, c->d_med, (size_t)W * 2, (size_t)W * 2, (size_t)H * B, cudaMemcpyDeviceToDevice, c->stream));
+        else
+            for (int i = 0; i < B; i++)
+                CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io->disp + (size_t)i * io->disp_frame_stride, io->disp_step, c->d_med + (size_t)i * W * H, (size_t)W * 2,
+                                              (size_t)W * 2, H, cudaMemcpyDeviceToDevice, c->stream));
+    }
     cvr_stage_mark(c, "out");
     CVR_CUDA(c, cudaEventRecord(sl.evDone, c->stream));
     c->tset = 0;
@@ -764,41 +890,44 @@ extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     return CVR_OK;
 }
 
+// Collects the oldest batch; whatever happens, its slot is released and the pipeline moves on.
+static int wait_slot(cvr_ctx* c, PipeSlot& sl, int set)
+{
+    const cvr_batch& io = sl.io;
+    const int B = sl.nframes, W = c->sg.W, H = c->sg.H;
+    CVR_CUDA(c, cudaEventSynchronize(sl.evDone));
+    timers_end(c, set);
+    set_last_pack(c, sl.d_out, sl.d_meta, sl.h_meta, B, sl.hasCloud);
+    if (io.mem != CVR_MEM_HOST) {                                      // device-resident batch: the results are already in the caller's buffers
+        if (sl.hasCloud && sl.h_meta[2 * (size_t)c->maxB + 3]) {
+            c->err = "a cloud did not fit the caller's device buffer (cloud_capacity / cloud_packed_capacity too small)";
+            return CVR_ERR_CAPACITY;
+        }
+        return CVR_OK;
+    }
+    int rc = CVR_OK;
+    if (sl.hasCloud) rc = fetch_host_outputs(c, B, &io, sl.d_out, sl.h_meta, c->d2h_stream);
+    if (io.disp && rc == CVR_OK) {
+        if (io.disp_frame_stride == io.disp_step * (size_t)H)
+            CVR_CUDA(c, cudaMemcpy2DAsync(io.disp, io.disp_step, sl.d_outdisp, (size_t)W * 2, (size_t)W * 2, (size_t)H * B, cudaMemcpyDeviceToHost, c->d2h_stream));
+        else
+            for (int i = 0; i < B; i++)
+                CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io.disp + (size_t)i * io.disp_frame_stride, io.disp_step, sl.d_outdisp + (size_t)i * W * H, (size_t)W * 2,
+                                              (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->d2h_stream));
+    }
+    cudaError_t e = cudaStreamSynchronize(c->d2h_stream);
+    if (e != cudaSuccess && rc == CVR_OK) { c->err = std::string("d2h stream sync: ") + cudaGetErrorString(e); rc = CVR_ERR_CUDA; }
+    return rc;
+}
+
 extern "C" int cvr_wait_batch(cvr_ctx* c)
 {
     if (!c) return CVR_ERR_INVALID_ARG;
     if (!c->pipe_ready || c->n_wait >= c->n_submit) { c->err = "no batch in flight"; return CVR_ERR_INVALID_ARG; }
     CVR_CUDA(c, cudaSetDevice(c->device));
     PipeSlot& sl = c->slot[c->n_wait & 1];
-    const cvr_batch& io = sl.io;
-    const int B = sl.nframes, W = c->sg.W, H = c->sg.H;
-    CVR_CUDA(c, cudaEventSynchronize(sl.evDone));
-    timers_end(c, 1 + (c->n_wait & 1));
-    int* hc = c->h_counts + (size_t)c->maxB * (1 + (c->n_wait & 1));
-    int rc = CVR_OK;
-    if (io.mem != CVR_MEM_HOST) {                                      // device-resident batch: the results are already in the caller's buffers
-        sl.busy = false;
-        c->n_wait++;
-        return CVR_OK;
-    }
-    if (sl.hasCloud && (io.cloud || io.cloud_count)) {
-        CVR_CUDA(c, cudaMemcpyAsync(hc, sl.d_outcnt, sizeof(int) * B, cudaMemcpyDeviceToHost, c->d2h_stream));
-        CVR_CUDA(c, cudaStreamSynchronize(c->d2h_stream));
-        if (io.cloud_count) memcpy(io.cloud_count, hc, sizeof(int) * B);
-        if (io.cloud)
-            for (int i = 0; i < B; i++) {
-                if ((size_t)hc[i] > io.cloud_capacity) { c->err = "cloud_capacity too small"; rc = CVR_ERR_CAPACITY; break; }
-                if (hc[i] > 0)
-                    CVR_CUDA(c, cudaMemcpyAsync(io.cloud + (size_t)i * io.cloud_capacity, sl.d_out + (size_t)i * c->maxN, (size_t)hc[i] * sizeof(cvr_point),
-                                                cudaMemcpyDeviceToHost, c->d2h_stream));
-            }
-    }
-    if (io.disp)
-        for (int i = 0; i < B; i++)
-            CVR_CUDA(c, cudaMemcpy2DAsync((uint8_t*)io.disp + (size_t)i * io.disp_frame_stride, io.disp_step, sl.d_outdisp + (size_t)i * W * H, (size_t)W * 2,
-                                          (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->d2h_stream));
-    CVR_CUDA(c, cudaStreamSynchronize(c->d2h_stream));
-    sl.busy = false;
+    const int rc = wait_slot(c, sl, 1 + (int)(c->n_wait & 1));
+    sl.busy = false;                                                   // also on errors: a failed batch must not wedge the pipeline
     c->n_wait++;
     return rc;
 }

@@ -79,8 +79,9 @@ struct StageTimer {
 // One in-flight batch of the pipelined host path (cvr_submit_batch / cvr_wait_batch).
 struct PipeSlot {
     uint8_t* d_in[2];        // staged BGR/gray input of this slot
-    cvr_point* d_out;        // filtered clouds [B][maxN]
-    int* d_outcnt;           // [B]
+    cvr_point* d_out;        // filtered clouds of the batch, packed back to back (capacity B * maxN)
+    int* d_meta;             // offsets / gather header / overflow flag of the packed payload (layout: k_pack_clouds)
+    int* h_meta;             // pinned copy of d_meta, valid once evDone has fired
     int16_t* d_outdisp;      // [B][H][W]
     cudaEvent_t evH2D, evDone;   // inputs uploaded / results parked, slot reusable
     bool busy, used;
@@ -160,10 +161,17 @@ struct cvr_ctx {
     bool pipe_ready;
     cudaStream_t copy_stream, d2h_stream;
     long long n_submit, n_wait;
+    int* d_meta0; int* h_meta0;   // as PipeSlot::d_meta / h_meta, for the synchronous cvr_process_batch
+    // the packed payload of the batch completed last (cvr_process_batch / cvr_wait_batch): what cvr_gather_clouds sends
+    bool lp_valid; const cvr_point* lp_pts; const int* lp_dhdr; int lp_nframes; int lp_total;
+    // cloud gather (gather.cu): NCCL communicator bound at run time, its stream and staging
+    void* comm; bool comm_owned; int comm_nranks, comm_rank;
+    cudaStream_t comm_stream;
+    int* d_hdr_all; int* h_hdr_all;           // [nranks][2 + maxB] gathered headers (device / pinned)
+    cvr_point* d_gather; size_t gather_cap;   // root: receive buffer when the caller wants the clouds on the host
     int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
     int smem_optin;          // max dynamic shared memory per block (opt-in)
     bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)
-    size_t hsum_smem_set;    // dynamic shared memory k_pix_hsum has been opted in to on this context's device
     bool keep_S;             // CVR_KEEP_S=1: the last aggregation pass also writes the final S volume (cvr_debug_fetch(1); test hook)
     bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)
@@ -179,6 +187,17 @@ struct cvr_ctx {
             return CVR_ERR_CUDA;                                                                  \
         }                                                                                         \
     } while (0)
+
+// after a kernel launch: report a failed launch (and only count the ones that were accepted)
+#define LAUNCH_CHECK(c)                                                                  \
+    do {                                                                                 \
+        cudaError_t e__ = cudaGetLastError();                                            \
+        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
+        (c)->launches++;                                                                 \
+    } while (0)
+
+// ints in a packed payload's meta record (k_pack_clouds, api.cu)
+#define CVR_META_INTS(maxB) (2 * (size_t)(maxB) + 4)
 
 static inline int cvr_div_up(int a, int b) { return (a + b - 1) / b; }
 static inline size_t cvr_div_up_sz(size_t a, size_t b) { return (a + b - 1) / b; }
@@ -209,3 +228,7 @@ int cvr_launch_transform(cvr_ctx* c, const cvr_point* in, cvr_point* out, int n,
 void cvr_stage_mark(cvr_ctx* c, const char* name);
 // message slot read by cvr_last_error(NULL): used by entry points that have no context
 void cvr_set_thread_error(const char* msg);
+// gather.cu
+void cvr_comm_reset(cvr_ctx* c);      // fields to their empty state (context creation)
+void cvr_comm_release(cvr_ctx* c);    // destroys an owned communicator and the gather staging
+

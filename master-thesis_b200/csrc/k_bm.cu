@@ -12,12 +12,6 @@
 // SAD array index d stands for disparity ndisp - 1 - d + minDisparity, exactly as in OpenCV (ties go to the larger disparity).
 #include "cvr_internal.cuh"
 
-#define LAUNCH_CHECK(c)                                                                  \
-    do {                                                                                 \
-        (c)->launches++;                                                                 \
-        cudaError_t e__ = cudaGetLastError();                                            \
-        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
-    } while (0)
 
 __global__ void k_bm_prefilter(const uint8_t* __restrict__ gray, size_t grayFrameStride, uint8_t* __restrict__ pre, BmDev p)
 {

@@ -11,12 +11,6 @@
 #include <float.h>
 #include <mutex>
 
-#define LAUNCH_CHECK(c)                                                                  \
-    do {                                                                                 \
-        (c)->launches++;                                                                 \
-        cudaError_t e__ = cudaGetLastError();                                            \
-        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
-    } while (0)
 
 // ------------------------------------------------------------------------------------------------
 // prune
@@ -70,8 +64,9 @@ __global__ void k_prune_norm(const int16_t* __restrict__ disp, int N, PruneStats
 }
 // cv::meanStdDev (population sigma, f64) -> cv::threshold(u8 > floor(sigma*factor)) -> zero pruned disparities ->
 // convertTo(CV_32F, 1/16) -> mask &= disparity > 0.
-__global__ void k_prune_apply(const int16_t* __restrict__ disp, const uint8_t* u8, int N, const PruneStats* __restrict__ st,
-                              double factor, int16_t* __restrict__ pruned, float* __restrict__ dispf, uint8_t* mask)
+// disp / pruned and u8 / mask may alias (in-place use): every element is read before the same thread writes it.
+__global__ void k_prune_apply(const int16_t* disp, const uint8_t* u8, int N, const PruneStats* __restrict__ st,
+                              double factor, int16_t* pruned, float* __restrict__ dispf, uint8_t* mask)
 {
     const int b = blockIdx.y;
     const double inv = __ddiv_rn(1.0, (double)N);
@@ -267,6 +262,7 @@ extern "C" int cvr_prune_noalloc(const int16_t* d_disp, int width, int height, d
     const int N = (int)npix;
     const int gx = min(cvr_div_up(N, 256), 296);
     // the record keeps the previous call's min/max/sums: reset it first; the 8-bit image is fully rewritten before use
+    (void)cudaGetLastError();                                      // an earlier, unrelated error of the caller is not this call's failure
     k_prune_init<<<1, 32, 0, s>>>(st, 1);
     k_prune_minmax<<<dim3(gx, 1), 256, 0, s>>>(d_disp, N, st);
     k_prune_norm<<<dim3(gx, 1), 256, 0, s>>>(d_disp, N, st, u8);

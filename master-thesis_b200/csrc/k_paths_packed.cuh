@@ -591,11 +591,13 @@ __device__ __forceinline__ void v3_finish(const V3Ctx& x, const SgbmDev& p, cons
     unsigned iA, iB;
     path_info<NN>(lane == 0 ? mn1 : (lane == 1 ? mn2 : mn3), x.P2, iA, iB);
     if (lane < 3) *(uint2*)(cb + lane * BLK + DW) = make_uint2(iA, iB);
-    if (FT != 0 && firstCol && x.hasL) {                              // my first column's down-left block -> left neighbour's right inbox
+    // the last row's edges have no consumer (nobody posts expect_tx for them): not pushed, so that no st.async can still be
+    // in flight towards a CTA that has already left the kernel
+    if (FT != 0 && firstCol && x.hasL && x.moreRows) {                // my first column's down-left block -> left neighbour's right inbox
         st_async_words<NWD>(x.pushL_dst + lane * NWD * 4, M3, x.pushL_bar);
         if (lane == 2) st_async_v2(x.pushL_dst + DW * 4, iA, iB, x.pushL_bar);
     }
-    if (LT != 0 && lastCol && x.hasR) {                               // my last column's down-right block -> right neighbour's left inbox
+    if (LT != 0 && lastCol && x.hasR && x.moreRows) {                 // my last column's down-right block -> right neighbour's left inbox
         st_async_words<NWD>(x.pushR_dst + lane * NWD * 4, M1, x.pushR_bar);
         if (lane == 0) st_async_v2(x.pushR_dst + DW * 4, iA, iB, x.pushR_bar);
     }

@@ -717,12 +717,6 @@ __global__ void k_fill_s16(int16_t* p, size_t n, int v)
 
 // ------------------------------------------------------------------------------------------------
 // host-side launchers
-#define LAUNCH_CHECK(c)                                                                  \
-    do {                                                                                 \
-        (c)->launches++;                                                                 \
-        cudaError_t e__ = cudaGetLastError();                                            \
-        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
-    } while (0)
 
 int cvr_launch_gray(cvr_ctx* c, int B, const uint8_t* left, size_t lstep, size_t lfs, const uint8_t* right, size_t rstep,
                     size_t rfs, int channels)
@@ -943,11 +937,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         const int segMax = cvr_div_up(p.W1, nseg) + 1;
         const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;
         const size_t smem = (nLmax + nRmax + 4) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)4 * p.ring * p.Dp;   // descriptors + two rings (one per thread group) of packed cost pairs
-        size_t& smem_set = c->hsum_smem_set;                          // per context: the attribute belongs to this context's device
-        if (smem > 48 * 1024 && smem > smem_set) {
-            CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            smem_set = smem;
-        }
+        // the opt-in is per function and device, shared by every context on that device: set it before each launch that needs it
+        if (smem > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_pix_hsum<<<dim3(p.H * nseg, B), p.Dp, smem, c->stream>>>(c->d_gray, (size_t)2 * p.H * p.Wp, c->d_volA, p, nseg);
         LAUNCH_CHECK(c);
         cvr_stage_mark(c, "pix_hsum");
@@ -973,7 +964,9 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         default: c->err = "unsupported padded disparity count"; return CVR_ERR_UNSUPPORTED;
     }
     if (rc) return rc;
-    k_lrcheck<<<dim3(p.H, B), 256, (size_t)p.W * 2 * sizeof(int), c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p);
+    const size_t lrSmem = (size_t)p.W * 2 * sizeof(int);              // validate() keeps this within the opt-in limit (width <= 16384)
+    if (lrSmem > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_lrcheck, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lrSmem));
+    k_lrcheck<<<dim3(p.H, B), 256, lrSmem, c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p);
     LAUNCH_CHECK(c);
     if ((p.W & 1) == 0) k_median3_x2<<<dim3(cvr_div_up(p.W, 256), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
     else k_median3<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);

@@ -9,12 +9,6 @@
 #include "cvr_scan.cuh"
 #include <float.h>
 
-#define LAUNCH_CHECK(c)                                                                  \
-    do {                                                                                 \
-        (c)->launches++;                                                                 \
-        cudaError_t e__ = cudaGetLastError();                                            \
-        if (e__ != cudaSuccess) { (c)->err = std::string("kernel launch: ") + cudaGetErrorString(e__) + " at " + __FILE__ + ":" + std::to_string(__LINE__); return CVR_ERR_CUDA; } \
-    } while (0)
 
 struct SorGrid {
     float mn[3];

@@ -179,7 +179,42 @@ def rect_cases():
         print(name, "interior taps %.1f%%" % (100 * inside))
 
 
+# ---- the full-size BASELINE.json shapes (configs[2], configs[3]) at the reference's block size: too large to store whole,
+# so a fixture keeps the CRC32 of cv2's disparity / pruned disparity / mask plus every 16th row of the disparity
+BIG_CASES = {   # name: (H, W, D, block_size, mode, seed)
+    "hd_d256_bs27": (1080, 1920, 256, 27, 0, 5),
+    "hd_d256_bs27_hh": (1080, 1920, 256, 27, 1, 5),
+    "hd_d256_bs5": (1080, 1920, 256, 5, 0, 6),
+    "spi_d192_bs27_hh": (720, 1280, 192, 27, 1, 5),
+}
+
+
+def big_cases():
+    for name, (H, W, D, bs, mode, seed) in BIG_CASES.items():
+        lb, rb = O.synth_pair(H, W, D, seed, color=True)
+        gl = cv2.cvtColor(lb, cv2.COLOR_BGR2GRAY); gr = cv2.cvtColor(rb, cv2.COLOR_BGR2GRAY)
+        p = O.reference_sgbm_params(block_size=bs, num_disparities=D, mode=mode)
+        disp = cv_sgbm(gl, gr, p, True)
+        dn = cv2.normalize(disp, None, 0, 255, cv2.NORM_MINMAX, cv2.CV_8U)
+        _, std = cv2.meanStdDev(dn)
+        _, mask = cv2.threshold(dn, std[0][0] * 1.3, 255, cv2.THRESH_BINARY)
+        pruned = disp.copy(); pruned[mask == 0] = 0
+        dispf = cv2.multiply(pruned.astype(np.float32), 1.0 / 16.0)
+        mask2 = mask.copy(); mask2[dispf <= 0] = 0
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), meta=np.array([H, W, D, bs, mode, 0, seed], np.int64),
+                            crc=np.array([zlib.crc32(lb.tobytes()), zlib.crc32(rb.tobytes())], np.uint64),
+                            disp_crc=np.array([zlib.crc32(disp.tobytes())], np.uint64), rows16=disp[::16].copy(),
+                            valid_count=np.array([int((disp >= 0).sum())], np.int64),
+                            pruned_crc=np.array([zlib.crc32(pruned.tobytes())], np.uint64), mask_crc=np.array([zlib.crc32(mask2.tobytes())], np.uint64),
+                            sigma=np.float64(std[0][0]), cv_version=np.array(cv2.__version__))
+        print(name, "valid %.1f%%" % (100 * (disp >= 0).mean()), os.path.getsize(os.path.join(HERE, name + ".npz")) // 1024, "KiB")
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "big":
+        big_cases()
+        sys.exit(0)
+    big_cases()
     rect_cases()
     bm_cases()
     special()

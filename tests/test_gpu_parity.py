@@ -7,7 +7,7 @@ import zlib
 import numpy as np
 import pytest
 
-from conftest import GOLDEN_LARGE, GOLDEN_SMALL, load_golden
+from conftest import GOLDEN_BIG, GOLDEN_LARGE, GOLDEN_SMALL, load_golden
 
 pytestmark = pytest.mark.gpu
 
@@ -55,6 +55,38 @@ def test_disparity_bit_exact_vs_cv2_golden(cvr, oracle, name):
     rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD, spw=0), mode=mode)
     got = rec.GenerateDisparityMap(lb, rb)
     assert np.array_equal(got, g["disp_nospeckle"])
+    rec.close()
+
+
+@pytest.mark.parametrize("name", GOLDEN_BIG)
+def test_full_size_bit_exact_vs_cv2_golden(cvr, oracle, name):
+    """BASELINE.json configs[2] / configs[3] at the reference's block size 27 (and 5): cv2's disparity, pruned disparity and
+    prune mask by CRC32 plus every 16th disparity row.  hd_* is the shape that runs the vertical path kernel as a
+    non-portable 16-CTA cluster with 512-thread CTAs (8 disparities per lane)."""
+    g = load_golden(name)
+    H, W, D, bs, mode, minD, lb, rb = _golden_inputs(oracle, g)
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD), mode=mode)
+    disp = rec.GenerateDisparityMap(lb, rb)
+    bad = int((disp[::16] != g["rows16"]).sum())
+    assert bad == 0, "%d pixels of the sampled rows differ from cv2" % bad
+    assert zlib.crc32(disp.tobytes()) == int(g["disp_crc"][0])
+    assert int((disp >= 0).sum()) == int(g["valid_count"][0])
+    pruned, dispf, mask = rec.SetupFrame(disp)
+    assert zlib.crc32(pruned.tobytes()) == int(g["pruned_crc"][0]) and zlib.crc32(mask.tobytes()) == int(g["mask_crc"][0])
+    assert np.array_equal(dispf, pruned.astype(np.float32) / np.float32(16))
+    rec.close()
+
+
+@pytest.mark.parametrize("name", GOLDEN_SMALL + GOLDEN_LARGE)
+def test_prune_vs_cv2_golden(cvr, oracle, name):
+    """TrackingFrame::SetupFrame on every fixture's cv2 disparity: pruned map and mask equal cv2's normalize / meanStdDev /
+    threshold / convertTo chain."""
+    g = load_golden(name)
+    H, W, D, bs, mode, minD, seed = [int(v) for v in g["meta"]]
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, minD), mode=mode)
+    pruned, dispf, mask = rec.SetupFrame(g["disp"])
+    assert np.array_equal(pruned, g["pruned"]) and np.array_equal(mask, g["mask"])
+    assert np.array_equal(dispf, g["pruned"].astype(np.float32) / np.float32(16))
     rec.close()
 
 

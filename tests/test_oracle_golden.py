@@ -6,7 +6,7 @@ import zlib
 import numpy as np
 import pytest
 
-from conftest import GOLDEN_LARGE, GOLDEN_SMALL, load_golden
+from conftest import GOLDEN_BIG, GOLDEN_LARGE, GOLDEN_SMALL, load_golden
 
 
 def _inputs(O, g):
@@ -49,6 +49,19 @@ def test_prune_and_reproject_oracle_matches_cv2(oracle, name):
     assert int((xyz[..., 2] != 10000.0).sum()) == int(g["xyz_valid_count"][0])
     if "xyz" in g:
         assert np.array_equal(xyz.view(np.uint32), g["xyz"].view(np.uint32))
+
+
+@pytest.mark.parametrize("name", GOLDEN_BIG)
+def test_oracle_matches_cv2_at_full_size(oracle, name):
+    """BASELINE.json configs[2] / configs[3] at the reference's parameters: 1920x1080 D=256 and 1280x720 D=192 MODE_HH."""
+    g = load_golden(name)
+    lb, rb, p = _inputs(oracle, g)
+    disp = oracle.sgbm(oracle.gray_bgr(lb), oracle.gray_bgr(rb), p)
+    assert zlib.crc32(disp.tobytes()) == int(g["disp_crc"][0])
+    assert np.array_equal(disp[::16], g["rows16"])
+    pruned, dispf, mask, _, st = oracle.prune(disp)
+    assert zlib.crc32(pruned.tobytes()) == int(g["pruned_crc"][0]) and zlib.crc32(mask.tobytes()) == int(g["mask_crc"][0])
+    assert st[2] == float(g["sigma"])
 
 
 def test_known_answers(oracle):

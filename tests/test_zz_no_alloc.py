@@ -52,11 +52,37 @@ def test_prune_noalloc_matches_cvr_prune_twice_in_a_row(cvr, oracle):
         assert np.array_equal(d_f32.cpu().numpy(), want_f32)
         assert np.array_equal(d_mask.cpu().numpy(), want_mask)
         assert want_mask.any() and not want_mask.all()           # the comparison is not vacuous
+        # ... and both equal the CPU oracle's prune (itself pinned against cv2 by tests/test_oracle_golden.py)
+        o_pruned, o_f32, o_mask, _, _ = oracle.prune(disp)
+        assert np.array_equal(want_pruned, o_pruned) and np.array_equal(want_f32, o_f32) and np.array_equal(want_mask, o_mask)
     # optional outputs may be left out
     rc = lib.cvr_prune_noalloc(d_in.data_ptr(), W, H, C.c_double(1.3), None, None, d_mask.data_ptr(), None)
     torch.cuda.synchronize()
     assert rc == 0 and np.array_equal(d_mask.cpu().numpy(), want_mask)
+    # in place (d_pruned == d_disp), the natural port of TrackingFrame::PruneDisparityImage
+    rc = lib.cvr_prune_noalloc(d_in.data_ptr(), W, H, C.c_double(1.3), d_in.data_ptr(), None, None, None)
+    torch.cuda.synchronize()
+    assert rc == 0 and np.array_equal(d_in.cpu().numpy(), want_pruned)
     rec.close()
+
+
+def test_prune_noalloc_matches_cv2_golden(cvr):
+    """The allocation-free prune against the cv2 fixture of the KITTI-shape frame (pruned map and mask by value)."""
+    import torch
+    from conftest import load_golden
+    lib = cvr.load_library()
+    g = load_golden("kitti_d128_bs27")
+    H, W = g["disp"].shape
+    torch.cuda.set_device(0)
+    d_in = torch.from_numpy(g["disp"]).cuda()
+    d_pruned = torch.empty((H, W), dtype=torch.int16, device="cuda")
+    d_mask = torch.empty((H, W), dtype=torch.uint8, device="cuda")
+    for _ in range(2):
+        d_pruned.fill_(-1); d_mask.fill_(7)
+        rc = lib.cvr_prune_noalloc(d_in.data_ptr(), W, H, C.c_double(1.3), d_pruned.data_ptr(), None, d_mask.data_ptr(), None)
+        assert rc == 0, lib.cvr_last_error(None)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_pruned.cpu().numpy(), g["pruned"]) and np.array_equal(d_mask.cpu().numpy(), g["mask"])
 
 
 def test_prune_noalloc_refuses_frames_beyond_its_scratch(cvr):
