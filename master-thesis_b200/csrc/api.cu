@@ -161,7 +161,7 @@ extern "C" int cvr_last_timings(const cvr_ctx* ctx, const char** names, float* m
 static void free_all(cvr_ctx* c)
 {
     void* ptrs[] = { c->d_in[0], c->d_in[1], c->d_gray, c->d_volA, c->d_volC, c->d_lr, c->d_minlr, c->d_raw, c->d_aux, c->d_disp, c->d_med,
-                     c->d_label, c->d_size, c->d_pruned, c->d_dispf, c->d_mask, c->d_pstats, c->d_rowcnt, c->d_cloud, c->d_ncloud, c->d_vhdr,
+                     c->d_label, c->d_size, c->d_pruned, c->d_dispf, c->d_mask, c->d_pstats, c->d_sel, c->d_boxv, c->d_boxs, c->d_cloud, c->d_ncloud, c->d_vhdr,
                      c->d_keys[0], c->d_keys[1], c->d_vals[0], c->d_vals[1], c->d_hist, c->d_segstart, c->d_vox, c->d_cellstart, c->d_scanaux, c->d_cellidx,
                      c->d_meand, c->d_sstats, c->d_sorout, c->d_nout, c->d_nvox, c->d_spts, c->d_flags, c->d_sgflags, c->d_bmpre,
                      c->d_rmap1[0], c->d_rmap1[1], c->d_rmap2[0], c->d_rmap2[1], c->d_rect[0], c->d_rect[1] };
@@ -213,7 +213,6 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     if (!p->filter_only && (size_t)c->maxN < HW) c->maxN = (int)HW;
     const size_t N = (size_t)c->maxN;
     c->sor_grid_cap = c->maxN < 4096 ? 4096 : c->maxN;
-    const size_t nblk = (N + 1023) / 1024 + 2;
     const size_t nRuns = (N + 511) / 512;
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
 #define A(call) if (e == cudaSuccess) e = (call)
@@ -231,7 +230,8 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
         A(dalloc(&c->d_pruned, B * HW)); A(dalloc(&c->d_dispf, B * HW)); A(dalloc(&c->d_mask, B * HW));
         A(dalloc(&c->d_pstats, B));
     }
-    A(dalloc(&c->d_rowcnt, B * nblk));
+    A(dalloc(&c->d_sel, 3 * B * cvr_sel_stride(c->maxN)));
+    A(dalloc(&c->d_boxv, B)); A(dalloc(&c->d_boxs, B));
     A(dalloc(&c->d_cloud, B * N)); A(dalloc(&c->d_ncloud, B));
     A(dalloc(&c->d_vhdr, B));
     A(dalloc(&c->d_keys[0], B * N)); A(dalloc(&c->d_keys[1], B * N)); A(dalloc(&c->d_vals[0], B * N)); A(dalloc(&c->d_vals[1], B * N));
@@ -447,7 +447,7 @@ extern "C" int cvr_reproject_cloud(cvr_ctx* c, const int16_t* disp, size_t sd, c
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_pruned, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
-    int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, c->d_in[0], (size_t)W * 3, 0, 3);
+    int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, c->d_in[0], (size_t)W * 3, 0, 3, false);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
     timers_end(c, 0);
@@ -467,7 +467,7 @@ extern "C" int cvr_triangulate(cvr_ctx* c, const float* dispf, size_t sd, const 
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_dispf, (size_t)W * 4, dispf, sd, (size_t)W * 4, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
     if (mask) CVR_CUDA(c, cudaMemcpy2DAsync(c->d_mask, (size_t)W, mask, sm, (size_t)W, H, cudaMemcpyHostToDevice, c->stream));
-    int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, mask ? c->d_mask : nullptr, c->d_in[0], (size_t)W * 3, 0, 3);
+    int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, mask ? c->d_mask : nullptr, c->d_in[0], (size_t)W * 3, 0, 3, false);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
     timers_end(c, 0);
@@ -487,7 +487,7 @@ extern "C" int cvr_voxel_grid(cvr_ctx* c, const cvr_point* in, int n, cvr_point*
     CVR_CUDA(c, cudaMemcpyAsync(c->d_cloud, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_ncloud, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
-    int rc = cvr_launch_voxel(c, 1, c->d_cloud, (size_t)c->maxN, c->d_ncloud);
+    int rc = cvr_launch_voxel(c, 1, c->d_cloud, (size_t)c->maxN, c->d_ncloud, false);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_vox, c->d_nvox, out, capacity, m_out);
     if (rc) return rc;
@@ -512,7 +512,7 @@ extern "C" int cvr_sor(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, i
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_nvox, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
-    int rc = cvr_launch_sor(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, 0);
+    int rc = cvr_launch_sor(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, false);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_sorout, c->d_nout, out, capacity, kept_out);
     timers_end(c, 0);
@@ -642,21 +642,28 @@ static int enqueue_filters(cvr_ctx* c, int B, int stages, const int16_t* disp, c
     const bool wantCloud = (stages & 2) != 0, wantVox = (stages & 4) != 0, wantSor = (stages & 8) != 0;
     *fin = nullptr; *fcnt = nullptr;
     if (!(wantCloud || wantVox || wantSor)) return CVR_OK;
-    int rc = cvr_launch_prune(c, B, disp);
+    // per-frame records of the chain (prune statistics, the bounding boxes the cloud and voxel kernels accumulate)
+    int rc = cvr_launch_chain_init(c, B, true, true, true);
     if (rc) return rc;
-    if (c->prm.cloud_mode == CVR_CLOUD_REPROJECT)
-        rc = cvr_launch_cloud(c, B, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, dl, lstep, lfs, ch);
-    else
-        rc = cvr_launch_cloud(c, B, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, c->d_mask, dl, lstep, lfs, ch);
+    if (c->prm.cloud_mode == CVR_CLOUD_REPROJECT) {
+        rc = cvr_launch_prune(c, B, disp);                             // GeneratePointCloud reads the pruned CV_16S map (and its minimum)
+        if (rc) return rc;
+        rc = cvr_launch_cloud(c, B, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, dl, lstep, lfs, ch, true);
+    } else {
+        rc = cvr_launch_prune_stats(c, B, disp);                       // the cloud kernel prunes on the fly from these
+        if (rc) return rc;
+        rc = cvr_launch_cloud(c, B, CVR_CLOUD_TRIANGULATE, disp, nullptr, nullptr, dl, lstep, lfs, ch, true);
+    }
     if (rc) return rc;
     *fin = c->d_cloud; *fcnt = c->d_ncloud;
+    bool haveBox = true;                                               // d_boxv by the cloud kernel, d_boxs by the centroid kernel
     if (wantVox) {
-        rc = cvr_launch_voxel(c, B, *fin, (size_t)c->maxN, *fcnt);
+        rc = cvr_launch_voxel(c, B, *fin, (size_t)c->maxN, *fcnt, true);
         if (rc) return rc;
         *fin = c->d_vox; *fcnt = c->d_nvox;
-    }
+    } else haveBox = false;
     if (wantSor) {
-        rc = cvr_launch_sor(c, B, *fin, (size_t)c->maxN, *fcnt, 0);
+        rc = cvr_launch_sor(c, B, *fin, (size_t)c->maxN, *fcnt, haveBox);
         if (rc) return rc;
         *fin = c->d_sorout; *fcnt = c->d_nout;
     }

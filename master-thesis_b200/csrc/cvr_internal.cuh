@@ -56,6 +56,9 @@ struct VoxelHdr {
     int maxkey;
 };
 
+// per-frame bounding box of a point array: floats through an order-preserving uint mapping (f2ord, cvr_scan.cuh)
+struct VoxBox { unsigned mn[3], mx[3]; };
+
 struct PruneStats {
     int mn, mx;
     unsigned long long sum, sq;
@@ -128,7 +131,9 @@ struct cvr_ctx {
     float* d_dispf;          // [B][H][W]
     uint8_t* d_mask;         // [B][H][W]
     PruneStats* d_pstats;    // [B]
-    int* d_rowcnt;           // [B][H+1]
+    int* d_sel;              // status words + ticket of the ordered selections (cvr_scan.cuh): [3 uses][B][cvr_sel_stride(maxN)]
+    VoxBox* d_boxv;         // per-frame bounding box of the cloud entering the voxel grid [B]
+    VoxBox* d_boxs;         // ... of the cloud entering the outlier filters [B]
     cvr_point* d_cloud;      // dense cloud [B][H*W]
     int* d_ncloud;           // [B]
     // voxel
@@ -199,8 +204,24 @@ struct cvr_ctx {
 // ints in a packed payload's meta record (k_pack_clouds, api.cu)
 #define CVR_META_INTS(maxB) (2 * (size_t)(maxB) + 4)
 
+struct cvr_ctx;
 static inline int cvr_div_up(int a, int b) { return (a + b - 1) / b; }
 static inline size_t cvr_div_up_sz(size_t a, size_t b) { return (a + b - 1) / b; }
+
+// ints per frame of an ordered selection's status record (cvr_scan.cuh): one word per 1024-element chunk, spare, ticket
+static inline size_t cvr_sel_stride(int maxItems) { return ((size_t)maxItems + 1023) / 1024 + 2; }
+
+// Blocks per frame (grid.x of a (x, B) grid) for a kernel that strides over a per-frame item count known only on the
+// device: enough to cover `maxItems`, but no more than this frame's share of `blocksPerSM` resident blocks per SM --
+// a batch of small clouds must not launch W*H-sized grids of idle blocks.
+static inline int cvr_frame_blocks(const cvr_ctx* c, int B, size_t maxItems, int itemsPerBlock, int blocksPerSM)
+{
+    size_t need = (maxItems + (size_t)itemsPerBlock - 1) / (size_t)itemsPerBlock;
+    size_t share = ((size_t)c->sm_count * (size_t)blocksPerSM + (size_t)B - 1) / (size_t)B;
+    if (need < 1) need = 1;
+    if (share < 1) share = 1;
+    return (int)(need < share ? need : share);
+}
 
 // ---- stage launchers (each returns cudaError_t of the launch; all on ctx->stream) ----
 // k_sgbm.cu
@@ -216,13 +237,14 @@ int cvr_launch_bm(cvr_ctx* c, int B);       // k_bm.cu: gray -> d_med with Stere
 int cvr_launch_speckle(cvr_ctx* c, int B, int newVal, int maxSize, int maxDiff);   // in place on d_med
 // k_cloud.cu
 int cvr_launch_prune(cvr_ctx* c, int B, const int16_t* disp_in /*[B][H][W] tight*/);
+int cvr_launch_chain_init(cvr_ctx* c, int B, bool stats, bool boxA, bool boxB);   // d_pstats / d_boxv / d_boxs to their neutral values
+int cvr_launch_prune_stats(cvr_ctx* c, int B, const int16_t* disp_in);           // batch path: statistics only (the cloud kernel prunes on the fly)
 int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const float* dispf, const uint8_t* mask,
-                     const uint8_t* bgr, size_t bstep, size_t bfs, int channels);
-// k_voxel.cu
-int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in);
-// k_sor.cu
-int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in /*device*/, int n_is_vox);
-
+                     const uint8_t* bgr, size_t bstep, size_t bfs, int channels, bool fused);
+// k_voxel.cu / k_sor.cu.  haveBox: the producer of `in` already accumulated its bounding box (d_boxv for the voxel grid,
+// d_boxs for the outlier filters); otherwise the launcher measures it first.
+int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox);
+int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in /*device*/, bool haveBox);
 int cvr_launch_ror(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, float radius, int min_pts);
 int cvr_launch_transform(cvr_ctx* c, const cvr_point* in, cvr_point* out, int n, const float* T);
 void cvr_stage_mark(cvr_ctx* c, const char* name);

@@ -81,7 +81,6 @@ static __global__ void __launch_bounds__(1024) k_scan_addoff(int* data, size_t f
 // ---- per-frame bounding box of a point array (float min/max through an order-preserving uint mapping) ----
 __device__ __forceinline__ unsigned f2ord(float f) { unsigned u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
 __device__ __forceinline__ float ord2f(unsigned u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
-struct VoxBox { unsigned mn[3], mx[3]; };
 
 static __global__ void k_bbox_init(VoxBox* box, int B)
 {
@@ -104,4 +103,47 @@ static __global__ void k_bbox_minmax(const void* __restrict__ pts, size_t stride
     for (int k = 0; k < 3; k++) { mn[k] = __reduce_min_sync(0xffffffffu, mn[k]); mx[k] = __reduce_max_sync(0xffffffffu, mx[k]); }
     if ((threadIdx.x & 31) == 0 && n > 0)
         for (int k = 0; k < 3; k++) { atomicMin(&box[b].mn[k], mn[k]); atomicMax(&box[b].mx[k], mx[k]); }
+}
+
+// ---- single-pass ordered selection ("chained scan") ----------------------------------------------------------------
+// An ordered compaction in ONE pass over its input instead of count -> scan -> write: the blocks of a frame draw chunk
+// numbers from a ticket counter (so a chunk's predecessors have always been started by a running block: no deadlock
+// whatever the number of resident blocks), each publishes its chunk's total and looks back along the status words of the
+// earlier chunks until it meets one that already carries an inclusive prefix.
+// Per frame: sel[0 .. nchMax] status words, sel[nchMax + 1] the ticket counter; all zero before the launch
+// (cvr_sel_stride ints per frame).  Status word: bit 31 = inclusive prefix, bit 30 = chunk aggregate, low 30 bits = value.
+#define CVR_SEL_INCL 0x80000000u
+#define CVR_SEL_AGG 0x40000000u
+static_assert(CVR_SEL_BLOCK == 1024, "cvr_sel_stride (cvr_internal.cuh) assumes 1024-element chunks");
+
+__device__ __forceinline__ int sel_next_chunk(int* ticket, int* sh)
+{
+    if (threadIdx.x == 0) *sh = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int c = *sh;
+    __syncthreads();
+    return c;
+}
+// exclusive prefix of chunk `chunk` over the frame, given the chunk's own total (all threads call; sh = one shared int)
+__device__ __forceinline__ int sel_chain_prefix(unsigned* status, int chunk, int total, int* sh)
+{
+    if (threadIdx.x == 0) {
+        int run = 0;
+        volatile unsigned* st = status;
+        if (chunk > 0) {
+            st[chunk] = CVR_SEL_AGG | (unsigned)total;
+            for (int j = chunk - 1;; j--) {
+                unsigned v;
+                do { v = st[j]; } while (v == 0u);
+                run += (int)(v & 0x3fffffffu);
+                if (v & CVR_SEL_INCL) break;
+            }
+        }
+        st[chunk] = CVR_SEL_INCL | (unsigned)(run + total);
+        *sh = run;
+    }
+    __syncthreads();
+    const int r = *sh;
+    __syncthreads();
+    return r;
 }

@@ -103,26 +103,141 @@ int cvr_launch_prune(cvr_ctx* c, int B, const int16_t* disp_in)
 }
 
 // ------------------------------------------------------------------------------------------------
+// The batch path does not materialise the pruned disparity, the float disparity or the mask: two reduction passes over
+// the final disparity give the frame's PruneStats (min/max, then sum and sum of squares of the normalised 8-bit image),
+// and the cloud kernel evaluates normalize / threshold / convertTo per pixel on the fly (k_cloud_select<.., FUSED>).
+// 16-byte loads over the aligned body of the frame, scalar head and tail.
+template <typename F1, typename F8>
+__device__ __forceinline__ void s16_stream(const int16_t* p, int n, int tid, int nthreads, F1 f1, F8 f8)
+{
+    int head = (int)(((16 - ((size_t)p & 15)) & 15) >> 1);
+    if (head > n) head = n;
+    const int nv = (n - head) >> 3;
+    for (int i = tid; i < head; i += nthreads) f1((int)p[i]);
+    const uint4* v = (const uint4*)(p + head);
+    for (int i = tid; i < nv; i += nthreads) f8(v[i]);
+    for (int i = head + nv * 8 + tid; i < n; i += nthreads) f1((int)p[i]);
+}
+__global__ void __launch_bounds__(256) k_prune_minmax8(const int16_t* __restrict__ disp, int N, PruneStats* st)
+{
+    const int b = blockIdx.y;
+    unsigned mn2 = 0x7fff7fffu, mx2 = 0x80008000u;
+    int mn = 32767, mx = -32768;
+    s16_stream(disp + (size_t)b * N, N, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x,
+               [&](int v) { mn = min(mn, v); mx = max(mx, v); },
+               [&](const uint4& q) {
+                   mn2 = __vmins2(__vmins2(mn2, q.x), __vmins2(q.y, __vmins2(q.z, q.w)));
+                   mx2 = __vmaxs2(__vmaxs2(mx2, q.x), __vmaxs2(q.y, __vmaxs2(q.z, q.w)));
+               });
+    mn = min(mn, min((int)(short)(mn2 & 0xffffu), (int)mn2 >> 16));
+    mx = max(mx, max((int)(short)(mx2 & 0xffffu), (int)mx2 >> 16));
+    mn = __reduce_min_sync(0xffffffffu, mn); mx = __reduce_max_sync(0xffffffffu, mx);
+    if ((threadIdx.x & 31) == 0) { atomicMin(&st[b].mn, mn); atomicMax(&st[b].mx, mx); }
+}
+// scale / shift of cv::normalize(NORM_MINMAX, 0, 255) as the two f32 constants of its single-rounding FMA
+__device__ __forceinline__ void prune_scale(const PruneStats& s, float& fa, float& fb)
+{
+    const double dmn = (double)s.mn, dmx = (double)s.mx;
+    const double rng = __dsub_rn(dmx, dmn);
+    const double scale = __dmul_rn(255.0, (rng > DBL_EPSILON ? __ddiv_rn(1.0, rng) : 0.0));
+    fa = (float)scale; fb = (float)__dsub_rn(0.0, __dmul_rn(dmn, scale));
+}
+__device__ __forceinline__ int prune_u8(int d, float fa, float fb) { return min(max(__float2int_rn(__fmaf_rn((float)d, fa, fb)), 0), 255); }
+__device__ __forceinline__ int prune_threshold(const PruneStats& s, int N, double factor)
+{
+    const double inv = __ddiv_rn(1.0, (double)N);
+    const double mean = __dmul_rn((double)s.sum, inv);
+    const double var = __dsub_rn(__dmul_rn((double)s.sq, inv), __dmul_rn(mean, mean));
+    return (int)floor(__dmul_rn(sqrt(var > 0.0 ? var : 0.0), factor));
+}
+__global__ void __launch_bounds__(256) k_prune_stats8(const int16_t* __restrict__ disp, int N, PruneStats* st)
+{
+    const int b = blockIdx.y;
+    float fa, fb;
+    prune_scale(st[b], fa, fb);
+    unsigned sum = 0; unsigned long long sq = 0;                       // a thread sees < 2^24 pixels: the 8-bit sum fits 32 bits
+    auto one = [&](int v) { const unsigned r = (unsigned)prune_u8(v, fa, fb); sum += r; sq += r * r; };
+    s16_stream(disp + (size_t)b * N, N, blockIdx.x * blockDim.x + threadIdx.x, gridDim.x * blockDim.x, one,
+               [&](const uint4& q) {
+                   const unsigned w[4] = { q.x, q.y, q.z, q.w };
+#pragma unroll
+                   for (int j = 0; j < 4; j++) { one((int)(short)(w[j] & 0xffffu)); one((int)w[j] >> 16); }
+               });
+    unsigned long long s64 = sum;
+    __shared__ unsigned long long ssum[8], ssq[8];
+#pragma unroll
+    for (int k = 16; k > 0; k >>= 1) { s64 += __shfl_down_sync(0xffffffffu, s64, k); sq += __shfl_down_sync(0xffffffffu, sq, k); }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0) { ssum[w] = s64; ssq[w] = sq; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int k = 1; k < 8; k++) { s64 += ssum[k]; sq += ssq[k]; }
+        atomicAdd(&st[b].sum, s64); atomicAdd(&st[b].sq, sq);
+    }
+}
+// per-frame records a batch of the filter chain starts from: prune statistics and the two bounding boxes (cloud -> voxel
+// grid, voxel centroids -> outlier search grid) that the producing kernels accumulate
+__global__ void k_chain_init(PruneStats* st, VoxBox* boxA, VoxBox* boxB, int B)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    if (st) { st[b].mn = 32767; st[b].mx = -32768; st[b].sum = 0; st[b].sq = 0; st[b].a = 0; st[b].b = 0; st[b].ithr = 0; }
+    for (int k = 0; k < 3; k++) {
+        if (boxA) { boxA[b].mn[k] = 0xffffffffu; boxA[b].mx[k] = 0u; }
+        if (boxB) { boxB[b].mn[k] = 0xffffffffu; boxB[b].mx[k] = 0u; }
+    }
+}
+int cvr_launch_chain_init(cvr_ctx* c, int B, bool stats, bool boxA, bool boxB)
+{
+    k_chain_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(stats ? c->d_pstats : nullptr, boxA ? c->d_boxv : nullptr, boxB ? c->d_boxs : nullptr, B);
+    LAUNCH_CHECK(c);
+    return CVR_OK;
+}
+// prune statistics only (batch path); d_pstats initialised by cvr_launch_chain_init
+int cvr_launch_prune_stats(cvr_ctx* c, int B, const int16_t* disp_in)
+{
+    const int N = c->sg.W * c->sg.H;
+    const int gx = cvr_frame_blocks(c, B, (size_t)N / 8 + 1, 256, 8);
+    k_prune_minmax8<<<dim3(gx, B), 256, 0, c->stream>>>(disp_in, N, c->d_pstats);
+    LAUNCH_CHECK(c);
+    k_prune_stats8<<<dim3(gx, B), 256, 0, c->stream>>>(disp_in, N, c->d_pstats);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "prune");
+    return CVR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // cloud generation
 struct CloudArgs {
-    const int16_t* disp16;   // reproject input  [B][H][W]
+    const int16_t* disp16;   // reproject input / fused input (final disparity) [B][H][W]
     const float* dispf;      // triangulate input [B][H][W]
     const uint8_t* mask;     // optional [B][H][W]
     const uint8_t* bgr; size_t bstep, bfs; int ch;
     int W, H;
     CloudDev cl;
     const int* minDisp;      // reproject: per-frame min disparity (handleMissingValues)
+    const PruneStats* pstats;   // FUSED: the frame's prune statistics
 };
 
-template <int MODE>
-__device__ __forceinline__ bool make_point(const CloudArgs& a, int b, int i, cvr_point& pt)
+// FUSED (triangulate only): disparity, mask and float conversion of TrackingFrame::SetupFrame evaluated here from the
+// final disparity: keep = u8 > ithr; v = keep ? d : 0; f = v / 16; mask = keep && f > 0; a point iff f > 0 && mask.
+template <int MODE, bool FUSED>
+__device__ __forceinline__ bool make_point(const CloudArgs& a, int b, int i, cvr_point& pt, float fa, float fb, int ithr)
 {
     const int W = a.W, y = i / W, x = i - y * W;
     const size_t o = (size_t)b * W * a.H + i;
     if (MODE == CVR_CLOUD_TRIANGULATE) {
-        const float d = a.dispf[o];
-        if (!(d > 0.0f)) return false;                        // `if (d <= 0.0) continue;` (NaN falls through in the reference; disparities are finite)
-        if (a.mask && a.mask[o] == 0) return false;
+        float d;
+        if (FUSED) {
+            const int d16 = a.disp16[o];
+            if (!(prune_u8(d16, fa, fb) > ithr)) return false;
+            d = __fmul_rn((float)d16, 0.0625f);
+            if (!(d > 0.0f)) return false;
+        } else {
+            d = a.dispf[o];
+            if (!(d > 0.0f)) return false;                    // `if (d <= 0.0) continue;` (NaN falls through in the reference; disparities are finite)
+            if (a.mask && a.mask[o] == 0) return false;
+        }
         const float z = __fdiv_rn(__fmul_rn(a.cl.f, a.cl.b), d);
         const float zf = __fdiv_rn(z, a.cl.f);
         pt.z = z;
@@ -163,55 +278,82 @@ __global__ void k_min_s16(const int16_t* __restrict__ disp, int N, int* out)
 }
 __global__ void k_fill_int(int* p, int n, int v) { int i = blockIdx.x * blockDim.x + threadIdx.x; if (i < n) p[i] = v; }
 
-template <int MODE>
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_cloud_count(CloudArgs a, int* blkcnt, size_t cntStride)
+// Surviving pixels in row-major order (the reference's push_back order) by the single-pass ordered selection of
+// cvr_scan.cuh; the kernel also accumulates the cloud's bounding box for the voxel grid that follows.
+template <int MODE, bool FUSED>
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_cloud_select(CloudArgs a, int* sel, size_t selStride, cvr_point* __restrict__ out, size_t outStride,
+                                                                int* __restrict__ nout, VoxBox* box, double factor)
 {
     __shared__ int ws[33];
-    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
-    cvr_point pt;
-    const int f = (i < a.W * a.H) ? (int)make_point<MODE>(a, b, i, pt) : 0;
-    int tot;
-    block_excl_scan(f, ws, &tot);
-    if (threadIdx.x == 0) blkcnt[(size_t)b * cntStride + blockIdx.x] = tot;
-}
-template <int MODE>
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_cloud_write(CloudArgs a, const int* __restrict__ blkoff, size_t cntStride, int nblk,
-                                                               cvr_point* __restrict__ out, size_t outStride, int* __restrict__ nout)
-{
-    __shared__ int ws[33];
-    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
-    cvr_point pt;
-    const int f = (i < a.W * a.H) ? (int)make_point<MODE>(a, b, i, pt) : 0;
-    const int e = block_excl_scan(f, ws, nullptr);
-    if (f) out[(size_t)b * outStride + blkoff[(size_t)b * cntStride + blockIdx.x] + e] = pt;
-    if (blockIdx.x == 0 && threadIdx.x == 0) nout[b] = blkoff[(size_t)b * cntStride + nblk];
+    __shared__ int sh;
+    __shared__ float sfa, sfb;
+    __shared__ int sthr;
+    const int b = blockIdx.y, N = a.W * a.H, nch = (N + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;
+    if (FUSED && threadIdx.x == 0) {
+        const PruneStats s = a.pstats[b];
+        float fa, fb;
+        prune_scale(s, fa, fb);
+        sfa = fa; sfb = fb; sthr = prune_threshold(s, N, factor);
+    }
+    __syncthreads();
+    const float fa = FUSED ? sfa : 0.f, fb = FUSED ? sfb : 0.f;
+    const int ithr = FUSED ? sthr : 0;
+    unsigned* status = (unsigned*)sel + (size_t)b * selStride;
+    int* ticket = (int*)status + (selStride - 1);
+    unsigned mn[3] = { 0xffffffffu, 0xffffffffu, 0xffffffffu }, mx[3] = { 0, 0, 0 };
+    bool any = false;
+    for (;;) {
+        const int chunk = sel_next_chunk(ticket, &sh);
+        if (chunk >= nch) break;
+        const int i = chunk * CVR_SEL_BLOCK + threadIdx.x;
+        cvr_point pt;
+        const int f = (i < N) ? (int)make_point<MODE, FUSED>(a, b, i, pt, fa, fb, ithr) : 0;
+        int tot;
+        const int e = block_excl_scan(f, ws, &tot);
+        const int base = sel_chain_prefix(status, chunk, tot, &sh);
+        if (f) {
+            *(uint4*)(out + (size_t)b * outStride + base + e) = *(const uint4*)&pt;
+            const unsigned ox = f2ord(pt.x), oy = f2ord(pt.y), oz = f2ord(pt.z);
+            mn[0] = min(mn[0], ox); mx[0] = max(mx[0], ox); mn[1] = min(mn[1], oy); mx[1] = max(mx[1], oy); mn[2] = min(mn[2], oz); mx[2] = max(mx[2], oz);
+            any = true;
+        }
+        if (chunk == nch - 1 && threadIdx.x == 0) nout[b] = base + tot;
+    }
+    if (box && __any_sync(0xffffffffu, any)) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) { mn[k] = __reduce_min_sync(0xffffffffu, mn[k]); mx[k] = __reduce_max_sync(0xffffffffu, mx[k]); }
+        if ((threadIdx.x & 31) == 0)
+            for (int k = 0; k < 3; k++) { atomicMin(&box[b].mn[k], mn[k]); atomicMax(&box[b].mx[k], mx[k]); }
+    }
 }
 
+// fused = true: triangulate straight from the final disparity `disp16` and the frame's PruneStats (batch path);
+// d_boxv must have been initialised (cvr_launch_chain_init): the cloud's bounding box lands there.
 int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const float* dispf, const uint8_t* mask,
-                     const uint8_t* bgr, size_t bstep, size_t bfs, int channels)
+                     const uint8_t* bgr, size_t bstep, size_t bfs, int channels, bool fused)
 {
     const int W = c->sg.W, H = c->sg.H, N = W * H;
-    const int nblk = cvr_div_up(N, CVR_SEL_BLOCK);
-    const size_t cntStride = (size_t)nblk + 1;
+    const size_t selStride = cvr_sel_stride(c->maxN);
     CloudArgs a;
     a.disp16 = disp16; a.dispf = dispf; a.mask = mask; a.bgr = bgr; a.bstep = bstep; a.bfs = bfs; a.ch = channels;
-    a.W = W; a.H = H; a.cl = c->cl; a.minDisp = c->d_flags;
+    a.W = W; a.H = H; a.cl = c->cl; a.minDisp = c->d_flags; a.pstats = c->d_pstats;
+    int* sel = c->d_sel;                                               // selection 0 of the chain
+    if (!fused) { const int rc0 = cvr_launch_chain_init(c, B, false, true, false); if (rc0) return rc0; }   // stand-alone call: nobody prepared the box
+    CVR_CUDA(c, cudaMemsetAsync(sel, 0, (size_t)B * selStride * sizeof(int), c->stream));
+    const int nch = cvr_div_up(N, CVR_SEL_BLOCK);
+    const dim3 g(cvr_frame_blocks(c, B, (size_t)nch, 1, 2), B);
+    const double factor = c->cl.sigma_factor;
     if (mode == CVR_CLOUD_REPROJECT) {
         k_fill_int<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_flags, B, 32767);
         LAUNCH_CHECK(c);
         k_min_s16<<<dim3(min(cvr_div_up(N, 256), 296), B), 256, 0, c->stream>>>(disp16, N, c->d_flags);
         LAUNCH_CHECK(c);
-        k_cloud_count<CVR_CLOUD_REPROJECT><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride);
+        k_cloud_select<CVR_CLOUD_REPROJECT, false><<<g, CVR_SEL_BLOCK, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
+    } else if (fused) {
+        k_cloud_select<CVR_CLOUD_TRIANGULATE, true><<<g, CVR_SEL_BLOCK, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
     } else {
-        k_cloud_count<CVR_CLOUD_TRIANGULATE><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride);
+        k_cloud_select<CVR_CLOUD_TRIANGULATE, false><<<g, CVR_SEL_BLOCK, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
     }
-    LAUNCH_CHECK(c);
-    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
-    LAUNCH_CHECK(c);
-    if (mode == CVR_CLOUD_REPROJECT)
-        k_cloud_write<CVR_CLOUD_REPROJECT><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride, nblk, c->d_cloud, (size_t)c->maxN, c->d_ncloud);
-    else
-        k_cloud_write<CVR_CLOUD_TRIANGULATE><<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(a, c->d_rowcnt, cntStride, nblk, c->d_cloud, (size_t)c->maxN, c->d_ncloud);
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "cloud");
     return CVR_OK;

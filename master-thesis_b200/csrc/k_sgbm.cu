@@ -927,9 +927,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         return CVR_OK;
     }
     CVR_CUDA(c, cudaMemsetAsync(c->d_sgflags, 0, sizeof(int) * B, c->stream));
-    // raw disparity: columns outside [minX1, maxX1) are never written by WTA
-    k_fill_s16<<<(unsigned)cvr_div_up_sz(npix, 256), 256, 0, c->stream>>>(c->d_raw, npix, p.INVALID);
-    LAUNCH_CHECK(c);
+    // (d_raw needs no clearing: k_lrcheck writes every pixel of it)
     {
         static const int segLen = getenv("CVR_HSUM_SEG") ? atoi(getenv("CVR_HSUM_SEG")) : 320;   // tuning hook
         int nseg = (p.W1 + segLen / 2) / segLen;

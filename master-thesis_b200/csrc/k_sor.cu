@@ -18,23 +18,22 @@ struct SorGrid {
     int n;
 };
 
-__global__ void k_sor_grid(const VoxBox* box, const int* nPtr, SorGrid* grid, int* ncellOut, int cap, int B)
+// the search grid of one frame from its bounding box: about two points per cell on a volume-filling cloud
+__device__ __forceinline__ SorGrid sor_make_grid(const VoxBox& box, int n, int cap)
 {
-    int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
     SorGrid g;
-    g.n = nPtr[b];
+    g.n = n;
     float ext[3], emax = 0.f;
     for (int k = 0; k < 3; k++) {
-        g.mn[k] = g.n > 0 ? ord2f(box[b].mn[k]) : 0.f;
-        const float mx = g.n > 0 ? ord2f(box[b].mx[k]) : 0.f;
+        g.mn[k] = g.n > 0 ? ord2f(box.mn[k]) : 0.f;
+        const float mx = g.n > 0 ? ord2f(box.mx[k]) : 0.f;
         ext[k] = mx - g.mn[k];
         emax = fmaxf(emax, ext[k]);
     }
     if (!(emax > 0.f)) emax = 1.f;
     double vol = 1.0;
     for (int k = 0; k < 3; k++) { ext[k] = fmaxf(ext[k], emax * 1e-3f); vol *= (double)ext[k]; }
-    // about two points per cell on a volume-filling cloud; surface-like clouds end up sparser, which only costs time
+    // surface-like clouds end up sparser than two points per cell, which only costs time
     float s = (float)cbrt(2.0 * vol / (double)max(g.n, 1));
     s = fmaxf(s, emax * 1e-4f);
     for (int it = 0; it < 8; it++) {
@@ -45,8 +44,43 @@ __global__ void k_sor_grid(const VoxBox* box, const int* nPtr, SorGrid* grid, in
     }
     g.cell = s; g.inv = 1.0f / s;
     g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
-    grid[b] = g;
-    ncellOut[b] = g.ncell;
+    return g;
+}
+// pcl::RadiusOutlierRemoval's grid: cell edge = the radius (a multiple of it when the grid would get too large)
+__device__ __forceinline__ SorGrid ror_make_grid(const VoxBox& box, int n, float radius, int cap)
+{
+    SorGrid g;
+    g.n = n;
+    float ext[3];
+    for (int k = 0; k < 3; k++) {
+        g.mn[k] = g.n > 0 ? ord2f(box.mn[k]) : 0.f;
+        const float mx = g.n > 0 ? ord2f(box.mx[k]) : 0.f;
+        ext[k] = fmaxf(mx - g.mn[k], 0.f);
+    }
+    float s = radius;
+    for (int it = 0; it < 32; it++) {
+        long long tot = 1;
+        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
+        if (tot <= cap) break;
+        s *= 1.5f;
+    }
+    g.cell = s; g.inv = 1.0f / s;
+    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
+    return g;
+}
+// Builds the frame's grid (every block computes it, block 0 stores it) and clears the two cell tables it needs.
+__global__ void __launch_bounds__(256) k_sor_grid_zero(const VoxBox* __restrict__ box, const int* __restrict__ nPtr, SorGrid* grid, int* ncellOut, int cap, float radius,
+                                                       int* cellA, int* cellB, size_t cellStride)
+{
+    __shared__ SorGrid sg;
+    const int b = blockIdx.y;
+    if (threadIdx.x == 0) {
+        sg = radius > 0.f ? ror_make_grid(box[b], nPtr[b], radius, cap) : sor_make_grid(box[b], nPtr[b], cap);
+        if (blockIdx.x == 0) { grid[b] = sg; ncellOut[b] = sg.ncell; }
+    }
+    __syncthreads();
+    const int len = sg.ncell + 1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) { cellA[(size_t)b * cellStride + i] = 0; cellB[(size_t)b * cellStride + i] = 0; }
 }
 __device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, float z, int& cx, int& cy, int& cz)
 {
@@ -54,34 +88,31 @@ __device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, flo
     cy = min(max((int)((y - g.mn[1]) * g.inv), 0), g.dim[1] - 1);
     cz = min(max((int)((z - g.mn[2]) * g.inv), 0), g.dim[2] - 1);
 }
-__global__ void k_sor_zero(int* a, size_t stride, const int* lenPtr, int extra)
-{
-    const int b = blockIdx.y, len = lenPtr[b] + extra;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) a[(size_t)b * stride + i] = 0;
-}
 __global__ void k_sor_cellcount(const cvr_point* __restrict__ pts, size_t stride, const SorGrid* __restrict__ grid, int* cellcnt, size_t cellStride,
                                 int* __restrict__ cellOfPt, size_t ptStride)
 {
-    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
     const SorGrid g = grid[b];
-    if (i >= g.n) return;
-    const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
-    int cx, cy, cz;
-    sor_cell(g, q.x, q.y, q.z, cx, cy, cz);
-    const int cid = (cz * g.dim[1] + cy) * g.dim[0] + cx;
-    cellOfPt[(size_t)b * ptStride + i] = cid;
-    atomicAdd(&cellcnt[(size_t)b * cellStride + cid], 1);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += gridDim.x * blockDim.x) {
+        const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
+        int cx, cy, cz;
+        sor_cell(g, q.x, q.y, q.z, cx, cy, cz);
+        const int cid = (cz * g.dim[1] + cy) * g.dim[0] + cx;
+        cellOfPt[(size_t)b * ptStride + i] = cid;
+        atomicAdd(&cellcnt[(size_t)b * cellStride + cid], 1);
+    }
 }
 __global__ void k_sor_scatter(const cvr_point* __restrict__ pts, size_t stride, const SorGrid* __restrict__ grid, const int* __restrict__ cellstart,
                               int* cellfill, size_t cellStride, const int* __restrict__ cellOfPt, size_t ptStride, float4* __restrict__ spts)
 {
-    const int b = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= grid[b].n) return;
-    const int cid = cellOfPt[(size_t)b * ptStride + i];
-    const int pos = cellstart[(size_t)b * cellStride + cid] + atomicAdd(&cellfill[(size_t)b * cellStride + cid], 1);
-    float4 q = *(const float4*)(pts + (size_t)b * stride + i);
-    q.w = __int_as_float(i);
-    spts[(size_t)b * ptStride + pos] = q;
+    const int b = blockIdx.y, n = grid[b].n;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int cid = cellOfPt[(size_t)b * ptStride + i];
+        const int pos = cellstart[(size_t)b * cellStride + cid] + atomicAdd(&cellfill[(size_t)b * cellStride + cid], 1);
+        float4 q = *(const float4*)(pts + (size_t)b * stride + i);
+        q.w = __int_as_float(i);
+        spts[(size_t)b * ptStride + pos] = q;
+    }
 }
 
 // One thread per query point (in cell-sorted order).  best[] holds the k+1 smallest squared distances seen,
@@ -90,16 +121,16 @@ template <int KCAP>
 __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
                                                  const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
 {
-    const int b = blockIdx.y, t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
     const SorGrid g = grid[b];
-    if (t >= g.n) return;
     const float4* sp = spts + (size_t)b * ptStride;
     const int* cs = cellstart + (size_t)b * cellStride;
-    const float4 q = sp[t];
-    const int orig = __float_as_int(q.w);
     float* out = meand + (size_t)b * ptStride;
     const int K1 = k + 1;
-    if (g.n < K1) { out[orig] = 0.f; return; }
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < g.n; t += gridDim.x * blockDim.x) {
+    const float4 q = sp[t];
+    const int orig = __float_as_int(q.w);
+    if (g.n < K1) { out[orig] = 0.f; continue; }
     float best[KCAP];
     int cnt = 0;
     int cx, cy, cz;
@@ -178,6 +209,7 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
     double s = 0.0;
     for (int j = 1; j < K1; j++) s = __dadd_rn(s, (double)__fsqrt_rn(best[j]));
     out[orig] = (float)__ddiv_rn(s, (double)k);
+    }
 }
 
 // mean / sample variance over all mean distances, f64, fixed reduction order (deterministic).
@@ -203,26 +235,29 @@ __global__ void __launch_bounds__(1024) k_sor_stats(const float* __restrict__ me
         st[b].sum = sum; st[b].sq = sqs; st[b].thr = thr; st[b].valid = valid;
     }
 }
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_count(const float* __restrict__ meand, size_t ptStride, const int* __restrict__ nPtr,
-                                                             const SorStats* __restrict__ st, int* blkcnt, size_t cntStride)
+// kept points (mean distance not above the threshold) in input order, by the single-pass ordered selection
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_select(const cvr_point* __restrict__ pts, size_t stride, const float* __restrict__ meand, size_t ptStride,
+                                                              const int* __restrict__ nPtr, SorStats* st, int* sel, size_t selStride,
+                                                              cvr_point* __restrict__ out, size_t outStride, int* __restrict__ nOut)
 {
     __shared__ int ws[33];
-    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
-    const int f = (i < nPtr[b]) && !((double)meand[(size_t)b * ptStride + i] > st[b].thr);
-    int tot;
-    block_excl_scan(f, ws, &tot);
-    if (threadIdx.x == 0) blkcnt[(size_t)b * cntStride + blockIdx.x] = tot;
-}
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_write(const cvr_point* __restrict__ pts, size_t stride, const float* __restrict__ meand, size_t ptStride,
-                                                             const int* __restrict__ nPtr, SorStats* st, const int* __restrict__ blkoff, size_t cntStride,
-                                                             int nblk, cvr_point* __restrict__ out, size_t outStride, int* __restrict__ nOut)
-{
-    __shared__ int ws[33];
-    const int b = blockIdx.y, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
-    const int f = (i < nPtr[b]) && !((double)meand[(size_t)b * ptStride + i] > st[b].thr);
-    const int e = block_excl_scan(f, ws, nullptr);
-    if (f) out[(size_t)b * outStride + blkoff[(size_t)b * cntStride + blockIdx.x] + e] = pts[(size_t)b * stride + i];
-    if (blockIdx.x == 0 && threadIdx.x == 0) { const int m = blkoff[(size_t)b * cntStride + nblk]; nOut[b] = m; st[b].kept = m; }
+    __shared__ int sh;
+    const int b = blockIdx.y, n = nPtr[b], nch = (n + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;
+    const double thr = st[b].thr;
+    unsigned* status = (unsigned*)sel + (size_t)b * selStride;
+    int* ticket = (int*)status + (selStride - 1);
+    if (nch == 0) { if (blockIdx.x == 0 && threadIdx.x == 0) { nOut[b] = 0; st[b].kept = 0; } return; }
+    for (;;) {
+        const int chunk = sel_next_chunk(ticket, &sh);
+        if (chunk >= nch) break;
+        const int i = chunk * CVR_SEL_BLOCK + threadIdx.x;
+        const int f = (i < n) && !((double)meand[(size_t)b * ptStride + i] > thr);
+        int tot;
+        const int e = block_excl_scan(f, ws, &tot);
+        const int base = sel_chain_prefix(status, chunk, tot, &sh);
+        if (f) *(uint4*)(out + (size_t)b * outStride + base + e) = *(const uint4*)(pts + (size_t)b * stride + i);
+        if (chunk == nch - 1 && threadIdx.x == 0) { nOut[b] = base + tot; st[b].kept = base + tot; }
+    }
 }
 
 // exclusive scan of the per-frame cell counts: one CTA per frame while the table is short, two levels when it is long
@@ -244,36 +279,59 @@ static int scan_cells(cvr_ctx* c, int B, int* cellstart, size_t cellStride, int 
     return CVR_OK;
 }
 
-int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, int /*unused*/)
+// shared front half of the two outlier filters: bounding box (unless the producer accumulated it), grid, points sorted by cell
+static int sor_build_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox, float radius, SorGrid** gridOut, int** cellstartOut)
 {
     const int maxN = c->maxN;
     const size_t ptStride = (size_t)maxN;
     const int cap = c->sor_grid_cap;
     const size_t cellStride = (size_t)cap + 2;
-    const int k = c->cl.sor_k;
-    if (k < 1 || k + 1 > 320) { c->err = "sor_mean_k must be in [1, 319]"; return CVR_ERR_UNSUPPORTED; }
-    VoxBox* box = (VoxBox*)c->d_flags;
     SorGrid* grid = (SorGrid*)(c->d_flags + (size_t)c->maxB * 16);
     int* ncell = c->d_flags + (size_t)c->maxB * 32;
     int* cellstart = c->d_cellstart;
     int* cellfill = c->d_cellstart + (size_t)c->maxB * cellStride;
-    k_bbox_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, B);
+    if (!haveBox) {
+        const int rc0 = cvr_launch_chain_init(c, B, false, false, true);
+        if (rc0) return rc0;
+        k_bbox_minmax<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B), 256, 0, c->stream>>>(in, in_stride, n_in, c->d_boxs);
+        LAUNCH_CHECK(c);
+    }
+    const dim3 gp(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B);     // strides over the frame's points / cells
+    k_sor_grid_zero<<<dim3(cvr_frame_blocks(c, B, (size_t)cap + 1, 256, 8), B), 256, 0, c->stream>>>(c->d_boxs, n_in, grid, ncell, cap, radius, cellstart, cellfill, cellStride);
     LAUNCH_CHECK(c);
-    k_bbox_minmax<<<dim3(64, B), 256, 0, c->stream>>>(in, in_stride, n_in, box);
-    LAUNCH_CHECK(c);
-    k_sor_grid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, n_in, grid, ncell, cap, B);
-    LAUNCH_CHECK(c);
-    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellstart, cellStride, ncell, 1);
-    LAUNCH_CHECK(c);
-    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellfill, cellStride, ncell, 1);
-    LAUNCH_CHECK(c);
-    k_sor_cellcount<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
+    k_sor_cellcount<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
     LAUNCH_CHECK(c);
     { const int rcs = scan_cells(c, B, cellstart, cellStride, cap, ncell); if (rcs) return rcs; }
-    k_sor_scatter<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
+    k_sor_scatter<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
     LAUNCH_CHECK(c);
+    *gridOut = grid; *cellstartOut = cellstart;
+    return CVR_OK;
+}
+static int sor_select(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in)
+{
+    const int maxN = c->maxN;
+    const size_t selStride = cvr_sel_stride(maxN);
+    int* sel = c->d_sel + (size_t)2 * c->maxB * selStride;             // selection 2 of the chain
+    CVR_CUDA(c, cudaMemsetAsync(sel, 0, (size_t)B * selStride * sizeof(int), c->stream));
+    const int nch = cvr_div_up(maxN, CVR_SEL_BLOCK);
+    k_sor_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 2), B), CVR_SEL_BLOCK, 0, c->stream>>>(in, in_stride, c->d_meand, (size_t)maxN, n_in, c->d_sstats, sel, selStride,
+                                                                                                  c->d_sorout, (size_t)maxN, c->d_nout);
+    LAUNCH_CHECK(c);
+    return CVR_OK;
+}
+
+int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox)
+{
+    const int maxN = c->maxN;
+    const size_t ptStride = (size_t)maxN;
+    const size_t cellStride = (size_t)c->sor_grid_cap + 2;
+    const int k = c->cl.sor_k;
+    if (k < 1 || k + 1 > 320) { c->err = "sor_mean_k must be in [1, 319]"; return CVR_ERR_UNSUPPORTED; }
+    SorGrid* grid; int* cellstart;
+    int rc = sor_build_grid(c, B, in, in_stride, n_in, haveBox, 0.f, &grid, &cellstart);
+    if (rc) return rc;
     const float4* sp = c->d_spts;
-    dim3 g(cvr_div_up(maxN, 128), B);
+    const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B);
     if (k + 1 <= 32) k_sor_knn<32><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
     else if (k + 1 <= 64) k_sor_knn<64><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
     else if (k + 1 <= 128) k_sor_knn<128><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
@@ -281,15 +339,8 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     LAUNCH_CHECK(c);
     k_sor_stats<<<B, 1024, 0, c->stream>>>(c->d_meand, ptStride, n_in, k, c->cl.sor_alpha, c->d_sstats);
     LAUNCH_CHECK(c);
-    const int nblk = cvr_div_up(maxN, CVR_SEL_BLOCK);
-    const size_t cntStride = (size_t)nblk + 1;
-    k_sor_count<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride);
-    LAUNCH_CHECK(c);
-    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
-    LAUNCH_CHECK(c);
-    k_sor_write<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(in, in_stride, c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride, nblk,
-                                                                c->d_sorout, (size_t)maxN, c->d_nout);
-    LAUNCH_CHECK(c);
+    rc = sor_select(c, B, in, in_stride, n_in);
+    if (rc) return rc;
     cvr_stage_mark(c, "sor");
     return CVR_OK;
 }
@@ -298,40 +349,16 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
 // SURVEY 8(f) row n3 -- what MappingSystem does with the cloud right after the path.
 // pcl::RadiusOutlierRemoval (cv_reconstruct/src/system/MappingSystem.cpp:303-307): keep a point iff at least min_pts + 1 points
 // (itself included) lie within `radius` (squared distance <= r^2).  Same uniform grid as the SOR search, cell = radius.
-__global__ void k_ror_grid(const VoxBox* box, const int* nPtr, SorGrid* grid, int* ncellOut, float radius, int cap, int B)
-{
-    int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
-    SorGrid g;
-    g.n = nPtr[b];
-    float ext[3];
-    for (int k = 0; k < 3; k++) {
-        g.mn[k] = g.n > 0 ? ord2f(box[b].mn[k]) : 0.f;
-        const float mx = g.n > 0 ? ord2f(box[b].mx[k]) : 0.f;
-        ext[k] = fmaxf(mx - g.mn[k], 0.f);
-    }
-    float s = radius;                                  // cell edge: a multiple of the radius when the grid would get too large
-    for (int it = 0; it < 32; it++) {
-        long long tot = 1;
-        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
-        if (tot <= cap) break;
-        s *= 1.5f;
-    }
-    g.cell = s; g.inv = 1.0f / s;
-    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
-    grid[b] = g;
-    ncellOut[b] = g.ncell;
-}
 __global__ void __launch_bounds__(128) k_ror_count(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
                                                    const int* __restrict__ cellstart, size_t cellStride, float radius, int min_pts, float* __restrict__ flag)
 {
-    const int b = blockIdx.y, t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
     const SorGrid g = grid[b];
-    if (t >= g.n) return;
     const float4* sp = spts + (size_t)b * ptStride;
     const int* cs = cellstart + (size_t)b * cellStride;
-    const float4 q = sp[t];
     const float r2 = __fmul_rn(radius, radius);
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < g.n; t += gridDim.x * blockDim.x) {
+    const float4 q = sp[t];
     int cx, cy, cz;
     sor_cell(g, q.x, q.y, q.z, cx, cy, cz);
     const int R = (int)ceilf(radius * g.inv);           // rings of cells that can hold a point within the radius (1 unless the grid was coarsened)
@@ -351,6 +378,7 @@ __global__ void __launch_bounds__(128) k_ror_count(const float4* __restrict__ sp
         }
     // reuse the SOR compaction: "mean distance" 0 keeps, 1 drops against a threshold of 0.5
     flag[(size_t)b * ptStride + __float_as_int(q.w)] = cnt > min_pts ? 0.f : 1.f;
+    }
 }
 __global__ void k_ror_thr(SorStats* st, int B) { int b = blockIdx.x * blockDim.x + threadIdx.x; if (b < B) st[b].thr = 0.5; }
 
@@ -358,41 +386,16 @@ int cvr_launch_ror(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
 {
     const int maxN = c->maxN;
     const size_t ptStride = (size_t)maxN;
-    const int cap = c->sor_grid_cap;
-    const size_t cellStride = (size_t)cap + 2;
-    VoxBox* box = (VoxBox*)c->d_flags;
-    SorGrid* grid = (SorGrid*)(c->d_flags + (size_t)c->maxB * 16);
-    int* ncell = c->d_flags + (size_t)c->maxB * 32;
-    int* cellstart = c->d_cellstart;
-    int* cellfill = c->d_cellstart + (size_t)c->maxB * cellStride;
-    k_bbox_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, B);
-    LAUNCH_CHECK(c);
-    k_bbox_minmax<<<dim3(64, B), 256, 0, c->stream>>>(in, in_stride, n_in, box);
-    LAUNCH_CHECK(c);
-    k_ror_grid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, n_in, grid, ncell, radius, cap, B);
-    LAUNCH_CHECK(c);
-    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellstart, cellStride, ncell, 1);
-    LAUNCH_CHECK(c);
-    k_sor_zero<<<dim3(64, B), 256, 0, c->stream>>>(cellfill, cellStride, ncell, 1);
-    LAUNCH_CHECK(c);
-    k_sor_cellcount<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
-    LAUNCH_CHECK(c);
-    { const int rcs = scan_cells(c, B, cellstart, cellStride, cap, ncell); if (rcs) return rcs; }
-    k_sor_scatter<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
-    LAUNCH_CHECK(c);
-    k_ror_count<<<dim3(cvr_div_up(maxN, 128), B), 128, 0, c->stream>>>(c->d_spts, ptStride, grid, cellstart, cellStride, radius, min_pts, c->d_meand);
+    const size_t cellStride = (size_t)c->sor_grid_cap + 2;
+    SorGrid* grid; int* cellstart;
+    int rc = sor_build_grid(c, B, in, in_stride, n_in, false, radius, &grid, &cellstart);
+    if (rc) return rc;
+    k_ror_count<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B), 128, 0, c->stream>>>(c->d_spts, ptStride, grid, cellstart, cellStride, radius, min_pts, c->d_meand);
     LAUNCH_CHECK(c);
     k_ror_thr<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_sstats, B);
     LAUNCH_CHECK(c);
-    const int nblk = cvr_div_up(maxN, CVR_SEL_BLOCK);
-    const size_t cntStride = (size_t)nblk + 1;
-    k_sor_count<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride);
-    LAUNCH_CHECK(c);
-    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
-    LAUNCH_CHECK(c);
-    k_sor_write<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(in, in_stride, c->d_meand, ptStride, n_in, c->d_sstats, c->d_rowcnt, cntStride, nblk,
-                                                                c->d_sorout, (size_t)maxN, c->d_nout);
-    LAUNCH_CHECK(c);
+    rc = sor_select(c, B, in, in_stride, n_in);
+    if (rc) return rc;
     cvr_stage_mark(c, "ror");
     return CVR_OK;
 }

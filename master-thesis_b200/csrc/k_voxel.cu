@@ -36,14 +36,15 @@ __global__ void k_vox_keys(const cvr_point* __restrict__ pts, size_t stride, con
 {
     const int b = blockIdx.y;
     const VoxelHdr h = hdr[b];
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= h.n) return;
-    const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
-    const int i0 = (int)floorf(__fmul_rn(q.x, __fdiv_rn(1.0f, lx))) - h.minb[0];
-    const int i1 = (int)floorf(__fmul_rn(q.y, __fdiv_rn(1.0f, ly))) - h.minb[1];
-    const int i2 = (int)floorf(__fmul_rn(q.z, __fdiv_rn(1.0f, lz))) - h.minb[2];
-    keys[(size_t)b * kvStride + i] = h.passthrough ? 0u : (uint32_t)(i0 + i1 * h.div[0] + i2 * h.div[0] * h.div[1]);
-    vals[(size_t)b * kvStride + i] = (uint32_t)i;
+    const float ix = __fdiv_rn(1.0f, lx), iy = __fdiv_rn(1.0f, ly), iz = __fdiv_rn(1.0f, lz);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < h.n; i += gridDim.x * blockDim.x) {
+        const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
+        const int i0 = (int)floorf(__fmul_rn(q.x, ix)) - h.minb[0];
+        const int i1 = (int)floorf(__fmul_rn(q.y, iy)) - h.minb[1];
+        const int i2 = (int)floorf(__fmul_rn(q.z, iz)) - h.minb[2];
+        keys[(size_t)b * kvStride + i] = h.passthrough ? 0u : (uint32_t)(i0 + i1 * h.div[0] + i2 * h.div[0] * h.div[1]);
+        vals[(size_t)b * kvStride + i] = (uint32_t)i;
+    }
 }
 
 // ---- stable LSD radix sort, 8 bits per pass ------------------------------------------------------
@@ -60,16 +61,18 @@ __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_hist(const uint32_t*
     const int b = blockIdx.y, n = nPtr[b * nOff];
     if (!rs_pass_needed(hdr, b, shift)) return;
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int run = blockIdx.x * RS_BLOCK_WARPS + w;
-    const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
-    if (run >= nRuns || beg >= end) return;
-    for (int k = lane; k < 256; k += 32) sh[w][k] = 0;
-    __syncwarp();
     const uint32_t* kk = keys + (size_t)b * kvStride;
-    for (int i = beg + lane; i < end; i += 32) atomicAdd(&sh[w][(kk[i] >> shift) & 255], 1);
-    __syncwarp();
-    int* h = hist + (size_t)b * histStride + (size_t)run * 256;
-    for (int k = lane; k < 256; k += 32) h[k] = sh[w][k];
+    for (int run = blockIdx.x * RS_BLOCK_WARPS + w; run < nRuns; run += gridDim.x * RS_BLOCK_WARPS) {   // a warp per 1024-element run
+        const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
+        if (beg >= end) break;
+        for (int k = lane; k < 256; k += 32) sh[w][k] = 0;
+        __syncwarp();
+        for (int i = beg + lane; i < end; i += 32) atomicAdd(&sh[w][(kk[i] >> shift) & 255], 1);
+        __syncwarp();
+        int* h = hist + (size_t)b * histStride + (size_t)run * 256;
+        for (int k = lane; k < 256; k += 32) h[k] = sh[w][k];
+        __syncwarp();
+    }
 }
 // one CTA of 256 threads per frame: thread d walks the runs of digit d (coalesced 1 KB rows)
 __global__ void __launch_bounds__(256) k_rs_scan(int* __restrict__ hist, size_t histStride, const int* __restrict__ nPtr, int nOff, int shift,
@@ -93,91 +96,105 @@ __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_scatter(const uint32
     __shared__ int base[RS_BLOCK_WARPS][256];
     const int b = blockIdx.y, n = nPtr[b * nOff];
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int run = blockIdx.x * RS_BLOCK_WARPS + w;
-    if (run >= nRuns) return;
-    const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
-    if (beg >= end) return;
     const uint32_t* kk = keys + (size_t)b * kvStride; const uint32_t* vv = vals + (size_t)b * kvStride;
     uint32_t* ok = okeys + (size_t)b * kvStride; uint32_t* ov = ovals + (size_t)b * kvStride;
-    if (!rs_pass_needed(hdr, b, shift)) {                              // digit is 0 for every key: the pass is the identity
-        for (int i = beg + lane; i < end; i += 32) { ok[i] = kk[i]; ov[i] = vv[i]; }
-        return;
-    }
-    const int* h = hist + (size_t)b * histStride + (size_t)run * 256;
-    for (int k = lane; k < 256; k += 32) base[w][k] = h[k];
-    __syncwarp();
-    for (int i0 = beg; i0 < end; i0 += 32) {
-        const int i = i0 + lane;
-        const bool act = i < end;
-        const unsigned amask = __ballot_sync(0xffffffffu, act);
-        if (act) {
-            const uint32_t key = kk[i], val = vv[i];
-            const int dg = (key >> shift) & 255;
-            const unsigned peers = __match_any_sync(amask, dg);
-            const int rank = __popc(peers & ((1u << lane) - 1));
-            const int dst = base[w][dg] + rank;
-            ok[dst] = key; ov[dst] = val;
-            __syncwarp(amask);
-            if (rank == 0) base[w][dg] += __popc(peers);
+    const bool needed = rs_pass_needed(hdr, b, shift);
+    for (int run = blockIdx.x * RS_BLOCK_WARPS + w; run < nRuns; run += gridDim.x * RS_BLOCK_WARPS) {
+        const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
+        if (beg >= end) break;
+        if (!needed) {                                                 // digit is 0 for every key: the pass is the identity
+            for (int i = beg + lane; i < end; i += 32) { ok[i] = kk[i]; ov[i] = vv[i]; }
+            continue;
         }
+        const int* h = hist + (size_t)b * histStride + (size_t)run * 256;
+        for (int k = lane; k < 256; k += 32) base[w][k] = h[k];
         __syncwarp();
+        for (int i0 = beg; i0 < end; i0 += 32) {
+            const int i = i0 + lane;
+            const bool act = i < end;
+            const unsigned amask = __ballot_sync(0xffffffffu, act);
+            if (act) {
+                const uint32_t key = kk[i], val = vv[i];
+                const int dg = (key >> shift) & 255;
+                const unsigned peers = __match_any_sync(amask, dg);
+                const int rank = __popc(peers & ((1u << lane) - 1));
+                const int dst = base[w][dg] + rank;
+                ok[dst] = key; ov[dst] = val;
+                __syncwarp(amask);
+                if (rank == 0) base[w][dg] += __popc(peers);
+            }
+            __syncwarp();
+        }
     }
 }
 
 // ---- segments + centroids -------------------------------------------------------------------------
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_seg_count(const uint32_t* __restrict__ keys, size_t kvStride, const VoxelHdr* __restrict__ hdr,
-                                                             int* blkcnt, size_t cntStride)
+// Segment heads of the sorted keys (first index of every voxel) by the single-pass ordered selection.
+__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_seg_select(const uint32_t* __restrict__ keys, size_t kvStride, VoxelHdr* hdr, int* sel, size_t selStride,
+                                                              int* __restrict__ segstart, size_t segStride)
 {
     __shared__ int ws[33];
-    const int b = blockIdx.y, n = hdr[b].n, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
+    __shared__ int sh;
+    const int b = blockIdx.y, n = hdr[b].n, nch = (n + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;
+    const bool pass = hdr[b].passthrough != 0;
     const uint32_t* k = keys + (size_t)b * kvStride;
-    const int f = (i < n) && (hdr[b].passthrough || i == 0 || k[i] != k[i - 1]);
-    int tot;
-    block_excl_scan(f, ws, &tot);
-    if (threadIdx.x == 0) blkcnt[(size_t)b * cntStride + blockIdx.x] = tot;
-}
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_seg_write(const uint32_t* __restrict__ keys, size_t kvStride, VoxelHdr* hdr,
-                                                             const int* __restrict__ blkoff, size_t cntStride, int nblk, int* __restrict__ segstart, size_t segStride)
-{
-    __shared__ int ws[33];
-    const int b = blockIdx.y, n = hdr[b].n, i = blockIdx.x * CVR_SEL_BLOCK + threadIdx.x;
-    const uint32_t* k = keys + (size_t)b * kvStride;
-    const int f = (i < n) && (hdr[b].passthrough || i == 0 || k[i] != k[i - 1]);
-    const int e = block_excl_scan(f, ws, nullptr);
     int* ss = segstart + (size_t)b * segStride;
-    if (f) ss[blkoff[(size_t)b * cntStride + blockIdx.x] + e] = i;
-    if (blockIdx.x == 0 && threadIdx.x == 0) {
-        const int m = blkoff[(size_t)b * cntStride + nblk];
-        ss[m] = n;
-        hdr[b].m = m;
+    unsigned* status = (unsigned*)sel + (size_t)b * selStride;
+    int* ticket = (int*)status + (selStride - 1);
+    if (nch == 0) { if (blockIdx.x == 0 && threadIdx.x == 0) { ss[0] = 0; hdr[b].m = 0; } return; }
+    for (;;) {
+        const int chunk = sel_next_chunk(ticket, &sh);
+        if (chunk >= nch) break;
+        const int i = chunk * CVR_SEL_BLOCK + threadIdx.x;
+        const int f = (i < n) && (pass || i == 0 || k[i] != k[i - 1]);
+        int tot;
+        const int e = block_excl_scan(f, ws, &tot);
+        const int base = sel_chain_prefix(status, chunk, tot, &sh);
+        if (f) ss[base + e] = i;
+        if (chunk == nch - 1 && threadIdx.x == 0) { ss[base + tot] = n; hdr[b].m = base + tot; }
     }
 }
 // One thread per voxel: PCL's CentroidPoint accumulates x,y,z and r,g,b,a as floats in member order, divides by
 // the count, truncates the colours.  Member order = ascending point index (stable sort), as in the oracle.
-__global__ void k_vox_centroid(const cvr_point* __restrict__ pts, size_t stride, const uint32_t* __restrict__ vals, size_t kvStride,
+// Also accumulates the bounding box of the centroids (the outlier filter that follows builds its search grid from it).
+__global__ void __launch_bounds__(128) k_vox_centroid(const cvr_point* __restrict__ pts, size_t stride, const uint32_t* __restrict__ vals, size_t kvStride,
                                const VoxelHdr* __restrict__ hdr, const int* __restrict__ segstart, size_t segStride,
-                               cvr_point* __restrict__ out, size_t outStride, int* __restrict__ mOut)
+                               cvr_point* __restrict__ out, size_t outStride, int* __restrict__ mOut, VoxBox* box)
 {
-    const int b = blockIdx.y, j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int b = blockIdx.y;
     const VoxelHdr h = hdr[b];
-    if (j == 0) mOut[b] = h.m;
-    if (j >= h.m) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0) mOut[b] = h.m;
     const cvr_point* p = pts + (size_t)b * stride;
-    if (h.passthrough) { out[(size_t)b * outStride + j] = p[j]; return; }
     const int* ss = segstart + (size_t)b * segStride;
     const uint32_t* v = vals + (size_t)b * kvStride;
-    const int s = ss[j], e = ss[j + 1];
-    float sx = 0, sy = 0, sz = 0, sr = 0, sg = 0, sb = 0, sa = 0;
-    for (int i = s; i < e; i++) {
-        const cvr_point q = p[v[i]];
-        sx = __fadd_rn(sx, q.x); sy = __fadd_rn(sy, q.y); sz = __fadd_rn(sz, q.z);
-        sr = __fadd_rn(sr, (float)q.r); sg = __fadd_rn(sg, (float)q.g); sb = __fadd_rn(sb, (float)q.b); sa = __fadd_rn(sa, (float)q.a);
+    unsigned mn[3] = { 0xffffffffu, 0xffffffffu, 0xffffffffu }, mx[3] = { 0, 0, 0 };
+    bool any = false;
+    for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < h.m; j += gridDim.x * blockDim.x) {
+        cvr_point o;
+        if (h.passthrough) o = p[j];
+        else {
+            const int s = ss[j], e = ss[j + 1];
+            float sx = 0, sy = 0, sz = 0, sr = 0, sg = 0, sb = 0, sa = 0;
+            for (int i = s; i < e; i++) {
+                const cvr_point q = p[v[i]];
+                sx = __fadd_rn(sx, q.x); sy = __fadd_rn(sy, q.y); sz = __fadd_rn(sz, q.z);
+                sr = __fadd_rn(sr, (float)q.r); sg = __fadd_rn(sg, (float)q.g); sb = __fadd_rn(sb, (float)q.b); sa = __fadd_rn(sa, (float)q.a);
+            }
+            const float cnt = (float)(e - s);
+            o.x = __fdiv_rn(sx, cnt); o.y = __fdiv_rn(sy, cnt); o.z = __fdiv_rn(sz, cnt);
+            o.r = (uint8_t)__fdiv_rn(sr, cnt); o.g = (uint8_t)__fdiv_rn(sg, cnt); o.b = (uint8_t)__fdiv_rn(sb, cnt); o.a = (uint8_t)__fdiv_rn(sa, cnt);
+        }
+        out[(size_t)b * outStride + j] = o;
+        const unsigned ox = f2ord(o.x), oy = f2ord(o.y), oz = f2ord(o.z);
+        mn[0] = min(mn[0], ox); mx[0] = max(mx[0], ox); mn[1] = min(mn[1], oy); mx[1] = max(mx[1], oy); mn[2] = min(mn[2], oz); mx[2] = max(mx[2], oz);
+        any = true;
     }
-    const float cnt = (float)(e - s);
-    cvr_point o;
-    o.x = __fdiv_rn(sx, cnt); o.y = __fdiv_rn(sy, cnt); o.z = __fdiv_rn(sz, cnt);
-    o.r = (uint8_t)__fdiv_rn(sr, cnt); o.g = (uint8_t)__fdiv_rn(sg, cnt); o.b = (uint8_t)__fdiv_rn(sb, cnt); o.a = (uint8_t)__fdiv_rn(sa, cnt);
-    out[(size_t)b * outStride + j] = o;
+    if (box && __any_sync(0xffffffffu, any)) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) { mn[k] = __reduce_min_sync(0xffffffffu, mn[k]); mx[k] = __reduce_max_sync(0xffffffffu, mx[k]); }
+        if ((threadIdx.x & 31) == 0)
+            for (int k = 0; k < 3; k++) { atomicMin(&box[b].mn[k], mn[k]); atomicMax(&box[b].mx[k], mx[k]); }
+    }
 }
 
 // Sort (keys, vals) of every frame: d_keys[0]/d_vals[0] -> ... ; returns the index (0/1) of the buffer holding the result.
@@ -186,10 +203,10 @@ int cvr_radix_sort_pairs(cvr_ctx* c, int B, const int* nPtr, int nOff, int maxN,
     const int nRuns = cvr_div_up(maxN, RS_WARP_ELEMS);
     const size_t histStride = (size_t)256 * nRuns + 1;
     const size_t kvStride = (size_t)c->maxN;
+    const dim3 g(cvr_frame_blocks(c, B, (size_t)nRuns, RS_BLOCK_WARPS, 8), B);
     int cur = 0;
     for (int pass = 0; pass < passes; pass++) {
         const int shift = pass * 8;
-        dim3 g(cvr_div_up(nRuns, RS_BLOCK_WARPS), B);
         k_rs_hist<<<g, RS_BLOCK_WARPS * 32, 0, c->stream>>>(c->d_keys[cur], kvStride, nPtr, nOff, shift, (int*)c->d_hist, histStride, nRuns, hdr);
         LAUNCH_CHECK(c);
         k_rs_scan<<<B, 256, 0, c->stream>>>((int*)c->d_hist, histStride, nPtr, nOff, shift, hdr);
@@ -203,33 +220,33 @@ int cvr_radix_sort_pairs(cvr_ctx* c, int B, const int* nPtr, int nOff, int maxN,
     return CVR_OK;
 }
 
-int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in)
+int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox)
 {
     const int maxN = c->maxN;
     const size_t kvStride = (size_t)maxN;
     const float lx = c->cl.leaf[0], ly = c->cl.leaf[1], lz = c->cl.leaf[2];
-    VoxBox* box = (VoxBox*)c->d_flags;    // d_flags is sized >= B * sizeof(VoxBox)
-    k_bbox_init<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, B);
+    if (!haveBox) {                                                    // stand-alone call: measure the input's bounding box
+        int rc0 = cvr_launch_chain_init(c, B, false, true, true);
+        if (rc0) return rc0;
+        k_bbox_minmax<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B), 256, 0, c->stream>>>(in, in_stride, n_in, c->d_boxv);
+        LAUNCH_CHECK(c);
+    }
+    const size_t selStride = cvr_sel_stride(maxN);
+    int* sel = c->d_sel + (size_t)c->maxB * selStride;                 // selection 1 of the chain
+    CVR_CUDA(c, cudaMemsetAsync(sel, 0, (size_t)B * selStride * sizeof(int), c->stream));
+    k_vox_setup<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_boxv, n_in, c->d_vhdr, lx, ly, lz, B);
     LAUNCH_CHECK(c);
-    k_bbox_minmax<<<dim3(64, B), 256, 0, c->stream>>>(in, in_stride, n_in, box);
-    LAUNCH_CHECK(c);
-    k_vox_setup<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(box, n_in, c->d_vhdr, lx, ly, lz, B);
-    LAUNCH_CHECK(c);
-    k_vox_keys<<<dim3(cvr_div_up(maxN, 256), B), 256, 0, c->stream>>>(in, in_stride, c->d_vhdr, lx, ly, lz, c->d_keys[0], c->d_vals[0], kvStride);
+    k_vox_keys<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B), 256, 0, c->stream>>>(in, in_stride, c->d_vhdr, lx, ly, lz, c->d_keys[0], c->d_vals[0], kvStride);
     LAUNCH_CHECK(c);
     int buf = 0;
     int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, c->d_vhdr, &buf);
     if (rc) return rc;
-    const int nblk = cvr_div_up(maxN, CVR_SEL_BLOCK);
-    const size_t cntStride = (size_t)nblk + 1;
-    k_seg_count<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, c->d_rowcnt, cntStride);
+    const int nch = cvr_div_up(maxN, CVR_SEL_BLOCK);
+    k_seg_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 2), B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, sel, selStride,
+                                                                                                 c->d_segstart, (size_t)maxN + 1);
     LAUNCH_CHECK(c);
-    k_scan_excl<<<B, 1024, 0, c->stream>>>(c->d_rowcnt, cntStride, nblk, nullptr, 1);
-    LAUNCH_CHECK(c);
-    k_seg_write<<<dim3(nblk, B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, c->d_rowcnt, cntStride, nblk, c->d_segstart, (size_t)maxN + 1);
-    LAUNCH_CHECK(c);
-    k_vox_centroid<<<dim3(cvr_div_up(maxN, 128), B), 128, 0, c->stream>>>(in, in_stride, c->d_vals[buf], kvStride, c->d_vhdr, c->d_segstart, (size_t)maxN + 1,
-                                                                         c->d_vox, (size_t)maxN, c->d_nvox);
+    k_vox_centroid<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 128, 8), B), 128, 0, c->stream>>>(in, in_stride, c->d_vals[buf], kvStride, c->d_vhdr, c->d_segstart,
+                                                                                                (size_t)maxN + 1, c->d_vox, (size_t)maxN, c->d_nvox, c->d_boxs);
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "voxel");
     return CVR_OK;
