@@ -1,23 +1,30 @@
 #!/usr/bin/env python
 """bench.py -- stereo frames/sec through SGBM -> cloud -> filter (BASELINE.json metric) on N B200s.
 
-A "step" = one pass of the hot path (cvr_process_batch: cvtColor, StereoSGBM-exact disparity, prune, triangulate,
-voxel grid, statistical outlier removal) over one batch of `--batch` KITTI-shape synthetic pairs per GPU.
-Workload = BASELINE.json configs[1]: KITTI-odometry-shape sequence, 1242x375, D=128, config_default.json SGBM
-parameters, frames sharded over the ranks (frame-level data parallelism, weak scaling: per-GPU batch fixed); the
-only exchange is the gather of the filtered clouds to the mapping rank (rank 0) over NCCL.
+A "step" = one pass of the hot path (cvtColor, StereoSGBM-exact disparity, prune, triangulate, voxel grid, statistical
+outlier removal, then the gather of the filtered clouds to the mapping rank) over one batch of `--batch` KITTI-shape
+synthetic pairs per GPU.  Workload = BASELINE.json configs[1]: KITTI-odometry-shape sequence, 1242x375, D=128,
+config_default.json SGBM parameters, frames sharded over the ranks (frame-level data parallelism, weak scaling: per-GPU
+batch fixed); the only exchange is cvr_gather_clouds (NCCL) to rank 0.
 
-  value : frames/s with the batch already resident in HBM (device pointers through the C ABI)
-  e2e   : frames/s through the same C-ABI call with pinned HOST buffers (H2D of both images and D2H of the
-          filtered clouds inside the timed region)
-  roofline     : dominant kernel (k_path_v, the fused vertical/diagonal path aggregation), algorithmic bytes / its
-                 CUDA-event time measured on the library's stream during the timed steps
+  value : frames/s with the batch already resident in HBM (device pointers through the C ABI), clouds gathered into a
+          device buffer of rank 0
+  e2e   : frames/s through the same C-ABI calls with pinned HOST buffers: H2D of both images inside the timed region, and
+          the filtered clouds of EVERY rank delivered to rank 0's host memory (N = 1: the D2H copy of cvr_wait_batch)
+  roofline     : dominant kernel (k_path_v3), algorithmic bytes / its CUDA-event time measured on the library's stream
+                 during the timed steps; `path` = the whole step against SURVEY 8(d)'s 458 MB per frame;
+                 `traffic` / `dram_bytes_per_frame` from the ncu capture committed under profiles/ (refused when the
+                 capture was taken on other kernel sources or another batch size)
+  side_shapes  : BASELINE.json configs[2], [3], [4] (1280x720 D=192 MODE_HH; 1920x1080 D=256; 20 M-point filter stress),
+                 device-resident, each with its own clock sample and fraction of the HBM roofline (N = 1 only)
   cpu_baseline : the reference's CPU path on this box's host cores (cv2 = the OpenCV the reference calls; the PCL
                  half through the C port in oracle/), bounded sample, rank 0 at N=1 only
   --impl reference : that CPU path as its own arm.
 """
 import argparse
 import ctypes as C
+import glob
+import hashlib
 import importlib
 import json
 import os
@@ -35,6 +42,9 @@ W, H, D, BS = 1242, 375, 128, 27
 WORKLOAD = "KITTI-odometry-shape sequence, synthetic rectified pairs 1242x375 BGR, StereoSGBM D=128 bs=27 (config_default.json), " \
            "prune + Triangulate3D + VoxelGrid(0.2) + SOR(k=30, 0.5), frames sharded over ranks"
 UNIQUE_PAIRS = 16
+# algorithmic bytes per frame (each stage boundary written once and read once)
+ALG_BYTES = {"kitti": 458e6, "spi_hh": 2.14e9, "hd": 3.76e9, "filter_stress": 13.9e9}
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "r02_traffic.json")
 
 
 def hbm_peak():
@@ -43,6 +53,16 @@ def hbm_peak():
             return float(json.load(f)["hbm_gbs"]), "measured"
     except Exception:
         return 6650.0, "fallback"
+
+
+def source_sha():
+    """Hash of the kernel sources: an ncu capture only describes the kernels it was taken on."""
+    h = hashlib.sha256()
+    for f in sorted(glob.glob(os.path.join(ROOT, "master-thesis_b200", "csrc", "*.cu*"))):
+        h.update(os.path.basename(f).encode())
+        with open(f, "rb") as fh:
+            h.update(fh.read())
+    return h.hexdigest()[:16]
 
 
 class ClockSampler:
@@ -90,11 +110,11 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def make_pairs(n):
+def make_pairs(n, h=H, w=W, d=D):
     synth = importlib.import_module("master-thesis_b200.synth")
     Ls, Rs = [], []
     for s in range(n):
-        l, r = synth.synth_pair(H, W, D, seed=s, color=True)
+        l, r = synth.synth_pair(h, w, d, seed=s, color=True)
         Ls.append(l); Rs.append(r)
     return np.stack(Ls), np.stack(Rs)
 
@@ -187,6 +207,100 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------------------
+# side shapes: BASELINE.json configs[2..4] on one GPU, device-resident
+def _side_stereo(cvr, torch, dev, local, name, h, w, d, bs, mode, batch, steps, peak):
+    cfg = cvr.parse_config(None)
+    cfg.update(block_size=bs, num_disparities=d)
+    rec = cvr.Reconstruct3D(w, h, config=cfg, mode=mode, max_batch=batch + batch // 4, device=local)
+    B = rec.suggest_batch(batch)
+    Ls, Rs = make_pairs(4, h, w, d)
+    idx = [i % 4 for i in range(B)]
+    dL = torch.from_numpy(Ls[idx]).to(dev); dR = torch.from_numpy(Rs[idx]).to(dev)
+    cap = 200000 * B                                                   # packed points of a whole batch
+    ios = []
+    keep = []
+    for _ in range(2):
+        cl = torch.empty((cap, 16), dtype=torch.uint8, device=dev); off = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+        cnt = torch.zeros(B, dtype=torch.int32, device=dev)
+        io = cvr.Batch()
+        io.mem, io.channels, io.stages = cvr.MEM_DEVICE, 3, 15
+        io.left, io.left_step, io.left_frame_stride = dL.data_ptr(), w * 3, w * h * 3
+        io.right, io.right_step, io.right_frame_stride = dR.data_ptr(), w * 3, w * h * 3
+        io.cloud_packed, io.cloud_packed_capacity, io.cloud_offsets, io.cloud_count = cl.data_ptr(), cap, off.data_ptr(), cnt.data_ptr()
+        ios.append(io); keep.append((cl, off, cnt))
+
+    def run(n):
+        torch.cuda.synchronize()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        e0.record()
+        rec.submit_batch_raw(ios[0], B)
+        for i in range(1, n):
+            rec.submit_batch_raw(ios[i & 1], B)
+            rec.wait_batch()
+        rec.wait_batch()
+        e1.record()
+        torch.cuda.synchronize()
+        return max(e0.elapsed_time(e1), 0.9 * (time.perf_counter() - t0) * 1e3)
+    run(3)
+    clocks = ClockSampler(local)
+    ms = run(steps)
+    clk = clocks.stop()
+    rec.close()
+    fps = steps * B / (ms * 1e-3)
+    key = "spi_hh" if name.startswith("spi") else "hd"
+    alg = ALG_BYTES[key] if not (key == "hd" and mode == 1) else 6.5e9
+    ach = alg * fps / 1e9
+    return {"workload": "%dx%d D=%d bs=%d %s, prune + Triangulate3D + VoxelGrid(0.2) + SOR(30, 0.5), device-resident" % (w, h, d, bs, "MODE_HH" if mode else "MODE_SGBM"),
+            "frames_per_s": fps, "batch": B, "steps": steps, "ms_per_step": ms / steps,
+            "roofline": {"bound": "hbm", "alg_bytes_per_frame": alg, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak}, "clocks": clk}
+
+
+def _side_filter_stress(cvr, torch, dev, local, n, peak):
+    rng = np.random.default_rng(0)
+    xyz = rng.random((n, 3), dtype=np.float32) * np.array([40, 12, 40], np.float32)
+    no = n // 100
+    # SURVEY 8(d) cfg5 puts the 1 % outliers in a 3x larger box, which overflows PCL's int32 voxel index at leaf 0.05 (the
+    # filter would pass the cloud through); a 1.5x box keeps the grid (1200 x 360 x 1200) inside it
+    xyz[:no] = (rng.random((no, 3), dtype=np.float32) - np.float32(1 / 6)) * np.array([60, 18, 60], np.float32)
+    pts = np.zeros(n, cvr.POINT_DTYPE)
+    pts["x"], pts["y"], pts["z"] = xyz[:, 0], xyz[:, 1], xyz[:, 2]
+    pts["r"] = rng.integers(0, 256, n); pts["g"] = 7; pts["b"] = 9; pts["a"] = 255
+    cfg = cvr.parse_config(None)
+    cfg.update(outlier_min_k=50, outlier_std_threshold=1.0)
+    rec = cvr.Reconstruct3D(64, 64, config=cfg, voxel_leaf=0.05, max_points=n, filter_only=True, device=local)
+    d_in = torch.from_numpy(pts.view(np.uint8).reshape(n, 16)).to(dev)
+    d_vox = torch.empty((n, 16), dtype=torch.uint8, device=dev)
+    d_out = torch.empty((n, 16), dtype=torch.uint8, device=dev)
+
+    def run():
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        m = rec.filter_cloud_device(d_in.data_ptr(), n, cvr.STAGE_VOXEL, d_vox.data_ptr(), n)
+        t1 = time.perf_counter()
+        tv = dict(rec.last_timings())
+        k = rec.filter_cloud_device(d_vox.data_ptr(), m, cvr.STAGE_SOR, d_out.data_ptr(), n)
+        t2 = time.perf_counter()
+        ts = dict(rec.last_timings())
+        return m, k, tv.get("voxel", 0.0), ts.get("sor", 0.0), (t1 - t0) * 1e3, (t2 - t1) * 1e3
+    rec.set_profiling(True)
+    run()
+    clocks = ClockSampler(local)
+    res = [run() for _ in range(3)]
+    clk = clocks.stop()
+    rec.close()
+    m, k = res[0][0], res[0][1]
+    vox_ms = float(np.mean([r[2] for r in res])); sor_ms = float(np.mean([r[3] for r in res]))
+    call_ms = float(np.mean([r[4] + r[5] for r in res]))
+    alg = 16.0 * n + 24.0 * n + 16.0 * m + m * (24.0 + 12 * 50) + 16.0 * k            # SURVEY 8(d) cfg5 formula with the measured M, K
+    ach = alg / ((vox_ms + sor_ms) * 1e-3) / 1e9
+    return {"workload": "%d-point cloud (uniform 40x12x40 m + 1 %% outliers), VoxelGrid leaf 0.05 then SOR k=50 alpha=1.0, device-resident" % n,
+            "points_in": n, "voxels": m, "kept": k, "voxel_ms": vox_ms, "sor_ms": sor_ms, "both_calls_wall_ms": call_ms,
+            "roofline": {"bound": "hbm", "alg_bytes": alg, "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                         "floor_ms": alg / (peak * 1e9) * 1e3}, "clocks": clk}
+
+
+# ------------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -196,6 +310,8 @@ def main():
     ap.add_argument("--batch", type=int, default=104, help="frames per GPU per step")
     ap.add_argument("--exact-batch", action="store_true", help="use --batch as given instead of letting the library round it to full cluster waves")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-side-shapes", action="store_true", help="skip BASELINE.json configs[2..4] (they are measured at N=1 only)")
+    ap.add_argument("--stress-points", type=int, default=20_000_000)
     ap.add_argument("--rectify", action="store_true", help="side measurement: config requires_rectification = true (RectifyImages on the device before the matcher)")
     ap.add_argument("--matcher", default="sgbm", choices=["sgbm", "bm"], help="sgbm = the headline path; bm = the reference's other block matcher (side measurement)")
     args = ap.parse_args()
@@ -223,7 +339,7 @@ def main():
         cfg["block_matcher"] = cvr.MATCHER_BM
     cfg["requires_rectification"] = bool(args.rectify)
     # --batch is a target: the library rounds it to a multiple of the clusters its vertical path kernel runs at once on this
-    # GPU (26 on the B200s measured so far => 104); every rank asks its own GPU, all ranks then use the smallest answer
+    # GPU; every rank asks its own GPU, all ranks then use the smallest answer
     rec = cvr.Reconstruct3D(W, H, config=cfg, max_batch=B + B // 4, device=local)   # defaults = config_default.json SGBM/SBM sections, leaf 0.2, SOR 30/0.5
     if args.rectify:                                                   # a KITTI-like raw calibration (5 distortion terms, small rotation)
         K = np.array([[959.791, 0, 696.0217], [0, 956.9251, 224.1806], [0, 0, 1]])
@@ -238,52 +354,59 @@ def main():
             tb = torch.tensor([B], dtype=torch.int32, device=dev)
             dist.all_reduce(tb, op=dist.ReduceOp.MIN)
             B = int(tb.item())
+    if world > 1:
+        # the library's own communicator for cvr_gather_clouds: rank 0 makes the NCCL id, torch carries the 128 bytes
+        idt = torch.zeros(cvr.COMM_ID_BYTES, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            idt.copy_(torch.frombuffer(bytearray(cvr.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        rec.comm_init(world, rank, idt.cpu().numpy().tobytes())
     Ls, Rs = make_pairs(UNIQUE_PAIRS)
     idx = [(rank * B + i) % UNIQUE_PAIRS for i in range(B)]            # frame_id sharding; the pool of unique pairs is cycled
     hL = torch.from_numpy(Ls[idx]).pin_memory(); hR = torch.from_numpy(Rs[idx]).pin_memory()
     dL = hL.to(dev); dR = hR.to(dev)
-    cap = 65536                                                        # points per frame after voxel + SOR (~11k observed)
+    cap = 16384 * B                                                    # points per batch after voxel + SOR (~1.6k per frame observed)
     # two batches are in flight at a time: two sets of output buffers, used alternately
-    d_clouds = [torch.empty((B, cap, 16), dtype=torch.uint8, device=dev) for _ in range(2)]
-    d_cnts = [torch.zeros(B, dtype=torch.int32, device=dev) for _ in range(2)]
-    h_clouds = [torch.empty((B, cap, 16), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    d_clouds = [torch.empty((cap, 16), dtype=torch.uint8, device=dev) for _ in range(2)]
+    d_offs = [torch.zeros(B + 1, dtype=torch.int32, device=dev) for _ in range(2)]
+    h_clouds = [torch.empty((cap, 16), dtype=torch.uint8).pin_memory() for _ in range(2)]
+    h_offs = [torch.zeros(B + 1, dtype=torch.int32).pin_memory() for _ in range(2)]
     h_cnts = [torch.zeros(B, dtype=torch.int32).pin_memory() for _ in range(2)]
-    h_cnt = h_cnts[0]
     frame_bytes = W * H * 3
+    gathered_bytes = [0]
 
-    def batch_struct(mem, L, R, cloud, cnt):
+    def batch_struct(mem, L, R, cloud, off, cnt):
         io = cvr.Batch()
         io.mem = mem; io.channels = 3
         io.left, io.left_step, io.left_frame_stride = L.data_ptr(), W * 3, frame_bytes
         io.right, io.right_step, io.right_frame_stride = R.data_ptr(), W * 3, frame_bytes
-        io.cloud, io.cloud_capacity, io.cloud_count = cloud.data_ptr(), cap, cnt.data_ptr()
+        if cloud is not None:
+            io.cloud_packed, io.cloud_packed_capacity, io.cloud_offsets = cloud.data_ptr(), cap, off.data_ptr()
+        if cnt is not None:
+            io.cloud_count = cnt.data_ptr()
         io.stages = 15
         return io
-    io_dev = [batch_struct(cvr.MEM_DEVICE, dL, dR, d_clouds[k], d_cnts[k]) for k in range(2)]
-    io_host = [batch_struct(cvr.MEM_HOST, hL, hR, h_clouds[k], h_cnts[k]) for k in range(2)]
+    io_dev = [batch_struct(cvr.MEM_DEVICE, dL, dR, d_clouds[k], d_offs[k], None) for k in range(2)]
+    if world == 1:
+        io_host = [batch_struct(cvr.MEM_HOST, hL, hR, h_clouds[k], h_offs[k], h_cnts[k]) for k in range(2)]
+    else:       # N > 1: no local download of the clouds -- they travel device to device to rank 0, which takes them to its host
+        io_host = [batch_struct(cvr.MEM_HOST, hL, hR, None, None, h_cnts[k]) for k in range(2)]
 
-    # gather of the filtered clouds to the mapping rank (rank 0): counts by all_gather, payload by grouped send/recv
-    gather_buf = torch.empty((world, B * cap // 4, 16), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None
+    # the mapping rank's receive buffers for cvr_gather_clouds
+    gcap = cap * world
+    g_dev = torch.empty((gcap, 16), dtype=torch.uint8, device=dev) if (world > 1 and rank == 0) else None
+    g_host = torch.empty((gcap, 16), dtype=torch.uint8).pin_memory() if (world > 1 and rank == 0) else None
+    g_foff = np.zeros(B * world + 1, np.int32); g_fr = np.zeros(world, np.int32)
 
-    def gather_clouds(k):
+    def gather(to_host):
         if world == 1:
             return
-        d_cnt, d_cloud = d_cnts[k], d_clouds[k]
-        cnts = [torch.empty_like(d_cnt) for _ in range(world)]
-        dist.all_gather(cnts, d_cnt)
-        tot = [int(c.sum().item()) for c in cnts]
-        # compact this rank's clouds (variable length per frame) into one contiguous payload
-        mask = torch.arange(cap, device=dev)[None, :] < d_cnt[:, None]
-        payload = d_cloud[mask]
-        ops = []
         if rank == 0:
-            for r in range(1, world):
-                ops.append(dist.P2POp(dist.irecv, gather_buf[r, :tot[r]], r))
+            buf = g_host if to_host else g_dev
+            rec.gather_clouds_raw(0, cvr.MEM_HOST if to_host else cvr.MEM_DEVICE, buf.data_ptr(), gcap, g_foff.ctypes.data, len(g_foff), g_fr.ctypes.data)
+            gathered_bytes[0] = int(g_foff[int(g_fr.sum())]) * 16
         else:
-            ops.append(dist.P2POp(dist.isend, payload, 0))
-        if ops:
-            for w_ in dist.batch_isend_irecv(ops):
-                w_.wait()
+            rec.gather_clouds_raw(0, cvr.MEM_HOST if to_host else cvr.MEM_DEVICE, None, 0, None, 0, None)
 
     def barrier():
         torch.cuda.synchronize()
@@ -291,7 +414,7 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(io, steps, with_gather=True, profile=False, pipelined=False):
+    def timed(io, steps, profile=False, host=False):
         rec.set_profiling(profile)
         stage_ms = {}
         barrier()
@@ -300,14 +423,12 @@ def main():
         e0.record()
         t0 = time.perf_counter()
         # Two batches in flight (cvr_submit_batch / cvr_wait_batch): the upload and the matcher of step i+1 overlap the
-        # filter stages of step i and the download of step i-1.  `pipelined` = host buffers (every step's H2D and D2H are
-        # inside the timed region; the same pinned host buffers are re-sent every step; each rank delivers its filtered
-        # clouds to its own host process).  Otherwise device-resident inputs and outputs, and the NCCL gather of each
-        # step's clouds to the mapping rank follows its wait.  With `profile` the library brackets every stage with
-        # events on the stream it runs on and hands the durations back at the wait.
+        # download of step i.  `host`: pinned host buffers (every step's H2D and D2H inside the timed region; the same
+        # buffers are re-sent every step).  After each wait the step's clouds are gathered to rank 0 (cvr_gather_clouds,
+        # on the library's communication stream, while the next batch computes).  With `profile` the library brackets
+        # every stage with events on the stream it runs on and hands the durations back at the wait.
         def collected(i):
-            if with_gather and not pipelined:
-                gather_clouds(i & 1)
+            gather(host)
             if profile:
                 for n_, ms_ in rec.last_timings():
                     stage_ms.setdefault(n_, []).append(ms_)
@@ -333,16 +454,18 @@ def main():
         return float(t.item()), rec.launch_count() - l0, stage_ms
 
     # warm-up (both paths), then the timed regions
-    timed(io_dev, max(args.warmup, 3), profile=False)
-    timed(io_host, 2, pipelined=True)
+    timed(io_dev, max(args.warmup, 3))
+    timed(io_host, 2, host=True)
     clocks = ClockSampler(local) if rank == 0 else None
     ms_dev, launches, stage_ms = timed(io_dev, args.steps, profile=True)
-    ms_e2e, _, _ = timed(io_host, args.steps, pipelined=True)
+    ms_e2e, _, _ = timed(io_host, args.steps, host=True)
     clk = clocks.stop() if clocks else None
-    counts = h_cnt.numpy().copy()
+    counts = h_cnts[(args.steps - 1) & 1].numpy().copy()
     frames = args.steps * B * world
     value = frames / (ms_dev * 1e-3)
     e2e_v = frames / (ms_e2e * 1e-3)
+    vcfg = rec.path_kernel_config() if hasattr(rec, "path_kernel_config") else None
+    rec.close()
 
     if rank == 0:
         peak, peak_kind = hbm_peak()
@@ -352,29 +475,64 @@ def main():
         if args.matcher == "bm":
             kv = []
         kv_ms = float(np.mean(kv)) if kv else None
+        step_ms = ms_dev / args.steps
         roof = None
         if kv_ms:
             ach = alg_bytes / (kv_ms * 1e-3) / 1e9
-            # DRAM traffic of this kernel from the committed ncu --set full capture (profiles/r01f_k_path_v3_raw.csv:
-            # dram__bytes_read.sum + dram__bytes_write.sum = 22.245 + 11.087 GB for a 104-frame launch), scaled to this batch
-            traffic = (22.245403e9 + 11.087477e9) / 104.0 * B
-            roof = {"bound": "hbm", "kernel": "k_path_v3<4,false,false,false,true,1024>", "achieved": ach, "peak": peak, "peak_kind": peak_kind,
-                    "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": kv_ms,
-                    "share_of_step": kv_ms / (ms_dev / args.steps)}
+            # measured DRAM traffic: the ncu capture committed under profiles/, valid only for these kernel sources and this batch
+            traffic, dram_frame, note = None, None, None
+            try:
+                with open(TRAFFIC_FILE) as f:
+                    tr = json.load(f)
+                if tr.get("src_sha") != source_sha():
+                    note = "profiles/r02_traffic.json was captured on other kernel sources: refused"
+                elif int(tr.get("batch", -1)) != B:
+                    note = "profiles/r02_traffic.json was captured at batch %s, this run uses %d: refused" % (tr.get("batch"), B)
+                else:
+                    kk = tr["kernels"]["k_path_v3"]
+                    traffic = float(kk["dram_read"]) + float(kk["dram_write"])
+                    dram_frame = float(tr["dram_bytes_per_frame"])
+                    note = "ncu --set full / dram__bytes of %s" % tr.get("source", "profiles/")
+            except Exception as ex:      # noqa: BLE001
+                note = "no usable capture: %r" % (ex,)
+            path_ach = ALG_BYTES["kitti"] * B / (step_ms * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": "k_path_v3 (fused down-right / down / down-left path aggregation)", "achieved": ach, "peak": peak, "peak_kind": peak_kind,
+                    "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_note": note, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": kv_ms,
+                    "share_of_step": kv_ms / step_ms,
+                    "path": {"alg_bytes_per_frame": ALG_BYTES["kitti"], "achieved": path_ach, "frac": path_ach / peak,
+                             "what": "SURVEY 8(d): every stage boundary written once and read once; whole step time"},
+                    "dram_bytes_per_frame": dram_frame,
+                    "dram_achieved": (dram_frame * B / (step_ms * 1e-3) / 1e9) if dram_frame else None}
+        h2d = 2 * frame_bytes * B
+        d2h = (int(counts.sum()) * 16 + 4 * (2 * B + 1)) if world == 1 else (gathered_bytes[0] + 4 * B)
         out = {
             "metric": "stereo frames/sec (SGBM->cloud->filter)", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-            "warmup": max(args.warmup, 3), "ms_per_step": ms_dev / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "int16", "data": "synthetic (%d unique seeded pairs cycled)" % UNIQUE_PAIRS,
             "config": {"workload": WORKLOAD + (" + RectifyImages (requires_rectification)" if args.rectify else ""), "frames_per_gpu_per_step": B, "l2": "inputs larger than L2: working set per step (cost volumes 214 MB/frame x batch) >> 126 MB L2",
-                       "parallelism": "frames sharded, dp%d, NCCL gather of filtered clouds to rank 0" % world},
-            "e2e": {"value": e2e_v, "unit": "frames/s", "h2d_bytes_per_step": 2 * frame_bytes * B, "d2h_bytes_per_step": int(counts.sum()) * 16 + 4 * B,
-                    "ms_per_step": ms_e2e / args.steps},
+                       "parallelism": "frames sharded, dp%d, cvr_gather_clouds (NCCL send/recv) of the filtered clouds to rank 0 in both arms" % world},
+            "e2e": {"value": e2e_v, "unit": "frames/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
+                    "delivery": "rank 0 host memory holds the clouds of all ranks" if world > 1 else "host memory (one packed copy per batch)"},
             "gpu_launches": int(launches),
+            "launches_per_step": launches / args.steps,
             "clocks": clk,
             "roofline": roof,
             "stage_ms_per_step": {k: float(np.mean(v)) for k, v in stage_ms.items()},
+            "stage_us_per_frame": {k: float(np.mean(v)) / B * 1e3 for k, v in stage_ms.items()},
             "points_per_frame_after_filter": float(counts.mean()),
         }
+        if world == 1 and not args.no_side_shapes and args.matcher == "sgbm" and not args.rectify:
+            side = {}
+            for nm, fn in (("spi_hh_bs27", lambda: _side_stereo(cvr, torch, dev, local, "spi", 720, 1280, 192, 27, 1, 30, 4, peak)),
+                           ("spi_hh_bs5", lambda: _side_stereo(cvr, torch, dev, local, "spi", 720, 1280, 192, 5, 1, 30, 4, peak)),
+                           ("hd", lambda: _side_stereo(cvr, torch, dev, local, "hd", 1080, 1920, 256, 27, 0, 14, 4, peak)),
+                           ("filter_stress", lambda: _side_filter_stress(cvr, torch, dev, local, args.stress_points, peak))):
+                try:
+                    side[nm] = fn()
+                except Exception as ex:      # noqa: BLE001
+                    side[nm] = {"error": repr(ex)}
+                torch.cuda.empty_cache()
+            out["side_shapes"] = side
         if world == 1 and not args.no_cpu_baseline:
             # run in a fresh process: no fork after CUDA initialisation, no interference with the GPU timing above
             try:
@@ -385,7 +543,6 @@ def main():
                 out["cpu_baseline"] = {"value": None, "unit": "frames/s", "cores": 0, "kind": "port", "sample": "failed: %r" % (ex,)}
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(out) + "\n").encode())
-    rec.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

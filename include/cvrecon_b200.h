@@ -157,6 +157,12 @@ int cvr_voxel_grid(cvr_ctx* ctx, const cvr_point* in, int n, cvr_point* out, int
  * pcl::StatisticalOutlierRemoval with meanK / stddevMulThresh from cvr_params.  in == out allowed. */
 int cvr_sor(cvr_ctx* ctx, const cvr_point* in, int n, cvr_point* out, int capacity, int* kept_out);
 
+/* The two filters above on one cloud that may already live in DEVICE memory (mem = CVR_MEM_HOST | CVR_MEM_DEVICE for `in` and
+ * `out` alike): stages = 4 (VoxelGrid), 8 (StatisticalOutlierRemoval) or 12 (VoxelGrid then SOR, the order of MappingSystem.cpp:297-300
+ * followed by PointCloudPostProcessor::RemoveOutliers).  Lets a cloud the path produced be filtered again (e.g. a merged map
+ * block) without a round trip through the host. */
+int cvr_filter_cloud(cvr_ctx* ctx, int mem, const cvr_point* in, int n, int stages, cvr_point* out, int capacity, int* n_out);
+
 /* SURVEY 8(f) row n3 -- the consumer-side steps MappingSystem applies to the cloud right after the path.
  * Replaces: pcl::RadiusOutlierRemoval::filter at MappingSystem.cpp:303-307 (setRadiusSearch(1.0), setMinNeighborsInRadius(300)):
  * a point is kept iff at least min_neighbors + 1 points (itself included) lie within `radius`.  Input order preserved. */

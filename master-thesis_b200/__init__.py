@@ -36,6 +36,7 @@ EXPORTS = [
     "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
     "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps", "cvr_suggest_batch",
     "cvr_comm_get_unique_id", "cvr_comm_init", "cvr_comm_attach", "cvr_comm_destroy", "cvr_gather_clouds", "cvr_gather_layout",
+    "cvr_filter_cloud",
 ]
 COMM_ID_BYTES = 128
 
@@ -126,6 +127,7 @@ def load_library():
     lib.cvr_points_to_pcl.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.cvr_points_to_pcl.restype = None
     lib.cvr_prune_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.cvr_filter_cloud.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     lib.cvr_comm_get_unique_id.argtypes = [C.c_void_p]
     lib.cvr_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.cvr_comm_attach.argtypes = [C.c_void_p, C.c_void_p]
@@ -407,6 +409,20 @@ class Reconstruct3D:
         k = C.c_int()
         self._check(self.lib.cvr_sor(self.ctx, _ptr(pts), len(pts), _ptr(out), len(out), C.byref(k)))
         return out[:k.value].copy()
+
+    def FilterCloud(self, cloud, stages=STAGE_VOXEL | STAGE_SOR):
+        """VoxelGrid and/or RemoveOutliers in one call (host arrays)."""
+        pts = np.ascontiguousarray(cloud, POINT_DTYPE)
+        out = np.empty(max(len(pts), 1), POINT_DTYPE)
+        m = C.c_int()
+        self._check(self.lib.cvr_filter_cloud(self.ctx, MEM_HOST, _ptr(pts), len(pts), int(stages), _ptr(out), len(out), C.byref(m)))
+        return out[:m.value].copy()
+
+    def filter_cloud_device(self, in_ptr, n, stages, out_ptr, capacity):
+        """cvr_filter_cloud on device pointers; returns the output count."""
+        m = C.c_int()
+        self._check(self.lib.cvr_filter_cloud(self.ctx, MEM_DEVICE, C.c_void_p(in_ptr), int(n), int(stages), C.c_void_p(out_ptr), int(capacity), C.byref(m)))
+        return m.value
 
     # -- pcl::RadiusOutlierRemoval::filter at MappingSystem.cpp:303-307 --
     def RadiusOutlierRemoval(self, cloud, radius=1.0, min_neighbors=300):

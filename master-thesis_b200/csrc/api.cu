@@ -519,6 +519,43 @@ extern "C" int cvr_sor(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, i
     return rc;
 }
 
+// VoxelGrid and/or StatisticalOutlierRemoval on one cloud in host OR device memory (the per-stage entry points above take host
+// pointers only): the MappingSystem call sites run on clouds that are already on the device when the path produced them.
+extern "C" int cvr_filter_cloud(cvr_ctx* c, int mem, const cvr_point* in, int n, int stages, cvr_point* out, int capacity, int* n_out)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    REQUIRE(c, n >= 0 && (n == 0 || (in && out)) && (stages & 12) != 0 && (mem == CVR_MEM_HOST || mem == CVR_MEM_DEVICE), "bad argument");
+    if (n > c->maxN) { c->err = "cloud larger than the context's point capacity (cvr_params.max_points)"; return CVR_ERR_CAPACITY; }
+    if (n_out) *n_out = 0;
+    if (n == 0) return CVR_OK;
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    timers_begin(c, 0);
+    const cudaMemcpyKind kin = mem == CVR_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    const cudaMemcpyKind kout = mem == CVR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+    const bool vox = (stages & 4) != 0, sor = (stages & 8) != 0;
+    cvr_point* first = vox ? c->d_cloud : c->d_vox;                     // the slab the first enabled stage reads
+    int* firstN = vox ? c->d_ncloud : c->d_nvox;
+    CVR_CUDA(c, cudaMemcpyAsync(first, in, (size_t)n * sizeof(cvr_point), kin, c->stream));
+    c->h_counts[1] = n;
+    CVR_CUDA(c, cudaMemcpyAsync(firstN, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
+    cvr_stage_mark(c, "in");
+    int rc;
+    const cvr_point* fin = first; const int* fcnt = firstN;
+    if (vox) { rc = cvr_launch_voxel(c, 1, c->d_cloud, (size_t)c->maxN, c->d_ncloud, false); if (rc) return rc; fin = c->d_vox; fcnt = c->d_nvox; }
+    if (sor) { rc = cvr_launch_sor(c, 1, fin, (size_t)c->maxN, fcnt, vox); if (rc) return rc; fin = c->d_sorout; fcnt = c->d_nout; }
+    CVR_CUDA(c, cudaMemcpyAsync(c->h_counts, fcnt, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    rc = sync_check(c);
+    if (rc) return rc;
+    const int m = c->h_counts[0];
+    if (n_out) *n_out = m;
+    if (m > capacity) { c->err = "output capacity too small for the cloud"; return CVR_ERR_CAPACITY; }
+    if (m > 0) CVR_CUDA(c, cudaMemcpyAsync(out, fin, (size_t)m * sizeof(cvr_point), kout, c->stream));
+    cvr_stage_mark(c, "out");
+    rc = sync_check(c);
+    timers_end(c, 0);
+    return rc;
+}
+
 extern "C" int cvr_radius_outlier_removal(cvr_ctx* c, const cvr_point* in, int n, float radius, int min_neighbors, cvr_point* out, int capacity, int* kept_out)
 {
     if (!c) return CVR_ERR_INVALID_ARG;
