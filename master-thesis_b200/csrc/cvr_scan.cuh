@@ -5,7 +5,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
-#define CVR_SEL_BLOCK 1024   // elements per block in the ordered-select passes
+#define CVR_SEL_BLOCK 1024   // elements per chunk of the ordered selections
+#define CVR_SEL_THREADS 256  // threads of a selection block ...
+#define CVR_SEL_ITEMS 4      // ... each owning this many consecutive elements of the chunk
 
 // Block-wide exclusive scan of one int per thread (blockDim.x multiple of 32, <= 1024).  Returns the exclusive
 // prefix; *total receives the block sum.  `ws` is >= 33 ints of shared memory.

@@ -281,8 +281,8 @@ __global__ void k_fill_int(int* p, int n, int v) { int i = blockIdx.x * blockDim
 // Surviving pixels in row-major order (the reference's push_back order) by the single-pass ordered selection of
 // cvr_scan.cuh; the kernel also accumulates the cloud's bounding box for the voxel grid that follows.
 template <int MODE, bool FUSED>
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_cloud_select(CloudArgs a, int* sel, size_t selStride, cvr_point* __restrict__ out, size_t outStride,
-                                                                int* __restrict__ nout, VoxBox* box, double factor)
+__global__ void __launch_bounds__(CVR_SEL_THREADS) k_cloud_select(CloudArgs a, int* sel, size_t selStride, cvr_point* __restrict__ out, size_t outStride,
+                                                                  int* __restrict__ nout, VoxBox* box, double factor)
 {
     __shared__ int ws[33];
     __shared__ int sh;
@@ -305,18 +305,26 @@ __global__ void __launch_bounds__(CVR_SEL_BLOCK) k_cloud_select(CloudArgs a, int
     for (;;) {
         const int chunk = sel_next_chunk(ticket, &sh);
         if (chunk >= nch) break;
-        const int i = chunk * CVR_SEL_BLOCK + threadIdx.x;
-        cvr_point pt;
-        const int f = (i < N) ? (int)make_point<MODE, FUSED>(a, b, i, pt, fa, fb, ithr) : 0;
-        int tot;
-        const int e = block_excl_scan(f, ws, &tot);
-        const int base = sel_chain_prefix(status, chunk, tot, &sh);
-        if (f) {
-            *(uint4*)(out + (size_t)b * outStride + base + e) = *(const uint4*)&pt;
-            const unsigned ox = f2ord(pt.x), oy = f2ord(pt.y), oz = f2ord(pt.z);
-            mn[0] = min(mn[0], ox); mx[0] = max(mx[0], ox); mn[1] = min(mn[1], oy); mx[1] = max(mx[1], oy); mn[2] = min(mn[2], oz); mx[2] = max(mx[2], oz);
-            any = true;
+        const int i0 = chunk * CVR_SEL_BLOCK + threadIdx.x * CVR_SEL_ITEMS;
+        cvr_point pt[CVR_SEL_ITEMS];
+        int f[CVR_SEL_ITEMS], cnt = 0;
+#pragma unroll
+        for (int k = 0; k < CVR_SEL_ITEMS; k++) {
+            f[k] = (i0 + k < N) ? (int)make_point<MODE, FUSED>(a, b, i0 + k, pt[k], fa, fb, ithr) : 0;
+            cnt += f[k];
         }
+        int tot;
+        const int e = block_excl_scan(cnt, ws, &tot);
+        const int base = sel_chain_prefix(status, chunk, tot, &sh);
+        cvr_point* o = out + (size_t)b * outStride + base + e;
+#pragma unroll
+        for (int k = 0; k < CVR_SEL_ITEMS; k++)
+            if (f[k]) {
+                *(uint4*)o = *(const uint4*)&pt[k]; o++;
+                const unsigned ox = f2ord(pt[k].x), oy = f2ord(pt[k].y), oz = f2ord(pt[k].z);
+                mn[0] = min(mn[0], ox); mx[0] = max(mx[0], ox); mn[1] = min(mn[1], oy); mx[1] = max(mx[1], oy); mn[2] = min(mn[2], oz); mx[2] = max(mx[2], oz);
+                any = true;
+            }
         if (chunk == nch - 1 && threadIdx.x == 0) nout[b] = base + tot;
     }
     if (box && __any_sync(0xffffffffu, any)) {
@@ -341,18 +349,18 @@ int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const f
     if (!fused) { const int rc0 = cvr_launch_chain_init(c, B, false, true, false); if (rc0) return rc0; }   // stand-alone call: nobody prepared the box
     CVR_CUDA(c, cudaMemsetAsync(sel, 0, (size_t)B * selStride * sizeof(int), c->stream));
     const int nch = cvr_div_up(N, CVR_SEL_BLOCK);
-    const dim3 g(cvr_frame_blocks(c, B, (size_t)nch, 1, 2), B);
+    const dim3 g(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B);
     const double factor = c->cl.sigma_factor;
     if (mode == CVR_CLOUD_REPROJECT) {
         k_fill_int<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_flags, B, 32767);
         LAUNCH_CHECK(c);
         k_min_s16<<<dim3(min(cvr_div_up(N, 256), 296), B), 256, 0, c->stream>>>(disp16, N, c->d_flags);
         LAUNCH_CHECK(c);
-        k_cloud_select<CVR_CLOUD_REPROJECT, false><<<g, CVR_SEL_BLOCK, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
+        k_cloud_select<CVR_CLOUD_REPROJECT, false><<<g, CVR_SEL_THREADS, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
     } else if (fused) {
-        k_cloud_select<CVR_CLOUD_TRIANGULATE, true><<<g, CVR_SEL_BLOCK, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
+        k_cloud_select<CVR_CLOUD_TRIANGULATE, true><<<g, CVR_SEL_THREADS, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
     } else {
-        k_cloud_select<CVR_CLOUD_TRIANGULATE, false><<<g, CVR_SEL_BLOCK, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
+        k_cloud_select<CVR_CLOUD_TRIANGULATE, false><<<g, CVR_SEL_THREADS, 0, c->stream>>>(a, sel, selStride, c->d_cloud, (size_t)c->maxN, c->d_ncloud, c->d_boxv, factor);
     }
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "cloud");

@@ -640,17 +640,21 @@ __device__ __forceinline__ void uf_union(int* L, int a, int b)
         else done = true;
     } while (!done);
 }
-// Run-based labelling: a pixel's first label is the start of its horizontal run (maximal stretch of valid pixels
-// whose neighbours differ by <= maxDiff), found with one ballot per 32 pixels; unions are then only needed between
-// vertically connected runs, once per run pair (at the first column of their overlap), and component sizes are
-// accumulated with one atomic per (warp, root) instead of one per pixel.
+// Run-based labelling.  A horizontal run is a maximal stretch of valid pixels whose neighbours differ by <= maxDiff; its
+// first pixel (the "start") represents it: label[start] = start, label[member] = start | CCL_MEMBER, and the run's length is
+// left in size[start] (no other entry of size[] is ever read).  Found with two ballots per 32 pixels.  Unions are then only
+// needed between vertically connected runs, once per run pair (at the first column of their overlap), and they only ever
+// relabel starts (roots are starts).  Component sizes are summed over RUNS -- one atomic per run that is not its
+// component's root -- instead of over pixels.
+#define CCL_MEMBER 0x40000000
 __global__ void __launch_bounds__(128) k_ccl_runs(const int16_t* __restrict__ img, int* __restrict__ label, int* __restrict__ size, int W, int H, int B,
                                                   int newVal, int maxDiff)
 {
     const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (row >= B * H) return;
     const size_t base = (size_t)row * W;
-    const int rowInFrame = row % H;
+    const int rowOff = (row % H) * W;
+    int* const sizeRow = size + base;
     int carry = -1;                                           // start of the run that reaches into this chunk
     int prevV = newVal;
     for (int x0 = 0; x0 < W; x0 += 32) {
@@ -660,10 +664,20 @@ __global__ void __launch_bounds__(128) k_ccl_runs(const int16_t* __restrict__ im
         if (lane == 0) left = prevV;
         const bool valid = v != newVal;
         const bool conn = valid && left != newVal && abs(v - left) <= maxDiff;       // connected to x-1 (false at x == 0: prevV starts as newVal)
-        const unsigned starts = __ballot_sync(0xffffffffu, valid && !conn);
+        const bool isStart = valid && !conn;
+        const unsigned starts = __ballot_sync(0xffffffffu, isStart);
+        const unsigned vmask = __ballot_sync(0xffffffffu, valid);
         const unsigned le = starts & (0xffffffffu >> (31 - lane));
         const int s = le ? x0 + 31 - __clz(le) : carry;
-        if (x < W) { label[base + x] = valid ? rowInFrame * W + s : -1; size[base + x] = 0; }
+        if (x < W) label[base + x] = !valid ? -1 : (isStart ? rowOff + x : ((rowOff + s) | CCL_MEMBER));
+        // the first member of a run inside this chunk counts the run's members here: up to the next start or invalid pixel
+        if (valid && (isStart || lane == 0)) {
+            const unsigned stops = (starts | ~vmask) & ~((2u << lane) - 1u);
+            const int cnt = (stops ? __ffs(stops) - 1 : 32) - lane;
+            if (isStart) sizeRow[x] = cnt;
+            else atomicAdd(&sizeRow[carry], cnt);                                     // continues a run begun in an earlier chunk (same warp: ordered)
+        }
+        __syncwarp();
         // the run continuing into the next chunk starts at the last start of this chunk, or is the carried one
         const int lastS = starts ? x0 + 31 - __clz(starts) : carry;
         carry = __shfl_sync(0xffffffffu, valid ? lastS : -1, 31);
@@ -684,27 +698,30 @@ __global__ void k_ccl_vmerge(const int16_t* __restrict__ img, int* label, int W,
         if (vl != newVal && ql != newVal && abs(v - vl) <= maxDiff && abs(q - ql) <= maxDiff && abs(vl - ql) <= maxDiff) return;
     }
     int* L = label + fo;
-    uf_union(L, L[i], L[i + W]);
+    uf_union(L, L[i] & ~CCL_MEMBER, L[i + W] & ~CCL_MEMBER);
 }
+// run starts that are not roots: add the run's length to the root's and point straight at it (roots stay fixed points,
+// so concurrent flattening is safe)
 __global__ void k_ccl_count(int* label, int* size, int N)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (i >= N) return;
     int* L = label + (size_t)b * N;
-    const bool act = i < N && L[i] >= 0;
-    const unsigned amask = __ballot_sync(0xffffffffu, act);
-    if (!act) return;
-    const int r = uf_find(L, L[i]);
-    L[i] = r;                       // roots stay fixed points, so concurrent flattening is safe
-    const unsigned peers = __match_any_sync(amask, r);
-    if ((peers & ((1u << (threadIdx.x & 31)) - 1)) == 0) atomicAdd(&size[(size_t)b * N + r], __popc(peers));
+    const int l = L[i];
+    if (l < 0 || (l & CCL_MEMBER) || l == i) return;          // invalid pixel, member of a run, or a root
+    const int r = uf_find(L, l);
+    L[i] = r;
+    atomicAdd(&size[(size_t)b * N + r], size[(size_t)b * N + i]);
 }
 __global__ void k_ccl_apply(int16_t* img, const int* __restrict__ label, const int* __restrict__ size, int N, int newVal, int maxSize)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
     if (i >= N) return;
-    const size_t o = (size_t)b * N + i;
-    const int l = label[o];
-    if (l >= 0 && size[(size_t)b * N + l] <= maxSize) img[o] = (int16_t)newVal;
+    const size_t o = (size_t)b * N;
+    const int l = label[o + i];
+    if (l < 0) return;
+    const int r = (l & CCL_MEMBER) ? label[o + (l & ~CCL_MEMBER)] : l;   // a start's label is its root after k_ccl_count
+    if (size[o + r] <= maxSize) img[o + i] = (int16_t)newVal;
 }
 
 __global__ void k_fill_s16(int16_t* p, size_t n, int v)

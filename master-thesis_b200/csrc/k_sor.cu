@@ -236,9 +236,9 @@ __global__ void __launch_bounds__(1024) k_sor_stats(const float* __restrict__ me
     }
 }
 // kept points (mean distance not above the threshold) in input order, by the single-pass ordered selection
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_select(const cvr_point* __restrict__ pts, size_t stride, const float* __restrict__ meand, size_t ptStride,
-                                                              const int* __restrict__ nPtr, SorStats* st, int* sel, size_t selStride,
-                                                              cvr_point* __restrict__ out, size_t outStride, int* __restrict__ nOut)
+__global__ void __launch_bounds__(CVR_SEL_THREADS) k_sor_select(const cvr_point* __restrict__ pts, size_t stride, const float* __restrict__ meand, size_t ptStride,
+                                                                const int* __restrict__ nPtr, SorStats* st, int* sel, size_t selStride,
+                                                                cvr_point* __restrict__ out, size_t outStride, int* __restrict__ nOut)
 {
     __shared__ int ws[33];
     __shared__ int sh;
@@ -247,15 +247,21 @@ __global__ void __launch_bounds__(CVR_SEL_BLOCK) k_sor_select(const cvr_point* _
     unsigned* status = (unsigned*)sel + (size_t)b * selStride;
     int* ticket = (int*)status + (selStride - 1);
     if (nch == 0) { if (blockIdx.x == 0 && threadIdx.x == 0) { nOut[b] = 0; st[b].kept = 0; } return; }
+    const float* md = meand + (size_t)b * ptStride;
+    const cvr_point* pin = pts + (size_t)b * stride;
     for (;;) {
         const int chunk = sel_next_chunk(ticket, &sh);
         if (chunk >= nch) break;
-        const int i = chunk * CVR_SEL_BLOCK + threadIdx.x;
-        const int f = (i < n) && !((double)meand[(size_t)b * ptStride + i] > thr);
+        const int i0 = chunk * CVR_SEL_BLOCK + threadIdx.x * CVR_SEL_ITEMS;
+        int f[CVR_SEL_ITEMS], cnt = 0;
+#pragma unroll
+        for (int j = 0; j < CVR_SEL_ITEMS; j++) { f[j] = (i0 + j < n) && !((double)md[i0 + j] > thr); cnt += f[j]; }
         int tot;
-        const int e = block_excl_scan(f, ws, &tot);
+        const int e = block_excl_scan(cnt, ws, &tot);
         const int base = sel_chain_prefix(status, chunk, tot, &sh);
-        if (f) *(uint4*)(out + (size_t)b * outStride + base + e) = *(const uint4*)(pts + (size_t)b * stride + i);
+        cvr_point* o = out + (size_t)b * outStride + base + e;
+#pragma unroll
+        for (int j = 0; j < CVR_SEL_ITEMS; j++) if (f[j]) { *(uint4*)o = *(const uint4*)(pin + i0 + j); o++; }
         if (chunk == nch - 1 && threadIdx.x == 0) { nOut[b] = base + tot; st[b].kept = base + tot; }
     }
 }
@@ -314,7 +320,7 @@ static int sor_select(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, 
     int* sel = c->d_sel + (size_t)2 * c->maxB * selStride;             // selection 2 of the chain
     CVR_CUDA(c, cudaMemsetAsync(sel, 0, (size_t)B * selStride * sizeof(int), c->stream));
     const int nch = cvr_div_up(maxN, CVR_SEL_BLOCK);
-    k_sor_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 2), B), CVR_SEL_BLOCK, 0, c->stream>>>(in, in_stride, c->d_meand, (size_t)maxN, n_in, c->d_sstats, sel, selStride,
+    k_sor_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B), CVR_SEL_THREADS, 0, c->stream>>>(in, in_stride, c->d_meand, (size_t)maxN, n_in, c->d_sstats, sel, selStride,
                                                                                                   c->d_sorout, (size_t)maxN, c->d_nout);
     LAUNCH_CHECK(c);
     return CVR_OK;

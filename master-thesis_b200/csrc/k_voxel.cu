@@ -130,8 +130,8 @@ __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_scatter(const uint32
 
 // ---- segments + centroids -------------------------------------------------------------------------
 // Segment heads of the sorted keys (first index of every voxel) by the single-pass ordered selection.
-__global__ void __launch_bounds__(CVR_SEL_BLOCK) k_seg_select(const uint32_t* __restrict__ keys, size_t kvStride, VoxelHdr* hdr, int* sel, size_t selStride,
-                                                              int* __restrict__ segstart, size_t segStride)
+__global__ void __launch_bounds__(CVR_SEL_THREADS) k_seg_select(const uint32_t* __restrict__ keys, size_t kvStride, VoxelHdr* hdr, int* sel, size_t selStride,
+                                                                int* __restrict__ segstart, size_t segStride)
 {
     __shared__ int ws[33];
     __shared__ int sh;
@@ -145,12 +145,22 @@ __global__ void __launch_bounds__(CVR_SEL_BLOCK) k_seg_select(const uint32_t* __
     for (;;) {
         const int chunk = sel_next_chunk(ticket, &sh);
         if (chunk >= nch) break;
-        const int i = chunk * CVR_SEL_BLOCK + threadIdx.x;
-        const int f = (i < n) && (pass || i == 0 || k[i] != k[i - 1]);
+        const int i0 = chunk * CVR_SEL_BLOCK + threadIdx.x * CVR_SEL_ITEMS;
+        int f[CVR_SEL_ITEMS], cnt = 0;
+        uint32_t prev = (i0 > 0 && i0 - 1 < n) ? k[i0 - 1] : 0u;
+#pragma unroll
+        for (int j = 0; j < CVR_SEL_ITEMS; j++) {
+            const int i = i0 + j;
+            const uint32_t cur = i < n ? k[i] : 0u;
+            f[j] = (i < n) && (pass || i == 0 || cur != prev);
+            prev = cur; cnt += f[j];
+        }
         int tot;
-        const int e = block_excl_scan(f, ws, &tot);
+        const int e = block_excl_scan(cnt, ws, &tot);
         const int base = sel_chain_prefix(status, chunk, tot, &sh);
-        if (f) ss[base + e] = i;
+        int* o = ss + base + e;
+#pragma unroll
+        for (int j = 0; j < CVR_SEL_ITEMS; j++) if (f[j]) *o++ = i0 + j;
         if (chunk == nch - 1 && threadIdx.x == 0) { ss[base + tot] = n; hdr[b].m = base + tot; }
     }
 }
@@ -242,7 +252,7 @@ int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, c
     int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, c->d_vhdr, &buf);
     if (rc) return rc;
     const int nch = cvr_div_up(maxN, CVR_SEL_BLOCK);
-    k_seg_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 2), B), CVR_SEL_BLOCK, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, sel, selStride,
+    k_seg_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B), CVR_SEL_THREADS, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, sel, selStride,
                                                                                                  c->d_segstart, (size_t)maxN + 1);
     LAUNCH_CHECK(c);
     k_vox_centroid<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 128, 8), B), 128, 0, c->stream>>>(in, in_stride, c->d_vals[buf], kvStride, c->d_vhdr, c->d_segstart,
