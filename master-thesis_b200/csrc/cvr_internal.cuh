@@ -181,6 +181,7 @@ struct cvr_ctx {
     bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)
     int pathv_active[3][17]; // concurrent clusters of the vertical path kernel per (CTA size, cluster size): 0 = not asked yet, -1 = cannot run
+    int path_h_variant;      // 3 = several rows per warp (default), 2 = one row per warp (CVR_PATH_H=2)
     int path_v_variant;      // 3 = point-to-point edge hand-over (default), 2 = per-row cluster barrier (CVR_PATH_KERNELS=v2)
 };
 
@@ -217,7 +218,7 @@ static inline size_t cvr_sel_stride(int maxItems) { return ((size_t)maxItems + 1
 static inline int cvr_frame_blocks(const cvr_ctx* c, int B, size_t maxItems, int itemsPerBlock, int blocksPerSM)
 {
     size_t need = (maxItems + (size_t)itemsPerBlock - 1) / (size_t)itemsPerBlock;
-    size_t share = ((size_t)c->sm_count * (size_t)blocksPerSM + (size_t)B - 1) / (size_t)B;
+    size_t share = ((size_t)c->sm_count * (size_t)blocksPerSM) / (size_t)B;      // rounded down: the whole grid is resident at once
     if (need < 1) need = 1;
     if (share < 1) share = 1;
     return (int)(need < share ? need : share);

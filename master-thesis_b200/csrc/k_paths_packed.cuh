@@ -785,3 +785,242 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
     }
     cluster.sync();                                                   // nobody exits while a neighbour may still write into its inbox
 }
+
+// ------------------------------------------------------------------------------------------------
+// k_path_h3: the horizontal path with SEVERAL ROWS PER WARP.
+// k_path_h2 gives a warp one row, a lane DPL disparities: at D = 128 the packed arithmetic of a column is a dozen
+// instructions while the warp-uniform rest (loop, addresses, prefetch, the minimum over the column, path_info, the scalar
+// half of winner-take-all) is ten times that -- the kernel is bound by instruction issue, not by HBM.  Here a group of LPR
+// lanes owns a row (Dp / LPR disparities per lane, 32 / LPR rows per warp), so that per-column overhead is shared by all
+// rows of the warp; minima are taken over the lane group with xor-shuffles.  Every lane prefetches exactly the C and S
+// words it will consume itself (cp.async into a per-warp ring, piece-major layout: conflict-free 16-byte accesses), so
+// cp.async.wait_group is the only synchronisation of the ring.  Arithmetic and regimes (fast / no-neighbour / general /
+// exact) are those of k_path_h2; a column takes the fast form only when every row of the warp may.
+template <int NWD, int LPR, bool HASPAD, bool NN>
+__device__ __forceinline__ unsigned colx_fast_pk(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int sub, int D, const PathK& k)
+{
+    unsigned mnp = 0x7fff7fffu;
+    if (NN) {
+#pragma unroll
+        for (int j = 0; j < NWD; j++) {
+            unsigned v = __vadd2(__viaddmin_s16x2(Lp[j], ndeltap, k.Z), c[j]);
+            if (HASPAD && (sub * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            L[j] = v;
+            mnp = __vmins2(mnp, v);
+        }
+    } else {
+        unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1, LPR);
+        unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1, LPR);
+        if (sub == 0) left = 0x7fff7fffu;
+        if (sub == LPR - 1) right = 0x7fff7fffu;
+#pragma unroll
+        for (int j = 0; j < NWD; j++) {
+            const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
+            const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
+            const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);
+            const unsigned t = __viaddmin_s16x2(n, k.P1p, Lp[j]);
+            unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, k.Z), c[j]);
+            if (HASPAD && (sub * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            L[j] = v;
+            mnp = __vmins2(mnp, v);
+        }
+    }
+    return mnp;
+}
+template <int NWD, int LPR, bool EXACT, bool HASPAD>
+__device__ __forceinline__ unsigned colx_general_pk(const unsigned (&Lp)[NWD], int delta, const unsigned (&c)[NWD], unsigned (&L)[NWD], int sub, int D, const PathK& k)
+{
+    unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1, LPR);
+    unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1, LPR);
+    if (sub == 0) left = 0x7fff7fffu;
+    if (sub == LPR - 1) right = 0x7fff7fffu;
+    const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768)), ndeltap = pk2(-delta);
+    unsigned mnp = 0x7fff7fffu;
+#pragma unroll
+    for (int j = 0; j < NWD; j++) {
+        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
+        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
+        unsigned v = path_cost2<EXACT>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
+        if (HASPAD && (sub * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+        L[j] = v;
+        mnp = __vmins2(mnp, v);
+    }
+    return mnp;
+}
+// minimum over the LPR lanes of a row group (every lane of the group receives it)
+template <int LPR>
+__device__ __forceinline__ int group_min(int v)
+{
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+#define CVR_H3_DEPTH 3          // columns in flight per warp
+#define CVR_H3_WARPS 4          // warps per CTA
+template <int NWD, int LPR, bool REVERSE, bool WTA, bool HASPAD, bool NN>
+__global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int2* __restrict__ aux, SgbmDev p, int B,
+                                                               int accumulate, int storeS, int* flags)
+{
+    constexpr int R = 32 / LPR;                                      // rows per warp
+    constexpr int PW = (NWD % 4 == 0) ? 4 : 2;                       // words per cp.async piece (16 or 8 bytes)
+    constexpr int NP = NWD / PW;                                     // pieces per lane and array
+    constexpr int SLOTW = 2 * NWD * 32;                              // words per ring slot: [array][piece][lane][PW]
+    __shared__ __align__(16) unsigned ringsm[CVR_H3_WARPS][CVR_H3_DEPTH][SLOTW];
+    const int wib = threadIdx.x >> 5;
+    int lane = threadIdx.x & 31;
+    const int wpf = (p.H + R - 1) / R;                               // warps per frame: the rows of a warp belong to one frame
+    const int gw = blockIdx.x * CVR_H3_WARPS + wib;
+    if (gw >= B * wpf) return;
+    const int b = gw / wpf;
+    const int sub = lane % LPR, rsel = lane / LPR;
+    const int y0 = (gw - b * wpf) * R + rsel;
+    const bool rowOn = y0 < p.H;                                     // a group past the last row shadows it (same loads, no stores)
+    const int y = rowOn ? y0 : p.H - 1;
+    const int W1 = p.W1, D = p.D;
+    int P2 = p.P2;
+    const long long colW = (long long)p.Dp / 2;                      // 32-bit words per column
+    const size_t rowBase = (((size_t)b * p.H + y) * W1) * colW + (size_t)sub * NWD;
+    const int dx = REVERSE ? -1 : 1;
+    const long long stepW = dx * colW;
+    const unsigned* Cp = (const unsigned*)C + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
+    unsigned* Sp = (unsigned*)S + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
+    int2* auxp = aux + ((size_t)b * p.H + y) * W1 + (REVERSE ? W1 - 1 : 0);
+    int* flagp = flags + b;
+    bool exact = *flagp != 0;
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s); k.Z = (unsigned)p.D >> 20; CVR_PIN(k.Z);
+    CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2); CVR_PIN(lane);
+    const int d0 = sub * NWD * 2;                                    // first disparity of this lane
+    unsigned Lp[NWD];
+#pragma unroll
+    for (int j = 0; j < NWD; j++) Lp[j] = ((sub * NWD + j) * 2 < D) ? 0u : 0x7fff7fffu;
+    unsigned iA, iB;
+    path_info<NN>(0, P2, iA, iB);                                    // the border column: minimum 0
+    unsigned* const ring = &ringsm[wib][0][0];
+    const unsigned ringBase = (unsigned)__cvta_generic_to_shared(ring) + (unsigned)lane * PW * 4u;
+    const unsigned* pfC = Cp;
+    const unsigned* pfS = Sp;
+    auto prefetch = [&](int slot) {
+#pragma unroll
+        for (int q = 0; q < NP; q++) {
+            const unsigned dst = ringBase + (unsigned)(slot * SLOTW + q * 32 * PW) * 4u;
+            if (PW == 4) {
+                cpa_16(dst, pfC + q * PW);
+                if (accumulate) cpa_16(dst + NP * 32 * PW * 4u, pfS + q * PW);
+            } else {
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(pfC + q * PW) : "memory");
+                if (accumulate) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + NP * 32 * PW * 4u), "l"(pfS + q * PW) : "memory");
+            }
+        }
+    };
+#pragma unroll
+    for (int i = 0; i < CVR_H3_DEPTH; i++) {
+        if (i < W1) prefetch(i);
+        cpa_commit();
+        pfC += stepW; pfS += stepW;
+    }
+    const int mul = 100 - p.uniq;
+    int slot = 0;
+    for (int step = 0; step < W1; step++) {
+        unsigned c[NWD], s[NWD], L[NWD];
+        cpa_wait<CVR_H3_DEPTH - 1>();                                 // this lane's own pieces of the oldest slot have landed
+        const unsigned* rs = ring + slot * SLOTW + lane * PW;
+#pragma unroll
+        for (int q = 0; q < NP; q++) {
+            if (PW == 4) { const uint4 a = *(const uint4*)(rs + q * 32 * PW); c[4 * q] = a.x; c[4 * q + 1] = a.y; c[4 * q + 2] = a.z; c[4 * q + 3] = a.w; }
+            else { const uint2 a = *(const uint2*)(rs + q * 32 * PW); c[2 * q] = a.x; c[2 * q + 1] = a.y; }
+        }
+        if (accumulate) {
+#pragma unroll
+            for (int q = 0; q < NP; q++) {
+                if (PW == 4) { const uint4 a = *(const uint4*)(rs + (NP + q) * 32 * PW); s[4 * q] = a.x; s[4 * q + 1] = a.y; s[4 * q + 2] = a.z; s[4 * q + 3] = a.w; }
+                else { const uint2 a = *(const uint2*)(rs + (NP + q) * 32 * PW); s[2 * q] = a.x; s[2 * q + 1] = a.y; }
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < NWD; j++) s[j] = 0u;
+        }
+        const bool fastCol = !exact && __all_sync(0xffffffffu, (int)iB >= 0);     // every row of the warp is in the fast regime
+        unsigned mnp;
+        if (fastCol) mnp = colx_fast_pk<NWD, LPR, HASPAD, NN>(Lp, iA, c, L, sub, D, k);
+        else if (!exact) mnp = colx_general_pk<NWD, LPR, false, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, sub, D, k);
+        else mnp = colx_general_pk<NWD, LPR, true, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, sub, D, k);
+        const int mn = group_min<LPR>(min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16));
+        path_info<NN>(mn, P2, iA, iB);
+        const bool anyNeg = __any_sync(0xffffffffu, mn < 0);
+        if (accumulate) {
+            if (fastCol && !anyNeg) acc_fast<NWD>(s, L);
+            else acc_exact<NWD>(s, L);
+        }
+        if (anyNeg) {                                                // negative path cost: later unsigned sums would be void -> exact from here on
+            exact = true;
+            if (mn < 0 && sub == 0) atomicOr(flagp, 2);
+        }
+#pragma unroll
+        for (int j = 0; j < NWD; j++) { Lp[j] = L[j]; if (!accumulate) s[j] = L[j]; }
+        if ((!WTA || storeS) && rowOn) {
+#pragma unroll
+            for (int q = 0; q < NP; q++) {
+                if (PW == 4) *(uint4*)(Sp + 4 * q) = make_uint4(s[4 * q], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
+                else *(uint2*)(Sp + 2 * q) = make_uint2(s[2 * q], s[2 * q + 1]);
+            }
+        }
+        if (WTA) {
+            // A.5 first half for the row of this lane group (as wta_column2)
+            int key = 0x7fffffff;
+#pragma unroll
+            for (int j = 0; j < NWD; j++)
+                if (!HASPAD || d0 + 2 * j < D) {
+                    key = min(key, (int)((s[j] << 16) | (unsigned)(d0 + 2 * j)));
+                    key = min(key, (int)((s[j] & 0xffff0000u) | (unsigned)(d0 + 2 * j + 1)));
+                }
+            key = group_min<LPR>(key);
+            const int minS = key >> 16, best = key & 0xffff;
+            const int lim = minS * 100;
+            const int rel = best - d0 + 1;                            // position i is within one of best iff (unsigned)(rel - i) < 3
+            bool bad = false;
+#pragma unroll
+            for (int j = 0; j < NWD; j++) {
+                if (!HASPAD || d0 + 2 * j < D) {
+                    const int v0 = lo16(s[j]), v1 = hi16(s[j]);
+                    bad |= (v0 * mul < lim) && ((unsigned)(rel - 2 * j) >= 3u);
+                    bad |= (v1 * mul < lim) && ((unsigned)(rel - 2 * j - 1) >= 3u);
+                }
+            }
+            // the updated S of the column goes back into the slot's S pieces (same conflict-free layout), where the leader lane of
+            // each row picks up S[best - 1] and S[best + 1]
+            unsigned* ws = ring + slot * SLOTW + (NP * 32 + lane) * PW;
+#pragma unroll
+            for (int q = 0; q < NP; q++) {
+                if (PW == 4) *(uint4*)(ws + q * 32 * PW) = make_uint4(s[4 * q], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
+                else *(uint2*)(ws + q * 32 * PW) = make_uint2(s[2 * q], s[2 * q + 1]);
+            }
+            __syncwarp();
+            const unsigned badMask = __ballot_sync(0xffffffffu, bad);
+            const unsigned grp = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << (rsel * LPR);
+            const bool reject = (badMask & grp) != 0u || minS == CVR_MAX_COST;
+            if (sub == 0 && rowOn) {
+                int2 a2 = make_int2(0x7fffffff, 0);
+                if (!reject) {
+                    unsigned ac = 0;
+                    if (0 < best && best < D - 1) {
+                        auto fetch = [&](int d) -> unsigned {         // S of disparity d of this row, from the slot
+                            const int w = d >> 1, so = w / NWD, j = w - so * NWD, q = j / PW, e = j - q * PW;
+                            const unsigned v = ring[slot * SLOTW + ((NP + q) * 32 + rsel * LPR + so) * PW + e];
+                            return (d & 1) ? (v >> 16) : (v & 0xffffu);
+                        };
+                        ac = (fetch(best - 1) << 16) | fetch(best + 1);
+                    }
+                    a2 = make_int2((int)(((unsigned)minS << 16) | (unsigned)best), (int)ac);
+                }
+                *auxp = a2;
+            }
+            __syncwarp();                                            // the slot is refilled below
+        }
+        if (step + CVR_H3_DEPTH < W1) prefetch(slot);                 // refill the slot just consumed (only this lane ever reads these pieces)
+        cpa_commit();
+        pfC += stepW; pfS += stepW;
+        Cp += stepW; Sp += stepW; auxp += dx;
+        slot = (slot + 1 == CVR_H3_DEPTH) ? 0 : slot + 1;
+    }
+}

@@ -701,27 +701,46 @@ __global__ void k_ccl_vmerge(const int16_t* __restrict__ img, int* label, int W,
     uf_union(L, L[i] & ~CCL_MEMBER, L[i + W] & ~CCL_MEMBER);
 }
 // run starts that are not roots: add the run's length to the root's and point straight at it (roots stay fixed points,
-// so concurrent flattening is safe)
-__global__ void k_ccl_count(int* label, int* size, int N)
+// so concurrent flattening is safe).  Both passes below walk the label array of the whole batch as one flat array, four
+// labels per thread (16-byte loads; the frame of an element is recovered by a division only where it is needed).
+__global__ void __launch_bounds__(256) k_ccl_count(int* label, int* size, int N, size_t total)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
-    if (i >= N) return;
-    int* L = label + (size_t)b * N;
-    const int l = L[i];
-    if (l < 0 || (l & CCL_MEMBER) || l == i) return;          // invalid pixel, member of a run, or a root
-    const int r = uf_find(L, l);
-    L[i] = r;
-    atomicAdd(&size[(size_t)b * N + r], size[(size_t)b * N + i]);
+    const size_t g0 = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
+    if (g0 >= total) return;
+    int l4[4] = { -1, -1, -1, -1 };
+    if (g0 + 3 < total) { const int4 q = *(const int4*)(label + g0); l4[0] = q.x; l4[1] = q.y; l4[2] = q.z; l4[3] = q.w; }
+    else for (int k = 0; g0 + k < total; k++) l4[k] = label[g0 + k];
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int l = l4[k];
+        if (l < 0 || (l & CCL_MEMBER)) continue;              // invalid pixel or member of a run
+        const size_t g = g0 + k, fo = (g / (size_t)N) * (size_t)N;
+        const int i = (int)(g - fo);
+        if (l == i) continue;                                 // a root
+        int* L = label + fo;
+        const int r = uf_find(L, l);
+        L[i] = r;
+        atomicAdd(&size[fo + r], size[fo + i]);
+    }
 }
-__global__ void k_ccl_apply(int16_t* img, const int* __restrict__ label, const int* __restrict__ size, int N, int newVal, int maxSize)
+__global__ void __launch_bounds__(256) k_ccl_apply(int16_t* img, const int* __restrict__ label, const int* __restrict__ size, int N, size_t total, int newVal, int maxSize)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
-    if (i >= N) return;
-    const size_t o = (size_t)b * N;
-    const int l = label[o + i];
-    if (l < 0) return;
-    const int r = (l & CCL_MEMBER) ? label[o + (l & ~CCL_MEMBER)] : l;   // a start's label is its root after k_ccl_count
-    if (size[o + r] <= maxSize) img[o + i] = (int16_t)newVal;
+    const size_t g0 = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
+    if (g0 >= total) return;
+    int l4[4] = { -1, -1, -1, -1 };
+    if (g0 + 3 < total) { const int4 q = *(const int4*)(label + g0); l4[0] = q.x; l4[1] = q.y; l4[2] = q.z; l4[3] = q.w; }
+    else for (int k = 0; g0 + k < total; k++) l4[k] = label[g0 + k];
+    if ((l4[0] & l4[1] & l4[2] & l4[3]) < 0 && l4[0] < 0 && l4[1] < 0 && l4[2] < 0 && l4[3] < 0) return;
+    size_t fo = (g0 / (size_t)N) * (size_t)N;
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int l = l4[k];
+        if (l < 0) continue;
+        const size_t g = g0 + k;
+        if (g >= fo + (size_t)N) fo += (size_t)N;             // the four elements straddle a frame boundary
+        const int r = (l & CCL_MEMBER) ? label[fo + (size_t)(l & ~CCL_MEMBER)] : l;   // a start's label is its root after k_ccl_count
+        if (size[fo + r] <= maxSize) img[g] = (int16_t)newVal;
+    }
 }
 
 __global__ void k_fill_s16(int16_t* p, size_t n, int v)
@@ -884,7 +903,16 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
         return CVR_OK;
     };
     auto launch_h = [&](bool rev, bool wta, int accumulate, int store) -> int {
-        if (packed) {
+        if (packed && c->path_h_variant == 3) {
+            // several rows per warp: 8 lanes per row up to 128 disparities, 16 lanes beyond (k_paths_packed.cuh)
+            constexpr int LPR = DPL <= 4 ? 8 : 16;
+            constexpr int NWD3 = DPL * 16 / LPR;
+            const int wpf = cvr_div_up(p.H, 32 / LPR);
+            const int blocks = cvr_div_up(B * wpf, CVR_H3_WARPS);
+            if (!rev) k_path_h3<NWD3, LPR, false, false, HASPAD, NN><<<blocks, CVR_H3_WARPS * 32, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl);
+            else if (wta) k_path_h3<NWD3, LPR, true, true, HASPAD, NN><<<blocks, CVR_H3_WARPS * 32, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl);
+            else k_path_h3<NWD3, LPR, true, false, HASPAD, NN><<<blocks, CVR_H3_WARPS * 32, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl);
+        } else if (packed) {
             if (!rev) k_path_h2<DPL, false, false, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
             else if (wta) k_path_h2<DPL, true, true, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
             else k_path_h2<DPL, true, false, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
@@ -926,9 +954,11 @@ int cvr_launch_speckle(cvr_ctx* c, int B, int newVal, int maxSize, int maxDiff)
     LAUNCH_CHECK(c);
     k_ccl_vmerge<<<dim3(cvr_div_up(W, 128), H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, W, H, newVal, maxDiff);
     LAUNCH_CHECK(c);
-    k_ccl_count<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_label, c->d_size, N);
+    const size_t total = (size_t)B * N;
+    const unsigned g4 = (unsigned)cvr_div_up_sz(total, 1024);
+    k_ccl_count<<<g4, 256, 0, c->stream>>>(c->d_label, c->d_size, N, total);
     LAUNCH_CHECK(c);
-    k_ccl_apply<<<dim3(cvr_div_up(N, 256), B), 256, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, N, newVal, maxSize);
+    k_ccl_apply<<<g4, 256, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, N, total, newVal, maxSize);
     LAUNCH_CHECK(c);
     return CVR_OK;
 }

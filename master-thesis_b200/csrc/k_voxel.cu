@@ -52,6 +52,13 @@ __global__ void k_vox_keys(const cvr_point* __restrict__ pts, size_t stride, con
 // run's elements with that digit.  Passes whose digit lies above the top bit of the largest possible key
 // (VoxelHdr::maxkey) only copy the pairs through, so the ping-pong order stays fixed without a host round trip.
 __device__ __forceinline__ bool rs_pass_needed(const VoxelHdr* hdr, int b, int shift) { return !hdr || ((unsigned)hdr[b].maxkey >> shift) != 0 || shift == 0; }
+// The needed passes are a prefix of the four (digits above the key range are all zero), every needed pass flips the
+// ping-pong buffer and a skipped one leaves the pairs in place: the sorted pairs of frame b are in buffer (#needed & 1).
+__device__ __forceinline__ int rs_result_buf(const VoxelHdr* hdr, int b)
+{
+    const unsigned mk = (unsigned)hdr[b].maxkey;
+    return (1 + (mk >> 8 ? 1 : 0) + (mk >> 16 ? 1 : 0) + (mk >> 24 ? 1 : 0)) & 1;
+}
 
 __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_hist(const uint32_t* __restrict__ keys, size_t kvStride, const int* __restrict__ nPtr,
                                                                  int nOff, int shift, int* __restrict__ hist, size_t histStride, int nRuns,
@@ -98,14 +105,10 @@ __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_scatter(const uint32
     const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t* kk = keys + (size_t)b * kvStride; const uint32_t* vv = vals + (size_t)b * kvStride;
     uint32_t* ok = okeys + (size_t)b * kvStride; uint32_t* ov = ovals + (size_t)b * kvStride;
-    const bool needed = rs_pass_needed(hdr, b, shift);
+    if (!rs_pass_needed(hdr, b, shift)) return;                        // the pairs stay where they are: see rs_result_buf
     for (int run = blockIdx.x * RS_BLOCK_WARPS + w; run < nRuns; run += gridDim.x * RS_BLOCK_WARPS) {
         const int beg = run * RS_WARP_ELEMS, end = min(beg + RS_WARP_ELEMS, n);
         if (beg >= end) break;
-        if (!needed) {                                                 // digit is 0 for every key: the pass is the identity
-            for (int i = beg + lane; i < end; i += 32) { ok[i] = kk[i]; ov[i] = vv[i]; }
-            continue;
-        }
         const int* h = hist + (size_t)b * histStride + (size_t)run * 256;
         for (int k = lane; k < 256; k += 32) base[w][k] = h[k];
         __syncwarp();
@@ -130,14 +133,14 @@ __global__ void __launch_bounds__(RS_BLOCK_WARPS * 32) k_rs_scatter(const uint32
 
 // ---- segments + centroids -------------------------------------------------------------------------
 // Segment heads of the sorted keys (first index of every voxel) by the single-pass ordered selection.
-__global__ void __launch_bounds__(CVR_SEL_THREADS) k_seg_select(const uint32_t* __restrict__ keys, size_t kvStride, VoxelHdr* hdr, int* sel, size_t selStride,
+__global__ void __launch_bounds__(CVR_SEL_THREADS) k_seg_select(const uint32_t* __restrict__ keys0, const uint32_t* __restrict__ keys1, size_t kvStride, VoxelHdr* hdr, int* sel, size_t selStride,
                                                                 int* __restrict__ segstart, size_t segStride)
 {
     __shared__ int ws[33];
     __shared__ int sh;
     const int b = blockIdx.y, n = hdr[b].n, nch = (n + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;
     const bool pass = hdr[b].passthrough != 0;
-    const uint32_t* k = keys + (size_t)b * kvStride;
+    const uint32_t* k = (rs_result_buf(hdr, b) ? keys1 : keys0) + (size_t)b * kvStride;
     int* ss = segstart + (size_t)b * segStride;
     unsigned* status = (unsigned*)sel + (size_t)b * selStride;
     int* ticket = (int*)status + (selStride - 1);
@@ -167,7 +170,7 @@ __global__ void __launch_bounds__(CVR_SEL_THREADS) k_seg_select(const uint32_t* 
 // One thread per voxel: PCL's CentroidPoint accumulates x,y,z and r,g,b,a as floats in member order, divides by
 // the count, truncates the colours.  Member order = ascending point index (stable sort), as in the oracle.
 // Also accumulates the bounding box of the centroids (the outlier filter that follows builds its search grid from it).
-__global__ void __launch_bounds__(128) k_vox_centroid(const cvr_point* __restrict__ pts, size_t stride, const uint32_t* __restrict__ vals, size_t kvStride,
+__global__ void __launch_bounds__(128) k_vox_centroid(const cvr_point* __restrict__ pts, size_t stride, const uint32_t* __restrict__ vals0, const uint32_t* __restrict__ vals1, size_t kvStride,
                                const VoxelHdr* __restrict__ hdr, const int* __restrict__ segstart, size_t segStride,
                                cvr_point* __restrict__ out, size_t outStride, int* __restrict__ mOut, VoxBox* box)
 {
@@ -176,7 +179,7 @@ __global__ void __launch_bounds__(128) k_vox_centroid(const cvr_point* __restric
     if (blockIdx.x == 0 && threadIdx.x == 0) mOut[b] = h.m;
     const cvr_point* p = pts + (size_t)b * stride;
     const int* ss = segstart + (size_t)b * segStride;
-    const uint32_t* v = vals + (size_t)b * kvStride;
+    const uint32_t* v = (rs_result_buf(hdr, b) ? vals1 : vals0) + (size_t)b * kvStride;
     unsigned mn[3] = { 0xffffffffu, 0xffffffffu, 0xffffffffu }, mx[3] = { 0, 0, 0 };
     bool any = false;
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < h.m; j += gridDim.x * blockDim.x) {
@@ -249,13 +252,13 @@ int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, c
     k_vox_keys<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B), 256, 0, c->stream>>>(in, in_stride, c->d_vhdr, lx, ly, lz, c->d_keys[0], c->d_vals[0], kvStride);
     LAUNCH_CHECK(c);
     int buf = 0;
-    int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, c->d_vhdr, &buf);
+    int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, c->d_vhdr, &buf);   // the result buffer is per frame: rs_result_buf
     if (rc) return rc;
     const int nch = cvr_div_up(maxN, CVR_SEL_BLOCK);
-    k_seg_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B), CVR_SEL_THREADS, 0, c->stream>>>(c->d_keys[buf], kvStride, c->d_vhdr, sel, selStride,
+    k_seg_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B), CVR_SEL_THREADS, 0, c->stream>>>(c->d_keys[0], c->d_keys[1], kvStride, c->d_vhdr, sel, selStride,
                                                                                                  c->d_segstart, (size_t)maxN + 1);
     LAUNCH_CHECK(c);
-    k_vox_centroid<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 128, 8), B), 128, 0, c->stream>>>(in, in_stride, c->d_vals[buf], kvStride, c->d_vhdr, c->d_segstart,
+    k_vox_centroid<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 128, 8), B), 128, 0, c->stream>>>(in, in_stride, c->d_vals[0], c->d_vals[1], kvStride, c->d_vhdr, c->d_segstart,
                                                                                                 (size_t)maxN + 1, c->d_vox, (size_t)maxN, c->d_nvox, c->d_boxs);
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "voxel");
