@@ -204,7 +204,8 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     fill_dev_params(c);
     c->smem_optin = (int)prop.sharedMemPerBlockOptin;
     { const char* e_ = getenv("CVR_PATH_KERNELS"); c->force_generic = e_ && strcmp(e_, "generic") == 0; c->path_v_variant = (e_ && strcmp(e_, "v2") == 0) ? 2 : 3;
-      const char* ph_ = getenv("CVR_PATH_H"); c->path_h_variant = (ph_ && atoi(ph_) == 2) ? 2 : 3;
+      const char* pf_ = getenv("CVR_PATH_H_FWD"); c->path_h_fwd = (pf_ && atoi(pf_) == 3) ? 3 : 2;   // -> : one row per warp already runs at the HBM rate
+      const char* pr_ = getenv("CVR_PATH_H_REV"); c->path_h_rev = (pr_ && atoi(pr_) == 2) ? 2 : 3;   // <- + WTA: several rows per warp
       const char* ks_ = getenv("CVR_KEEP_S"); c->keep_S = ks_ && atoi(ks_) != 0;
       const char* nn_ = getenv("CVR_NO_NN"); c->force_no_nn = nn_ && atoi(nn_) != 0;
       const char* n_ = getenv("CVR_PATHV_NT"); c->pathv_max_nt = n_ ? atoi(n_) : 1024; memset(c->pathv_active, 0, sizeof(c->pathv_active)); }

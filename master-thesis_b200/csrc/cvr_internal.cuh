@@ -181,7 +181,7 @@ struct cvr_ctx {
     bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)
     int pathv_active[3][17]; // concurrent clusters of the vertical path kernel per (CTA size, cluster size): 0 = not asked yet, -1 = cannot run
-    int path_h_variant;      // 3 = several rows per warp (default), 2 = one row per warp (CVR_PATH_H=2)
+    int path_h_fwd, path_h_rev;   // horizontal path kernel per direction: 3 = several rows per warp, 2 = one row per warp (CVR_PATH_H_FWD / _REV)
     int path_v_variant;      // 3 = point-to-point edge hand-over (default), 2 = per-row cluster barrier (CVR_PATH_KERNELS=v2)
 };
 

@@ -792,11 +792,40 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v3(const int16_t* __restrict__
 // instructions while the warp-uniform rest (loop, addresses, prefetch, the minimum over the column, path_info, the scalar
 // half of winner-take-all) is ten times that -- the kernel is bound by instruction issue, not by HBM.  Here a group of LPR
 // lanes owns a row (Dp / LPR disparities per lane, 32 / LPR rows per warp), so that per-column overhead is shared by all
-// rows of the warp; minima are taken over the lane group with xor-shuffles.  Every lane prefetches exactly the C and S
-// words it will consume itself (cp.async into a per-warp ring, piece-major layout: conflict-free 16-byte accesses), so
-// cp.async.wait_group is the only synchronisation of the ring.  Arithmetic and regimes (fast / no-neighbour / general /
-// exact) are those of k_path_h2; a column takes the fast form only when every row of the warp may.
-template <int NWD, int LPR, bool HASPAD, bool NN>
+// rows of the warp; minima are taken over the lane group with xor-shuffles.
+// Ownership is PIECE-INTERLEAVED: a column is cut into NP pieces of LPR * PW words; lane `sub` of the group owns words
+// [sub * PW, sub * PW + PW) of every piece.  One cp.async / one store instruction of the group then covers LPR * PW * 4
+// contiguous bytes (whole 32-byte sectors; a lane-contiguous split requested every sector twice and ran into the L2 read
+// bandwidth), and every lane prefetches exactly the words it consumes itself, so cp.async.wait_group is the only
+// synchronisation of the ring (layout [array][piece][lane][PW]: conflict-free 16-byte accesses).  Arithmetic and regimes
+// (fast / no-neighbour / general / exact) are those of k_path_h2; a column takes the fast form only when every row of
+// the warp may.
+template <int NWD, int LPR, int PW>
+__device__ __forceinline__ int h3_word(int sub, int j) { return (j / PW) * (LPR * PW) + sub * PW + (j % PW); }   // column word index of this lane's word j
+
+// neighbour words of the lane's words: lm1[j] = (L[2w-1], L[2w]), lp1[j] = (L[2w+1], L[2w+2]) as packed pairs
+template <int NWD, int LPR, int PW>
+__device__ __forceinline__ void h3_neighbours(const unsigned (&Lp)[NWD], int sub, unsigned (&lm1)[NWD], unsigned (&lp1)[NWD])
+{
+    constexpr int NP = NWD / PW;
+#pragma unroll
+    for (int q = 0; q < NP; q++) {
+        // word before this lane's first word of piece q: the last word of piece q of lane sub-1, or of piece q-1 of the last lane
+        unsigned up = __shfl_up_sync(0xffffffffu, Lp[q * PW + PW - 1], 1, LPR);
+        const unsigned wrapUp = q > 0 ? __shfl_sync(0xffffffffu, Lp[(q > 0 ? q - 1 : 0) * PW + PW - 1], LPR - 1, LPR) : 0x7fff7fffu;
+        if (sub == 0) up = wrapUp;
+        unsigned dn = __shfl_down_sync(0xffffffffu, Lp[q * PW], 1, LPR);
+        const unsigned wrapDn = q + 1 < NP ? __shfl_sync(0xffffffffu, Lp[(q + 1 < NP ? q + 1 : q) * PW], 0, LPR) : 0x7fff7fffu;
+        if (sub == LPR - 1) dn = wrapDn;
+#pragma unroll
+        for (int e = 0; e < PW; e++) {
+            const int j = q * PW + e;
+            lm1[j] = __byte_perm(e == 0 ? up : Lp[j - 1], Lp[j], 0x5432);
+            lp1[j] = __byte_perm(Lp[j], e == PW - 1 ? dn : Lp[j + 1], 0x5432);
+        }
+    }
+}
+template <int NWD, int LPR, int PW, bool HASPAD, bool NN>
 __device__ __forceinline__ unsigned colx_fast_pk(const unsigned (&Lp)[NWD], unsigned ndeltap, const unsigned (&c)[NWD], unsigned (&L)[NWD], int sub, int D, const PathK& k)
 {
     unsigned mnp = 0x7fff7fffu;
@@ -804,44 +833,36 @@ __device__ __forceinline__ unsigned colx_fast_pk(const unsigned (&Lp)[NWD], unsi
 #pragma unroll
         for (int j = 0; j < NWD; j++) {
             unsigned v = __vadd2(__viaddmin_s16x2(Lp[j], ndeltap, k.Z), c[j]);
-            if (HASPAD && (sub * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            if (HASPAD && h3_word<NWD, LPR, PW>(sub, j) * 2 >= D) v = 0x7fff7fffu;
             L[j] = v;
             mnp = __vmins2(mnp, v);
         }
     } else {
-        unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1, LPR);
-        unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1, LPR);
-        if (sub == 0) left = 0x7fff7fffu;
-        if (sub == LPR - 1) right = 0x7fff7fffu;
+        unsigned lm1[NWD], lp1[NWD];
+        h3_neighbours<NWD, LPR, PW>(Lp, sub, lm1, lp1);
 #pragma unroll
         for (int j = 0; j < NWD; j++) {
-            const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
-            const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
-            const unsigned n = __vimin3_s16x2(lm1, lp1, k.Qp);
+            const unsigned n = __vimin3_s16x2(lm1[j], lp1[j], k.Qp);
             const unsigned t = __viaddmin_s16x2(n, k.P1p, Lp[j]);
             unsigned v = __vadd2(__viaddmin_s16x2(t, ndeltap, k.Z), c[j]);
-            if (HASPAD && (sub * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+            if (HASPAD && h3_word<NWD, LPR, PW>(sub, j) * 2 >= D) v = 0x7fff7fffu;
             L[j] = v;
             mnp = __vmins2(mnp, v);
         }
     }
     return mnp;
 }
-template <int NWD, int LPR, bool EXACT, bool HASPAD>
+template <int NWD, int LPR, int PW, bool EXACT, bool HASPAD>
 __device__ __forceinline__ unsigned colx_general_pk(const unsigned (&Lp)[NWD], int delta, const unsigned (&c)[NWD], unsigned (&L)[NWD], int sub, int D, const PathK& k)
 {
-    unsigned left = __shfl_up_sync(0xffffffffu, Lp[NWD - 1], 1, LPR);
-    unsigned right = __shfl_down_sync(0xffffffffu, Lp[0], 1, LPR);
-    if (sub == 0) left = 0x7fff7fffu;
-    if (sub == LPR - 1) right = 0x7fff7fffu;
+    unsigned lm1[NWD], lp1[NWD];
+    h3_neighbours<NWD, LPR, PW>(Lp, sub, lm1, lp1);
     const unsigned deltap = pk2(delta), lop = pk2(max(delta - 32768, -32768)), ndeltap = pk2(-delta);
     unsigned mnp = 0x7fff7fffu;
 #pragma unroll
     for (int j = 0; j < NWD; j++) {
-        const unsigned lm1 = __byte_perm(j == 0 ? left : Lp[j - 1], Lp[j], 0x5432);
-        const unsigned lp1 = __byte_perm(Lp[j], j == NWD - 1 ? right : Lp[j + 1], 0x5432);
-        unsigned v = path_cost2<EXACT>(lm1, Lp[j], lp1, deltap, lop, ndeltap, k, c[j]);
-        if (HASPAD && (sub * NWD + j) * 2 >= D) v = 0x7fff7fffu;
+        unsigned v = path_cost2<EXACT>(lm1[j], Lp[j], lp1[j], deltap, lop, ndeltap, k, c[j]);
+        if (HASPAD && h3_word<NWD, LPR, PW>(sub, j) * 2 >= D) v = 0x7fff7fffu;
         L[j] = v;
         mnp = __vmins2(mnp, v);
     }
@@ -863,8 +884,9 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
                                                                int accumulate, int storeS, int* flags)
 {
     constexpr int R = 32 / LPR;                                      // rows per warp
-    constexpr int PW = (NWD % 4 == 0) ? 4 : 2;                       // words per cp.async piece (16 or 8 bytes)
-    constexpr int NP = NWD / PW;                                     // pieces per lane and array
+    constexpr int PW = (NWD % 4 == 0) ? 4 : 2;                       // words per piece (16- or 8-byte accesses)
+    constexpr int NP = NWD / PW;                                     // pieces per column
+    constexpr int PIECEW = LPR * PW;                                 // words per piece of a column
     constexpr int SLOTW = 2 * NWD * 32;                              // words per ring slot: [array][piece][lane][PW]
     __shared__ __align__(16) unsigned ringsm[CVR_H3_WARPS][CVR_H3_DEPTH][SLOTW];
     const int wib = threadIdx.x >> 5;
@@ -880,20 +902,19 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
     const int W1 = p.W1, D = p.D;
     int P2 = p.P2;
     const long long colW = (long long)p.Dp / 2;                      // 32-bit words per column
-    const size_t rowBase = (((size_t)b * p.H + y) * W1) * colW + (size_t)sub * NWD;
+    const size_t rowBase = (((size_t)b * p.H + y) * W1) * colW + (size_t)sub * PW;
     const int dx = REVERSE ? -1 : 1;
     const long long stepW = dx * colW;
-    const unsigned* Cp = (const unsigned*)C + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
+    const unsigned* Cp = (const unsigned*)C + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);   // this lane's words of piece 0 of the current column
     unsigned* Sp = (unsigned*)S + rowBase + (REVERSE ? (size_t)(W1 - 1) * colW : 0);
     int2* auxp = aux + ((size_t)b * p.H + y) * W1 + (REVERSE ? W1 - 1 : 0);
     int* flagp = flags + b;
     bool exact = *flagp != 0;
     PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s); k.Z = (unsigned)p.D >> 20; CVR_PIN(k.Z);
     CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2); CVR_PIN(lane);
-    const int d0 = sub * NWD * 2;                                    // first disparity of this lane
     unsigned Lp[NWD];
 #pragma unroll
-    for (int j = 0; j < NWD; j++) Lp[j] = ((sub * NWD + j) * 2 < D) ? 0u : 0x7fff7fffu;
+    for (int j = 0; j < NWD; j++) Lp[j] = (h3_word<NWD, LPR, PW>(sub, j) * 2 < D) ? 0u : 0x7fff7fffu;
     unsigned iA, iB;
     path_info<NN>(0, P2, iA, iB);                                    // the border column: minimum 0
     unsigned* const ring = &ringsm[wib][0][0];
@@ -905,11 +926,11 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
         for (int q = 0; q < NP; q++) {
             const unsigned dst = ringBase + (unsigned)(slot * SLOTW + q * 32 * PW) * 4u;
             if (PW == 4) {
-                cpa_16(dst, pfC + q * PW);
-                if (accumulate) cpa_16(dst + NP * 32 * PW * 4u, pfS + q * PW);
+                cpa_16(dst, pfC + q * PIECEW);
+                if (accumulate) cpa_16(dst + NP * 32 * PW * 4u, pfS + q * PIECEW);
             } else {
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(pfC + q * PW) : "memory");
-                if (accumulate) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + NP * 32 * PW * 4u), "l"(pfS + q * PW) : "memory");
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(pfC + q * PIECEW) : "memory");
+                if (accumulate) asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst + NP * 32 * PW * 4u), "l"(pfS + q * PIECEW) : "memory");
             }
         }
     };
@@ -942,9 +963,9 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
         }
         const bool fastCol = !exact && __all_sync(0xffffffffu, (int)iB >= 0);     // every row of the warp is in the fast regime
         unsigned mnp;
-        if (fastCol) mnp = colx_fast_pk<NWD, LPR, HASPAD, NN>(Lp, iA, c, L, sub, D, k);
-        else if (!exact) mnp = colx_general_pk<NWD, LPR, false, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, sub, D, k);
-        else mnp = colx_general_pk<NWD, LPR, true, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, sub, D, k);
+        if (fastCol) mnp = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp, iA, c, L, sub, D, k);
+        else if (!exact) mnp = colx_general_pk<NWD, LPR, PW, false, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, sub, D, k);
+        else mnp = colx_general_pk<NWD, LPR, PW, true, HASPAD>(Lp, (int)(short)(iB & 0xffffu), c, L, sub, D, k);
         const int mn = group_min<LPR>(min((int)(short)(mnp & 0xffffu), ((int)mnp) >> 16));
         path_info<NN>(mn, P2, iA, iB);
         const bool anyNeg = __any_sync(0xffffffffu, mn < 0);
@@ -961,30 +982,32 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
         if ((!WTA || storeS) && rowOn) {
 #pragma unroll
             for (int q = 0; q < NP; q++) {
-                if (PW == 4) *(uint4*)(Sp + 4 * q) = make_uint4(s[4 * q], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
-                else *(uint2*)(Sp + 2 * q) = make_uint2(s[2 * q], s[2 * q + 1]);
+                if (PW == 4) *(uint4*)(Sp + q * PIECEW) = make_uint4(s[4 * q], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
+                else *(uint2*)(Sp + q * PIECEW) = make_uint2(s[2 * q], s[2 * q + 1]);
             }
         }
         if (WTA) {
             // A.5 first half for the row of this lane group (as wta_column2)
             int key = 0x7fffffff;
 #pragma unroll
-            for (int j = 0; j < NWD; j++)
-                if (!HASPAD || d0 + 2 * j < D) {
-                    key = min(key, (int)((s[j] << 16) | (unsigned)(d0 + 2 * j)));
-                    key = min(key, (int)((s[j] & 0xffff0000u) | (unsigned)(d0 + 2 * j + 1)));
+            for (int j = 0; j < NWD; j++) {
+                const int d = h3_word<NWD, LPR, PW>(sub, j) * 2;
+                if (!HASPAD || d < D) {
+                    key = min(key, (int)((s[j] << 16) | (unsigned)d));
+                    key = min(key, (int)((s[j] & 0xffff0000u) | (unsigned)(d + 1)));
                 }
+            }
             key = group_min<LPR>(key);
             const int minS = key >> 16, best = key & 0xffff;
             const int lim = minS * 100;
-            const int rel = best - d0 + 1;                            // position i is within one of best iff (unsigned)(rel - i) < 3
             bool bad = false;
 #pragma unroll
             for (int j = 0; j < NWD; j++) {
-                if (!HASPAD || d0 + 2 * j < D) {
+                const int d = h3_word<NWD, LPR, PW>(sub, j) * 2;
+                if (!HASPAD || d < D) {
                     const int v0 = lo16(s[j]), v1 = hi16(s[j]);
-                    bad |= (v0 * mul < lim) && ((unsigned)(rel - 2 * j) >= 3u);
-                    bad |= (v1 * mul < lim) && ((unsigned)(rel - 2 * j - 1) >= 3u);
+                    bad |= (v0 * mul < lim) && ((unsigned)(best + 1 - d) >= 3u);     // |d - best| > 1
+                    bad |= (v1 * mul < lim) && ((unsigned)(best - d) >= 3u);         // |d + 1 - best| > 1
                 }
             }
             // the updated S of the column goes back into the slot's S pieces (same conflict-free layout), where the leader lane of
@@ -1005,7 +1028,7 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
                     unsigned ac = 0;
                     if (0 < best && best < D - 1) {
                         auto fetch = [&](int d) -> unsigned {         // S of disparity d of this row, from the slot
-                            const int w = d >> 1, so = w / NWD, j = w - so * NWD, q = j / PW, e = j - q * PW;
+                            const int w = d >> 1, q = w / PIECEW, r = w - q * PIECEW, so = r / PW, e = r - so * PW;
                             const unsigned v = ring[slot * SLOTW + ((NP + q) * 32 + rsel * LPR + so) * PW + e];
                             return (d & 1) ? (v >> 16) : (v & 0xffffu);
                         };

@@ -850,6 +850,50 @@ static cudaError_t launch_cluster(K kernel, int CL, int B, int NT, size_t smem, 
     return cudaLaunchKernelEx(&cfg, kernel, C, S, raw, aux, p, CL, storeS, flags, vs);
 }
 
+// A row of the horizontal path is one long sequential task, so a launch runs in waves of (resident CTAs) equal tasks and a
+// part-filled last wave costs as much as a full one (2.2 waves of 8 CTAs per SM run as 3).  Fewer resident CTAs per SM can
+// make the waves come out even at the same total throughput: pick the CTA count per SM (>= 4) that minimises
+// waves x CTAs-per-SM and enforce it with a dynamic shared-memory pad.  Returns the pad in bytes.
+template <typename K>
+static size_t wave_balanced_pad_query(cvr_ctx* c, K kernel, int threads, int nCTA, int forced);
+template <typename K>
+static size_t wave_balanced_pad(cvr_ctx* c, K kernel, int threads, int nCTA)
+{
+    static const int forced = getenv("CVR_H3_OCC") ? atoi(getenv("CVR_H3_OCC")) : 0;   // tuning hook: CTAs per SM
+    struct Memo { const void* k; int n; int dev; size_t pad; };
+    static std::vector<Memo> memo;                                     // (a context is driven by one thread; contexts of one process share the answers)
+    for (const Memo& m : memo) if (m.k == (const void*)kernel && m.n == nCTA && m.dev == c->device) return m.pad;
+    const size_t pad = wave_balanced_pad_query(c, kernel, threads, nCTA, forced);
+    memo.push_back(Memo{ (const void*)kernel, nCTA, c->device, pad });
+    return pad;
+}
+template <typename K>
+static size_t wave_balanced_pad_query(cvr_ctx* c, K kernel, int threads, int nCTA, int forced)
+{
+    int omax = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&omax, kernel, threads, 0) != cudaSuccess || omax < 1) { (void)cudaGetLastError(); return 0; }
+    int best = omax; long long bestCost = -1;
+    for (int o = omax; o >= (omax < 4 ? 1 : 4); o--) {
+        const long long waves = ((long long)nCTA + (long long)o * c->sm_count - 1) / ((long long)o * c->sm_count);
+        const long long cost = waves * o;
+        if (bestCost < 0 || cost < bestCost) { bestCost = cost; best = o; }
+    }
+    if (forced > 0 && forced <= omax) best = forced;
+    if (best >= omax) return 0;
+    cudaFuncAttributes fa;
+    if (cudaFuncGetAttributes(&fa, kernel) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+    size_t pad = 0;
+    for (int it = 0; it < 64; it++) {                                  // grow the pad until the occupancy query answers `best`
+        pad += 2048;
+        if (fa.sharedSizeBytes + pad > 48 * 1024 &&
+            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+        int o = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kernel, threads, pad) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+        if (o <= best) return o == best ? pad : (pad > 2048 ? pad - 2048 : 0);
+    }
+    return 0;
+}
+
 template <int DPL, bool HASPAD, bool NN>
 static int launch_paths(cvr_ctx* c, int B, int storeS)
 {
@@ -903,15 +947,19 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
         return CVR_OK;
     };
     auto launch_h = [&](bool rev, bool wta, int accumulate, int store) -> int {
-        if (packed && c->path_h_variant == 3) {
+        if (packed && (rev ? c->path_h_rev : c->path_h_fwd) == 3) {
             // several rows per warp: 8 lanes per row up to 128 disparities, 16 lanes beyond (k_paths_packed.cuh)
             constexpr int LPR = DPL <= 4 ? 8 : 16;
             constexpr int NWD3 = DPL * 16 / LPR;
             const int wpf = cvr_div_up(p.H, 32 / LPR);
             const int blocks = cvr_div_up(B * wpf, CVR_H3_WARPS);
-            if (!rev) k_path_h3<NWD3, LPR, false, false, HASPAD, NN><<<blocks, CVR_H3_WARPS * 32, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl);
-            else if (wta) k_path_h3<NWD3, LPR, true, true, HASPAD, NN><<<blocks, CVR_H3_WARPS * 32, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl);
-            else k_path_h3<NWD3, LPR, true, false, HASPAD, NN><<<blocks, CVR_H3_WARPS * 32, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl);
+            constexpr int NT3 = CVR_H3_WARPS * 32;
+            if (!rev) { const size_t pad = wave_balanced_pad(c, k_path_h3<NWD3, LPR, false, false, HASPAD, NN>, NT3, blocks);
+                        k_path_h3<NWD3, LPR, false, false, HASPAD, NN><<<blocks, NT3, pad, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl); }
+            else if (wta) { const size_t pad = wave_balanced_pad(c, k_path_h3<NWD3, LPR, true, true, HASPAD, NN>, NT3, blocks);
+                            k_path_h3<NWD3, LPR, true, true, HASPAD, NN><<<blocks, NT3, pad, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl); }
+            else { const size_t pad = wave_balanced_pad(c, k_path_h3<NWD3, LPR, true, false, HASPAD, NN>, NT3, blocks);
+                   k_path_h3<NWD3, LPR, true, false, HASPAD, NN><<<blocks, NT3, pad, c->stream>>>(c->d_volC, c->d_volA, c->d_aux, p, B, accumulate, store, fl); }
         } else if (packed) {
             if (!rev) k_path_h2<DPL, false, false, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
             else if (wta) k_path_h2<DPL, true, true, HASPAD, NN><<<hblocks, 128, 0, c->stream>>>(c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, B, accumulate, store, fl);
