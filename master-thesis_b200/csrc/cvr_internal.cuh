@@ -182,7 +182,8 @@ struct cvr_ctx {
     int pathv_max_nt;        // CVR_PATHV_NT: upper bound on threads per CTA of the vertical path kernel (tuning hook)
     int pathv_active[3][17]; // concurrent clusters of the vertical path kernel per (CTA size, cluster size): 0 = not asked yet, -1 = cannot run
     int path_h_fwd, path_h_rev;   // horizontal path kernel per direction: 3 = several rows per warp, 2 = one row per warp (CVR_PATH_H_FWD / _REV)
-    int path_v_variant;      // 3 = point-to-point edge hand-over (default), 2 = per-row cluster barrier (CVR_PATH_KERNELS=v2)
+    int pathv4_active[17];   // the same for k_path_v4 (512-thread CTAs) per cluster size
+    int path_v_variant;      // 4 = several columns per warp (default), 3 = one column per warp (CVR_PATH_KERNELS=v3), 2 = per-row cluster barrier (=v2)
 };
 
 #define CVR_CUDA(ctx, call)                                                                       \

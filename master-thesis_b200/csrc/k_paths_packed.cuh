@@ -1047,3 +1047,306 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
         slot = (slot + 1 == CVR_H3_DEPTH) ? 0 : slot + 1;
     }
 }
+
+// ------------------------------------------------------------------------------------------------
+// k_path_v4: the vertical / diagonal paths with SEVERAL COLUMNS PER WARP.
+// Same cluster-per-frame organisation, shared-memory row state, inboxes and st.async / mbarrier edge hand-over as
+// k_path_v3.  The columns of a row do not depend on each other (all three paths read the PREVIOUS row), so a warp can work
+// on G = 32 / LPR adjacent columns of its chunk at once: a group of LPR lanes owns a column (Dp / LPR disparities per
+// lane, piece-interleaved like k_path_h3 so that every global access of a group covers whole sectors).  The warp-uniform
+// part of a column step (loop, addresses, the minima over the column, path_info, edge logic) -- two thirds of
+// k_path_v3's instructions at D = 128 -- is then shared by G columns.  The state is still updated in place: a step first
+// reads everything it needs (old blocks of columns x-1 .. x+G), then writes the G new columns; only the down-right
+// block of the step's last column is needed again by the next step (its first column's source) and is carried in the
+// registers of group 0.  512 threads per CTA (the register budget of 40 packed words of state per lane).
+template <int NWD, int LPR, int PW, bool HASPAD>
+__device__ __forceinline__ void group_wta(const unsigned (&s)[NWD], int sub, int grp, int D, int uniq, bool on, int2* auxPix)
+{
+    constexpr int PIECEW = LPR * PW;
+    int key = 0x7fffffff;
+#pragma unroll
+    for (int j = 0; j < NWD; j++) {
+        const int d = h3_word<NWD, LPR, PW>(sub, j) * 2;
+        if (!HASPAD || d < D) {
+            key = min(key, (int)((s[j] << 16) | (unsigned)d));
+            key = min(key, (int)((s[j] & 0xffff0000u) | (unsigned)(d + 1)));
+        }
+    }
+    key = group_min<LPR>(key);
+    const int minS = key >> 16, best = key & 0xffff;
+    const int lim = minS * 100, mul = 100 - uniq;
+    bool bad = false;
+#pragma unroll
+    for (int j = 0; j < NWD; j++) {
+        const int d = h3_word<NWD, LPR, PW>(sub, j) * 2;
+        if (!HASPAD || d < D) {
+            const int v0 = lo16(s[j]), v1 = hi16(s[j]);
+            bad |= (v0 * mul < lim) && ((unsigned)(best + 1 - d) >= 3u);
+            bad |= (v1 * mul < lim) && ((unsigned)(best - d) >= 3u);
+        }
+    }
+    const unsigned badMask = __ballot_sync(0xffffffffu, bad);
+    const unsigned gm = (LPR == 32 ? 0xffffffffu : ((1u << LPR) - 1u)) << (grp * LPR);
+    const bool reject = (badMask & gm) != 0u || minS == CVR_MAX_COST;
+    // S[best - 1], S[best + 1] from their owner lanes (every lane takes part in the shuffles)
+    const bool inner = 0 < best && best < D - 1;
+    unsigned va = 0, vc = 0;
+    {
+        const int da = inner ? best - 1 : 0, dc = inner ? best + 1 : 0;
+        const int wa = da >> 1, wc = dc >> 1;
+        const int qa = wa / PIECEW, ra = wa - qa * PIECEW, soa = ra / PW, ja = qa * PW + (ra - soa * PW);
+        const int qc = wc / PIECEW, rc = wc - qc * PIECEW, soc = rc / PW, jc = qc * PW + (rc - soc * PW);
+        unsigned ma = s[0], mc = s[0];
+#pragma unroll
+        for (int j = 1; j < NWD; j++) { if (ja == j) ma = s[j]; if (jc == j) mc = s[j]; }
+        ma = __shfl_sync(0xffffffffu, ma, grp * LPR + soa);
+        mc = __shfl_sync(0xffffffffu, mc, grp * LPR + soc);
+        va = (da & 1) ? (ma >> 16) : (ma & 0xffffu);
+        vc = (dc & 1) ? (mc >> 16) : (mc & 0xffffu);
+    }
+    if (sub == 0 && on) {
+        int2 a2 = make_int2(0x7fffffff, 0);
+        if (!reject) a2 = make_int2((int)(((unsigned)minS << 16) | (unsigned)best), inner ? (int)((va << 16) | vc) : 0);
+        *auxPix = a2;
+    }
+}
+// packed 16-bit minimum over the lanes of a group, both halves at once
+template <int LPR>
+__device__ __forceinline__ unsigned group_min2(unsigned v)
+{
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) v = __vmins2(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+template <int NWD, int LPR, bool UP, bool WTA, bool HASPAD, bool NN>
+__global__ void __launch_bounds__(512, 1) k_path_v4(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
+                                                    int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
+{
+    (void)raw;
+    constexpr int G = 32 / LPR;                                       // columns per step
+    constexpr int PW = (NWD % 4 == 0) ? 4 : 2, NP = NWD / PW, PIECEW = LPR * PW;
+    constexpr int dwords = NWD * LPR;                                 // Dp / 2 words per direction per column
+    constexpr int blk = dwords + 4;                                   // costs, A, B (path_info), 2 pad words
+    constexpr int colWords = 3 * blk;
+    const int NT = blockDim.x, NW = NT / 32;
+    extern __shared__ uint4 smv4[];
+    cg::cluster_group cluster = cg::this_cluster();
+    const int b = blockIdx.y, rank = blockIdx.x;
+    const int W1 = p.W1, D = p.D, H = p.H;
+    int P2 = p.P2;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int sub = lane % LPR, g = lane / LPR;
+    const int GW = CL * NW, gw = rank * NW + warp;
+    const int ctaFirst = (int)(((long long)W1 * (rank * NW)) / GW);
+    const int a = (int)(((long long)W1 * gw) / GW), e = (int)(((long long)W1 * (gw + 1)) / GW);
+    unsigned* const state = (unsigned*)smv4;                          // [colsMax][3 directions][blk]
+    unsigned* const inbox = state + (size_t)vs.colsMax * colWords;    // [2 parity][NW][2 sides][blk]
+    const size_t parityStride = (size_t)NW * 2 * blk;
+    unsigned long long* bars = (unsigned long long*)(inbox + 2 * parityStride);
+    {
+        unsigned A0, B0;
+        path_info<NN>(0, P2, A0, B0);                                 // the zero state: all costs 0 (padding: MAX_COST), minimum 0
+        const int nwords = (vs.colsMax * 3 + 2 * NW * 2) * blk;       // state and inboxes are one run of blocks
+        for (int i = threadIdx.x; i < nwords; i += NT) {
+            const int w = i % blk;
+            state[i] = (w < dwords) ? ((w * 2 < D) ? 0u : 0x7fff7fffu) : (w == dwords ? A0 : (w == dwords + 1 ? B0 : 0u));
+        }
+    }
+    if (threadIdx.x < 2 * NW * 2) mbar_init(smem_u32(bars + threadIdx.x), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    bool exact = flags[b] != 0;
+    PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s); k.Z = (unsigned)p.D >> 20; CVR_PIN(k.Z);
+    CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
+    constexpr size_t colW = (size_t)dwords;
+    const unsigned edgeBytes = (unsigned)dwords * 4u + 8u;             // a block's costs + A + B
+    const unsigned* myInL = inbox + ((size_t)warp * 2 + 0) * blk;
+    const unsigned* myInR = inbox + ((size_t)warp * 2 + 1) * blk;
+    const unsigned myBarL = smem_u32(bars + (size_t)warp * 2 + 0), myBarR = smem_u32(bars + (size_t)warp * 2 + 1);
+    const unsigned barParityStride = (unsigned)(NW * 2 * 8), inboxParityBytes = (unsigned)(parityStride * 4);
+    const bool hasL = gw > 0, hasR = gw + 1 < GW;
+    unsigned pushR_data = 0, pushR_bar = 0, pushL_data = 0, pushL_bar = 0;
+    if (hasR) {
+        const int r2 = (gw + 1) / NW, w2 = (gw + 1) % NW;
+        pushR_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 0) * blk), r2);
+        pushR_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 0), r2);
+    }
+    if (hasL) {
+        const int r2 = (gw - 1) / NW, w2 = (gw - 1) % NW;
+        pushL_data = mapa_u32(smem_u32(inbox + ((size_t)w2 * 2 + 1) * blk), r2);
+        pushL_bar = mapa_u32(smem_u32(bars + (size_t)w2 * 2 + 1), r2);
+    }
+    unsigned* const colBase0 = state + (size_t)(a - ctaFirst) * colWords;
+    cluster.sync();                                                   // state, inboxes and barriers of every CTA are initialised
+
+    const int ncols = e - a;
+    const size_t frameRow0 = (size_t)b * H;
+    const long long nextRow = (UP ? -1LL : 1LL) * (long long)W1 * (long long)colW;
+    // this lane's words of piece 0 of column a in the current row
+    const size_t rb0 = ((frameRow0 + (UP ? H - 1 : 0)) * W1 + a) * colW + (size_t)sub * PW;
+    const unsigned* rowC = (const unsigned*)C + rb0;
+    unsigned* rowS = (unsigned*)S + rb0;
+    const int lw = sub * PW;                                          // this lane's word offset inside a piece
+    auto ldblk = [&](const unsigned* blkp, unsigned (&v)[NWD]) {      // this lane's words of a block in shared memory
+#pragma unroll
+        for (int q = 0; q < NP; q++) {
+            if (PW == 4) { const uint4 t4 = *(const uint4*)(blkp + q * PIECEW + lw); v[4 * q] = t4.x; v[4 * q + 1] = t4.y; v[4 * q + 2] = t4.z; v[4 * q + 3] = t4.w; }
+            else { const uint2 t2 = *(const uint2*)(blkp + q * PIECEW + lw); v[2 * q] = t2.x; v[2 * q + 1] = t2.y; }
+        }
+    };
+    auto stblk = [&](unsigned* blkp, const unsigned (&v)[NWD]) {
+#pragma unroll
+        for (int q = 0; q < NP; q++) {
+            if (PW == 4) *(uint4*)(blkp + q * PIECEW + lw) = make_uint4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+            else *(uint2*)(blkp + q * PIECEW + lw) = make_uint2(v[2 * q], v[2 * q + 1]);
+        }
+    };
+    auto ldg = [&](const unsigned* gp, unsigned (&v)[NWD]) {          // this lane's words of a column in global memory
+#pragma unroll
+        for (int q = 0; q < NP; q++) {
+            if (PW == 4) { const uint4 t4 = *(const uint4*)(gp + q * PIECEW); v[4 * q] = t4.x; v[4 * q + 1] = t4.y; v[4 * q + 2] = t4.z; v[4 * q + 3] = t4.w; }
+            else { const uint2 t2 = *(const uint2*)(gp + q * PIECEW); v[2 * q] = t2.x; v[2 * q + 1] = t2.y; }
+        }
+    };
+    // the first step's C and S words (column a + g, clamped into the chunk for groups past its end)
+    unsigned cN[NWD], sN[NWD];
+    {
+        const int c0 = min(g, ncols - 1);
+        ldg(rowC + (size_t)c0 * colW, cN);
+        ldg(rowS + (size_t)c0 * colW, sN);
+    }
+    for (int t = 0; t < H; t++, rowC += nextRow, rowS += nextRow) {
+        const int y = UP ? H - 1 - t : t;
+        const int rd = (t + 1) & 1, wr = t & 1;
+        const bool moreRows = t + 1 < H;
+        if (t > 0) {                                                   // previous row's edges of both neighbours
+            const unsigned waitPhase = (unsigned)(((t - 1) >> 1) & 1);
+            if (lane == 0) {
+                if (hasL) mbar_arrive_expect_tx(myBarL + rd * barParityStride, edgeBytes);
+                if (hasR) mbar_arrive_expect_tx(myBarR + rd * barParityStride, edgeBytes);
+            }
+            __syncwarp();                                              // also: the blocks and info words written in the previous row
+            if (hasL) mbar_wait(myBarL + rd * barParityStride, waitPhase);
+            if (hasR) mbar_wait(myBarR + rd * barParityStride, waitPhase);
+        }
+        const unsigned* inL = myInL + rd * parityStride;               // filled by the neighbours in the previous row; this row's
+        const unsigned* inR = myInR + rd * parityStride;               // pushes go to the other parity
+        const unsigned pL_dst = pushL_data + wr * inboxParityBytes, pL_bar = pushL_bar + wr * barParityStride;
+        const unsigned pR_dst = pushR_data + wr * inboxParityBytes, pR_bar = pushR_bar + wr * barParityStride;
+        unsigned carry[NWD];                                           // group 0: old down-right block of the column left of this step
+        uint2 carryI;
+        ldblk(inL, carry);
+        carryI = *(const uint2*)(inL + dwords);
+        for (int ci = 0; ci < ncols; ci += G) {
+            const int col = ci + g;
+            const bool on = col < ncols;
+            const int cc = on ? col : ncols - 1;                       // groups past the chunk's end shadow its last column (no stores)
+            unsigned* const cb = colBase0 + (size_t)cc * colWords;
+            unsigned c[NWD], s[NWD];
+#pragma unroll
+            for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = sN[j]; }
+            // ---- prefetch: the next step of this row, or the first step of the next row ----
+            {
+                const bool lastStep = ci + G >= ncols;
+                const int nc = lastStep ? min(g, ncols - 1) : min(col + G, ncols - 1);
+                const unsigned* nC = (lastStep ? rowC + nextRow : rowC) + (size_t)nc * colW;
+                const unsigned* nS = (lastStep ? rowS + nextRow : rowS) + (size_t)nc * colW;
+                if (!lastStep || moreRows) { ldg(nC, cN); ldg(nS, sN); }
+            }
+            // ---- sources: everything is read before any block of this step is overwritten ----
+            unsigned Lp1[NWD], Lp2[NWD], Lp3[NWD];
+            uint2 i1, i2, i3;
+            if (g == 0) {
+#pragma unroll
+                for (int j = 0; j < NWD; j++) Lp1[j] = carry[j];
+                i1 = carryI;
+            } else {
+                const unsigned* src1 = colBase0 + (size_t)(cc > 0 ? cc - 1 : 0) * colWords;     // old down-right block of column x-1
+                ldblk(src1, Lp1);
+                i1 = *(const uint2*)(src1 + dwords);
+            }
+            ldblk(cb + blk, Lp2);
+            i2 = *(const uint2*)(cb + blk + dwords);
+            const unsigned* src3 = (cc + 1 < ncols) ? cb + colWords + 2 * blk : inR;
+            ldblk(src3, Lp3);
+            i3 = *(const uint2*)(src3 + dwords);
+            if (g == 0 && ci + G < ncols) {                            // the next step's first column reads the old down-right block of this step's last
+                const unsigned* nx = colBase0 + (size_t)(ci + G - 1) * colWords;
+                ldblk(nx, carry);
+                carryI = *(const uint2*)(nx + dwords);
+            }
+            __syncwarp();                                              // all reads of the step precede its writes
+            unsigned L1[NWD], L2[NWD], L3[NWD];
+            int mn1, mn2, mn3;
+            const bool fast = !exact && __all_sync(0xffffffffu, (int)(i1.y | i2.y | i3.y) >= 0);
+            if (fast) {
+                const unsigned q1 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp1, i1.x, c, L1, sub, D, k);
+                const unsigned q2 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp2, i2.x, c, L2, sub, D, k);
+                const unsigned q3 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp3, i3.x, c, L3, sub, D, k);
+                // lane minima of two directions side by side, reduced over the group as packed pairs
+                const unsigned z12 = group_min2<LPR>(__vmins2(__byte_perm(q1, q2, 0x5410), __byte_perm(q1, q2, 0x7632)));   // (min1 | min2 << 16)
+                const unsigned z3 = group_min2<LPR>(__vmins2(q3, __byte_perm(q3, q3, 0x1032)));                              // min3 in both halves
+                mn1 = (int)(short)(z12 & 0xffffu); mn2 = (int)z12 >> 16; mn3 = (int)z3 >> 16;
+            } else {
+                const int d1 = (int)(short)(i1.y & 0xffffu), d2 = (int)(short)(i2.y & 0xffffu), d3 = (int)(short)(i3.y & 0xffffu);
+                unsigned q1, q2, q3;
+                if (!exact) {
+                    q1 = colx_general_pk<NWD, LPR, PW, false, HASPAD>(Lp1, d1, c, L1, sub, D, k);
+                    q2 = colx_general_pk<NWD, LPR, PW, false, HASPAD>(Lp2, d2, c, L2, sub, D, k);
+                    q3 = colx_general_pk<NWD, LPR, PW, false, HASPAD>(Lp3, d3, c, L3, sub, D, k);
+                } else {
+                    q1 = colx_general_pk<NWD, LPR, PW, true, HASPAD>(Lp1, d1, c, L1, sub, D, k);
+                    q2 = colx_general_pk<NWD, LPR, PW, true, HASPAD>(Lp2, d2, c, L2, sub, D, k);
+                    q3 = colx_general_pk<NWD, LPR, PW, true, HASPAD>(Lp3, d3, c, L3, sub, D, k);
+                }
+                const unsigned z12 = group_min2<LPR>(__vmins2(__byte_perm(q1, q2, 0x5410), __byte_perm(q1, q2, 0x7632)));
+                const unsigned z3 = group_min2<LPR>(__vmins2(q3, __byte_perm(q3, q3, 0x1032)));
+                mn1 = (int)(short)(z12 & 0xffffu); mn2 = (int)z12 >> 16; mn3 = (int)z3 >> 16;
+            }
+            const bool anyNeg = __any_sync(0xffffffffu, (mn1 | mn2 | mn3) < 0);
+            if (fast && !anyNeg) { acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3); }
+            else { acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3); }       // valid for any signs
+            if (anyNeg && !exact) {                                    // a negative path cost: unsigned sums are void, stay exact from here on
+                exact = true;
+                if (lane == 0) atomicOr(&flags[b], 2);
+            }
+            // ---- stores of the finished columns ----
+            unsigned iA1, iB1, iA3, iB3;
+            path_info<NN>(mn1, P2, iA1, iB1);
+            path_info<NN>(mn3, P2, iA3, iB3);
+            if (on) {
+                stblk(cb, L1); stblk(cb + blk, L2); stblk(cb + 2 * blk, L3);
+                if (sub == 0) *(uint2*)(cb + dwords) = make_uint2(iA1, iB1);
+                if (sub == 1) { unsigned iA2, iB2; path_info<NN>(mn2, P2, iA2, iB2); *(uint2*)(cb + blk + dwords) = make_uint2(iA2, iB2); }
+                if (sub == 2) *(uint2*)(cb + 2 * blk + dwords) = make_uint2(iA3, iB3);
+                // the last row's edges have no consumer: not pushed (no st.async may be in flight towards a CTA that has left)
+                if (col == 0 && hasL && moreRows) {                    // my first column's down-left block -> left neighbour's right inbox
+#pragma unroll
+                    for (int q = 0; q < NP; q++) {
+                        if (PW == 4) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(pL_dst + (q * PIECEW + lw) * 4), "r"(L3[4 * q]), "r"(L3[4 * q + 1]), "r"(L3[4 * q + 2]), "r"(L3[4 * q + 3]), "r"(pL_bar) : "memory");
+                        else st_async_v2(pL_dst + (q * PIECEW + lw) * 4, L3[2 * q], L3[2 * q + 1], pL_bar);
+                    }
+                    if (sub == 2) st_async_v2(pL_dst + dwords * 4, iA3, iB3, pL_bar);
+                }
+                if (col == ncols - 1 && hasR && moreRows) {            // my last column's down-right block -> right neighbour's left inbox
+#pragma unroll
+                    for (int q = 0; q < NP; q++) {
+                        if (PW == 4) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(pR_dst + (q * PIECEW + lw) * 4), "r"(L1[4 * q]), "r"(L1[4 * q + 1]), "r"(L1[4 * q + 2]), "r"(L1[4 * q + 3]), "r"(pR_bar) : "memory");
+                        else st_async_v2(pR_dst + (q * PIECEW + lw) * 4, L1[2 * q], L1[2 * q + 1], pR_bar);
+                    }
+                    if (sub == 0) st_async_v2(pR_dst + dwords * 4, iA1, iB1, pR_bar);
+                }
+                if (!WTA || storeS) {
+                    unsigned* Sp = rowS + (size_t)col * colW;
+#pragma unroll
+                    for (int q = 0; q < NP; q++) {
+                        if (PW == 4) *(uint4*)(Sp + q * PIECEW) = make_uint4(s[4 * q], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
+                        else *(uint2*)(Sp + q * PIECEW) = make_uint2(s[2 * q], s[2 * q + 1]);
+                    }
+                }
+            }
+            if (WTA) group_wta<NWD, LPR, PW, HASPAD>(s, sub, g, D, p.uniq, on, aux + (frameRow0 + y) * W1 + a + cc);
+        }
+    }
+    cluster.sync();                                                   // nobody exits while a neighbour may still write into its inbox
+}
