@@ -115,8 +115,10 @@ __global__ void k_sor_scatter(const cvr_point* __restrict__ pts, size_t stride, 
     }
 }
 
-// One thread per query point (in cell-sorted order).  best[] holds the k+1 smallest squared distances seen,
-// ascending; the query itself (distance 0) is one of them, exactly like nearestKSearch(i, k+1).
+// One thread per query point (in cell-sorted order).  best[] holds the k+1 smallest squared distances seen as a binary
+// max-heap; the query itself (distance 0) is one of them, exactly like nearestKSearch(i, k+1).  The heap lives in SHARED
+// memory, one column per thread (best[i] of thread t at heap[i * 128 + t]: conflict-free however the threads' heap
+// positions diverge); as a per-thread array it was dynamically indexed and ended up in local memory.
 template <int KCAP>
 __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
                                                  const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
@@ -131,7 +133,9 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
     const float4 q = sp[t];
     const int orig = __float_as_int(q.w);
     if (g.n < K1) { out[orig] = 0.f; continue; }
-    float best[KCAP];
+    extern __shared__ float heapsm[];
+    struct HeapCol { float* p; __device__ __forceinline__ float& operator[](int i) const { return p[i * 128]; } };
+    const HeapCol best{ heapsm + threadIdx.x };
     int cnt = 0;
     int cx, cy, cz;
     sor_cell(g, q.x, q.y, q.z, cx, cy, cz);
@@ -338,10 +342,9 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     if (rc) return rc;
     const float4* sp = c->d_spts;
     const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B);
-    if (k + 1 <= 32) k_sor_knn<32><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
-    else if (k + 1 <= 64) k_sor_knn<64><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
-    else if (k + 1 <= 128) k_sor_knn<128><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
-    else k_sor_knn<320><<<g, 128, 0, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    const size_t heapBytes = (size_t)(k + 1) * 128 * sizeof(float);   // one heap column per thread
+    if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
+    k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
     LAUNCH_CHECK(c);
     k_sor_stats<<<B, 1024, 0, c->stream>>>(c->d_meand, ptStride, n_in, k, c->cl.sor_alpha, c->d_sstats);
     LAUNCH_CHECK(c);

@@ -1,7 +1,7 @@
 #!/bin/bash
 # compute-sanitizer over one small-shape pass of every kernel family (tests/gpu_sanitize_pass.py), for the default kernels and
 # for each alternative path-kernel variant; one GPU, run under gpurun.  Summaries land in gpurun_out/sanitize_*.log
-run() {  # name tool env...
+run() {  # name tool env...   (compute-sanitizer answers "closed on this pool" here: profiles/r02_sanitizer_closed.log)
   name=$1; tool=$2; shift 2
   env "$@" timeout 1500 compute-sanitizer --tool $tool --print-limit 5 python tests/gpu_sanitize_pass.py > gpurun_out/sanitize_${name}_${tool}.log 2>&1
   echo "== $name $tool: exit $? : $(grep -E 'ERROR SUMMARY|RACECHECK SUMMARY|sanitize pass' gpurun_out/sanitize_${name}_${tool}.log | tr '\n' ' ')"
