@@ -214,7 +214,9 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     c->maxN = (int)(p->max_points > 0 ? (size_t)p->max_points : HW);
     if (!p->filter_only && (size_t)c->maxN < HW) c->maxN = (int)HW;
     const size_t N = (size_t)c->maxN;
-    c->sor_grid_cap = c->maxN < 4096 ? 4096 : c->maxN;
+    // search-grid cells per frame: a filter-only context (one large cloud) gets room for ~2 points per cell even when outliers
+    // blow up the bounding box; the batch path's clouds are far smaller than W*H anyway
+    { const long long cap = p->filter_only ? 4LL * c->maxN : (long long)c->maxN; c->sor_grid_cap = (int)(cap < 4096 ? 4096 : (cap > 0x3fffffffLL ? 0x3fffffffLL : cap)); }
     const size_t nRuns = (N + 511) / 512;
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
 #define A(call) if (e == cudaSuccess) e = (call)
@@ -243,6 +245,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     A(dalloc(&c->d_meand, B * N)); A(dalloc(&c->d_sstats, B)); A(dalloc(&c->d_sorout, B * N));
     A(dalloc(&c->d_nout, B)); A(dalloc(&c->d_nvox, B)); A(dalloc(&c->d_spts, B * N));
     A(dalloc(&c->d_flags, B * 64));
+    if (e == cudaSuccess) e = cudaMemset(c->d_flags, 0, B * 64 * sizeof(int));     // (holds counters that every use leaves at zero)
     A(dalloc(&c->d_sgflags, B));
     A(cudaHostAlloc((void**)&c->h_counts, sizeof(int) * B * 4, cudaHostAllocDefault));
     A(dalloc(&c->d_meta0, CVR_META_INTS(B))); A(cudaHostAlloc((void**)&c->h_meta0, CVR_META_INTS(B) * sizeof(int), cudaHostAllocDefault));

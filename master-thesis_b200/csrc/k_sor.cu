@@ -12,12 +12,27 @@
 
 struct SorGrid {
     float mn[3];
+    float ext[3];        // extent of the bounding box (floored at a thousandth of the largest)
     float cell, inv;
     int dim[3];
     int ncell;
     int n;
 };
 
+// cell edge s (grown until the grid fits `cap` cells) -> dims of the grid over the frame's bounding box
+__device__ __forceinline__ void sor_fit_cells(SorGrid& g, float s, int cap)
+{
+    float ext[3], emax = 0.f;
+    for (int k = 0; k < 3; k++) { ext[k] = g.ext[k]; emax = fmaxf(emax, ext[k]); }
+    for (int it = 0; it < 16; it++) {
+        long long tot = 1;
+        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
+        if (tot <= cap) break;
+        s *= 1.15f;
+    }
+    g.cell = s; g.inv = 1.0f / s;
+    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
+}
 // the search grid of one frame from its bounding box: about two points per cell on a volume-filling cloud
 __device__ __forceinline__ SorGrid sor_make_grid(const VoxBox& box, int n, int cap)
 {
@@ -32,18 +47,12 @@ __device__ __forceinline__ SorGrid sor_make_grid(const VoxBox& box, int n, int c
     }
     if (!(emax > 0.f)) emax = 1.f;
     double vol = 1.0;
-    for (int k = 0; k < 3; k++) { ext[k] = fmaxf(ext[k], emax * 1e-3f); vol *= (double)ext[k]; }
-    // surface-like clouds end up sparser than two points per cell, which only costs time
+    for (int k = 0; k < 3; k++) { ext[k] = fmaxf(ext[k], emax * 1e-3f); vol *= (double)ext[k]; g.ext[k] = ext[k]; }
+    // surface-like clouds end up sparser than two points per cell, which only costs time; clouds that fill a fraction of
+    // their bounding box end up denser, which k_sor_regrid corrects
     float s = (float)cbrt(2.0 * vol / (double)max(g.n, 1));
     s = fmaxf(s, emax * 1e-4f);
-    for (int it = 0; it < 8; it++) {
-        long long tot = 1;
-        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
-        if (tot <= cap) break;
-        s *= 1.3f;
-    }
-    g.cell = s; g.inv = 1.0f / s;
-    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
+    sor_fit_cells(g, s, cap);
     return g;
 }
 // pcl::RadiusOutlierRemoval's grid: cell edge = the radius (a multiple of it when the grid would get too large)
@@ -56,6 +65,7 @@ __device__ __forceinline__ SorGrid ror_make_grid(const VoxBox& box, int n, float
         g.mn[k] = g.n > 0 ? ord2f(box.mn[k]) : 0.f;
         const float mx = g.n > 0 ? ord2f(box.mx[k]) : 0.f;
         ext[k] = fmaxf(mx - g.mn[k], 0.f);
+        g.ext[k] = ext[k];
     }
     float s = radius;
     for (int it = 0; it < 32; it++) {
@@ -82,6 +92,41 @@ __global__ void __launch_bounds__(256) k_sor_grid_zero(const VoxBox* __restrict_
     const int len = sg.ncell + 1;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) { cellA[(size_t)b * cellStride + i] = 0; cellB[(size_t)b * cellStride + i] = 0; }
 }
+// Second look at the grid: a cloud that fills only part of its bounding box (a dense scene plus far outliers) has many more
+// points per occupied cell than the two the bounding-box estimate aimed at, and every neighbour search would wade through
+// them.  k_sor_occupancy counts the occupied cells; k_sor_regrid shrinks the cell edge of such a frame so that OCCUPIED cells
+// hold about two points, and flags it; flagged frames get their cell tables cleared and counted again.
+__global__ void __launch_bounds__(256) k_sor_occupancy(const int* __restrict__ cellcnt, size_t cellStride, const int* __restrict__ ncell, int* occ)
+{
+    const int b = blockIdx.y, len = ncell[b];
+    int c = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) c += cellcnt[(size_t)b * cellStride + i] > 0;
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&occ[b], c);
+}
+__global__ void k_sor_regrid(SorGrid* grid, int* ncellOut, int* occ, int* flag, int cap, int B)
+{
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    SorGrid g = grid[b];
+    const int used = occ[b];
+    occ[b] = 0;                                                       // ready for the next call
+    const float per = used > 0 ? (float)g.n / (float)used : 0.f;
+    int f = 0;
+    if (per > 3.0f && g.n > 4096) {
+        sor_fit_cells(g, g.cell * cbrtf(2.0f / per), cap);
+        f = g.ncell > grid[b].ncell ? 1 : 0;                          // (the cap may have pushed the edge back up)
+        if (f) { grid[b] = g; ncellOut[b] = g.ncell; }
+    }
+    flag[b] = f;
+}
+__global__ void __launch_bounds__(256) k_sor_rezero(const int* __restrict__ flag, const int* __restrict__ ncell, int* cellA, int* cellB, size_t cellStride)
+{
+    const int b = blockIdx.y;
+    if (!flag[b]) return;
+    const int len = ncell[b] + 1;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) { cellA[(size_t)b * cellStride + i] = 0; cellB[(size_t)b * cellStride + i] = 0; }
+}
 __device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, float z, int& cx, int& cy, int& cz)
 {
     cx = min(max((int)((x - g.mn[0]) * g.inv), 0), g.dim[0] - 1);
@@ -89,9 +134,10 @@ __device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, flo
     cz = min(max((int)((z - g.mn[2]) * g.inv), 0), g.dim[2] - 1);
 }
 __global__ void k_sor_cellcount(const cvr_point* __restrict__ pts, size_t stride, const SorGrid* __restrict__ grid, int* cellcnt, size_t cellStride,
-                                int* __restrict__ cellOfPt, size_t ptStride)
+                                int* __restrict__ cellOfPt, size_t ptStride, const int* __restrict__ onlyFlagged)
 {
     const int b = blockIdx.y;
+    if (onlyFlagged && !onlyFlagged[b]) return;
     const SorGrid g = grid[b];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += gridDim.x * blockDim.x) {
         const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
@@ -309,8 +355,21 @@ static int sor_build_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stri
     const dim3 gp(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B);     // strides over the frame's points / cells
     k_sor_grid_zero<<<dim3(cvr_frame_blocks(c, B, (size_t)cap + 1, 256, 8), B), 256, 0, c->stream>>>(c->d_boxs, n_in, grid, ncell, cap, radius, cellstart, cellfill, cellStride);
     LAUNCH_CHECK(c);
-    k_sor_cellcount<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
+    k_sor_cellcount<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride, nullptr);
     LAUNCH_CHECK(c);
+    if (radius <= 0.f) {                                               // kNN grid: re-fit to the occupied cells where the cloud is much denser than its box
+        int* occ = c->d_flags + (size_t)c->maxB * 33;
+        int* flag = c->d_flags + (size_t)c->maxB * 34;
+        const dim3 gc(cvr_frame_blocks(c, B, (size_t)cap + 1, 256, 8), B);
+        k_sor_occupancy<<<gc, 256, 0, c->stream>>>(cellstart, cellStride, ncell, occ);
+        LAUNCH_CHECK(c);
+        k_sor_regrid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(grid, ncell, occ, flag, cap, B);
+        LAUNCH_CHECK(c);
+        k_sor_rezero<<<gc, 256, 0, c->stream>>>(flag, ncell, cellstart, cellfill, cellStride);
+        LAUNCH_CHECK(c);
+        k_sor_cellcount<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride, flag);
+        LAUNCH_CHECK(c);
+    }
     { const int rcs = scan_cells(c, B, cellstart, cellStride, cap, ncell); if (rcs) return rcs; }
     k_sor_scatter<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
     LAUNCH_CHECK(c);
