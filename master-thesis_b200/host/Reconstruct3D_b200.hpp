@@ -9,6 +9,7 @@
 // Errors: the reference lets cv::Exception propagate; this mirror throws std::runtime_error with cvr_last_error().
 #pragma once
 #include <cstdint>
+#include <cstring>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -201,6 +202,65 @@ public:
     }
     cvr_ctx* context() const { return m_ctx; }
 
+    // ---- batched / multi-GPU side (no counterpart class in the reference: it processes one frame per call on one machine) ----
+    // What MapDataBase::InsertBlock (MapDataBase.cpp:28-54) receives per processed frame, for a whole batch: the filtered
+    // clouds back to back, frame i = points[offsets[i] .. offsets[i + 1]).
+    struct MapBlocks {
+        std::vector<cvr_point> points;
+        std::vector<int32_t> offsets;          // frames + 1 entries
+        std::vector<int32_t> framesOfRank;     // GatherMapBlocks on the root: frames contributed by each rank
+        std::size_t frames() const { return offsets.empty() ? 0 : offsets.size() - 1; }
+    };
+    // ReconstructionSystem::ProcessStereoFrame (ReconstructionSystem.cpp:35-61) + the filter call sites for `n` frames at once
+    // (n <= maxBatch of the constructor): left[i] / right[i] are the frames, all of the constructor's size.
+    MapBlocks ProcessStereoFrames(const Mat* left, const Mat* right, int n, std::size_t pointCapacity = 0) const
+    {
+        const std::size_t rowBytes = static_cast<std::size_t>(m_width) * left[0].channels, frameBytes = rowBytes * m_height;
+        std::vector<uint8_t> l(frameBytes * n), r(frameBytes * n);                                // one dense staging copy per camera
+        for (int i = 0; i < n; i++)
+            for (int y = 0; y < m_height; y++) {
+                std::memcpy(&l[i * frameBytes + y * rowBytes], static_cast<const uint8_t*>(left[i].data) + y * left[i].step, rowBytes);
+                std::memcpy(&r[i * frameBytes + y * rowBytes], static_cast<const uint8_t*>(right[i].data) + y * right[i].step, rowBytes);
+            }
+        MapBlocks out;
+        out.points.resize(pointCapacity ? pointCapacity : static_cast<std::size_t>(m_width) * m_height * n);
+        out.offsets.assign(n + 1, 0);
+        cvr_batch io;
+        std::memset(&io, 0, sizeof(io));
+        io.mem = CVR_MEM_HOST; io.channels = left[0].channels; io.stages = 15;
+        io.left = l.data(); io.left_step = rowBytes; io.left_frame_stride = frameBytes;
+        io.right = r.data(); io.right_step = rowBytes; io.right_frame_stride = frameBytes;
+        io.cloud_packed = out.points.data(); io.cloud_packed_capacity = out.points.size(); io.cloud_offsets = out.offsets.data();
+        check(cvr_process_batch(m_ctx, n, &io));
+        out.points.resize(static_cast<std::size_t>(out.offsets[n]));
+        return out;
+    }
+    // One process per GPU: every rank joins the communicator once (the 128-byte id comes from rank 0's NewCommId by whatever
+    // channel the host has), then GatherMapBlocks after each batch brings all ranks' map blocks to the mapping rank
+    // (MappingSystem.cpp:344-345: AddFrame -> InsertBlock) -- a collective call; only the root's return value is filled.
+    static std::vector<uint8_t> NewCommId()
+    {
+        std::vector<uint8_t> id(CVR_COMM_ID_BYTES);
+        if (cvr_comm_get_unique_id(id.data()) != CVR_OK) throw std::runtime_error(std::string("cvrecon_b200: ") + cvr_last_error(nullptr));
+        return id;
+    }
+    void JoinComm(int nranks, int rank, const std::vector<uint8_t>& id) { check(cvr_comm_init(m_ctx, nranks, rank, id.data())); m_nranks = nranks; m_rank = rank; }
+    MapBlocks GatherMapBlocks(int root, std::size_t pointCapacity, int maxFramesPerRank) const
+    {
+        MapBlocks out;
+        if (m_rank != root) { check(cvr_gather_clouds(m_ctx, root, CVR_MEM_HOST, nullptr, 0, nullptr, 0, nullptr)); return out; }
+        out.points.resize(pointCapacity);
+        out.offsets.assign(static_cast<std::size_t>(m_nranks) * maxFramesPerRank + 1, 0);
+        out.framesOfRank.assign(m_nranks, 0);
+        check(cvr_gather_clouds(m_ctx, root, CVR_MEM_HOST, out.points.data(), out.points.size(), out.offsets.data(),
+                                static_cast<int>(out.offsets.size()), out.framesOfRank.data()));
+        int frames = 0;
+        for (int v : out.framesOfRank) frames += v;
+        out.offsets.resize(frames + 1);
+        out.points.resize(static_cast<std::size_t>(out.offsets[frames]));
+        return out;
+    }
+
 private:
     void check(int rc) const { if (rc != CVR_OK) throw std::runtime_error(std::string("cvrecon_b200: ") + cvr_last_error(m_ctx)); }
     void rebuild()
@@ -215,6 +275,7 @@ private:
     cvr_ctx* m_ctx = nullptr;
     StereoCalib m_calib;
     int m_width = 0, m_height = 0;
+    int m_nranks = 1, m_rank = 0;
 };
 
 }  // namespace cvr

@@ -10,15 +10,19 @@ import pytest
 from conftest import ROOT
 
 
-def _build_example(tmp_path, cvr):
+def _build_example(tmp_path, cvr, name="example_frame"):
     if not os.path.exists(cvr.LIB_PATH):
         cvr.build()
-    exe = str(tmp_path / "example_frame")
+    exe = str(tmp_path / name)
     libdir = os.path.dirname(cvr.LIB_PATH)
     subprocess.check_call(["g++", "-std=c++14", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"),
-                           os.path.join(ROOT, "master-thesis_b200", "host", "example_frame.cpp"), "-L", libdir, "-lcvrecon_b200",
+                           os.path.join(ROOT, "master-thesis_b200", "host", name + ".cpp"), "-L", libdir, "-lcvrecon_b200",
                            "-Wl,-rpath," + libdir, "-o", exe])
     return exe
+
+
+def test_cpp_gather_example_compiles(tmp_path, cvr):
+    _build_example(tmp_path, cvr, "example_gather")
 
 
 def test_cpp_mirror_compiles_and_has_no_cpu_fallback(tmp_path, cvr):
@@ -78,3 +82,39 @@ def test_cpp_example_matches_python_harness(tmp_path, cvr, oracle):
     uv = [float(v) for v in r.stdout.split("uv")[1].split()]
     f = np.float32((np.float32(959.791) + np.float32(956.9251)) / np.float32(2)); z = f * np.float32(0.532671) / np.float32(16)
     assert np.allclose(uv, [(np.float32(100) - np.float32(696.0217)) * (z / f), -(np.float32(50) - np.float32(224.1806)) * (z / f), z], rtol=1e-5)
+
+
+def _gather_frames(tmp_path, oracle, world, n, H, W, D):
+    with open(tmp_path / "frames.bgr", "wb") as f:
+        for p in range(world * n):
+            lb, rb = oracle.synth_pair(H, W, D, seed=900 + p, color=True)
+            f.write(lb.tobytes()); f.write(rb.tobytes())
+    return str(tmp_path / "frames.bgr")
+
+
+@pytest.mark.gpu
+def test_cpp_gather_example_one_rank(tmp_path, cvr, oracle):
+    """A C++ host runs a batch through ProcessStereoFrames and gathers its map blocks (one rank: a local copy)."""
+    exe = _build_example(tmp_path, cvr, "example_gather")
+    H, W, D, n = 60, 330, 64, 3
+    frames = _gather_frames(tmp_path, oracle, 1, n, H, W, D)
+    r = subprocess.run([exe, str(W), str(H), str(n), frames], capture_output=True, text=True)
+    assert r.returncode == 0 and "gather ok ranks 1 frames 3" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_cpp_gather_example_two_ranks(tmp_path, cvr, oracle):
+    """Two C++ processes, one GPU each, exchanging the NCCL id through a file; rank 0 checks every gathered frame."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    exe = _build_example(tmp_path, cvr, "example_gather")
+    H, W, D, n = 60, 330, 64, 3
+    frames = _gather_frames(tmp_path, oracle, 2, n, H, W, D)
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank), CVR_ID_FILE=str(tmp_path / "nccl.id"))
+        procs.append(subprocess.Popen([exe, str(W), str(H), str(n), frames], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = [p.communicate(timeout=300) for p in procs]
+    assert procs[0].returncode == 0 and procs[1].returncode == 0, outs
+    assert "gather ok ranks 2 frames 6" in outs[0][0]
