@@ -17,6 +17,7 @@ struct SorGrid {
     int dim[3];
     int ncell;
     int n;
+    int r0;              // cube radius (in cells) the warp-per-cell search starts with
 };
 
 // cell edge s (grown until the grid fits `cap` cells) -> dims of the grid over the frame's bounding box
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(256) k_sor_occupancy(const int* __restrict__ c
     c = __reduce_add_sync(0xffffffffu, c);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(&occ[b], c);
 }
-__global__ void k_sor_regrid(SorGrid* grid, int* ncellOut, int* occ, int* flag, int cap, int B)
+__global__ void k_sor_regrid(SorGrid* grid, int* ncellOut, int* occ, int* flag, int cap, int B, int k)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
@@ -113,11 +114,17 @@ __global__ void k_sor_regrid(SorGrid* grid, int* ncellOut, int* occ, int* flag, 
     occ[b] = 0;                                                       // ready for the next call
     const float per = used > 0 ? (float)g.n / (float)used : 0.f;
     int f = 0;
+    float perNew = per;
     if (per > 3.0f && g.n > 4096) {
+        const float old = g.cell;
         sor_fit_cells(g, g.cell * cbrtf(2.0f / per), cap);
         f = g.ncell > grid[b].ncell ? 1 : 0;                          // (the cap may have pushed the edge back up)
-        if (f) { grid[b] = g; ncellOut[b] = g.ncell; }
+        if (f) perNew = per * (g.cell / old) * (g.cell / old) * (g.cell / old); else g = grid[b];
     }
+    // radius of the sphere that holds k + 1 points at this density, in cells: where the cube search starts
+    const float rk = cbrtf(3.0f * (float)(k + 1) / (4.0f * 3.14159265f * fmaxf(perNew, 0.05f)));
+    g.r0 = min(max((int)ceilf(rk - 0.2f), 1), 3);
+    grid[b] = g; ncellOut[b] = g.ncell;
     flag[b] = f;
 }
 __global__ void __launch_bounds__(256) k_sor_rezero(const int* __restrict__ flag, const int* __restrict__ ncell, int* cellA, int* cellB, size_t cellStride)
@@ -167,7 +174,7 @@ __global__ void k_sor_scatter(const cvr_point* __restrict__ pts, size_t stride, 
 // positions diverge); as a per-thread array it was dynamically indexed and ended up in local memory.
 template <int KCAP>
 __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
-                                                 const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
+                                                 const int* __restrict__ cellstart, size_t cellStride, int k, float* meand, int onlyMarked)
 {
     const int b = blockIdx.y;
     const SorGrid g = grid[b];
@@ -178,6 +185,7 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < g.n; t += gridDim.x * blockDim.x) {
     const float4 q = sp[t];
     const int orig = __float_as_int(q.w);
+    if (onlyMarked && out[orig] != -1.f) continue;                    // already answered by k_sor_knn_warp
     if (g.n < K1) { out[orig] = 0.f; continue; }
     extern __shared__ float heapsm[];
     struct HeapCol { float* p; __device__ __forceinline__ float& operator[](int i) const { return p[i * 128]; } };
@@ -259,6 +267,153 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
     double s = 0.0;
     for (int j = 1; j < K1; j++) s = __dadd_rn(s, (double)__fsqrt_rn(best[j]));
     out[orig] = (float)__ddiv_rn(s, (double)k);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// The same search, one WARP per occupied grid cell.  All queries of a cell see exactly the same candidates (the cube of
+// cells around it), so the warp stages them once in shared memory (coalesced reads of the cell-sorted points) and then, per
+// query, computes the squared distances with the lanes striding over the candidates and SELECTS the (k+1)-th smallest by a
+// four-pass radix select on the float bits (a 256-bin histogram per pass) -- no per-thread heaps, no divergence between the
+// queries of a warp.  The mean distance is the f64 sum of the square roots of everything below that value plus as many
+// copies of it as are still missing (ties).  The cube starts at SorGrid::r0 cells and grows while the (k+1)-th distance is
+// not yet provably final (same stop rule as k_sor_knn).  Queries whose cube holds more than KNW_CMAX candidates, or that
+// are still open at KNW_RMAX, are marked (-1) and answered by k_sor_knn afterwards.
+#define KNW_CMAX 512
+#define KNW_WARPS 8
+#define KNW_RMAX 3
+#define KNW_RUNS 49           // (2 * KNW_RMAX + 1)^2 runs of cells along x
+struct KnwWarp { float x[KNW_CMAX], y[KNW_CMAX], z[KNW_CMAX]; unsigned d2[KNW_CMAX]; int hist[256]; int runBeg[KNW_RUNS + 1], runOff[KNW_RUNS + 1]; };
+
+__global__ void __launch_bounds__(KNW_WARPS * 32) k_sor_knn_warp(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
+                                                                 const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
+{
+    extern __shared__ __align__(16) unsigned char knwsm[];
+    KnwWarp& S = ((KnwWarp*)knwsm)[threadIdx.x >> 5];
+    const int lane = threadIdx.x & 31, b = blockIdx.y;
+    const SorGrid g = grid[b];
+    const float4* sp = spts + (size_t)b * ptStride;
+    const int* cs = cellstart + (size_t)b * cellStride;
+    float* out = meand + (size_t)b * ptStride;
+    const int K1 = k + 1;
+    const int nWarps = gridDim.x * KNW_WARPS, wg = blockIdx.x * KNW_WARPS + (threadIdx.x >> 5);
+    if (g.n < K1) {                                                    // nothing can be judged: every mean distance is 0 (PCL: search fails)
+        for (int i = wg * 32 + lane; i < g.n; i += nWarps * 32) out[__float_as_int(sp[i].w)] = 0.f;
+        return;
+    }
+    for (int cbase = wg * 32; cbase < g.ncell; cbase += nWarps * 32) {
+        const int cell = cbase + lane;
+        const int myBeg = cell < g.ncell ? cs[cell] : 0;
+        const int myCnt = cell < g.ncell ? cs[cell + 1] - myBeg : 0;
+        unsigned occ = __ballot_sync(0xffffffffu, myCnt > 0);
+        while (occ) {
+            const int l = __ffs(occ) - 1;
+            occ &= occ - 1;
+            const int c = cbase + l;
+            const int qb = __shfl_sync(0xffffffffu, myBeg, l), qn = __shfl_sync(0xffffffffu, myCnt, l);
+            const int cz = c / (g.dim[0] * g.dim[1]), cy = (c - cz * g.dim[0] * g.dim[1]) / g.dim[0], cx = c - (cz * g.dim[1] + cy) * g.dim[0];
+            for (int q0 = 0; q0 < qn; q0 += 32) {                      // the cell's queries, 32 at a time
+                unsigned pending = (qn - q0 >= 32) ? 0xffffffffu : ((1u << (qn - q0)) - 1u);
+                for (int R = g.r0; pending; R++) {
+                    if (R > KNW_RMAX) {                                // leave the rest to k_sor_knn
+                        if ((pending >> lane) & 1u) out[__float_as_int(sp[qb + q0 + lane].w)] = -1.f;
+                        break;
+                    }
+                    // ---- the cube's runs of cells along x: (2R+1)^2 of them, each a contiguous range of the sorted points ----
+                    const int side = 2 * R + 1, nruns = side * side;
+                    const int xa = max(cx - R, 0), xb = min(cx + R, g.dim[0] - 1);
+                    int nc = 0;
+                    for (int p0 = 0; p0 < nruns; p0 += 32) {
+                        const int p = p0 + lane;
+                        int jb = 0, len = 0;
+                        if (p < nruns) {
+                            const int iz = cz - R + p / side, iy = cy - R + p % side;
+                            if (iz >= 0 && iz < g.dim[2] && iy >= 0 && iy < g.dim[1]) {
+                                const int rowc = (iz * g.dim[1] + iy) * g.dim[0];
+                                jb = cs[rowc + xa];
+                                len = cs[rowc + xb + 1] - jb;
+                            }
+                        }
+                        int inc = len;                                 // inclusive scan of the run lengths
+#pragma unroll
+                        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+                        if (p < nruns) { S.runBeg[p] = jb; S.runOff[p] = nc + inc - len; }
+                        nc += __shfl_sync(0xffffffffu, inc, 31);
+                    }
+                    if (lane == 0) S.runOff[nruns] = nc;
+                    const bool covered = cx - R <= 0 && cx + R >= g.dim[0] - 1 && cy - R <= 0 && cy + R >= g.dim[1] - 1 && cz - R <= 0 && cz + R >= g.dim[2] - 1;
+                    if (nc > KNW_CMAX) {
+                        if ((pending >> lane) & 1u) out[__float_as_int(sp[qb + q0 + lane].w)] = -1.f;
+                        break;
+                    }
+                    if (nc < K1 && !covered) continue;                 // too few candidates to decide anything: a larger cube
+                    __syncwarp();
+                    // ---- stage the candidates ----
+                    for (int r = 0; r < nruns; r++) {
+                        const int jb = S.runBeg[r], off = S.runOff[r], len = S.runOff[r + 1] - off;
+                        for (int t = lane; t < len; t += 32) { const float4 pt = sp[jb + t]; S.x[off + t] = pt.x; S.y[off + t] = pt.y; S.z[off + t] = pt.z; }
+                    }
+                    __syncwarp();
+                    // ---- the pending queries, one after the other ----
+                    const float lim = (float)R * g.cell, lim2 = lim * lim * (1.0f - 1e-5f);
+                    unsigned todo = pending;
+                    while (todo) {
+                        const int qi = __ffs(todo) - 1;
+                        todo &= todo - 1;
+                        const float4 q = sp[qb + q0 + qi];
+                        for (int t = lane; t < nc; t += 32) {
+                            const float dx = __fsub_rn(q.x, S.x[t]), dy = __fsub_rn(q.y, S.y[t]), dz = __fsub_rn(q.z, S.z[t]);
+                            float d = __fmul_rn(dx, dx);
+                            d = __fadd_rn(d, __fmul_rn(dy, dy));
+                            d = __fadd_rn(d, __fmul_rn(dz, dz));
+                            S.d2[t] = __float_as_uint(d);                // non-negative floats order like their bit patterns
+                        }
+                        // radix select of the K1-th smallest: 8 bits per pass, most significant first
+                        unsigned prefix = 0;
+                        int need = K1;
+#pragma unroll 1
+                        for (int pass = 0; pass < 4; pass++) {
+                            const int shift = 24 - 8 * pass;
+#pragma unroll
+                            for (int i = 0; i < 8; i++) S.hist[lane * 8 + i] = 0;
+                            __syncwarp();
+                            for (int t = lane; t < nc; t += 32) {
+                                const unsigned v = S.d2[t];
+                                if (pass == 0 || (v >> (shift + 8)) == prefix) atomicAdd(&S.hist[(v >> shift) & 255u], 1);
+                            }
+                            __syncwarp();
+                            int h[8], sum = 0;
+#pragma unroll
+                            for (int i = 0; i < 8; i++) { h[i] = S.hist[lane * 8 + i]; sum += h[i]; }
+                            int inc = sum;
+#pragma unroll
+                            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+                            const int ex = inc - sum;
+                            const unsigned hit = __ballot_sync(0xffffffffu, ex < need && need <= inc);
+                            const int hl = __ffs(hit) - 1;             // the lane whose eight bins hold the K1-th smallest
+                            int bin = 0, below = ex;
+#pragma unroll
+                            for (int i = 0; i < 8; i++) { if (below + h[i] < need) { below += h[i]; bin = i + 1; } else break; }
+                            bin = __shfl_sync(0xffffffffu, lane * 8 + min(bin, 7), hl);
+                            below = __shfl_sync(0xffffffffu, below, hl);
+                            need -= below;
+                            prefix = (prefix << 8) | (unsigned)bin;
+                            __syncwarp();
+                        }
+                        const unsigned tau = prefix;                   // the K1-th smallest squared distance; `need` copies of it are still to be taken
+                        if (!covered && !(__uint_as_float(tau) <= lim2)) continue;   // not provably final in this cube: stays pending
+                        double s = 0.0;
+                        for (int t = lane; t < nc; t += 32) { const unsigned v = S.d2[t]; if (v < tau) s = __dadd_rn(s, (double)__fsqrt_rn(__uint_as_float(v))); }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) s = __dadd_rn(s, __shfl_xor_sync(0xffffffffu, s, o));
+                        s = __dadd_rn(s, __dmul_rn((double)need, (double)__fsqrt_rn(__uint_as_float(tau))));
+                        if (lane == 0) out[__float_as_int(q.w)] = (float)__ddiv_rn(s, (double)k);
+                        pending &= ~(1u << qi);
+                    }
+                    __syncwarp();                                      // the staging area is refilled by the next cube / cell
+                }
+            }
+        }
     }
 }
 
@@ -363,7 +518,7 @@ static int sor_build_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stri
         const dim3 gc(cvr_frame_blocks(c, B, (size_t)cap + 1, 256, 8), B);
         k_sor_occupancy<<<gc, 256, 0, c->stream>>>(cellstart, cellStride, ncell, occ);
         LAUNCH_CHECK(c);
-        k_sor_regrid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(grid, ncell, occ, flag, cap, B);
+        k_sor_regrid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(grid, ncell, occ, flag, cap, B, c->cl.sor_k);
         LAUNCH_CHECK(c);
         k_sor_rezero<<<gc, 256, 0, c->stream>>>(flag, ncell, cellstart, cellfill, cellStride);
         LAUNCH_CHECK(c);
@@ -403,7 +558,17 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B);
     const size_t heapBytes = (size_t)(k + 1) * 128 * sizeof(float);   // one heap column per thread
     if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
-    k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    static const bool warpSearch = !(getenv("CVR_SOR_WARP") && atoi(getenv("CVR_SOR_WARP")) == 0);   // test hook: 0 = per-thread heaps only
+    if (warpSearch && k + 1 <= KNW_CMAX / 2) {
+        const size_t wsm = sizeof(KnwWarp) * KNW_WARPS;
+        CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
+        const int cells = c->sor_grid_cap;
+        k_sor_knn_warp<<<dim3(cvr_frame_blocks(c, B, (size_t)cells / 32 + 1, KNW_WARPS, 2), B), KNW_WARPS * 32, wsm, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+        LAUNCH_CHECK(c);
+        k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand, 1);   // whatever the warp search left open
+    } else {
+        k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand, 0);
+    }
     LAUNCH_CHECK(c);
     k_sor_stats<<<B, 1024, 0, c->stream>>>(c->d_meand, ptStride, n_in, k, c->cl.sor_alpha, c->d_sstats);
     LAUNCH_CHECK(c);
