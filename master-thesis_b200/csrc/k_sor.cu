@@ -12,28 +12,12 @@
 
 struct SorGrid {
     float mn[3];
-    float ext[3];        // extent of the bounding box (floored at a thousandth of the largest)
     float cell, inv;
     int dim[3];
     int ncell;
     int n;
-    int r0;              // cube radius (in cells) the warp-per-cell search starts with
 };
 
-// cell edge s (grown until the grid fits `cap` cells) -> dims of the grid over the frame's bounding box
-__device__ __forceinline__ void sor_fit_cells(SorGrid& g, float s, int cap)
-{
-    float ext[3], emax = 0.f;
-    for (int k = 0; k < 3; k++) { ext[k] = g.ext[k]; emax = fmaxf(emax, ext[k]); }
-    for (int it = 0; it < 16; it++) {
-        long long tot = 1;
-        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
-        if (tot <= cap) break;
-        s *= 1.15f;
-    }
-    g.cell = s; g.inv = 1.0f / s;
-    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
-}
 // the search grid of one frame from its bounding box: about two points per cell on a volume-filling cloud
 __device__ __forceinline__ SorGrid sor_make_grid(const VoxBox& box, int n, int cap)
 {
@@ -48,12 +32,18 @@ __device__ __forceinline__ SorGrid sor_make_grid(const VoxBox& box, int n, int c
     }
     if (!(emax > 0.f)) emax = 1.f;
     double vol = 1.0;
-    for (int k = 0; k < 3; k++) { ext[k] = fmaxf(ext[k], emax * 1e-3f); vol *= (double)ext[k]; g.ext[k] = ext[k]; }
-    // surface-like clouds end up sparser than two points per cell, which only costs time; clouds that fill a fraction of
-    // their bounding box end up denser, which k_sor_regrid corrects
+    for (int k = 0; k < 3; k++) { ext[k] = fmaxf(ext[k], emax * 1e-3f); vol *= (double)ext[k]; }
+    // surface-like clouds end up sparser than two points per cell, which only costs time
     float s = (float)cbrt(2.0 * vol / (double)max(g.n, 1));
     s = fmaxf(s, emax * 1e-4f);
-    sor_fit_cells(g, s, cap);
+    for (int it = 0; it < 8; it++) {
+        long long tot = 1;
+        for (int k = 0; k < 3; k++) { g.dim[k] = (int)(ext[k] / s) + 1; tot *= g.dim[k]; }
+        if (tot <= cap) break;
+        s *= 1.3f;
+    }
+    g.cell = s; g.inv = 1.0f / s;
+    g.ncell = g.dim[0] * g.dim[1] * g.dim[2];
     return g;
 }
 // pcl::RadiusOutlierRemoval's grid: cell edge = the radius (a multiple of it when the grid would get too large)
@@ -66,7 +56,6 @@ __device__ __forceinline__ SorGrid ror_make_grid(const VoxBox& box, int n, float
         g.mn[k] = g.n > 0 ? ord2f(box.mn[k]) : 0.f;
         const float mx = g.n > 0 ? ord2f(box.mx[k]) : 0.f;
         ext[k] = fmaxf(mx - g.mn[k], 0.f);
-        g.ext[k] = ext[k];
     }
     float s = radius;
     for (int it = 0; it < 32; it++) {
@@ -93,47 +82,6 @@ __global__ void __launch_bounds__(256) k_sor_grid_zero(const VoxBox* __restrict_
     const int len = sg.ncell + 1;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) { cellA[(size_t)b * cellStride + i] = 0; cellB[(size_t)b * cellStride + i] = 0; }
 }
-// Second look at the grid: a cloud that fills only part of its bounding box (a dense scene plus far outliers) has many more
-// points per occupied cell than the two the bounding-box estimate aimed at, and every neighbour search would wade through
-// them.  k_sor_occupancy counts the occupied cells; k_sor_regrid shrinks the cell edge of such a frame so that OCCUPIED cells
-// hold about two points, and flags it; flagged frames get their cell tables cleared and counted again.
-__global__ void __launch_bounds__(256) k_sor_occupancy(const int* __restrict__ cellcnt, size_t cellStride, const int* __restrict__ ncell, int* occ)
-{
-    const int b = blockIdx.y, len = ncell[b];
-    int c = 0;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) c += cellcnt[(size_t)b * cellStride + i] > 0;
-    c = __reduce_add_sync(0xffffffffu, c);
-    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&occ[b], c);
-}
-__global__ void k_sor_regrid(SorGrid* grid, int* ncellOut, int* occ, int* flag, int cap, int B, int k)
-{
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B) return;
-    SorGrid g = grid[b];
-    const int used = occ[b];
-    occ[b] = 0;                                                       // ready for the next call
-    const float per = used > 0 ? (float)g.n / (float)used : 0.f;
-    int f = 0;
-    float perNew = per;
-    if (per > 3.0f && g.n > 4096) {
-        const float old = g.cell;
-        sor_fit_cells(g, g.cell * cbrtf(2.0f / per), cap);
-        f = g.ncell > grid[b].ncell ? 1 : 0;                          // (the cap may have pushed the edge back up)
-        if (f) perNew = per * (g.cell / old) * (g.cell / old) * (g.cell / old); else g = grid[b];
-    }
-    // radius of the sphere that holds k + 1 points at this density, in cells: where the cube search starts
-    const float rk = cbrtf(3.0f * (float)(k + 1) / (4.0f * 3.14159265f * fmaxf(perNew, 0.05f)));
-    g.r0 = min(max((int)ceilf(rk - 0.2f), 1), 3);
-    grid[b] = g; ncellOut[b] = g.ncell;
-    flag[b] = f;
-}
-__global__ void __launch_bounds__(256) k_sor_rezero(const int* __restrict__ flag, const int* __restrict__ ncell, int* cellA, int* cellB, size_t cellStride)
-{
-    const int b = blockIdx.y;
-    if (!flag[b]) return;
-    const int len = ncell[b] + 1;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) { cellA[(size_t)b * cellStride + i] = 0; cellB[(size_t)b * cellStride + i] = 0; }
-}
 __device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, float z, int& cx, int& cy, int& cz)
 {
     cx = min(max((int)((x - g.mn[0]) * g.inv), 0), g.dim[0] - 1);
@@ -141,10 +89,9 @@ __device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, flo
     cz = min(max((int)((z - g.mn[2]) * g.inv), 0), g.dim[2] - 1);
 }
 __global__ void k_sor_cellcount(const cvr_point* __restrict__ pts, size_t stride, const SorGrid* __restrict__ grid, int* cellcnt, size_t cellStride,
-                                int* __restrict__ cellOfPt, size_t ptStride, const int* __restrict__ onlyFlagged)
+                                int* __restrict__ cellOfPt, size_t ptStride)
 {
     const int b = blockIdx.y;
-    if (onlyFlagged && !onlyFlagged[b]) return;
     const SorGrid g = grid[b];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += gridDim.x * blockDim.x) {
         const float4 q = *(const float4*)(pts + (size_t)b * stride + i);
@@ -174,7 +121,7 @@ __global__ void k_sor_scatter(const cvr_point* __restrict__ pts, size_t stride, 
 // positions diverge); as a per-thread array it was dynamically indexed and ended up in local memory.
 template <int KCAP>
 __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
-                                                 const int* __restrict__ cellstart, size_t cellStride, int k, float* meand, int onlyMarked)
+                                                 const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
 {
     const int b = blockIdx.y;
     const SorGrid g = grid[b];
@@ -185,7 +132,6 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < g.n; t += gridDim.x * blockDim.x) {
     const float4 q = sp[t];
     const int orig = __float_as_int(q.w);
-    if (onlyMarked && out[orig] != -1.f) continue;                    // already answered by k_sor_knn_warp
     if (g.n < K1) { out[orig] = 0.f; continue; }
     extern __shared__ float heapsm[];
     struct HeapCol { float* p; __device__ __forceinline__ float& operator[](int i) const { return p[i * 128]; } };
@@ -267,153 +213,6 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
     double s = 0.0;
     for (int j = 1; j < K1; j++) s = __dadd_rn(s, (double)__fsqrt_rn(best[j]));
     out[orig] = (float)__ddiv_rn(s, (double)k);
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// The same search, one WARP per occupied grid cell.  All queries of a cell see exactly the same candidates (the cube of
-// cells around it), so the warp stages them once in shared memory (coalesced reads of the cell-sorted points) and then, per
-// query, computes the squared distances with the lanes striding over the candidates and SELECTS the (k+1)-th smallest by a
-// four-pass radix select on the float bits (a 256-bin histogram per pass) -- no per-thread heaps, no divergence between the
-// queries of a warp.  The mean distance is the f64 sum of the square roots of everything below that value plus as many
-// copies of it as are still missing (ties).  The cube starts at SorGrid::r0 cells and grows while the (k+1)-th distance is
-// not yet provably final (same stop rule as k_sor_knn).  Queries whose cube holds more than KNW_CMAX candidates, or that
-// are still open at KNW_RMAX, are marked (-1) and answered by k_sor_knn afterwards.
-#define KNW_CMAX 512
-#define KNW_WARPS 8
-#define KNW_RMAX 3
-#define KNW_RUNS 49           // (2 * KNW_RMAX + 1)^2 runs of cells along x
-struct KnwWarp { float x[KNW_CMAX], y[KNW_CMAX], z[KNW_CMAX]; unsigned d2[KNW_CMAX]; int hist[256]; int runBeg[KNW_RUNS + 1], runOff[KNW_RUNS + 1]; };
-
-__global__ void __launch_bounds__(KNW_WARPS * 32) k_sor_knn_warp(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
-                                                                 const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
-{
-    extern __shared__ __align__(16) unsigned char knwsm[];
-    KnwWarp& S = ((KnwWarp*)knwsm)[threadIdx.x >> 5];
-    const int lane = threadIdx.x & 31, b = blockIdx.y;
-    const SorGrid g = grid[b];
-    const float4* sp = spts + (size_t)b * ptStride;
-    const int* cs = cellstart + (size_t)b * cellStride;
-    float* out = meand + (size_t)b * ptStride;
-    const int K1 = k + 1;
-    const int nWarps = gridDim.x * KNW_WARPS, wg = blockIdx.x * KNW_WARPS + (threadIdx.x >> 5);
-    if (g.n < K1) {                                                    // nothing can be judged: every mean distance is 0 (PCL: search fails)
-        for (int i = wg * 32 + lane; i < g.n; i += nWarps * 32) out[__float_as_int(sp[i].w)] = 0.f;
-        return;
-    }
-    for (int cbase = wg * 32; cbase < g.ncell; cbase += nWarps * 32) {
-        const int cell = cbase + lane;
-        const int myBeg = cell < g.ncell ? cs[cell] : 0;
-        const int myCnt = cell < g.ncell ? cs[cell + 1] - myBeg : 0;
-        unsigned occ = __ballot_sync(0xffffffffu, myCnt > 0);
-        while (occ) {
-            const int l = __ffs(occ) - 1;
-            occ &= occ - 1;
-            const int c = cbase + l;
-            const int qb = __shfl_sync(0xffffffffu, myBeg, l), qn = __shfl_sync(0xffffffffu, myCnt, l);
-            const int cz = c / (g.dim[0] * g.dim[1]), cy = (c - cz * g.dim[0] * g.dim[1]) / g.dim[0], cx = c - (cz * g.dim[1] + cy) * g.dim[0];
-            for (int q0 = 0; q0 < qn; q0 += 32) {                      // the cell's queries, 32 at a time
-                unsigned pending = (qn - q0 >= 32) ? 0xffffffffu : ((1u << (qn - q0)) - 1u);
-                for (int R = g.r0; pending; R++) {
-                    if (R > KNW_RMAX) {                                // leave the rest to k_sor_knn
-                        if ((pending >> lane) & 1u) out[__float_as_int(sp[qb + q0 + lane].w)] = -1.f;
-                        break;
-                    }
-                    // ---- the cube's runs of cells along x: (2R+1)^2 of them, each a contiguous range of the sorted points ----
-                    const int side = 2 * R + 1, nruns = side * side;
-                    const int xa = max(cx - R, 0), xb = min(cx + R, g.dim[0] - 1);
-                    int nc = 0;
-                    for (int p0 = 0; p0 < nruns; p0 += 32) {
-                        const int p = p0 + lane;
-                        int jb = 0, len = 0;
-                        if (p < nruns) {
-                            const int iz = cz - R + p / side, iy = cy - R + p % side;
-                            if (iz >= 0 && iz < g.dim[2] && iy >= 0 && iy < g.dim[1]) {
-                                const int rowc = (iz * g.dim[1] + iy) * g.dim[0];
-                                jb = cs[rowc + xa];
-                                len = cs[rowc + xb + 1] - jb;
-                            }
-                        }
-                        int inc = len;                                 // inclusive scan of the run lengths
-#pragma unroll
-                        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-                        if (p < nruns) { S.runBeg[p] = jb; S.runOff[p] = nc + inc - len; }
-                        nc += __shfl_sync(0xffffffffu, inc, 31);
-                    }
-                    if (lane == 0) S.runOff[nruns] = nc;
-                    const bool covered = cx - R <= 0 && cx + R >= g.dim[0] - 1 && cy - R <= 0 && cy + R >= g.dim[1] - 1 && cz - R <= 0 && cz + R >= g.dim[2] - 1;
-                    if (nc > KNW_CMAX) {
-                        if ((pending >> lane) & 1u) out[__float_as_int(sp[qb + q0 + lane].w)] = -1.f;
-                        break;
-                    }
-                    if (nc < K1 && !covered) continue;                 // too few candidates to decide anything: a larger cube
-                    __syncwarp();
-                    // ---- stage the candidates ----
-                    for (int r = 0; r < nruns; r++) {
-                        const int jb = S.runBeg[r], off = S.runOff[r], len = S.runOff[r + 1] - off;
-                        for (int t = lane; t < len; t += 32) { const float4 pt = sp[jb + t]; S.x[off + t] = pt.x; S.y[off + t] = pt.y; S.z[off + t] = pt.z; }
-                    }
-                    __syncwarp();
-                    // ---- the pending queries, one after the other ----
-                    const float lim = (float)R * g.cell, lim2 = lim * lim * (1.0f - 1e-5f);
-                    unsigned todo = pending;
-                    while (todo) {
-                        const int qi = __ffs(todo) - 1;
-                        todo &= todo - 1;
-                        const float4 q = sp[qb + q0 + qi];
-                        for (int t = lane; t < nc; t += 32) {
-                            const float dx = __fsub_rn(q.x, S.x[t]), dy = __fsub_rn(q.y, S.y[t]), dz = __fsub_rn(q.z, S.z[t]);
-                            float d = __fmul_rn(dx, dx);
-                            d = __fadd_rn(d, __fmul_rn(dy, dy));
-                            d = __fadd_rn(d, __fmul_rn(dz, dz));
-                            S.d2[t] = __float_as_uint(d);                // non-negative floats order like their bit patterns
-                        }
-                        // radix select of the K1-th smallest: 8 bits per pass, most significant first
-                        unsigned prefix = 0;
-                        int need = K1;
-#pragma unroll 1
-                        for (int pass = 0; pass < 4; pass++) {
-                            const int shift = 24 - 8 * pass;
-#pragma unroll
-                            for (int i = 0; i < 8; i++) S.hist[lane * 8 + i] = 0;
-                            __syncwarp();
-                            for (int t = lane; t < nc; t += 32) {
-                                const unsigned v = S.d2[t];
-                                if (pass == 0 || (v >> (shift + 8)) == prefix) atomicAdd(&S.hist[(v >> shift) & 255u], 1);
-                            }
-                            __syncwarp();
-                            int h[8], sum = 0;
-#pragma unroll
-                            for (int i = 0; i < 8; i++) { h[i] = S.hist[lane * 8 + i]; sum += h[i]; }
-                            int inc = sum;
-#pragma unroll
-                            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-                            const int ex = inc - sum;
-                            const unsigned hit = __ballot_sync(0xffffffffu, ex < need && need <= inc);
-                            const int hl = __ffs(hit) - 1;             // the lane whose eight bins hold the K1-th smallest
-                            int bin = 0, below = ex;
-#pragma unroll
-                            for (int i = 0; i < 8; i++) { if (below + h[i] < need) { below += h[i]; bin = i + 1; } else break; }
-                            bin = __shfl_sync(0xffffffffu, lane * 8 + min(bin, 7), hl);
-                            below = __shfl_sync(0xffffffffu, below, hl);
-                            need -= below;
-                            prefix = (prefix << 8) | (unsigned)bin;
-                            __syncwarp();
-                        }
-                        const unsigned tau = prefix;                   // the K1-th smallest squared distance; `need` copies of it are still to be taken
-                        if (!covered && !(__uint_as_float(tau) <= lim2)) continue;   // not provably final in this cube: stays pending
-                        double s = 0.0;
-                        for (int t = lane; t < nc; t += 32) { const unsigned v = S.d2[t]; if (v < tau) s = __dadd_rn(s, (double)__fsqrt_rn(__uint_as_float(v))); }
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) s = __dadd_rn(s, __shfl_xor_sync(0xffffffffu, s, o));
-                        s = __dadd_rn(s, __dmul_rn((double)need, (double)__fsqrt_rn(__uint_as_float(tau))));
-                        if (lane == 0) out[__float_as_int(q.w)] = (float)__ddiv_rn(s, (double)k);
-                        pending &= ~(1u << qi);
-                    }
-                    __syncwarp();                                      // the staging area is refilled by the next cube / cell
-                }
-            }
-        }
     }
 }
 
@@ -510,21 +309,8 @@ static int sor_build_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stri
     const dim3 gp(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B);     // strides over the frame's points / cells
     k_sor_grid_zero<<<dim3(cvr_frame_blocks(c, B, (size_t)cap + 1, 256, 8), B), 256, 0, c->stream>>>(c->d_boxs, n_in, grid, ncell, cap, radius, cellstart, cellfill, cellStride);
     LAUNCH_CHECK(c);
-    k_sor_cellcount<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride, nullptr);
+    k_sor_cellcount<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride);
     LAUNCH_CHECK(c);
-    if (radius <= 0.f) {                                               // kNN grid: re-fit to the occupied cells where the cloud is much denser than its box
-        int* occ = c->d_flags + (size_t)c->maxB * 33;
-        int* flag = c->d_flags + (size_t)c->maxB * 34;
-        const dim3 gc(cvr_frame_blocks(c, B, (size_t)cap + 1, 256, 8), B);
-        k_sor_occupancy<<<gc, 256, 0, c->stream>>>(cellstart, cellStride, ncell, occ);
-        LAUNCH_CHECK(c);
-        k_sor_regrid<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(grid, ncell, occ, flag, cap, B, c->cl.sor_k);
-        LAUNCH_CHECK(c);
-        k_sor_rezero<<<gc, 256, 0, c->stream>>>(flag, ncell, cellstart, cellfill, cellStride);
-        LAUNCH_CHECK(c);
-        k_sor_cellcount<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellStride, c->d_cellidx, ptStride, flag);
-        LAUNCH_CHECK(c);
-    }
     { const int rcs = scan_cells(c, B, cellstart, cellStride, cap, ncell); if (rcs) return rcs; }
     k_sor_scatter<<<gp, 256, 0, c->stream>>>(in, in_stride, grid, cellstart, cellfill, cellStride, c->d_cellidx, ptStride, c->d_spts);
     LAUNCH_CHECK(c);
@@ -558,17 +344,7 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B);
     const size_t heapBytes = (size_t)(k + 1) * 128 * sizeof(float);   // one heap column per thread
     if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
-    static const bool warpSearch = !(getenv("CVR_SOR_WARP") && atoi(getenv("CVR_SOR_WARP")) == 0);   // test hook: 0 = per-thread heaps only
-    if (warpSearch && k + 1 <= KNW_CMAX / 2) {
-        const size_t wsm = sizeof(KnwWarp) * KNW_WARPS;
-        CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsm));
-        const int cells = c->sor_grid_cap;
-        k_sor_knn_warp<<<dim3(cvr_frame_blocks(c, B, (size_t)cells / 32 + 1, KNW_WARPS, 2), B), KNW_WARPS * 32, wsm, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
-        LAUNCH_CHECK(c);
-        k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand, 1);   // whatever the warp search left open
-    } else {
-        k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand, 0);
-    }
+    k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
     LAUNCH_CHECK(c);
     k_sor_stats<<<B, 1024, 0, c->stream>>>(c->d_meand, ptStride, n_in, k, c->cl.sor_alpha, c->d_sstats);
     LAUNCH_CHECK(c);
