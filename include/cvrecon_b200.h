@@ -171,6 +171,30 @@ int cvr_radius_outlier_removal(cvr_ctx* ctx, const cvr_point* in, int n, float r
 /* Replaces: pcl::transformPointCloud(cloud, cloud, pose) at MappingSystem.cpp:318 (T: row-major 4x4, f32; colours untouched). */
 int cvr_transform_cloud(cvr_ctx* ctx, const cvr_point* in, int n, const float* T, cvr_point* out);
 
+/* SURVEY 8(f) row n4 -- the alignment MappingSystem sets up between a key frame's cloud and the previous map block.
+ * Replaces: pcl::IterativeClosestPoint<PointXYZRGB, PointXYZRGB>::align at MappingSystem.cpp:321-341 (the same settings at
+ * :104-127; PointCloudPostProcessor.cpp:26-31 configures a second instance): point-to-point ICP with PCL's defaults -- nearest
+ * neighbour correspondences within max_correspondence_distance, transformation by SVD, the three stop rules of PCL's default
+ * convergence criteria (iterations, transformation epsilon, absolute / relative change of the mean squared correspondence
+ * distance).  cvr_icp_default_params fills in the reference's numbers (5, 50, 1e-8, 1).  source / target / aligned are host or
+ * device arrays according to `mem`; aligned (optional) receives the source cloud moved by T; T is row-major, applied to column
+ * vectors like Eigen::Matrix4f (p' = T * p), and maps the source onto the target (getFinalTransformation()).
+ * state: 0 not converged (fewer than three correspondences), 1 iterations, 2 transformation epsilon, 3 absolute, 4 relative MSE. */
+typedef struct cvr_icp_params {
+    double max_correspondence_distance;
+    int max_iterations;
+    double transformation_epsilon;
+    double euclidean_fitness_epsilon;
+} cvr_icp_params;
+typedef struct cvr_icp_result {
+    float T[16];
+    int iterations, converged, state, correspondences;   /* correspondences of the last iteration */
+    double fitness;                                       /* getFitnessScore(): mean squared distance to the nearest target point */
+} cvr_icp_result;
+void cvr_icp_default_params(cvr_icp_params* p);
+int cvr_icp_align(cvr_ctx* ctx, int mem, const cvr_point* source, int n_source, const cvr_point* target, int n_target, const cvr_icp_params* params,
+                  cvr_point* aligned, cvr_icp_result* result);
+
 /* Frame-parallel fused path: for each of nframes frames
  *   GenerateDisparityMap -> SetupFrame(prune) -> Triangulate3D|GeneratePointCloud -> VoxelGrid -> SOR
  * (the per-frame chain of ReconstructionSystem::ProcessStereoFrame, ReconstructionSystem.cpp:35-61,

@@ -36,7 +36,7 @@ EXPORTS = [
     "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
     "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps", "cvr_suggest_batch",
     "cvr_comm_get_unique_id", "cvr_comm_init", "cvr_comm_attach", "cvr_comm_destroy", "cvr_gather_clouds", "cvr_gather_layout",
-    "cvr_filter_cloud",
+    "cvr_filter_cloud", "cvr_icp_default_params", "cvr_icp_align",
 ]
 COMM_ID_BYTES = 128
 
@@ -68,6 +68,16 @@ class Batch(C.Structure):
         ("cloud", C.c_void_p), ("cloud_capacity", C.c_size_t), ("cloud_count", C.c_void_p), ("stages", C.c_int),
         ("cloud_packed", C.c_void_p), ("cloud_packed_capacity", C.c_size_t), ("cloud_offsets", C.c_void_p),
     ]
+
+
+class IcpParams(C.Structure):
+    _fields_ = [("max_correspondence_distance", C.c_double), ("max_iterations", C.c_int), ("transformation_epsilon", C.c_double),
+                ("euclidean_fitness_epsilon", C.c_double)]
+
+
+class IcpResult(C.Structure):
+    _fields_ = [("T", C.c_float * 16), ("iterations", C.c_int), ("converged", C.c_int), ("state", C.c_int), ("correspondences", C.c_int),
+                ("fitness", C.c_double)]
 
 
 class CvrError(RuntimeError):
@@ -128,6 +138,9 @@ def load_library():
     lib.cvr_points_to_pcl.restype = None
     lib.cvr_prune_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.cvr_filter_cloud.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
+    lib.cvr_icp_default_params.argtypes = [C.POINTER(IcpParams)]
+    lib.cvr_icp_default_params.restype = None
+    lib.cvr_icp_align.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(IcpParams), C.c_void_p, C.POINTER(IcpResult)]
     lib.cvr_comm_get_unique_id.argtypes = [C.c_void_p]
     lib.cvr_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.cvr_comm_attach.argtypes = [C.c_void_p, C.c_void_p]
@@ -423,6 +436,20 @@ class Reconstruct3D:
         m = C.c_int()
         self._check(self.lib.cvr_filter_cloud(self.ctx, MEM_DEVICE, C.c_void_p(in_ptr), int(n), int(stages), C.c_void_p(out_ptr), int(capacity), C.byref(m)))
         return m.value
+
+    # -- pcl::IterativeClosestPoint::align at MappingSystem.cpp:321-341 --
+    def AlignICP(self, source, target, **kw):
+        """Returns (T 4x4 f32, aligned source points, IcpResult)."""
+        src = np.ascontiguousarray(source, POINT_DTYPE)
+        tgt = np.ascontiguousarray(target, POINT_DTYPE)
+        prm = IcpParams()
+        self.lib.cvr_icp_default_params(C.byref(prm))
+        for k_, v in kw.items():
+            setattr(prm, k_, v)
+        res = IcpResult()
+        out = np.empty(len(src), POINT_DTYPE)
+        self._check(self.lib.cvr_icp_align(self.ctx, MEM_HOST, _ptr(src), len(src), _ptr(tgt), len(tgt), C.byref(prm), _ptr(out), C.byref(res)))
+        return np.array(list(res.T), np.float32).reshape(4, 4), out, res
 
     # -- pcl::RadiusOutlierRemoval::filter at MappingSystem.cpp:303-307 --
     def RadiusOutlierRemoval(self, cloud, radius=1.0, min_neighbors=300):

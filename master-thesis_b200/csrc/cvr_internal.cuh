@@ -74,6 +74,23 @@ struct SorStats {
     int kept;
 };
 
+// uniform search grid over one frame's cloud (k_sor.cu builds it; the outlier filters and the ICP search walk it)
+struct SorGrid {
+    float mn[3];
+    float cell, inv;
+    int dim[3];
+    int ncell;
+    int n;
+};
+#ifdef __CUDACC__
+__device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, float z, int& cx, int& cy, int& cz)
+{
+    cx = min(max((int)((x - g.mn[0]) * g.inv), 0), g.dim[0] - 1);
+    cy = min(max((int)((y - g.mn[1]) * g.inv), 0), g.dim[1] - 1);
+    cz = min(max((int)((z - g.mn[2]) * g.inv), 0), g.dim[2] - 1);
+}
+#endif
+
 struct StageTimer {
     const char* name;
     cudaEvent_t ev;
@@ -174,6 +191,7 @@ struct cvr_ctx {
     cudaStream_t comm_stream;
     int* d_hdr_all; int* h_hdr_all;           // [nranks][2 + maxB] gathered headers (device / pinned)
     cvr_point* d_gather; size_t gather_cap;   // root: receive buffer when the caller wants the clouds on the host
+    double* d_icp; double* h_icp;   // cvr_icp_align: block partials + totals of its 17 sums (device), the totals (pinned)
     int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
     int smem_optin;          // max dynamic shared memory per block (opt-in)
     bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)
@@ -249,6 +267,8 @@ int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, c
 int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in /*device*/, bool haveBox);
 int cvr_launch_ror(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, float radius, int min_pts);
 int cvr_launch_transform(cvr_ctx* c, const cvr_point* in, cvr_point* out, int n, const float* T);
+// k_sor.cu: bounding box (unless haveBox), grid (radius > 0: cell = radius, else ~2 points per cell), points sorted by cell into d_spts
+int cvr_build_point_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox, float radius, SorGrid** gridOut, int** cellstartOut);
 void cvr_stage_mark(cvr_ctx* c, const char* name);
 // message slot read by cvr_last_error(NULL): used by entry points that have no context
 void cvr_set_thread_error(const char* msg);

@@ -10,13 +10,6 @@
 #include <float.h>
 
 
-struct SorGrid {
-    float mn[3];
-    float cell, inv;
-    int dim[3];
-    int ncell;
-    int n;
-};
 
 // the search grid of one frame from its bounding box: about two points per cell on a volume-filling cloud
 __device__ __forceinline__ SorGrid sor_make_grid(const VoxBox& box, int n, int cap)
@@ -81,12 +74,6 @@ __global__ void __launch_bounds__(256) k_sor_grid_zero(const VoxBox* __restrict_
     __syncthreads();
     const int len = sg.ncell + 1;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < len; i += gridDim.x * blockDim.x) { cellA[(size_t)b * cellStride + i] = 0; cellB[(size_t)b * cellStride + i] = 0; }
-}
-__device__ __forceinline__ void sor_cell(const SorGrid& g, float x, float y, float z, int& cx, int& cy, int& cz)
-{
-    cx = min(max((int)((x - g.mn[0]) * g.inv), 0), g.dim[0] - 1);
-    cy = min(max((int)((y - g.mn[1]) * g.inv), 0), g.dim[1] - 1);
-    cz = min(max((int)((z - g.mn[2]) * g.inv), 0), g.dim[2] - 1);
 }
 __global__ void k_sor_cellcount(const cvr_point* __restrict__ pts, size_t stride, const SorGrid* __restrict__ grid, int* cellcnt, size_t cellStride,
                                 int* __restrict__ cellOfPt, size_t ptStride)
@@ -290,7 +277,7 @@ static int scan_cells(cvr_ctx* c, int B, int* cellstart, size_t cellStride, int 
 }
 
 // shared front half of the two outlier filters: bounding box (unless the producer accumulated it), grid, points sorted by cell
-static int sor_build_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox, float radius, SorGrid** gridOut, int** cellstartOut)
+int cvr_build_point_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox, float radius, SorGrid** gridOut, int** cellstartOut)
 {
     const int maxN = c->maxN;
     const size_t ptStride = (size_t)maxN;
@@ -338,7 +325,7 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     const int k = c->cl.sor_k;
     if (k < 1 || k + 1 > 320) { c->err = "sor_mean_k must be in [1, 319]"; return CVR_ERR_UNSUPPORTED; }
     SorGrid* grid; int* cellstart;
-    int rc = sor_build_grid(c, B, in, in_stride, n_in, haveBox, 0.f, &grid, &cellstart);
+    int rc = cvr_build_point_grid(c, B, in, in_stride, n_in, haveBox, 0.f, &grid, &cellstart);
     if (rc) return rc;
     const float4* sp = c->d_spts;
     const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B);
@@ -397,7 +384,7 @@ int cvr_launch_ror(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     const size_t ptStride = (size_t)maxN;
     const size_t cellStride = (size_t)c->sor_grid_cap + 2;
     SorGrid* grid; int* cellstart;
-    int rc = sor_build_grid(c, B, in, in_stride, n_in, false, radius, &grid, &cellstart);
+    int rc = cvr_build_point_grid(c, B, in, in_stride, n_in, false, radius, &grid, &cellstart);
     if (rc) return rc;
     k_ror_count<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B), 128, 0, c->stream>>>(c->d_spts, ptStride, grid, cellstart, cellStride, radius, min_pts, c->d_meand);
     LAUNCH_CHECK(c);

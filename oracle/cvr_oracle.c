@@ -773,3 +773,161 @@ void orc_remap_bilinear_u8(const uint8_t* src, size_t sstep, int sw, int sh, int
             }
         }
 }
+
+/* ---------------------------------------------------------------------------------------------------------------------
+ * pcl::IterativeClosestPoint<PointXYZRGB, PointXYZRGB>::align as MappingSystem.cpp:321-341 (and the earlier
+ * copy :104-127) configures it: setMaxCorrespondenceDistance(5), setMaximumIterations(50), setTransformationEpsilon(1e-8),
+ * setEuclideanFitnessEpsilon(1); every other setting at PCL's default (point-to-point, TransformationEstimationSVD, no
+ * reciprocal correspondences, no rejectors, identity guess).
+ * Restated from PCL's registration/impl/icp.hpp, correspondence_estimation.hpp, transformation_estimation_svd.hpp and
+ * default_convergence_criteria.hpp FROM MEMORY -- PCL is absent here and the reference calls are commented out / hold no
+ * vectors => PARITY UNPINNED (tests cross-check this file against numpy + scipy.cKDTree instead).
+ *   per iteration: nearest target point of every (already transformed) source point, kept iff d^2 <= max_dist^2 (f32 L2);
+ *   fewer than 3 correspondences => stop, not converged; Umeyama / SVD without scaling on the correspondences; the source is
+ *   transformed by the increment (f32, like pcl::transformPointCloud); final = increment * final; convergence:
+ *     iterations >= max                                            -> converged (ITERATIONS)
+ *     cos = (trace(R) - 1) / 2 >= 1 - transformation_epsilon  and  |t|^2 <= transformation_epsilon   -> converged (TRANSFORM)
+ *     mse = mean d^2 of the correspondences:  |mse - prev| < 1e-12                   -> converged (ABS_MSE)
+ *                                             |mse - prev| / prev < fitness_epsilon  -> converged (REL_MSE)
+ *   (prev starts at DBL_MAX, so the relative test first fires in the second iteration: with the reference's epsilon of 1 the
+ *   alignment ends after two iterations unless the error more than doubled.)
+ * Arithmetic here: distances and point transforms in f32 without FMA, sums / covariance / SVD in f64, the increment rounded to
+ * f32 before it is applied. */
+static void orc_svd3(double A[3][3], double U[3][3], double S[3], double V[3][3])
+{
+    /* one-sided Jacobi (Hestenes): rotate column pairs of A until they are orthogonal; A = U diag(S) V^T */
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) V[i][j] = i == j;
+    for (int sweep = 0; sweep < 60; sweep++) {
+        double off = 0;
+        for (int p = 0; p < 2; p++) for (int q = p + 1; q < 3; q++) {
+            double al = 0, be = 0, ga = 0;
+            for (int i = 0; i < 3; i++) { al += A[i][p] * A[i][p]; be += A[i][q] * A[i][q]; ga += A[i][p] * A[i][q]; }
+            if (fabs(ga) <= 1e-300 || fabs(ga) <= 1e-17 * sqrt(al * be)) continue;
+            off += fabs(ga);
+            const double zeta = (be - al) / (2.0 * ga);
+            const double t = (zeta >= 0 ? 1.0 : -1.0) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+            const double c = 1.0 / sqrt(1.0 + t * t), s = c * t;
+            for (int i = 0; i < 3; i++) {
+                const double ap = A[i][p], aq = A[i][q];
+                A[i][p] = c * ap - s * aq; A[i][q] = s * ap + c * aq;
+                const double vp = V[i][p], vq = V[i][q];
+                V[i][p] = c * vp - s * vq; V[i][q] = s * vp + c * vq;
+            }
+        }
+        if (off == 0) break;
+    }
+    for (int j = 0; j < 3; j++) { S[j] = sqrt(A[0][j] * A[0][j] + A[1][j] * A[1][j] + A[2][j] * A[2][j]); }
+    /* columns of U; a vanishing singular value gets the cross product of the other two (or any completion) */
+    int big[3] = { 0, 1, 2 };
+    for (int a = 0; a < 3; a++) for (int b2 = a + 1; b2 < 3; b2++) if (S[big[b2]] > S[big[a]]) { int t = big[a]; big[a] = big[b2]; big[b2] = t; }
+    const double tiny = 1e-12 * (S[big[0]] > 0 ? S[big[0]] : 1.0);
+    for (int r = 0; r < 3; r++) {
+        const int j = big[r];
+        if (S[j] > tiny) { for (int i = 0; i < 3; i++) U[i][j] = A[i][j] / S[j]; continue; }
+        double u[3];
+        if (r == 2) {       /* two good columns: complete with their cross product */
+            const int a = big[0], b2 = big[1];
+            u[0] = U[1][a] * U[2][b2] - U[2][a] * U[1][b2]; u[1] = U[2][a] * U[0][b2] - U[0][a] * U[2][b2]; u[2] = U[0][a] * U[1][b2] - U[1][a] * U[0][b2];
+        } else if (r == 1) { /* one good column: any unit vector orthogonal to it */
+            const int a = big[0];
+            const int m = fabs(U[0][a]) < fabs(U[1][a]) ? (fabs(U[0][a]) < fabs(U[2][a]) ? 0 : 2) : (fabs(U[1][a]) < fabs(U[2][a]) ? 1 : 2);
+            double e[3] = { 0, 0, 0 }; e[m] = 1;
+            const double d = U[m][a];
+            for (int i = 0; i < 3; i++) u[i] = e[i] - d * U[i][a];
+        } else { u[0] = 1; u[1] = 0; u[2] = 0; }
+        const double nn = sqrt(u[0] * u[0] + u[1] * u[1] + u[2] * u[2]);
+        for (int i = 0; i < 3; i++) U[i][j] = u[i] / nn;
+    }
+}
+static double orc_det3(double M[3][3])
+{
+    return M[0][0] * (M[1][1] * M[2][2] - M[1][2] * M[2][1]) - M[0][1] * (M[1][0] * M[2][2] - M[1][2] * M[2][0]) + M[0][2] * (M[1][0] * M[2][1] - M[1][1] * M[2][0]);
+}
+/* Umeyama without scaling from the 17 sums {n, sum src[3], sum dst[3], sum dst*src^T [9], sum d^2}: T (row-major 4x4, f32) */
+void orc_umeyama_from_sums(const double* sums, float* T)
+{
+    const double n = sums[0];
+    double ms[3], md[3], H[3][3];
+    for (int i = 0; i < 3; i++) { ms[i] = sums[1 + i] / n; md[i] = sums[4 + i] / n; }
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) H[i][j] = sums[7 + 3 * i + j] / n - md[i] * ms[j];   /* sigma = mean (d - md)(s - ms)^T */
+    double A[3][3], U[3][3], S[3], V[3][3];
+    memcpy(A, H, sizeof(A));
+    orc_svd3(A, U, S, V);
+    double sg[3] = { 1, 1, 1 };
+    if (orc_det3(U) * orc_det3(V) < 0) { int m = 0; for (int j = 1; j < 3; j++) if (S[j] < S[m]) m = j; sg[m] = -1; }
+    double R[3][3];
+    for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { double v = 0; for (int k = 0; k < 3; k++) v += U[i][k] * sg[k] * V[j][k]; R[i][j] = v; }
+    for (int i = 0; i < 3; i++) {
+        double t = md[i];
+        for (int j = 0; j < 3; j++) { T[4 * i + j] = (float)R[i][j]; t -= R[i][j] * ms[j]; }
+        T[4 * i + 3] = (float)t;
+    }
+    T[12] = T[13] = T[14] = 0.f; T[15] = 1.f;
+}
+static void orc_mat4_mul_f32(const float* A, const float* B, float* C)   /* C = A * B, f32 like Eigen::Matrix4f */
+{
+    float R[16];
+    for (int i = 0; i < 4; i++) for (int j = 0; j < 4; j++) { float v = 0.f; for (int k = 0; k < 4; k++) v += A[4 * i + k] * B[4 * k + j]; R[4 * i + j] = v; }
+    memcpy(C, R, sizeof(R));
+}
+/* state: 0 not converged (too few correspondences), 1 ITERATIONS, 2 TRANSFORM, 3 ABS_MSE, 4 REL_MSE */
+int orc_icp(const orc_point* src, int ns, const orc_point* tgt, int nt, double max_dist, int max_iter, double trans_eps, double fit_eps,
+            float* T_out, orc_point* aligned, int* iters_out, double* fitness_out, int* corr_out)
+{
+    orc_point* cur = (orc_point*)malloc(sizeof(orc_point) * (size_t)(ns > 0 ? ns : 1));
+    memcpy(cur, src, sizeof(orc_point) * (size_t)ns);
+    float Tf[16] = { 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+    const float md2 = (float)(max_dist * max_dist);
+    double prev_mse = DBL_MAX;
+    int state = 0, it = 0, ncorr = 0;
+    for (;;) {
+        double sums[17];
+        for (int i = 0; i < 17; i++) sums[i] = 0;
+        for (int i = 0; i < ns; i++) {
+            float best = FLT_MAX; int bj = -1;
+            for (int j = 0; j < nt; j++) {
+                const float dx = cur[i].x - tgt[j].x, dy = cur[i].y - tgt[j].y, dz = cur[i].z - tgt[j].z;
+                float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
+                if (d < best) { best = d; bj = j; }
+            }
+            if (bj < 0 || best > md2) continue;
+            const double s[3] = { cur[i].x, cur[i].y, cur[i].z }, d3[3] = { tgt[bj].x, tgt[bj].y, tgt[bj].z };
+            sums[0] += 1;
+            for (int a = 0; a < 3; a++) { sums[1 + a] += s[a]; sums[4 + a] += d3[a]; for (int b2 = 0; b2 < 3; b2++) sums[7 + 3 * a + b2] += d3[a] * s[b2]; }
+            sums[16] += (double)best;
+        }
+        ncorr = (int)sums[0];
+        if (ncorr < 3) { state = 0; break; }
+        float Ti[16];
+        orc_umeyama_from_sums(sums, Ti);
+        orc_transform_cloud(cur, ns, Ti, cur);
+        orc_mat4_mul_f32(Ti, Tf, Tf);
+        it++;
+        if (it >= max_iter) { state = 1; break; }
+        const double cosang = 0.5 * ((double)Ti[0] + (double)Ti[5] + (double)Ti[10] - 1.0);
+        const double tsq = (double)Ti[3] * Ti[3] + (double)Ti[7] * Ti[7] + (double)Ti[11] * Ti[11];
+        if (cosang >= 1.0 - trans_eps && tsq <= trans_eps) { state = 2; break; }
+        const double mse = sums[16] / sums[0];
+        if (fabs(mse - prev_mse) < 1e-12) { state = 3; break; }
+        if (fabs(mse - prev_mse) / prev_mse < fit_eps) { state = 4; break; }
+        prev_mse = mse;
+    }
+    /* getFitnessScore(): mean squared distance of every aligned source point to its nearest target point */
+    double fs = 0; int fn = 0;
+    for (int i = 0; i < ns && nt > 0; i++) {
+        float best = FLT_MAX;
+        for (int j = 0; j < nt; j++) {
+            const float dx = cur[i].x - tgt[j].x, dy = cur[i].y - tgt[j].y, dz = cur[i].z - tgt[j].z;
+            float d = dx * dx; d = d + dy * dy; d = d + dz * dz;
+            if (d < best) best = d;
+        }
+        fs += (double)best; fn++;
+    }
+    if (T_out) memcpy(T_out, Tf, sizeof(Tf));
+    if (aligned) memcpy(aligned, cur, sizeof(orc_point) * (size_t)ns);
+    if (iters_out) *iters_out = it;
+    if (fitness_out) *fitness_out = fn ? fs / fn : 0.0;
+    if (corr_out) *corr_out = ncorr;
+    free(cur);
+    return state;
+}

@@ -260,3 +260,26 @@ if os.path.dirname(_HERE) not in _sys.path:
 _synth = _il.import_module("master-thesis_b200.synth")
 synth_pair = _synth.synth_pair
 satdrift_pair = _synth.satdrift_pair
+
+
+def icp(source, target, max_dist=5.0, max_iter=50, trans_eps=1e-8, fit_eps=1.0):
+    """pcl::IterativeClosestPoint::align with the reference's settings (MappingSystem.cpp:321-341); brute-force neighbours.
+    Returns (T 4x4 f32, aligned points, iterations, fitness score, state, correspondences of the last iteration)."""
+    src = np.ascontiguousarray(source, POINT_DTYPE)
+    tgt = np.ascontiguousarray(target, POINT_DTYPE)
+    T = np.zeros(16, np.float32)
+    out = np.empty(max(len(src), 1), POINT_DTYPE)
+    it, nc = C.c_int(0), C.c_int(0)
+    fit = C.c_double(0)
+    L = lib()
+    L.orc_icp.restype = C.c_int
+    st = L.orc_icp(_p(src), len(src), _p(tgt), len(tgt), C.c_double(max_dist), int(max_iter), C.c_double(trans_eps), C.c_double(fit_eps),
+                   _p(T), _p(out), C.byref(it), C.byref(fit), C.byref(nc))
+    return T.reshape(4, 4).copy(), out[:len(src)].copy(), it.value, fit.value, st, nc.value
+
+
+def umeyama_from_sums(sums):
+    s = np.ascontiguousarray(sums, np.float64)
+    T = np.zeros(16, np.float32)
+    lib().orc_umeyama_from_sums(_p(s), _p(T))
+    return T.reshape(4, 4).copy()
