@@ -2,7 +2,7 @@
 // cv_reconstruct/src/system/MappingSystem.cpp:321-341 (and the earlier copy :104-127): setMaxCorrespondenceDistance(5),
 // setMaximumIterations(50), setTransformationEpsilon(1e-8), setEuclideanFitnessEpsilon(1); point-to-point, SVD (Umeyama without
 // scaling), no reciprocal correspondences, no rejectors, identity guess.  PCL is absent from this image: the rules below follow
-// PCL's registration/impl/icp.hpp and default_convergence_criteria.hpp as restated in oracle/cvr_oracle.c ("parity unpinned").
+// PCL's registration/impl/icp.hpp and default_convergence_criteria.hpp as written down in DESIGN.md section 7 ("parity unpinned").
 //
 // Per iteration, on the device: nearest target point of every source point through the uniform grid the outlier filters use
 // (expanding cubic shells with a proven stop; ties go to the lower point index, like a linear scan), and the 17 sums the
