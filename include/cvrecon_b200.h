@@ -133,6 +133,17 @@ int cvr_rectify(cvr_ctx* ctx, int channels, const uint8_t* left, size_t step_lef
 /* Test hook: copies the maps of one camera (0 = left, 1 = right) to the host: map1 = H*W*2 int16, map2 = H*W uint16. */
 int cvr_get_rectification_maps(cvr_ctx* ctx, int camera, int16_t* map1, uint16_t* map2);
 
+/* SURVEY 8(f) row n1 -- the step before the path.  Replaces: the two cv::imdecode(message.LeftImageData / RightImageData,
+ * cv::IMREAD_COLOR) calls of MessageConverter::ConvertStereoMessage (cv_reconstruct/src/server/MessageConverter.cpp:65-66) for a
+ * batch of n PNG files (what the streamers produce with cv::imencode(".png", ...)): zlib inflate and the PNG scanline filters on
+ * the device, output = 8UC3 frames in B, G, R order exactly as cv::imdecode returns them (image i at bgr + i * image_stride, rows
+ * `step` bytes apart), in host or device memory according to mem_out -- device output can be handed to cvr_submit_batch as a
+ * CVR_MEM_DEVICE input without ever touching the host.  png[i] / png_bytes[i] are host pointers / sizes of the encoded files.
+ * Every image must have the context's width x height.  Decoded on the device: 8-bit, non-interlaced, colour types gray, RGB and
+ * RGBA (alpha dropped); other PNG flavours return CVR_ERR_UNSUPPORTED, a damaged stream CVR_ERR_INVALID_ARG. */
+int cvr_decode_png_batch(cvr_ctx* ctx, int n, const uint8_t* const* png, const size_t* png_bytes, int mem_out, uint8_t* bgr, size_t step,
+                         size_t image_stride);
+
 /* Replaces: TrackingFrame::SetupFrame + PruneDisparityImage (TrackingFrame.cpp:25-67).
  * disp is pruned in place; disp_f32 (CV_32F, tight W*4 step) and mask (CV_8U, tight) are outputs
  * and may be NULL. */

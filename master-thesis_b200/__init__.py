@@ -36,7 +36,7 @@ EXPORTS = [
     "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
     "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps", "cvr_suggest_batch",
     "cvr_comm_get_unique_id", "cvr_comm_init", "cvr_comm_attach", "cvr_comm_destroy", "cvr_gather_clouds", "cvr_gather_layout",
-    "cvr_filter_cloud", "cvr_icp_default_params", "cvr_icp_align",
+    "cvr_filter_cloud", "cvr_icp_default_params", "cvr_icp_align", "cvr_decode_png_batch",
 ]
 COMM_ID_BYTES = 128
 
@@ -141,6 +141,7 @@ def load_library():
     lib.cvr_icp_default_params.argtypes = [C.POINTER(IcpParams)]
     lib.cvr_icp_default_params.restype = None
     lib.cvr_icp_align.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.POINTER(IcpParams), C.c_void_p, C.POINTER(IcpResult)]
+    lib.cvr_decode_png_batch.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t), C.c_int, C.c_void_p, C.c_size_t, C.c_size_t]
     lib.cvr_comm_get_unique_id.argtypes = [C.c_void_p]
     lib.cvr_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
     lib.cvr_comm_attach.argtypes = [C.c_void_p, C.c_void_p]
@@ -348,6 +349,22 @@ class Reconstruct3D:
         m2 = np.empty((self.H, self.W), np.uint16)
         self._check(self.lib.cvr_get_rectification_maps(self.ctx, int(camera), _ptr(m1), _ptr(m2)))
         return m1, m2
+
+    # -- cv::imdecode(png, IMREAD_COLOR) x n (MessageConverter.cpp:65-66) --
+    def DecodePNG(self, files, device_out=None):
+        """files: list of bytes objects (PNG files).  Returns an (n, H, W, 3) uint8 array, or fills device_out (a device pointer to
+        n dense frames) when given."""
+        n = len(files)
+        bufs = [np.frombuffer(f, np.uint8) for f in files]
+        ptrs = (C.c_void_p * n)(*[b.ctypes.data for b in bufs])
+        sizes = (C.c_size_t * n)(*[len(b) for b in bufs])
+        step, stride = self.W * 3, self.W * 3 * self.H
+        if device_out is not None:
+            self._check(self.lib.cvr_decode_png_batch(self.ctx, n, ptrs, sizes, MEM_DEVICE, C.c_void_p(device_out), step, stride))
+            return None
+        out = np.empty((n, self.H, self.W, 3), np.uint8)
+        self._check(self.lib.cvr_decode_png_batch(self.ctx, n, ptrs, sizes, MEM_HOST, _ptr(out), step, stride))
+        return out
 
     # -- Reconstruct3D::GenerateDisparityMap (Reconstruct3D.cpp:72-84) --
     def GenerateDisparityMap(self, leftImage, rightImage):

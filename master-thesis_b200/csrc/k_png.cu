@@ -1,0 +1,406 @@
+// k_png.cu -- SURVEY 8(f) row n1, the step BEFORE the path: the two cv::imdecode(message.*ImageData, cv::IMREAD_COLOR) calls of
+// MessageConverter::ConvertStereoMessage (cv_reconstruct/src/server/MessageConverter.cpp:65-66).  The streamers send every frame
+// as a PNG made by cv::imencode(".png", img) (kitti_vision_streamer/src/main.cpp:217-220, stereopi_video_streamer/src/main.cpp:
+// 230-231; wire format network_protocol/src/core/StereoStream.cpp:69-126), so at the rate the path now runs the host would have to
+// inflate thousands of PNGs per second.  Here a batch of PNG files is decoded on the device into the BGR frames the path reads:
+//   host      : walk the chunk list of each file (signature, IHDR, the IDAT segments) -- byte bookkeeping only
+//   k_png_idat: the IDAT payloads of every file -> one contiguous zlib stream per image
+//   k_png_inflate: zlib / DEFLATE (stored, fixed and dynamic Huffman blocks), ONE WARP PER IMAGE: the lanes keep an input ring
+//               and the 32 KiB sliding window in shared memory full / flushed with coalesced accesses, lane 0 walks the bit stream
+//               (first-level Huffman tables in shared memory, canonical-code search for the rare longer codes)
+//   k_png_unfilter: the five PNG scanline filters (None / Sub / Up / Average / Paeth, sequential per image where the filter
+//               demands it, the colour chains of a row in parallel) and the channel order of IMREAD_COLOR (RGB(A) / gray -> BGR)
+// Supported: 8-bit, non-interlaced, colour types 0 (gray), 2 (RGB) and 6 (RGBA; alpha dropped as IMREAD_COLOR does).  Anything
+// else is refused with CVR_ERR_UNSUPPORTED (the caller keeps its host decoder for such files).  Results are bit-exact against
+// cv2.imdecode (tests/test_png.py): PNG is lossless, there is exactly one right answer.
+#include "cvr_internal.cuh"
+#include <string.h>
+
+struct PngImg {                 // per image, built on the host
+    long long fileOff;          // offset of the file in the uploaded byte blob
+    int segFirst, segCount;     // its IDAT segments in the segment table
+    long long zOff, zLen;       // offset / length of its zlib stream in the gathered buffer
+    int colorType, bpp;         // 0 / 2 / 6; bytes per pixel 1 / 3 / 4
+    int status;                 // device: 0 ok, else an error code of the inflater
+};
+struct PngSeg { long long src, dst; int len; int img; };
+
+__global__ void k_png_idat(const uint8_t* __restrict__ blob, const PngSeg* __restrict__ segs, int nseg, uint8_t* __restrict__ z)
+{
+    for (int s = blockIdx.x; s < nseg; s += gridDim.x) {
+        const PngSeg g = segs[s];
+        for (int i = threadIdx.x; i < g.len; i += blockDim.x) z[g.dst + i] = blob[g.src + i];
+    }
+}
+
+// ---- inflate ---------------------------------------------------------------------------------------------------------
+#define PNG_INRING 2048         // bytes of input kept in shared memory (power of two; half of it exceeds the longest dynamic block header)
+#define PNG_WIN 32768           // DEFLATE's sliding window = the output ring
+#define PNG_LBITS 10            // first-level table bits, literal/length codes
+#define PNG_DBITS 8             // ... distance codes
+struct Huff {                   // canonical code: counts per length, symbols sorted by (length, symbol)
+    unsigned short count[16];
+    unsigned short symbol[288];
+};
+struct InflateSm {
+    uint8_t in[PNG_INRING];
+    uint8_t win[PNG_WIN];
+    unsigned short ltab[1 << PNG_LBITS];   // (length << 9) | symbol; 0 = code longer than the table
+    unsigned short dtab[1 << PNG_DBITS];
+    Huff lh, dh;
+    unsigned short lens[320];
+};
+
+__device__ __forceinline__ int huff_build(Huff& h, const unsigned short* lens, int n, unsigned short* tab, int tbits)
+{
+    for (int i = 0; i < 16; i++) h.count[i] = 0;
+    for (int i = 0; i < n; i++) h.count[lens[i]]++;
+    if (h.count[0] == n) { for (int i = 0; i < (1 << tbits); i++) tab[i] = 0; return 0; }   // no codes at all (legal for the distance alphabet)
+    int left = 1;
+    for (int l = 1; l < 16; l++) { left <<= 1; left -= h.count[l]; if (left < 0) return -1; }   // over-subscribed
+    unsigned short offs[16];
+    offs[1] = 0;
+    for (int l = 1; l < 15; l++) offs[l + 1] = offs[l] + h.count[l];
+    for (int i = 0; i < n; i++) if (lens[i]) h.symbol[offs[lens[i]]++] = (unsigned short)i;
+    // first-level table: every tbits-bit pattern whose low bits are a (bit-reversed) code of length <= tbits
+    for (int i = 0; i < (1 << tbits); i++) tab[i] = 0;
+    int code = 0, idx = 0;
+    for (int l = 1; l <= tbits; l++) {
+        for (int k = 0; k < h.count[l]; k++, idx++, code++) {
+            unsigned rev = __brev((unsigned)code) >> (32 - l);
+            const unsigned short e = (unsigned short)((l << 9) | h.symbol[idx]);
+            for (unsigned f = rev; f < (1u << tbits); f += (1u << l)) tab[f] = e;
+        }
+        code <<= 1;
+    }
+    return left > 0 ? 1 : 0;    // incomplete codes are tolerated where zlib tolerates them (single distance code)
+}
+
+struct BitIn {
+    unsigned long long bb; int bc;      // bit buffer (LSB first) and number of valid bits
+    long long pos;                      // next input byte to enter the buffer
+};
+
+// One warp per image.  Returns through img.status: 0 ok, 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol /
+// distance, 5 output overrun, 6 input overrun, 7 stored-block length check.
+__global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ z, PngImg* imgs, uint8_t* __restrict__ raw, long long rawStride, long long rawLen)
+{
+    extern __shared__ __align__(16) unsigned char ism[];
+    InflateSm& S = *(InflateSm*)ism;
+    const int lane = threadIdx.x;
+    PngImg& im = imgs[blockIdx.x];
+    const uint8_t* in = z + im.zOff;
+    const long long inLen = im.zLen;
+    uint8_t* out = raw + (long long)blockIdx.x * rawStride;
+    // the input ring holds bytes [inBase, inBase + PNG_INRING); refilled in halves by all lanes
+    long long inBase = 0;
+    for (int i = lane; i < PNG_INRING; i += 32) S.in[i] = (long long)i < inLen ? in[i] : 0;
+    __syncwarp();
+    BitIn b; b.bb = 0; b.bc = 0; b.pos = 0;
+    long long outPos = 0, flushed = 0;
+    int status = 0, done = 0;
+    // decoder state that survives the cooperative refill / flush points
+    int phase = 0;                  // 0 block header, 1 stored copy, 2 huffman symbols
+    int last = 0, storedLeft = 0;
+    int pendLen = 0, pendDist = 0;  // a match being copied
+    while (true) {
+        if (lane == 0 && !done && !status) {
+            // lane 0 runs until it has eaten half of the input ring, filled half of the window since the last flush, or finished
+            const long long inStop = inBase + PNG_INRING / 2, outStop = flushed + PNG_WIN / 2;
+#define NEED(n) while (b.bc < (n)) { b.bb |= (unsigned long long)S.in[b.pos & (PNG_INRING - 1)] << b.bc; b.bc += 8; b.pos++; }
+#define TAKE(n) (b.bb & ((1ull << (n)) - 1)); b.bb >>= (n); b.bc -= (n)
+            if (outPos == 0 && b.pos == 0) {                           // zlib header
+                NEED(16);
+                const unsigned cmf = (unsigned)TAKE(8); const unsigned flg = (unsigned)TAKE(8);
+                if ((cmf & 15) != 8 || ((cmf << 8) | flg) % 31 != 0 || (flg & 32)) status = 1;
+            }
+            while (!status && !done && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
+                if (b.pos - 8 > inLen + 8) { status = 6; break; }
+                if (phase == 0) {
+                    NEED(3);
+                    last = (int)TAKE(1);
+                    const int type = (int)TAKE(2);
+                    if (type == 0) {
+                        const int drop = b.bc & 7; b.bb >>= drop; b.bc -= drop;       // to the byte boundary
+                        NEED(32);
+                        const unsigned len = (unsigned)TAKE(16); const unsigned nlen = (unsigned)TAKE(16);
+                        if ((len ^ 0xffffu) != nlen) { status = 7; break; }
+                        storedLeft = (int)len; phase = 1;
+                    } else if (type == 1) {
+                        for (int i = 0; i < 144; i++) S.lens[i] = 8;
+                        for (int i = 144; i < 256; i++) S.lens[i] = 9;
+                        for (int i = 256; i < 280; i++) S.lens[i] = 7;
+                        for (int i = 280; i < 288; i++) S.lens[i] = 8;
+                        huff_build(S.lh, S.lens, 288, S.ltab, PNG_LBITS);
+                        for (int i = 0; i < 30; i++) S.lens[i] = 5;
+                        huff_build(S.dh, S.lens, 30, S.dtab, PNG_DBITS);
+                        phase = 2;
+                    } else if (type == 2) {
+                        NEED(14);
+                        const int nlen = (int)TAKE(5) + 257; const int ndist = (int)TAKE(5) + 1; const int ncode = (int)TAKE(4) + 4;
+                        if (nlen > 286 || ndist > 30) { status = 3; break; }
+                        const unsigned char order[19] = { 16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15 };
+                        for (int i = 0; i < 19; i++) S.lens[i] = 0;
+                        for (int i = 0; i < ncode; i++) { NEED(3); S.lens[order[i]] = (unsigned short)TAKE(3); }
+                        if (huff_build(S.lh, S.lens, 19, S.ltab, 7) < 0) { status = 3; break; }   // the code-length code (7-bit table in ltab)
+                        int idx = 0;
+                        unsigned short* ll = S.lens + 0;                // decoded lengths are written over lens[] after the 19 are consumed:
+                        unsigned short tmp[320];                        // ... so collect them in local memory first
+                        while (idx < nlen + ndist) {
+                            NEED(7);
+                            const unsigned short e = S.ltab[b.bb & 127];
+                            if (!e) { status = 3; break; }
+                            const int l = e >> 9, sym = e & 511;
+                            b.bb >>= l; b.bc -= l;
+                            if (sym < 16) tmp[idx++] = (unsigned short)sym;
+                            else {
+                                int rep, val = 0;
+                                if (sym == 16) { if (idx == 0) { status = 3; break; } val = tmp[idx - 1]; NEED(2); rep = 3 + (int)TAKE(2); }
+                                else if (sym == 17) { NEED(3); rep = 3 + (int)TAKE(3); }
+                                else { NEED(7); rep = 11 + (int)TAKE(7); }
+                                if (idx + rep > nlen + ndist) { status = 3; break; }
+                                while (rep--) tmp[idx++] = (unsigned short)val;
+                            }
+                        }
+                        if (status) break;
+                        if (tmp[256] == 0) { status = 3; break; }      // no end-of-block code
+                        for (int i = 0; i < nlen; i++) ll[i] = tmp[i];
+                        if (huff_build(S.lh, ll, nlen, S.ltab, PNG_LBITS) != 0 && !(S.lh.count[0] + S.lh.count[1] == nlen)) { status = 3; break; }
+                        for (int i = 0; i < ndist; i++) ll[i] = tmp[nlen + i];
+                        if (huff_build(S.dh, ll, ndist, S.dtab, PNG_DBITS) < 0) { status = 3; break; }
+                        phase = 2;
+                    } else { status = 2; break; }
+                } else if (phase == 1) {
+                    // stored bytes: straight from the bit buffer / input ring into the window
+                    while (storedLeft > 0 && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
+                        NEED(8);
+                        S.win[outPos & (PNG_WIN - 1)] = (uint8_t)TAKE(8);
+                        outPos++; storedLeft--;
+                    }
+                    if (storedLeft == 0) { phase = 0; if (last) done = 1; }
+                } else {
+                    if (pendLen > 0) {                                 // continue a match that was cut by a flush point
+                        while (pendLen > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - pendDist) & (PNG_WIN - 1)]; outPos++; pendLen--; }
+                        if (pendLen > 0) break;
+                    }
+                    NEED(48);
+                    unsigned short e = S.ltab[b.bb & ((1u << PNG_LBITS) - 1)];
+                    int l, sym;
+                    if (e) { l = e >> 9; sym = e & 511; }
+                    else {                                             // longer than the table: canonical search from length PNG_LBITS + 1
+                        int code = 0, first = 0, index = 0; l = 0; sym = -1;
+                        for (int len = 1; len <= 15; len++) {
+                            code |= (int)((b.bb >> (len - 1)) & 1);
+                            const int cnt = S.lh.count[len];
+                            if (code - cnt < first) { sym = S.lh.symbol[index + (code - first)]; l = len; break; }
+                            index += cnt; first += cnt; first <<= 1; code <<= 1;
+                        }
+                        if (sym < 0) { status = 4; break; }
+                    }
+                    b.bb >>= l; b.bc -= l;
+                    if (sym < 256) { S.win[outPos & (PNG_WIN - 1)] = (uint8_t)sym; outPos++; }
+                    else if (sym == 256) { phase = 0; if (last) done = 1; }
+                    else {
+                        sym -= 257;
+                        if (sym >= 29) { status = 4; break; }
+                        const unsigned short lbase[29] = { 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258 };
+                        const unsigned char lext[29] = { 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0 };
+                        int len = lbase[sym] + (int)(b.bb & ((1u << lext[sym]) - 1));
+                        b.bb >>= lext[sym]; b.bc -= lext[sym];
+                        unsigned short de = S.dtab[b.bb & ((1u << PNG_DBITS) - 1)];
+                        int dl, ds;
+                        if (de) { dl = de >> 9; ds = de & 511; }
+                        else {
+                            int code = 0, first = 0, index = 0; dl = 0; ds = -1;
+                            for (int q = 1; q <= 15; q++) {
+                                code |= (int)((b.bb >> (q - 1)) & 1);
+                                const int cnt = S.dh.count[q];
+                                if (code - cnt < first) { ds = S.dh.symbol[index + (code - first)]; dl = q; break; }
+                                index += cnt; first += cnt; first <<= 1; code <<= 1;
+                            }
+                            if (ds < 0) { status = 4; break; }
+                        }
+                        b.bb >>= dl; b.bc -= dl;
+                        if (ds >= 30) { status = 4; break; }
+                        const unsigned short dbase[30] = { 1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577 };
+                        const unsigned char dext[30] = { 0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13 };
+                        const int dist = dbase[ds] + (int)(b.bb & ((1u << dext[ds]) - 1));
+                        b.bb >>= dext[ds]; b.bc -= dext[ds];
+                        if ((long long)dist > outPos) { status = 4; break; }
+                        pendDist = dist;
+                        while (len > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - dist) & (PNG_WIN - 1)]; outPos++; len--; }
+                        pendLen = len;
+                    }
+                }
+                if (outPos > rawLen) { status = 5; break; }
+            }
+#undef NEED
+#undef TAKE
+        }
+        // ---- cooperative part: flush finished window halves, refill consumed input halves ----
+        done = __shfl_sync(0xffffffffu, done, 0); status = __shfl_sync(0xffffffffu, status, 0);
+        outPos = __shfl_sync(0xffffffffu, outPos, 0);
+        const long long consumed = __shfl_sync(0xffffffffu, b.pos - (b.bc >> 3), 0);
+        const long long upto = (done || status) ? outPos : (outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);   // whole halves, or everything at the end
+        for (long long i = flushed + lane; i < upto && i < rawLen; i += 32) out[i] = S.win[i & (PNG_WIN - 1)];
+        flushed = upto > flushed ? upto : flushed;
+        if (done || status) break;
+        while (consumed >= inBase + PNG_INRING / 2) {                   // the older half of the ring is free: bring in the next bytes
+            const long long src = inBase + PNG_INRING;
+            for (int i = lane; i < PNG_INRING / 2; i += 32) S.in[(src + i) & (PNG_INRING - 1)] = (src + i) < inLen ? in[src + i] : 0;
+            inBase += PNG_INRING / 2;
+        }
+        __syncwarp();
+    }
+    if (lane == 0) im.status = status ? status : (outPos == rawLen ? 0 : 5);
+}
+
+// ---- scanline filters + channel order --------------------------------------------------------------------------------
+__device__ __forceinline__ int paeth(int a, int b, int c)
+{
+    const int p = a + b - c, pa = abs(p - a), pb = abs(p - b), pc = abs(p - c);
+    return (pa <= pb && pa <= pc) ? a : (pb <= pc ? b : c);
+}
+// One warp per image, rows top-down (Up / Average / Paeth need the row above).  Lane c < bpp owns the chain of channel c along the
+// row for Sub / Average / Paeth (each byte depends on the byte bpp positions to its left); None and Up rows are done by all lanes.
+// The reconstructed bytes are written back over the raw scanline (so the next row finds its "prior" there), then the row is
+// converted to BGR with all lanes.
+__global__ void __launch_bounds__(32) k_png_unfilter(uint8_t* raw, long long rawStride, const PngImg* __restrict__ imgs, int W, int H,
+                                                     uint8_t* __restrict__ dst, size_t step, size_t imgStride)
+{
+    const int lane = threadIdx.x;
+    const PngImg im = imgs[blockIdx.x];
+    if (im.status) return;
+    const int bpp = im.bpp, rowBytes = W * bpp;
+    uint8_t* base = raw + (long long)blockIdx.x * rawStride;
+    uint8_t* o = dst + (size_t)blockIdx.x * imgStride;
+    for (int y = 0; y < H; y++) {
+        uint8_t* cur = base + (long long)y * (rowBytes + 1) + 1;
+        const uint8_t* up = y ? cur - (rowBytes + 1) : nullptr;
+        const int ft = cur[-1];
+        if (ft == 0) { /* None */ }
+        else if (ft == 2) { if (up) for (int i = lane; i < rowBytes; i += 32) cur[i] = (uint8_t)(cur[i] + up[i]); }
+        else if (lane < bpp) {
+            int a = 0, c = 0;                                          // left and upper-left of this channel
+            for (int i = lane; i < rowBytes; i += bpp) {
+                const int b = up ? up[i] : 0;
+                int v = cur[i];
+                if (ft == 1) v += a;
+                else if (ft == 3) v += (a + b) >> 1;
+                else if (ft == 4) v += paeth(a, b, c);
+                v &= 255;
+                cur[i] = (uint8_t)v;
+                a = v; c = b;
+            }
+        }
+        __syncwarp();
+        uint8_t* orow = o + (size_t)y * step;
+        for (int x = lane; x < W; x += 32) {                            // IMREAD_COLOR: 8UC3 in B, G, R order
+            uint8_t r, g, bl;
+            if (bpp == 1) r = g = bl = cur[x];
+            else { r = cur[x * bpp]; g = cur[x * bpp + 1]; bl = cur[x * bpp + 2]; }
+            orow[3 * x] = bl; orow[3 * x + 1] = g; orow[3 * x + 2] = r;
+        }
+        __syncwarp();
+    }
+}
+
+// ---- host ------------------------------------------------------------------------------------------------------------
+static unsigned be32(const uint8_t* p) { return ((unsigned)p[0] << 24) | ((unsigned)p[1] << 16) | ((unsigned)p[2] << 8) | p[3]; }
+
+extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png, const size_t* png_bytes, int mem_out, uint8_t* bgr, size_t step, size_t image_stride)
+{
+    if (!c) return CVR_ERR_INVALID_ARG;
+    const int W = c->prm.width, H = c->prm.height;
+    if (n < 1 || !png || !png_bytes || !bgr || step < (size_t)W * 3 || image_stride < step * (size_t)H || (mem_out != CVR_MEM_HOST && mem_out != CVR_MEM_DEVICE)) {
+        c->err = "cvr_decode_png_batch: bad argument"; return CVR_ERR_INVALID_ARG;
+    }
+    static const uint8_t sig[8] = { 0x89, 'P', 'N', 'G', 0x0d, 0x0a, 0x1a, 0x0a };
+    std::vector<PngImg> imgs((size_t)n);
+    std::vector<PngSeg> segs;
+    long long blobLen = 0, zTotal = 0;
+    for (int i = 0; i < n; i++) {
+        const uint8_t* f = png[i];
+        const size_t len = png_bytes[i];
+        if (!f || len < 8 + 25 || memcmp(f, sig, 8) != 0) { c->err = "cvr_decode_png_batch: not a PNG file"; return CVR_ERR_INVALID_ARG; }
+        PngImg& im = imgs[(size_t)i];
+        im.fileOff = blobLen; im.segFirst = (int)segs.size(); im.segCount = 0; im.zOff = zTotal; im.zLen = 0; im.status = 0; im.colorType = -1; im.bpp = 0;
+        size_t p = 8;
+        bool end = false;
+        while (!end && p + 12 <= len) {
+            const unsigned clen = be32(f + p);
+            const uint8_t* type = f + p + 4;
+            if ((size_t)clen > len - p - 12) { c->err = "cvr_decode_png_batch: truncated PNG chunk"; return CVR_ERR_INVALID_ARG; }
+            if (!memcmp(type, "IHDR", 4)) {
+                if (clen != 13) { c->err = "cvr_decode_png_batch: bad IHDR"; return CVR_ERR_INVALID_ARG; }
+                const uint8_t* d = f + p + 8;
+                const unsigned w = be32(d), h = be32(d + 4);
+                const int depth = d[8], ct = d[9], interlace = d[12];
+                if ((int)w != W || (int)h != H) { c->err = "cvr_decode_png_batch: image size differs from the context's width x height"; return CVR_ERR_INVALID_ARG; }
+                if (depth != 8 || !(ct == 0 || ct == 2 || ct == 6) || interlace != 0 || d[10] != 0 || d[11] != 0) {
+                    c->err = "cvr_decode_png_batch: only 8-bit non-interlaced gray / RGB / RGBA PNGs are decoded on the device"; return CVR_ERR_UNSUPPORTED;
+                }
+                im.colorType = ct; im.bpp = ct == 0 ? 1 : (ct == 2 ? 3 : 4);
+            } else if (!memcmp(type, "IDAT", 4)) {
+                if (clen) { PngSeg s; s.src = blobLen + (long long)p + 8; s.dst = zTotal + im.zLen; s.len = (int)clen; s.img = i; segs.push_back(s); im.zLen += clen; im.segCount++; }
+            } else if (!memcmp(type, "IEND", 4)) end = true;
+            p += 12 + (size_t)clen;
+        }
+        if (im.colorType < 0 || im.zLen < 6) { c->err = "cvr_decode_png_batch: PNG without IHDR / IDAT"; return CVR_ERR_INVALID_ARG; }
+        blobLen += (long long)len;
+        zTotal += im.zLen;
+    }
+    CVR_CUDA(c, cudaSetDevice(c->device));
+    const long long rawStride = ((long long)H * ((long long)W * 4 + 1) + 15) & ~15LL;     // room for RGBA scanlines + filter bytes
+    const size_t needBlob = (size_t)blobLen + 16, needZ = (size_t)zTotal + 16, needRaw = (size_t)rawStride * n, needOut = (size_t)W * 3 * H * n;
+    auto grow = [&](uint8_t** p, size_t* cap, size_t need) -> int {
+        if (*cap >= need) return CVR_OK;
+        if (*p) cudaFree(*p);
+        *p = nullptr; *cap = 0;
+        CVR_CUDA(c, cudaMalloc((void**)p, need + need / 4));
+        *cap = need + need / 4;
+        return CVR_OK;
+    };
+    int rc;
+    if ((rc = grow(&c->png_blob, &c->png_blob_cap, needBlob)) || (rc = grow(&c->png_z, &c->png_z_cap, needZ)) || (rc = grow(&c->png_raw, &c->png_raw_cap, needRaw)) ||
+        (rc = grow(&c->png_tab, &c->png_tab_cap, sizeof(PngImg) * (size_t)n + sizeof(PngSeg) * segs.size() + 64))) return rc;
+    uint8_t* dOut = bgr; size_t dStep = step, dStride = image_stride;
+    if (mem_out == CVR_MEM_HOST) {
+        if ((rc = grow(&c->png_out, &c->png_out_cap, needOut))) return rc;
+        dOut = c->png_out; dStep = (size_t)W * 3; dStride = dStep * H;
+    }
+    long long off = 0;
+    for (int i = 0; i < n; i++) { CVR_CUDA(c, cudaMemcpyAsync(c->png_blob + off, png[i], png_bytes[i], cudaMemcpyHostToDevice, c->stream)); off += (long long)png_bytes[i]; }
+    PngImg* dImgs = (PngImg*)c->png_tab;
+    PngSeg* dSegs = (PngSeg*)(c->png_tab + ((sizeof(PngImg) * (size_t)n + 15) & ~(size_t)15));
+    CVR_CUDA(c, cudaMemcpyAsync(dImgs, imgs.data(), sizeof(PngImg) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
+    CVR_CUDA(c, cudaMemcpyAsync(dSegs, segs.data(), sizeof(PngSeg) * segs.size(), cudaMemcpyHostToDevice, c->stream));
+    k_png_idat<<<(unsigned)(segs.size() < 4096 ? segs.size() : 4096), 128, 0, c->stream>>>(c->png_blob, dSegs, (int)segs.size(), c->png_z);
+    LAUNCH_CHECK(c);
+    CVR_CUDA(c, cudaFuncSetAttribute(k_png_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(InflateSm)));
+    // every image inflates to H scanlines of 1 + W * bpp bytes; the images of a batch may differ in colour type
+    std::vector<long long> rawLens((size_t)n);
+    bool same = true;
+    for (int i = 0; i < n; i++) { rawLens[(size_t)i] = (long long)H * ((long long)W * imgs[(size_t)i].bpp + 1); same = same && rawLens[(size_t)i] == rawLens[0]; }
+    if (same) {
+        k_png_inflate<<<n, 32, sizeof(InflateSm), c->stream>>>(c->png_z, dImgs, c->png_raw, rawStride, rawLens[0]);
+        LAUNCH_CHECK(c);
+    } else {
+        for (int i = 0; i < n; i++) {
+            k_png_inflate<<<1, 32, sizeof(InflateSm), c->stream>>>(c->png_z, dImgs + i, c->png_raw + (long long)i * rawStride, rawStride, rawLens[(size_t)i]);
+            LAUNCH_CHECK(c);
+        }
+    }
+    k_png_unfilter<<<n, 32, 0, c->stream>>>(c->png_raw, rawStride, dImgs, W, H, dOut, dStep, dStride);
+    LAUNCH_CHECK(c);
+    CVR_CUDA(c, cudaMemcpyAsync(imgs.data(), dImgs, sizeof(PngImg) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    if (mem_out == CVR_MEM_HOST) {
+        if (image_stride == step * (size_t)H) CVR_CUDA(c, cudaMemcpy2DAsync(bgr, step, dOut, dStep, (size_t)W * 3, (size_t)H * n, cudaMemcpyDeviceToHost, c->stream));
+        else for (int i = 0; i < n; i++) CVR_CUDA(c, cudaMemcpy2DAsync(bgr + (size_t)i * image_stride, step, dOut + (size_t)i * dStride, dStep, (size_t)W * 3, H, cudaMemcpyDeviceToHost, c->stream));
+    }
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) { c->err = std::string("stream sync: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
+    for (int i = 0; i < n; i++)
+        if (imgs[(size_t)i].status) { c->err = "cvr_decode_png_batch: corrupt or unsupported deflate stream in image " + std::to_string(i) + " (code " + std::to_string(imgs[(size_t)i].status) + ")"; return CVR_ERR_INVALID_ARG; }
+    return CVR_OK;
+}
