@@ -38,6 +38,12 @@ __global__ void k_png_idat(const uint8_t* __restrict__ blob, const PngSeg* __res
 #define PNG_WIN 32768           // DEFLATE's sliding window = the output ring
 #define PNG_LBITS 10            // first-level table bits, literal/length codes
 #define PNG_DBITS 8             // ... distance codes
+#ifdef __CUDA_ARCH__
+#define PNG_BREV(x) __brev(x)
+#else
+static inline unsigned png_brev_host(unsigned v) { unsigned r = 0; for (int i = 0; i < 32; i++) { r = (r << 1) | (v & 1); v >>= 1; } return r; }
+#define PNG_BREV(x) png_brev_host(x)
+#endif
 struct Huff {                   // canonical code: counts per length, symbols sorted by (length, symbol)
     unsigned short count[16];
     unsigned short symbol[288];
@@ -51,7 +57,7 @@ struct InflateSm {
     unsigned short lens[320];
 };
 
-__device__ __forceinline__ int huff_build(Huff& h, const unsigned short* lens, int n, unsigned short* tab, int tbits)
+__host__ __device__ inline int huff_build(Huff& h, const unsigned short* lens, int n, unsigned short* tab, int tbits)
 {
     for (int i = 0; i < 16; i++) h.count[i] = 0;
     for (int i = 0; i < n; i++) h.count[lens[i]]++;
@@ -67,7 +73,7 @@ __device__ __forceinline__ int huff_build(Huff& h, const unsigned short* lens, i
     int code = 0, idx = 0;
     for (int l = 1; l <= tbits; l++) {
         for (int k = 0; k < h.count[l]; k++, idx++, code++) {
-            unsigned rev = __brev((unsigned)code) >> (32 - l);
+            unsigned rev = PNG_BREV((unsigned)code) >> (32 - l);
             const unsigned short e = (unsigned short)((l << 9) | h.symbol[idx]);
             for (unsigned f = rev; f < (1u << tbits); f += (1u << l)) tab[f] = e;
         }
@@ -80,9 +86,164 @@ struct BitIn {
     unsigned long long bb; int bc;      // bit buffer (LSB first) and number of valid bits
     long long pos;                      // next input byte to enter the buffer
 };
+struct InflateState {               // what lane 0 carries across the cooperative refill / flush points
+    BitIn b;
+    long long outPos;
+    int status, done;
+    int phase;                      // 0 block header, 1 stored copy, 2 huffman symbols
+    int last, storedLeft;
+    int pendLen, pendDist;          // a match being copied
+};
+// The sequential part of inflate: decodes until `inStop` input bytes are consumed, the output reaches `outStop`, the stream ends
+// or an error is found.  Input comes from the ring S.in (byte p at S.in[p % PNG_INRING]), output goes to the window ring S.win.
+// status: 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol / distance, 5 output overrun, 6 input overrun,
+// 7 stored-block length check.  (Host-callable too: tests/png_inflate_host.cu runs it on the CPU.)
+__host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, long long inStop, long long outStop, long long inLen, long long rawLen)
+{
+    BitIn b = st.b;
+    long long outPos = st.outPos;
+    int status = st.status, done = st.done, phase = st.phase, last = st.last, storedLeft = st.storedLeft, pendLen = st.pendLen, pendDist = st.pendDist;
+#define NEED(n) while (b.bc < (n)) { b.bb |= (unsigned long long)S.in[b.pos & (PNG_INRING - 1)] << b.bc; b.bc += 8; b.pos++; }
+#define TAKE(var, n) { var = (b.bb & ((1ull << (n)) - 1)); b.bb >>= (n); b.bc -= (n); }
+    if (outPos == 0 && b.pos == 0) {                                   // zlib header
+        unsigned cmf, flg;
+        NEED(16);
+        TAKE(cmf, 8); TAKE(flg, 8);
+        if ((cmf & 15) != 8 || ((cmf << 8) | flg) % 31 != 0 || (flg & 32)) status = 1;
+    }
+    while (!status && !done && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
+        if (b.pos - (b.bc >> 3) > inLen) { status = 6; break; }
+        if (phase == 0) {
+            int type;
+            NEED(3);
+            TAKE(last, 1); TAKE(type, 2);
+            if (type == 0) {
+                const int drop = b.bc & 7; b.bb >>= drop; b.bc -= drop;           // to the byte boundary
+                unsigned len, nlen;
+                NEED(32);
+                TAKE(len, 16); TAKE(nlen, 16);
+                if ((len ^ 0xffffu) != nlen) { status = 7; break; }
+                storedLeft = (int)len; phase = 1;
+                if (storedLeft == 0) { phase = 0; if (last) done = 1; }
+            } else if (type == 1) {
+                for (int i = 0; i < 144; i++) S.lens[i] = 8;
+                for (int i = 144; i < 256; i++) S.lens[i] = 9;
+                for (int i = 256; i < 280; i++) S.lens[i] = 7;
+                for (int i = 280; i < 288; i++) S.lens[i] = 8;
+                huff_build(S.lh, S.lens, 288, S.ltab, PNG_LBITS);
+                for (int i = 0; i < 30; i++) S.lens[i] = 5;
+                huff_build(S.dh, S.lens, 30, S.dtab, PNG_DBITS);
+                phase = 2;
+            } else if (type == 2) {
+                int nlen, ndist, ncode;
+                NEED(14);
+                TAKE(nlen, 5); TAKE(ndist, 5); TAKE(ncode, 4);
+                nlen += 257; ndist += 1; ncode += 4;
+                if (nlen > 286 || ndist > 30) { status = 3; break; }
+                const unsigned char order[19] = { 16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15 };
+                for (int i = 0; i < 19; i++) S.lens[i] = 0;
+                for (int i = 0; i < ncode; i++) { unsigned v; NEED(3); TAKE(v, 3); S.lens[order[i]] = (unsigned short)v; }
+                if (huff_build(S.lh, S.lens, 19, S.ltab, 7) < 0) { status = 3; break; }   // the code-length code (7-bit table in ltab)
+                int idx = 0;
+                unsigned short* tmp = S.lens + 0;                        // the decoded lengths replace the 19 (already consumed by huff_build)
+                while (idx < nlen + ndist) {
+                    NEED(7);
+                    const unsigned short e = S.ltab[b.bb & 127];
+                    if (!e) { status = 3; break; }
+                    const int l = e >> 9, sym = e & 511;
+                    b.bb >>= l; b.bc -= l;
+                    if (sym < 16) tmp[idx++] = (unsigned short)sym;
+                    else {
+                        int rep, val = 0;
+                        if (sym == 16) { if (idx == 0) { status = 3; break; } val = tmp[idx - 1]; NEED(2); TAKE(rep, 2); rep += 3; }
+                        else if (sym == 17) { NEED(3); TAKE(rep, 3); rep += 3; }
+                        else { NEED(7); TAKE(rep, 7); rep += 11; }
+                        if (idx + rep > nlen + ndist) { status = 3; break; }
+                        while (rep--) tmp[idx++] = (unsigned short)val;
+                    }
+                }
+                if (status) break;
+                if (tmp[256] == 0) { status = 3; break; }              // no end-of-block code
+                // the distance lengths first (they sit behind the literal/length ones, which building the first code leaves alone)
+                if (huff_build(S.dh, tmp + nlen, ndist, S.dtab, PNG_DBITS) < 0) { status = 3; break; }
+                if (huff_build(S.lh, tmp, nlen, S.ltab, PNG_LBITS) < 0) { status = 3; break; }
+                phase = 2;
+            } else { status = 2; break; }
+        } else if (phase == 1) {
+            // stored bytes: straight from the bit buffer / input ring into the window
+            while (storedLeft > 0 && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
+                unsigned v;
+                NEED(8);
+                TAKE(v, 8);
+                S.win[outPos & (PNG_WIN - 1)] = (uint8_t)v;
+                outPos++; storedLeft--;
+            }
+            if (storedLeft == 0) { phase = 0; if (last) done = 1; }
+        } else {
+            if (pendLen > 0) {                                         // continue a match that was cut by a flush point
+                while (pendLen > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - pendDist) & (PNG_WIN - 1)]; outPos++; pendLen--; }
+                if (pendLen > 0) break;
+            }
+            NEED(48);
+            unsigned short e = S.ltab[b.bb & ((1u << PNG_LBITS) - 1)];
+            int l, sym;
+            if (e) { l = e >> 9; sym = e & 511; }
+            else {                                                     // longer than the table: canonical search, one bit at a time
+                int code = 0, first = 0, index = 0; l = 0; sym = -1;
+                for (int len = 1; len <= 15; len++) {
+                    code |= (int)((b.bb >> (len - 1)) & 1);
+                    const int cnt = S.lh.count[len];
+                    if (code - cnt < first) { sym = S.lh.symbol[index + (code - first)]; l = len; break; }
+                    index += cnt; first += cnt; first <<= 1; code <<= 1;
+                }
+                if (sym < 0) { status = 4; break; }
+            }
+            b.bb >>= l; b.bc -= l;
+            if (sym < 256) { S.win[outPos & (PNG_WIN - 1)] = (uint8_t)sym; outPos++; }
+            else if (sym == 256) { phase = 0; if (last) done = 1; }
+            else {
+                sym -= 257;
+                if (sym >= 29) { status = 4; break; }
+                const unsigned short lbase[29] = { 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258 };
+                const unsigned char lext[29] = { 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0 };
+                int len = lbase[sym] + (int)(b.bb & ((1u << lext[sym]) - 1));
+                b.bb >>= lext[sym]; b.bc -= lext[sym];
+                unsigned short de = S.dtab[b.bb & ((1u << PNG_DBITS) - 1)];
+                int dl, ds;
+                if (de) { dl = de >> 9; ds = de & 511; }
+                else {
+                    int code = 0, first = 0, index = 0; dl = 0; ds = -1;
+                    for (int q = 1; q <= 15; q++) {
+                        code |= (int)((b.bb >> (q - 1)) & 1);
+                        const int cnt = S.dh.count[q];
+                        if (code - cnt < first) { ds = S.dh.symbol[index + (code - first)]; dl = q; break; }
+                        index += cnt; first += cnt; first <<= 1; code <<= 1;
+                    }
+                    if (ds < 0) { status = 4; break; }
+                }
+                b.bb >>= dl; b.bc -= dl;
+                if (ds >= 30) { status = 4; break; }
+                const unsigned short dbase[30] = { 1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577 };
+                const unsigned char dext[30] = { 0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13 };
+                const int dist = dbase[ds] + (int)(b.bb & ((1u << dext[ds]) - 1));
+                b.bb >>= dext[ds]; b.bc -= dext[ds];
+                if ((long long)dist > outPos) { status = 4; break; }
+                pendDist = dist;
+                while (len > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - dist) & (PNG_WIN - 1)]; outPos++; len--; }
+                pendLen = len;
+            }
+        }
+        if (outPos > rawLen) { status = 5; break; }
+    }
+#undef NEED
+#undef TAKE
+    st.b = b; st.outPos = outPos; st.status = status; st.done = done; st.phase = phase; st.last = last; st.storedLeft = storedLeft;
+    st.pendLen = pendLen; st.pendDist = pendDist;
+}
 
-// One warp per image.  Returns through img.status: 0 ok, 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol /
-// distance, 5 output overrun, 6 input overrun, 7 stored-block length check.
+#ifndef PNG_HOST_ONLY
+// One warp per image: lane 0 decodes (inflate_run), all lanes flush finished halves of the window to global memory and refill
+// consumed halves of the input ring.  Result in img.status (0 ok).
 __global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ z, PngImg* imgs, uint8_t* __restrict__ raw, long long rawStride, long long rawLen)
 {
     extern __shared__ __align__(16) unsigned char ism[];
@@ -92,159 +253,21 @@ __global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ 
     const uint8_t* in = z + im.zOff;
     const long long inLen = im.zLen;
     uint8_t* out = raw + (long long)blockIdx.x * rawStride;
-    // the input ring holds bytes [inBase, inBase + PNG_INRING); refilled in halves by all lanes
-    long long inBase = 0;
+    long long inBase = 0;                                              // the input ring holds bytes [inBase, inBase + PNG_INRING)
     for (int i = lane; i < PNG_INRING; i += 32) S.in[i] = (long long)i < inLen ? in[i] : 0;
     __syncwarp();
-    BitIn b; b.bb = 0; b.bc = 0; b.pos = 0;
-    long long outPos = 0, flushed = 0;
-    int status = 0, done = 0;
-    // decoder state that survives the cooperative refill / flush points
-    int phase = 0;                  // 0 block header, 1 stored copy, 2 huffman symbols
-    int last = 0, storedLeft = 0;
-    int pendLen = 0, pendDist = 0;  // a match being copied
+    InflateState st;
+    memset(&st, 0, sizeof(st));
+    long long flushed = 0;
     while (true) {
-        if (lane == 0 && !done && !status) {
-            // lane 0 runs until it has eaten half of the input ring, filled half of the window since the last flush, or finished
-            const long long inStop = inBase + PNG_INRING / 2, outStop = flushed + PNG_WIN / 2;
-#define NEED(n) while (b.bc < (n)) { b.bb |= (unsigned long long)S.in[b.pos & (PNG_INRING - 1)] << b.bc; b.bc += 8; b.pos++; }
-#define TAKE(n) (b.bb & ((1ull << (n)) - 1)); b.bb >>= (n); b.bc -= (n)
-            if (outPos == 0 && b.pos == 0) {                           // zlib header
-                NEED(16);
-                const unsigned cmf = (unsigned)TAKE(8); const unsigned flg = (unsigned)TAKE(8);
-                if ((cmf & 15) != 8 || ((cmf << 8) | flg) % 31 != 0 || (flg & 32)) status = 1;
-            }
-            while (!status && !done && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
-                if (b.pos - 8 > inLen + 8) { status = 6; break; }
-                if (phase == 0) {
-                    NEED(3);
-                    last = (int)TAKE(1);
-                    const int type = (int)TAKE(2);
-                    if (type == 0) {
-                        const int drop = b.bc & 7; b.bb >>= drop; b.bc -= drop;       // to the byte boundary
-                        NEED(32);
-                        const unsigned len = (unsigned)TAKE(16); const unsigned nlen = (unsigned)TAKE(16);
-                        if ((len ^ 0xffffu) != nlen) { status = 7; break; }
-                        storedLeft = (int)len; phase = 1;
-                    } else if (type == 1) {
-                        for (int i = 0; i < 144; i++) S.lens[i] = 8;
-                        for (int i = 144; i < 256; i++) S.lens[i] = 9;
-                        for (int i = 256; i < 280; i++) S.lens[i] = 7;
-                        for (int i = 280; i < 288; i++) S.lens[i] = 8;
-                        huff_build(S.lh, S.lens, 288, S.ltab, PNG_LBITS);
-                        for (int i = 0; i < 30; i++) S.lens[i] = 5;
-                        huff_build(S.dh, S.lens, 30, S.dtab, PNG_DBITS);
-                        phase = 2;
-                    } else if (type == 2) {
-                        NEED(14);
-                        const int nlen = (int)TAKE(5) + 257; const int ndist = (int)TAKE(5) + 1; const int ncode = (int)TAKE(4) + 4;
-                        if (nlen > 286 || ndist > 30) { status = 3; break; }
-                        const unsigned char order[19] = { 16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15 };
-                        for (int i = 0; i < 19; i++) S.lens[i] = 0;
-                        for (int i = 0; i < ncode; i++) { NEED(3); S.lens[order[i]] = (unsigned short)TAKE(3); }
-                        if (huff_build(S.lh, S.lens, 19, S.ltab, 7) < 0) { status = 3; break; }   // the code-length code (7-bit table in ltab)
-                        int idx = 0;
-                        unsigned short* ll = S.lens + 0;                // decoded lengths are written over lens[] after the 19 are consumed:
-                        unsigned short tmp[320];                        // ... so collect them in local memory first
-                        while (idx < nlen + ndist) {
-                            NEED(7);
-                            const unsigned short e = S.ltab[b.bb & 127];
-                            if (!e) { status = 3; break; }
-                            const int l = e >> 9, sym = e & 511;
-                            b.bb >>= l; b.bc -= l;
-                            if (sym < 16) tmp[idx++] = (unsigned short)sym;
-                            else {
-                                int rep, val = 0;
-                                if (sym == 16) { if (idx == 0) { status = 3; break; } val = tmp[idx - 1]; NEED(2); rep = 3 + (int)TAKE(2); }
-                                else if (sym == 17) { NEED(3); rep = 3 + (int)TAKE(3); }
-                                else { NEED(7); rep = 11 + (int)TAKE(7); }
-                                if (idx + rep > nlen + ndist) { status = 3; break; }
-                                while (rep--) tmp[idx++] = (unsigned short)val;
-                            }
-                        }
-                        if (status) break;
-                        if (tmp[256] == 0) { status = 3; break; }      // no end-of-block code
-                        for (int i = 0; i < nlen; i++) ll[i] = tmp[i];
-                        if (huff_build(S.lh, ll, nlen, S.ltab, PNG_LBITS) != 0 && !(S.lh.count[0] + S.lh.count[1] == nlen)) { status = 3; break; }
-                        for (int i = 0; i < ndist; i++) ll[i] = tmp[nlen + i];
-                        if (huff_build(S.dh, ll, ndist, S.dtab, PNG_DBITS) < 0) { status = 3; break; }
-                        phase = 2;
-                    } else { status = 2; break; }
-                } else if (phase == 1) {
-                    // stored bytes: straight from the bit buffer / input ring into the window
-                    while (storedLeft > 0 && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
-                        NEED(8);
-                        S.win[outPos & (PNG_WIN - 1)] = (uint8_t)TAKE(8);
-                        outPos++; storedLeft--;
-                    }
-                    if (storedLeft == 0) { phase = 0; if (last) done = 1; }
-                } else {
-                    if (pendLen > 0) {                                 // continue a match that was cut by a flush point
-                        while (pendLen > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - pendDist) & (PNG_WIN - 1)]; outPos++; pendLen--; }
-                        if (pendLen > 0) break;
-                    }
-                    NEED(48);
-                    unsigned short e = S.ltab[b.bb & ((1u << PNG_LBITS) - 1)];
-                    int l, sym;
-                    if (e) { l = e >> 9; sym = e & 511; }
-                    else {                                             // longer than the table: canonical search from length PNG_LBITS + 1
-                        int code = 0, first = 0, index = 0; l = 0; sym = -1;
-                        for (int len = 1; len <= 15; len++) {
-                            code |= (int)((b.bb >> (len - 1)) & 1);
-                            const int cnt = S.lh.count[len];
-                            if (code - cnt < first) { sym = S.lh.symbol[index + (code - first)]; l = len; break; }
-                            index += cnt; first += cnt; first <<= 1; code <<= 1;
-                        }
-                        if (sym < 0) { status = 4; break; }
-                    }
-                    b.bb >>= l; b.bc -= l;
-                    if (sym < 256) { S.win[outPos & (PNG_WIN - 1)] = (uint8_t)sym; outPos++; }
-                    else if (sym == 256) { phase = 0; if (last) done = 1; }
-                    else {
-                        sym -= 257;
-                        if (sym >= 29) { status = 4; break; }
-                        const unsigned short lbase[29] = { 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258 };
-                        const unsigned char lext[29] = { 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0 };
-                        int len = lbase[sym] + (int)(b.bb & ((1u << lext[sym]) - 1));
-                        b.bb >>= lext[sym]; b.bc -= lext[sym];
-                        unsigned short de = S.dtab[b.bb & ((1u << PNG_DBITS) - 1)];
-                        int dl, ds;
-                        if (de) { dl = de >> 9; ds = de & 511; }
-                        else {
-                            int code = 0, first = 0, index = 0; dl = 0; ds = -1;
-                            for (int q = 1; q <= 15; q++) {
-                                code |= (int)((b.bb >> (q - 1)) & 1);
-                                const int cnt = S.dh.count[q];
-                                if (code - cnt < first) { ds = S.dh.symbol[index + (code - first)]; dl = q; break; }
-                                index += cnt; first += cnt; first <<= 1; code <<= 1;
-                            }
-                            if (ds < 0) { status = 4; break; }
-                        }
-                        b.bb >>= dl; b.bc -= dl;
-                        if (ds >= 30) { status = 4; break; }
-                        const unsigned short dbase[30] = { 1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577 };
-                        const unsigned char dext[30] = { 0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13 };
-                        const int dist = dbase[ds] + (int)(b.bb & ((1u << dext[ds]) - 1));
-                        b.bb >>= dext[ds]; b.bc -= dext[ds];
-                        if ((long long)dist > outPos) { status = 4; break; }
-                        pendDist = dist;
-                        while (len > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - dist) & (PNG_WIN - 1)]; outPos++; len--; }
-                        pendLen = len;
-                    }
-                }
-                if (outPos > rawLen) { status = 5; break; }
-            }
-#undef NEED
-#undef TAKE
-        }
-        // ---- cooperative part: flush finished window halves, refill consumed input halves ----
-        done = __shfl_sync(0xffffffffu, done, 0); status = __shfl_sync(0xffffffffu, status, 0);
-        outPos = __shfl_sync(0xffffffffu, outPos, 0);
-        const long long consumed = __shfl_sync(0xffffffffu, b.pos - (b.bc >> 3), 0);
+        if (lane == 0 && !st.done && !st.status) inflate_run(st, S, inBase + PNG_INRING / 2, flushed + PNG_WIN / 2, inLen, rawLen);
+        const int done = __shfl_sync(0xffffffffu, st.done, 0), status = __shfl_sync(0xffffffffu, st.status, 0);
+        const long long outPos = __shfl_sync(0xffffffffu, st.outPos, 0);
+        const long long consumed = __shfl_sync(0xffffffffu, st.b.pos - (st.b.bc >> 3), 0);
         const long long upto = (done || status) ? outPos : (outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);   // whole halves, or everything at the end
         for (long long i = flushed + lane; i < upto && i < rawLen; i += 32) out[i] = S.win[i & (PNG_WIN - 1)];
         flushed = upto > flushed ? upto : flushed;
-        if (done || status) break;
+        if (done || status) { if (lane == 0) im.status = status ? status : (outPos == rawLen ? 0 : 5); break; }
         while (consumed >= inBase + PNG_INRING / 2) {                   // the older half of the ring is free: bring in the next bytes
             const long long src = inBase + PNG_INRING;
             for (int i = lane; i < PNG_INRING / 2; i += 32) S.in[(src + i) & (PNG_INRING - 1)] = (src + i) < inLen ? in[src + i] : 0;
@@ -252,7 +275,6 @@ __global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ 
         }
         __syncwarp();
     }
-    if (lane == 0) im.status = status ? status : (outPos == rawLen ? 0 : 5);
 }
 
 // ---- scanline filters + channel order --------------------------------------------------------------------------------
@@ -404,3 +426,4 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
         if (imgs[(size_t)i].status) { c->err = "cvr_decode_png_batch: corrupt or unsupported deflate stream in image " + std::to_string(i) + " (code " + std::to_string(imgs[(size_t)i].status) + ")"; return CVR_ERR_INVALID_ARG; }
     return CVR_OK;
 }
+#endif  // PNG_HOST_ONLY
