@@ -300,6 +300,36 @@ def _side_filter_stress(cvr, torch, dev, local, n, peak):
                          "floor_ms": alg / (peak * 1e9) * 1e3}, "clocks": clk}
 
 
+def _side_png(cvr, torch, dev, local):
+    """Ingest: the PNG files the reference's streamers send, decoded on the device (cvr_decode_png_batch,
+    device output) next to cv2.imdecode on one host core."""
+    import cv2
+    Ls, Rs = make_pairs(8)
+    files = [cv2.imencode(".png", im)[1].tobytes() for im in list(Ls) + list(Rs)]      # OpenCV's default PNG settings, as the streamers use
+    n = 64
+    batch = [files[i % len(files)] for i in range(n)]
+    rec = cvr.Reconstruct3D(W, H, filter_only=True, max_points=16, device=local)
+    out = torch.empty((n, H, W, 3), dtype=torch.uint8, device=dev)
+    rec.DecodePNG(batch, device_out=out.data_ptr())
+    ok = bool(np.array_equal(out[0].cpu().numpy(), cv2.imdecode(np.frombuffer(batch[0], np.uint8), cv2.IMREAD_COLOR)))
+    clocks = ClockSampler(local)
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        rec.DecodePNG(batch, device_out=out.data_ptr())
+    dt = time.perf_counter() - t0
+    clk = clocks.stop()
+    rec.close()
+    cv2.setNumThreads(1)
+    t0 = time.perf_counter()
+    for f in batch:
+        cv2.imdecode(np.frombuffer(f, np.uint8), cv2.IMREAD_COLOR)
+    dth = time.perf_counter() - t0
+    return {"workload": "%d PNG files per call (1242x375 BGR, cv2.imencode defaults, %.0f KB each) -> BGR frames in device memory" % (n, np.mean([len(f) for f in batch]) / 1e3),
+            "images_per_s": reps * n / dt, "stereo_frames_per_s": reps * n / dt / 2, "matches_cv2": ok,
+            "host_cv2_imdecode_images_per_s_per_core": n / dth, "clocks": clk}
+
+
 # ------------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
@@ -526,7 +556,8 @@ def main():
             for nm, fn in (("spi_hh_bs27", lambda: _side_stereo(cvr, torch, dev, local, "spi", 720, 1280, 192, 27, 1, 30, 4, peak)),
                            ("spi_hh_bs5", lambda: _side_stereo(cvr, torch, dev, local, "spi", 720, 1280, 192, 5, 1, 30, 4, peak)),
                            ("hd", lambda: _side_stereo(cvr, torch, dev, local, "hd", 1080, 1920, 256, 27, 0, 14, 4, peak)),
-                           ("filter_stress", lambda: _side_filter_stress(cvr, torch, dev, local, args.stress_points, peak))):
+                           ("filter_stress", lambda: _side_filter_stress(cvr, torch, dev, local, args.stress_points, peak)),
+                           ("png_ingest", lambda: _side_png(cvr, torch, dev, local))):
                 try:
                     side[nm] = fn()
                 except Exception as ex:      # noqa: BLE001
