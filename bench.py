@@ -306,7 +306,7 @@ def _side_png(cvr, torch, dev, local):
     import cv2
     Ls, Rs = make_pairs(8)
     files = [cv2.imencode(".png", im)[1].tobytes() for im in list(Ls) + list(Rs)]      # OpenCV's default PNG settings, as the streamers use
-    n = 64
+    n = 220                                                            # both cameras of a 110-frame batch
     batch = [files[i % len(files)] for i in range(n)]
     rec = cvr.Reconstruct3D(W, H, filter_only=True, max_points=16, device=local)
     out = torch.empty((n, H, W, 3), dtype=torch.uint8, device=dev)

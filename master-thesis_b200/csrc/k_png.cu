@@ -84,11 +84,11 @@ __host__ __device__ inline int huff_build(Huff& h, const unsigned short* lens, i
 
 struct BitIn {
     unsigned long long bb; int bc;      // bit buffer (LSB first) and number of valid bits
-    long long pos;                      // next input byte to enter the buffer
+    int pos;                            // next input byte to enter the buffer: always a multiple of 4 (the buffer is refilled a word at a time)
 };
 struct InflateState {               // what lane 0 carries across the cooperative refill / flush points
     BitIn b;
-    long long outPos;
+    int outPos;
     int status, done;
     int phase;                      // 0 block header, 1 stored copy, 2 huffman symbols
     int last, storedLeft;
@@ -98,12 +98,13 @@ struct InflateState {               // what lane 0 carries across the cooperativ
 // or an error is found.  Input comes from the ring S.in (byte p at S.in[p % PNG_INRING]), output goes to the window ring S.win.
 // status: 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol / distance, 5 output overrun, 6 input overrun,
 // 7 stored-block length check.  (Host-callable too: tests/png_inflate_host.cu runs it on the CPU.)
-__host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, long long inStop, long long outStop, long long inLen, long long rawLen)
+__host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, int inStop, int outStop, int inLen, int rawLen)
 {
     BitIn b = st.b;
-    long long outPos = st.outPos;
+    int outPos = st.outPos;
     int status = st.status, done = st.done, phase = st.phase, last = st.last, storedLeft = st.storedLeft, pendLen = st.pendLen, pendDist = st.pendDist;
-#define NEED(n) while (b.bc < (n)) { b.bb |= (unsigned long long)S.in[b.pos & (PNG_INRING - 1)] << b.bc; b.bc += 8; b.pos++; }
+    // NEED(n), n <= 33: one aligned 32-bit word of the input ring enters the buffer when fewer than n bits are left
+#define NEED(n) if (b.bc < (n)) { b.bb |= (unsigned long long)(*(const unsigned*)&S.in[b.pos & (PNG_INRING - 1)]) << b.bc; b.bc += 32; b.pos += 4; }
 #define TAKE(var, n) { var = (b.bb & ((1ull << (n)) - 1)); b.bb >>= (n); b.bc -= (n); }
     if (outPos == 0 && b.pos == 0) {                                   // zlib header
         unsigned cmf, flg;
@@ -120,8 +121,10 @@ __host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, long
             if (type == 0) {
                 const int drop = b.bc & 7; b.bb >>= drop; b.bc -= drop;           // to the byte boundary
                 unsigned len, nlen;
-                NEED(32);
-                TAKE(len, 16); TAKE(nlen, 16);
+                NEED(16);
+                TAKE(len, 16);
+                NEED(16);
+                TAKE(nlen, 16);
                 if ((len ^ 0xffffu) != nlen) { status = 7; break; }
                 storedLeft = (int)len; phase = 1;
                 if (storedLeft == 0) { phase = 0; if (last) done = 1; }
@@ -184,7 +187,7 @@ __host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, long
                 while (pendLen > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - pendDist) & (PNG_WIN - 1)]; outPos++; pendLen--; }
                 if (pendLen > 0) break;
             }
-            NEED(48);
+            NEED(20);                                                  // a literal/length code (<= 15 bits) and its extra bits (<= 5)
             unsigned short e = S.ltab[b.bb & ((1u << PNG_LBITS) - 1)];
             int l, sym;
             if (e) { l = e >> 9; sym = e & 511; }
@@ -208,6 +211,7 @@ __host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, long
                 const unsigned char lext[29] = { 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0 };
                 int len = lbase[sym] + (int)(b.bb & ((1u << lext[sym]) - 1));
                 b.bb >>= lext[sym]; b.bc -= lext[sym];
+                NEED(28);                                              // a distance code (<= 15 bits) and its extra bits (<= 13)
                 unsigned short de = S.dtab[b.bb & ((1u << PNG_DBITS) - 1)];
                 int dl, ds;
                 if (de) { dl = de >> 9; ds = de & 511; }
@@ -227,7 +231,7 @@ __host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, long
                 const unsigned char dext[30] = { 0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13 };
                 const int dist = dbase[ds] + (int)(b.bb & ((1u << dext[ds]) - 1));
                 b.bb >>= dext[ds]; b.bc -= dext[ds];
-                if ((long long)dist > outPos) { status = 4; break; }
+                if (dist > outPos) { status = 4; break; }
                 pendDist = dist;
                 while (len > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - dist) & (PNG_WIN - 1)]; outPos++; len--; }
                 pendLen = len;
@@ -244,32 +248,35 @@ __host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, long
 #ifndef PNG_HOST_ONLY
 // One warp per image: lane 0 decodes (inflate_run), all lanes flush finished halves of the window to global memory and refill
 // consumed halves of the input ring.  Result in img.status (0 ok).
-__global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ z, PngImg* imgs, uint8_t* __restrict__ raw, long long rawStride, long long rawLen)
+__global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ z, PngImg* imgs, uint8_t* __restrict__ raw, long long rawStride, int rawLen)
 {
     extern __shared__ __align__(16) unsigned char ism[];
     InflateSm& S = *(InflateSm*)ism;
     const int lane = threadIdx.x;
     PngImg& im = imgs[blockIdx.x];
     const uint8_t* in = z + im.zOff;
-    const long long inLen = im.zLen;
+    const int inLen = (int)im.zLen;
     uint8_t* out = raw + (long long)blockIdx.x * rawStride;
-    long long inBase = 0;                                              // the input ring holds bytes [inBase, inBase + PNG_INRING)
-    for (int i = lane; i < PNG_INRING; i += 32) S.in[i] = (long long)i < inLen ? in[i] : 0;
+    int inBase = 0;                                                    // the input ring holds bytes [inBase, inBase + PNG_INRING)
+    for (int i = lane; i < PNG_INRING; i += 32) S.in[i] = i < inLen ? in[i] : 0;
     __syncwarp();
     InflateState st;
     memset(&st, 0, sizeof(st));
-    long long flushed = 0;
+    int flushed = 0;
     while (true) {
         if (lane == 0 && !st.done && !st.status) inflate_run(st, S, inBase + PNG_INRING / 2, flushed + PNG_WIN / 2, inLen, rawLen);
         const int done = __shfl_sync(0xffffffffu, st.done, 0), status = __shfl_sync(0xffffffffu, st.status, 0);
-        const long long outPos = __shfl_sync(0xffffffffu, st.outPos, 0);
-        const long long consumed = __shfl_sync(0xffffffffu, st.b.pos - (st.b.bc >> 3), 0);
-        const long long upto = (done || status) ? outPos : (outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);   // whole halves, or everything at the end
-        for (long long i = flushed + lane; i < upto && i < rawLen; i += 32) out[i] = S.win[i & (PNG_WIN - 1)];
+        const int outPos = __shfl_sync(0xffffffffu, st.outPos, 0);
+        const int consumed = __shfl_sync(0xffffffffu, st.b.pos - (st.b.bc >> 3), 0);
+        const int upto = (done || status) ? outPos : (outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);   // whole halves, or everything at the end
+        // (the window and the scanline buffer are both 16-byte aligned and `flushed` is a multiple of 16 until the very end)
+        const int vend = min(upto, rawLen) & ~15;
+        for (int i = flushed + lane * 16; i < vend; i += 32 * 16) *(uint4*)(out + i) = *(const uint4*)&S.win[i & (PNG_WIN - 1)];
+        for (int i = max(flushed, vend) + lane; i < upto && i < rawLen; i += 32) out[i] = S.win[i & (PNG_WIN - 1)];
         flushed = upto > flushed ? upto : flushed;
         if (done || status) { if (lane == 0) im.status = status ? status : (outPos == rawLen ? 0 : 5); break; }
         while (consumed >= inBase + PNG_INRING / 2) {                   // the older half of the ring is free: bring in the next bytes
-            const long long src = inBase + PNG_INRING;
+            const int src = inBase + PNG_INRING;
             for (int i = lane; i < PNG_INRING / 2; i += 32) S.in[(src + i) & (PNG_INRING - 1)] = (src + i) < inLen ? in[src + i] : 0;
             inBase += PNG_INRING / 2;
         }
@@ -302,6 +309,22 @@ __global__ void __launch_bounds__(32) k_png_unfilter(uint8_t* raw, long long raw
         const int ft = cur[-1];
         if (ft == 0) { /* None */ }
         else if (ft == 2) { if (up) for (int i = lane; i < rowBytes; i += 32) cur[i] = (uint8_t)(cur[i] + up[i]); }
+        else if (ft == 1) {
+            // Sub: a running sum per channel (mod 256) -- every lane sums a stretch of pixels, a warp scan joins the stretches
+            const int per = (W + 31) / 32, x0 = min(lane * per, W), x1 = min(x0 + per, W);
+            int tot[4] = { 0, 0, 0, 0 };
+            for (int x = x0; x < x1; x++)
+                for (int ch = 0; ch < bpp; ch++) tot[ch] += cur[x * bpp + ch];
+            int offc[4];
+            for (int ch = 0; ch < bpp; ch++) {
+                int inc = tot[ch];
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+                offc[ch] = inc - tot[ch];
+            }
+            for (int x = x0; x < x1; x++)
+                for (int ch = 0; ch < bpp; ch++) { offc[ch] += cur[x * bpp + ch]; cur[x * bpp + ch] = (uint8_t)offc[ch]; }
+        }
         else if (lane < bpp) {
             int a = 0, c = 0;                                          // left and upper-left of this channel
             for (int i = lane; i < rowBytes; i += bpp) {
@@ -401,9 +424,10 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
     LAUNCH_CHECK(c);
     CVR_CUDA(c, cudaFuncSetAttribute(k_png_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(InflateSm)));
     // every image inflates to H scanlines of 1 + W * bpp bytes; the images of a batch may differ in colour type
-    std::vector<long long> rawLens((size_t)n);
+    if ((long long)H * ((long long)W * 4 + 1) > 0x3fffffffLL) { c->err = "cvr_decode_png_batch: image too large for the device decoder"; return CVR_ERR_UNSUPPORTED; }
+    std::vector<int> rawLens((size_t)n);
     bool same = true;
-    for (int i = 0; i < n; i++) { rawLens[(size_t)i] = (long long)H * ((long long)W * imgs[(size_t)i].bpp + 1); same = same && rawLens[(size_t)i] == rawLens[0]; }
+    for (int i = 0; i < n; i++) { rawLens[(size_t)i] = H * (W * imgs[(size_t)i].bpp + 1); same = same && rawLens[(size_t)i] == rawLens[0]; }
     if (same) {
         k_png_inflate<<<n, 32, sizeof(InflateSm), c->stream>>>(c->png_z, dImgs, c->png_raw, rawStride, rawLens[0]);
         LAUNCH_CHECK(c);

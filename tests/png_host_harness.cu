@@ -10,17 +10,17 @@ extern "C" int png_inflate_host(const uint8_t* z, long long zlen, uint8_t* out, 
     for (int i = 0; i < PNG_INRING; i++) S->in[i] = i < zlen ? z[i] : 0;
     InflateState st;
     memset(&st, 0, sizeof(st));
-    long long inBase = 0, flushed = 0;
+    int inBase = 0, flushed = 0;
     int result;
     for (;;) {
-        if (!st.done && !st.status) inflate_run(st, *S, inBase + PNG_INRING / 2, flushed + PNG_WIN / 2, zlen, rawLen);
-        const long long consumed = st.b.pos - (st.b.bc >> 3);
-        const long long upto = (st.done || st.status) ? st.outPos : (st.outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);
-        for (long long i = flushed; i < upto && i < rawLen; i++) out[i] = S->win[i & (PNG_WIN - 1)];
+        if (!st.done && !st.status) inflate_run(st, *S, inBase + PNG_INRING / 2, flushed + PNG_WIN / 2, (int)zlen, (int)rawLen);
+        const int consumed = st.b.pos - (st.b.bc >> 3);
+        const int upto = (st.done || st.status) ? st.outPos : (st.outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);
+        for (int i = flushed; i < upto && i < rawLen; i++) out[i] = S->win[i & (PNG_WIN - 1)];
         if (upto > flushed) flushed = upto;
         if (st.done || st.status) { result = st.status ? st.status : (st.outPos == rawLen ? 0 : 5); break; }
         while (consumed >= inBase + PNG_INRING / 2) {
-            const long long src = inBase + PNG_INRING;
+            const int src = inBase + PNG_INRING;
             for (int i = 0; i < PNG_INRING / 2; i++) S->in[(src + i) & (PNG_INRING - 1)] = (src + i) < zlen ? z[src + i] : 0;
             inBase += PNG_INRING / 2;
         }
