@@ -126,23 +126,28 @@ __device__ __forceinline__ int sel_next_chunk(int* ticket, int* sh)
     __syncthreads();
     return c;
 }
-// exclusive prefix of chunk `chunk` over the frame, given the chunk's own total (all threads call; sh = one shared int)
+// exclusive prefix of chunk `chunk` over the frame, given the chunk's own total (all threads call; sh = one shared int).
+// The look-back is done by the first warp, 32 predecessors at a time: every lane reads one status word, the nearest
+// inclusive prefix ends the search and the aggregates in front of it are summed with one warp reduction.
 __device__ __forceinline__ int sel_chain_prefix(unsigned* status, int chunk, int total, int* sh)
 {
-    if (threadIdx.x == 0) {
-        int run = 0;
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
         volatile unsigned* st = status;
-        if (chunk > 0) {
-            st[chunk] = CVR_SEL_AGG | (unsigned)total;
-            for (int j = chunk - 1;; j--) {
-                unsigned v;
-                do { v = st[j]; } while (v == 0u);
-                run += (int)(v & 0x3fffffffu);
-                if (v & CVR_SEL_INCL) break;
-            }
+        if (lane == 0 && chunk > 0) st[chunk] = CVR_SEL_AGG | (unsigned)total;
+        int run = 0;
+        for (int hi = chunk - 1; hi >= 0;) {                            // window [hi - 31, hi], lane l looks at hi - l
+            const int j = hi - lane;
+            unsigned v;
+            do { v = j >= 0 ? st[j] : CVR_SEL_INCL; } while (__any_sync(0xffffffffu, v == 0u));   // (entries before the frame count as an inclusive 0)
+            const unsigned incl = __ballot_sync(0xffffffffu, (v & CVR_SEL_INCL) != 0u);
+            const int stop = incl ? __ffs(incl) - 1 : 32;               // nearest lane (= nearest predecessor) that carries an inclusive prefix
+            const int add = lane <= stop ? (int)(v & 0x3fffffffu) : 0;
+            run += __reduce_add_sync(0xffffffffu, add);
+            if (incl) break;
+            hi -= 32;
         }
-        st[chunk] = CVR_SEL_INCL | (unsigned)(run + total);
-        *sh = run;
+        if (lane == 0) { st[chunk] = CVR_SEL_INCL | (unsigned)(run + total); *sh = run; }
     }
     __syncthreads();
     const int r = *sh;

@@ -700,6 +700,38 @@ __global__ void k_ccl_vmerge(const int16_t* __restrict__ img, int* label, int W,
     int* L = label + fo;
     uf_union(L, L[i] & ~CCL_MEMBER, L[i + W] & ~CCL_MEMBER);
 }
+// The same for even image widths, a warp per pair of rows: every lane takes two adjacent pixels of both rows with aligned
+// 32-bit loads and gets the pixel to its left from the neighbouring lane.
+__global__ void __launch_bounds__(128) k_ccl_vmerge2(const int16_t* __restrict__ img, int* label, int W, int H, int B, int newVal, int maxDiff)
+{
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (row >= B * H) return;
+    const int y = row % H;
+    if (y + 1 >= H) return;
+    const size_t fo = (size_t)(row / H) * W * H;
+    const unsigned* up = (const unsigned*)(img + fo + (size_t)y * W);          // W even: every row starts 4-byte aligned
+    const unsigned* dn = (const unsigned*)(img + fo + (size_t)(y + 1) * W);
+    int* L = label + fo;
+    const int W2 = W >> 1;
+    int carryV = newVal, carryQ = newVal;                                       // the pixel left of this chunk (none at x = 0)
+    for (int x0 = 0; x0 < W2; x0 += 32) {
+        const int xw = x0 + lane;
+        const unsigned a = xw < W2 ? up[xw] : ((unsigned)(newVal & 0xffff) * 0x10001u), c = xw < W2 ? dn[xw] : ((unsigned)(newVal & 0xffff) * 0x10001u);
+        const int v0 = (int)(short)(a & 0xffffu), v1 = (int)a >> 16, q0 = (int)(short)(c & 0xffffu), q1 = (int)c >> 16;
+        int vl = __shfl_up_sync(0xffffffffu, v1, 1), ql = __shfl_up_sync(0xffffffffu, q1, 1);
+        if (lane == 0) { vl = carryV; ql = carryQ; }
+        carryV = __shfl_sync(0xffffffffu, v1, 31); carryQ = __shfl_sync(0xffffffffu, q1, 31);
+        if (xw >= W2) continue;
+        const int x = 2 * xw, i = y * W + x;
+        // pixel x: united here unless the pair (x-1) already united the same two runs
+        if (v0 != newVal && q0 != newVal && abs(v0 - q0) <= maxDiff &&
+            !(vl != newVal && ql != newVal && abs(v0 - vl) <= maxDiff && abs(q0 - ql) <= maxDiff && abs(vl - ql) <= maxDiff))
+            uf_union(L, L[i] & ~CCL_MEMBER, L[i + W] & ~CCL_MEMBER);
+        if (v1 != newVal && q1 != newVal && abs(v1 - q1) <= maxDiff &&
+            !(v0 != newVal && q0 != newVal && abs(v1 - v0) <= maxDiff && abs(q1 - q0) <= maxDiff && abs(v0 - q0) <= maxDiff))
+            uf_union(L, L[i + 1] & ~CCL_MEMBER, L[i + 1 + W] & ~CCL_MEMBER);
+    }
+}
 // run starts that are not roots: add the run's length to the root's and point straight at it (roots stay fixed points,
 // so concurrent flattening is safe).  Both passes below walk the label array of the whole batch as one flat array, four
 // labels per thread (16-byte loads; the frame of an element is recovered by a division only where it is needed).
@@ -1008,7 +1040,8 @@ int cvr_launch_speckle(cvr_ctx* c, int B, int newVal, int maxSize, int maxDiff)
     const int W = c->prm.width, H = c->prm.height, N = W * H;
     k_ccl_runs<<<cvr_div_up(B * H, 4), 128, 0, c->stream>>>(c->d_med, c->d_label, c->d_size, W, H, B, newVal, maxDiff);
     LAUNCH_CHECK(c);
-    k_ccl_vmerge<<<dim3(cvr_div_up(W, 128), H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, W, H, newVal, maxDiff);
+    if ((W & 1) == 0) k_ccl_vmerge2<<<cvr_div_up(B * H, 4), 128, 0, c->stream>>>(c->d_med, c->d_label, W, H, B, newVal, maxDiff);
+    else k_ccl_vmerge<<<dim3(cvr_div_up(W, 128), H, B), 128, 0, c->stream>>>(c->d_med, c->d_label, W, H, newVal, maxDiff);
     LAUNCH_CHECK(c);
     const size_t total = (size_t)B * N;
     const unsigned g4 = (unsigned)cvr_div_up_sz(total, 1024);

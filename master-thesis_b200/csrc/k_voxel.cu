@@ -188,11 +188,18 @@ __global__ void __launch_bounds__(128) k_vox_centroid(const cvr_point* __restric
         else {
             const int s = ss[j], e = ss[j + 1];
             float sx = 0, sy = 0, sz = 0, sr = 0, sg = 0, sb = 0, sa = 0;
-            for (int i = s; i < e; i++) {
-                const cvr_point q = p[v[i]];
-                sx = __fadd_rn(sx, q.x); sy = __fadd_rn(sy, q.y); sz = __fadd_rn(sz, q.z);
-                sr = __fadd_rn(sr, (float)q.r); sg = __fadd_rn(sg, (float)q.g); sb = __fadd_rn(sb, (float)q.b); sa = __fadd_rn(sa, (float)q.a);
+            auto acc = [&](const uint4& w) {                           // one member, in member order (the sums are sequential f32 adds)
+                sx = __fadd_rn(sx, __uint_as_float(w.x)); sy = __fadd_rn(sy, __uint_as_float(w.y)); sz = __fadd_rn(sz, __uint_as_float(w.z));
+                sb = __fadd_rn(sb, (float)(w.w & 255u)); sg = __fadd_rn(sg, (float)((w.w >> 8) & 255u)); sr = __fadd_rn(sr, (float)((w.w >> 16) & 255u));
+                sa = __fadd_rn(sa, (float)(w.w >> 24));
+            };
+            const uint4* p4 = (const uint4*)p;
+            int i = s;
+            for (; i + 4 <= e; i += 4) {                               // four gathers in flight, then the four sequential accumulations
+                const uint4 q0 = p4[v[i]], q1 = p4[v[i + 1]], q2 = p4[v[i + 2]], q3 = p4[v[i + 3]];
+                acc(q0); acc(q1); acc(q2); acc(q3);
             }
+            for (; i < e; i++) acc(p4[v[i]]);
             const float cnt = (float)(e - s);
             o.x = __fdiv_rn(sx, cnt); o.y = __fdiv_rn(sy, cnt); o.z = __fdiv_rn(sz, cnt);
             o.r = (uint8_t)__fdiv_rn(sr, cnt); o.g = (uint8_t)__fdiv_rn(sg, cnt); o.b = (uint8_t)__fdiv_rn(sb, cnt); o.a = (uint8_t)__fdiv_rn(sa, cnt);

@@ -32,7 +32,7 @@ def load(path):
 def main():
     path, batch = sys.argv[1], int(sys.argv[2])
     L = [l for l in load(path) if "at::" not in l["name"] and "nccl" not in l["name"].lower()]
-    steps = sum(1 for l in L if l["name"].startswith("k_path_v3") or l["name"].startswith("k_path_v2") or l["name"].startswith("k_path_v<"))
+    steps = sum(1 for l in L if l["name"].startswith(("k_path_v4", "k_path_v3", "k_path_v2", "k_path_v<")))
     agg = collections.OrderedDict()
     for l in L:
         a = agg.setdefault(l["name"], {"n": 0, "ns": 0.0, "rd": 0.0, "wr": 0.0, "grid": l["grid"]})
