@@ -219,11 +219,14 @@ __device__ __forceinline__ unsigned sat_add_pos2(unsigned a, unsigned n) { retur
 __device__ __forceinline__ unsigned sat_sub_pos2(unsigned a, unsigned b) { return __vsub2(__vmaxs2(a, b ^ 0x80008000u), b); }
 
 // One thread per (frame, x', 8 disparities) marching down the rows.  The "old" row (y - SH2 - 1) was read as the "new"
-// row bs rows earlier and is simply read again.  ncu: 288 MB of DRAM traffic per KITTI frame (214 MB algorithmic: the
-// re-read mostly misses the L2, whose share per resident row step is too small for 27 rows) at 92 % of the measured HBM
-// peak.  Measured and rejected on B200: a shared-memory ring of the last bs rows (caps the resident threads: 58-61 us
-// against 48 us), the window in a statically indexed register ring with one 32-bit word per thread (104 us), register
-// prefetch 2-3 rows ahead, and capping the occupancy to make the window fit the L2 (all slower).
+// row bs rows earlier and is simply read again -- from the L2, IF the rows between the two reads fit there.  With one row in
+// flight per thread and full occupancy they do not (300 k resident threads x 28 rows x 16 B = 136 MB: ncu showed 288 MB of DRAM
+// traffic per KITTI frame for 214 MB algorithmic).  Here a thread keeps the loads of P = 16 rows in flight (2 P uint4 registers:
+// 152 registers per thread, so only 12 warps per SM are resident): the same bytes are in flight with a fifth of the columns,
+// and the windows of all resident threads, (28 + P) rows each, shrink to ~40 MB and stay in the L2.  Measured on B200, KITTI
+// batch 110 (us per frame): P = 1 48.3, P = 8 40.2, P = 16 35.9, P = 24 43.4, P = 32 53.5; capping the occupancy further with
+// a shared-memory pad (CVR_VSUM_OCC) changes nothing at P = 16 and hurts at P = 8.
+template <int P>
 __global__ void __launch_bounds__(128) k_vsum(const int16_t* __restrict__ hsum, int16_t* __restrict__ C, SgbmDev p, int B, int* flags)
 {
     const size_t rowWords = (size_t)p.W1 * p.Dp / 8;          // uint4 words per row (Dp is a multiple of 32)
@@ -251,16 +254,25 @@ __global__ void __launch_bounds__(128) k_vsum(const int16_t* __restrict__ hsum, 
     unsigned w[4] = { pack16(c[0], c[1]), pack16(c[2], c[3]), pack16(c[4], c[5]), pack16(c[6], c[7]) };
     unsigned negw = w[0] | w[1] | w[2] | w[3];
     cs[0] = make_uint4(w[0], w[1], w[2], w[3]);
-    for (int y = 1; y < H; y++) {
-        const uint4 ho = __ldcs(hs + (size_t)max(y - SH2 - 1, 0) * rowWords);   // last use of that row: evict-first
-        const uint4 hn = hs[(size_t)min(y + SH2, H - 1) * rowWords];              // read again bs rows later
-        const unsigned o[4] = { ho.x, ho.y, ho.z, ho.w }, n[4] = { hn.x, hn.y, hn.z, hn.w };
+    for (int y0 = 1; y0 < H; y0 += P) {
+        uint4 ho[P], hn[P];
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            w[j] = first ? sat_sub_pos2(sat_add_pos2(w[j], n[j]), o[j]) : sat_add_pos2(sat_sub_pos2(w[j], o[j]), n[j]);
-            negw |= w[j];
+        for (int k = 0; k < P; k++) {                                   // all loads of the next P rows first
+            const int y = min(y0 + k, H - 1);
+            ho[k] = __ldcs(hs + (size_t)max(y - SH2 - 1, 0) * rowWords);  // last use of that row: evict-first
+            hn[k] = hs[(size_t)min(y + SH2, H - 1) * rowWords];           // read again bs rows later
         }
-        __stcs(cs + (size_t)y * rowWords, make_uint4(w[0], w[1], w[2], w[3]));   // streamed out, not re-read here
+#pragma unroll
+        for (int k = 0; k < P; k++) {
+            if (y0 + k >= H) break;
+            const unsigned o[4] = { ho[k].x, ho[k].y, ho[k].z, ho[k].w }, n[4] = { hn[k].x, hn[k].y, hn[k].z, hn[k].w };
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                w[j] = first ? sat_sub_pos2(sat_add_pos2(w[j], n[j]), o[j]) : sat_add_pos2(sat_sub_pos2(w[j], o[j]), n[j]);
+                negw |= w[j];
+            }
+            __stcs(cs + (size_t)(y0 + k) * rowWords, make_uint4(w[0], w[1], w[2], w[3]));   // streamed out, not re-read here
+        }
     }
     if (negw & 0x80008000u) atomicOr(&flags[b], 1);   // a negative C exists in this frame: the packed path kernels take their exact t + C form
 }
@@ -1079,7 +1091,24 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     }
     {
         const size_t nthreads = (size_t)p.W1 * p.Dp / 8 * B;
-        k_vsum<<<(unsigned)cvr_div_up_sz(nthreads, 128), 128, 0, c->stream>>>(c->d_volA, c->d_volC, p, B, c->d_sgflags);
+        // low occupancy + deep prefetch (see k_vsum); tuning hooks: CVR_VSUM_OCC blocks per SM (0 = no cap), CVR_VSUM_P rows ahead (1, 4, 8)
+        static const int occ = getenv("CVR_VSUM_OCC") ? atoi(getenv("CVR_VSUM_OCC")) : 0;
+        static const int P = getenv("CVR_VSUM_P") ? atoi(getenv("CVR_VSUM_P")) : 16;
+        const size_t pad = occ > 0 ? (size_t)(c->smem_optin / occ - 2048) & ~(size_t)255 : 0;
+        const unsigned nb = (unsigned)cvr_div_up_sz(nthreads, 128);
+        if (P >= 16) {
+            if (pad > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_vsum<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad));
+            k_vsum<16><<<nb, 128, pad, c->stream>>>(c->d_volA, c->d_volC, p, B, c->d_sgflags);
+        } else if (P >= 8) {
+            if (pad > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_vsum<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad));
+            k_vsum<8><<<nb, 128, pad, c->stream>>>(c->d_volA, c->d_volC, p, B, c->d_sgflags);
+        } else if (P >= 4) {
+            if (pad > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_vsum<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad));
+            k_vsum<4><<<nb, 128, pad, c->stream>>>(c->d_volA, c->d_volC, p, B, c->d_sgflags);
+        } else {
+            if (pad > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_vsum<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad));
+            k_vsum<1><<<nb, 128, pad, c->stream>>>(c->d_volA, c->d_volC, p, B, c->d_sgflags);
+        }
         LAUNCH_CHECK(c);
         cvr_stage_mark(c, "vsum");
     }
