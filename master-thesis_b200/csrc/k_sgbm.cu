@@ -204,6 +204,148 @@ __global__ void k_pix_hsum(const uint8_t* __restrict__ gray, size_t grayFrameStr
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_pix_hsum4: as k_pix_hsum, FOUR adjacent disparities per thread (two packed pairs).  The per-column work that does not
+// depend on the disparity (the broadcast load of the left descriptor, loop and address arithmetic, the ring slot) is shared
+// by twice as many disparities, and the right-image descriptors are reused from column to column: the thread of disparities
+// d .. d+3 needs R[i], R[i-1], R[i-2], R[i-3] (i = right pixel of disparity d) and one column later R[i+1], R[i], R[i-1],
+// R[i-2] -- ONE new descriptor per column, kept in four registers whose roles rotate (the column loop is unrolled by four so the
+// rotation is register renaming).  The descriptors are stored as four arrays by index mod 4: at a given column every thread
+// reads the same array at consecutive entries (conflict-free 16-byte loads).  Shared-memory wavefronts per column and 64
+// disparities: 9 -> 4.5; the CTA has Dp / 2 threads (two groups of Dp / 4, each owning half of the segment).
+__global__ void k_pix_hsum4(const uint8_t* __restrict__ gray, size_t grayFrameStride, int16_t* __restrict__ hsum, SgbmDev p, int nseg)
+{
+    extern __shared__ uint4 sm4[];
+    const int y = blockIdx.x / nseg, seg = blockIdx.x % nseg, b = blockIdx.y, W = p.W, H = p.H;
+    const int W1 = p.W1, Dp = p.Dp, SW2 = p.SW2;
+    const int s = (int)(((long long)W1 * seg) / nseg), e = (int)(((long long)W1 * (seg + 1)) / nseg);
+    const int ps = max(s - SW2, 0), pe = min(e - 1 + SW2, W1 - 1);                 // computed columns whose pixel cost is needed
+    const int xl0 = ps + p.minX1, xl1 = pe + p.minX1;                              // left pixels needed: [xl0, xl1]
+    const int xr0 = max(xl0 - p.minD - (p.D - 1), 0), xr1 = min(xl1 - p.minD, W - 1);   // right pixels needed: [xr0, xr1]
+    const int nL = xl1 - xl0 + 1, nR = xr1 - xr0 + 1;
+    const int nR4 = (nR + 3) / 4 + 1;                   // entries per residue array
+    uint4* Lpk = sm4;                                   // [nL]
+    uint4* R4 = sm4 + nL;                               // [4][nR4]: R4[k][j] = descriptor of right pixel xr0 + 4 j + k
+    unsigned* aL = (unsigned*)(R4 + 4 * nR4);           // [nL + 2]  packed (G | R << 16) of left pixels xl0-1 .. xl1+1
+    unsigned* aR = aL + nL + 2;                         // [nR + 2]
+    uint2* ringbuf = (uint2*)(((size_t)(aR + nR + 2) + 7) & ~(size_t)7);
+    const int tid = threadIdx.x, nt = blockDim.x;
+    const uint8_t* gl = gray + (size_t)b * grayFrameStride;
+    const uint8_t* gr = gl + (size_t)H * p.Wp;
+    const int yn = max(y - 1, 0), ys = min(y + 1, H - 1);
+    const int ft = p.ftzero;
+    const unsigned border = (unsigned)ft | ((unsigned)ft << 16);
+    for (int i = tid; i < nL + 2 + nR + 2; i += nt) {
+        const bool right = i >= nL + 2;
+        const int x = right ? xr0 - 1 + (i - nL - 2) : xl0 - 1 + i;
+        const uint8_t* g = right ? gr : gl;
+        unsigned v = border;
+        if (x > 0 && x < W - 1) {
+            const uint8_t *r0 = g + (size_t)y * p.Wp + x, *rn = g + (size_t)yn * p.Wp + x, *rs = g + (size_t)ys * p.Wp + x;
+            int a = 2 * ((int)r0[1] - (int)r0[-1]) + ((int)rn[1] - (int)rn[-1]) + ((int)rs[1] - (int)rs[-1]);
+            a = min(max(a, -ft), ft) + ft;
+            v = (unsigned)a | ((unsigned)r0[0] << 16);
+        }
+        (right ? aR : aL)[right ? i - nL - 2 : i] = v;      // columns outside the image never matter (guarded below)
+    }
+    __syncthreads();
+    for (int i = tid; i < nL + nR; i += nt) {
+        const bool right = i >= nL;
+        const int j = right ? i - nL : i;
+        const int x = (right ? xr0 : xl0) + j;
+        const unsigned* a = (right ? aR : aL) + j + 1;
+        const unsigned u = a[0];
+        const unsigned ul = x > 0 ? (((u + a[-1]) >> 1) & 0x7fff7fffu) : u;
+        const unsigned ur = x < W - 1 ? (((u + a[1]) >> 1) & 0x7fff7fffu) : u;
+        const unsigned u0 = __vimin3_s16x2(ul, ur, u), u1 = __vimax3_s16x2(ul, ur, u);
+        const uint4 dsc = make_uint4(u, u0, pk_neg(u), pk_neg(u1));
+        if (right) R4[(j & 3) * nR4 + (j >> 2)] = dsc; else Lpk[j] = dsc;
+    }
+    __syncthreads();
+
+    const int quarter = Dp >> 2, grp = tid / quarter, q = tid - grp * quarter, d = 4 * q;
+    const int mid = s + ((e - s + 1) >> 1);
+    const int hs_ = grp ? mid : s, he_ = grp ? e : mid;                        // this group's output columns [hs_, he_)
+    if (hs_ >= he_) return;
+    const int half = Dp >> 1;                                                  // words per output column
+    uint2* out = (uint2*)((unsigned*)(hsum + (((size_t)b * H + y) * W1) * Dp) + 2 * q);   // this thread's two words of column 0
+    if (d >= p.D) {                                                            // padding disparities (D is a multiple of 16: all four or none)
+        for (int xp = hs_; xp < he_; xp++) out[(size_t)xp * (half / 2)] = make_uint2(0u, 0u);
+        return;
+    }
+    const int offR = p.minX1 - p.minD - d - xr0;        // right descriptor index of computed column xp for disparity d: xp + offR (d + t: t less)
+    const int offL = p.minX1 - xl0;
+    auto cost1 = [](const uint4& l, const uint4& r) -> unsigned {
+        const unsigned c0 = __vimax3_s16x2_relu(__vadd2(l.x, r.w), __vadd2(r.y, l.z), 0u);   // max(0, u - v1, v0 - u)
+        const unsigned c1 = __vimax3_s16x2_relu(__vadd2(r.x, l.w), __vadd2(l.y, r.z), 0u);   // max(0, v - u1, u0 - v)
+        const unsigned m = __vmins2(c0, c1);
+        return (m & 0xffffu) + (m >> 18);                                     // Sobel-channel cost + (intensity cost >> 2), <= 255
+    };
+    auto rdesc = [&](int i) -> uint4 { return R4[(i & 3) * nR4 + (i >> 2)]; };
+    auto pixcost4 = [&](int xp) -> uint2 {                                     // generic form: the four descriptors fetched afresh
+        const uint4 l = Lpk[xp + offL];
+        const int i = xp + offR;
+        return make_uint2(cost1(l, rdesc(i)) | (cost1(l, rdesc(i - 1)) << 16), cost1(l, rdesc(i - 2)) | (cost1(l, rdesc(i - 3)) << 16));
+    };
+    // ring of the last bs + 1 cost quadruples per thread: p.ring slots (a power of two), slot s of this thread at ring[s * quarter]
+    uint2* ring = ringbuf + (size_t)grp * p.ring * quarter + q;
+    const int mask = p.ring - 1, bs = p.bs;
+    unsigned run0 = 0, run1 = 0;                                               // four running sums (each < 2^15: provably unsaturated)
+    const int j0 = hs_ - SW2, j1 = he_ - 1 + SW2;
+    int j = j0, ws = 0;                                                        // ws: the ring slot written next
+    for (; j < hs_ + SW2; j++) {                                               // warm-up: the first bs - 1 window elements
+        const uint2 cp = pixcost4(min(max(j, 0), W1 - 1));
+        run0 += cp.x; run1 += cp.y;
+        ring[ws * quarter] = cp;
+        ws = (ws + 1) & mask;
+    }
+    uint2* o = out + (size_t)hs_ * (half / 2);
+    {
+        const uint2 cp = pixcost4(min(j, W1 - 1));
+        run0 += cp.x; run1 += cp.y;
+        ring[ws * quarter] = cp; ws = (ws + 1) & mask;
+        *o = make_uint2(run0, run1); o += half / 2; j++;
+    }
+    const int jmid = min(j1, W1 - 1);
+    auto emit = [&](const uint2 cp) {                                          // one steady-state step with the cost quadruple of element j
+        const uint2 old = ring[((ws - bs) & mask) * quarter];                  // the element written bs steps ago leaves the window
+        run0 = run0 + cp.x - old.x; run1 = run1 + cp.y - old.y;
+        ring[ws * quarter] = cp;
+        *o = make_uint2(run0, run1); o += half / 2;
+        ws = (ws + 1) & mask;
+    };
+    while (j <= jmid && ((j + offR) & 3) != 0) { emit(pixcost4(j)); j++; }    // make the right index of disparity d a multiple of four
+    if (j + 3 <= jmid) {
+        const int i0 = j + offR;                                               // multiple of 4
+        uint4 ra = rdesc(i0), rb = rdesc(i0 - 1), rc = rdesc(i0 - 2), rd = rdesc(i0 - 3);   // R[i0], R[i0-1], R[i0-2], R[i0-3]
+        const uint4* lp = Lpk + (j + offL);
+        const uint4* r1 = R4 + 1 * nR4 + (i0 >> 2);                            // R[i0 + 1], then + 4 per turn
+        const uint4* r2 = R4 + 2 * nR4 + (i0 >> 2);
+        const uint4* r3 = R4 + 3 * nR4 + (i0 >> 2);
+        const uint4* r0n = R4 + 0 * nR4 + (i0 >> 2) + 1;                       // R[i0 + 4]
+        for (;;) {
+            const uint4 l0 = lp[0], l1 = lp[1], l2 = lp[2], l3 = lp[3];
+            emit(make_uint2(cost1(l0, ra) | (cost1(l0, rb) << 16), cost1(l0, rc) | (cost1(l0, rd) << 16)));     // column j    : d..d+3 <- R[i0], R[i0-1], R[i0-2], R[i0-3]
+            rd = *r1;                                                                                            // R[i0+1]
+            emit(make_uint2(cost1(l1, rd) | (cost1(l1, ra) << 16), cost1(l1, rb) | (cost1(l1, rc) << 16)));     // column j + 1
+            rc = *r2;                                                                                            // R[i0+2]
+            emit(make_uint2(cost1(l2, rc) | (cost1(l2, rd) << 16), cost1(l2, ra) | (cost1(l2, rb) << 16)));     // column j + 2
+            rb = *r3;                                                                                            // R[i0+3]
+            emit(make_uint2(cost1(l3, rb) | (cost1(l3, rc) << 16), cost1(l3, rd) | (cost1(l3, ra) << 16)));     // column j + 3
+            j += 4;
+            if (j + 3 > jmid) break;
+            ra = *r0n;                                                                                           // R[i0+4]: the next turn's R[i0]
+            // roles for the next turn: R[i0'] = ra, R[i0'-1] = rb (R[i0+3]), R[i0'-2] = rc (R[i0+2]), R[i0'-3] = rd (R[i0+1])
+            lp += 4; r1++; r2++; r3++; r0n++;
+        }
+    }
+    for (; j <= jmid; j++) emit(pixcost4(j));
+    if (j <= j1) {                                                            // right image border: the last column repeats
+        const uint2 cl = pixcost4(W1 - 1);
+        for (; j <= j1; j++) emit(cl);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // A.3 (vertical): C[0] = s16(P2) (+) hsum[0]*(SH2+1) (+) hsum[1..SH2];  C[y] = sat(sat(C[y-1] - old) + new)
 // (x' = 0: sat(sat(C[y-1] + new) - old)).
 // One thread per (frame, x', 4 disparities) marching down the rows.
@@ -1082,10 +1224,18 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         if (nseg < 1) nseg = 1;
         const int segMax = cvr_div_up(p.W1, nseg) + 1;
         const size_t nLmax = (size_t)segMax + 2 * p.SW2 + 2, nRmax = nLmax + p.D;
+        static const int pixVariant = getenv("CVR_PIX_HSUM") ? atoi(getenv("CVR_PIX_HSUM")) : 4;   // 4 disparities per thread (default) or 2
+        if (pixVariant == 4) {
+            // descriptors (left + four residue arrays of the right ones) + unpacked pixels + two rings (one per thread group) of cost quadruples
+            const size_t smem = (nLmax + nRmax + 20) * sizeof(uint4) + (nLmax + nRmax + 6) * sizeof(unsigned) + 16 + (size_t)4 * p.ring * p.Dp;
+            if (smem > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            k_pix_hsum4<<<dim3(p.H * nseg, B), p.Dp / 2, smem, c->stream>>>(c->d_gray, (size_t)2 * p.H * p.Wp, c->d_volA, p, nseg);
+        } else {
         const size_t smem = (nLmax + nRmax + 4) * (sizeof(uint4) + sizeof(unsigned)) + 16 + (size_t)4 * p.ring * p.Dp;   // descriptors + two rings (one per thread group) of packed cost pairs
         // the opt-in is per function and device, shared by every context on that device: set it before each launch that needs it
         if (smem > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         k_pix_hsum<<<dim3(p.H * nseg, B), p.Dp, smem, c->stream>>>(c->d_gray, (size_t)2 * p.H * p.Wp, c->d_volA, p, nseg);
+        }
         LAUNCH_CHECK(c);
         cvr_stage_mark(c, "pix_hsum");
     }
