@@ -227,7 +227,9 @@ __global__ void k_pix_hsum4(const uint8_t* __restrict__ gray, size_t grayFrameSt
     uint4* R4 = sm4 + nL;                               // [4][nR4]: R4[k][j] = descriptor of right pixel xr0 + 4 j + k
     unsigned* aL = (unsigned*)(R4 + 4 * nR4);           // [nL + 2]  packed (G | R << 16) of left pixels xl0-1 .. xl1+1
     unsigned* aR = aL + nL + 2;                         // [nR + 2]
-    uint2* ringbuf = (uint2*)(((size_t)(aR + nR + 2) + 7) & ~(size_t)7);
+    // the ring of the last bs + 1 cost quadruples (one byte per cost: <= 2 * ftzero + 63 <= 189) reuses the unpacked-pixel staging,
+    // which is dead once the descriptors are built
+    unsigned* ringbuf = aL;
     const int tid = threadIdx.x, nt = blockDim.x;
     const uint8_t* gl = gray + (size_t)b * grayFrameStride;
     const uint8_t* gr = gl + (size_t)H * p.Wp;
@@ -287,7 +289,8 @@ __global__ void k_pix_hsum4(const uint8_t* __restrict__ gray, size_t grayFrameSt
         return make_uint2(cost1(l, rdesc(i)) | (cost1(l, rdesc(i - 1)) << 16), cost1(l, rdesc(i - 2)) | (cost1(l, rdesc(i - 3)) << 16));
     };
     // ring of the last bs + 1 cost quadruples per thread: p.ring slots (a power of two), slot s of this thread at ring[s * quarter]
-    uint2* ring = ringbuf + (size_t)grp * p.ring * quarter + q;
+    unsigned* ring = ringbuf + (size_t)grp * p.ring * quarter + q;
+    auto pack8 = [](const uint2 cp) -> unsigned { return __byte_perm(cp.x, cp.y, 0x6420); };          // four costs, a byte each
     const int mask = p.ring - 1, bs = p.bs;
     unsigned run0 = 0, run1 = 0;                                               // four running sums (each < 2^15: provably unsaturated)
     const int j0 = hs_ - SW2, j1 = he_ - 1 + SW2;
@@ -295,21 +298,21 @@ __global__ void k_pix_hsum4(const uint8_t* __restrict__ gray, size_t grayFrameSt
     for (; j < hs_ + SW2; j++) {                                               // warm-up: the first bs - 1 window elements
         const uint2 cp = pixcost4(min(max(j, 0), W1 - 1));
         run0 += cp.x; run1 += cp.y;
-        ring[ws * quarter] = cp;
+        ring[ws * quarter] = pack8(cp);
         ws = (ws + 1) & mask;
     }
     uint2* o = out + (size_t)hs_ * (half / 2);
     {
         const uint2 cp = pixcost4(min(j, W1 - 1));
         run0 += cp.x; run1 += cp.y;
-        ring[ws * quarter] = cp; ws = (ws + 1) & mask;
+        ring[ws * quarter] = pack8(cp); ws = (ws + 1) & mask;
         *o = make_uint2(run0, run1); o += half / 2; j++;
     }
     const int jmid = min(j1, W1 - 1);
     auto emit = [&](const uint2 cp) {                                          // one steady-state step with the cost quadruple of element j
-        const uint2 old = ring[((ws - bs) & mask) * quarter];                  // the element written bs steps ago leaves the window
-        run0 = run0 + cp.x - old.x; run1 = run1 + cp.y - old.y;
-        ring[ws * quarter] = cp;
+        const unsigned old = ring[((ws - bs) & mask) * quarter];               // the element written bs steps ago leaves the window
+        run0 = run0 + cp.x - __byte_perm(old, 0u, 0x4140); run1 = run1 + cp.y - __byte_perm(old, 0u, 0x4342);
+        ring[ws * quarter] = pack8(cp);
         *o = make_uint2(run0, run1); o += half / 2;
         ws = (ws + 1) & mask;
     };
@@ -1227,7 +1230,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         static const int pixVariant = getenv("CVR_PIX_HSUM") ? atoi(getenv("CVR_PIX_HSUM")) : 4;   // 4 disparities per thread (default) or 2
         if (pixVariant == 4) {
             // descriptors (left + four residue arrays of the right ones) + unpacked pixels + two rings (one per thread group) of cost quadruples
-            const size_t smem = (nLmax + nRmax + 20) * sizeof(uint4) + (nLmax + nRmax + 6) * sizeof(unsigned) + 16 + (size_t)4 * p.ring * p.Dp;
+            const size_t stage = (nLmax + nRmax + 6) * sizeof(unsigned), ringB = (size_t)2 * p.ring * p.Dp;   // the ring (one byte per cost) reuses the staging area
+            const size_t smem = (nLmax + nRmax + 20) * sizeof(uint4) + (stage > ringB ? stage : ringB) + 16;
             if (smem > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_pix_hsum4, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             k_pix_hsum4<<<dim3(p.H * nseg, B), p.Dp / 2, smem, c->stream>>>(c->d_gray, (size_t)2 * p.H * p.Wp, c->d_volA, p, nseg);
         } else {
