@@ -54,6 +54,8 @@ struct VoxelHdr {
     int n;               // number of input points
     int m;               // number of voxels (output points)
     int maxkey;
+    int nruns;           // number of runs of consecutive points with equal voxel index (what is actually sorted)
+    int pad;
 };
 
 // per-frame bounding box of a point array: floats through an order-preserving uint mapping (f2ord, cvr_scan.cuh)

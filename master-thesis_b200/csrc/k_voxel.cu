@@ -16,7 +16,7 @@ __global__ void k_vox_setup(const VoxBox* box, const int* nPtr, VoxelHdr* hdr, f
     int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
     VoxelHdr h;
-    h.n = nPtr[b]; h.m = 0; h.passthrough = 0; h.maxkey = 0;
+    h.n = nPtr[b]; h.m = 0; h.passthrough = 0; h.maxkey = 0; h.nruns = 0; h.pad = 0;
     const float inv[3] = { __fdiv_rn(1.0f, lx), __fdiv_rn(1.0f, ly), __fdiv_rn(1.0f, lz) };
     long long cells = 1;
     for (int k = 0; k < 3; k++) {
@@ -32,7 +32,7 @@ __global__ void k_vox_setup(const VoxBox* box, const int* nPtr, VoxelHdr* hdr, f
     hdr[b] = h;
 }
 __global__ void k_vox_keys(const cvr_point* __restrict__ pts, size_t stride, const VoxelHdr* __restrict__ hdr, float lx, float ly, float lz,
-                           uint32_t* __restrict__ keys, uint32_t* __restrict__ vals, size_t kvStride)
+                           uint32_t* __restrict__ pkeys, size_t kvStride)
 {
     const int b = blockIdx.y;
     const VoxelHdr h = hdr[b];
@@ -42,8 +42,48 @@ __global__ void k_vox_keys(const cvr_point* __restrict__ pts, size_t stride, con
         const int i0 = (int)floorf(__fmul_rn(q.x, ix)) - h.minb[0];
         const int i1 = (int)floorf(__fmul_rn(q.y, iy)) - h.minb[1];
         const int i2 = (int)floorf(__fmul_rn(q.z, iz)) - h.minb[2];
-        keys[(size_t)b * kvStride + i] = h.passthrough ? 0u : (uint32_t)(i0 + i1 * h.div[0] + i2 * h.div[0] * h.div[1]);
-        vals[(size_t)b * kvStride + i] = (uint32_t)i;
+        pkeys[(size_t)b * kvStride + i] = h.passthrough ? 0u : (uint32_t)(i0 + i1 * h.div[0] + i2 * h.div[0] * h.div[1]);
+    }
+}
+// Points arrive in pixel order, and neighbouring pixels mostly fall into the same voxel: the cloud is a sequence of RUNS of
+// consecutive points with equal voxel index, several times fewer than points.  Only the runs are sorted (stable, by index);
+// a voxel is then a stretch of sorted runs, its members the points of those runs in ascending point order -- exactly the
+// member order a stable sort of the points would give, which is the order the centroid sums are defined in.
+// Run heads by the single-pass ordered selection: run r starts at point runStart[r] and has voxel index runKey[r].
+__global__ void __launch_bounds__(CVR_SEL_THREADS) k_vox_runs(const uint32_t* __restrict__ pkeys, size_t kvStride, VoxelHdr* hdr, int* sel, size_t selStride,
+                                                              uint32_t* __restrict__ runKey, uint32_t* __restrict__ runId, int* __restrict__ runStart)
+{
+    __shared__ int ws[33];
+    __shared__ int sh;
+    const int b = blockIdx.y, n = hdr[b].n, nch = (n + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;
+    const bool pass = hdr[b].passthrough != 0;
+    const uint32_t* k = pkeys + (size_t)b * kvStride;
+    uint32_t* rk = runKey + (size_t)b * kvStride; uint32_t* ri = runId + (size_t)b * kvStride;
+    int* rs = runStart + (size_t)b * kvStride;
+    unsigned* status = (unsigned*)sel + (size_t)b * selStride;
+    int* ticket = (int*)status + (selStride - 1);
+    if (nch == 0) { if (blockIdx.x == 0 && threadIdx.x == 0) hdr[b].nruns = 0; return; }
+    for (;;) {
+        const int chunk = sel_next_chunk(ticket, &sh);
+        if (chunk >= nch) break;
+        const int i0 = chunk * CVR_SEL_BLOCK + threadIdx.x * CVR_SEL_ITEMS;
+        int f[CVR_SEL_ITEMS], cnt = 0;
+        uint32_t key[CVR_SEL_ITEMS];
+        uint32_t prev = (i0 > 0 && i0 - 1 < n) ? k[i0 - 1] : 0u;
+#pragma unroll
+        for (int j = 0; j < CVR_SEL_ITEMS; j++) {
+            const int i = i0 + j;
+            key[j] = i < n ? k[i] : 0u;
+            f[j] = (i < n) && (pass || i == 0 || key[j] != prev);
+            prev = key[j]; cnt += f[j];
+        }
+        int tot;
+        const int e = block_excl_scan(cnt, ws, &tot);
+        const int base = sel_chain_prefix(status, chunk, tot, &sh);
+        int o = base + e;
+#pragma unroll
+        for (int j = 0; j < CVR_SEL_ITEMS; j++) if (f[j]) { rk[o] = key[j]; ri[o] = (uint32_t)o; rs[o] = i0 + j; o++; }
+        if (chunk == nch - 1 && threadIdx.x == 0) hdr[b].nruns = base + tot;
     }
 }
 
@@ -138,7 +178,7 @@ __global__ void __launch_bounds__(CVR_SEL_THREADS) k_seg_select(const uint32_t* 
 {
     __shared__ int ws[33];
     __shared__ int sh;
-    const int b = blockIdx.y, n = hdr[b].n, nch = (n + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;
+    const int b = blockIdx.y, n = hdr[b].nruns, nch = (n + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;   // over the SORTED RUNS
     const bool pass = hdr[b].passthrough != 0;
     const uint32_t* k = (rs_result_buf(hdr, b) ? keys1 : keys0) + (size_t)b * kvStride;
     int* ss = segstart + (size_t)b * segStride;
@@ -171,7 +211,7 @@ __global__ void __launch_bounds__(CVR_SEL_THREADS) k_seg_select(const uint32_t* 
 // the count, truncates the colours.  Member order = ascending point index (stable sort), as in the oracle.
 // Also accumulates the bounding box of the centroids (the outlier filter that follows builds its search grid from it).
 __global__ void __launch_bounds__(128) k_vox_centroid(const cvr_point* __restrict__ pts, size_t stride, const uint32_t* __restrict__ vals0, const uint32_t* __restrict__ vals1, size_t kvStride,
-                               const VoxelHdr* __restrict__ hdr, const int* __restrict__ segstart, size_t segStride,
+                               const VoxelHdr* __restrict__ hdr, const int* __restrict__ segstart, size_t segStride, const int* __restrict__ runStart,
                                cvr_point* __restrict__ out, size_t outStride, int* __restrict__ mOut, VoxBox* box)
 {
     const int b = blockIdx.y;
@@ -179,28 +219,35 @@ __global__ void __launch_bounds__(128) k_vox_centroid(const cvr_point* __restric
     if (blockIdx.x == 0 && threadIdx.x == 0) mOut[b] = h.m;
     const cvr_point* p = pts + (size_t)b * stride;
     const int* ss = segstart + (size_t)b * segStride;
-    const uint32_t* v = (rs_result_buf(hdr, b) ? vals1 : vals0) + (size_t)b * kvStride;
+    const uint32_t* v = (rs_result_buf(hdr, b) ? vals1 : vals0) + (size_t)b * kvStride;   // sorted run ids
+    const int* rs = runStart + (size_t)b * kvStride;
     unsigned mn[3] = { 0xffffffffu, 0xffffffffu, 0xffffffffu }, mx[3] = { 0, 0, 0 };
     bool any = false;
     for (int j = blockIdx.x * blockDim.x + threadIdx.x; j < h.m; j += gridDim.x * blockDim.x) {
         cvr_point o;
         if (h.passthrough) o = p[j];
         else {
-            const int s = ss[j], e = ss[j + 1];
+            const int s = ss[j], e = ss[j + 1];                        // the voxel's stretch of sorted runs
             float sx = 0, sy = 0, sz = 0, sr = 0, sg = 0, sb = 0, sa = 0;
+            int cntPts = 0;
             auto acc = [&](const uint4& w) {                           // one member, in member order (the sums are sequential f32 adds)
                 sx = __fadd_rn(sx, __uint_as_float(w.x)); sy = __fadd_rn(sy, __uint_as_float(w.y)); sz = __fadd_rn(sz, __uint_as_float(w.z));
                 sb = __fadd_rn(sb, (float)(w.w & 255u)); sg = __fadd_rn(sg, (float)((w.w >> 8) & 255u)); sr = __fadd_rn(sr, (float)((w.w >> 16) & 255u));
                 sa = __fadd_rn(sa, (float)(w.w >> 24));
             };
             const uint4* p4 = (const uint4*)p;
-            int i = s;
-            for (; i + 4 <= e; i += 4) {                               // four gathers in flight, then the four sequential accumulations
-                const uint4 q0 = p4[v[i]], q1 = p4[v[i + 1]], q2 = p4[v[i + 2]], q3 = p4[v[i + 3]];
-                acc(q0); acc(q1); acc(q2); acc(q3);
+            for (int r = s; r < e; r++) {                              // runs in ascending run id = ascending point index (stable sort)
+                const int rid = (int)v[r];
+                const int pb = rs[rid], pe = rid + 1 < h.nruns ? rs[rid + 1] : h.n;
+                int i = pb;
+                for (; i + 4 <= pe; i += 4) {                          // a run's points are contiguous: four loads in flight
+                    const uint4 q0 = p4[i], q1 = p4[i + 1], q2 = p4[i + 2], q3 = p4[i + 3];
+                    acc(q0); acc(q1); acc(q2); acc(q3);
+                }
+                for (; i < pe; i++) acc(p4[i]);
+                cntPts += pe - pb;
             }
-            for (; i < e; i++) acc(p4[v[i]]);
-            const float cnt = (float)(e - s);
+            const float cnt = (float)cntPts;
             o.x = __fdiv_rn(sx, cnt); o.y = __fdiv_rn(sy, cnt); o.z = __fdiv_rn(sz, cnt);
             o.r = (uint8_t)__fdiv_rn(sr, cnt); o.g = (uint8_t)__fdiv_rn(sg, cnt); o.b = (uint8_t)__fdiv_rn(sb, cnt); o.a = (uint8_t)__fdiv_rn(sa, cnt);
         }
@@ -252,21 +299,29 @@ int cvr_launch_voxel(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, c
         LAUNCH_CHECK(c);
     }
     const size_t selStride = cvr_sel_stride(maxN);
-    int* sel = c->d_sel + (size_t)c->maxB * selStride;                 // selection 1 of the chain
+    int* sel = c->d_sel + (size_t)c->maxB * selStride;                 // selection 1 of the chain (run heads), then selection 0 again (voxel heads)
+    int* sel2 = c->d_sel;
     CVR_CUDA(c, cudaMemsetAsync(sel, 0, (size_t)B * selStride * sizeof(int), c->stream));
+    CVR_CUDA(c, cudaMemsetAsync(sel2, 0, (size_t)B * selStride * sizeof(int), c->stream));
     k_vox_setup<<<cvr_div_up(B, 128), 128, 0, c->stream>>>(c->d_boxv, n_in, c->d_vhdr, lx, ly, lz, B);
     LAUNCH_CHECK(c);
-    k_vox_keys<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B), 256, 0, c->stream>>>(in, in_stride, c->d_vhdr, lx, ly, lz, c->d_keys[0], c->d_vals[0], kvStride);
+    uint32_t* pkeys = (uint32_t*)c->d_cellidx;                         // per-point voxel index (scratch of the outlier filters, idle here)
+    int* runStart = (int*)c->d_meand;                                  // first point of every run (ditto)
+    const dim3 gp(cvr_frame_blocks(c, B, (size_t)maxN, 256, 8), B);
+    k_vox_keys<<<gp, 256, 0, c->stream>>>(in, in_stride, c->d_vhdr, lx, ly, lz, pkeys, kvStride);
+    LAUNCH_CHECK(c);
+    const int nch = cvr_div_up(maxN, CVR_SEL_BLOCK);
+    const dim3 gs(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B);
+    k_vox_runs<<<gs, CVR_SEL_THREADS, 0, c->stream>>>(pkeys, kvStride, c->d_vhdr, sel, selStride, c->d_keys[0], c->d_vals[0], runStart);
     LAUNCH_CHECK(c);
     int buf = 0;
-    int rc = cvr_radix_sort_pairs(c, B, n_in, 1, maxN, 4, c->d_vhdr, &buf);   // the result buffer is per frame: rs_result_buf
+    const int hdrInts = (int)(sizeof(VoxelHdr) / sizeof(int));
+    int rc = cvr_radix_sort_pairs(c, B, &c->d_vhdr[0].nruns, hdrInts, maxN, 4, c->d_vhdr, &buf);   // sorts the RUNS; the result buffer is per frame: rs_result_buf
     if (rc) return rc;
-    const int nch = cvr_div_up(maxN, CVR_SEL_BLOCK);
-    k_seg_select<<<dim3(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B), CVR_SEL_THREADS, 0, c->stream>>>(c->d_keys[0], c->d_keys[1], kvStride, c->d_vhdr, sel, selStride,
-                                                                                                 c->d_segstart, (size_t)maxN + 1);
+    k_seg_select<<<gs, CVR_SEL_THREADS, 0, c->stream>>>(c->d_keys[0], c->d_keys[1], kvStride, c->d_vhdr, sel2, selStride, c->d_segstart, (size_t)maxN + 1);
     LAUNCH_CHECK(c);
     k_vox_centroid<<<dim3(cvr_frame_blocks(c, B, (size_t)maxN, 128, 8), B), 128, 0, c->stream>>>(in, in_stride, c->d_vals[0], c->d_vals[1], kvStride, c->d_vhdr, c->d_segstart,
-                                                                                                (size_t)maxN + 1, c->d_vox, (size_t)maxN, c->d_nvox, c->d_boxs);
+                                                                                                (size_t)maxN + 1, runStart, c->d_vox, (size_t)maxN, c->d_nvox, c->d_boxs);
     LAUNCH_CHECK(c);
     cvr_stage_mark(c, "voxel");
     return CVR_OK;
