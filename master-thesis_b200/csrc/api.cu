@@ -401,7 +401,9 @@ extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, i
         case 1:
             if (!c->keep_S) { c->err = "the final S volume is only kept when the context was created with CVR_KEEP_S=1 in the environment"; return CVR_ERR_INVALID_ARG; }
             src = c->d_volA; need = vol; break;
-        case 2: src = c->d_raw; need = (size_t)g.W * g.H * 2; break;
+        case 2:
+            if (!c->keep_S) { c->err = "the raw disparity is only kept when the context was created with CVR_KEEP_S=1 in the environment"; return CVR_ERR_INVALID_ARG; }
+            src = c->d_raw; need = (size_t)g.W * g.H * 2; break;
         case 3: src = c->d_disp; need = (size_t)g.W * g.H * 2; break;
         default: c->err = "unknown debug buffer"; return CVR_ERR_INVALID_ARG;
     }

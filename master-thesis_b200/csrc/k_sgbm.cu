@@ -651,7 +651,7 @@ __global__ void __launch_bounds__(NT) k_path_v(const int16_t* __restrict__ C, in
 // ------------------------------------------------------------------------------------------------
 // A.5 second half.  One CTA per (row, frame).  disp2[x2] is the `best` of the pixel with the smallest minS
 // among those mapping to x2, the largest x' winning ties (the sequential right-to-left scan with strict '>').
-__global__ void k_lrcheck(int16_t* __restrict__ raw, const int2* __restrict__ aux, int16_t* __restrict__ disp, SgbmDev p)
+__global__ void k_lrcheck(int16_t* __restrict__ raw, const int2* __restrict__ aux, int16_t* __restrict__ disp, SgbmDev p, int keepRaw)
 {
     extern __shared__ unsigned key[];                   // [W] right-view keys, then [W] raw disparities of this row
     int* rawsm = (int*)(key + p.W);
@@ -682,7 +682,7 @@ __global__ void k_lrcheck(int16_t* __restrict__ raw, const int2* __restrict__ au
     for (int x = threadIdx.x; x < W; x += blockDim.x) {
         int v = p.INVALID;
         const int d1 = rawsm[x];
-        rawr[x] = (int16_t)d1;                          // kept for cvr_debug_fetch
+        if (keepRaw) rawr[x] = (int16_t)d1;             // only kept for cvr_debug_fetch(2) (CVR_KEEP_S=1)
         if (x >= p.minX1 && x < p.maxX1) {
             v = d1;
             if (d1 != p.INVALID) {
@@ -1283,7 +1283,7 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     if (rc) return rc;
     const size_t lrSmem = (size_t)p.W * 2 * sizeof(int);              // validate() keeps this within the opt-in limit (width <= 16384)
     if (lrSmem > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_lrcheck, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lrSmem));
-    k_lrcheck<<<dim3(p.H, B), 256, lrSmem, c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p);
+    k_lrcheck<<<dim3(p.H, B), 256, lrSmem, c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p, c->keep_S ? 1 : 0);
     LAUNCH_CHECK(c);
     if ((p.W & 1) == 0) k_median3_x2<<<dim3(cvr_div_up(p.W, 256), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
     else k_median3<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
