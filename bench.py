@@ -11,7 +11,7 @@ batch fixed); the only exchange is cvr_gather_clouds (NCCL) to rank 0.
           device buffer of rank 0
   e2e   : frames/s through the same C-ABI calls with pinned HOST buffers: H2D of both images inside the timed region, and
           the filtered clouds of EVERY rank delivered to rank 0's host memory (N = 1: the D2H copy of cvr_wait_batch)
-  roofline     : dominant kernel (k_path_v3), algorithmic bytes / its CUDA-event time measured on the library's stream
+  roofline     : dominant kernel (k_path_v4), algorithmic bytes / its CUDA-event time measured on the library's stream
                  during the timed steps; `path` = the whole step against SURVEY 8(d)'s 458 MB per frame;
                  `traffic` / `dram_bytes_per_frame` from the ncu capture committed under profiles/ (refused when the
                  capture was taken on other kernel sources or another batch size)
@@ -500,7 +500,7 @@ def main():
     if rank == 0:
         peak, peak_kind = hbm_peak()
         cells = (W - D) * H * D
-        alg_bytes = 6.0 * cells * B                 # k_path_v3 per launch: read C, read S, write S (int16 each)
+        alg_bytes = 6.0 * cells * B                 # k_path_v4 per launch: read C, read S, write S (int16 each)
         kv = stage_ms.get("path_v_down", [])
         if args.matcher == "bm":
             kv = []
@@ -519,14 +519,14 @@ def main():
                 elif int(tr.get("batch", -1)) != B:
                     note = "profiles/r02_traffic.json was captured at batch %s, this run uses %d: refused" % (tr.get("batch"), B)
                 else:
-                    kk = tr["kernels"]["k_path_v3"]
+                    kk = tr["kernels"].get("k_path_v4") or tr["kernels"]["k_path_v3"]
                     traffic = float(kk["dram_read"]) + float(kk["dram_write"])
                     dram_frame = float(tr["dram_bytes_per_frame"])
-                    note = "ncu --set full / dram__bytes of %s" % tr.get("source", "profiles/")
+                    note = "dram__bytes_read + dram__bytes_write per launch, ncu capture profiles/r02/%s" % tr.get("source", "")
             except Exception as ex:      # noqa: BLE001
                 note = "no usable capture: %r" % (ex,)
             path_ach = ALG_BYTES["kitti"] * B / (step_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": "k_path_v3 (fused down-right / down / down-left path aggregation)", "achieved": ach, "peak": peak, "peak_kind": peak_kind,
+            roof = {"bound": "hbm", "kernel": "k_path_v4 (fused down-right / down / down-left path aggregation, several columns per warp)", "achieved": ach, "peak": peak, "peak_kind": peak_kind,
                     "unit": "GB/s", "frac": ach / peak, "traffic": traffic, "traffic_note": note, "alg_bytes_per_launch": alg_bytes, "ms_per_launch": kv_ms,
                     "share_of_step": kv_ms / step_ms,
                     "path": {"alg_bytes_per_frame": ALG_BYTES["kitti"], "achieved": path_ach, "frac": path_ach / peak,
