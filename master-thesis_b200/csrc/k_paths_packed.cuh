@@ -1237,59 +1237,59 @@ __global__ void __launch_bounds__(512, 1) k_path_v4(const int16_t* __restrict__ 
         uint2 carryI;
         ldblk(inL, carry);
         carryI = *(const uint2*)(inL + dwords);
-        for (int ci = 0; ci < ncols; ci += G) {
+        // this group's column pointers, advanced by G columns per step (the group's column is clamped into the chunk only in a
+        // part-filled last step)
+        const unsigned* gC = rowC + (size_t)g * colW;
+        unsigned* gS = rowS + (size_t)g * colW;
+        for (int ci = 0; ci < ncols; ci += G, gC += G * colW, gS += G * colW) {
             const int col = ci + g;
             const bool on = col < ncols;
-            const int cc = on ? col : ncols - 1;                       // groups past the chunk's end shadow its last column (no stores)
-            unsigned* const cb = colBase0 + (size_t)cc * colWords;
+            const bool lastStep = ci + G >= ncols;
+            const int cc = min(col, ncols - 1);                        // groups past the chunk's end shadow its last column (no stores)
+            unsigned* const cb = colBase0 + cc * colWords;
             unsigned c[NWD], s[NWD];
 #pragma unroll
             for (int j = 0; j < NWD; j++) { c[j] = cN[j]; s[j] = sN[j]; }
             // ---- prefetch: the next step of this row, or the first step of the next row ----
-            {
-                const bool lastStep = ci + G >= ncols;
-                const int nc = lastStep ? min(g, ncols - 1) : min(col + G, ncols - 1);
-                const unsigned* nC = (lastStep ? rowC + nextRow : rowC) + (size_t)nc * colW;
-                const unsigned* nS = (lastStep ? rowS + nextRow : rowS) + (size_t)nc * colW;
-                if (!lastStep || moreRows) { ldg(nC, cN); ldg(nS, sN); }
+            if (!lastStep) {
+                const long long back = (long long)(col + G - min(col + G, ncols - 1)) * (long long)colW;   // 0 unless the next step is part-filled
+                ldg(gC + G * colW - back, cN); ldg(gS + G * colW - back, sN);
+            } else if (moreRows) {
+                const size_t o = (size_t)min(g, ncols - 1) * colW;
+                ldg(rowC + nextRow + o, cN); ldg(rowS + nextRow + o, sN);
             }
             // ---- sources: everything is read before any block of this step is overwritten ----
             unsigned Lp1[NWD], Lp2[NWD], Lp3[NWD];
             uint2 i1, i2, i3;
-            if (g == 0) {
-#pragma unroll
-                for (int j = 0; j < NWD; j++) Lp1[j] = carry[j];
-                i1 = carryI;
-            } else {
-                const unsigned* src1 = colBase0 + (size_t)(cc > 0 ? cc - 1 : 0) * colWords;     // old down-right block of column x-1
+            {                                                          // (no divergent branches here: every group does the same loads, group 0 then takes the carried block)
+                const unsigned* src1 = cb - (cc > 0 ? colWords : 0);   // old down-right block of column x-1
                 ldblk(src1, Lp1);
                 i1 = *(const uint2*)(src1 + dwords);
+                const bool g0 = g == 0;
+#pragma unroll
+                for (int j = 0; j < NWD; j++) Lp1[j] = g0 ? carry[j] : Lp1[j];
+                i1.x = g0 ? carryI.x : i1.x; i1.y = g0 ? carryI.y : i1.y;
             }
             ldblk(cb + blk, Lp2);
             i2 = *(const uint2*)(cb + blk + dwords);
             const unsigned* src3 = (cc + 1 < ncols) ? cb + colWords + 2 * blk : inR;
             ldblk(src3, Lp3);
             i3 = *(const uint2*)(src3 + dwords);
-            if (g == 0 && ci + G < ncols) {                            // the next step's first column reads the old down-right block of this step's last
-                const unsigned* nx = colBase0 + (size_t)(ci + G - 1) * colWords;
+            {                                                          // the next step's first column reads the old down-right block of this step's last column
+                const unsigned* nx = colBase0 + min(ci + G - 1, ncols - 1) * colWords;
                 ldblk(nx, carry);
                 carryI = *(const uint2*)(nx + dwords);
             }
             __syncwarp();                                              // all reads of the step precede its writes
             unsigned L1[NWD], L2[NWD], L3[NWD];
-            int mn1, mn2, mn3;
+            unsigned q1, q2, q3;
             const bool fast = !exact && __all_sync(0xffffffffu, (int)(i1.y | i2.y | i3.y) >= 0);
             if (fast) {
-                const unsigned q1 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp1, i1.x, c, L1, sub, D, k);
-                const unsigned q2 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp2, i2.x, c, L2, sub, D, k);
-                const unsigned q3 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp3, i3.x, c, L3, sub, D, k);
-                // lane minima of two directions side by side, reduced over the group as packed pairs
-                const unsigned z12 = group_min2<LPR>(__vmins2(__byte_perm(q1, q2, 0x5410), __byte_perm(q1, q2, 0x7632)));   // (min1 | min2 << 16)
-                const unsigned z3 = group_min2<LPR>(__vmins2(q3, __byte_perm(q3, q3, 0x1032)));                              // min3 in both halves
-                mn1 = (int)(short)(z12 & 0xffffu); mn2 = (int)z12 >> 16; mn3 = (int)z3 >> 16;
+                q1 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp1, i1.x, c, L1, sub, D, k);
+                q2 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp2, i2.x, c, L2, sub, D, k);
+                q3 = colx_fast_pk<NWD, LPR, PW, HASPAD, NN>(Lp3, i3.x, c, L3, sub, D, k);
             } else {
                 const int d1 = (int)(short)(i1.y & 0xffffu), d2 = (int)(short)(i2.y & 0xffffu), d3 = (int)(short)(i3.y & 0xffffu);
-                unsigned q1, q2, q3;
                 if (!exact) {
                     q1 = colx_general_pk<NWD, LPR, PW, false, HASPAD>(Lp1, d1, c, L1, sub, D, k);
                     q2 = colx_general_pk<NWD, LPR, PW, false, HASPAD>(Lp2, d2, c, L2, sub, D, k);
@@ -1299,11 +1299,11 @@ __global__ void __launch_bounds__(512, 1) k_path_v4(const int16_t* __restrict__ 
                     q2 = colx_general_pk<NWD, LPR, PW, true, HASPAD>(Lp2, d2, c, L2, sub, D, k);
                     q3 = colx_general_pk<NWD, LPR, PW, true, HASPAD>(Lp3, d3, c, L3, sub, D, k);
                 }
-                const unsigned z12 = group_min2<LPR>(__vmins2(__byte_perm(q1, q2, 0x5410), __byte_perm(q1, q2, 0x7632)));
-                const unsigned z3 = group_min2<LPR>(__vmins2(q3, __byte_perm(q3, q3, 0x1032)));
-                mn1 = (int)(short)(z12 & 0xffffu); mn2 = (int)z12 >> 16; mn3 = (int)z3 >> 16;
             }
-            const bool anyNeg = __any_sync(0xffffffffu, (mn1 | mn2 | mn3) < 0);
+            // lane minima of two directions side by side, reduced over the group as packed pairs
+            const unsigned z12 = group_min2<LPR>(__vmins2(__byte_perm(q1, q2, 0x5410), __byte_perm(q1, q2, 0x7632)));   // (min1 | min2 << 16)
+            const unsigned z3 = group_min2<LPR>(__vmins2(q3, __byte_perm(q3, q3, 0x1032)));                              // min3 in both halves
+            const bool anyNeg = __any_sync(0xffffffffu, (int)((z12 | z3) & 0x80008000u) != 0);
             if (fast && !anyNeg) { acc_fast<NWD>(s, L1); acc_fast<NWD>(s, L2); acc_fast<NWD>(s, L3); }
             else { acc_exact<NWD>(s, L1); acc_exact<NWD>(s, L2); acc_exact<NWD>(s, L3); }       // valid for any signs
             if (anyNeg && !exact) {                                    // a negative path cost: unsigned sums are void, stay exact from here on
@@ -1311,37 +1311,37 @@ __global__ void __launch_bounds__(512, 1) k_path_v4(const int16_t* __restrict__ 
                 if (lane == 0) atomicOr(&flags[b], 2);
             }
             // ---- stores of the finished columns ----
-            unsigned iA1, iB1, iA3, iB3;
-            path_info<NN>(mn1, P2, iA1, iB1);
-            path_info<NN>(mn3, P2, iA3, iB3);
+            // lanes 0..2 of the group derive what the next pixel on "their" path needs from this pixel's minimum
+            const int mnSel = sub == 0 ? (int)(short)(z12 & 0xffffu) : (sub == 1 ? (int)z12 >> 16 : (int)z3 >> 16);
+            unsigned iA, iB;
+            path_info<NN>(mnSel, P2, iA, iB);
             if (on) {
                 stblk(cb, L1); stblk(cb + blk, L2); stblk(cb + 2 * blk, L3);
-                if (sub == 0) *(uint2*)(cb + dwords) = make_uint2(iA1, iB1);
-                if (sub == 1) { unsigned iA2, iB2; path_info<NN>(mn2, P2, iA2, iB2); *(uint2*)(cb + blk + dwords) = make_uint2(iA2, iB2); }
-                if (sub == 2) *(uint2*)(cb + 2 * blk + dwords) = make_uint2(iA3, iB3);
+                if (sub < 3) *(uint2*)(cb + sub * blk + dwords) = make_uint2(iA, iB);
                 // the last row's edges have no consumer: not pushed (no st.async may be in flight towards a CTA that has left)
-                if (col == 0 && hasL && moreRows) {                    // my first column's down-left block -> left neighbour's right inbox
+                if (moreRows && (col == 0 || lastStep)) {
+                    if (col == 0 && hasL) {                            // my first column's down-left block -> left neighbour's right inbox
 #pragma unroll
-                    for (int q = 0; q < NP; q++) {
-                        if (PW == 4) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(pL_dst + (q * PIECEW + lw) * 4), "r"(L3[4 * q]), "r"(L3[4 * q + 1]), "r"(L3[4 * q + 2]), "r"(L3[4 * q + 3]), "r"(pL_bar) : "memory");
-                        else st_async_v2(pL_dst + (q * PIECEW + lw) * 4, L3[2 * q], L3[2 * q + 1], pL_bar);
+                        for (int q = 0; q < NP; q++) {
+                            if (PW == 4) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(pL_dst + (q * PIECEW + lw) * 4), "r"(L3[4 * q]), "r"(L3[4 * q + 1]), "r"(L3[4 * q + 2]), "r"(L3[4 * q + 3]), "r"(pL_bar) : "memory");
+                            else st_async_v2(pL_dst + (q * PIECEW + lw) * 4, L3[2 * q], L3[2 * q + 1], pL_bar);
+                        }
+                        if (sub == 2) st_async_v2(pL_dst + dwords * 4, iA, iB, pL_bar);
                     }
-                    if (sub == 2) st_async_v2(pL_dst + dwords * 4, iA3, iB3, pL_bar);
-                }
-                if (col == ncols - 1 && hasR && moreRows) {            // my last column's down-right block -> right neighbour's left inbox
+                    if (col == ncols - 1 && hasR) {                    // my last column's down-right block -> right neighbour's left inbox
 #pragma unroll
-                    for (int q = 0; q < NP; q++) {
-                        if (PW == 4) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(pR_dst + (q * PIECEW + lw) * 4), "r"(L1[4 * q]), "r"(L1[4 * q + 1]), "r"(L1[4 * q + 2]), "r"(L1[4 * q + 3]), "r"(pR_bar) : "memory");
-                        else st_async_v2(pR_dst + (q * PIECEW + lw) * 4, L1[2 * q], L1[2 * q + 1], pR_bar);
+                        for (int q = 0; q < NP; q++) {
+                            if (PW == 4) asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.b32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(pR_dst + (q * PIECEW + lw) * 4), "r"(L1[4 * q]), "r"(L1[4 * q + 1]), "r"(L1[4 * q + 2]), "r"(L1[4 * q + 3]), "r"(pR_bar) : "memory");
+                            else st_async_v2(pR_dst + (q * PIECEW + lw) * 4, L1[2 * q], L1[2 * q + 1], pR_bar);
+                        }
+                        if (sub == 0) st_async_v2(pR_dst + dwords * 4, iA, iB, pR_bar);
                     }
-                    if (sub == 0) st_async_v2(pR_dst + dwords * 4, iA1, iB1, pR_bar);
                 }
                 if (!WTA || storeS) {
-                    unsigned* Sp = rowS + (size_t)col * colW;
 #pragma unroll
                     for (int q = 0; q < NP; q++) {
-                        if (PW == 4) *(uint4*)(Sp + q * PIECEW) = make_uint4(s[4 * q], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
-                        else *(uint2*)(Sp + q * PIECEW) = make_uint2(s[2 * q], s[2 * q + 1]);
+                        if (PW == 4) *(uint4*)(gS + q * PIECEW) = make_uint4(s[4 * q], s[4 * q + 1], s[4 * q + 2], s[4 * q + 3]);
+                        else *(uint2*)(gS + q * PIECEW) = make_uint2(s[2 * q], s[2 * q + 1]);
                     }
                 }
             }
