@@ -1119,8 +1119,8 @@ __device__ __forceinline__ unsigned group_min2(unsigned v)
     return v;
 }
 
-template <int NWD, int LPR, bool UP, bool WTA, bool HASPAD, bool NN>
-__global__ void __launch_bounds__(512, 1) k_path_v4(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
+template <int NWD, int LPR, bool UP, bool WTA, bool HASPAD, bool NN, int MAXT = 512>
+__global__ void __launch_bounds__(MAXT, 1) k_path_v4(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
                                                     int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     (void)raw;

@@ -976,7 +976,7 @@ static size_t vcfg_smem(const SgbmDev& p, int CL, int NT, VState* vs)
 // proportional to the columns per CTA, and the batch runs in ceil(B / concurrent clusters) waves.  The cluster size
 // with the smallest waves x columns-per-CTA wins.  The query results are cached per context (first launch only).
 template <typename K>
-static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512, bool v4 = false)
+static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512, bool v4 = false, int v4nt = 512)
 {
     const SgbmDev& p = c->sg;
     VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.cost = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = 0;
@@ -985,8 +985,8 @@ static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512, bool v4 = fa
     const int forced = fcl ? atoi(fcl) : 0;
     for (int ni = (c->pathv_max_nt <= 256 ? 2 : (c->pathv_max_nt <= 512 ? 1 : 0)); ni < 3; ni++) {
         const int NT = nts[ni], NW = NT / 32;
-        if (NT > 512 && (p.Dp > 128 || v4)) continue;                  // wide disparity ranges (and k_path_v4) need > 64 registers per thread
-        if (v4 && NT != 512) continue;
+        if (NT > 512 && p.Dp > 128) continue;                          // wide disparity ranges need > 64 registers per thread
+        if (v4 && NT != v4nt) continue;                                // k_path_v4 is built for one CTA size
         double best = 0;
         for (int CL = 16; CL >= 1; CL--) {                              // 9..16: non-portable cluster sizes (wide disparity ranges at HD need them)
             if (forced && CL != forced) continue;
@@ -1090,10 +1090,12 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     const SgbmDev& p = c->sg;
     const int hblocks = cvr_div_up(B * p.H, 4);
     const bool packed = !c->force_generic && p.P1s >= 0;               // P1s < 0 (P1 in [32768, 65535] mod 65536): int32 kernels
-    constexpr int LPRV = DPL <= 4 ? 8 : 16, NWDV = DPL * 16 / LPRV;     // k_path_v4: lanes per column, words per lane
+    // k_path_v4: lanes per column, words per lane, threads per CTA (measured and rejected at D = 128: 16 lanes per column in
+    // 1024-thread CTAs -- 64 registers per thread spill, 90 us per frame against 61)
+    constexpr int LPRV = DPL <= 4 ? 8 : 16, NWDV = DPL * 16 / LPRV, NTV4 = 512;
     const bool useV4 = packed && c->path_v_variant == 4;
     const VCfg vc = !packed ? VCfg{ false, 1, 0, { 0, 0, 0 }, 0, 0 }
-                    : useV4 ? pick_vcfg(c, B, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN>, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN>, true)
+                    : useV4 ? pick_vcfg(c, B, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, true, NTV4)
                             : pick_vcfg(c, B, k_path_v3<DPL, false, false, HASPAD, NN, 1024>, k_path_v3<DPL, false, false, HASPAD, NN, 512>);
     int* fl = c->d_sgflags;
     // generic vertical kernel geometry: a cluster of CL CTAs per frame; fewer, larger clusters when the batch is small
@@ -1109,9 +1111,9 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
                 else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             } else if (useV4) {
-                if (!up) e = launch_cluster(k_path_v4<NWDV, LPRV, false, false, HASPAD, NN>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else if (wta) e = launch_cluster(k_path_v4<NWDV, LPRV, true, true, HASPAD, NN>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else e = launch_cluster(k_path_v4<NWDV, LPRV, true, false, HASPAD, NN>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                if (!up) e = launch_cluster(k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v4<NWDV, LPRV, true, true, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                else e = launch_cluster(k_path_v4<NWDV, LPRV, true, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             } else if (vc.NT > 512) {
                 if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
@@ -1307,8 +1309,8 @@ static int suggest_batch(cvr_ctx* c, int around)
     int bestB = around < c->maxB ? around : c->maxB;
     double bestCost = -1;
     for (int B = lo; B <= hi; B++) {
-        constexpr int LPRV = DPL <= 4 ? 8 : 16, NWDV = DPL * 16 / LPRV;
-        const VCfg vc = c->path_v_variant == 4 ? pick_vcfg(c, B, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN>, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN>, true)
+        constexpr int LPRV = DPL <= 4 ? 8 : 16, NWDV = DPL * 16 / LPRV, NTV4 = 512;
+        const VCfg vc = c->path_v_variant == 4 ? pick_vcfg(c, B, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, true, NTV4)
                                                : pick_vcfg(c, B, k_path_v3<DPL, false, false, HASPAD, NN, 1024>, k_path_v3<DPL, false, false, HASPAD, NN, 512>);
         if (!vc.ok) return bestB;
         const double perFrame = vc.cost / B;
