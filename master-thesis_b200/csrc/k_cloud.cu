@@ -280,6 +280,8 @@ __global__ void k_fill_int(int* p, int n, int v) { int i = blockIdx.x * blockDim
 
 // Surviving pixels in row-major order (the reference's push_back order) by the single-pass ordered selection of
 // cvr_scan.cuh; the kernel also accumulates the cloud's bounding box for the voxel grid that follows.
+#define CLOUD_ITEMS 8                                              // pixels per thread: a chunk of the cloud selection is 2048 pixels
+#define CLOUD_CHUNK (CVR_SEL_THREADS * CLOUD_ITEMS)
 template <int MODE, bool FUSED>
 __global__ void __launch_bounds__(CVR_SEL_THREADS) k_cloud_select(CloudArgs a, int* sel, size_t selStride, cvr_point* __restrict__ out, size_t outStride,
                                                                   int* __restrict__ nout, VoxBox* box, double factor)
@@ -288,7 +290,7 @@ __global__ void __launch_bounds__(CVR_SEL_THREADS) k_cloud_select(CloudArgs a, i
     __shared__ int sh;
     __shared__ float sfa, sfb;
     __shared__ int sthr;
-    const int b = blockIdx.y, N = a.W * a.H, nch = (N + CVR_SEL_BLOCK - 1) / CVR_SEL_BLOCK;
+    const int b = blockIdx.y, N = a.W * a.H, nch = (N + CLOUD_CHUNK - 1) / CLOUD_CHUNK;
     if (FUSED && threadIdx.x == 0) {
         const PruneStats s = a.pstats[b];
         float fa, fb;
@@ -305,11 +307,11 @@ __global__ void __launch_bounds__(CVR_SEL_THREADS) k_cloud_select(CloudArgs a, i
     for (;;) {
         const int chunk = sel_next_chunk(ticket, &sh);
         if (chunk >= nch) break;
-        const int i0 = chunk * CVR_SEL_BLOCK + threadIdx.x * CVR_SEL_ITEMS;
-        cvr_point pt[CVR_SEL_ITEMS];
-        int f[CVR_SEL_ITEMS], cnt = 0;
+        const int i0 = chunk * CLOUD_CHUNK + threadIdx.x * CLOUD_ITEMS;
+        cvr_point pt[CLOUD_ITEMS];
+        int f[CLOUD_ITEMS], cnt = 0;
 #pragma unroll
-        for (int k = 0; k < CVR_SEL_ITEMS; k++) {
+        for (int k = 0; k < CLOUD_ITEMS; k++) {
             f[k] = (i0 + k < N) ? (int)make_point<MODE, FUSED>(a, b, i0 + k, pt[k], fa, fb, ithr) : 0;
             cnt += f[k];
         }
@@ -318,7 +320,7 @@ __global__ void __launch_bounds__(CVR_SEL_THREADS) k_cloud_select(CloudArgs a, i
         const int base = sel_chain_prefix(status, chunk, tot, &sh);
         cvr_point* o = out + (size_t)b * outStride + base + e;
 #pragma unroll
-        for (int k = 0; k < CVR_SEL_ITEMS; k++)
+        for (int k = 0; k < CLOUD_ITEMS; k++)
             if (f[k]) {
                 *(uint4*)o = *(const uint4*)&pt[k]; o++;
                 const unsigned ox = f2ord(pt[k].x), oy = f2ord(pt[k].y), oz = f2ord(pt[k].z);
@@ -348,7 +350,7 @@ int cvr_launch_cloud(cvr_ctx* c, int B, int mode, const int16_t* disp16, const f
     int* sel = c->d_sel;                                               // selection 0 of the chain
     if (!fused) { const int rc0 = cvr_launch_chain_init(c, B, false, true, false); if (rc0) return rc0; }   // stand-alone call: nobody prepared the box
     CVR_CUDA(c, cudaMemsetAsync(sel, 0, (size_t)B * selStride * sizeof(int), c->stream));
-    const int nch = cvr_div_up(N, CVR_SEL_BLOCK);
+    const int nch = cvr_div_up(N, CLOUD_CHUNK);
     const dim3 g(cvr_frame_blocks(c, B, (size_t)nch, 1, 8), B);
     const double factor = c->cl.sigma_factor;
     if (mode == CVR_CLOUD_REPROJECT) {
