@@ -50,6 +50,38 @@ void cvr_stage_mark(cvr_ctx* c, const char* name)
     cudaEventRecord(tv[used].ev, c->stream);
     used++;
 }
+// ---- tail stream of the pipelined batches (see cvr_ctx::tail_stream) ----
+int cvr_tail_split(cvr_ctx* c)
+{
+    if (!c->split_tail || c->path_stream) return CVR_OK;
+    CVR_CUDA(c, cudaEventRecord(c->evPath, c->stream));
+    CVR_CUDA(c, cudaStreamWaitEvent(c->tail_stream, c->evPath, 0));
+    c->path_stream = c->stream; c->stream = c->tail_stream;           // every launcher enqueues on c->stream
+    return CVR_OK;
+}
+int cvr_tail_aux_consumed(cvr_ctx* c)
+{
+    if (!c->split_tail || !c->path_stream) return CVR_OK;
+    CVR_CUDA(c, cudaEventRecord(c->evAuxFree, c->stream));
+    c->aux_pending = true;
+    return CVR_OK;
+}
+int cvr_path_wait_aux(cvr_ctx* c)
+{
+    if (!c->aux_pending) return CVR_OK;
+    CVR_CUDA(c, cudaStreamWaitEvent(c->stream, c->evAuxFree, 0));
+    c->aux_pending = false;
+    return CVR_OK;
+}
+// Entry points other than cvr_submit_batch work on c->stream alone: whatever a pipelined batch still has on the tail stream
+// comes first (they share the workspace).
+int cvr_join_tail(cvr_ctx* c)
+{
+    if (!c->tail_dirty) return CVR_OK;
+    CVR_CUDA(c, cudaStreamWaitEvent(c->stream, c->evTailLast, 0));
+    c->tail_dirty = false; c->aux_pending = false;
+    return CVR_OK;
+}
 static void timers_begin(cvr_ctx* c, int set) { c->tset = set; c->timers_used[set] = 0; cvr_stage_mark(c, "begin"); }
 static void timers_end(cvr_ctx* c, int set)                           // after the events of that set have completed
 {
@@ -180,6 +212,10 @@ static void free_all(cvr_ctx* c)
             cudaEventDestroy(sl.evH2D); cudaEventDestroy(sl.evDone);
         }
         cudaStreamDestroy(c->copy_stream); cudaStreamDestroy(c->d2h_stream);
+        if (c->tail_stream) cudaStreamDestroy(c->tail_stream);
+        if (c->evPath) cudaEventDestroy(c->evPath);
+        if (c->evAuxFree) cudaEventDestroy(c->evAuxFree);
+        if (c->evTailLast) cudaEventDestroy(c->evTailLast);
     }
     for (auto& tv : c->timers) for (auto& t : tv) cudaEventDestroy(t.ev);
     if (c->stream) cudaStreamDestroy(c->stream);
@@ -203,6 +239,8 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     c->prm = *p; c->device = device; c->maxB = p->max_batch; c->sm_count = prop.multiProcessorCount;
     c->launches = 0; c->profiling = false; c->timers_used[0] = c->timers_used[1] = c->timers_used[2] = 0; c->tset = 0; c->stream = nullptr; c->h_counts = nullptr; c->h_meta0 = nullptr; c->d_meta0 = nullptr; c->lp_valid = false; c->d_icp = nullptr; c->h_icp = nullptr; c->png_blob = c->png_z = c->png_raw = c->png_tab = c->png_out = nullptr; c->png_blob_cap = c->png_z_cap = c->png_raw_cap = c->png_tab_cap = c->png_out_cap = 0; cvr_comm_reset(c);
     c->pipe_ready = false; c->copy_stream = nullptr; c->d2h_stream = nullptr; c->n_submit = c->n_wait = 0;
+    c->tail_stream = nullptr; c->path_stream = nullptr; c->evPath = c->evAuxFree = c->evTailLast = nullptr; c->split_tail = c->aux_pending = c->tail_dirty = false;
+    { const char* e_ = getenv("CVR_TAIL_STREAM"); c->tail_mode = e_ ? atoi(e_) : 0; }
     memset(c->slot, 0, sizeof(c->slot));
     fill_dev_params(c);
     c->smem_optin = (int)prop.sharedMemPerBlockOptin;
@@ -267,7 +305,7 @@ extern "C" int cvr_destroy(cvr_ctx* c)
     if (!c) return CVR_OK;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    if (c->pipe_ready) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->d2h_stream); }
+    if (c->pipe_ready) { cudaStreamSynchronize(c->copy_stream); cudaStreamSynchronize(c->d2h_stream); if (c->tail_stream) cudaStreamSynchronize(c->tail_stream); }
     free_all(c);
     delete c;
     return CVR_OK;
@@ -293,6 +331,7 @@ extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const u
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sl >= (size_t)W * ch && sr >= (size_t)W * ch && sd >= (size_t)W * 2, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * ch, left, sl, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], (size_t)W * ch, right, sr, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
@@ -329,6 +368,7 @@ extern "C" int cvr_set_rectification(cvr_ctx* c, const double* K1, const double*
     REQUIRE(c, nD1 >= 0 && nD2 >= 0 && (nD1 == 0 || D1) && (nD2 == 0 || D2), "bad distortion vector");
     if (nD1 > 12 || nD2 > 12) { c->err = "distortion vectors with tilt terms (more than 12 coefficients) are not supported"; return CVR_ERR_UNSUPPORTED; }
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     int rc = rect_alloc(c);
     if (rc) return rc;
     c->rect_ready = false;
@@ -349,6 +389,7 @@ extern "C" int cvr_get_rectification_maps(cvr_ctx* c, int cam, int16_t* map1, ui
     REQUIRE(c, cam == 0 || cam == 1, "camera must be 0 or 1");
     const size_t HW = (size_t)c->prm.width * c->prm.height;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     if (map1) CVR_CUDA(c, cudaMemcpy(map1, c->d_rmap1[cam], HW * 4, cudaMemcpyDeviceToHost));
     if (map2) CVR_CUDA(c, cudaMemcpy(map2, c->d_rmap2[cam], HW * 2, cudaMemcpyDeviceToHost));
     return CVR_OK;
@@ -366,6 +407,7 @@ extern "C" int cvr_rectify(cvr_ctx* c, int ch, const uint8_t* left, size_t sl, c
     const size_t rowBytes = (size_t)W * ch;
     REQUIRE(c, sl >= rowBytes && sr >= rowBytes && sol >= rowBytes && sor_ >= rowBytes, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], rowBytes, left, sl, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], rowBytes, right, sr, rowBytes, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_remap(c, 1, ch, c->d_in[0], rowBytes, rowBytes * H, c->d_in[1], rowBytes, rowBytes * H, c->d_rect[0], c->d_rect[1], rowBytes, rowBytes * H);
@@ -386,6 +428,7 @@ extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, i
         if (!dst) return CVR_OK;
         REQUIRE(c, bytes >= need && (which == 5 || bytes <= (size_t)c->maxN * 4), "debug buffer size");
         CVR_CUDA(c, cudaSetDevice(c->device));
+        { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
         CVR_CUDA(c, cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
         return CVR_OK;
     }
@@ -410,6 +453,7 @@ extern "C" int cvr_debug_fetch(cvr_ctx* c, int which, void* dst, size_t bytes, i
     if (!dst) return CVR_OK;
     REQUIRE(c, bytes >= need, "debug buffer too small");
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     CVR_CUDA(c, cudaMemcpy(dst, src, need, cudaMemcpyDeviceToHost));
     return CVR_OK;
 }
@@ -422,6 +466,7 @@ extern "C" int cvr_prune(cvr_ctx* c, int16_t* disp, size_t sd, float* dispf, uin
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sd >= (size_t)W * 2, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_med, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_prune(c, 1, c->d_med);
@@ -454,6 +499,7 @@ extern "C" int cvr_reproject_cloud(cvr_ctx* c, const int16_t* disp, size_t sd, c
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sd >= (size_t)W * 2 && sb >= (size_t)W * 3, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_pruned, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
@@ -473,6 +519,7 @@ extern "C" int cvr_triangulate(cvr_ctx* c, const float* dispf, size_t sd, const 
     const int W = c->sg.W, H = c->sg.H;
     REQUIRE(c, sd >= (size_t)W * 4 && sb >= (size_t)W * 3 && (!mask || sm >= (size_t)W), "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_dispf, (size_t)W * 4, dispf, sd, (size_t)W * 4, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
@@ -493,6 +540,7 @@ extern "C" int cvr_voxel_grid(cvr_ctx* c, const cvr_point* in, int n, cvr_point*
     if (passthrough) *passthrough = 0;
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_cloud, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
@@ -518,6 +566,7 @@ extern "C" int cvr_sor(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, i
     if (kept_out) *kept_out = 0;
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
@@ -539,6 +588,7 @@ extern "C" int cvr_filter_cloud(cvr_ctx* c, int mem, const cvr_point* in, int n,
     if (n_out) *n_out = 0;
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     const cudaMemcpyKind kin = mem == CVR_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
     const cudaMemcpyKind kout = mem == CVR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
@@ -574,6 +624,7 @@ extern "C" int cvr_radius_outlier_removal(cvr_ctx* c, const cvr_point* in, int n
     if (kept_out) *kept_out = 0;
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
@@ -592,6 +643,7 @@ extern "C" int cvr_transform_cloud(cvr_ctx* c, const cvr_point* in, int n, const
     if (n > c->maxN) { c->err = "cloud larger than the context's point capacity (cvr_params.max_points)"; return CVR_ERR_CAPACITY; }
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_transform(c, c->d_vox, c->d_sorout, n, T);
     if (rc) return rc;
@@ -805,12 +857,16 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     const int stages = io->stages ? io->stages : 15;
     const bool host = io->mem == CVR_MEM_HOST;
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     c->lp_valid = false;
     timers_begin(c, 0);
     const uint8_t *dl, *dr; size_t lstep, lfs, rstep, rfs;
     if (host) {
         const bool dense = io->left_frame_stride == io->left_step * (size_t)H && io->right_frame_stride == io->right_step * (size_t)H;
-        if (dense) {                                                   // frames back to back: one 2-D copy per camera for the whole batch
+        if (dense && io->left_step == rowBytes && io->right_step == rowBytes) {   // no row padding either: plain copies run at the full link rate
+            CVR_CUDA(c, cudaMemcpyAsync(c->d_in[0], io->left, rowBytes * H * B, cudaMemcpyHostToDevice, c->stream));
+            CVR_CUDA(c, cudaMemcpyAsync(c->d_in[1], io->right, rowBytes * H * B, cudaMemcpyHostToDevice, c->stream));
+        } else if (dense) {                                            // frames back to back: one 2-D copy per camera for the whole batch
             CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], rowBytes, io->left, io->left_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->stream));
             CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], rowBytes, io->right, io->right_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->stream));
         } else {
@@ -861,6 +917,14 @@ static int pipe_init(cvr_ctx* c)
     const size_t B = (size_t)c->maxB, HW = (size_t)c->sg.W * c->sg.H, N = (size_t)c->maxN;
     CVR_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     CVR_CUDA(c, cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
+    {
+        int prLow = 0, prHigh = 0;                                     // numerically lowest = highest priority
+        CVR_CUDA(c, cudaDeviceGetStreamPriorityRange(&prLow, &prHigh));
+        CVR_CUDA(c, cudaStreamCreateWithPriority(&c->tail_stream, cudaStreamNonBlocking, prHigh));
+        CVR_CUDA(c, cudaEventCreateWithFlags(&c->evPath, cudaEventDisableTiming));
+        CVR_CUDA(c, cudaEventCreateWithFlags(&c->evAuxFree, cudaEventDisableTiming));
+        CVR_CUDA(c, cudaEventCreateWithFlags(&c->evTailLast, cudaEventDisableTiming));
+    }
     for (int s = 0; s < 2; s++) {
         PipeSlot& sl = c->slot[s];
         CVR_CUDA(c, dalloc(&sl.d_in[0], B * HW * 4)); CVR_CUDA(c, dalloc(&sl.d_in[1], B * HW * 4));
@@ -875,9 +939,11 @@ static int pipe_init(cvr_ctx* c)
 }
 
 // ---- pipelined path: two batches in flight.  The upload of batch i+1 (copy stream) overlaps the kernels of batch i
-// (compute stream) and the download of batch i-1 (d2h stream).  Measured and rejected: running the filter stages of batch
-// i on a third stream beside the matcher of batch i+1 -- the matcher kernels already saturate HBM, both halves only slow
-// each other down (+1 % device-resident, -6 % end to end).
+// (compute stream) and the download of batch i-1 (d2h stream).  CVR_TAIL_STREAM=1 (off by default) issues everything after the
+// path kernels of a batch on a high-priority stream of its own, beside the matcher of the next batch.  Measured on B200 (KITTI,
+// batch 110): the tail then runs beside k_pix_hsum4, which slows down by what the tail saves (+0.6 % device-resident, +1 % end
+// to end); started later, beside k_vsum / k_path_h2 / k_path_v4, it costs more than it saves (-1 .. -11 %): every matcher
+// kernel already keeps the SMs or the HBM busy, the tail is not free to hide.
 extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
 {
     if (!c) return CVR_ERR_INVALID_ARG;
@@ -899,7 +965,10 @@ extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
         // upload on the copy stream, after the kernels of the batch that last used this slot's staging buffers
         if (sl.used) CVR_CUDA(c, cudaStreamWaitEvent(c->copy_stream, sl.evDone, 0));
         const bool dense = io->left_frame_stride == io->left_step * (size_t)H && io->right_frame_stride == io->right_step * (size_t)H;
-        if (dense) {                                                   // frames back to back: one 2-D copy per camera for the whole batch
+        if (dense && io->left_step == rowBytes && io->right_step == rowBytes) {   // no row padding either: plain copies run at the full link rate
+            CVR_CUDA(c, cudaMemcpyAsync(sl.d_in[0], io->left, rowBytes * H * B, cudaMemcpyHostToDevice, c->copy_stream));
+            CVR_CUDA(c, cudaMemcpyAsync(sl.d_in[1], io->right, rowBytes * H * B, cudaMemcpyHostToDevice, c->copy_stream));
+        } else if (dense) {                                            // frames back to back: one 2-D copy per camera for the whole batch
             CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[0], rowBytes, io->left, io->left_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->copy_stream));
             CVR_CUDA(c, cudaMemcpy2DAsync(sl.d_in[1], rowBytes, io->right, io->right_step, rowBytes, (size_t)H * B, cudaMemcpyHostToDevice, c->copy_stream));
         } else {
@@ -916,6 +985,13 @@ extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     }
     timers_begin(c, tset);                                             // stage timers of this slot (read back by cvr_wait_batch)
     const cvr_point* fin = nullptr; const int* fcnt = nullptr;
+    // From the matcher's hand-over point (cvr_tail_split) on, this batch is enqueued on the tail stream; c->stream is put back
+    // when this function returns.  Not with rectification: the tail reads the rectified image the next batch's matcher rewrites.
+    struct TailScope {
+        cvr_ctx* c;
+        ~TailScope() { if (c->path_stream) { c->stream = c->path_stream; c->path_stream = nullptr; } c->split_tail = false; }
+    } tailScope{c};
+    c->split_tail = c->tail_mode != 0 && !c->prm.requires_rectification && c->prm.block_matcher == CVR_MATCHER_SGBM;
     rc = enqueue_chain(c, B, stages, dl, lstep, lfs, dr, rstep, rfs, ch, &fin, &fcnt);
     if (rc) return rc;
     sl.hasCloud = fin != nullptr;
@@ -938,6 +1014,7 @@ extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     }
     cvr_stage_mark(c, "out");
     CVR_CUDA(c, cudaEventRecord(sl.evDone, c->stream));
+    if (c->path_stream) { CVR_CUDA(c, cudaEventRecord(c->evTailLast, c->stream)); c->tail_dirty = true; }
     c->tset = 0;
     sl.io = *io; sl.nframes = B; sl.busy = true; sl.used = true;
     c->n_submit++;

@@ -184,6 +184,14 @@ struct cvr_ctx {
     PipeSlot slot[2];
     bool pipe_ready;
     cudaStream_t copy_stream, d2h_stream;
+    // pipelined batches (cvr_submit_batch), optional: everything after the path kernels of a batch ("tail": LR check .. pack) is
+    // issued on tail_stream (high priority), so that the tail kernels of batch i run beside the matcher of batch i+1
+    cudaStream_t tail_stream; cudaStream_t path_stream;   // path_stream: c->stream while a tail is being enqueued on tail_stream
+    cudaEvent_t evPath, evAuxFree, evTailLast;
+    bool split_tail;         // set by cvr_submit_batch around its enqueue
+    bool aux_pending;        // evAuxFree is recorded: the next batch's path kernels wait for it before they overwrite d_aux
+    bool tail_dirty;         // work is (or may be) outstanding on tail_stream: other entry points make c->stream wait for evTailLast
+    int tail_mode;           // CVR_TAIL_STREAM: 1 = on, 0 = off (default; see cvr_submit_batch)
     long long n_submit, n_wait;
     int* d_meta0; int* h_meta0;   // as PipeSlot::d_meta / h_meta, for the synchronous cvr_process_batch
     // the packed payload of the batch completed last (cvr_process_batch / cvr_wait_batch): what cvr_gather_clouds sends
@@ -274,6 +282,10 @@ int cvr_launch_transform(cvr_ctx* c, const cvr_point* in, cvr_point* out, int n,
 // k_sor.cu: bounding box (unless haveBox), grid (radius > 0: cell = radius, else ~2 points per cell), points sorted by cell into d_spts
 int cvr_build_point_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox, float radius, SorGrid** gridOut, int** cellstartOut);
 void cvr_stage_mark(cvr_ctx* c, const char* name);
+int cvr_join_tail(cvr_ctx* c);         // entry points that work on c->stream alone: outstanding tail-stream work comes first
+int cvr_tail_split(cvr_ctx* c);        // matcher launchers: the path kernels of this batch are enqueued, the tail follows
+int cvr_tail_aux_consumed(cvr_ctx* c); // ... the tail no longer reads the WTA records (d_aux)
+int cvr_path_wait_aux(cvr_ctx* c);     // ... about to enqueue kernels that overwrite d_aux
 // message slot read by cvr_last_error(NULL): used by entry points that have no context
 void cvr_set_thread_error(const char* msg);
 // gather.cu

@@ -207,6 +207,7 @@ extern "C" int cvr_icp_align(cvr_ctx* c, int mem, const cvr_point* source, int n
     if (ns > c->maxN || nt > c->maxN) { c->err = "cloud larger than the context's point capacity (cvr_params.max_points)"; return CVR_ERR_CAPACITY; }
     if (!(prm->max_correspondence_distance > 0.0) || prm->max_iterations < 1) { c->err = "cvr_icp_align: bad parameters"; return CVR_ERR_INVALID_ARG; }
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     if (!c->d_icp) CVR_CUDA(c, cudaMalloc((void**)&c->d_icp, sizeof(double) * ICP_NSUM * (ICP_MAX_BLOCKS + 1)));
     if (!c->h_icp) CVR_CUDA(c, cudaHostAlloc((void**)&c->h_icp, sizeof(double) * ICP_NSUM, cudaHostAllocDefault));
     const cudaMemcpyKind kin = mem == CVR_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;

@@ -396,6 +396,7 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
         zTotal += im.zLen;
     }
     CVR_CUDA(c, cudaSetDevice(c->device));
+    { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     const long long rawStride = ((long long)H * ((long long)W * 4 + 1) + 15) & ~15LL;     // room for RGBA scanlines + filter bytes
     const size_t needBlob = (size_t)blobLen + 16, needZ = (size_t)zTotal + 16, needRaw = (size_t)rawStride * n, needOut = (size_t)W * 3 * H * n;
     auto grow = [&](uint8_t** p, size_t* cap, size_t need) -> int {

@@ -1268,7 +1268,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         LAUNCH_CHECK(c);
         cvr_stage_mark(c, "vsum");
     }
-    int rc;
+    int rc = cvr_path_wait_aux(c);                                     // the previous pipelined batch's LR check has read d_aux
+    if (rc) return rc;
     const bool nn = !c->force_no_nn && p.P2s >= 0 && p.P1s >= p.P2s;
     switch (p.Dp / 32) {
         // NN: 0 <= (short)P2 <= (short)P1 -- the neighbour terms of the path update can never win (see col_fast); this is the
@@ -1283,6 +1284,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
         default: c->err = "unsupported padded disparity count"; return CVR_ERR_UNSUPPORTED;
     }
     if (rc) return rc;
+    rc = cvr_tail_split(c);                                            // pipelined batches: the rest goes to the tail stream
+    if (rc) return rc;
     const size_t lrSmem = (size_t)p.W * 2 * sizeof(int);              // validate() keeps this within the opt-in limit (width <= 16384)
     if (lrSmem > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_lrcheck, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lrSmem));
     k_lrcheck<<<dim3(p.H, B), 256, lrSmem, c->stream>>>(c->d_raw, c->d_aux, c->d_disp, p, c->keep_S ? 1 : 0);
@@ -1290,6 +1293,8 @@ int cvr_launch_sgbm(cvr_ctx* c, int B)
     if ((p.W & 1) == 0) k_median3_x2<<<dim3(cvr_div_up(p.W, 256), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
     else k_median3<<<dim3(cvr_div_up(p.W, 128), p.H, B), 128, 0, c->stream>>>(c->d_disp, c->d_med, p.W, p.H);
     LAUNCH_CHECK(c);
+    rc = cvr_tail_aux_consumed(c);
+    if (rc) return rc;
     cvr_stage_mark(c, "lr_median");
     if (c->prm.sgbm.speckle_window_size > 0) {
         rc = cvr_launch_speckle(c, B, p.INVALID, c->prm.sgbm.speckle_window_size, CVR_DISP_SCALE * c->prm.sgbm.speckle_range);

@@ -170,3 +170,39 @@ def test_gather_two_ranks_nccl():
                         "--master-port", "29517", os.path.join(ROOT, "tests", "gpu_gather_ranks.py")], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert "gather ok" in r.stdout
+
+
+def test_tail_stream_option_gives_the_same_clouds(cvr, oracle, monkeypatch):
+    """CVR_TAIL_STREAM=1: the stages after the path kernels run on a second stream beside the next batch's matcher.  Same
+    results as the single-stream order, batch after batch, also when a synchronous call is made while batches are in flight."""
+    L0, R0 = _batch(oracle, 600)
+    L1, R1 = _batch(oracle, 610)
+    ref = cvr.Reconstruct3D(W, H, config=_cfg(), max_batch=B, voxel_leaf=0.05)
+    want = [ref.ProcessFrames(L0, R0)[1], ref.ProcessFrames(L1, R1)[1]]
+    want_disp = ref.GenerateDisparityMap(L0[0], R0[0])
+    ref.close()
+    monkeypatch.setenv("CVR_TAIL_STREAM", "1")
+    rec = cvr.Reconstruct3D(W, H, config=_cfg(), max_batch=B, voxel_leaf=0.05)
+    monkeypatch.delenv("CVR_TAIL_STREAM")
+    cap = W * H
+    bufs = [(np.zeros((B, cap), cvr.POINT_DTYPE), np.zeros(B, np.int32)) for _ in range(2)]
+    ios = []
+    for k, (L, R) in enumerate(((L0, R0), (L1, R1))):
+        io = _io(cvr, cvr.MEM_HOST, L, R)
+        io.cloud, io.cloud_capacity, io.cloud_count = bufs[k][0].ctypes.data, cap, bufs[k][1].ctypes.data
+        ios.append(io)
+    rec.submit_batch_raw(ios[0], B)
+    for i in range(1, 7):                                           # two batches in flight, alternating inputs
+        rec.submit_batch_raw(ios[i & 1], B)
+        rec.wait_batch()
+        k = (i - 1) & 1
+        for f in range(B):
+            assert bufs[k][1][f] == len(want[k][f]) and np.array_equal(bufs[k][0][f, :bufs[k][1][f]], want[k][f]), (i, f)
+        bufs[k][0][:] = 0; bufs[k][1][:] = 0
+    # a synchronous entry point while a batch is still in flight: ordered after it, and the batch is unharmed
+    d = rec.GenerateDisparityMap(L0[0], R0[0])
+    assert np.array_equal(d, want_disp)
+    rec.wait_batch()
+    for f in range(B):
+        assert bufs[0][1][f] == len(want[0][f]) and np.array_equal(bufs[0][0][f, :bufs[0][1][f]], want[0][f])
+    rec.close()
