@@ -309,6 +309,12 @@ int cvr_prune_noalloc(const int16_t* d_disp, int width, int height, double sigma
 /* Expands 16-byte points to pcl::PointXYZRGB (32 B: x,y,z,1.0f, b,g,r,a, 12 B pad).  Host side. */
 void cvr_points_to_pcl(const cvr_point* in, int n, void* pcl_points_32B);
 
+/* Replaces: pcl::io::savePCDFileBinary(path, cloud) as the reference dumps its clouds (ReconstructionServer.cpp:165,
+ * MappingSystem.cpp:61, 84; test/reconstruct_test_kitti_rectified.cpp:77): a PCD v0.7 file, DATA binary, FIELDS x y z rgb
+ * (4 x 4 bytes per point, rgb = the bytes b, g, r, a read as one 32-bit word -- PCL's packed colour), unorganised
+ * (WIDTH n, HEIGHT 1).  Host memory in, host side only; pcl::io::loadPCDFile / pcl_viewer / CloudCompare read it. */
+int cvr_save_pcd(const char* path, const cvr_point* points, int n);
+
 /* Test/inspection hooks (no reference counterpart): copy an intermediate of the most recent
  * cvr_disparity call to host.  which: 0 = C volume, 1 = S volume (both int16 [H][W1][Dp]),
  * 2 = raw disparity before median/speckle (int16 [H][W]), 3 = after the LR check.  *dp receives the padded D pitch.

@@ -31,7 +31,7 @@ POINT_DTYPE = np.dtype([("x", "<f4"), ("y", "<f4"), ("z", "<f4"), ("b", "u1"), (
 # every symbol include/cvrecon_b200.h declares
 EXPORTS = [
     "cvr_default_params", "cvr_create", "cvr_destroy", "cvr_last_error", "cvr_version", "cvr_disparity", "cvr_prune",
-    "cvr_reproject_cloud", "cvr_triangulate", "cvr_voxel_grid", "cvr_sor", "cvr_process_batch", "cvr_points_to_pcl",
+    "cvr_reproject_cloud", "cvr_triangulate", "cvr_voxel_grid", "cvr_sor", "cvr_process_batch", "cvr_points_to_pcl", "cvr_save_pcd",
     "cvr_debug_fetch", "cvr_launch_count", "cvr_last_timings", "cvr_set_profiling", "cvr_prune_noalloc",
     "cvr_submit_batch", "cvr_wait_batch", "cvr_radius_outlier_removal", "cvr_transform_cloud",
     "cvr_set_rectification", "cvr_rectify", "cvr_get_rectification_maps", "cvr_suggest_batch",
@@ -136,6 +136,8 @@ def load_library():
     lib.cvr_set_profiling.argtypes = [C.c_void_p, C.c_int]
     lib.cvr_points_to_pcl.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
     lib.cvr_points_to_pcl.restype = None
+    lib.cvr_save_pcd.argtypes = [C.c_char_p, C.c_void_p, C.c_int]
+    lib.cvr_save_pcd.restype = C.c_int
     lib.cvr_prune_noalloc.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.cvr_filter_cloud.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.POINTER(C.c_int)]
     lib.cvr_icp_default_params.argtypes = [C.POINTER(IcpParams)]
@@ -541,6 +543,14 @@ class Reconstruct3D:
         self.gather_clouds_raw(root, MEM_HOST, _ptr(out), cap, _ptr(foff), len(foff), _ptr(fr))
         nf = int(fr.sum())
         return out[:foff[nf]].copy(), foff[:nf + 1].copy(), fr
+
+
+def save_pcd(path, points):
+    """pcl::io::savePCDFileBinary of a cloud (ReconstructionServer.cpp:165)."""
+    pts = np.ascontiguousarray(points, POINT_DTYPE)
+    rc = load_library().cvr_save_pcd(os.fsencode(path), _ptr(pts), len(pts))
+    if rc != 0:
+        raise CvrError(rc, load_library().cvr_last_error(None).decode())
 
 
 def points_to_pcl(points):

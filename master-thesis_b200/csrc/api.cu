@@ -3,8 +3,10 @@
 // cvr_create fails.
 #include "cvr_internal.cuh"
 #include <string.h>
+#include <stdio.h>
 #include <stdlib.h>
 #include <new>
+#include <nvtx3/nvToolsExt.h>   // header-only; a no-op unless a profiler injects its library
 
 static const char* kVersion = "cvrecon_b200 0.1 (sm_100a)";
 static thread_local std::string g_create_err;
@@ -48,6 +50,7 @@ void cvr_stage_mark(cvr_ctx* c, const char* name)
     }
     tv[used].name = name;
     cudaEventRecord(tv[used].ev, c->stream);
+    nvtxMarkA(name);                                                   // the end of the stage's enqueue, for profiler timelines
     used++;
 }
 // ---- tail stream of the pipelined batches (see cvr_ctx::tail_stream) ----
@@ -1061,6 +1064,20 @@ extern "C" int cvr_wait_batch(cvr_ctx* c)
     sl.busy = false;                                                   // also on errors: a failed batch must not wedge the pipeline
     c->n_wait++;
     return rc;
+}
+
+extern "C" int cvr_save_pcd(const char* path, const cvr_point* pts, int n)
+{
+    if (!path || n < 0 || (n > 0 && !pts)) { g_create_err = "cvr_save_pcd: bad arguments"; return CVR_ERR_INVALID_ARG; }
+    FILE* f = fopen(path, "wb");
+    if (!f) { g_create_err = std::string("cvr_save_pcd: cannot open ") + path; return CVR_ERR_INVALID_ARG; }
+    // the header PCL's PCDWriter emits for pcl::PointXYZRGB (the 16 padding bytes of the in-memory point are not stored)
+    fprintf(f, "# .PCD v0.7 - Point Cloud Data file format\nVERSION 0.7\nFIELDS x y z rgb\nSIZE 4 4 4 4\nTYPE F F F F\nCOUNT 1 1 1 1\n"
+               "WIDTH %d\nHEIGHT 1\nVIEWPOINT 0 0 0 1 0 0 0\nPOINTS %d\nDATA binary\n", n, n);
+    const size_t w = n ? fwrite(pts, sizeof(cvr_point), (size_t)n, f) : 0;
+    const bool ok = w == (size_t)n && fclose(f) == 0;
+    if (!ok) { g_create_err = std::string("cvr_save_pcd: short write to ") + path; return CVR_ERR_INVALID_ARG; }
+    return CVR_OK;
 }
 
 extern "C" void cvr_points_to_pcl(const cvr_point* in, int n, void* pcl32)

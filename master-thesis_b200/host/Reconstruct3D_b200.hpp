@@ -238,6 +238,12 @@ public:
     // One process per GPU: every rank joins the communicator once (the 128-byte id comes from rank 0's NewCommId by whatever
     // channel the host has), then GatherMapBlocks after each batch brings all ranks' map blocks to the mapping rank
     // (MappingSystem.cpp:344-345: AddFrame -> InsertBlock) -- a collective call; only the root's return value is filled.
+    // pcl::io::savePCDFileBinary(path, cloud) (ReconstructionServer.cpp:165, MappingSystem.cpp:61, 84)
+    static void SavePCD(const std::string& path, const std::vector<cvr_point>& cloud)
+    {
+        if (cvr_save_pcd(path.c_str(), cloud.data(), static_cast<int>(cloud.size())) != CVR_OK)
+            throw std::runtime_error(std::string("cvrecon_b200: ") + cvr_last_error(nullptr));
+    }
     static std::vector<uint8_t> NewCommId()
     {
         std::vector<uint8_t> id(CVR_COMM_ID_BYTES);

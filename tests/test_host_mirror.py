@@ -62,6 +62,33 @@ def test_points_to_pcl_layout(cvr):
     assert (raw[:, 20:] == 0).all()
 
 
+def test_save_pcd_is_a_binary_pcd_of_pcl_pointxyzrgb(tmp_path, cvr):
+    """cvr_save_pcd: the file pcl::io::savePCDFileBinary writes for a PointXYZRGB cloud -- header fields, then 16 bytes per point."""
+    rng = np.random.default_rng(3)
+    pts = np.zeros(257, cvr.POINT_DTYPE)
+    for k in "xyz":
+        pts[k] = rng.standard_normal(257).astype(np.float32)
+    for k in "bgr":
+        pts[k] = rng.integers(0, 256, 257)
+    pts["a"] = 255
+    path = tmp_path / "cloud.pcd"
+    cvr.save_pcd(str(path), pts)
+    raw = path.read_bytes()
+    head, _, body = raw.partition(b"DATA binary\n")
+    fields = dict(l.split(" ", 1) for l in head.decode().splitlines() if l and not l.startswith("#"))
+    assert fields["VERSION"] in ("0.7", ".7") and fields["FIELDS"] == "x y z rgb" and fields["SIZE"] == "4 4 4 4"
+    assert fields["TYPE"] == "F F F F" and fields["COUNT"] == "1 1 1 1" and fields["HEIGHT"] == "1"
+    assert int(fields["WIDTH"]) == int(fields["POINTS"]) == 257 and len(body) == 257 * 16
+    back = np.frombuffer(body, cvr.POINT_DTYPE)
+    assert np.array_equal(back, pts)
+    rgb = np.frombuffer(body, np.uint32).reshape(-1, 4)[:, 3]      # PCL's packed colour word: 0xAARRGGBB
+    assert np.array_equal(rgb, (255 << 24) | (pts["r"].astype(np.uint32) << 16) | (pts["g"].astype(np.uint32) << 8) | pts["b"])
+    cvr.save_pcd(str(tmp_path / "empty.pcd"), pts[:0])
+    assert b"POINTS 0" in (tmp_path / "empty.pcd").read_bytes()
+    with pytest.raises(cvr.CvrError):
+        cvr.save_pcd(str(tmp_path / "no_such_dir" / "x.pcd"), pts)
+
+
 @pytest.mark.gpu
 def test_cpp_example_matches_python_harness(tmp_path, cvr, oracle):
     exe = _build_example(tmp_path, cvr)
