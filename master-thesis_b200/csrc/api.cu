@@ -246,7 +246,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     { const char* e_ = getenv("CVR_TAIL_STREAM"); c->tail_mode = e_ ? atoi(e_) : 0; }
     memset(c->slot, 0, sizeof(c->slot));
     fill_dev_params(c);
-    c->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    c->smem_optin = (int)prop.sharedMemPerBlockOptin; c->smem_sm = (int)prop.sharedMemPerMultiprocessor;
     { const char* e_ = getenv("CVR_PATH_KERNELS"); c->force_generic = e_ && strcmp(e_, "generic") == 0; c->path_v_variant = (e_ && strcmp(e_, "v2") == 0) ? 2 : ((e_ && strcmp(e_, "v3") == 0) ? 3 : 4); memset(c->pathv4_active, 0, sizeof(c->pathv4_active));
       const char* pf_ = getenv("CVR_PATH_H_FWD"); c->path_h_fwd = (pf_ && atoi(pf_) == 3) ? 3 : 2;   // -> : one row per warp already runs at the HBM rate
       const char* pr_ = getenv("CVR_PATH_H_REV"); c->path_h_rev = (pr_ && atoi(pr_) == 2) ? 2 : 3;   // <- + WTA: several rows per warp

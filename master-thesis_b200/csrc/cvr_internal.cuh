@@ -206,6 +206,7 @@ struct cvr_ctx {
     double* d_icp; double* h_icp;   // cvr_icp_align: block partials + totals of its 17 sums (device), the totals (pinned)
     int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
     int smem_optin;          // max dynamic shared memory per block (opt-in)
+    int smem_sm;             // shared memory per SM
     bool force_generic;      // CVR_PATH_KERNELS=generic: use the int32 path kernels (test hook)
     bool keep_S;             // CVR_KEEP_S=1: the last aggregation pass also writes the final S volume (cvr_debug_fetch(1); test hook)
     bool force_no_nn;        // CVR_NO_NN=1: never take the no-neighbour shortcut (test hook)

@@ -106,8 +106,11 @@ __global__ void k_sor_scatter(const cvr_point* __restrict__ pts, size_t stride, 
 // max-heap; the query itself (distance 0) is one of them, exactly like nearestKSearch(i, k+1).  The heap lives in SHARED
 // memory, one column per thread (best[i] of thread t at heap[i * 128 + t]: conflict-free however the threads' heap
 // positions diverge); as a per-thread array it was dynamically indexed and ended up in local memory.
-template <int KCAP>
-__global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
+// Measured and rejected for the 20 M-point case (k = 50; this kernel: 53 ms): a warp per occupied cell with the candidates shared
+// through shared memory and the heap updates batched (98 - 140 ms: the batched sifts still run with 5 of 32 lanes busy), the
+// same with a radix select (115 ms), re-fitting the cell size to the occupied cells (51 - 123 ms for 5 .. 1 points per cell).
+template <int KCAP, int MINB>
+__global__ void __launch_bounds__(128, MINB) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
                                                  const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
 {
     const int b = blockIdx.y;
@@ -148,13 +151,17 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
                     if (xa > xb) continue;
                     const int rowc = (iz * g.dim[1] + iy) * g.dim[0];
                     const int jb = cs[rowc + xa], je = cs[rowc + xb + 1];     // cells of one x run are contiguous in the sorted order
-                    for (int j = jb; j < je; j++) {
-                        const float4 p = sp[j];
+                    // four candidates per turn: their loads are issued together (with one load per turn the warp waited on each
+                    // candidate in turn: a third of all stall samples at 20 M points), then each is offered to the heap
+                    auto dist2 = [&](int jj) -> float {
+                        const float4 p = sp[jj];
                         const float dx = __fsub_rn(q.x, p.x), dy = __fsub_rn(q.y, p.y), dz = __fsub_rn(q.z, p.z);
                         float d2 = __fmul_rn(dx, dx);
                         d2 = __fadd_rn(d2, __fmul_rn(dy, dy));
-                        d2 = __fadd_rn(d2, __fmul_rn(dz, dz));
-                        // binary max-heap of the K1 smallest squared distances seen so far (root = the largest of them)
+                        return __fadd_rn(d2, __fmul_rn(dz, dz));
+                    };
+                    // binary max-heap of the K1 smallest squared distances seen so far (root = the largest of them)
+                    auto offer = [&](const float d2) {
                         if (cnt < K1) {
                             int pz = cnt++;
                             while (pz > 0) { const int par = (pz - 1) >> 1; const float pv = best[par]; if (pv >= d2) break; best[pz] = pv; pz = par; }
@@ -171,6 +178,14 @@ __global__ void __launch_bounds__(128) k_sor_knn(const float4* __restrict__ spts
                             }
                             best[pz] = d2;
                         }
+                    };
+                    for (int j = jb; j < je; j += 4) {
+                        const int last = je - 1;
+                        const float e0 = dist2(j), e1 = dist2(min(j + 1, last)), e2 = dist2(min(j + 2, last)), e3 = dist2(min(j + 3, last));
+                        offer(e0);
+                        if (j + 1 < je) offer(e1);
+                        if (j + 2 < je) offer(e2);
+                        if (j + 3 < je) offer(e3);
                     }
                 }
             }
@@ -328,10 +343,22 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     int rc = cvr_build_point_grid(c, B, in, in_stride, n_in, haveBox, 0.f, &grid, &cellstart);
     if (rc) return rc;
     const float4* sp = c->d_spts;
-    const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, 12), B);
     const size_t heapBytes = (size_t)(k + 1) * 128 * sizeof(float);   // one heap column per thread
-    if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
-    k_sor_knn<320><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    // a grid-stride kernel: exactly as many CTAs as are resident at once (a part-filled second wave cost a quarter of the time at 20 M points)
+    // two register budgets: 8 CTAs per SM (62 registers, no spills) for one large cloud, 10 (a few spilled words, more warps) for
+    // the many small clouds of a batch
+    const bool big = B == 1 && maxN >= (1 << 18);
+    const int regCap = big ? 8 : 10;
+    int perSM = (int)((size_t)c->smem_sm / (heapBytes + 1024));
+    perSM = perSM > regCap ? regCap : (perSM < 1 ? 1 : perSM);
+    const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, perSM), B);
+    if (big) {
+        if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
+        k_sor_knn<320, 8><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    } else {
+        if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
+        k_sor_knn<320, 10><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+    }
     LAUNCH_CHECK(c);
     k_sor_stats<<<B, 1024, 0, c->stream>>>(c->d_meand, ptStride, n_in, k, c->cl.sor_alpha, c->d_sstats);
     LAUNCH_CHECK(c);
