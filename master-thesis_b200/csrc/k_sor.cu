@@ -109,7 +109,7 @@ __global__ void k_sor_scatter(const cvr_point* __restrict__ pts, size_t stride, 
 // Measured and rejected for the 20 M-point case (k = 50; this kernel: 53 ms): a warp per occupied cell with the candidates shared
 // through shared memory and the heap updates batched (98 - 140 ms: the batched sifts still run with 5 of 32 lanes busy), the
 // same with a radix select (115 ms), re-fitting the cell size to the occupied cells (51 - 123 ms for 5 .. 1 points per cell).
-template <int KCAP, int MINB>
+template <int KCAP, int MINB, bool UNROLL>
 __global__ void __launch_bounds__(128, MINB) k_sor_knn(const float4* __restrict__ spts, size_t ptStride, const SorGrid* __restrict__ grid,
                                                  const int* __restrict__ cellstart, size_t cellStride, int k, float* __restrict__ meand)
 {
@@ -179,13 +179,17 @@ __global__ void __launch_bounds__(128, MINB) k_sor_knn(const float4* __restrict_
                             best[pz] = d2;
                         }
                     };
-                    for (int j = jb; j < je; j += 4) {
-                        const int last = je - 1;
-                        const float e0 = dist2(j), e1 = dist2(min(j + 1, last)), e2 = dist2(min(j + 2, last)), e3 = dist2(min(j + 3, last));
-                        offer(e0);
-                        if (j + 1 < je) offer(e1);
-                        if (j + 2 < je) offer(e2);
-                        if (j + 3 < je) offer(e3);
+                    if (UNROLL) {
+                        for (int j = jb; j < je; j += 4) {
+                            const int last = je - 1;
+                            const float e0 = dist2(j), e1 = dist2(min(j + 1, last)), e2 = dist2(min(j + 2, last)), e3 = dist2(min(j + 3, last));
+                            offer(e0);
+                            if (j + 1 < je) offer(e1);
+                            if (j + 2 < je) offer(e2);
+                            if (j + 3 < je) offer(e3);
+                        }
+                    } else {                                           // the small clouds of a batch: x runs of a few points, nothing to overlap
+                        for (int j = jb; j < je; j++) offer(dist2(j));
                     }
                 }
             }
@@ -345,19 +349,19 @@ int cvr_launch_sor(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, con
     const float4* sp = c->d_spts;
     const size_t heapBytes = (size_t)(k + 1) * 128 * sizeof(float);   // one heap column per thread
     // a grid-stride kernel: exactly as many CTAs as are resident at once (a part-filled second wave cost a quarter of the time at 20 M points)
-    // two register budgets: 8 CTAs per SM (62 registers, no spills) for one large cloud, 10 (a few spilled words, more warps) for
-    // the many small clouds of a batch
+    // two forms: 8 CTAs per SM (62 registers) and four candidate loads in flight for one large cloud; 10 CTAs per SM and the plain
+    // candidate loop for the many small clouds of a batch
     const bool big = B == 1 && maxN >= (1 << 18);
-    const int regCap = big ? 8 : 10;
+    const int regCap = big ? 8 : 12;                                   // (12: the batch form as measured best, a little more than is resident at once)
     int perSM = (int)((size_t)c->smem_sm / (heapBytes + 1024));
     perSM = perSM > regCap ? regCap : (perSM < 1 ? 1 : perSM);
     const dim3 g(cvr_frame_blocks(c, B, (size_t)maxN, 128, perSM), B);
     if (big) {
-        if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
-        k_sor_knn<320, 8><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+        if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320, 8, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
+        k_sor_knn<320, 8, true><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
     } else {
-        if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320, 10>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
-        k_sor_knn<320, 10><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
+        if (heapBytes > 48 * 1024) CVR_CUDA(c, cudaFuncSetAttribute(k_sor_knn<320, 10, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)heapBytes));
+        k_sor_knn<320, 10, false><<<g, 128, heapBytes, c->stream>>>(sp, ptStride, grid, cellstart, cellStride, k, c->d_meand);
     }
     LAUNCH_CHECK(c);
     k_sor_stats<<<B, 1024, 0, c->stream>>>(c->d_meand, ptStride, n_in, k, c->cl.sor_alpha, c->d_sstats);
