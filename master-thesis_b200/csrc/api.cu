@@ -85,8 +85,8 @@ int cvr_join_tail(cvr_ctx* c)
     c->tail_dirty = false; c->aux_pending = false;
     return CVR_OK;
 }
-static void timers_begin(cvr_ctx* c, int set) { c->tset = set; c->timers_used[set] = 0; cvr_stage_mark(c, "begin"); }
-static void timers_end(cvr_ctx* c, int set)                           // after the events of that set have completed
+void cvr_timers_begin(cvr_ctx* c, int set) { c->tset = set; c->timers_used[set] = 0; cvr_stage_mark(c, "begin"); }
+void cvr_timers_end(cvr_ctx* c, int set)                           // after the events of that set have completed
 {
     c->t_names.clear(); c->t_ms.clear();
     if (!c->profiling) return;
@@ -335,7 +335,7 @@ extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const u
     REQUIRE(c, sl >= (size_t)W * ch && sr >= (size_t)W * ch && sd >= (size_t)W * 2, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * ch, left, sl, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[1], (size_t)W * ch, right, sr, (size_t)W * ch, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_gray(c, 1, c->d_in[0], (size_t)W * ch, 0, c->d_in[1], (size_t)W * ch, 0, ch);
@@ -346,7 +346,7 @@ extern "C" int cvr_disparity(cvr_ctx* c, const uint8_t* left, size_t sl, const u
     CVR_CUDA(c, cudaMemcpy2DAsync(disp, sd, c->d_med, (size_t)W * 2, (size_t)W * 2, H, cudaMemcpyDeviceToHost, c->stream));
     cvr_stage_mark(c, "d2h");
     rc = sync_check(c);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -470,7 +470,7 @@ extern "C" int cvr_prune(cvr_ctx* c, int16_t* disp, size_t sd, float* dispf, uin
     REQUIRE(c, sd >= (size_t)W * 2, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_med, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_prune(c, 1, c->d_med);
     if (rc) return rc;
@@ -478,7 +478,7 @@ extern "C" int cvr_prune(cvr_ctx* c, int16_t* disp, size_t sd, float* dispf, uin
     if (dispf) CVR_CUDA(c, cudaMemcpyAsync(dispf, c->d_dispf, (size_t)W * H * 4, cudaMemcpyDeviceToHost, c->stream));
     if (mask) CVR_CUDA(c, cudaMemcpyAsync(mask, c->d_mask, (size_t)W * H, cudaMemcpyDeviceToHost, c->stream));
     rc = sync_check(c);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -503,13 +503,13 @@ extern "C" int cvr_reproject_cloud(cvr_ctx* c, const int16_t* disp, size_t sd, c
     REQUIRE(c, sd >= (size_t)W * 2 && sb >= (size_t)W * 3, "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_pruned, (size_t)W * 2, disp, sd, (size_t)W * 2, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_REPROJECT, c->d_pruned, nullptr, nullptr, c->d_in[0], (size_t)W * 3, 0, 3, false);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -523,14 +523,14 @@ extern "C" int cvr_triangulate(cvr_ctx* c, const float* dispf, size_t sd, const 
     REQUIRE(c, sd >= (size_t)W * 4 && sb >= (size_t)W * 3 && (!mask || sm >= (size_t)W), "step smaller than a row");
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_dispf, (size_t)W * 4, dispf, sd, (size_t)W * 4, H, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpy2DAsync(c->d_in[0], (size_t)W * 3, bgr, sb, (size_t)W * 3, H, cudaMemcpyHostToDevice, c->stream));
     if (mask) CVR_CUDA(c, cudaMemcpy2DAsync(c->d_mask, (size_t)W, mask, sm, (size_t)W, H, cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_cloud(c, 1, CVR_CLOUD_TRIANGULATE, nullptr, c->d_dispf, mask ? c->d_mask : nullptr, c->d_in[0], (size_t)W * 3, 0, 3, false);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_cloud, c->d_ncloud, out, capacity, n_out);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -544,7 +544,7 @@ extern "C" int cvr_voxel_grid(cvr_ctx* c, const cvr_point* in, int n, cvr_point*
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_cloud, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_ncloud, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
@@ -557,7 +557,7 @@ extern "C" int cvr_voxel_grid(cvr_ctx* c, const cvr_point* in, int n, cvr_point*
         CVR_CUDA(c, cudaMemcpy(&h, c->d_vhdr, sizeof(h), cudaMemcpyDeviceToHost));
         *passthrough = h.passthrough;
     }
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return CVR_OK;
 }
 
@@ -570,14 +570,14 @@ extern "C" int cvr_sor(cvr_ctx* c, const cvr_point* in, int n, cvr_point* out, i
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_nvox, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_sor(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, false);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_sorout, c->d_nout, out, capacity, kept_out);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -592,7 +592,7 @@ extern "C" int cvr_filter_cloud(cvr_ctx* c, int mem, const cvr_point* in, int n,
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     const cudaMemcpyKind kin = mem == CVR_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
     const cudaMemcpyKind kout = mem == CVR_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
     const bool vox = (stages & 4) != 0, sor = (stages & 8) != 0;
@@ -615,7 +615,7 @@ extern "C" int cvr_filter_cloud(cvr_ctx* c, int mem, const cvr_point* in, int n,
     if (m > 0) CVR_CUDA(c, cudaMemcpyAsync(out, fin, (size_t)m * sizeof(cvr_point), kout, c->stream));
     cvr_stage_mark(c, "out");
     rc = sync_check(c);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -628,14 +628,14 @@ extern "C" int cvr_radius_outlier_removal(cvr_ctx* c, const cvr_point* in, int n
     if (n == 0) return CVR_OK;
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     CVR_CUDA(c, cudaMemcpyAsync(c->d_vox, in, (size_t)n * sizeof(cvr_point), cudaMemcpyHostToDevice, c->stream));
     c->h_counts[1] = n;
     CVR_CUDA(c, cudaMemcpyAsync(c->d_nvox, &c->h_counts[1], sizeof(int), cudaMemcpyHostToDevice, c->stream));
     int rc = cvr_launch_ror(c, 1, c->d_vox, (size_t)c->maxN, c->d_nvox, radius, min_neighbors);
     if (rc) return rc;
     rc = fetch_cloud(c, c->d_sorout, c->d_nout, out, capacity, kept_out);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -862,7 +862,7 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
     c->lp_valid = false;
-    timers_begin(c, 0);
+    cvr_timers_begin(c, 0);
     const uint8_t *dl, *dr; size_t lstep, lfs, rstep, rfs;
     if (host) {
         const bool dense = io->left_frame_stride == io->left_step * (size_t)H && io->right_frame_stride == io->right_step * (size_t)H;
@@ -910,7 +910,7 @@ extern "C" int cvr_process_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     }
     cvr_stage_mark(c, "out");
     rc = sync_check(c);
-    timers_end(c, 0);
+    cvr_timers_end(c, 0);
     return rc;
 }
 
@@ -986,7 +986,7 @@ extern "C" int cvr_submit_batch(cvr_ctx* c, int nframes, const cvr_batch* io)
     } else {                                                           // device-resident inputs: read in place (the caller keeps them until cvr_wait_batch)
         dl = io->left; dr = io->right; lstep = io->left_step; rstep = io->right_step; lfs = io->left_frame_stride; rfs = io->right_frame_stride;
     }
-    timers_begin(c, tset);                                             // stage timers of this slot (read back by cvr_wait_batch)
+    cvr_timers_begin(c, tset);                                             // stage timers of this slot (read back by cvr_wait_batch)
     const cvr_point* fin = nullptr; const int* fcnt = nullptr;
     // From the matcher's hand-over point (cvr_tail_split) on, this batch is enqueued on the tail stream; c->stream is put back
     // when this function returns.  Not with rectification: the tail reads the rectified image the next batch's matcher rewrites.
@@ -1030,7 +1030,7 @@ static int wait_slot(cvr_ctx* c, PipeSlot& sl, int set)
     const cvr_batch& io = sl.io;
     const int B = sl.nframes, W = c->sg.W, H = c->sg.H;
     CVR_CUDA(c, cudaEventSynchronize(sl.evDone));
-    timers_end(c, set);
+    cvr_timers_end(c, set);
     set_last_pack(c, sl.d_out, sl.d_meta, sl.h_meta, B, sl.hasCloud);
     if (io.mem != CVR_MEM_HOST) {                                      // device-resident batch: the results are already in the caller's buffers
         if (sl.hasCloud && sl.h_meta[2 * (size_t)c->maxB + 3]) {

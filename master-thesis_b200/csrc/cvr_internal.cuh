@@ -283,6 +283,8 @@ int cvr_launch_transform(cvr_ctx* c, const cvr_point* in, cvr_point* out, int n,
 // k_sor.cu: bounding box (unless haveBox), grid (radius > 0: cell = radius, else ~2 points per cell), points sorted by cell into d_spts
 int cvr_build_point_grid(cvr_ctx* c, int B, const cvr_point* in, size_t in_stride, const int* n_in, bool haveBox, float radius, SorGrid** gridOut, int** cellstartOut);
 void cvr_stage_mark(cvr_ctx* c, const char* name);
+void cvr_timers_begin(cvr_ctx* c, int set);   // stage timers of a call: begin, marks, end (after the stream is idle) -> cvr_last_timings
+void cvr_timers_end(cvr_ctx* c, int set);
 int cvr_join_tail(cvr_ctx* c);         // entry points that work on c->stream alone: outstanding tail-stream work comes first
 int cvr_tail_split(cvr_ctx* c);        // matcher launchers: the path kernels of this batch are enqueued, the tail follows
 int cvr_tail_aux_consumed(cvr_ctx* c); // ... the tail no longer reads the WTA records (d_aux)

@@ -5,9 +5,11 @@
 // inflate thousands of PNGs per second.  Here a batch of PNG files is decoded on the device into the BGR frames the path reads:
 //   host      : walk the chunk list of each file (signature, IHDR, the IDAT segments) -- byte bookkeeping only
 //   k_png_idat: the IDAT payloads of every file -> one contiguous zlib stream per image
-//   k_png_inflate: zlib / DEFLATE (stored, fixed and dynamic Huffman blocks), ONE WARP PER IMAGE: the lanes keep an input ring
-//               and the 32 KiB sliding window in shared memory full / flushed with coalesced accesses, lane 0 walks the bit stream
-//               (first-level Huffman tables in shared memory, canonical-code search for the rare longer codes)
+//   k_png_inflate: zlib / DEFLATE (stored, fixed and dynamic Huffman blocks), ONE THREAD PER IMAGE (a single-warp CTA each): the
+//               bit stream is read and the scanlines are written directly in global memory (the output is its own 32 KiB
+//               window), only the Huffman tables live in shared memory (first-level tables, canonical-code search for the
+//               rare longer codes) -- 32 streams in flight per SM; a stream is a chain of dependent instructions, so the rate
+//               of the decoder is the number of streams in flight (measured: inflate_all below)
 //   k_png_unfilter: the five PNG scanline filters (None / Sub / Up / Average / Paeth, sequential per image where the filter
 //               demands it, the colour chains of a row in parallel) and the channel order of IMREAD_COLOR (RGB(A) / gray -> BGR)
 // Supported: 8-bit, non-interlaced, colour types 0 (gray), 2 (RGB) and 6 (RGBA; alpha dropped as IMREAD_COLOR does).  Anything
@@ -34,8 +36,6 @@ __global__ void k_png_idat(const uint8_t* __restrict__ blob, const PngSeg* __res
 }
 
 // ---- inflate ---------------------------------------------------------------------------------------------------------
-#define PNG_INRING 2048         // bytes of input kept in shared memory (power of two; half of it exceeds the longest dynamic block header)
-#define PNG_WIN 32768           // DEFLATE's sliding window = the output ring
 #define PNG_LBITS 10            // first-level table bits, literal/length codes
 #define PNG_DBITS 8             // ... distance codes
 #ifdef __CUDA_ARCH__
@@ -48,9 +48,7 @@ struct Huff {                   // canonical code: counts per length, symbols so
     unsigned short count[16];
     unsigned short symbol[288];
 };
-struct InflateSm {
-    uint8_t in[PNG_INRING];
-    uint8_t win[PNG_WIN];
+struct InflateTab {             // per image: shared memory on the device
     unsigned short ltab[1 << PNG_LBITS];   // (length << 9) | symbol; 0 = code longer than the table
     unsigned short dtab[1 << PNG_DBITS];
     Huff lh, dh;
@@ -82,53 +80,53 @@ __host__ __device__ inline int huff_build(Huff& h, const unsigned short* lens, i
     return left > 0 ? 1 : 0;    // incomplete codes are tolerated where zlib tolerates them (single distance code)
 }
 
-struct BitIn {
-    unsigned long long bb; int bc;      // bit buffer (LSB first) and number of valid bits
-    int pos;                            // next input byte to enter the buffer: always a multiple of 4 (the buffer is refilled a word at a time)
-};
-struct InflateState {               // what lane 0 carries across the cooperative refill / flush points
-    BitIn b;
-    int outPos;
-    int status, done;
-    int phase;                      // 0 block header, 1 stored copy, 2 huffman symbols
-    int last, storedLeft;
-    int pendLen, pendDist;          // a match being copied
-};
-// The sequential part of inflate: decodes until `inStop` input bytes are consumed, the output reaches `outStop`, the stream ends
-// or an error is found.  Input comes from the ring S.in (byte p at S.in[p % PNG_INRING]), output goes to the window ring S.win.
-// status: 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol / distance, 5 output overrun, 6 input overrun,
-// 7 stored-block length check.  (Host-callable too: tests/png_inflate_host.cu runs it on the CPU.)
-__host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, int inStop, int outStop, int inLen, int rawLen)
+// zlib / DEFLATE of one stream, start to end, by ONE thread: `in` holds inLen bytes, is 4-byte aligned and readable for 8 bytes
+// more (the bit buffer is refilled a 32-bit word at a time); the output goes straight to `out` (rawLen bytes), which also serves
+// as the 32 KiB window -- a match reads what this thread wrote earlier.  Nothing of a stream lives in shared memory but its
+// Huffman tables (4.4 KB), so that 32 streams are in flight per SM: the decoder is a chain of dependent instructions per symbol
+// and its throughput is the number of streams in flight.
+// Returns 0, or: 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol / distance, 5 output size differs from
+// rawLen, 6 input overrun, 7 stored-block length check.  (Host-callable: tests/png_host_harness.cu runs it on the CPU.)
+__host__ __device__ inline int inflate_all(InflateTab& S, const uint8_t* __restrict__ in, int inLen, uint8_t* out, int rawLen)
 {
-    BitIn b = st.b;
-    int outPos = st.outPos;
-    int status = st.status, done = st.done, phase = st.phase, last = st.last, storedLeft = st.storedLeft, pendLen = st.pendLen, pendDist = st.pendDist;
-    // NEED(n), n <= 33: one aligned 32-bit word of the input ring enters the buffer when fewer than n bits are left
-#define NEED(n) if (b.bc < (n)) { b.bb |= (unsigned long long)(*(const unsigned*)&S.in[b.pos & (PNG_INRING - 1)]) << b.bc; b.bc += 32; b.pos += 4; }
-#define TAKE(var, n) { var = (b.bb & ((1ull << (n)) - 1)); b.bb >>= (n); b.bc -= (n); }
-    if (outPos == 0 && b.pos == 0) {                                   // zlib header
-        unsigned cmf, flg;
-        NEED(16);
-        TAKE(cmf, 8); TAKE(flg, 8);
-        if ((cmf & 15) != 8 || ((cmf << 8) | flg) % 31 != 0 || (flg & 32)) status = 1;
-    }
-    while (!status && !done && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
-        if (b.pos - (b.bc >> 3) > inLen) { status = 6; break; }
-        if (phase == 0) {
-            int type;
+    unsigned long long bb = 0;          // bit buffer (LSB first)
+    int bc = 0;                         // valid bits
+    const unsigned* ip = (const unsigned*)in;                          // next input word to enter the buffer
+    const unsigned* const ipLimit = ip + (inLen + 4) / 4 + 1;          // a refill beyond this word: the stream was overrun
+    uint8_t* op = out;                                                 // next output byte
+    uint8_t* const oend = out + rawLen;
+    int status = 0, last = 0;
+    // NEED(n), n <= 32: one aligned word enters the buffer when fewer than n bits are left (bits of the padding behind the stream
+    // are never legitimately consumed: checked at the end)
+#define NEED(n) if (bc < (n)) { if (ip >= ipLimit) { status = 6; break; } bb |= (unsigned long long)(*ip++) << bc; bc += 32; }
+#define CONSUMED() ((int)((const uint8_t*)ip - in) - (bc >> 3))
+#define TAKE(var, n) { var = (unsigned)(bb & ((1ull << (n)) - 1)); bb >>= (n); bc -= (n); }
+    do {                                                               // (a block for `break` on errors)
+        {
+            unsigned cmf, flg;
+            NEED(16);
+            TAKE(cmf, 8); TAKE(flg, 8);
+            if ((cmf & 15) != 8 || ((cmf << 8) | flg) % 31 != 0 || (flg & 32)) { status = 1; break; }
+        }
+        while (!last && !status) {
+            unsigned type;
             NEED(3);
             TAKE(last, 1); TAKE(type, 2);
             if (type == 0) {
-                const int drop = b.bc & 7; b.bb >>= drop; b.bc -= drop;           // to the byte boundary
+                const int drop = bc & 7; bb >>= drop; bc -= drop;      // to the byte boundary
                 unsigned len, nlen;
                 NEED(16);
                 TAKE(len, 16);
                 NEED(16);
                 TAKE(nlen, 16);
                 if ((len ^ 0xffffu) != nlen) { status = 7; break; }
-                storedLeft = (int)len; phase = 1;
-                if (storedLeft == 0) { phase = 0; if (last) done = 1; }
-            } else if (type == 1) {
+                if ((long long)len > oend - op) { status = 5; break; }
+                if (CONSUMED() + (int)len > inLen) { status = 6; break; }
+                for (unsigned i = 0; i < len; i++) { unsigned v; NEED(8); TAKE(v, 8); *op++ = (uint8_t)v; }
+                if (status) break;
+                continue;
+            }
+            if (type == 1) {
                 for (int i = 0; i < 144; i++) S.lens[i] = 8;
                 for (int i = 144; i < 256; i++) S.lens[i] = 9;
                 for (int i = 256; i < 280; i++) S.lens[i] = 7;
@@ -136,31 +134,31 @@ __host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, int 
                 huff_build(S.lh, S.lens, 288, S.ltab, PNG_LBITS);
                 for (int i = 0; i < 30; i++) S.lens[i] = 5;
                 huff_build(S.dh, S.lens, 30, S.dtab, PNG_DBITS);
-                phase = 2;
             } else if (type == 2) {
-                int nlen, ndist, ncode;
+                unsigned nlen, ndist, ncode;
                 NEED(14);
                 TAKE(nlen, 5); TAKE(ndist, 5); TAKE(ncode, 4);
                 nlen += 257; ndist += 1; ncode += 4;
                 if (nlen > 286 || ndist > 30) { status = 3; break; }
                 const unsigned char order[19] = { 16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15 };
                 for (int i = 0; i < 19; i++) S.lens[i] = 0;
-                for (int i = 0; i < ncode; i++) { unsigned v; NEED(3); TAKE(v, 3); S.lens[order[i]] = (unsigned short)v; }
+                for (unsigned i = 0; i < ncode; i++) { unsigned v; NEED(3); TAKE(v, 3); S.lens[order[i]] = (unsigned short)v; }
+                if (status) break;
                 if (huff_build(S.lh, S.lens, 19, S.ltab, 7) < 0) { status = 3; break; }   // the code-length code (7-bit table in ltab)
-                int idx = 0;
-                unsigned short* tmp = S.lens + 0;                        // the decoded lengths replace the 19 (already consumed by huff_build)
+                unsigned idx = 0;
+                unsigned short* tmp = S.lens + 0;                      // the decoded lengths replace the 19 (already consumed by huff_build)
                 while (idx < nlen + ndist) {
-                    NEED(7);
-                    const unsigned short e = S.ltab[b.bb & 127];
+                    NEED(14);                                          // a code (<= 7 bits) and its extra bits (<= 7)
+                    const unsigned short e = S.ltab[bb & 127];
                     if (!e) { status = 3; break; }
                     const int l = e >> 9, sym = e & 511;
-                    b.bb >>= l; b.bc -= l;
+                    bb >>= l; bc -= l;
                     if (sym < 16) tmp[idx++] = (unsigned short)sym;
                     else {
-                        int rep, val = 0;
-                        if (sym == 16) { if (idx == 0) { status = 3; break; } val = tmp[idx - 1]; NEED(2); TAKE(rep, 2); rep += 3; }
-                        else if (sym == 17) { NEED(3); TAKE(rep, 3); rep += 3; }
-                        else { NEED(7); TAKE(rep, 7); rep += 11; }
+                        unsigned rep, val = 0;
+                        if (sym == 16) { if (idx == 0) { status = 3; break; } val = tmp[idx - 1]; TAKE(rep, 2); rep += 3; }
+                        else if (sym == 17) { TAKE(rep, 3); rep += 3; }
+                        else { TAKE(rep, 7); rep += 11; }
                         if (idx + rep > nlen + ndist) { status = 3; break; }
                         while (rep--) tmp[idx++] = (unsigned short)val;
                     }
@@ -168,120 +166,89 @@ __host__ __device__ inline void inflate_run(InflateState& st, InflateSm& S, int 
                 if (status) break;
                 if (tmp[256] == 0) { status = 3; break; }              // no end-of-block code
                 // the distance lengths first (they sit behind the literal/length ones, which building the first code leaves alone)
-                if (huff_build(S.dh, tmp + nlen, ndist, S.dtab, PNG_DBITS) < 0) { status = 3; break; }
-                if (huff_build(S.lh, tmp, nlen, S.ltab, PNG_LBITS) < 0) { status = 3; break; }
-                phase = 2;
+                if (huff_build(S.dh, tmp + nlen, (int)ndist, S.dtab, PNG_DBITS) < 0) { status = 3; break; }
+                if (huff_build(S.lh, tmp, (int)nlen, S.ltab, PNG_LBITS) < 0) { status = 3; break; }
             } else { status = 2; break; }
-        } else if (phase == 1) {
-            // stored bytes: straight from the bit buffer / input ring into the window
-            while (storedLeft > 0 && b.pos - (b.bc >> 3) < inStop && outPos < outStop) {
-                unsigned v;
-                NEED(8);
-                TAKE(v, 8);
-                S.win[outPos & (PNG_WIN - 1)] = (uint8_t)v;
-                outPos++; storedLeft--;
-            }
-            if (storedLeft == 0) { phase = 0; if (last) done = 1; }
-        } else {
-            if (pendLen > 0) {                                         // continue a match that was cut by a flush point
-                while (pendLen > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - pendDist) & (PNG_WIN - 1)]; outPos++; pendLen--; }
-                if (pendLen > 0) break;
-            }
-            NEED(20);                                                  // a literal/length code (<= 15 bits) and its extra bits (<= 5)
-            unsigned short e = S.ltab[b.bb & ((1u << PNG_LBITS) - 1)];
-            int l, sym;
-            if (e) { l = e >> 9; sym = e & 511; }
-            else {                                                     // longer than the table: canonical search, one bit at a time
-                int code = 0, first = 0, index = 0; l = 0; sym = -1;
-                for (int len = 1; len <= 15; len++) {
-                    code |= (int)((b.bb >> (len - 1)) & 1);
-                    const int cnt = S.lh.count[len];
-                    if (code - cnt < first) { sym = S.lh.symbol[index + (code - first)]; l = len; break; }
-                    index += cnt; first += cnt; first <<= 1; code <<= 1;
+            // ---- the symbols of a Huffman block ----
+            for (;;) {
+                NEED(20);                                              // a literal/length code (<= 15 bits) and its extra bits (<= 5)
+                const unsigned short e = S.ltab[bb & ((1u << PNG_LBITS) - 1)];
+                int l, sym;
+                if (e) { l = e >> 9; sym = e & 511; }
+                else {                                                 // longer than the table: canonical search, one bit at a time
+                    int code = 0, first = 0, index = 0; l = 0; sym = -1;
+                    for (int len = 1; len <= 15; len++) {
+                        code |= (int)((bb >> (len - 1)) & 1);
+                        const int cnt = S.lh.count[len];
+                        if (code - cnt < first) { sym = S.lh.symbol[index + (code - first)]; l = len; break; }
+                        index += cnt; first += cnt; first <<= 1; code <<= 1;
+                    }
+                    if (sym < 0) { status = 4; break; }
                 }
-                if (sym < 0) { status = 4; break; }
-            }
-            b.bb >>= l; b.bc -= l;
-            if (sym < 256) { S.win[outPos & (PNG_WIN - 1)] = (uint8_t)sym; outPos++; }
-            else if (sym == 256) { phase = 0; if (last) done = 1; }
-            else {
+                bb >>= l; bc -= l;
+                if (sym < 256) {
+                    if (op >= oend) { status = 5; break; }
+                    *op++ = (uint8_t)sym;
+                    continue;
+                }
+                if (sym == 256) break;                                 // end of block
                 sym -= 257;
                 if (sym >= 29) { status = 4; break; }
                 const unsigned short lbase[29] = { 3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258 };
                 const unsigned char lext[29] = { 0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0 };
-                int len = lbase[sym] + (int)(b.bb & ((1u << lext[sym]) - 1));
-                b.bb >>= lext[sym]; b.bc -= lext[sym];
+                int len = lbase[sym] + (int)(bb & ((1u << lext[sym]) - 1));
+                bb >>= lext[sym]; bc -= lext[sym];
                 NEED(28);                                              // a distance code (<= 15 bits) and its extra bits (<= 13)
-                unsigned short de = S.dtab[b.bb & ((1u << PNG_DBITS) - 1)];
+                const unsigned short de = S.dtab[bb & ((1u << PNG_DBITS) - 1)];
                 int dl, ds;
                 if (de) { dl = de >> 9; ds = de & 511; }
                 else {
                     int code = 0, first = 0, index = 0; dl = 0; ds = -1;
                     for (int q = 1; q <= 15; q++) {
-                        code |= (int)((b.bb >> (q - 1)) & 1);
+                        code |= (int)((bb >> (q - 1)) & 1);
                         const int cnt = S.dh.count[q];
                         if (code - cnt < first) { ds = S.dh.symbol[index + (code - first)]; dl = q; break; }
                         index += cnt; first += cnt; first <<= 1; code <<= 1;
                     }
                     if (ds < 0) { status = 4; break; }
                 }
-                b.bb >>= dl; b.bc -= dl;
+                bb >>= dl; bc -= dl;
                 if (ds >= 30) { status = 4; break; }
                 const unsigned short dbase[30] = { 1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577 };
                 const unsigned char dext[30] = { 0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13 };
-                const int dist = dbase[ds] + (int)(b.bb & ((1u << dext[ds]) - 1));
-                b.bb >>= dext[ds]; b.bc -= dext[ds];
-                if (dist > outPos) { status = 4; break; }
-                pendDist = dist;
-                while (len > 0 && outPos < outStop) { S.win[outPos & (PNG_WIN - 1)] = S.win[(outPos - dist) & (PNG_WIN - 1)]; outPos++; len--; }
-                pendLen = len;
+                const int dist = dbase[ds] + (int)(bb & ((1u << dext[ds]) - 1));
+                bb >>= dext[ds]; bc -= dext[ds];
+                if (dist > op - out) { status = 4; break; }
+                if (len > oend - op) { status = 5; break; }
+                if (dist == 1) {                                       // a run (all that zlib's Z_RLE strategy, OpenCV's default for PNG, ever emits)
+                    const uint8_t v = op[-1];
+                    for (int i = 0; i < len; i++) op[i] = v;
+                } else {
+                    const uint8_t* sp_ = op - dist;
+                    for (int i = 0; i < len; i++) op[i] = sp_[i];     // byte order matters when dist < len
+                }
+                op += len;
             }
         }
-        if (outPos > rawLen) { status = 5; break; }
-    }
+        if (status) break;
+        if (CONSUMED() > inLen) { status = 6; break; }                 // bits beyond the end of the stream were consumed
+        if (op != oend) status = 5;
+    } while (false);
 #undef NEED
 #undef TAKE
-    st.b = b; st.outPos = outPos; st.status = status; st.done = done; st.phase = phase; st.last = last; st.storedLeft = storedLeft;
-    st.pendLen = pendLen; st.pendDist = pendDist;
+#undef CONSUMED
+    return status;
 }
 
 #ifndef PNG_HOST_ONLY
-// One warp per image: lane 0 decodes (inflate_run), all lanes flush finished halves of the window to global memory and refill
-// consumed halves of the input ring.  Result in img.status (0 ok).
-__global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ z, PngImg* imgs, uint8_t* __restrict__ raw, long long rawStride, int rawLen)
+// One single-warp CTA per image; lane 0 decodes (the other lanes only keep the CTA at warp granularity: 32 CTAs, i.e. 32 streams,
+// per SM).  Result in img.status (0 ok).
+__global__ void __launch_bounds__(32) k_png_inflate(const uint8_t* __restrict__ z, PngImg* imgs, uint8_t* raw, long long rawStride, int W, int H)
 {
-    extern __shared__ __align__(16) unsigned char ism[];
-    InflateSm& S = *(InflateSm*)ism;
-    const int lane = threadIdx.x;
+    __shared__ InflateTab S;
+    if (threadIdx.x != 0) return;
     PngImg& im = imgs[blockIdx.x];
-    const uint8_t* in = z + im.zOff;
-    const int inLen = (int)im.zLen;
-    uint8_t* out = raw + (long long)blockIdx.x * rawStride;
-    int inBase = 0;                                                    // the input ring holds bytes [inBase, inBase + PNG_INRING)
-    for (int i = lane; i < PNG_INRING; i += 32) S.in[i] = i < inLen ? in[i] : 0;
-    __syncwarp();
-    InflateState st;
-    memset(&st, 0, sizeof(st));
-    int flushed = 0;
-    while (true) {
-        if (lane == 0 && !st.done && !st.status) inflate_run(st, S, inBase + PNG_INRING / 2, flushed + PNG_WIN / 2, inLen, rawLen);
-        const int done = __shfl_sync(0xffffffffu, st.done, 0), status = __shfl_sync(0xffffffffu, st.status, 0);
-        const int outPos = __shfl_sync(0xffffffffu, st.outPos, 0);
-        const int consumed = __shfl_sync(0xffffffffu, st.b.pos - (st.b.bc >> 3), 0);
-        const int upto = (done || status) ? outPos : (outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);   // whole halves, or everything at the end
-        // (the window and the scanline buffer are both 16-byte aligned and `flushed` is a multiple of 16 until the very end)
-        const int vend = min(upto, rawLen) & ~15;
-        for (int i = flushed + lane * 16; i < vend; i += 32 * 16) *(uint4*)(out + i) = *(const uint4*)&S.win[i & (PNG_WIN - 1)];
-        for (int i = max(flushed, vend) + lane; i < upto && i < rawLen; i += 32) out[i] = S.win[i & (PNG_WIN - 1)];
-        flushed = upto > flushed ? upto : flushed;
-        if (done || status) { if (lane == 0) im.status = status ? status : (outPos == rawLen ? 0 : 5); break; }
-        while (consumed >= inBase + PNG_INRING / 2) {                   // the older half of the ring is free: bring in the next bytes
-            const int src = inBase + PNG_INRING;
-            for (int i = lane; i < PNG_INRING / 2; i += 32) S.in[(src + i) & (PNG_INRING - 1)] = (src + i) < inLen ? in[src + i] : 0;
-            inBase += PNG_INRING / 2;
-        }
-        __syncwarp();
-    }
+    im.status = inflate_all(S, z + im.zOff, (int)im.zLen, raw + (long long)blockIdx.x * rawStride, H * (W * im.bpp + 1));
 }
 
 // ---- scanline filters + channel order --------------------------------------------------------------------------------
@@ -393,7 +360,7 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
         }
         if (im.colorType < 0 || im.zLen < 6) { c->err = "cvr_decode_png_batch: PNG without IHDR / IDAT"; return CVR_ERR_INVALID_ARG; }
         blobLen += (long long)len;
-        zTotal += im.zLen;
+        zTotal = (zTotal + im.zLen + 15) & ~15LL;                        // every stream starts 16-byte aligned (the decoder reads whole words)
     }
     CVR_CUDA(c, cudaSetDevice(c->device));
     { const int rcj_ = cvr_join_tail(c); if (rcj_) return rcj_; }
@@ -415,31 +382,25 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
         if ((rc = grow(&c->png_out, &c->png_out_cap, needOut))) return rc;
         dOut = c->png_out; dStep = (size_t)W * 3; dStride = dStep * H;
     }
+    cvr_timers_begin(c, 0);
     long long off = 0;
     for (int i = 0; i < n; i++) { CVR_CUDA(c, cudaMemcpyAsync(c->png_blob + off, png[i], png_bytes[i], cudaMemcpyHostToDevice, c->stream)); off += (long long)png_bytes[i]; }
     PngImg* dImgs = (PngImg*)c->png_tab;
     PngSeg* dSegs = (PngSeg*)(c->png_tab + ((sizeof(PngImg) * (size_t)n + 15) & ~(size_t)15));
     CVR_CUDA(c, cudaMemcpyAsync(dImgs, imgs.data(), sizeof(PngImg) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpyAsync(dSegs, segs.data(), sizeof(PngSeg) * segs.size(), cudaMemcpyHostToDevice, c->stream));
+    cvr_stage_mark(c, "png_upload");
     k_png_idat<<<(unsigned)(segs.size() < 4096 ? segs.size() : 4096), 128, 0, c->stream>>>(c->png_blob, dSegs, (int)segs.size(), c->png_z);
     LAUNCH_CHECK(c);
-    CVR_CUDA(c, cudaFuncSetAttribute(k_png_inflate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(InflateSm)));
+    cvr_stage_mark(c, "png_idat");
     // every image inflates to H scanlines of 1 + W * bpp bytes; the images of a batch may differ in colour type
     if ((long long)H * ((long long)W * 4 + 1) > 0x3fffffffLL) { c->err = "cvr_decode_png_batch: image too large for the device decoder"; return CVR_ERR_UNSUPPORTED; }
-    std::vector<int> rawLens((size_t)n);
-    bool same = true;
-    for (int i = 0; i < n; i++) { rawLens[(size_t)i] = H * (W * imgs[(size_t)i].bpp + 1); same = same && rawLens[(size_t)i] == rawLens[0]; }
-    if (same) {
-        k_png_inflate<<<n, 32, sizeof(InflateSm), c->stream>>>(c->png_z, dImgs, c->png_raw, rawStride, rawLens[0]);
-        LAUNCH_CHECK(c);
-    } else {
-        for (int i = 0; i < n; i++) {
-            k_png_inflate<<<1, 32, sizeof(InflateSm), c->stream>>>(c->png_z, dImgs + i, c->png_raw + (long long)i * rawStride, rawStride, rawLens[(size_t)i]);
-            LAUNCH_CHECK(c);
-        }
-    }
+    k_png_inflate<<<n, 32, 0, c->stream>>>(c->png_z, dImgs, c->png_raw, rawStride, W, H);
+    LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "png_inflate");
     k_png_unfilter<<<n, 32, 0, c->stream>>>(c->png_raw, rawStride, dImgs, W, H, dOut, dStep, dStride);
     LAUNCH_CHECK(c);
+    cvr_stage_mark(c, "png_unfilter");
     CVR_CUDA(c, cudaMemcpyAsync(imgs.data(), dImgs, sizeof(PngImg) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
     if (mem_out == CVR_MEM_HOST) {
         if (image_stride == step * (size_t)H) CVR_CUDA(c, cudaMemcpy2DAsync(bgr, step, dOut, dStep, (size_t)W * 3, (size_t)H * n, cudaMemcpyDeviceToHost, c->stream));
@@ -447,6 +408,7 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
     }
     cudaError_t e = cudaStreamSynchronize(c->stream);
     if (e != cudaSuccess) { c->err = std::string("stream sync: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
+    cvr_timers_end(c, 0);
     for (int i = 0; i < n; i++)
         if (imgs[(size_t)i].status) { c->err = "cvr_decode_png_batch: corrupt or unsupported deflate stream in image " + std::to_string(i) + " (code " + std::to_string(imgs[(size_t)i].status) + ")"; return CVR_ERR_INVALID_ARG; }
     return CVR_OK;

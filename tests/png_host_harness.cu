@@ -1,30 +1,19 @@
-// Test infrastructure: runs the sequential inflate routine of master-thesis_b200/csrc/k_png.cu (inflate_run, a __host__ __device__
-// function) on the CPU, driving its input ring / output window exactly as the kernel's cooperative loop does, so that the bit-stream
-// logic is covered by the CPU test suite (tests/test_png_host.py compares it with zlib).  Built with nvcc -DPNG_HOST_ONLY.
+// Test infrastructure: runs the inflate routine of master-thesis_b200/csrc/k_png.cu (inflate_all, a __host__ __device__ function:
+// the very code lane 0 of the kernel executes) on the CPU, so that the bit-stream logic is covered by the CPU test suite
+// (tests/test_png_host.py compares it with zlib).  Built with nvcc -DPNG_HOST_ONLY.
 #define PNG_HOST_ONLY 1
 #include "../master-thesis_b200/csrc/k_png.cu"
 
 extern "C" int png_inflate_host(const uint8_t* z, long long zlen, uint8_t* out, long long rawLen)
 {
-    InflateSm* S = new InflateSm;
-    for (int i = 0; i < PNG_INRING; i++) S->in[i] = i < zlen ? z[i] : 0;
-    InflateState st;
-    memset(&st, 0, sizeof(st));
-    int inBase = 0, flushed = 0;
-    int result;
-    for (;;) {
-        if (!st.done && !st.status) inflate_run(st, *S, inBase + PNG_INRING / 2, flushed + PNG_WIN / 2, (int)zlen, (int)rawLen);
-        const int consumed = st.b.pos - (st.b.bc >> 3);
-        const int upto = (st.done || st.status) ? st.outPos : (st.outPos / (PNG_WIN / 2)) * (PNG_WIN / 2);
-        for (int i = flushed; i < upto && i < rawLen; i++) out[i] = S->win[i & (PNG_WIN - 1)];
-        if (upto > flushed) flushed = upto;
-        if (st.done || st.status) { result = st.status ? st.status : (st.outPos == rawLen ? 0 : 5); break; }
-        while (consumed >= inBase + PNG_INRING / 2) {
-            const int src = inBase + PNG_INRING;
-            for (int i = 0; i < PNG_INRING / 2; i++) S->in[(src + i) & (PNG_INRING - 1)] = (src + i) < zlen ? z[src + i] : 0;
-            inBase += PNG_INRING / 2;
-        }
-    }
-    delete S;
+    InflateTab* S = new InflateTab;
+    // the decoder reads its input a 32-bit word at a time: 4-byte aligned, readable 8 bytes past the end (as cvr_decode_png_batch lays it out)
+    unsigned* buf = new unsigned[(size_t)(zlen + 16) / 4 + 1];
+    memset(buf, 0, ((size_t)(zlen + 16) / 4 + 1) * 4);
+    memcpy(buf, z, (size_t)zlen);
+    uint8_t* o = new uint8_t[(size_t)rawLen + 1];
+    const int result = inflate_all(*S, (const uint8_t*)buf, (int)zlen, o, (int)rawLen);
+    memcpy(out, o, (size_t)rawLen);
+    delete[] o; delete[] buf; delete S;
     return result;
 }

@@ -1,5 +1,5 @@
-"""CPU: the sequential inflate routine of the device PNG decoder (inflate_run in master-thesis_b200/csrc/k_png.cu, a
-__host__ __device__ function) compiled for the host and driven through the same input-ring / window protocol as the kernel
+"""CPU: the sequential inflate routine of the device PNG decoder (master-thesis_b200/csrc/k_png.cu, a
+__host__ __device__ function: inflate_all, the code lane 0 of the kernel runs) compiled for the host
 (tests/png_host_harness.cu), against zlib on streams that use every block type, long matches and long Huffman codes."""
 import ctypes as C
 import os
