@@ -204,6 +204,8 @@ static void free_all(cvr_ctx* c)
     if (c->h_counts) cudaFreeHost(c->h_counts);
     if (c->h_meta0) cudaFreeHost(c->h_meta0);
     for (uint8_t* q : { c->png_blob, c->png_z, c->png_raw, c->png_tab, c->png_out }) if (q) cudaFree(q);
+    for (auto& st_ : c->png_stream) if (st_) cudaStreamDestroy(st_);
+    for (auto& ev_ : c->png_ev) if (ev_) cudaEventDestroy(ev_);
     if (c->d_icp) cudaFree(c->d_icp);
     if (c->h_icp) cudaFreeHost(c->h_icp);
     if (c->d_meta0) cudaFree(c->d_meta0);
@@ -240,7 +242,7 @@ extern "C" int cvr_create(const cvr_params* p, int device, cvr_ctx** out)
     cvr_ctx* c = new (std::nothrow) cvr_ctx();
     if (!c) return CVR_ERR_CUDA;
     c->prm = *p; c->device = device; c->maxB = p->max_batch; c->sm_count = prop.multiProcessorCount;
-    c->launches = 0; c->profiling = false; c->timers_used[0] = c->timers_used[1] = c->timers_used[2] = 0; c->tset = 0; c->stream = nullptr; c->h_counts = nullptr; c->h_meta0 = nullptr; c->d_meta0 = nullptr; c->lp_valid = false; c->d_icp = nullptr; c->h_icp = nullptr; c->png_blob = c->png_z = c->png_raw = c->png_tab = c->png_out = nullptr; c->png_blob_cap = c->png_z_cap = c->png_raw_cap = c->png_tab_cap = c->png_out_cap = 0; cvr_comm_reset(c);
+    c->launches = 0; c->profiling = false; c->timers_used[0] = c->timers_used[1] = c->timers_used[2] = 0; c->tset = 0; c->stream = nullptr; c->h_counts = nullptr; c->h_meta0 = nullptr; c->d_meta0 = nullptr; c->lp_valid = false; c->d_icp = nullptr; c->h_icp = nullptr; c->png_blob = c->png_z = c->png_raw = c->png_tab = c->png_out = nullptr; c->png_blob_cap = c->png_z_cap = c->png_raw_cap = c->png_tab_cap = c->png_out_cap = 0; for (auto& st_ : c->png_stream) st_ = nullptr; for (auto& ev_ : c->png_ev) ev_ = nullptr; cvr_comm_reset(c);
     c->pipe_ready = false; c->copy_stream = nullptr; c->d2h_stream = nullptr; c->n_submit = c->n_wait = 0;
     c->tail_stream = nullptr; c->path_stream = nullptr; c->evPath = c->evAuxFree = c->evTailLast = nullptr; c->split_tail = c->aux_pending = c->tail_dirty = false;
     { const char* e_ = getenv("CVR_TAIL_STREAM"); c->tail_mode = e_ ? atoi(e_) : 0; }

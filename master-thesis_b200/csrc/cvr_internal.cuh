@@ -203,6 +203,7 @@ struct cvr_ctx {
     cvr_point* d_gather; size_t gather_cap;   // root: receive buffer when the caller wants the clouds on the host
     uint8_t *png_blob, *png_z, *png_raw, *png_tab, *png_out;   // cvr_decode_png_batch: files, zlib streams, scanlines, tables, BGR staging (grown on demand)
     size_t png_blob_cap, png_z_cap, png_raw_cap, png_tab_cap, png_out_cap;
+    cudaStream_t png_stream[4]; cudaEvent_t png_ev[5];   // large calls: four chunks of files, each uploaded and decoded on its own stream
     double* d_icp; double* h_icp;   // cvr_icp_align: block partials + totals of its 17 sums (device), the totals (pinned)
     int* d_sgflags;          // per-frame SGBM regime flags (bit 0: negative C seen, bit 1: negative path cost seen) [B]
     int smem_optin;          // max dynamic shared memory per block (opt-in)

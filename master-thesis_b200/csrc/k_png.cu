@@ -382,30 +382,51 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
         if ((rc = grow(&c->png_out, &c->png_out_cap, needOut))) return rc;
         dOut = c->png_out; dStep = (size_t)W * 3; dStride = dStep * H;
     }
+    // every image inflates to H scanlines of 1 + W * bpp bytes; the images of a batch may differ in colour type
+    if ((long long)H * ((long long)W * 4 + 1) > 0x3fffffffLL) { c->err = "cvr_decode_png_batch: image too large for the device decoder"; return CVR_ERR_UNSUPPORTED; }
     cvr_timers_begin(c, 0);
-    long long off = 0;
-    for (int i = 0; i < n; i++) { CVR_CUDA(c, cudaMemcpyAsync(c->png_blob + off, png[i], png_bytes[i], cudaMemcpyHostToDevice, c->stream)); off += (long long)png_bytes[i]; }
     PngImg* dImgs = (PngImg*)c->png_tab;
     PngSeg* dSegs = (PngSeg*)(c->png_tab + ((sizeof(PngImg) * (size_t)n + 15) & ~(size_t)15));
     CVR_CUDA(c, cudaMemcpyAsync(dImgs, imgs.data(), sizeof(PngImg) * (size_t)n, cudaMemcpyHostToDevice, c->stream));
     CVR_CUDA(c, cudaMemcpyAsync(dSegs, segs.data(), sizeof(PngSeg) * segs.size(), cudaMemcpyHostToDevice, c->stream));
-    cvr_stage_mark(c, "png_upload");
-    k_png_idat<<<(unsigned)(segs.size() < 4096 ? segs.size() : 4096), 128, 0, c->stream>>>(c->png_blob, dSegs, (int)segs.size(), c->png_z);
-    LAUNCH_CHECK(c);
-    cvr_stage_mark(c, "png_idat");
-    // every image inflates to H scanlines of 1 + W * bpp bytes; the images of a batch may differ in colour type
-    if ((long long)H * ((long long)W * 4 + 1) > 0x3fffffffLL) { c->err = "cvr_decode_png_batch: image too large for the device decoder"; return CVR_ERR_UNSUPPORTED; }
-    k_png_inflate<<<n, 32, 0, c->stream>>>(c->png_z, dImgs, c->png_raw, rawStride, W, H);
-    LAUNCH_CHECK(c);
-    cvr_stage_mark(c, "png_inflate");
-    k_png_unfilter<<<n, 32, 0, c->stream>>>(c->png_raw, rawStride, dImgs, W, H, dOut, dStep, dStride);
-    LAUNCH_CHECK(c);
-    cvr_stage_mark(c, "png_unfilter");
-    CVR_CUDA(c, cudaMemcpyAsync(imgs.data(), dImgs, sizeof(PngImg) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    if (mem_out == CVR_MEM_HOST) {
-        if (image_stride == step * (size_t)H) CVR_CUDA(c, cudaMemcpy2DAsync(bgr, step, dOut, dStep, (size_t)W * 3, (size_t)H * n, cudaMemcpyDeviceToHost, c->stream));
-        else for (int i = 0; i < n; i++) CVR_CUDA(c, cudaMemcpy2DAsync(bgr + (size_t)i * image_stride, step, dOut + (size_t)i * dStride, dStep, (size_t)W * 3, H, cudaMemcpyDeviceToHost, c->stream));
+    // Large calls run as four chunks of files, each on a stream of its own: the upload of a chunk overlaps the decoding of the
+    // chunks before it, and the chunks decode side by side (a stream is latency bound: what counts is how many are in flight).
+    const int NCH = n >= 256 ? 4 : 1;
+    if (NCH > 1) {
+        for (auto& st_ : c->png_stream) if (!st_) CVR_CUDA(c, cudaStreamCreateWithFlags(&st_, cudaStreamNonBlocking));
+        for (auto& ev_ : c->png_ev) if (!ev_) CVR_CUDA(c, cudaEventCreateWithFlags(&ev_, cudaEventDisableTiming));
+        CVR_CUDA(c, cudaEventRecord(c->png_ev[4], c->stream));          // the tables are on their way
     }
+    long long off = 0;
+    for (int k = 0; k < NCH; k++) {
+        const int i0 = (int)((long long)n * k / NCH), i1 = (int)((long long)n * (k + 1) / NCH), nk = i1 - i0;
+        cudaStream_t st = NCH > 1 ? c->png_stream[k] : c->stream;
+        if (NCH > 1) CVR_CUDA(c, cudaStreamWaitEvent(st, c->png_ev[4], 0));
+        for (int i = i0; i < i1; i++) { CVR_CUDA(c, cudaMemcpyAsync(c->png_blob + off, png[i], png_bytes[i], cudaMemcpyHostToDevice, st)); off += (long long)png_bytes[i]; }
+        if (NCH == 1) cvr_stage_mark(c, "png_upload");
+        const int s0 = imgs[(size_t)i0].segFirst, s1 = i1 < n ? imgs[(size_t)i1].segFirst : (int)segs.size(), ns = s1 - s0;
+        if (ns > 0) {
+            k_png_idat<<<(unsigned)(ns < 4096 ? ns : 4096), 128, 0, st>>>(c->png_blob, dSegs + s0, ns, c->png_z);
+            LAUNCH_CHECK(c);
+        }
+        if (NCH == 1) cvr_stage_mark(c, "png_idat");
+        k_png_inflate<<<nk, 32, 0, st>>>(c->png_z, dImgs + i0, c->png_raw + (long long)i0 * rawStride, rawStride, W, H);
+        LAUNCH_CHECK(c);
+        if (NCH == 1) cvr_stage_mark(c, "png_inflate");
+        k_png_unfilter<<<nk, 32, 0, st>>>(c->png_raw + (long long)i0 * rawStride, rawStride, dImgs + i0, W, H, dOut + (size_t)i0 * dStride, dStep, dStride);
+        LAUNCH_CHECK(c);
+        if (NCH == 1) cvr_stage_mark(c, "png_unfilter");
+        if (mem_out == CVR_MEM_HOST) {
+            if (image_stride == step * (size_t)H) CVR_CUDA(c, cudaMemcpy2DAsync(bgr + (size_t)i0 * image_stride, step, dOut + (size_t)i0 * dStride, dStep, (size_t)W * 3, (size_t)H * nk, cudaMemcpyDeviceToHost, st));
+            else for (int i = i0; i < i1; i++) CVR_CUDA(c, cudaMemcpy2DAsync(bgr + (size_t)i * image_stride, step, dOut + (size_t)i * dStride, dStep, (size_t)W * 3, H, cudaMemcpyDeviceToHost, st));
+        }
+        if (NCH > 1) {
+            CVR_CUDA(c, cudaEventRecord(c->png_ev[k], st));
+            CVR_CUDA(c, cudaStreamWaitEvent(c->stream, c->png_ev[k], 0));
+        }
+    }
+    if (NCH > 1) cvr_stage_mark(c, "png_pipeline");
+    CVR_CUDA(c, cudaMemcpyAsync(imgs.data(), dImgs, sizeof(PngImg) * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
     cudaError_t e = cudaStreamSynchronize(c->stream);
     if (e != cudaSuccess) { c->err = std::string("stream sync: ") + cudaGetErrorString(e); return CVR_ERR_CUDA; }
     cvr_timers_end(c, 0);

@@ -110,6 +110,33 @@ def test_every_filter_and_block_type(cvr, oracle, filters, level, strategy, idat
     rec.close()
 
 
+def test_large_call_runs_as_chunks_on_several_streams(cvr, oracle):
+    """From 256 files per call on, the files are uploaded and decoded in four chunks on streams of their own: same frames, in
+    the caller's order, to host and to device memory; a damaged file in the last chunk is still reported."""
+    import torch
+    rec = cvr.Reconstruct3D(W, H, filter_only=True, max_points=16)
+    base = _frames(oracle, 7)
+    gray = cv2.cvtColor(base[0], cv2.COLOR_BGR2GRAY)
+    enc = [cv2.imencode(".png", im, [cv2.IMWRITE_PNG_COMPRESSION, 1 + i % 3])[1].tobytes() for i, im in enumerate(base)]
+    enc.append(cv2.imencode(".png", gray)[1].tobytes())               # a batch that mixes colour types, odd sizes per chunk
+    wants = [cv2.imdecode(np.frombuffer(f, np.uint8), cv2.IMREAD_COLOR) for f in enc]
+    n = 263
+    order = [(5 * i + i // 8) % len(enc) for i in range(n)]
+    files = [enc[k] for k in order]
+    got = rec.DecodePNG(files)
+    for i, k in enumerate(order):
+        assert np.array_equal(got[i], wants[k]), i
+    dev = torch.zeros((n, H, W, 3), dtype=torch.uint8, device="cuda")
+    rec.DecodePNG(files, device_out=dev.data_ptr())
+    assert np.array_equal(dev.cpu().numpy(), got)
+    bad = bytearray(files[-2]); bad[bad.index(b"IDAT") + 4] ^= 0x07       # the zlib header of the stream (chunk CRCs are not checked on the device)
+    with pytest.raises(cvr.CvrError):
+        rec.DecodePNG(files[:-2] + [bytes(bad), files[-1]])
+    got2 = rec.DecodePNG(files[:300 - n] if n > 300 else files[:257])  # the decoder is usable after a failed call
+    assert np.array_equal(got2, got[:len(got2)])
+    rec.close()
+
+
 def test_refuses_what_it_does_not_decode(cvr, oracle):
     rec = cvr.Reconstruct3D(W, H, filter_only=True, max_points=16)
     im = _frames(oracle, 1)[0]
