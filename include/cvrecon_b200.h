@@ -140,7 +140,8 @@ int cvr_get_rectification_maps(cvr_ctx* ctx, int camera, int16_t* map1, uint16_t
  * `step` bytes apart), in host or device memory according to mem_out -- device output can be handed to cvr_submit_batch as a
  * CVR_MEM_DEVICE input without ever touching the host.  png[i] / png_bytes[i] are host pointers / sizes of the encoded files.
  * Every image must have the context's width x height.  Decoded on the device: 8-bit, non-interlaced, colour types gray, RGB and
- * RGBA (alpha dropped); other PNG flavours return CVR_ERR_UNSUPPORTED, a damaged stream CVR_ERR_INVALID_ARG.
+ * RGBA (alpha dropped); other PNG flavours return CVR_ERR_UNSUPPORTED, a damaged stream CVR_ERR_INVALID_ARG (the Adler-32 of
+ * every zlib stream is verified; the CRCs of the PNG chunks are not).
  * A DEFLATE stream is decoded by one thread, so the rate is set by the number of files per call (a B200 keeps 4736 streams in
  * flight): hand over several batches of frames at once where latency allows, and keep the files in pinned host memory. */
 int cvr_decode_png_batch(cvr_ctx* ctx, int n, const uint8_t* const* png, const size_t* png_bytes, int mem_out, uint8_t* bgr, size_t step,

@@ -85,7 +85,7 @@ __host__ __device__ inline int huff_build(Huff& h, const unsigned short* lens, i
 // as the 32 KiB window -- a match reads what this thread wrote earlier.  Nothing of a stream lives in shared memory but its
 // Huffman tables (4.4 KB), so that 32 streams are in flight per SM: the decoder is a chain of dependent instructions per symbol
 // and its throughput is the number of streams in flight.
-// Returns 0, or: 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol / distance, 5 output size differs from
+// Returns 0 (the Adler-32 is checked by k_png_unfilter: 8), or: 1 bad zlib header, 2 bad block type, 3 bad code lengths, 4 bad symbol / distance, 5 output size differs from
 // rawLen, 6 input overrun, 7 stored-block length check.  (Host-callable: tests/png_host_harness.cu runs it on the CPU.)
 __host__ __device__ inline int inflate_all(InflateTab& S, const uint8_t* __restrict__ in, int inLen, uint8_t* out, int rawLen)
 {
@@ -261,7 +261,9 @@ __device__ __forceinline__ int paeth(int a, int b, int c)
 // row for Sub / Average / Paeth (each byte depends on the byte bpp positions to its left); None and Up rows are done by all lanes.
 // The reconstructed bytes are written back over the raw scanline (so the next row finds its "prior" there), then the row is
 // converted to BGR with all lanes.
-__global__ void __launch_bounds__(32) k_png_unfilter(uint8_t* raw, long long rawStride, const PngImg* __restrict__ imgs, int W, int H,
+// The Adler-32 of the inflated bytes is accumulated on the way (a row at a time: A += sum d, B += len A + sum (len - i) d_i) and
+// compared with the four bytes that end the zlib stream, as zlib's inflate does: status 8 on a mismatch.
+__global__ void __launch_bounds__(32) k_png_unfilter(uint8_t* raw, long long rawStride, PngImg* imgs, const uint8_t* __restrict__ z, int W, int H,
                                                      uint8_t* __restrict__ dst, size_t step, size_t imgStride)
 {
     const int lane = threadIdx.x;
@@ -270,9 +272,19 @@ __global__ void __launch_bounds__(32) k_png_unfilter(uint8_t* raw, long long raw
     const int bpp = im.bpp, rowBytes = W * bpp;
     uint8_t* base = raw + (long long)blockIdx.x * rawStride;
     uint8_t* o = dst + (size_t)blockIdx.x * imgStride;
+    unsigned adA = 1, adB = 0;                                         // (lane 0's copy is the one that counts)
     for (int y = 0; y < H; y++) {
         uint8_t* cur = base + (long long)y * (rowBytes + 1) + 1;
         const uint8_t* up = y ? cur - (rowBytes + 1) : nullptr;
+        {
+            const int L = rowBytes + 1;                                // the filter byte belongs to the stream
+            unsigned long long sa = 0, sb = 0;
+            for (int i = lane; i < L; i += 32) { const unsigned d = cur[i - 1]; sa += d; sb += (unsigned long long)(L - i) * d; }
+#pragma unroll
+            for (int o2 = 16; o2 > 0; o2 >>= 1) { sa += __shfl_xor_sync(0xffffffffu, sa, o2); sb += __shfl_xor_sync(0xffffffffu, sb, o2); }
+            adB = (unsigned)((adB + (unsigned long long)(L % 65521) * adA + sb % 65521ull) % 65521ull);
+            adA = (unsigned)((adA + sa) % 65521ull);
+        }
         const int ft = cur[-1];
         if (ft == 0) { /* None */ }
         else if (ft == 2) { if (up) for (int i = lane; i < rowBytes; i += 32) cur[i] = (uint8_t)(cur[i] + up[i]); }
@@ -314,6 +326,11 @@ __global__ void __launch_bounds__(32) k_png_unfilter(uint8_t* raw, long long raw
             orow[3 * x] = bl; orow[3 * x + 1] = g; orow[3 * x + 2] = r;
         }
         __syncwarp();
+    }
+    if (lane == 0) {
+        const uint8_t* t = z + im.zOff + im.zLen - 4;                  // big-endian Adler-32 behind the last block
+        const unsigned want = ((unsigned)t[0] << 24) | ((unsigned)t[1] << 16) | ((unsigned)t[2] << 8) | t[3];
+        if (want != ((adB << 16) | adA)) imgs[blockIdx.x].status = 8;
     }
 }
 
@@ -413,7 +430,7 @@ extern "C" int cvr_decode_png_batch(cvr_ctx* c, int n, const uint8_t* const* png
         k_png_inflate<<<nk, 32, 0, st>>>(c->png_z, dImgs + i0, c->png_raw + (long long)i0 * rawStride, rawStride, W, H);
         LAUNCH_CHECK(c);
         if (NCH == 1) cvr_stage_mark(c, "png_inflate");
-        k_png_unfilter<<<nk, 32, 0, st>>>(c->png_raw + (long long)i0 * rawStride, rawStride, dImgs + i0, W, H, dOut + (size_t)i0 * dStride, dStep, dStride);
+        k_png_unfilter<<<nk, 32, 0, st>>>(c->png_raw + (long long)i0 * rawStride, rawStride, dImgs + i0, c->png_z, W, H, dOut + (size_t)i0 * dStride, dStep, dStride);
         LAUNCH_CHECK(c);
         if (NCH == 1) cvr_stage_mark(c, "png_unfilter");
         if (mem_out == CVR_MEM_HOST) {

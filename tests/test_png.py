@@ -132,6 +132,11 @@ def test_large_call_runs_as_chunks_on_several_streams(cvr, oracle):
     bad = bytearray(files[-2]); bad[bad.index(b"IDAT") + 4] ^= 0x07       # the zlib header of the stream (chunk CRCs are not checked on the device)
     with pytest.raises(cvr.CvrError):
         rec.DecodePNG(files[:-2] + [bytes(bad), files[-1]])
+    # damage inside the compressed data that may well still inflate to the right length: caught by the stream's Adler-32
+    for pos in (100, 1000, 5000):
+        bad = bytearray(files[3]); bad[bad.index(b"IDAT") + 4 + pos] ^= 0x10
+        with pytest.raises(cvr.CvrError):
+            rec.DecodePNG(files[:3] + [bytes(bad)] + files[4:9])
     got2 = rec.DecodePNG(files[:300 - n] if n > 300 else files[:257])  # the decoder is usable after a failed call
     assert np.array_equal(got2, got[:len(got2)])
     rec.close()
