@@ -275,15 +275,22 @@ __device__ __forceinline__ void wta_column2(const unsigned (&s)[NWD], int lane, 
 
 // ------------------------------------------------------------------------------------------------
 // Horizontal path, packed.  Same contract as k_path_h.
+// Frame selection of a launch (bits 8.. of the `storeSel` argument): 0 all frames; 1 only frames whose regime flags are clear
+// when the kernel starts (fast regime: all path costs >= 0 so far, the saturating sums of S do not depend on their order);
+// 2 only frames with a flag set.  MODE_HH uses it to run its second pass in the cheaper order (see launch_paths).
+__device__ __forceinline__ bool path_frame_skipped(int sel, int flag) { return (sel == 1 && flag != 0) || (sel == 2 && flag == 0); }
+
 template <int DPL, bool REVERSE, bool WTA, bool HASPAD, bool NN>
 __global__ void __launch_bounds__(128) k_path_h2(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                 int2* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeS, int* flags)
+                                                 int2* __restrict__ aux, SgbmDev p, int B, int accumulate, int storeSel, int* flags)
 {
     constexpr int NWD = DPL / 2;
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     int lane = threadIdx.x & 31;
     if (warp >= B * p.H) return;
     const int b = warp / p.H, y = warp % p.H;
+    const int storeS = storeSel & 255;
+    if (path_frame_skipped(storeSel >> 8, flags[b])) return;
     const int W1 = p.W1, D = p.D;
     int P2 = p.P2;
     const long long colW = (long long)p.Dp / 2;                             // 32-bit words per column
@@ -881,8 +888,9 @@ __device__ __forceinline__ int group_min(int v)
 #define CVR_H3_WARPS 4          // warps per CTA
 template <int NWD, int LPR, bool REVERSE, bool WTA, bool HASPAD, bool NN>
 __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __restrict__ C, int16_t* __restrict__ S, int2* __restrict__ aux, SgbmDev p, int B,
-                                                               int accumulate, int storeS, int* flags)
+                                                               int accumulate, int storeSel, int* flags)
 {
+    const int storeS = storeSel & 255;
     constexpr int R = 32 / LPR;                                      // rows per warp
     constexpr int PW = (NWD % 4 == 0) ? 4 : 2;                       // words per piece (16- or 8-byte accesses)
     constexpr int NP = NWD / PW;                                     // pieces per column
@@ -895,6 +903,7 @@ __global__ void __launch_bounds__(CVR_H3_WARPS * 32) k_path_h3(const int16_t* __
     const int gw = blockIdx.x * CVR_H3_WARPS + wib;
     if (gw >= B * wpf) return;
     const int b = gw / wpf;
+    if (path_frame_skipped(storeSel >> 8, flags[b])) return;
     const int sub = lane % LPR, rsel = lane / LPR;
     const int y0 = (gw - b * wpf) * R + rsel;
     const bool rowOn = y0 < p.H;                                     // a group past the last row shadows it (same loads, no stores)
@@ -1121,9 +1130,12 @@ __device__ __forceinline__ unsigned group_min2(unsigned v)
 
 template <int NWD, int LPR, bool UP, bool WTA, bool HASPAD, bool NN, int MAXT = 512>
 __global__ void __launch_bounds__(MAXT, 1) k_path_v4(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                    int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
+                                                    int2* __restrict__ aux, SgbmDev p, int CL, int storeSel, int* flags, VState vs)
 {
     (void)raw;
+    const int storeS = storeSel & 255;
+    // (every CTA of the cluster decides alike: a frame's flag only changes after the first cluster.sync of a kernel working on it)
+    if (path_frame_skipped(storeSel >> 8, flags[blockIdx.y])) return;
     constexpr int G = 32 / LPR;                                       // columns per step
     constexpr int PW = (NWD % 4 == 0) ? 4 : 2, NP = NWD / PW, PIECEW = LPR * PW;
     constexpr int dwords = NWD * LPR;                                 // Dp / 2 words per direction per column

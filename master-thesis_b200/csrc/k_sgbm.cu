@@ -1103,7 +1103,7 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     int CL = 1;
     while (CL < 8 && B * CL * 2 <= c->sm_count * 2 && (p.W1 / (CL * 2)) >= NT / 32) CL *= 2;
     const size_t lrN = (size_t)B * 2 * (p.W1 + 2) * 3 * p.Dp;
-    auto launch_v = [&](bool up, bool wta) -> int {
+    auto launch_v = [&](bool up, bool wta, int sel = 0) -> int {
         cudaError_t e;
         if (vc.ok) {
             if (c->path_v_variant == 2) {          // CVR_PATH_KERNELS=v2: per-row cluster barrier instead of point-to-point hand-over
@@ -1111,9 +1111,9 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
                 else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             } else if (useV4) {
-                if (!up) e = launch_cluster(k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else if (wta) e = launch_cluster(k_path_v4<NWDV, LPRV, true, true, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
-                else e = launch_cluster(k_path_v4<NWDV, LPRV, true, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
+                if (!up) e = launch_cluster(k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS | (sel << 8), fl, vc.vs);
+                else if (wta) e = launch_cluster(k_path_v4<NWDV, LPRV, true, true, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS | (sel << 8), fl, vc.vs);
+                else e = launch_cluster(k_path_v4<NWDV, LPRV, true, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS | (sel << 8), fl, vc.vs);
             } else if (vc.NT > 512) {
                 if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
@@ -1178,7 +1178,33 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     rc = launch_v(false, false);
     if (rc) return rc;
     cvr_stage_mark(c, "path_v_down");
-    if (p.mode == CVR_MODE_HH) {
+    static const bool hhExactOrder = getenv("CVR_HH_ORDER") && strcmp(getenv("CVR_HH_ORDER"), "exact") == 0;   // test hook
+    if (p.mode == CVR_MODE_HH && useV4 && vc.ok && !hhExactOrder) {    // (vc.ok: k_path_v4 serves this shape; the fallback kernels know no selection)
+        // MODE_HH, second pass.  OpenCV adds the paths to S in the order <- , up-left, up, up-right and takes the winner after
+        // the last one; with saturating sums that order matters as soon as a path cost is negative.  While none is (the regime
+        // flags of the frame are clear: every reference configuration on natural input), the sums are min(sum, 32767) in any
+        // order, and the cheaper order runs: the three upward paths first, then <- with the winner-take-all in the kernel that
+        // does it best (k_path_h3: 36 us per KITTI frame against 60+ in the vertical kernel, and S is not written again).
+        // Frames whose flags are set at the start of a kernel are skipped by these launches (selection 1) ...
+        rc = launch_v(true, false, 1);
+        if (rc) return rc;
+        cvr_stage_mark(c, "path_v_up");
+        rc = launch_h(true, true, 1, storeS | (1 << 8));
+        if (rc) return rc;
+        cvr_stage_mark(c, "path_h_rev_wta");
+        // ... and every frame with a flag set by now -- from the start, or raised on the way, which voids what the launches
+        // above made of it -- is done again from the first path on in OpenCV's order (selection 2; frames without flags leave
+        // these kernels at once).
+        rc = launch_h(false, false, 0, 1 | (2 << 8));
+        if (rc) return rc;
+        rc = launch_v(false, false, 2);
+        if (rc) return rc;
+        rc = launch_h(true, false, 1, 1 | (2 << 8));
+        if (rc) return rc;
+        rc = launch_v(true, true, 2);
+        if (rc) return rc;
+        cvr_stage_mark(c, "path_exact_order");
+    } else if (p.mode == CVR_MODE_HH) {
         rc = launch_h(true, false, 1, 1);
         if (rc) return rc;
         cvr_stage_mark(c, "path_h_rev");

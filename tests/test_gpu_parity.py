@@ -307,6 +307,39 @@ def test_batch_equals_single_frames(cvr, oracle):
     rec.close()
 
 
+@pytest.mark.parametrize("bs", [3, 9, 19])
+def test_mode_hh_second_pass_order_with_mixed_batches(cvr, oracle, monkeypatch, bs):
+    """MODE_HH: frames whose regime flags stay clear take the cheaper order of the second pass (upward paths, then <- with the
+    winner-take-all), frames with a flag (negative costs: small or wrapping P2, saturating input) are redone in OpenCV's order.
+    A batch that mixes textured, saturating, noise and constant frames must equal the oracle frame by frame in both settings,
+    and with the fallback kernels."""
+    H, W, D, B = 48, 300, 64, 6
+    rng = np.random.default_rng(bs)
+    Ls, Rs = [], []
+    for i in range(B):
+        l, r = oracle.synth_pair(H, W, D, seed=70 + i, color=True)
+        if i == 1:                                               # saturating: black / white stripes
+            l = np.where((np.arange(W) // 7 % 2)[None, :, None] > 0, 255, 0).astype(np.uint8) * np.ones((H, 1, 3), np.uint8); r = np.roll(l, -9, axis=1)
+        elif i == 3:
+            l = rng.integers(0, 256, (H, W, 3), dtype=np.uint8); r = rng.integers(0, 256, (H, W, 3), dtype=np.uint8)
+        elif i == 4:
+            l = np.full((H, W, 3), 90, np.uint8); r = l.copy()
+        Ls.append(np.ascontiguousarray(l)); Rs.append(np.ascontiguousarray(r))
+    Ls, Rs = np.stack(Ls), np.stack(Rs)
+    p = oracle.reference_sgbm_params(block_size=bs, num_disparities=D, mode=1, pre_filter_cap=63)
+    want = [oracle.sgbm(oracle.gray_bgr(Ls[i]), oracle.gray_bgr(Rs[i]), p) for i in range(B)]
+    for env in ({}, {"CVR_HH_ORDER": "exact"}, {"CVR_PATH_KERNELS": "v3"}):
+        for k in ("CVR_HH_ORDER", "CVR_PATH_KERNELS"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        rec = cvr.Reconstruct3D(W, H, config=_cfg(bs, D, cap=63), mode=1, max_batch=B)
+        disp, _ = rec.ProcessFrames(Ls, Rs, want_disp=True, stages=1)
+        for i in range(B):
+            assert np.array_equal(disp[i], want[i]), (env, i)
+        rec.close()
+
+
 def test_pipelined_submit_wait_equals_synchronous(cvr, oracle):
     """cvr_submit_batch / cvr_wait_batch (two batches in flight) return exactly what cvr_process_batch returns."""
     H, W, D, bs, B, NB = 60, 330, 64, 9, 3, 4
