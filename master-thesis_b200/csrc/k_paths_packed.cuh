@@ -390,6 +390,7 @@ struct VState {                // shared-memory carve-up (in 32-bit words) compu
     int colsMax;               // columns per CTA (upper bound)
     int colWords;              // words per column: 3 * (Dp/2 + 4) (k_path_v2 keeps its three minima after the 3 * Dp/2 cost words)
     int inboxWords;            // words per inbox slot: Dp/2 + 4
+    int sel;                   // frame selection of this launch (k_path_v4 only; see path_frame_skipped)
 };
 
 template <int DPL, bool UP, bool WTA, bool HASPAD>
@@ -1130,12 +1131,13 @@ __device__ __forceinline__ unsigned group_min2(unsigned v)
 
 template <int NWD, int LPR, bool UP, bool WTA, bool HASPAD, bool NN, int MAXT = 512>
 __global__ void __launch_bounds__(MAXT, 1) k_path_v4(const int16_t* __restrict__ C, int16_t* __restrict__ S, int16_t* __restrict__ raw,
-                                                    int2* __restrict__ aux, SgbmDev p, int CL, int storeSel, int* flags, VState vs)
+                                                    int2* __restrict__ aux, SgbmDev p, int CL, int storeS, int* flags, VState vs)
 {
     (void)raw;
-    const int storeS = storeSel & 255;
-    // (every CTA of the cluster decides alike: a frame's flag only changes after the first cluster.sync of a kernel working on it)
-    if (path_frame_skipped(storeSel >> 8, flags[blockIdx.y])) return;
+    // (every CTA of the cluster decides alike: a frame's flag only changes after the first cluster.sync of a kernel working on it;
+    // the selection travels in the parameter struct, not in a register: the kernel sits at its 128-register limit)
+    bool exact = flags[blockIdx.y] != 0;
+    if (vs.sel != 0 && (vs.sel == 1) == exact) asm volatile("exit;");   // (a plain `return` here costs the kernel three spilled registers)
     constexpr int G = 32 / LPR;                                       // columns per step
     constexpr int PW = (NWD % 4 == 0) ? 4 : 2, NP = NWD / PW, PIECEW = LPR * PW;
     constexpr int dwords = NWD * LPR;                                 // Dp / 2 words per direction per column
@@ -1167,7 +1169,6 @@ __global__ void __launch_bounds__(MAXT, 1) k_path_v4(const int16_t* __restrict__
     }
     if (threadIdx.x < 2 * NW * 2) mbar_init(smem_u32(bars + threadIdx.x), 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    bool exact = flags[b] != 0;
     PathK k; k.P1p = pk2(p.P1s); k.Qp = pk2(32767 - p.P1s); k.Z = (unsigned)p.D >> 20; CVR_PIN(k.Z);
     CVR_PIN(k.P1p); CVR_PIN(k.Qp); CVR_PIN(P2);
     constexpr size_t colW = (size_t)dwords;

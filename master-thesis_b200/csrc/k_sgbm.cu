@@ -966,7 +966,7 @@ struct VCfg { bool ok; int CL, NT; VState vs; size_t smem; double cost; };   // 
 static size_t vcfg_smem(const SgbmDev& p, int CL, int NT, VState* vs)
 {
     const int NW = NT / 32;
-    vs->colsMax = (p.W1 + CL - 1) / CL + 1; vs->colWords = 3 * (p.Dp / 2 + 4); vs->inboxWords = p.Dp / 2 + 4;
+    vs->colsMax = (p.W1 + CL - 1) / CL + 1; vs->colWords = 3 * (p.Dp / 2 + 4); vs->inboxWords = p.Dp / 2 + 4; vs->sel = 0;
     return 4 * ((size_t)vs->colsMax * vs->colWords + (size_t)2 * NW * 2 * vs->inboxWords) + (size_t)2 * NW * 2 * 8;
 }
 
@@ -979,7 +979,7 @@ template <typename K>
 static VCfg pick_vcfg(cvr_ctx* c, int B, K kernel1024, K kernel512, bool v4 = false, int v4nt = 512)
 {
     const SgbmDev& p = c->sg;
-    VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.cost = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = 0;
+    VCfg r; r.ok = false; r.CL = 1; r.NT = 0; r.smem = 0; r.cost = 0; r.vs.colsMax = r.vs.colWords = r.vs.inboxWords = r.vs.sel = 0;
     const int nts[3] = { 1024, 512, 256 };
     const char* fcl = getenv("CVR_PATHV_CL");
     const int forced = fcl ? atoi(fcl) : 0;
@@ -1094,7 +1094,7 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
     // 1024-thread CTAs -- 64 registers per thread spill, 90 us per frame against 61)
     constexpr int LPRV = DPL <= 4 ? 8 : 16, NWDV = DPL * 16 / LPRV, NTV4 = 512;
     const bool useV4 = packed && c->path_v_variant == 4;
-    const VCfg vc = !packed ? VCfg{ false, 1, 0, { 0, 0, 0 }, 0, 0 }
+    const VCfg vc = !packed ? VCfg{ false, 1, 0, { 0, 0, 0, 0 }, 0, 0 }
                     : useV4 ? pick_vcfg(c, B, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, true, NTV4)
                             : pick_vcfg(c, B, k_path_v3<DPL, false, false, HASPAD, NN, 1024>, k_path_v3<DPL, false, false, HASPAD, NN, 512>);
     int* fl = c->d_sgflags;
@@ -1111,9 +1111,10 @@ static int launch_paths(cvr_ctx* c, int B, int storeS)
                 else if (wta) e = launch_cluster(k_path_v2<DPL, true, true, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else e = launch_cluster(k_path_v2<DPL, true, false, HASPAD>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
             } else if (useV4) {
-                if (!up) e = launch_cluster(k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS | (sel << 8), fl, vc.vs);
-                else if (wta) e = launch_cluster(k_path_v4<NWDV, LPRV, true, true, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS | (sel << 8), fl, vc.vs);
-                else e = launch_cluster(k_path_v4<NWDV, LPRV, true, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS | (sel << 8), fl, vc.vs);
+                VState vsel = vc.vs; vsel.sel = sel;
+                if (!up) e = launch_cluster(k_path_v4<NWDV, LPRV, false, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vsel);
+                else if (wta) e = launch_cluster(k_path_v4<NWDV, LPRV, true, true, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vsel);
+                else e = launch_cluster(k_path_v4<NWDV, LPRV, true, false, HASPAD, NN, NTV4>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vsel);
             } else if (vc.NT > 512) {
                 if (!up) e = launch_cluster(k_path_v3<DPL, false, false, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
                 else if (wta) e = launch_cluster(k_path_v3<DPL, true, true, HASPAD, NN, 1024>, vc.CL, B, vc.NT, vc.smem, c->stream, c->d_volC, c->d_volA, c->d_raw, c->d_aux, p, storeS, fl, vc.vs);
